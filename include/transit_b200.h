@@ -1,0 +1,144 @@
+/* transit_b200.h -- C ABI of the B200 (sm_100a) implementation of Transit's line-by-line
+ * spectrum hot path.  This is the only boundary the host program (C, keeping the
+ * reference's CLI / cfg keys / file formats) crosses: plain pointers and sizes, int
+ * return codes (0 ok, <0 error, text from tb_last_error()), host owns every host
+ * pointer, all device buffers live in the context, no global state, NO CPU FALLBACK:
+ * every entry point fails with TB_ERR_CUDA when no sm_100 device is usable.
+ *
+ * Each entry point names the reference function(s) it replaces (paths into the
+ * exosports/transit tree).  Array layouts at the boundary are the reference's.
+ */
+#ifndef TRANSIT_B200_H
+#define TRANSIT_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct tb_ctx tb_ctx;
+
+enum { TB_OK = 0, TB_ERR_ARG = -1, TB_ERR_CUDA = -2, TB_ERR_STATE = -3, TB_ERR_UNSORTED = -4,
+       TB_ERR_NOMEM = -5, TB_ERR_DOMAIN = -6 };
+enum { TB_GEOM_TRANSIT = 0, TB_GEOM_ECLIPSE = 1 };   /* ray_solution slantpath / eclipsepath */
+
+const char *tb_last_error(void);
+int  tb_version(void);
+
+/* One context = one device (struct transit, transit/src/transit.c:7, made re-entrant). */
+int  tb_create(int device, tb_ctx **out);
+void tb_destroy(tb_ctx *c);
+int  tb_sync(tb_ctx *c);
+
+/* makewnsample / makesample1 (transit/src/makesample.c:27-120,308-400): coarse grid
+ * wns.v[k] = wn_i + k*wn_d, fine grid owns.v[k] = wn_i + k*(wn_d/wnosamp).
+ * nwn/onwn are the counts makesample1 computes (tb_grid_count).                       */
+int64_t tb_grid_count(double wn_i, double wn_f, double wn_d, int osamp);
+int  tb_set_wn_grid(tb_ctx *c, double wn_i, double wn_d, int wnosamp, int64_t nwn, int64_t onwn,
+                    double wn_fct);
+
+/* struct molecules / struct isotopes (transit/include/structures_tr.h:232-251),
+ * filled by getmoldata (readatm.c:625-717), readtli_bin + setimol (readlineinfo.c:87-278). */
+int  tb_set_species(tb_ctx *c, int nmol, const double *mol_mass, const double *mol_radius,
+                    const double *mol_pol, const int *mol_ID, int niso, const double *iso_mass,
+                    const double *iso_ratio, const int *iso_imol);
+
+/* struct line_transition as readdatarng leaves it (readlineinfo.c:416-537): SoA, per
+ * isotope ascending wavelength.  Builds the layer-independent line index on the device
+ * (fine/coarse bins, co-add groups of extinction.c:449-462, bin-sorted order).
+ * TB_ERR_UNSORTED if wavelengths are not non-decreasing within an isotope.            */
+int  tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, const double *gf,
+                     const int16_t *isoid, int64_t n, double wfct, double efct);
+
+/* calcprofiles (opacity.c:218-277) -> getprofile (extinction.c:8-57) -> voigtn
+ * (pu/src/voigt.c:369-483).  dmin..lmax are float as in struct transithint
+ * (structures_tr.h:333); nwidth = timesalpha.                                         */
+int  tb_build_profiles(tb_ctx *c, int nDop, int nLor, float dmin, float dmax, float lmin,
+                       float lmax, float nwidth);
+/* test taps: sizes then data of the table (concatenated float profiles)              */
+int  tb_get_profile_meta(tb_ctx *c, double *aDop, double *aLor, int64_t *psize, int64_t *off,
+                         int64_t *ndata);
+int  tb_get_profile_data(tb_ctx *c, float *data, int64_t ndata);
+
+/* Sampled atmosphere as makeradsample leaves it (makesample.c:408-549):
+ * rad[nrad] (bottom first) * rad_fct = cm; p[nrad]*p_fct = barye; t[nrad]*t_fct = K;
+ * density[nmol][nrad] g/cm3; Z[niso][nrad] partition function at the layer T.         */
+int  tb_set_atmosphere(tb_ctx *c, int nrad, const double *rad, double rad_fct, const double *p,
+                       double p_fct, const double *t, double t_fct, const double *density,
+                       const double *Z);
+
+/* computemolext with permol=0 for every layer (extinction.c:281-529, driven lazily by
+ * tau.c:159-177,238-271 in the reference; here all layers in one batch).             */
+int  tb_extinction_lbl(tb_ctx *c, double ethresh);
+/* generic batch: `ns` states (T, density[nmol], Z[niso]); out[ns][nout][nwn] on the host;
+ * nout = 1 (permol=0) or the number of line-list molecules in first-appearance order. */
+int  tb_molext_states(tb_ctx *c, int ns, const double *T, const double *density /*[ns][nmol]*/,
+                      const double *Z /*[ns][niso]*/, double ethresh, int permol, double *out);
+/* per-line trace of the last tb_molext_states/tb_extinction_lbl state `s`, in the ORIGINAL
+ * line order: status 0 out of range, 1 evaluated, 2 co-added, 3 below threshold; iown/idwn
+ * for 1 and 3, idop for 1.  nsamples[ns] = executed profile updates per state.        */
+int  tb_get_line_trace(tb_ctx *c, int s, int32_t *iown, int32_t *idwn, int32_t *idop,
+                       int8_t *status);
+int  tb_get_sample_counts(tb_ctx *c, int64_t *nsamples, int ns);
+int  tb_get_line_molIDs(tb_ctx *c, int *molID, int *nmolrows);   /* opacity.c:349-361 */
+
+/* calcopacity (opacity.c:281-427): grid[Nlayer][Ntemp][Nmol][Nwave] written to `grid`
+ * (host, file order).  ziso[niso][Ntemp]; q[nmol][nrad] number abundances; press cgs.  */
+int  tb_opacity_build(tb_ctx *c, int Ntemp, const double *temp, const double *ziso,
+                      const double *q, const double *mm, int bymass, double ethresh, double *grid);
+/* readopacity (opacity.c:432-503): make a grid resident in HBM                        */
+int  tb_opacity_load(tb_ctx *c, int64_t Nmol, int64_t Ntemp, int64_t Nlayer, int64_t Nwave,
+                     const int *molID, const double *temp, const double *press,
+                     const double *grid);
+/* interpolmolext for every layer (extinction.c:534-581)                               */
+int  tb_extinction_interp(tb_ctx *c);
+
+/* readcs tables (crosssec.c:9-268) and interpcs/bicubicinterpolate (crosssec.c:271-428) */
+int  tb_cia_clear(tb_ctx *c);
+int  tb_cia_add_table(tb_ctx *c, const double *wn, int nwn, const double *temp, int ntemp,
+                      const double *tab /*[nwn][ntemp]*/, const int *mol, int nspec);
+int  tb_cia_interp(tb_ctx *c);
+
+/* computeextscat / computeextcloud parameters (extinction.c:586-693; struct extscat,
+ * extcloud).  nH/mean_dens [nrad] as tau.c:194-214 builds them (may be NULL -> zeros). */
+int  tb_set_scattering(tb_ctx *c, int flag, double logext);
+int  tb_set_cloud(tb_ctx *c, int flag, double cloudext, double cloudtop, double cloudbot,
+                  double gamma, double Q, double r, double sig, double refwn,
+                  const double *nH, const double *mean_dens);
+
+/* tau (tau.c:59-356) with totaltau1 (slantpath.c:18-108) or eclipsetau (eclipse.c:28-105);
+ * rays h[nh]*hfct (impact parameters, top first; NULL = reversed radii as makeipsample
+ * with raddelt=-1, makesample.c:564-573).                                             */
+int  tb_tau(tb_ctx *c, int geometry, double toomuch, const double *h, int nh, double hfct);
+/* modulation/modulation1 (slantpath.c:274-436): out[nwn]                              */
+int  tb_modulation(tb_ctx *c, double starrad_cm, int transparent, double *out);
+/* eclipse_intens/emergent_intens/flux (eclipse.c:117-287): out[nwn] flux             */
+int  tb_intensity_flux(tb_ctx *c, const double *angles_deg, int nang, double *out);
+
+/* do_transit (transit.c:125-214) in one call: CIA + extinction (LBL if no grid is loaded,
+ * else grid interpolation) + tau + modulation | intensity+flux.  out[nwn].            */
+int  tb_spectrum(tb_ctx *c, int geometry, double toomuch, double ethresh, double starrad_cm,
+                 int transparent, const double *angles_deg, int nang, double *out);
+
+/* test taps in the reference's layouts                                                */
+int  tb_get_extinction(tb_ctx *c, double *e /*[nrad][nwn]*/);
+int  tb_get_cia(tb_ctx *c, double *e_cs /*[nwn][nrad]*/);
+int  tb_get_tau(tb_ctx *c, double *t /*[nwn][nh]*/, int64_t *last /*[nwn]*/);
+int  tb_get_intensity(tb_ctx *c, double *intens /*[nang][nwn]*/);
+int  tb_get_computed(tb_ctx *c, int16_t *computed /*[nrad]*/);   /* tau.c lazy-evaluation set */
+
+/* timing taps: device milliseconds of the last call's dominant kernel (CUDA events on the
+ * context stream) and launch counter                                                 */
+int  tb_get_kernel_ms(tb_ctx *c, const char *name, float *ms);
+/* user-named CUDA-event pair on the context stream (bench.py brackets whole steps with it) */
+int  tb_timer_start(tb_ctx *c, const char *name);
+int  tb_timer_stop(tb_ctx *c, const char *name);
+int64_t tb_launch_count(tb_ctx *c);
+void *tb_stream(tb_ctx *c);          /* cudaStream_t of the context */
+
+/* device micro-benchmarks used for the roofline denominators (FP64 FMA / exp / copy)   */
+int  tb_microbench(tb_ctx *c, double *dfma_tflops, double *dexp_gops, double *copy_gbs);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,231 @@
+// tb_internal.cuh -- shared declarations of the sm_100a implementation (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <math.h>
+#include <map>
+#include <string>
+#include <vector>
+#include "../../include/transit_b200.h"
+
+// ---- physical constants, transit/include/constants_tr.h:19-53 (cgs) -----------------
+#define TB_PI 3.141592653589793
+#define TB_AMU 1.66053886e-24
+#define TB_EC 4.8032068e-10
+#define TB_LS 2.99792458e10
+#define TB_ME 9.1093897e-28
+#define TB_KB 1.380658e-16
+#define TB_H 6.6260755e-27
+#define TB_SIGCTE (TB_PI * TB_EC * TB_EC / TB_LS / TB_LS / TB_ME / TB_AMU)
+#define TB_EXPCTE (TB_H * TB_LS / TB_KB)
+#define TB_NAVOGADRO 6.02214076e23
+#define TB_SQRTLN2 0.83255461115769775635
+#define TB_E0H2 4.911e-23
+#define TB_MICRON 1e-4
+#define TB_AMAGAT 2.68678e19
+#define TB_DEGREES (TB_PI / 180.0)
+
+void tb_set_error(const char *fmt, ...);
+
+#define TB_CUDA(call)                                                                   \
+  do {                                                                                  \
+    cudaError_t e_ = (call);                                                            \
+    if (e_ != cudaSuccess) {                                                            \
+      tb_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+      return TB_ERR_CUDA;                                                               \
+    }                                                                                   \
+  } while (0)
+#define TB_TRY(call)            \
+  do {                          \
+    int r_ = (call);            \
+    if (r_ != TB_OK) return r_; \
+  } while (0)
+#define TB_REQUIRE(cond, code, ...) \
+  do {                              \
+    if (!(cond)) {                  \
+      tb_set_error(__VA_ARGS__);    \
+      return (code);                \
+    }                               \
+  } while (0)
+
+// Device buffer that remembers its size; freed by tb_destroy through tb_ctx::bufs.
+template <typename T>
+struct DevBuf {
+  T *p = nullptr;
+  size_t n = 0;
+  int ensure(size_t want) {
+    if (want <= n && p) return TB_OK;
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+    if (want == 0) return TB_OK;
+    cudaError_t e = cudaMalloc((void **)&p, want * sizeof(T));
+    if (e != cudaSuccess) {
+      tb_set_error("cudaMalloc(%zu bytes) failed: %s", want * sizeof(T), cudaGetErrorString(e));
+      return TB_ERR_NOMEM;
+    }
+    n = want;
+    return TB_OK;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+};
+
+struct ProfEntry {  // one (iso, idop) cell of a state's profile lookup
+  int64_t off;      // offset of the profile in the float table
+  int32_t psize;    // half size in fine samples
+  int32_t pad;
+};
+
+struct CiaTable {
+  int nw = 0, nt = 0, nspec = 0;
+  int mol[2] = {0, 0};
+  std::vector<double> wn, temp, tab;
+  DevBuf<double> d_wn, d_temp, d_tab;
+};
+
+struct KernelTimer {
+  cudaEvent_t a = nullptr, b = nullptr;
+  bool pending = false;
+  float ms = 0.f;
+};
+
+struct tb_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  int64_t launches = 0;
+  std::map<std::string, KernelTimer> timers;
+
+  // ---- wavenumber grids (a2)
+  bool have_grid = false;
+  double wn_i = 0, wn_d = 0, odwn = 0, own_last = 0, wn_fct = 1;
+  int o = 1;
+  int64_t nwn = 0, onwn = 0;
+
+  // ---- species
+  bool have_species = false;
+  int nmol = 0, niso = 0, nrows = 0;  // nrows: line-list molecules (opacity.c:349-361)
+  std::vector<double> mol_mass, mol_radius, mol_pol, iso_mass, iso_ratio;
+  std::vector<int> mol_ID, iso_imol, iso_row, row_molID;
+  DevBuf<double> d_mol_mass, d_mol_radius, d_mol_pol, d_iso_mass, d_iso_ratio;
+  DevBuf<int> d_iso_imol, d_iso_row;
+
+  // ---- line index (a1), see tb_lines.cu
+  bool have_lines = false;
+  int64_t nlines = 0, M = 0, G = 0;
+  double wfct = 1e-4, efct = 1.0;
+  // original order (kept for the trace tap)
+  DevBuf<int32_t> l_iown, l_gpos;
+  DevBuf<uint8_t> l_flag;  // bit0 in range, bit1 head
+  // bin-sorted member lines
+  DevBuf<double> m_wavn, m_elow, m_gf;
+  DevBuf<int16_t> m_iso;
+  DevBuf<uint8_t> m_inr;
+  // bin-sorted groups
+  DevBuf<int32_t> g_start, g_iown, g_idwn, g_orig;
+  DevBuf<int16_t> g_iso;
+  DevBuf<double> g_wavn;       // leader wavenumber, sorted order
+  DevBuf<double> go_wavn;      // leader wavenumber, original group order
+  DevBuf<int32_t> binstart;    // [nrows][nwn+1]
+
+  // ---- Voigt table (a3/a4)
+  bool have_prof = false;
+  int nDop = 0, nLor = 0;
+  float nwidth = 20.f;
+  std::vector<double> aDop, aLor;
+  std::vector<int64_t> psize, poff;
+  int64_t ndata = 0;
+  DevBuf<double> d_aDop, d_aLor;
+  DevBuf<int32_t> d_psize;
+  DevBuf<int64_t> d_poff;
+  DevBuf<float> d_pdata;
+
+  // ---- atmosphere
+  bool have_atm = false;
+  int nrad = 0;
+  double rad_fct = 1, p_fct = 1, t_fct = 1;
+  std::vector<double> rad, p, t, dens, Z;
+  DevBuf<double> d_rad, d_p, d_t, d_dens;
+
+  // ---- state batch scratch (tb_lines.cu)
+  DevBuf<double> s_T, s_dens, s_Z, s_alphal, s_alphad, s_kmax, s_k;
+  DevBuf<int32_t> s_ilor, s_idop0, s_lastq, s_fb, s_psmax;
+  DevBuf<uint8_t> s_pidx;
+  DevBuf<ProfEntry> s_ptab;
+  DevBuf<unsigned long long> s_nsamp;
+  DevBuf<double> s_out;
+  int last_ns = 0, last_permol = 0;
+  bool nsamp_valid = false;
+
+  // ---- results
+  DevBuf<double> d_e, d_ecs, d_tau, d_intens, d_out;
+  DevBuf<int32_t> d_last;
+  DevBuf<int32_t> d_err;
+  bool have_e = false, have_ecs = false, have_tau = false;
+  int nh = 0, geometry = 0, nang = 0;
+  double toomuch = 0;
+  std::vector<double> h_h;
+  double hfct = 1;
+
+  // ---- ray geometry scratch
+  DevBuf<double> r_coef, r_par;
+  DevBuf<int32_t> r_meta;
+
+  // ---- opacity grid (a6-a8)
+  bool have_grid_o = false;
+  int64_t gNmol = 0, gNtemp = 0, gNlayer = 0, gNwave = 0;
+  std::vector<double> gtemp, gpress;
+  std::vector<int> gmolID, gmol_idx;
+  DevBuf<double> d_grid;
+
+  // ---- CIA
+  std::vector<CiaTable *> cia;
+  DevBuf<double> c_f2, c_z2, c_scr, c_densfac;
+
+  // ---- scattering / clouds
+  int sc_flag = 0;
+  double sc_logext = 0;
+  int cl_flag = 0;
+  double cl_ext = 0, cl_top = 0, cl_bot = 0, cl_gamma = 0, cl_Q = 0, cl_r = 0, cl_sig = 0, cl_refwn = 0;
+  std::vector<double> nH, mean_dens;
+  DevBuf<double> d_es_aux;  // [nH | mean_dens]
+
+  // CUB temp storage
+  DevBuf<uint8_t> cub_tmp;
+};
+
+// timing helpers: record CUDA events around the dominant kernels on the context stream
+void tb_timer_begin(tb_ctx *c, const char *name);
+void tb_timer_end(tb_ctx *c, const char *name);
+#define TB_LAUNCHED(c) ((c)->launches++)
+
+// ---- device helpers shared by several translation units ------------------------------
+
+// owns.v[k] exactly as makesample1 fills it (makesample.c:100-104): si + k*osd, as a
+// separate multiply and add (no FMA contraction: bin assignment must be bit-exact).
+__device__ __forceinline__ double tb_fine_wn(double wn_i, double odwn, long long k) {
+  return __dadd_rn(wn_i, __dmul_rn((double)k, odwn));
+}
+
+// binsearchapprox (pu/src/iomisc.c:1088-1108): nearest element by bisection on [lo,hi]
+__device__ __forceinline__ int tb_binsearchapprox(const double *__restrict__ a, double v, int lo,
+                                                  int hi) {
+  while (hi - lo > 1) {
+    int mid = (hi + lo) / 2;
+    if (a[mid] > v) hi = mid; else lo = mid;
+  }
+  if (hi - lo == 1) return (fabs(a[hi] - v) < fabs(a[lo] - v)) ? hi : lo;
+  return lo;
+}
+
+// internal entry points between translation units
+int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const double *Z,
+                  double ethresh, int permol, double *d_out_rows, double *h_out);
+int tb_cia_run(tb_ctx *c);
+int tb_interp_run(tb_ctx *c);

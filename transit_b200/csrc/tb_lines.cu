@@ -1,0 +1,675 @@
+// tb_lines.cu -- the extinction line sum (computemolext, transit/src/extinction.c:281-529)
+// re-designed for the GPU.
+//
+// The reference walks the line list once per layer, sequentially, carrying state from line
+// to line (co-added runs, the per-isotope Doppler index).  Here the layer-INDEPENDENT part of
+// that walk is done once, on the device, when the lines are uploaded:
+//   * fine/coarse bin of every line (extinction.c:445-447,476), bit-exact (no FMA contraction);
+//   * the greedy co-add runs (extinction.c:449-462) as a forward-pointer list whose heads are
+//     found by pointer doubling (deterministic, O(n log n), no sequential pass);
+//   * groups sorted by (molecule row, coarse bin) so that every output bin's contributors are
+//     one contiguous window of the group list.
+// Per batch of layer states (T, densities, partition functions) four kernels run:
+//   k_state_setup -> widths and width indices per isotope (extinction.c:364-395)
+//   k_kmax        -> strength maximum over all in-range lines (extinction.c:399-427)
+//   k_strength    -> group strengths, threshold, Doppler index (extinction.c:439-483)
+//   k_accumulate  -> Voigt-profile gather per output bin, fixed summation order, no atomics
+//                    on floating-point data (extinction.c:486-509)
+#include <cub/cub.cuh>
+#include "tb_internal.cuh"
+
+#define FB_IDOP 255  // "use the isotope's carried Doppler index" marker in s_pidx
+
+// ------------------------------------------------------------------ upload-time index
+
+// wavn, in-range flag, nearest fine bin (extinction.c:431,436,445-447)
+__global__ void k_line_prep(const double *__restrict__ wl, int64_t n, double wfct, double wn_i,
+                            double odwn, double own_last, double *__restrict__ wavn,
+                            int32_t *__restrict__ iown, uint8_t *__restrict__ flag) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double w = __ddiv_rn(1.0, __dmul_rn(wl[i], wfct));
+  wavn[i] = w;
+  bool inr = !((w < wn_i) || (w > own_last));
+  int32_t io = 0;
+  if (inr) {
+    io = (int32_t)__ddiv_rn(__dsub_rn(w, wn_i), odwn);
+    if (fabs(__dsub_rn(w, tb_fine_wn(wn_i, odwn, io + 1))) <
+        fabs(__dsub_rn(w, tb_fine_wn(wn_i, odwn, io))))
+      io++;
+  }
+  iown[i] = io;
+  flag[i] = inr ? 1 : 0;
+}
+
+// next[i]: the line the reference's for-loop visits after i (extinction.c:430,449-462)
+__global__ void k_line_next(const double *__restrict__ wavn, const int16_t *__restrict__ iso,
+                            const int32_t *__restrict__ iown, const uint8_t *__restrict__ flag,
+                            int64_t n, double wn_i, double odwn, int32_t *__restrict__ next) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int64_t j = i + 1;
+  if (flag[i] & 1) {
+    const double center = tb_fine_wn(wn_i, odwn, iown[i]);
+    const int16_t is = iso[i];
+    while (j < n && iso[j] == is && fabs(__dsub_rn(wavn[j], center)) < odwn) j++;
+  }
+  next[i] = (int32_t)j;
+}
+
+// one pointer-doubling round: heads reached so far mark the node 2^k visits ahead
+__global__ void k_mark_round(const int32_t *__restrict__ jump, int32_t *__restrict__ jump_out,
+                             uint8_t *__restrict__ flag, int64_t n) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int32_t j = jump[i];
+  if (j < n) {
+    if (flag[i] & 2) flag[j] |= 2;   // byte store of an idempotent bit: benign race
+    jump_out[i] = jump[j];
+  } else
+    jump_out[i] = j;
+}
+
+__global__ void k_iota(int32_t *__restrict__ a, int64_t n) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) a[i] = (int32_t)i;
+}
+
+__global__ void k_leader_flags(const uint8_t *__restrict__ flag, int64_t n, uint8_t *__restrict__ isl) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) isl[i] = (flag[i] == 3) ? 1 : 0;
+}
+
+// per group (original order): sort key and size; also the sortedness check
+__global__ void k_group_keys(const int32_t *__restrict__ lead, int64_t G, const double *__restrict__ wavn,
+                             const int16_t *__restrict__ iso, const int32_t *__restrict__ next,
+                             const int *__restrict__ iso_row, double wn_i, double dwn, int64_t nwn,
+                             int32_t *__restrict__ key, int32_t *__restrict__ size,
+                             double *__restrict__ go_wavn, int32_t *__restrict__ err) {
+  int64_t g = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (g >= G) return;
+  int32_t L = lead[g];
+  double w = wavn[L];
+  int32_t idwn = (int32_t)__ddiv_rn(__dsub_rn(w, wn_i), dwn);   // extinction.c:476
+  key[g] = iso_row[iso[L]] * (int32_t)nwn + idwn;
+  size[g] = next[L] - L;
+  go_wavn[g] = w;
+  if (g + 1 < G) {
+    int32_t L2 = lead[g + 1];
+    if (iso[L2] == iso[L] && wavn[L2] > w) atomicExch(err, 1);
+  }
+}
+
+// scatter groups and their member lines into bin-sorted order
+__global__ void k_group_fill(const int32_t *__restrict__ order, const int32_t *__restrict__ key_sorted,
+                             const int32_t *__restrict__ gstart, int64_t G,
+                             const int32_t *__restrict__ lead, const int32_t *__restrict__ next,
+                             const double *__restrict__ wavn, const double *__restrict__ elow,
+                             const double *__restrict__ gf, const int16_t *__restrict__ iso,
+                             const int32_t *__restrict__ iown, const uint8_t *__restrict__ flag,
+                             int64_t nwn, int32_t *__restrict__ g_iown, int32_t *__restrict__ g_idwn,
+                             int32_t *__restrict__ g_orig, int16_t *__restrict__ g_iso,
+                             double *__restrict__ g_wavn, double *__restrict__ m_wavn,
+                             double *__restrict__ m_elow, double *__restrict__ m_gf,
+                             int16_t *__restrict__ m_iso, uint8_t *__restrict__ m_inr,
+                             int32_t *__restrict__ l_gpos) {
+  int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (p >= G) return;
+  int32_t g = order[p], L = lead[g], E = next[L], s = gstart[p];
+  g_iown[p] = iown[L];
+  g_idwn[p] = key_sorted[p] % (int32_t)nwn;
+  g_orig[p] = g;
+  g_iso[p] = iso[L];
+  g_wavn[p] = wavn[L];
+  l_gpos[L] = (int32_t)p;
+  for (int32_t l = L; l < E; l++, s++) {
+    m_wavn[s] = wavn[l];
+    m_elow[s] = elow[l];
+    m_gf[s] = gf[l];
+    m_iso[s] = iso[l];
+    m_inr[s] = flag[l] & 1;
+  }
+}
+
+// binstart[row][j] = first sorted group with key >= row*nwn + j
+__global__ void k_binstart(const int32_t *__restrict__ key_sorted, int64_t G, int64_t nkeys,
+                           int32_t *__restrict__ binstart) {
+  int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k > nkeys) return;
+  int64_t lo = 0, hi = G;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (key_sorted[mid] < k) lo = mid + 1; else hi = mid;
+  }
+  binstart[k] = (int32_t)lo;
+}
+
+static inline int nblk(int64_t n, int t) { return (int)((n + t - 1) / t); }
+
+extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, const double *gf,
+                               const int16_t *isoid, int64_t n, double wfct, double efct) {
+  TB_REQUIRE(c->have_grid && c->have_species, TB_ERR_STATE,
+             "tb_set_wn_grid and tb_set_species must precede tb_upload_lines");
+  TB_REQUIRE(n >= 0 && n < 2000000000LL, TB_ERR_ARG, "line count out of range");
+  TB_REQUIRE((int64_t)c->nrows * c->nwn < 2000000000LL, TB_ERR_ARG, "nrows*nwn too large");
+  TB_CUDA(cudaSetDevice(c->device));
+  for (int64_t i = 0; i < n; i++)
+    TB_REQUIRE(isoid[i] >= 0 && isoid[i] < c->niso, TB_ERR_ARG, "isoid[%lld]=%d out of range",
+               (long long)i, (int)isoid[i]);
+  cudaStream_t st = c->stream;
+  c->nlines = n; c->wfct = wfct; c->efct = efct;
+  c->have_lines = false;
+  c->G = c->M = 0;
+  const int64_t nkeys = (int64_t)c->nrows * c->nwn;
+  TB_TRY(c->binstart.ensure(nkeys + 1));
+  if (n == 0) {
+    TB_CUDA(cudaMemsetAsync(c->binstart.p, 0, (nkeys + 1) * sizeof(int32_t), st));
+    c->have_lines = true;
+    return TB_OK;
+  }
+  DevBuf<double> d_wl, d_wavn, d_elow, d_gf;
+  DevBuf<int16_t> d_iso;
+  DevBuf<int32_t> nxt, jA, jB, lead, key, key_s, ord, ord_s, size, size_s, ngrp;
+  DevBuf<uint8_t> isl;
+  TB_TRY(d_wl.ensure(n)); TB_TRY(d_wavn.ensure(n)); TB_TRY(d_elow.ensure(n)); TB_TRY(d_gf.ensure(n));
+  TB_TRY(d_iso.ensure(n)); TB_TRY(nxt.ensure(n)); TB_TRY(jA.ensure(n)); TB_TRY(jB.ensure(n));
+  TB_TRY(isl.ensure(n)); TB_TRY(lead.ensure(n)); TB_TRY(ngrp.ensure(1));
+  TB_TRY(c->l_iown.ensure(n)); TB_TRY(c->l_gpos.ensure(n)); TB_TRY(c->l_flag.ensure(n));
+  TB_CUDA(cudaMemcpyAsync(d_wl.p, wl, n * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(d_elow.p, elow, n * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(d_gf.p, gf, n * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(d_iso.p, isoid, n * sizeof(int16_t), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemsetAsync(c->l_gpos.p, 0xff, n * sizeof(int32_t), st));
+  TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), st));
+
+  const int T = 256;
+  k_line_prep<<<nblk(n, T), T, 0, st>>>(d_wl.p, n, wfct, c->wn_i, c->odwn, c->own_last, d_wavn.p,
+                                        c->l_iown.p, c->l_flag.p);
+  k_line_next<<<nblk(n, T), T, 0, st>>>(d_wavn.p, d_iso.p, c->l_iown.p, c->l_flag.p, n, c->wn_i,
+                                        c->odwn, nxt.p);
+  // heads of the visit list: root = line 0, then pointer doubling
+  uint8_t one = 0;
+  TB_CUDA(cudaMemcpyAsync(&one, c->l_flag.p, 1, cudaMemcpyDeviceToHost, st));
+  TB_CUDA(cudaStreamSynchronize(st));
+  one |= 2;
+  TB_CUDA(cudaMemcpyAsync(c->l_flag.p, &one, 1, cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(jA.p, nxt.p, n * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  int rounds = 1;
+  while ((1LL << rounds) < n + 1) rounds++;
+  int32_t *ja = jA.p, *jb = jB.p;
+  for (int r = 0; r <= rounds; r++) {
+    k_mark_round<<<nblk(n, T), T, 0, st>>>(ja, jb, c->l_flag.p, n);
+    int32_t *t = ja; ja = jb; jb = t;
+  }
+  c->launches += 3 + rounds;
+  // leaders = heads that are in range, in original order
+  k_leader_flags<<<nblk(n, T), T, 0, st>>>(c->l_flag.p, n, isl.p);
+  size_t tmpb = 0;
+  cub::CountingInputIterator<int32_t> cnt(0);
+  cub::DeviceSelect::Flagged(nullptr, tmpb, cnt, isl.p, lead.p, ngrp.p, (int)n, st);
+  TB_TRY(c->cub_tmp.ensure(tmpb));
+  cub::DeviceSelect::Flagged(c->cub_tmp.p, tmpb, cnt, isl.p, lead.p, ngrp.p, (int)n, st);
+  int32_t G32 = 0;
+  TB_CUDA(cudaMemcpyAsync(&G32, ngrp.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  TB_CUDA(cudaStreamSynchronize(st));
+  const int64_t G = G32;
+  c->G = G;
+  if (G == 0) {
+    TB_CUDA(cudaMemsetAsync(c->binstart.p, 0, (nkeys + 1) * sizeof(int32_t), st));
+    c->have_lines = true;
+    return TB_OK;
+  }
+  TB_TRY(key.ensure(G)); TB_TRY(key_s.ensure(G)); TB_TRY(ord.ensure(G)); TB_TRY(ord_s.ensure(G));
+  TB_TRY(size.ensure(G)); TB_TRY(size_s.ensure(G)); TB_TRY(c->go_wavn.ensure(G));
+  k_group_keys<<<nblk(G, T), T, 0, st>>>(lead.p, G, d_wavn.p, d_iso.p, nxt.p, c->d_iso_row.p, c->wn_i,
+                                         c->wn_d, c->nwn, key.p, size.p, c->go_wavn.p, c->d_err.p);
+  // stable sort of (key, original group index): equal keys keep the reference's line order
+  k_iota<<<nblk(G, T), T, 0, st>>>(ord.p, G);
+  int end_bit = 1;
+  while ((1LL << end_bit) < nkeys + 1 && end_bit < 31) end_bit++;
+  tmpb = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmpb, key.p, key_s.p, ord.p, ord_s.p, (int)G, 0, end_bit, st);
+  TB_TRY(c->cub_tmp.ensure(tmpb));
+  cub::DeviceRadixSort::SortPairs(c->cub_tmp.p, tmpb, key.p, key_s.p, ord.p, ord_s.p, (int)G, 0, end_bit, st);
+  // sizes in sorted order -> member offsets
+  // (gather through a tiny transform iterator replacement: reuse SortPairs with sizes as values)
+  tmpb = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmpb, key.p, key_s.p, size.p, size_s.p, (int)G, 0, end_bit, st);
+  TB_TRY(c->cub_tmp.ensure(tmpb));
+  cub::DeviceRadixSort::SortPairs(c->cub_tmp.p, tmpb, key.p, key_s.p, size.p, size_s.p, (int)G, 0, end_bit, st);
+  TB_TRY(c->g_start.ensure(G + 1));
+  tmpb = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, tmpb, size_s.p, c->g_start.p, (int)G, st);
+  TB_TRY(c->cub_tmp.ensure(tmpb));
+  cub::DeviceScan::ExclusiveSum(c->cub_tmp.p, tmpb, size_s.p, c->g_start.p, (int)G, st);
+  int32_t last_start = 0, last_size = 0, err = 0;
+  TB_CUDA(cudaMemcpyAsync(&last_start, c->g_start.p + (G - 1), 4, cudaMemcpyDeviceToHost, st));
+  TB_CUDA(cudaMemcpyAsync(&last_size, size_s.p + (G - 1), 4, cudaMemcpyDeviceToHost, st));
+  TB_CUDA(cudaMemcpyAsync(&err, c->d_err.p, 4, cudaMemcpyDeviceToHost, st));
+  TB_CUDA(cudaStreamSynchronize(st));
+  TB_REQUIRE(err == 0, TB_ERR_UNSORTED,
+             "line list is not sorted by ascending wavelength within an isotope "
+             "(pylineread.py:369-383 guarantees it; the Doppler-index carry relies on it)");
+  const int64_t M = (int64_t)last_start + last_size;
+  c->M = M;
+  TB_CUDA(cudaMemcpyAsync(c->g_start.p + G, &M, 4, cudaMemcpyHostToDevice, st));
+  TB_TRY(c->m_wavn.ensure(M)); TB_TRY(c->m_elow.ensure(M)); TB_TRY(c->m_gf.ensure(M));
+  TB_TRY(c->m_iso.ensure(M)); TB_TRY(c->m_inr.ensure(M));
+  TB_TRY(c->g_iown.ensure(G)); TB_TRY(c->g_idwn.ensure(G)); TB_TRY(c->g_orig.ensure(G));
+  TB_TRY(c->g_iso.ensure(G)); TB_TRY(c->g_wavn.ensure(G));
+  k_group_fill<<<nblk(G, T), T, 0, st>>>(ord_s.p, key_s.p, c->g_start.p, G, lead.p, nxt.p, d_wavn.p,
+                                         d_elow.p, d_gf.p, d_iso.p, c->l_iown.p, c->l_flag.p, c->nwn,
+                                         c->g_iown.p, c->g_idwn.p, c->g_orig.p, c->g_iso.p,
+                                         c->g_wavn.p, c->m_wavn.p, c->m_elow.p, c->m_gf.p, c->m_iso.p,
+                                         c->m_inr.p, c->l_gpos.p);
+  k_binstart<<<nblk(nkeys + 1, T), T, 0, st>>>(key_s.p, G, nkeys, c->binstart.p);
+  c->launches += 8;
+  TB_CUDA(cudaStreamSynchronize(st));
+  d_wl.release(); d_wavn.release(); d_elow.release(); d_gf.release(); d_iso.release();
+  nxt.release(); jA.release(); jB.release(); lead.release(); key.release(); key_s.release();
+  ord.release(); ord_s.release(); size.release(); size_s.release(); ngrp.release(); isl.release();
+  c->have_lines = true;
+  return TB_OK;
+}
+
+// ------------------------------------------------------------------ per-state kernels
+
+// extinction.c:364-395: Lorentz/Doppler widths and their table indices per (state, isotope)
+__global__ void k_state_setup(int ns, int niso, int nmol, const double *__restrict__ T,
+                              const double *__restrict__ dens, const double *__restrict__ mol_mass,
+                              const double *__restrict__ mol_radius, const double *__restrict__ iso_mass,
+                              const int *__restrict__ iso_imol, const double *__restrict__ aDop, int nDop,
+                              const double *__restrict__ aLor, int nLor, double wn0,
+                              double *__restrict__ alphal, double *__restrict__ alphad,
+                              int32_t *__restrict__ ilor, int32_t *__restrict__ idop0,
+                              int32_t *__restrict__ lastq, int32_t *__restrict__ psmax,
+                              double *__restrict__ kmax, int nrows,
+                              unsigned long long *__restrict__ nsamp) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < ns * nrows) kmax[t] = 0.0;
+  if (t < ns) { psmax[t] = 0; nsamp[t] = 0ULL; }   // nsamp already points at this chunk
+  if (t >= ns * niso) return;
+  int s = t / niso, i = t % niso;
+  double temp = T[s];
+  double fdoppler = sqrt(2 * TB_KB * temp / TB_AMU) * TB_SQRTLN2 / TB_LS;
+  double florentz = sqrt(2 * TB_KB * temp / TB_PI / TB_AMU) / (TB_AMU * TB_LS);
+  double al = 0.0;
+  for (int j = 0; j < nmol; j++) {
+    double cs = mol_radius[j] + mol_radius[iso_imol[i]];
+    // separate multiply/add as the reference's x86-64 build has no FMA
+    double term = __dmul_rn(__dmul_rn(__dmul_rn(dens[s * nmol + j] / mol_mass[j], cs), cs),
+                            sqrt(__dadd_rn(1 / iso_mass[i], 1 / mol_mass[j])));
+    al = __dadd_rn(al, term);
+  }
+  al *= florentz;
+  double ad = fdoppler / sqrt(iso_mass[i]);
+  alphal[t] = al;
+  alphad[t] = ad;
+  idop0[t] = tb_binsearchapprox(aDop, __dmul_rn(ad, wn0), 0, nDop);
+  ilor[t] = tb_binsearchapprox(aLor, al, 0, nLor);
+  lastq[t] = -1;
+}
+
+__device__ __forceinline__ void atomicMaxPosDouble(double *addr, double v) {
+  // positive doubles order like their bit patterns: exact, order-independent maximum
+  atomicMax((unsigned long long *)addr, (unsigned long long)__double_as_longlong(v));
+}
+
+// extinction.c:399-427: per-line strength (reference operation order) and its maximum per
+// output row.  One thread per member line, SB states per thread so the 26 B line record is
+// read once per SB states.
+template <int SB>
+__global__ void k_kmax(int64_t M, int ns, int niso, const double *__restrict__ m_wavn,
+                       const double *__restrict__ m_elow, const double *__restrict__ m_gf,
+                       const int16_t *__restrict__ m_iso, const uint8_t *__restrict__ m_inr,
+                       const double *__restrict__ T, const double *__restrict__ Z,
+                       const double *__restrict__ iso_mass, const double *__restrict__ iso_ratio,
+                       const int *__restrict__ iso_row, double efct, int permol, int nrows,
+                       double *__restrict__ kmax) {
+  int64_t l = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int s0 = blockIdx.y * SB;
+  bool act = l < M && m_inr[l];
+  int iso = 0, row = 0;
+  double wavn = 0, a = 0, g = 0, mass = 1;
+  if (act) {
+    iso = m_iso[l];
+    wavn = m_wavn[l];
+    a = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
+    g = __dmul_rn(__dmul_rn(iso_ratio[iso], TB_SIGCTE), m_gf[l]);
+    mass = iso_mass[iso];
+    row = permol ? iso_row[iso] : 0;
+  }
+  // rows differ between lanes, so reduce per row only when a warp is uniform; otherwise go
+  // straight to the (exact) atomic maximum
+#pragma unroll
+  for (int k = 0; k < SB; k++) {
+    int s = s0 + k;
+    if (s >= ns) break;
+    double v = 0.0;
+    if (act) {
+      double temp = T[s];
+      v = g * exp(a / temp) * (1 - exp(__dmul_rn(-TB_EXPCTE, wavn) / temp)) / mass / Z[s * niso + iso];
+    }
+    unsigned mask = __activemask();
+    int row0 = __shfl_sync(mask, row, 0);
+    bool uni = __all_sync(mask, (!act) || row == row0);
+    if (uni) {
+      for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(mask, v, o));
+      if ((threadIdx.x & 31) == 0 && v > 0) atomicMaxPosDouble(&kmax[s * nrows + row0], v);
+    } else if (act && v > 0)
+      atomicMaxPosDouble(&kmax[s * nrows + row], v);
+  }
+}
+
+// extinction.c:439-483 for one (group, state): co-added strength in member order, scaling,
+// threshold, density factor, Doppler-index decision.
+template <int SB>
+__global__ void k_strength(int64_t G, int ns, int niso, const int32_t *__restrict__ g_start,
+                           const int16_t *__restrict__ g_iso, const int32_t *__restrict__ g_orig,
+                           const double *__restrict__ g_wavn, const double *__restrict__ m_wavn,
+                           const double *__restrict__ m_elow, const double *__restrict__ m_gf,
+                           const double *__restrict__ T, const double *__restrict__ Z,
+                           const double *__restrict__ dens, int nmol,
+                           const double *__restrict__ iso_mass, const double *__restrict__ iso_ratio,
+                           const int *__restrict__ iso_imol, const int *__restrict__ iso_row,
+                           const double *__restrict__ alphal, const double *__restrict__ alphad,
+                           const int32_t *__restrict__ ilor, const double *__restrict__ aDop, int nDop,
+                           const int32_t *__restrict__ psize_tab, int nLor, double efct, double ethresh,
+                           int permol, int nrows, const double *__restrict__ kmax,
+                           double *__restrict__ k_out, uint8_t *__restrict__ pidx,
+                           int32_t *__restrict__ lastq, int32_t *__restrict__ psmax) {
+  int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (p >= G) return;
+  int s0 = blockIdx.y * SB;
+  const int iso = g_iso[p];
+  const int b = g_start[p], e = g_start[p + 1];
+  const double wlead = g_wavn[p];
+  const int row = permol ? iso_row[iso] : 0;
+  const double fac0 = __dmul_rn(TB_SIGCTE, iso_ratio[iso]);
+  const double mass = iso_mass[iso];
+  const int imol = iso_imol[iso];
+#pragma unroll 1
+  for (int k = 0; k < SB; k++) {
+    int s = s0 + k;
+    if (s >= ns) break;
+    const double temp = T[s];
+    double acc = 0.0;
+    for (int l = b; l < e; l++) {
+      double a = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
+      double term = __dmul_rn(__dmul_rn(m_gf[l], exp(a / temp)),
+                              (1 - exp(__dmul_rn(-TB_EXPCTE, m_wavn[l]) / temp)));
+      acc = (l == b) ? term : __dadd_rn(acc, term);
+    }
+    double kk = __dmul_rn(acc, fac0 / __dmul_rn(mass, Z[s * niso + iso]));
+    size_t o = (size_t)s * G + p;
+    if (kk < __dmul_rn(ethresh, kmax[s * nrows + row])) {   // extinction.c:467-470
+      k_out[o] = -1.0;
+      pidx[o] = FB_IDOP;
+      continue;
+    }
+    if (!permol) kk = __dmul_rn(kk, dens[s * nmol + imol]);
+    k_out[o] = kk;
+    const double ad = alphad[s * niso + iso], al = alphal[s * niso + iso];
+    int id = FB_IDOP;
+    if (__dmul_rn(ad, wlead) / al >= 1e-1) {                 // extinction.c:480-483
+      id = tb_binsearchapprox(aDop, __dmul_rn(ad, wlead), 0, nDop);
+      atomicMax(&lastq[s * niso + iso], g_orig[p]);
+      atomicMax(&psmax[s], psize_tab[id * nLor + ilor[s * niso + iso]]);
+    }
+    pidx[o] = (uint8_t)id;
+  }
+}
+
+// carried Doppler index per (state, isotope): the index left by the last evaluated line that
+// refreshed it, else the one computed at wn[0] (extinction.c:393,480-483); plus the profile
+// lookup table of the state.
+__global__ void k_fallback(int ns, int niso, const int32_t *__restrict__ lastq,
+                           const int32_t *__restrict__ idop0, const double *__restrict__ go_wavn,
+                           const double *__restrict__ alphad, const int32_t *__restrict__ ilor,
+                           const double *__restrict__ aDop, int nDop, int nLor,
+                           const int32_t *__restrict__ psize_tab, const int64_t *__restrict__ poff_tab,
+                           int32_t *__restrict__ fb, ProfEntry *__restrict__ ptab,
+                           int32_t *__restrict__ psmax) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= ns * niso) return;
+  int s = t / niso;
+  int q = lastq[t];
+  int id = (q < 0) ? idop0[t] : tb_binsearchapprox(aDop, __dmul_rn(alphad[t], go_wavn[q]), 0, nDop);
+  fb[t] = id;
+  const int il = ilor[t];
+  atomicMax(&psmax[s], psize_tab[id * nLor + il]);
+  for (int d = 0; d < nDop; d++) {
+    ProfEntry pe;
+    pe.off = poff_tab[d * nLor + il];
+    pe.psize = psize_tab[d * nLor + il];
+    pe.pad = 0;
+    ptab[(size_t)t * nDop + d] = pe;
+  }
+}
+
+// extinction.c:486-509 turned inside out: one thread per (output bin, state) gathers every
+// contributing group from the bin-sorted window [j-W, j+W] of each molecule row, in sorted
+// order: a fixed summation order, no floating-point atomics.
+//   contributes  <=>  0 <= o*j - (iown - psize) <= 2*psize   (same test as the reference loop)
+__global__ void k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int nDop, int o, int nrows,
+                             int permol, const int32_t *__restrict__ binstart,
+                             const int32_t *__restrict__ g_iown, const int16_t *__restrict__ g_iso,
+                             const double *__restrict__ k_in, const uint8_t *__restrict__ pidx,
+                             const int32_t *__restrict__ fb, const ProfEntry *__restrict__ ptab,
+                             const int32_t *__restrict__ psmax, const float *__restrict__ pdata,
+                             double *__restrict__ out, unsigned long long *__restrict__ nsamp) {
+  int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int s = blockIdx.y;
+  unsigned long long cnt = 0;
+  if (j < nwn) {
+    const int W = psmax[s] / o + 2;
+    int64_t jlo = j - W < 0 ? 0 : j - W;
+    int64_t jhi = j + W + 1 > nwn ? nwn : j + W + 1;
+    const double *ks = k_in + (size_t)s * G;
+    const uint8_t *ps = pidx + (size_t)s * G;
+    const int64_t oj = (int64_t)o * j;
+    double acc = 0.0;
+    for (int row = 0; row < nrows; row++) {
+      const int32_t *bs = binstart + (size_t)row * nwn;
+      int p0 = bs[jlo], p1 = bs[jhi];
+      for (int p = p0; p < p1; p++) {
+        double k = ks[p];
+        if (k < 0) continue;
+        int iso = g_iso[p];
+        int id = ps[p];
+        if (id == FB_IDOP) id = fb[s * niso + iso];
+        ProfEntry pe = ptab[((size_t)s * niso + iso) * nDop + id];
+        int64_t idx = oj - g_iown[p] + pe.psize;
+        if (idx >= 0 && idx <= 2 * (int64_t)pe.psize) {
+          acc = fma(k, (double)pdata[pe.off + idx], acc);
+          cnt++;
+        }
+      }
+      if (permol) {
+        out[((size_t)s * nrows + row) * nwn + j] = acc;
+        acc = 0.0;
+      }
+    }
+    if (!permol) out[(size_t)s * nwn + j] = acc;
+  }
+  // sample counter (the benchmark's unit of work): integer atomics only
+  for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
+  if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(&nsamp[s], cnt);
+}
+
+// ------------------------------------------------------------------ host driver
+
+int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const double *Z,
+                  double ethresh, int permol, double *d_out_rows, double *h_out) {
+  TB_REQUIRE(c->have_lines && c->have_prof, TB_ERR_STATE,
+             "tb_upload_lines and tb_build_profiles must precede the line sum");
+  TB_REQUIRE(c->nDop < FB_IDOP, TB_ERR_ARG, "nDop must be < %d", FB_IDOP);
+  TB_CUDA(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const int niso = c->niso, nmol = c->nmol, nrows = c->nrows;
+  const int nout = permol ? nrows : 1;
+  const int64_t G = c->G, M = c->M, nwn = c->nwn;
+  c->last_ns = ns;
+  c->last_permol = permol;
+  // chunk the states so the per-(state, group) scratch stays below ~12 GB
+  int chunk = ns;
+  const size_t per_state = (size_t)G * 9 + (size_t)nout * nwn * 8 + 64;
+  const size_t budget = (size_t)12 << 30;
+  if (per_state * chunk > budget) chunk = (int)(budget / per_state);
+  if (chunk < 1) chunk = 1;
+  TB_TRY(c->s_T.ensure(chunk)); TB_TRY(c->s_dens.ensure((size_t)chunk * nmol));
+  TB_TRY(c->s_Z.ensure((size_t)chunk * (niso ? niso : 1)));
+  TB_TRY(c->s_alphal.ensure((size_t)chunk * niso + 1)); TB_TRY(c->s_alphad.ensure((size_t)chunk * niso + 1));
+  TB_TRY(c->s_ilor.ensure((size_t)chunk * niso + 1)); TB_TRY(c->s_idop0.ensure((size_t)chunk * niso + 1));
+  TB_TRY(c->s_lastq.ensure((size_t)chunk * niso + 1)); TB_TRY(c->s_fb.ensure((size_t)chunk * niso + 1));
+  TB_TRY(c->s_psmax.ensure(chunk)); TB_TRY(c->s_kmax.ensure((size_t)chunk * nrows + 1));
+  TB_TRY(c->s_nsamp.ensure(ns));
+  TB_TRY(c->s_ptab.ensure((size_t)chunk * niso * c->nDop + 1));
+  TB_TRY(c->s_k.ensure((size_t)chunk * G + 1)); TB_TRY(c->s_pidx.ensure((size_t)chunk * G + 1));
+  double *d_out = d_out_rows;
+  if (!d_out) {
+    TB_TRY(c->s_out.ensure((size_t)chunk * nout * nwn));
+    d_out = c->s_out.p;
+  }
+  const int Tn = 256;
+  constexpr int SB = 4;
+  tb_timer_begin(c, "molext");
+  for (int s0 = 0; s0 < ns; s0 += chunk) {
+    const int cs = (ns - s0 < chunk) ? ns - s0 : chunk;
+    TB_CUDA(cudaMemcpyAsync(c->s_T.p, T + s0, cs * sizeof(double), cudaMemcpyHostToDevice, st));
+    TB_CUDA(cudaMemcpyAsync(c->s_dens.p, dens + (size_t)s0 * nmol, (size_t)cs * nmol * sizeof(double),
+                            cudaMemcpyHostToDevice, st));
+    if (niso)
+      TB_CUDA(cudaMemcpyAsync(c->s_Z.p, Z + (size_t)s0 * niso, (size_t)cs * niso * sizeof(double),
+                              cudaMemcpyHostToDevice, st));
+    double *dst = d_out_rows ? d_out + (size_t)s0 * nout * nwn : d_out;
+    int nset = cs * (niso > nrows ? niso : nrows);
+    if (nset < cs) nset = cs;
+    k_state_setup<<<nblk(nset, 128), 128, 0, st>>>(
+        cs, niso, nmol, c->s_T.p, c->s_dens.p, c->d_mol_mass.p, c->d_mol_radius.p, c->d_iso_mass.p,
+        c->d_iso_imol.p, c->d_aDop.p, c->nDop, c->d_aLor.p, c->nLor, c->wn_i, c->s_alphal.p,
+        c->s_alphad.p, c->s_ilor.p, c->s_idop0.p, c->s_lastq.p, c->s_psmax.p, c->s_kmax.p, nrows,
+        c->s_nsamp.p + s0);
+    TB_LAUNCHED(c);
+    if (G > 0) {
+      dim3 g2(nblk(M, Tn), (cs + SB - 1) / SB);
+      tb_timer_begin(c, "kmax");
+      k_kmax<SB><<<g2, Tn, 0, st>>>(M, cs, niso, c->m_wavn.p, c->m_elow.p, c->m_gf.p, c->m_iso.p,
+                                    c->m_inr.p, c->s_T.p, c->s_Z.p, c->d_iso_mass.p, c->d_iso_ratio.p,
+                                    c->d_iso_row.p, c->efct, permol, nrows, c->s_kmax.p);
+      tb_timer_end(c, "kmax");
+      dim3 g3(nblk(G, Tn), (cs + SB - 1) / SB);
+      tb_timer_begin(c, "strength");
+      k_strength<SB><<<g3, Tn, 0, st>>>(
+          G, cs, niso, c->g_start.p, c->g_iso.p, c->g_orig.p, c->g_wavn.p, c->m_wavn.p, c->m_elow.p,
+          c->m_gf.p, c->s_T.p, c->s_Z.p, c->s_dens.p, nmol, c->d_iso_mass.p, c->d_iso_ratio.p,
+          c->d_iso_imol.p, c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
+          c->nDop, c->d_psize.p, c->nLor, c->efct, ethresh, permol, nrows, c->s_kmax.p, c->s_k.p,
+          c->s_pidx.p, c->s_lastq.p, c->s_psmax.p);
+      tb_timer_end(c, "strength");
+      k_fallback<<<nblk(cs * niso, 128), 128, 0, st>>>(
+          cs, niso, c->s_lastq.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
+          c->nDop, c->nLor, c->d_psize.p, c->d_poff.p, c->s_fb.p, c->s_ptab.p, c->s_psmax.p);
+      c->launches += 3;
+    }
+    dim3 g4(nblk(nwn, 128), cs);
+    tb_timer_begin(c, "accumulate");
+    k_accumulate<<<g4, 128, 0, st>>>(nwn, G, cs, niso, c->nDop, c->o, nrows, permol, c->binstart.p,
+                                     c->g_iown.p, c->g_iso.p, c->s_k.p, c->s_pidx.p, c->s_fb.p,
+                                     c->s_ptab.p, c->s_psmax.p, c->d_pdata.p, dst, c->s_nsamp.p + s0);
+    tb_timer_end(c, "accumulate");
+    TB_LAUNCHED(c);
+    TB_CUDA(cudaGetLastError());
+    if (h_out)
+      TB_CUDA(cudaMemcpyAsync(h_out + (size_t)s0 * nout * nwn, dst, (size_t)cs * nout * nwn * sizeof(double),
+                              cudaMemcpyDeviceToHost, st));
+    // the state scratch is reused by the next chunk: the host arrays staged above must be consumed
+    if (s0 + cs < ns) TB_CUDA(cudaStreamSynchronize(st));
+  }
+  tb_timer_end(c, "molext");
+  if (h_out) TB_CUDA(cudaStreamSynchronize(st));
+  c->nsamp_valid = false;
+  return TB_OK;
+}
+
+extern "C" int tb_molext_states(tb_ctx *c, int ns, const double *T, const double *density,
+                                const double *Z, double ethresh, int permol, double *out) {
+  TB_REQUIRE(ns > 0 && T && density && out, TB_ERR_ARG, "tb_molext_states: bad arguments");
+  return tb_states_run(c, ns, T, density, Z, ethresh, permol, nullptr, out);
+}
+
+extern "C" int tb_extinction_lbl(tb_ctx *c, double ethresh) {
+  TB_REQUIRE(c->have_atm, TB_ERR_STATE, "tb_set_atmosphere not called");
+  const int nrad = c->nrad, nmol = c->nmol, niso = c->niso;
+  std::vector<double> T(nrad), dens((size_t)nrad * nmol), Z((size_t)nrad * (niso ? niso : 1));
+  for (int r = 0; r < nrad; r++) {
+    T[r] = c->t[r] * c->t_fct;                               // tau.c:169,259
+    for (int j = 0; j < nmol; j++) dens[(size_t)r * nmol + j] = c->dens[(size_t)j * nrad + r];
+    for (int i = 0; i < niso; i++) Z[(size_t)r * niso + i] = c->Z[(size_t)i * nrad + r];
+  }
+  TB_TRY(c->d_e.ensure((size_t)nrad * c->nwn));
+  TB_TRY(tb_states_run(c, nrad, T.data(), dens.data(), Z.data(), ethresh, 0, c->d_e.p, nullptr));
+  c->have_e = true;
+  return TB_OK;
+}
+
+extern "C" int tb_get_sample_counts(tb_ctx *c, int64_t *nsamples, int ns) {
+  TB_REQUIRE(ns <= c->last_ns, TB_ERR_ARG, "only %d states in the last batch", c->last_ns);
+  TB_CUDA(cudaSetDevice(c->device));
+  std::vector<unsigned long long> h(ns);
+  TB_CUDA(cudaMemcpyAsync(h.data(), c->s_nsamp.p, ns * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  TB_CUDA(cudaStreamSynchronize(c->stream));
+  for (int i = 0; i < ns; i++) nsamples[i] = (int64_t)h[i];
+  return TB_OK;
+}
+
+// per-line trace in original order, for bit-exact index parity against the oracle
+__global__ void k_trace(int64_t n, int64_t G, int s_local, int niso, const uint8_t *__restrict__ flag,
+                        const int32_t *__restrict__ l_iown, const int32_t *__restrict__ l_gpos,
+                        const int32_t *__restrict__ g_idwn, const int16_t *__restrict__ g_iso,
+                        const double *__restrict__ k_in, const uint8_t *__restrict__ pidx,
+                        const int32_t *__restrict__ fb, int32_t *__restrict__ iown,
+                        int32_t *__restrict__ idwn, int32_t *__restrict__ idop, int8_t *__restrict__ status) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint8_t f = flag[i];
+  int8_t st = 0;
+  int32_t io = 0, id = 0, dp = -1;
+  if (f == 3) {
+    int32_t p = l_gpos[i];
+    io = l_iown[i];
+    id = g_idwn[p];
+    double k = k_in[(size_t)s_local * G + p];
+    if (k < 0) st = 3;
+    else {
+      st = 1;
+      dp = pidx[(size_t)s_local * G + p];
+      if (dp == FB_IDOP) dp = fb[s_local * niso + g_iso[p]];
+    }
+  } else if (!(f & 2)) st = 2;     // visited only as a co-added member
+  iown[i] = io; idwn[i] = id; idop[i] = dp; status[i] = st;
+}
+
+extern "C" int tb_get_line_trace(tb_ctx *c, int s, int32_t *iown, int32_t *idwn, int32_t *idop,
+                                 int8_t *status) {
+  TB_REQUIRE(c->have_lines && c->last_ns > 0, TB_ERR_STATE, "no line-sum batch has run");
+  TB_REQUIRE(s >= 0 && s < c->last_ns, TB_ERR_ARG, "state %d out of range", s);
+  TB_REQUIRE((size_t)c->last_ns * c->G + 1 <= c->s_k.n, TB_ERR_STATE,
+             "trace is only available when the batch ran as a single chunk");
+  TB_CUDA(cudaSetDevice(c->device));
+  const int64_t n = c->nlines;
+  if (n == 0) return TB_OK;
+  DevBuf<int32_t> a, b, d;
+  DevBuf<int8_t> e;
+  TB_TRY(a.ensure(n)); TB_TRY(b.ensure(n)); TB_TRY(d.ensure(n)); TB_TRY(e.ensure(n));
+  k_trace<<<nblk(n, 256), 256, 0, c->stream>>>(n, c->G, s, c->niso, c->l_flag.p, c->l_iown.p,
+                                               c->l_gpos.p, c->g_idwn.p, c->g_iso.p, c->s_k.p,
+                                               c->s_pidx.p, c->s_fb.p, a.p, b.p, d.p, e.p);
+  TB_CUDA(cudaMemcpyAsync(iown, a.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+  TB_CUDA(cudaMemcpyAsync(idwn, b.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+  TB_CUDA(cudaMemcpyAsync(idop, d.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+  TB_CUDA(cudaMemcpyAsync(status, e.p, n, cudaMemcpyDeviceToHost, c->stream));
+  TB_CUDA(cudaStreamSynchronize(c->stream));
+  a.release(); b.release(); d.release(); e.release();
+  return TB_OK;
+}

@@ -1,0 +1,131 @@
+// tb_opacity.cu -- the opacity grid: calcopacity (transit/src/opacity.c:281-427), readopacity
+// (opacity.c:432-503) and interpolmolext (extinction.c:534-581).  The grid keeps the file's
+// order o[layer][temp][molecule][wavenumber] in HBM (wavenumber innermost = coalesced), and
+// replaces the reference's SysV shared-memory copies (opacity.c:507-630) by residency.
+#include "tb_internal.cuh"
+
+static inline int nblk(int64_t n, int t) { return (int)((n + t - 1) / t); }
+
+extern "C" int tb_opacity_load(tb_ctx *c, int64_t Nmol, int64_t Ntemp, int64_t Nlayer, int64_t Nwave,
+                               const int *molID, const double *temp, const double *press,
+                               const double *grid) {
+  TB_REQUIRE(c->have_grid && c->have_species, TB_ERR_STATE, "grid and species must be set before tb_opacity_load");
+  TB_REQUIRE(Nmol >= 1 && Ntemp >= 2 && Nlayer >= 1 && Nwave == c->nwn, TB_ERR_ARG,
+             "opacity grid shape (%lld mol, %lld T, %lld layers, %lld wn) does not fit the problem (nwn=%lld)",
+             (long long)Nmol, (long long)Ntemp, (long long)Nlayer, (long long)Nwave, (long long)c->nwn);
+  TB_CUDA(cudaSetDevice(c->device));
+  c->gNmol = Nmol; c->gNtemp = Ntemp; c->gNlayer = Nlayer; c->gNwave = Nwave;
+  c->gtemp.assign(temp, temp + Ntemp);
+  c->gtemp.push_back(INFINITY);   // binsearchapprox(gtemp, T, 0, Ntemp) looks one past the end
+  c->gpress.assign(press, press + Nlayer);
+  c->gmolID.assign(molID, molID + Nmol);
+  c->gmol_idx.assign(Nmol, -1);
+  for (int m = 0; m < Nmol; m++) {       // valueinarray(mol->ID, gmol[m], nmol), extinction.c:575
+    for (int k = 0; k < c->nmol; k++)
+      if (c->mol_ID[k] == molID[m]) { c->gmol_idx[m] = k; break; }
+    TB_REQUIRE(c->gmol_idx[m] >= 0, TB_ERR_ARG, "opacity-grid molecule ID %d is not in the atmosphere", molID[m]);
+  }
+  const size_t n = (size_t)Nlayer * Ntemp * Nmol * Nwave;
+  TB_TRY(c->d_grid.ensure(n));
+  if (grid) {
+    TB_CUDA(cudaMemcpyAsync(c->d_grid.p, grid, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    TB_CUDA(cudaStreamSynchronize(c->stream));
+  }
+  c->have_grid_o = true;
+  return TB_OK;
+}
+
+struct InterpLayer {   // per layer: lower temperature index and the two weights' ingredients
+  int it;
+  double t, tlo, thi;
+};
+
+// extinction.c:568-578: e[r][w] = sum_m rho_m[r] * (o_lo*(T+ - T) + o_hi*(T - T-))/(T+ - T-)
+__global__ void k_grid_interp(int64_t nwn, int nrad, int Ntemp, int Nmol, const double *__restrict__ grid,
+                              const InterpLayer *__restrict__ L, const double *__restrict__ rho /*[Nmol][nrad]*/,
+                              double *__restrict__ e) {
+  int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int r = blockIdx.y;
+  if (w >= nwn) return;
+  const InterpLayer l = L[r];
+  const double *lo = grid + (((size_t)r * Ntemp + l.it) * Nmol) * nwn + w;
+  const double *hi = lo + (size_t)Nmol * nwn;
+  double acc = 0.0;
+  for (int m = 0; m < Nmol; m++) {
+    double ext = (lo[(size_t)m * nwn] * (l.thi - l.t) + hi[(size_t)m * nwn] * (l.t - l.tlo)) / (l.thi - l.tlo);
+    acc += rho[m * nrad + r] * ext;
+  }
+  e[(size_t)r * nwn + w] = acc;
+}
+
+int tb_interp_run(tb_ctx *c) {
+  TB_REQUIRE(c->have_grid_o && c->have_atm, TB_ERR_STATE, "tb_opacity_load and tb_set_atmosphere must precede the interpolation");
+  TB_REQUIRE(c->gNlayer == c->nrad, TB_ERR_ARG, "opacity grid has %lld layers, atmosphere %d", (long long)c->gNlayer, c->nrad);
+  TB_CUDA(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const int nrad = c->nrad, Nt = (int)c->gNtemp, Nm = (int)c->gNmol;
+  std::vector<InterpLayer> L(nrad);
+  std::vector<double> rho((size_t)Nm * nrad);
+  for (int r = 0; r < nrad; r++) {
+    const double T = c->t[r] * c->t_fct;
+    // binsearchapprox(gtemp, temp, 0, Ntemp) then step down (extinction.c:562-564)
+    int lo = 0, hi = Nt;
+    while (hi - lo > 1) {
+      int mid = (hi + lo) / 2;
+      if (c->gtemp[mid] > T) hi = mid; else lo = mid;
+    }
+    int it = (fabs(c->gtemp[hi] - T) < fabs(c->gtemp[lo] - T)) ? hi : lo;
+    if (T < c->gtemp[it]) it--;
+    TB_REQUIRE(it >= 0 && it + 1 < Nt, TB_ERR_DOMAIN,
+               "layer %d temperature %.2f K is outside the opacity grid [%.1f, %.1f] K", r, T, c->gtemp[0], c->gtemp[Nt - 1]);
+    L[r].it = it; L[r].t = T; L[r].tlo = c->gtemp[it]; L[r].thi = c->gtemp[it + 1];
+    for (int m = 0; m < Nm; m++) rho[(size_t)m * nrad + r] = c->dens[(size_t)c->gmol_idx[m] * nrad + r];
+  }
+  DevBuf<InterpLayer> dL;
+  DevBuf<double> drho;
+  TB_TRY(dL.ensure(nrad)); TB_TRY(drho.ensure(rho.size()));
+  TB_TRY(c->d_e.ensure((size_t)nrad * c->nwn));
+  TB_CUDA(cudaMemcpyAsync(dL.p, L.data(), nrad * sizeof(InterpLayer), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(drho.p, rho.data(), rho.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+  dim3 g(nblk(c->nwn, 256), nrad);
+  tb_timer_begin(c, "interp");
+  k_grid_interp<<<g, 256, 0, st>>>(c->nwn, nrad, Nt, Nm, c->d_grid.p, dL.p, drho.p, c->d_e.p);
+  tb_timer_end(c, "interp");
+  TB_LAUNCHED(c);
+  TB_CUDA(cudaGetLastError());
+  TB_CUDA(cudaStreamSynchronize(st));
+  dL.release(); drho.release();
+  c->have_e = true;
+  return TB_OK;
+}
+
+extern "C" int tb_extinction_interp(tb_ctx *c) { return tb_interp_run(c); }
+
+// calcopacity (opacity.c:387-403): every (layer, temperature) pair is one state of the line
+// sum with permol=1; densities follow stateeqnford (transit.h:58-69).
+extern "C" int tb_opacity_build(tb_ctx *c, int Ntemp, const double *temp, const double *ziso,
+                                const double *q, const double *mm, int bymass, double ethresh, double *grid) {
+  TB_REQUIRE(c->have_atm && c->have_lines && c->have_prof, TB_ERR_STATE,
+             "atmosphere, lines and profiles must be set before tb_opacity_build");
+  TB_REQUIRE(Ntemp >= 1 && temp && ziso && q && grid, TB_ERR_ARG, "tb_opacity_build: bad arguments");
+  const int nrad = c->nrad, nmol = c->nmol, niso = c->niso;
+  const int ns = nrad * Ntemp;
+  std::vector<double> T(ns), dens((size_t)ns * nmol), Z((size_t)ns * (niso ? niso : 1));
+  for (int r = 0; r < nrad; r++)
+    for (int t = 0; t < Ntemp; t++) {
+      const int s = r * Ntemp + t;
+      T[s] = temp[t];
+      const double press = c->p[r] * c->p_fct;            // opacity.c:345
+      for (int j = 0; j < nmol; j++) {
+        const double rho = TB_AMU * q[(size_t)j * nrad + r] * press / TB_KB / temp[t];
+        dens[(size_t)s * nmol + j] = bymass ? rho * mm[r] : rho * c->mol_mass[j];
+      }
+      for (int i = 0; i < niso; i++) Z[(size_t)s * niso + i] = ziso[(size_t)i * Ntemp + t];
+    }
+  TB_TRY(tb_states_run(c, ns, T.data(), dens.data(), Z.data(), ethresh, 1, nullptr, grid));
+  // keep the freshly built grid resident for interpolation, like a second run would read it
+  std::vector<double> press(nrad);
+  for (int r = 0; r < nrad; r++) press[r] = c->p[r] * c->p_fct;
+  TB_TRY(tb_opacity_load(c, c->nrows, Ntemp, nrad, c->nwn, c->row_molID.data(), temp, press.data(), grid));
+  return TB_OK;
+}

@@ -1,0 +1,574 @@
+// tb_radiative.cu -- CIA interpolation (crosssec.c:271-428), optical depth (tau.c:59-356 with
+// slantpath.c:18-108 / eclipse.c:28-105), modulation (slantpath.c:274-436) and emergent
+// intensity + flux (eclipse.c:117-287).
+//
+// Device layouts are wavenumber-innermost ([layer][wn], [ray][wn]) so that a warp of
+// consecutive wavenumbers reads and writes coalesced; the taps in tb_context.cu transpose
+// to the reference's [wn][layer] where it differs.  Ray geometry (the Simpson weights of
+// numerical.c:390-525) depends only on the radii, so it is computed once per call by one
+// thread per ray and shared by every wavenumber.
+#include "tb_internal.cuh"
+
+static inline int nblk(int64_t n, int t) { return (int)((n + t - 1) / t); }
+
+// =============================================================== natural cubic splines
+
+// tri + spline_init (pu/src/spline.c:12-48,186-206); scratch u,v of length n
+__device__ void tb_spline_init(double *z, const double *x, const double *y, int n, double *u, double *v) {
+  if (n > 2) {
+    double h0 = x[1] - x[0], h1 = x[2] - x[1];
+    double b0 = (y[1] - y[0]) / h0, b1 = (y[2] - y[1]) / h1;
+    u[1] = 2 * (h1 + h0);
+    v[1] = 6 * (b1 - b0);
+    for (int i = 2; i < n - 1; i++) {
+      double hi = x[i + 1] - x[i], hm = x[i] - x[i - 1];
+      double bi = (y[i + 1] - y[i]) / hi, bm = (y[i] - y[i - 1]) / hm;
+      u[i] = 2 * (hi + hm) - hm * hm / u[i - 1];
+      v[i] = 6 * (bi - bm) - v[i - 1] * hm / u[i - 1];
+    }
+  }
+  z[0] = z[n - 1] = 0;
+  for (int i = n - 2; i > 0; i--) z[i] = (v[i] - (x[i + 1] - x[i]) * z[i + 1]) / u[i];
+}
+
+// splinterp_pt (spline.c:131-183)
+__device__ double tb_splinterp_pt(const double *z, int N, const double *x, const double *y, double xout) {
+  int idx = tb_binsearchapprox(x, xout, 0, N - 1);
+  if (idx == N - 1 || xout < x[idx]) idx--;
+  double x_lo = x[idx], x_hi = x[idx + 1], y_lo = y[idx], y_hi = y[idx + 1];
+  double h = x_hi - x_lo, dy = y_hi - y_lo;
+  if (x[idx] == xout) return y[idx];
+  if (h > 0) {
+    double dx = xout - x_lo;
+    double a = (z[idx + 1] - z[idx]) / (6 * h), b = 0.5 * z[idx];
+    double cc = dy / h - h / 6 * (z[idx + 1] + 2 * z[idx]);
+    return y_lo + dx * (cc + dx * (b + dx * a));
+  }
+  return 0;
+}
+
+// =============================================================== CIA (a9)
+
+#define CIA_MAXT 64
+// pass 1 (crosssec.c:407-412): per table row, spline along temperature -> f2[layer][row]
+__global__ void k_cia_temp(const double *__restrict__ tab, const double *__restrict__ ttemp, int ntw,
+                           int ntt, const double *__restrict__ ltemp, int fj, int lj,
+                           double *__restrict__ f2) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= ntw) return;
+  double z[CIA_MAXT], u[CIA_MAXT], v[CIA_MAXT], y[CIA_MAXT], x[CIA_MAXT];
+  for (int k = 0; k < ntt; k++) { y[k] = tab[(size_t)i * ntt + k]; x[k] = ttemp[k]; }
+  tb_spline_init(z, x, y, ntt, u, v);
+  for (int j = fj; j < lj; j++) f2[(size_t)j * ntw + i] = tb_splinterp_pt(z, ntt, x, y, ltemp[j]);
+}
+
+// pass 2a (crosssec.c:415-416): per layer, second derivatives along the table wavenumbers
+__global__ void k_cia_wnspline(const double *__restrict__ twn, int ntw, int fj, int lj,
+                               const double *__restrict__ f2, double *__restrict__ z2,
+                               double *__restrict__ scr) {
+  int j = fj + blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= lj) return;
+  tb_spline_init(z2 + (size_t)j * ntw, twn, f2 + (size_t)j * ntw, ntw, scr + (size_t)j * 2 * ntw,
+                 scr + (size_t)j * 2 * ntw + ntw);
+}
+
+// pass 2b (crosssec.c:417-419) + density scaling and positivity (crosssec.c:321-336)
+__global__ void k_cia_eval(const double *__restrict__ twn, int ntw, const double *__restrict__ f2,
+                           const double *__restrict__ z2, double wn_i, double wn_d, double wn_fct,
+                           int64_t nwn, int64_t fi, int64_t li, int fj, int lj,
+                           const double *__restrict__ densfac, double *__restrict__ ecs) {
+  int64_t w = fi + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int j = fj + blockIdx.y;
+  if (w >= li || j >= lj) return;
+  double wn = wn_fct * __dadd_rn(wn_i, __dmul_rn((double)w, wn_d));
+  double val = tb_splinterp_pt(z2 + (size_t)j * ntw, ntw, twn, f2 + (size_t)j * ntw, wn);
+  if (val > 0) ecs[(size_t)j * nwn + w] += val * densfac[j];
+}
+
+extern "C" int tb_cia_clear(tb_ctx *c) {
+  for (CiaTable *t : c->cia) {
+    t->d_wn.release(); t->d_temp.release(); t->d_tab.release();
+    delete t;
+  }
+  c->cia.clear();
+  c->have_ecs = false;
+  return TB_OK;
+}
+
+extern "C" int tb_cia_add_table(tb_ctx *c, const double *wn, int nwn, const double *temp, int ntemp,
+                                const double *tab, const int *mol, int nspec) {
+  TB_REQUIRE(nwn >= 3 && ntemp >= 3 && ntemp <= CIA_MAXT, TB_ERR_ARG,
+             "CIA table needs >=3 wavenumbers and 3..%d temperatures", CIA_MAXT);
+  TB_REQUIRE(nspec >= 1 && nspec <= 2, TB_ERR_ARG, "CIA table has 1 or 2 species (crosssec.c:115-124)");
+  for (int k = 0; k < nspec; k++)
+    TB_REQUIRE(mol[k] >= 0 && mol[k] < c->nmol, TB_ERR_ARG, "CIA species index out of range");
+  TB_CUDA(cudaSetDevice(c->device));
+  CiaTable *t = new CiaTable();
+  t->nw = nwn; t->nt = ntemp; t->nspec = nspec;
+  for (int k = 0; k < nspec; k++) t->mol[k] = mol[k];
+  t->wn.assign(wn, wn + nwn);
+  t->temp.assign(temp, temp + ntemp);
+  t->tab.assign(tab, tab + (size_t)nwn * ntemp);
+  if (t->d_wn.ensure(nwn) || t->d_temp.ensure(ntemp) || t->d_tab.ensure((size_t)nwn * ntemp)) {
+    delete t;
+    return TB_ERR_NOMEM;
+  }
+  TB_CUDA(cudaMemcpyAsync(t->d_wn.p, wn, nwn * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  TB_CUDA(cudaMemcpyAsync(t->d_temp.p, temp, ntemp * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  TB_CUDA(cudaMemcpyAsync(t->d_tab.p, tab, (size_t)nwn * ntemp * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  TB_CUDA(cudaStreamSynchronize(c->stream));
+  c->cia.push_back(t);
+  return TB_OK;
+}
+
+int tb_cia_run(tb_ctx *c) {
+  TB_REQUIRE(c->have_atm && c->have_grid, TB_ERR_STATE, "grid and atmosphere must be set before tb_cia_interp");
+  TB_CUDA(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const int nrad = c->nrad;
+  const int64_t nwn = c->nwn;
+  TB_TRY(c->d_ecs.ensure((size_t)nrad * nwn));
+  TB_CUDA(cudaMemsetAsync(c->d_ecs.p, 0, sizeof(double) * nrad * nwn, st));
+  std::vector<double> ltemp(nrad);
+  for (int i = 0; i < nrad; i++) ltemp[i] = c->t_fct * c->t[i];
+  DevBuf<double> d_lt;
+  TB_TRY(d_lt.ensure(nrad));
+  TB_CUDA(cudaMemcpyAsync(d_lt.p, ltemp.data(), nrad * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_TRY(c->c_densfac.ensure(nrad));
+  tb_timer_begin(c, "cia");
+  for (CiaTable *t : c->cia) {
+    // bicubicinterpolate's range logic (crosssec.c:366-393), on the host: O(nwn + nrad)
+    const double fx1 = t->wn[0], lx1 = t->wn[t->nw - 1], fx2 = t->temp[0], lx2 = t->temp[t->nt - 1];
+    auto gw = [&](int64_t k) { return c->wn_fct * (c->wn_i + (double)k * c->wn_d); };
+    if (gw(0) > lx1 || gw(nwn - 1) < fx1 || ltemp[0] > lx2 || ltemp[nrad - 1] < fx2) continue;
+    int64_t fi = 0, li = nwn;
+    while (fi < nwn && gw(fi) < fx1) fi++;
+    for (int64_t i = 0; i < li; i++) if (gw(i) > lx1) li = i;
+    int fj = 0, lj = nrad;
+    while (fj < nrad && ltemp[fj] < fx2) fj++;
+    for (int j = 0; j < lj; j++) if (ltemp[j] > lx2) lj = j;
+    if (fi >= li || fj >= lj) continue;
+    std::vector<double> df(nrad, 1.0);
+    for (int i = 0; i < nrad; i++)
+      for (int k = 0; k < t->nspec; k++) {
+        int m = t->mol[k];
+        df[i] *= c->dens[(size_t)m * nrad + i] / (TB_AMU * c->mol_mass[m] * TB_AMAGAT);
+      }
+    TB_CUDA(cudaMemcpyAsync(c->c_densfac.p, df.data(), nrad * sizeof(double), cudaMemcpyHostToDevice, st));
+    TB_TRY(c->c_f2.ensure((size_t)nrad * t->nw));
+    TB_TRY(c->c_z2.ensure((size_t)nrad * t->nw));
+    TB_TRY(c->c_scr.ensure((size_t)nrad * 2 * t->nw));
+    k_cia_temp<<<nblk(t->nw, 64), 64, 0, st>>>(t->d_tab.p, t->d_temp.p, t->nw, t->nt, d_lt.p, fj, lj, c->c_f2.p);
+    k_cia_wnspline<<<nblk(lj - fj, 32), 32, 0, st>>>(t->d_wn.p, t->nw, fj, lj, c->c_f2.p, c->c_z2.p, c->c_scr.p);
+    dim3 g(nblk(li - fi, 128), lj - fj);
+    k_cia_eval<<<g, 128, 0, st>>>(t->d_wn.p, t->nw, c->c_f2.p, c->c_z2.p, c->wn_i, c->wn_d, c->wn_fct, nwn,
+                                  fi, li, fj, lj, c->c_densfac.p, c->d_ecs.p);
+    c->launches += 3;
+    TB_CUDA(cudaStreamSynchronize(st));   // df / densfac are reused by the next table
+  }
+  tb_timer_end(c, "cia");
+  TB_CUDA(cudaGetLastError());
+  TB_CUDA(cudaStreamSynchronize(st));
+  d_lt.release();
+  c->have_ecs = true;
+  return TB_OK;
+}
+
+extern "C" int tb_cia_interp(tb_ctx *c) { return tb_cia_run(c); }
+
+// =============================================================== ray geometry
+
+// meta[ray*4]: {rs, npts, mode, npairs}; mode 0: tau = 0, 1: normal, 2: two-point case, -1: error
+// par[ray*4]:  {dx, x0, xr, trap_h0}
+// coef[ray*stride + 4*i]: {2-hratio, hfactor, 2-1/hratio, hsum} (geth/simpson, numerical.c:390-525)
+__global__ void k_ray_geometry(int eclipse, const double *__restrict__ rad, int nrad, double rfct,
+                               const double *__restrict__ h, int nh, double hfct, int stride,
+                               int32_t *__restrict__ meta, double *__restrict__ par,
+                               double *__restrict__ coef, double *__restrict__ sbuf,
+                               int32_t *__restrict__ err) {
+  int ri = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ri >= nh) return;
+  const double b = __ddiv_rn(__dmul_rn(h[ri], hfct), rfct);   // tau.c:274
+  int rs, mode = 1;
+  if (eclipse) {
+    rs = tb_binsearchapprox(rad, b, 0, nrad - 1);             // eclipse.c:39
+    if (rs == nrad - 1) mode = 0;
+  } else {
+    // binsearchie (numerical.c:16-45)
+    const double r0 = b;                                       // refraction index 1 (slantpath.c:32)
+    if (rad[0] > r0) { mode = -1; rs = 0; }
+    else if (rad[nrad - 1] < r0) { mode = 0; rs = 0; }         // -2: above the top -> 0
+    else if (rad[nrad - 1] == r0) { mode = 0; rs = 0; }        // -5: outermost layer -> 0
+    else {
+      long i = 0, f = nrad - 1;
+      while (f - i > 1) {
+        long m = (f + i) >> 1;
+        if (rad[m] > r0) f = m; else i = m;
+      }
+      rs = (int)i;
+    }
+  }
+  int32_t *mt = meta + ri * 4;
+  double *pp = par + ri * 4;
+  if (mode <= 0) {
+    if (mode < 0) atomicExch(err + 1, 1);
+    mt[0] = rs; mt[1] = 0; mt[2] = mode; mt[3] = 0;
+    return;
+  }
+  int n = nrad - rs;
+  const double r0 = eclipse ? rad[rs] : b;
+  double *s = sbuf + (size_t)ri * (nrad + 3);
+  if (n == 2) {
+    mode = 2;
+    // interp_parab(rad-1, ex-1, r0): parabola through layers rs-1, rs, rs+1
+    const double *x = rad + rs - 1;
+    pp[0] = x[1] - x[0];
+    pp[1] = x[0] / pp[0];
+    pp[2] = r0;
+    // three points: r0, midpoint, rad[rs+1] (slantpath.c:62-74, eclipse.c:68-80)
+    double r3_0 = eclipse ? rad[rs] : r0, r3_2 = rad[rs + 1], r3_1 = (r3_0 + r3_2) / 2.0;
+    s[0] = 0;
+    if (eclipse) { s[1] = s[0] + (r3_1 - r3_0); s[2] = s[1] + (r3_2 - r3_1); }
+    else { s[1] = sqrt(r3_1 * r3_1 - r0 * r0); s[2] = sqrt(r3_2 * r3_2 - r0 * r0); }
+    n = 3;
+  } else {
+    const double *x = rad + rs;
+    pp[0] = x[1] - x[0];
+    pp[1] = x[0] / pp[0];
+    pp[2] = r0;
+    s[0] = 0;
+    if (eclipse) {
+      for (int i = 1; i < n; i++) s[i] = s[i - 1] + (rad[rs + i] - rad[rs + i - 1]);
+    } else {
+      for (int i = 1; i < n; i++) {
+        double ri_ = rad[rs + i];
+        s[i] = sqrt(__dsub_rn(__dmul_rn(ri_, ri_), __dmul_rn(r0, r0)));
+      }
+    }
+  }
+  const int even = (n % 2 == 0);
+  const int np = (n - 1) / 2;
+  double *cf = coef + (size_t)ri * stride;
+  for (int i = 0; i < np; i++) {
+    int j = 2 * i + even;
+    double h0 = s[j + 1] - s[j], h1 = s[j + 2] - s[j + 1];
+    double hsum = h0 + h1, hratio = h1 / h0, hfactor = hsum * hsum / (h0 * h1);
+    cf[4 * i + 0] = 2.0 - hratio;
+    cf[4 * i + 1] = hfactor;
+    cf[4 * i + 2] = 2.0 - 1.0 / hratio;
+    cf[4 * i + 3] = hsum;
+  }
+  pp[3] = even ? (s[1] - s[0]) : 0.0;
+  mt[0] = rs; mt[1] = n; mt[2] = mode; mt[3] = np;
+}
+
+// =============================================================== tau (a10-a13)
+
+struct TauPar {
+  int eclipse, nrad, nh, stride;
+  int64_t nwn;
+  double rfct, toomuch, wn_i, wn_d, wn_fct;
+  int sc_flag, cl_flag;
+  double sc_fac;                       // pow(10, logext) * E0H2
+  double cl_ext, cl_top, cl_bot, cl_gamma, cl_Q, cl_r, cl_sig, cl_refwn;
+};
+
+// interp_parab (numerical.c:182-195) with the per-ray constants dx, x0 = x[0]/dx
+__device__ __forceinline__ double tb_parab(double dx, double x0, double xr, double y0, double y1, double y2) {
+  const double my = y0 + y2 - 2 * y1;
+  const double a = my / (2.0 * dx * dx);
+  const double b = (y2 - y1 - (x0 + 1.5) * my) / dx;
+  const double cc = y0 + x0 * (y2 - 4 * y1 + 3 * y0 + x0 * my) / 2.0;
+  return xr * xr * a + xr * b + cc;
+}
+
+// One thread per wavenumber; its extinction column er[layer] lives in shared memory laid out
+// [layer][thread] (conflict-free).  Rays are walked top-down with the reference's early exit.
+__global__ void k_tau(TauPar P, const double *__restrict__ e, const double *__restrict__ ecs,
+                      const double *__restrict__ press, const double *__restrict__ temp,
+                      const double *__restrict__ aux, const double *__restrict__ mol_d,
+                      const double *__restrict__ mol_pol, const double *__restrict__ mol_mass, int nmol,
+                      const int32_t *__restrict__ meta, const double *__restrict__ par,
+                      const double *__restrict__ coef, double *__restrict__ tau,
+                      int32_t *__restrict__ last) {
+  extern __shared__ double sm[];
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int64_t w = blockIdx.x * (int64_t)nt + tid;
+  if (w >= P.nwn) return;
+  double *er = sm + tid;
+  const int nrad = P.nrad;
+  const double wn = P.wn_fct * __dadd_rn(P.wn_i, __dmul_rn((double)w, P.wn_d));
+  // scattering (extinction.c:586-624) and clouds (extinction.c:629-693), per layer
+  double kBP = 0, kFH = 0, refw = 1;
+  int ctop = -1, cbot = -1;   // cloud occupies layers (cbot, ctop]
+  if (P.cl_flag && P.cl_ext != 0) {
+    const double top = pow(10.0, P.cl_top), bot = pow(10.0, P.cl_bot);
+    int i = nrad - 1;
+    for (; i >= 0; i--) if (press[i] >= top) break;
+    ctop = i;
+    for (; i >= 0; i--) if (press[i] >= bot) break;
+    cbot = i;
+    const double x = 2 * TB_PI * P.cl_r * wn;
+    refw = pow(P.cl_refwn, P.cl_gamma);
+    kBP = P.cl_ext * pow(wn, P.cl_gamma);
+    kFH = P.cl_ext / (P.cl_Q * pow(x, -1 * P.cl_gamma) + pow(x, 0.2));
+  }
+  const double wn4 = pow(wn, 4.0);
+  for (int r = 0; r < nrad; r++) {
+    double es = 0, ec = 0;
+    if (P.sc_flag == 1) es = P.sc_fac * press[r] / temp[r] * wn4;
+    else if (P.sc_flag == 2) {
+      for (int j = 0; j < nmol; j++)
+        es += TB_PI * 8e-32 / 3. * pow(mol_pol[j], 2.0) * pow(2. * TB_PI * wn * TB_MICRON, 4.0) *
+              mol_d[(size_t)j * nrad + r] / mol_mass[j] * TB_NAVOGADRO;
+    }
+    if (r <= ctop && r > cbot) {
+      const double md = aux[nrad + r];
+      switch (P.cl_flag) {
+        case 1: ec = P.cl_ext; break;
+        case 2: ec = P.cl_ext * md; break;
+        case 3: ec = kBP * md; break;
+        case 4: ec = kFH * md; break;
+        case 5: ec = aux[r] * kBP * P.cl_sig / refw * md; break;
+      }
+    }
+    // tau.c:231-232, same left-to-right sum
+    er[r * nt] = e[(size_t)r * P.nwn + w] + es + ec + ecs[(size_t)r * P.nwn + w];
+  }
+  int lst = P.nh - 1;
+  for (int ri = 0; ri < P.nh; ri++) {
+    const int32_t *mt = meta + ri * 4;
+    const int mode = mt[2];
+    double t = 0.0;
+    if (mode > 0) {
+      const int rs = mt[0], n = mt[1], np = mt[3];
+      const double *pp = par + ri * 4;
+      const double *cf = coef + (size_t)ri * P.stride;
+      double y0, ya, yb;   // sliding window over the ray's samples
+      if (mode == 2) {
+        y0 = tb_parab(pp[0], pp[1], pp[2], er[(rs - 1) * nt], er[rs * nt], er[(rs + 1) * nt]);
+        yb = er[(rs + 1) * nt];
+        ya = (y0 + yb) / 2.0;
+        t = (y0 * cf[0] + ya * cf[1] + yb * cf[2]) * cf[3] / 6.0;   // three points: one Simpson pair
+      } else {
+        y0 = tb_parab(pp[0], pp[1], pp[2], er[rs * nt], er[(rs + 1) * nt], er[(rs + 2) * nt]);
+        if (P.eclipse) er[rs * nt] = y0;          // eclipse.c:66 never restores it
+        const int even = (n % 2 == 0);
+        double res = 0.0;
+        for (int i = 0; i < np; i++) {
+          const int j = 2 * i + even;
+          const double a0 = (j == 0) ? y0 : er[(rs + j) * nt];
+          res += (a0 * cf[4 * i] + er[(rs + j + 1) * nt] * cf[4 * i + 1] +
+                  er[(rs + j + 2) * nt] * cf[4 * i + 2]) * cf[4 * i + 3];
+        }
+        t = res / 6.0;
+        if (even) t += pp[3] * (y0 + er[(rs + 1) * nt]) / 2;
+      }
+      t = P.rfct * (P.eclipse ? t : 2 * t);
+    }
+    tau[(size_t)ri * P.nwn + w] = t;
+    if (t > P.toomuch) { lst = ri; break; }       // tau.c:277-287
+  }
+  last[w] = lst;
+}
+
+extern "C" int tb_tau(tb_ctx *c, int geometry, double toomuch, const double *h, int nh, double hfct) {
+  TB_REQUIRE(c->have_e && c->have_atm, TB_ERR_STATE, "extinction must be computed before tb_tau");
+  TB_REQUIRE(geometry == TB_GEOM_TRANSIT || geometry == TB_GEOM_ECLIPSE, TB_ERR_ARG, "bad geometry");
+  TB_CUDA(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const int nrad = c->nrad;
+  const int64_t nwn = c->nwn;
+  if (!h) {                                   // makeipsample with raddelt=-1 / tau.c:92-98
+    nh = nrad;
+    hfct = c->rad_fct;
+    c->h_h.resize(nrad);
+    for (int i = 0; i < nrad; i++) c->h_h[i] = c->rad[nrad - 1 - i];
+  } else {
+    TB_REQUIRE(nh >= 1, TB_ERR_ARG, "need at least one ray");
+    c->h_h.assign(h, h + nh);
+  }
+  if (geometry == TB_GEOM_ECLIPSE) TB_REQUIRE(nh == nrad, TB_ERR_ARG, "eclipse rays are the layers (tau.c:92-98)");
+  c->nh = nh; c->hfct = hfct; c->geometry = geometry; c->toomuch = toomuch;
+  if (!c->have_ecs) {                         // no CIA tables: zeros
+    TB_TRY(c->d_ecs.ensure((size_t)nrad * nwn));
+    TB_CUDA(cudaMemsetAsync(c->d_ecs.p, 0, sizeof(double) * nrad * nwn, st));
+    c->have_ecs = true;
+  }
+  const int stride = 4 * ((nrad + 2) / 2 + 1);
+  DevBuf<double> d_h, d_s;
+  TB_TRY(d_h.ensure(nh)); TB_TRY(d_s.ensure((size_t)nh * (nrad + 3)));
+  TB_TRY(c->r_meta.ensure((size_t)nh * 4)); TB_TRY(c->r_par.ensure((size_t)nh * 4));
+  TB_TRY(c->r_coef.ensure((size_t)nh * stride));
+  TB_TRY(c->d_tau.ensure((size_t)nh * nwn)); TB_TRY(c->d_last.ensure(nwn));
+  TB_TRY(c->d_es_aux.ensure(2 * (size_t)nrad));
+  std::vector<double> aux(2 * (size_t)nrad, 0.0);
+  if ((int)c->nH.size() == nrad) for (int i = 0; i < nrad; i++) { aux[i] = c->nH[i]; aux[nrad + i] = c->mean_dens[i]; }
+  TB_CUDA(cudaMemcpyAsync(c->d_es_aux.p, aux.data(), aux.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(d_h.p, c->h_h.data(), nh * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4 * sizeof(int32_t), st));
+  TB_CUDA(cudaMemsetAsync(c->d_tau.p, 0, sizeof(double) * nh * nwn, st));   // calloc, tau.c:34
+  k_ray_geometry<<<nblk(nh, 64), 64, 0, st>>>(geometry == TB_GEOM_ECLIPSE, c->d_rad.p, nrad, c->rad_fct, d_h.p, nh,
+                                              hfct, stride, c->r_meta.p, c->r_par.p, c->r_coef.p, d_s.p, c->d_err.p);
+  TauPar P;
+  P.eclipse = geometry == TB_GEOM_ECLIPSE; P.nrad = nrad; P.nh = nh; P.stride = stride; P.nwn = nwn;
+  P.rfct = c->rad_fct; P.toomuch = toomuch; P.wn_i = c->wn_i; P.wn_d = c->wn_d; P.wn_fct = c->wn_fct;
+  P.sc_flag = c->sc_flag; P.cl_flag = c->cl_flag;
+  P.sc_fac = pow(10.0, c->sc_logext) * TB_E0H2;
+  P.cl_ext = c->cl_ext; P.cl_top = c->cl_top; P.cl_bot = c->cl_bot; P.cl_gamma = c->cl_gamma;
+  P.cl_Q = c->cl_Q; P.cl_r = c->cl_r; P.cl_sig = c->cl_sig; P.cl_refwn = c->cl_refwn;
+  const int TPB = 64;
+  const size_t shm = (size_t)nrad * TPB * sizeof(double);
+  TB_REQUIRE(shm <= 200 * 1024, TB_ERR_ARG, "too many layers (%d) for the tau kernel's shared memory", nrad);
+  TB_CUDA(cudaFuncSetAttribute(k_tau, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
+  tb_timer_begin(c, "tau");
+  k_tau<<<nblk(nwn, TPB), TPB, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p, c->d_dens.p,
+                                          c->d_mol_pol.p, c->d_mol_mass.p, c->nmol, c->r_meta.p, c->r_par.p,
+                                          c->r_coef.p, c->d_tau.p, c->d_last.p);
+  tb_timer_end(c, "tau");
+  c->launches += 2;
+  int32_t err[4];
+  TB_CUDA(cudaMemcpyAsync(err, c->d_err.p, sizeof(err), cudaMemcpyDeviceToHost, st));
+  TB_CUDA(cudaStreamSynchronize(st));
+  d_h.release(); d_s.release();
+  TB_REQUIRE(err[1] == 0, TB_ERR_DOMAIN, "a ray's closest approach lies below the bottom layer (slantpath.c:40-44)");
+  c->have_tau = true;
+  return TB_OK;
+}
+
+// =============================================================== modulation (a14)
+
+__global__ void k_modulation(int64_t nwn, int nh, const double *__restrict__ tau,
+                             const int32_t *__restrict__ last, const double *__restrict__ ip, double ipfct,
+                             double toomuch, double srad, int transp, double *__restrict__ out,
+                             int32_t *__restrict__ err) {
+  int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (w >= nwn) return;
+  const int L0 = last[w];
+  int L1 = L0 + 1;
+  if (L1 > nh - 1) L1 = nh - 1;
+  const int n = L1 + 1;                                 // points handed to simps (slantpath.c:392-408)
+  if (n < 3) { atomicExch(err + 2, 1); out[w] = 0; return; }
+  // point k (ascending radius) is ray i = n-1-k; integrand exp(-tau_i)*ip_i for i<=L0, else 0
+  auto X = [&](int k) { return ip[n - 1 - k] * ipfct; };
+  auto Y = [&](int k) { int i = n - 1 - k; return (i <= L0) ? exp(-tau[(size_t)i * nwn + w]) * (ip[i] * ipfct) : 0.0; };
+  const int even = (n % 2 == 0);
+  double res = 0.0;
+  for (int i = 0; i < (n - 1) / 2; i++) {
+    const int j = 2 * i + even;
+    const double h0 = X(j + 1) - X(j), h1 = X(j + 2) - X(j + 1);
+    const double hsum = h0 + h1, hratio = h1 / h0, hfactor = hsum * hsum / (h0 * h1);
+    res += (Y(j) * (2.0 - hratio) + Y(j + 1) * hfactor + Y(j + 2) * (2.0 - 1.0 / hratio)) * hsum;
+  }
+  double integ = res / 6.0;
+  if (even) integ += (X(1) - X(0)) * (Y(0) + Y(1)) / 2;
+  const double rtop = ip[0] * ipfct;
+  double r = rtop * rtop - 2.0 * integ;
+  if (transp) {
+    const double tl = tau[(size_t)L0 * nwn + w];
+    const double maxtau = tl > toomuch ? tl : toomuch;
+    const double rb = X(0);
+    r -= exp(-maxtau) * rb * rb;
+  }
+  out[w] = r * (1.0 / (srad * srad));
+}
+
+extern "C" int tb_modulation(tb_ctx *c, double starrad_cm, int transparent, double *out) {
+  TB_REQUIRE(c->have_tau && c->geometry == TB_GEOM_TRANSIT, TB_ERR_STATE, "tb_tau (transit) must precede tb_modulation");
+  TB_CUDA(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  DevBuf<double> d_ip;
+  TB_TRY(d_ip.ensure(c->nh));
+  TB_TRY(c->d_out.ensure(c->nwn));
+  TB_CUDA(cudaMemcpyAsync(d_ip.p, c->h_h.data(), c->nh * sizeof(double), cudaMemcpyHostToDevice, st));
+  tb_timer_begin(c, "modulation");
+  k_modulation<<<nblk(c->nwn, 128), 128, 0, st>>>(c->nwn, c->nh, c->d_tau.p, c->d_last.p, d_ip.p, c->hfct, c->toomuch,
+                                                  starrad_cm, transparent, c->d_out.p, c->d_err.p);
+  tb_timer_end(c, "modulation");
+  TB_LAUNCHED(c);
+  int32_t err[4];
+  TB_CUDA(cudaMemcpyAsync(err, c->d_err.p, sizeof(err), cudaMemcpyDeviceToHost, st));
+  if (out) TB_CUDA(cudaMemcpyAsync(out, c->d_out.p, c->nwn * sizeof(double), cudaMemcpyDeviceToHost, st));
+  TB_CUDA(cudaStreamSynchronize(st));
+  d_ip.release();
+  TB_REQUIRE(err[2] == 0, TB_ERR_DOMAIN, "less than 3 items for radial integration (slantpath.c:393-397)");
+  return TB_OK;
+}
+
+// =============================================================== intensity + flux (a15)
+
+#define TB_MAXANG 16
+__global__ void k_intensity_flux(int64_t nwn, int nrad, const double *__restrict__ tau,
+                                 const int32_t *__restrict__ last, const double *__restrict__ temp,
+                                 double wn_i, double wn_d, double wn_fct, int nang,
+                                 const double *__restrict__ ang, const double *__restrict__ area,
+                                 double *__restrict__ intens, double *__restrict__ out) {
+  int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (w >= nwn) return;
+  const int L = last[w];
+  const double wv = __dadd_rn(wn_i, __dmul_rn((double)w, wn_d));   // wns.v[w]
+  const double ww = wv * wn_fct;
+  const double num = 2.0 * TB_H * pow(ww, 3.0) * TB_LS * TB_LS;     // eclipse.c:154
+  double icos[TB_MAXANG], dprev[TB_MAXANG], tz[TB_MAXANG];
+  for (int a = 0; a < nang; a++) { icos[a] = cos(ang[a] * TB_DEGREES); tz[a] = 0; dprev[a] = 0; }
+  double Bprev = 0;
+  for (int i = 0; i <= L; i++) {
+    const double t = tau[(size_t)i * nwn + w];
+    const double B = num / (exp(TB_H * ww * TB_LS / (TB_KB * temp[nrad - 1 - i])) - 1.0);
+    for (int a = 0; a < nang; a++) {
+      const double dt = exp(-t / icos[a]);
+      if (i > 0) tz[a] += (dt - dprev[a]) * (B + Bprev);             // integ_trapz, numerical.c:168-170
+      dprev[a] = dt;
+    }
+    Bprev = B;
+  }
+  double f = 0;
+  for (int a = 0; a < nang; a++) {
+    const double I = Bprev * dprev[a] - 0.5 * tz[a];                  // eclipse.c:158
+    intens[(size_t)a * nwn + w] = I;
+    f += TB_PI * I * area[a];                                         // eclipse.c:275-279
+  }
+  out[w] = f;
+}
+
+extern "C" int tb_intensity_flux(tb_ctx *c, const double *angles_deg, int nang, double *out) {
+  TB_REQUIRE(c->have_tau && c->geometry == TB_GEOM_ECLIPSE, TB_ERR_STATE, "tb_tau (eclipse) must precede tb_intensity_flux");
+  TB_REQUIRE(nang >= 1 && nang <= TB_MAXANG, TB_ERR_ARG, "1..%d angles supported", TB_MAXANG);
+  TB_CUDA(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  // area grid (eclipse.c:262-276)
+  std::vector<double> grid(nang + 1), area(nang), ang(angles_deg, angles_deg + nang);
+  grid[0] = 0.0 * TB_DEGREES;
+  grid[nang] = 90.0 * TB_DEGREES;
+  for (int i = 1; i < nang; i++) grid[i] = (ang[i - 1] + ang[i]) * TB_DEGREES / 2.0;
+  for (int i = 0; i < nang; i++) area[i] = pow(sin(grid[i + 1]), 2.0) - pow(sin(grid[i]), 2.0);
+  DevBuf<double> d_a;
+  TB_TRY(d_a.ensure(2 * (size_t)nang));
+  TB_TRY(c->d_intens.ensure((size_t)nang * c->nwn));
+  TB_TRY(c->d_out.ensure(c->nwn));
+  TB_CUDA(cudaMemcpyAsync(d_a.p, ang.data(), nang * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(d_a.p + nang, area.data(), nang * sizeof(double), cudaMemcpyHostToDevice, st));
+  tb_timer_begin(c, "intensity");
+  k_intensity_flux<<<nblk(c->nwn, 128), 128, 0, st>>>(c->nwn, c->nrad, c->d_tau.p, c->d_last.p, c->d_t.p, c->wn_i,
+                                                      c->wn_d, c->wn_fct, nang, d_a.p, d_a.p + nang, c->d_intens.p,
+                                                      c->d_out.p);
+  tb_timer_end(c, "intensity");
+  TB_LAUNCHED(c);
+  if (out) TB_CUDA(cudaMemcpyAsync(out, c->d_out.p, c->nwn * sizeof(double), cudaMemcpyDeviceToHost, st));
+  TB_CUDA(cudaStreamSynchronize(st));
+  d_a.release();
+  c->nang = nang;
+  return TB_OK;
+}
+
+// =============================================================== do_transit in one call
+
+extern "C" int tb_spectrum(tb_ctx *c, int geometry, double toomuch, double ethresh, double starrad_cm,
+                           int transparent, const double *angles_deg, int nang, double *out) {
+  TB_TRY(tb_cia_run(c));                                   // interpcs, transit.c:147
+  if (c->have_grid_o) TB_TRY(tb_interp_run(c));            // interpolmolext (opacity file given)
+  else TB_TRY(tb_extinction_lbl(c, ethresh));              // computemolext per layer
+  TB_TRY(tb_tau(c, geometry, toomuch, nullptr, 0, 0));     // tau, transit.c:165,189
+  if (geometry == TB_GEOM_ECLIPSE) return tb_intensity_flux(c, angles_deg, nang, out);
+  return tb_modulation(c, starrad_cm, transparent, out);
+}
