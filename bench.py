@@ -1,0 +1,360 @@
+#!/usr/bin/env python
+"""bench.py -- the headline measurement (BASELINE.json): spectra/s of the HAT-P-11b-shape
+transmission spectrum (config C2: 31 334 wavenumbers, 100 layers, 10^6 lines, 4 line-list
+molecules, 2 CIA tables, line-by-line extinction) on N B200s, with the line-sum
+G(line-samples)/s and the roofline of the dominant kernel beside it.
+
+    python bench.py --gpus N --steps K --warmup W            (our arm; torchrun for N>1)
+    python bench.py --impl reference ...                     (the unmodified reference binary
+                                                               on the host cores, oracle/_ref)
+
+A step = one do_transit (transit/src/transit.c:125-214): CIA interpolation + line-by-line
+extinction of every layer + tau + modulation for one atmosphere.  `value` is timed with the
+static inputs (line index, Voigt table, CIA tables) resident in HBM; `e2e` goes through the
+host mirror of run_transit with HOST buffers: per step the atmosphere is copied host->device
+and the spectrum device->host inside the timed region.  L2 is flushed between timed steps.
+The oracle / reference are used here only as the timed CPU baseline, never as the product.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CLOCK_Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+           "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+           "clocks_event_reasons.sw_power_cap")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={CLOCK_Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.th = threading.Thread(target=self._read, daemon=True)
+        self.th.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.th.join(timeout=2)
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2])); pw.append(float(r[3]))
+            except (ValueError, IndexError):
+                continue
+            for k, nm in enumerate(names):
+                if len(r) > 4 + k and r[4 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        # "under load" = samples drawing more than half of the highest power seen
+        load = [s for s, p in zip(sm, pw) if pw and p >= 0.5 * max(pw)] or sm
+        return {"sm_mhz": float(np.median(load)) if load else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+# ------------------------------------------------------------------ reference arm (CPU)
+
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libtransit_ref.so")
+REF_SEC_PER_SPECTRUM = 27.0      # measured: one do_transit of full C2 on one 2025-class x86 core
+
+
+def _ref_worker(cfg_path, conn):
+    """One process = one instance of the UNMODIFIED reference (global state, non re-entrant):
+    transit_init once (transit.c:25-74), then one do_transit (transit.c:125-214) per request."""
+    import ctypes as C
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    os.dup2(devnull, 1)                                   # the reference prints its banner per run
+    L = C.CDLL(REF_SO)
+    argv = [b"transit", b"-c", cfg_path.encode()]
+    arr = (C.c_char_p * len(argv))(*argv)
+    L.transit_init(len(argv), arr)
+    L.get_no_samples.restype = C.c_int
+    out = np.zeros(L.get_no_samples())
+    conn.send(("ready", out.size))
+    while True:
+        msg = conn.recv()
+        if msg == "stop":
+            break
+        t = time.perf_counter()
+        L.do_transit(out.ctypes.data_as(C.POINTER(C.c_double)))
+        conn.send((time.perf_counter() - t, float(out.sum())))
+
+
+class ReferencePool:
+    """`nproc` independent reference processes -- the only parallelism the reference supports
+    (N independent processes over disjoint atmospheres)."""
+
+    def __init__(self, cfg_paths):
+        import multiprocessing as mp
+        ctx = mp.get_context("fork")
+        self.pipes, self.procs = [], []
+        for cfg_path in cfg_paths:
+            a, b = ctx.Pipe()
+            p = ctx.Process(target=_ref_worker, args=(cfg_path, b), daemon=True)
+            p.start()
+            self.pipes.append(a); self.procs.append(p)
+        for a in self.pipes:
+            if not a.poll(600):
+                raise RuntimeError("reference worker did not initialise (transit_init exits on bad input)")
+            a.recv()
+
+    def step(self):
+        t = time.perf_counter()
+        for a in self.pipes:
+            a.send("go")
+        res = [a.recv() for a in self.pipes]
+        return time.perf_counter() - t, res
+
+    def close(self):
+        for a in self.pipes:
+            a.send("stop")
+        for p in self.procs:
+            p.join(timeout=5)
+
+
+def reference_inputs(workload, nbands, nproc, tag):
+    """The workload as reference input files, split into `nbands` contiguous wavenumber bands (the
+    reference's own way to spread one spectrum over processes); process i gets
+    band i mod nbands.  Every per-spectrum cost of the reference (line sum, CIA, tau, modulation)
+    is per wavenumber, so a band is a proportional sample of the spectrum."""
+    from transit_b200 import workloads
+    prob = workloads.make_problem(workload)
+    d = os.path.join("/tmp", f"transit_b200_ref_{tag}_{os.getpid()}")
+    edges = np.linspace(0, prob.nwn - 1, nbands + 1).astype(int)
+    cfgs = []
+    for i in range(nproc):
+        b = i % nbands
+        band = None if nbands == 1 else (int(edges[b]), int(edges[b + 1]))
+        cfg, nlines = workloads.write_reference_inputs(prob, d, band=band, tag=f"w{i}")
+        cfgs.append(cfg)
+    return prob, cfgs, nlines
+
+
+def run_reference(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return 0
+    if not os.path.exists(REF_SO):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libtransit_ref.so not built"}))
+        return 0
+    cores = max(1, min(os.cpu_count() or 1, args.ref_procs or 32))
+    # bounded sample: each process computes 1/nbands of the spectrum per step so that (K+W) steps
+    # end within a few minutes
+    nbands = int(np.ceil((args.steps + args.warmup) * REF_SEC_PER_SPECTRUM / args.ref_budget_s))
+    nbands = max(1, min(nbands, 64))
+    prob, cfgs, nlines = reference_inputs(args.workload, nbands, cores, "arm")
+    pool = ReferencePool(cfgs)
+    for _ in range(args.warmup):
+        pool.step()
+    t_steps = [pool.step()[0] for _ in range(args.steps)]
+    pool.close()
+    sec = float(np.sum(t_steps))
+    value = (cores / nbands) * args.steps / sec            # whole spectra per second
+    sample = (f"{cores} independent reference processes (libtransit_ref.so: transit_init once, do_transit per step), "
+              f"each computing one of {nbands} contiguous wavenumber bands of the {args.workload} spectrum per step "
+              f"(process i -> band i mod {nbands}; full {nlines}-line list on disk); value = processes / bands / step time")
+    line = {"impl": "reference", "metric": "spectra/s", "value": value, "unit": "spectra/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(prob, args.workload),
+            "cpu_baseline": {"value": value, "unit": "spectra/s", "cores": cores, "kind": "reference", "sample": sample},
+            "e2e": {"value": value, "unit": "spectra/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(prob, name):
+    return {"workload": f"{name}: HAT-P-11b-shape transmission 0.3-5 um, line-by-line" if name == "C2" else name,
+            "nwn": int(prob.nwn), "wnosamp": int(prob.wnosamp), "layers": int(prob.nrad), "lines": int(len(prob.wl)),
+            "isotopologues": int(prob.niso), "line_molecules": len(prob.cfg["molecules"]), "cia_tables": len(prob.cia),
+            "geometry": "eclipse" if prob.eclipse else "transit", "voigt_table": "60x60", "l2": "flushed between steps"}
+
+
+# ------------------------------------------------------------------ our arm (B200)
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except (OSError, KeyError, ValueError):
+        return 6650.0, "fallback (B200_PROFILING.md, 6.65 TB/s)"
+
+
+def cpu_baseline_leg(args):
+    """The unmodified reference on a bounded sample of the same workload: `nb` processes, one
+    wavenumber band each (together one whole spectrum)."""
+    if not os.path.exists(REF_SO):
+        return {"value": None, "unit": "spectra/s", "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+    nb = max(1, min(os.cpu_count() or 1, int(np.ceil(REF_SEC_PER_SPECTRUM / args.cpu_baseline_s))))
+    prob, cfgs, nlines = reference_inputs(args.workload, nb, nb, "cpu")
+    pool = ReferencePool(cfgs)
+    sec, _ = pool.step()
+    pool.close()
+    return {"value": 1.0 / sec, "unit": "spectra/s", "cores": nb, "kind": "reference",
+            "sample": f"one whole {args.workload} spectrum by the unmodified reference (oracle/_ref/libtransit_ref.so, "
+                      f"do_transit), split into {nb} wavenumber bands on {nb} processes/cores: {sec:.1f} s"}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from transit_b200 import api, workloads, sharding
+
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+
+    prob = workloads.make_problem(args.workload, scale=args.scale)
+    t0 = time.perf_counter()
+    tr = sharding.ShardedTransit(local_rank, rank, world)
+    tr.transit_init(prob)
+    tr.ctx.sync()
+    init_s = time.perf_counter() - t0
+    ctx = tr.ctx
+    out = np.zeros(prob.nwn)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        tr.do_transit(out)
+    ref_out = out.copy()
+
+    # ---- device-timed steps (static inputs resident; L2 flushed between steps)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    l0 = ctx.launch_count()
+    ms_steps, k_ms = [], {}
+    for _ in range(args.steps):
+        flush.zero_()
+        barrier()
+        ctx.timer_start("step")
+        tr.do_transit(out)
+        ctx.timer_stop("step")
+        ctx.sync()
+        ms_steps.append(ctx.kernel_ms("step"))
+        for nm in ("kmax", "strength", "accumulate", "molext", "cia", "tau", "modulation"):
+            try:
+                k_ms.setdefault(nm, []).append(ctx.kernel_ms(nm))
+            except api.TransitError:
+                pass
+    barrier()
+    launches = ctx.launch_count() - l0
+    nsamp = int(tr.sample_counts().sum())                 # this rank's executed profile updates per step
+    clocks = sampler.stop()
+    assert np.array_equal(out, ref_out), "spectrum changed between steps: the path is not deterministic"
+
+    # ---- end to end through the host mirror with HOST buffers (H2D atmosphere + D2H spectrum per step)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        tr.set_atmosphere(prob)
+        tr.do_transit(out)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    h2d = 8 * prob.nrad * (3 + prob.nmol + prob.niso)
+    d2h = 8 * prob.nwn
+
+    dev_ms = float(np.sum(ms_steps))
+    t = torch.tensor([dev_ms, e2e_s, float(nsamp), float(launches)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        dev_ms, e2e_s, nsamp, launches = float(tmax[0]), float(tmax[1]), int(tsum[2]), int(tsum[3])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    hbm_peak, peak_src = measured_peaks()
+    acc_ms = float(np.mean(k_ms["accumulate"]))
+    mol_ms = float(np.mean(k_ms["molext"]))
+    G, ns, nwn = tr.ngroups(), prob.nrad, tr.band_nwn()
+    my_samp = int(tr.sample_counts().sum())
+    acc_bytes = 4.0 * my_samp + 9.0 * G * ns + 8.0 * nwn * ns
+    achieved = acc_bytes / (acc_ms * 1e-3) / 1e9
+    line = {
+        "metric": "spectra/s", "value": args.steps / (dev_ms * 1e-3), "unit": "spectra/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": dict(workload_config(prob, args.workload), sharding=f"wavenumber bands x{world}" if world > 1 else "none"),
+        "e2e": {"value": args.steps / e2e_s, "unit": "spectra/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches,
+        "line_sum": {"gsamples_per_s": nsamp / (mol_ms * 1e-3) / 1e9, "samples_per_step": nsamp,
+                     "line_layers_per_s": len(prob.wl) * prob.nrad / (mol_ms * 1e-3), "molext_ms": mol_ms},
+        "kernel_ms": {k: float(np.mean(v)) for k, v in k_ms.items()},
+        "roofline": {"kernel": "k_accumulate", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src, "ms": acc_ms,
+                     "algorithmic_bytes": acc_bytes,
+                     "fp64_gflops": 2.0 * my_samp / (acc_ms * 1e-3) / 1e9},
+        "clocks": clocks, "init_s": init_s,
+    }
+    if args.microbench:
+        line["microbench"] = ctx.microbench()
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline_leg(args)
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C2")
+    ap.add_argument("--scale", type=float, default=1.0, help="line-count multiplier (debugging only; 1.0 = the named config)")
+    ap.add_argument("--microbench", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-baseline-s", type=float, default=14.0)
+    ap.add_argument("--ref-procs", type=int, default=0)
+    ap.add_argument("--ref-budget-s", type=float, default=150.0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    return run_reference(args) if args.impl == "reference" else run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -80,6 +80,8 @@ int  tb_get_line_trace(tb_ctx *c, int s, int32_t *iown, int32_t *idwn, int32_t *
                        int8_t *status);
 int  tb_get_sample_counts(tb_ctx *c, int64_t *nsamples, int ns);
 int  tb_get_line_molIDs(tb_ctx *c, int *molID, int *nmolrows);   /* opacity.c:349-361 */
+/* sizes of the device line index: lines uploaded, co-add groups (evaluated leaders), member lines */
+int  tb_get_line_counts(tb_ctx *c, int64_t *nlines, int64_t *ngroups, int64_t *nmembers);
 
 /* calcopacity (opacity.c:281-427): grid[Nlayer][Ntemp][Nmol][Nwave] written to `grid`
  * (host, file order).  ziso[niso][Ntemp]; q[nmol][nrad] number abundances; press cgs.  */

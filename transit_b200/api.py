@@ -49,6 +49,7 @@ ABI = {
     "tb_get_line_trace": (C.c_int, [C.c_void_p, C.c_int, i32p, i32p, i32p, i8p]),
     "tb_get_sample_counts": (C.c_int, [C.c_void_p, i64p, C.c_int]),
     "tb_get_line_molIDs": (C.c_int, [C.c_void_p, i32p, i32p]),
+    "tb_get_line_counts": (C.c_int, [C.c_void_p, i64p, i64p, i64p]),
     "tb_opacity_build": (C.c_int, [C.c_void_p, C.c_int, f64p, f64p, f64p, f64p, C.c_int, C.c_double, f64p]),
     "tb_opacity_load": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, i32p, f64p, f64p, f64p]),
     "tb_extinction_interp": (C.c_int, [C.c_void_p]),
@@ -223,6 +224,14 @@ class Context:
         ids = np.zeros(256, np.int32)
         self._ck(self.lib.tb_get_line_molIDs(self.h, _p(ids, i32p), C.byref(n)), "tb_get_line_molIDs")
         return ids[:n.value].copy()
+
+    def line_counts(self):
+        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
+        self._ck(self.lib.tb_get_line_counts(self.h, C.byref(a), C.byref(b), C.byref(c)), "tb_get_line_counts")
+        return a.value, b.value, c.value
+
+    def ngroups(self):
+        return self.line_counts()[1]
 
     # -- opacity grid -------------------------------------------------------------------
     def opacity_build(self, temp, ziso, q, mm, bymass, ethresh):

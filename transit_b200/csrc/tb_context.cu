@@ -200,6 +200,14 @@ extern "C" int tb_get_line_molIDs(tb_ctx *c, int *molID, int *nmolrows) {
   return TB_OK;
 }
 
+extern "C" int tb_get_line_counts(tb_ctx *c, int64_t *nlines, int64_t *ngroups, int64_t *nmembers) {
+  TB_REQUIRE(c->have_lines, TB_ERR_STATE, "tb_upload_lines not called");
+  if (nlines) *nlines = c->nlines;
+  if (ngroups) *ngroups = c->G;
+  if (nmembers) *nmembers = c->M;
+  return TB_OK;
+}
+
 extern "C" int tb_set_atmosphere(tb_ctx *c, int nrad, const double *rad, double rad_fct,
                                  const double *p, double p_fct, const double *t, double t_fct,
                                  const double *density, const double *Z) {

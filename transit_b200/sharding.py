@@ -1,0 +1,32 @@
+"""Wavenumber-band sharding of one spectrum over the GPUs of a box.
+
+One process per GPU.  Every rank holds the whole (layer-independent) line index but owns one
+contiguous band of the coarse wavenumber grid; the only exchanges are the per-layer strength
+maxima / carried Doppler indices (exact integer-ordered maxima, so results are bit-identical to
+the single-GPU run) and the final gather of the spectrum slices.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import api
+
+
+class ShardedTransit(api.Transit):
+    def __init__(self, device=0, rank=0, world=1):
+        super().__init__(device)
+        self.rank, self.world = rank, world
+        if world > 1:
+            raise NotImplementedError("band sharding lands with tb_set_band (next milestone)")
+
+    def set_atmosphere(self, prob):
+        self.ctx.set_atmosphere(prob.rad, prob.rad_fct, prob.p, prob.p_fct, prob.t, prob.t_fct, prob.mol_d, prob.iso_z)
+
+    def sample_counts(self):
+        return self.ctx.sample_counts(self.prob.nrad)
+
+    def ngroups(self):
+        return self.ctx.ngroups()
+
+    def band_nwn(self):
+        return self.ctx.nwn

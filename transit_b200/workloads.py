@@ -114,9 +114,17 @@ def make_problem(name="C2", scale=1.0, nlayers=None, wn_hi=None, wnosamp=None, s
         atm=atm)
 
 
-def write_reference_inputs(prob, outdir, line_fraction=1.0, molfile="/root/reference/inputs/molecules.dat"):
+def write_reference_inputs(prob, outdir, line_fraction=1.0, molfile=None, band=None, tag="run"):
     """The same problem as files for the unmodified reference binary (bench cpu_baseline)."""
     os.makedirs(outdir, exist_ok=True)
+    if molfile is None:
+        # our own molecules.dat in the layout getmoldata parses (readatm.c:625-717):
+        # ID name mass diameter(A) radius-source polarizability description
+        molfile = os.path.join(outdir, "molecules.dat")
+        with open(molfile, "w") as f:
+            f.write("# synthetic molecular info (transit_b200.workloads.MOLDAT)\n")
+            for nm, (mid, mass, diam, pol) in MOLDAT.items():
+                f.write(f" {mid:3d}    {nm:8s} {mass:10.6f}   {diam:5.2f}      01   {pol:8.3f}   {nm}\n")
     dbs = prob.dbs
     if line_fraction < 1.0:
         import copy
@@ -126,8 +134,11 @@ def write_reference_inputs(prob, outdir, line_fraction=1.0, molfile="/root/refer
                 n = max(1, int(len(db.wl[k]) * line_fraction))
                 idx = np.sort(np.random.default_rng(7).choice(len(db.wl[k]), n, replace=False))
                 db.wl[k], db.elow[k], db.gf[k] = db.wl[k][idx], db.elow[k][idx], db.gf[k][idx]
-    wn_f = prob.wn_i + (prob.nwn - 1) * prob.wn_d
-    n = synth.write_tli(os.path.join(outdir, "lines.tli"), dbs, 1e4 / (wn_f + 50), 1e4 / max(prob.wn_i - 50, 1.0))
+    wn_f = wn_full = prob.wn_i + (prob.nwn - 1) * prob.wn_d
+    wn_lo = prob.wn_i
+    if band is not None:          # a contiguous band of the coarse grid [j0, j1] (inclusive ends)
+        wn_lo, wn_f = prob.wn_i + band[0] * prob.wn_d, prob.wn_i + band[1] * prob.wn_d
+    n = synth.write_tli(os.path.join(outdir, "lines.tli"), dbs, 1e4 / (wn_full + 50), 1e4 / max(prob.wn_i - 50, 1.0))
     atm = dict(radius_km=prob.rad, p_bar=prob.p, T=prob.t, q={s: prob.mol_q[j] for j, s in enumerate(prob.species_names)})
     synth.write_atmosphere(os.path.join(outdir, "atm.dat"), atm)
     cs = []
@@ -140,11 +151,11 @@ def write_reference_inputs(prob, outdir, line_fraction=1.0, molfile="/root/refer
                 f.write(f" {tb['wn'][i]:9.2f}    " + " ".join(f"{v:.4e}" for v in tb["tab"][i]) + "\n")
         cs.append(fn)
     cfg = dict(atm=os.path.join(outdir, "atm.dat"), linedb=os.path.join(outdir, "lines.tli"), molfile=molfile,
-               csfile=",".join(cs), wnlow=prob.wn_i, wnhigh=wn_f, wndelt=prob.wn_d, wnosamp=prob.wnosamp,
+               csfile=",".join(cs), wnlow=wn_lo, wnhigh=wn_f, wndelt=prob.wn_d, wnosamp=prob.wnosamp,
                wnfct=1.0, wlfct=1e-4, solution="eclipse" if prob.eclipse else "transit",
                toomuch=prob.toomuch, ethreshold=prob.ethresh, starrad=prob.cfg["starrad"], nwidth=20, verb=0,
-               outspec=os.path.join(outdir, "spec.dat"))
+               outspec=os.path.join(outdir, f"spec_{tag}.dat"))
     if prob.eclipse:
         cfg["raygrid"] = " ".join(str(int(a)) for a in prob.angles)
-    synth.write_cfg(os.path.join(outdir, "run.cfg"), **cfg)
-    return os.path.join(outdir, "run.cfg"), n
+    synth.write_cfg(os.path.join(outdir, f"{tag}.cfg"), **cfg)
+    return os.path.join(outdir, f"{tag}.cfg"), n
