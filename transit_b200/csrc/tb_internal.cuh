@@ -76,9 +76,14 @@ struct DevBuf {
   }
 };
 
-struct ProfEntry {  // one (iso, idop) cell of a state's profile lookup
-  int64_t off;      // offset of the profile in the float table
+// One cell (idop, ilor) of the Voigt table as the line-sum kernels see it.  The profile is
+// stored "polyphase": sample idx of the reference layout lives at off + (idx % o)*nk + idx/o,
+// so the samples one line contributes to consecutive coarse bins (idx, idx+o, idx+2o, ...)
+// are consecutive floats (one coalesced 128-byte read per warp instead of 32 sectors).
+struct ProfEntry {
+  int32_t off;      // offset of the profile in the polyphase float table
   int32_t psize;    // half size in fine samples
+  int32_t nk;       // coarse samples per phase: 2*psize/o + 1
   int32_t pad;
 };
 
@@ -144,7 +149,9 @@ struct tb_ctx {
   DevBuf<double> d_aDop, d_aLor;
   DevBuf<int32_t> d_psize;
   DevBuf<int64_t> d_poff;
-  DevBuf<float> d_pdata;
+  DevBuf<float> d_pdata;      // reference layout (test tap)
+  DevBuf<float> d_pdata2;     // polyphase layout (line sum)
+  DevBuf<ProfEntry> d_ptab;   // [nDop*nLor]
 
   // ---- atmosphere
   bool have_atm = false;
@@ -155,9 +162,9 @@ struct tb_ctx {
 
   // ---- state batch scratch (tb_lines.cu)
   DevBuf<double> s_T, s_dens, s_Z, s_alphal, s_alphad, s_kmax, s_k;
-  DevBuf<int32_t> s_ilor, s_idop0, s_lastq, s_fb, s_psmax;
-  DevBuf<uint8_t> s_pidx;
-  DevBuf<ProfEntry> s_ptab;
+  DevBuf<int32_t> s_ilor, s_idop0, s_lastq, s_fb, s_fbpid, s_wtile, s_reach, s_fbmax;
+  DevBuf<uint16_t> s_pid;     // [state][group] profile cell, PID_SKIP, or PID_FB + isotope
+  DevBuf<uint8_t> s_hasfb;    // [state][tile]
   DevBuf<unsigned long long> s_nsamp;
   DevBuf<double> s_out;
   int last_ns = 0, last_permol = 0;

@@ -18,7 +18,6 @@
 #include <cub/cub.cuh>
 #include "tb_internal.cuh"
 
-#define FB_IDOP 255  // "use the isotope's carried Doppler index" marker in s_pidx
 
 // ------------------------------------------------------------------ upload-time index
 
@@ -274,6 +273,11 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
 
 // ------------------------------------------------------------------ per-state kernels
 
+#define PID_SKIP 0xFFFFu   // group below the strength threshold (extinction.c:467-470)
+#define PID_FB   0x8000u   // + isotope: "use the isotope's carried Doppler index"
+#define ACC_TILE 128       // output bins per block of k_accumulate (4 warps x 32 bins)
+#define MAXISO_SH 128      // isotopes handled with shared-memory maxima in k_strength
+
 // extinction.c:364-395: Lorentz/Doppler widths and their table indices per (state, isotope)
 __global__ void k_state_setup(int ns, int niso, int nmol, const double *__restrict__ T,
                               const double *__restrict__ dens, const double *__restrict__ mol_mass,
@@ -282,12 +286,13 @@ __global__ void k_state_setup(int ns, int niso, int nmol, const double *__restri
                               const double *__restrict__ aLor, int nLor, double wn0,
                               double *__restrict__ alphal, double *__restrict__ alphad,
                               int32_t *__restrict__ ilor, int32_t *__restrict__ idop0,
-                              int32_t *__restrict__ lastq, int32_t *__restrict__ psmax,
-                              double *__restrict__ kmax, int nrows,
-                              unsigned long long *__restrict__ nsamp) {
+                              int32_t *__restrict__ lastq, double *__restrict__ kmax, int nrows,
+                              unsigned long long *__restrict__ nsamp, int32_t *__restrict__ wtile,
+                              uint8_t *__restrict__ hasfb, int ntiles) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < ns * nrows) kmax[t] = 0.0;
-  if (t < ns) { psmax[t] = 0; nsamp[t] = 0ULL; }   // nsamp already points at this chunk
+  if (t < ns) nsamp[t] = 0ULL;   // nsamp already points at this chunk
+  for (int i = t; i < ns * ntiles; i += gridDim.x * blockDim.x) { wtile[i] = -1; hasfb[i] = 0; }
   if (t >= ns * niso) return;
   int s = t / niso, i = t % niso;
   double temp = T[s];
@@ -317,7 +322,9 @@ __device__ __forceinline__ void atomicMaxPosDouble(double *addr, double v) {
 
 // extinction.c:399-427: per-line strength (reference operation order) and its maximum per
 // output row.  One thread per member line, SB states per thread so the 26 B line record is
-// read once per SB states.
+// read once per SB states.  A line whose strength bound g/m/Z (both exponential factors are
+// <= 1 and every rounding is monotone) cannot raise the maximum found so far skips its two
+// exp(): the maximum stays exact, only the amount of work depends on the visiting order.
 template <int SB>
 __global__ void k_kmax(int64_t M, int ns, int niso, const double *__restrict__ m_wavn,
                        const double *__restrict__ m_elow, const double *__restrict__ m_gf,
@@ -325,7 +332,7 @@ __global__ void k_kmax(int64_t M, int ns, int niso, const double *__restrict__ m
                        const double *__restrict__ T, const double *__restrict__ Z,
                        const double *__restrict__ iso_mass, const double *__restrict__ iso_ratio,
                        const int *__restrict__ iso_row, double efct, int permol, int nrows,
-                       double *__restrict__ kmax) {
+                       double *kmax) {
   int64_t l = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   int s0 = blockIdx.y * SB;
   bool act = l < M && m_inr[l];
@@ -339,19 +346,25 @@ __global__ void k_kmax(int64_t M, int ns, int niso, const double *__restrict__ m
     mass = iso_mass[iso];
     row = permol ? iso_row[iso] : 0;
   }
-  // rows differ between lanes, so reduce per row only when a warp is uniform; otherwise go
-  // straight to the (exact) atomic maximum
 #pragma unroll
   for (int k = 0; k < SB; k++) {
     int s = s0 + k;
     if (s >= ns) break;
     double v = 0.0;
     if (act) {
-      double temp = T[s];
-      v = g * exp(a / temp) * (1 - exp(__dmul_rn(-TB_EXPCTE, wavn) / temp)) / mass / Z[s * niso + iso];
+      const double z = Z[s * niso + iso];
+      const double cur = __ldcg(&kmax[s * nrows + row]);      // any stale value is a valid lower bound
+      if (a > 0 || g / mass / z > cur) {
+        double temp = T[s];
+        v = g * exp(a / temp) * (1 - exp(__dmul_rn(-TB_EXPCTE, wavn) / temp)) / mass / z;
+        if (v <= cur) v = 0.0;
+      }
     }
+    // rows differ between lanes, so reduce per row only when a warp is uniform; otherwise go
+    // straight to the (exact) atomic maximum
     unsigned mask = __activemask();
-    int row0 = __shfl_sync(mask, row, 0);
+    if (!__any_sync(mask, v > 0)) continue;
+    int row0 = __shfl_sync(mask, row, __ffs(__ballot_sync(mask, act)) - 1);
     bool uni = __all_sync(mask, (!act) || row == row0);
     if (uni) {
       for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(mask, v, o));
@@ -362,10 +375,13 @@ __global__ void k_kmax(int64_t M, int ns, int niso, const double *__restrict__ m
 }
 
 // extinction.c:439-483 for one (group, state): co-added strength in member order, scaling,
-// threshold, density factor, Doppler-index decision.
+// threshold, density factor, Doppler-index decision.  Output per (state, group): the strength
+// and a 16-bit profile id.  The carried-index and tile-reach maxima are reduced in shared
+// memory first: a handful of global integer atomics per block instead of one per group.
 template <int SB>
 __global__ void k_strength(int64_t G, int ns, int niso, const int32_t *__restrict__ g_start,
                            const int16_t *__restrict__ g_iso, const int32_t *__restrict__ g_orig,
+                           const int32_t *__restrict__ g_idwn,
                            const double *__restrict__ g_wavn, const double *__restrict__ m_wavn,
                            const double *__restrict__ m_elow, const double *__restrict__ m_gf,
                            const double *__restrict__ T, const double *__restrict__ Z,
@@ -374,127 +390,240 @@ __global__ void k_strength(int64_t G, int ns, int niso, const int32_t *__restric
                            const int *__restrict__ iso_imol, const int *__restrict__ iso_row,
                            const double *__restrict__ alphal, const double *__restrict__ alphad,
                            const int32_t *__restrict__ ilor, const double *__restrict__ aDop, int nDop,
-                           const int32_t *__restrict__ psize_tab, int nLor, double efct, double ethresh,
+                           const ProfEntry *__restrict__ ptab, int nLor, double efct, double ethresh,
                            int permol, int nrows, const double *__restrict__ kmax,
-                           double *__restrict__ k_out, uint8_t *__restrict__ pidx,
-                           int32_t *__restrict__ lastq, int32_t *__restrict__ psmax) {
+                           double *__restrict__ k_out, uint16_t *__restrict__ pid_out,
+                           int32_t *__restrict__ lastq, int32_t *__restrict__ wtile,
+                           uint8_t *__restrict__ hasfb, int ntiles) {
+  __shared__ int32_t sh_lastq[SB][MAXISO_SH];
+  const bool use_sh = niso <= MAXISO_SH;
+  if (use_sh) {
+    for (int i = threadIdx.x; i < SB * MAXISO_SH; i += blockDim.x) (&sh_lastq[0][0])[i] = -1;
+    __syncthreads();
+  }
   int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (p >= G) return;
-  int s0 = blockIdx.y * SB;
-  const int iso = g_iso[p];
-  const int b = g_start[p], e = g_start[p + 1];
-  const double wlead = g_wavn[p];
-  const int row = permol ? iso_row[iso] : 0;
-  const double fac0 = __dmul_rn(TB_SIGCTE, iso_ratio[iso]);
-  const double mass = iso_mass[iso];
-  const int imol = iso_imol[iso];
+  const int s0 = blockIdx.y * SB;
+  const bool act = p < G;
+  int iso = 0, b = 0, e = 0, row = 0, imol = 0, tile = 0, orig = 0;
+  double wlead = 0, fac0 = 0, mass = 1;
+  if (act) {
+    iso = g_iso[p];
+    b = g_start[p]; e = g_start[p + 1];
+    wlead = g_wavn[p];
+    row = permol ? iso_row[iso] : 0;
+    fac0 = __dmul_rn(TB_SIGCTE, iso_ratio[iso]);
+    mass = iso_mass[iso];
+    imol = iso_imol[iso];
+    tile = g_idwn[p] / ACC_TILE;
+    orig = g_orig[p];
+  }
+  const unsigned lane = threadIdx.x & 31;
 #pragma unroll 1
   for (int k = 0; k < SB; k++) {
-    int s = s0 + k;
+    const int s = s0 + k;
     if (s >= ns) break;
-    const double temp = T[s];
-    double acc = 0.0;
-    for (int l = b; l < e; l++) {
-      double a = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
-      double term = __dmul_rn(__dmul_rn(m_gf[l], exp(a / temp)),
-                              (1 - exp(__dmul_rn(-TB_EXPCTE, m_wavn[l]) / temp)));
-      acc = (l == b) ? term : __dadd_rn(acc, term);
+    int ps = -1;          // psize of the profile this group will use, when known here
+    bool fbk = false;     // group uses the carried index
+    if (act) {
+      const double temp = T[s];
+      double acc = 0.0;
+      for (int l = b; l < e; l++) {
+        double a = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
+        double term = __dmul_rn(__dmul_rn(m_gf[l], exp(a / temp)),
+                                (1 - exp(__dmul_rn(-TB_EXPCTE, m_wavn[l]) / temp)));
+        acc = (l == b) ? term : __dadd_rn(acc, term);
+      }
+      double kk = __dmul_rn(acc, fac0 / __dmul_rn(mass, Z[s * niso + iso]));
+      const size_t o = (size_t)s * G + p;
+      if (kk < __dmul_rn(ethresh, kmax[s * nrows + row])) {   // extinction.c:467-470
+        pid_out[o] = (uint16_t)PID_SKIP;
+      } else {
+        if (!permol) kk = __dmul_rn(kk, dens[s * nmol + imol]);
+        k_out[o] = kk;
+        const double ad = alphad[s * niso + iso], al = alphal[s * niso + iso];
+        if (__dmul_rn(ad, wlead) / al >= 1e-1) {                 // extinction.c:480-483
+          const int id = tb_binsearchapprox(aDop, __dmul_rn(ad, wlead), 0, nDop);
+          const int cell = id * nLor + ilor[s * niso + iso];
+          pid_out[o] = (uint16_t)cell;
+          ps = ptab[cell].psize;
+          if (use_sh) atomicMax(&sh_lastq[k][iso], orig);
+          else atomicMax(&lastq[s * niso + iso], orig);
+        } else {
+          pid_out[o] = (uint16_t)(PID_FB + iso);
+          fbk = true;
+        }
+      }
     }
-    double kk = __dmul_rn(acc, fac0 / __dmul_rn(mass, Z[s * niso + iso]));
-    size_t o = (size_t)s * G + p;
-    if (kk < __dmul_rn(ethresh, kmax[s * nrows + row])) {   // extinction.c:467-470
-      k_out[o] = -1.0;
-      pidx[o] = FB_IDOP;
-      continue;
+    // widest profile per (state, tile of output bins): one atomic per warp when the warp sits
+    // in one tile (the usual case: groups are sorted by bin)
+    const unsigned full = 0xffffffffu;
+    const int t0 = __shfl_sync(full, tile, 0);
+    const bool uni = __all_sync(full, !act || tile == t0);
+    if (uni) {
+      int m = ps;
+      for (int d = 16; d > 0; d >>= 1) m = max(m, __shfl_xor_sync(full, m, d));
+      const bool anyfb = __any_sync(full, fbk);
+      if (lane == 0) {
+        if (m >= 0) atomicMax(&wtile[s * ntiles + t0], m);
+        if (anyfb) hasfb[s * ntiles + t0] = 1;
+      }
+    } else if (act) {
+      if (ps >= 0) atomicMax(&wtile[s * ntiles + tile], ps);
+      if (fbk) hasfb[s * ntiles + tile] = 1;
     }
-    if (!permol) kk = __dmul_rn(kk, dens[s * nmol + imol]);
-    k_out[o] = kk;
-    const double ad = alphad[s * niso + iso], al = alphal[s * niso + iso];
-    int id = FB_IDOP;
-    if (__dmul_rn(ad, wlead) / al >= 1e-1) {                 // extinction.c:480-483
-      id = tb_binsearchapprox(aDop, __dmul_rn(ad, wlead), 0, nDop);
-      atomicMax(&lastq[s * niso + iso], g_orig[p]);
-      atomicMax(&psmax[s], psize_tab[id * nLor + ilor[s * niso + iso]]);
+  }
+  if (use_sh) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < SB * niso; i += blockDim.x) {
+      const int k = i / niso, is = i % niso, s = s0 + k;
+      const int v = sh_lastq[k][is];
+      if (s < ns && v >= 0) atomicMax(&lastq[s * niso + is], v);
     }
-    pidx[o] = (uint8_t)id;
   }
 }
 
 // carried Doppler index per (state, isotope): the index left by the last evaluated line that
-// refreshed it, else the one computed at wn[0] (extinction.c:393,480-483); plus the profile
-// lookup table of the state.
+// refreshed it, else the one computed at wn[0] (extinction.c:393,480-483).
 __global__ void k_fallback(int ns, int niso, const int32_t *__restrict__ lastq,
                            const int32_t *__restrict__ idop0, const double *__restrict__ go_wavn,
                            const double *__restrict__ alphad, const int32_t *__restrict__ ilor,
                            const double *__restrict__ aDop, int nDop, int nLor,
-                           const int32_t *__restrict__ psize_tab, const int64_t *__restrict__ poff_tab,
-                           int32_t *__restrict__ fb, ProfEntry *__restrict__ ptab,
-                           int32_t *__restrict__ psmax) {
+                           const ProfEntry *__restrict__ ptab, int32_t *__restrict__ fb,
+                           int32_t *__restrict__ fbpid, int32_t *__restrict__ fbmax) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= ns * niso) return;
   int s = t / niso;
   int q = lastq[t];
   int id = (q < 0) ? idop0[t] : tb_binsearchapprox(aDop, __dmul_rn(alphad[t], go_wavn[q]), 0, nDop);
   fb[t] = id;
-  const int il = ilor[t];
-  atomicMax(&psmax[s], psize_tab[id * nLor + il]);
-  for (int d = 0; d < nDop; d++) {
-    ProfEntry pe;
-    pe.off = poff_tab[d * nLor + il];
-    pe.psize = psize_tab[d * nLor + il];
-    pe.pad = 0;
-    ptab[(size_t)t * nDop + d] = pe;
-  }
+  const int cell = id * nLor + ilor[t];
+  fbpid[t] = cell;
+  atomicMax(&fbmax[s], ptab[cell].psize);
 }
 
-// extinction.c:486-509 turned inside out: one thread per (output bin, state) gathers every
-// contributing group from the bin-sorted window [j-W, j+W] of each molecule row, in sorted
-// order: a fixed summation order, no floating-point atomics.
+// reach[s][t]: how many bins to either side an output bin of tile t must look for contributing
+// groups.  A group in coarse bin d with half-size psize touches bins d-(psize+1)/o .. d+1+psize/o.
+__global__ void k_reach(int ns, int ntiles, int o, const int32_t *__restrict__ wtile,
+                        const uint8_t *__restrict__ hasfb, const int32_t *__restrict__ fbmax,
+                        int32_t *__restrict__ reach) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= ns * ntiles) return;
+  const int s = i / ntiles, t = i % ntiles;
+  int R = 0;
+  for (int u = 0; u < ntiles; u++) {
+    int ps = wtile[s * ntiles + u];
+    if (hasfb[s * ntiles + u]) ps = max(ps, fbmax[s]);
+    if (ps < 0) continue;
+    const int w = 1 + (ps + 1) / o;
+    const int du = u > t ? u - t : t - u;
+    const int gap = du == 0 ? 0 : (du - 1) * ACC_TILE + 1;   // closest pair of bins of the two tiles
+    if (w >= gap) R = max(R, w);
+  }
+  reach[i] = R;
+}
+
+// extinction.c:486-509 turned inside out: every output bin gathers its contributing groups
+// from the bin-sorted windows [j-R, j+R] of each molecule row, always in sorted order: a fixed
+// summation order, no floating-point atomics.
 //   contributes  <=>  0 <= o*j - (iown - psize) <= 2*psize   (same test as the reference loop)
-__global__ void k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int nDop, int o, int nrows,
-                             int permol, const int32_t *__restrict__ binstart,
-                             const int32_t *__restrict__ g_iown, const int16_t *__restrict__ g_iso,
-                             const double *__restrict__ k_in, const uint8_t *__restrict__ pidx,
-                             const int32_t *__restrict__ fb, const ProfEntry *__restrict__ ptab,
-                             const int32_t *__restrict__ psmax, const float *__restrict__ pdata,
-                             double *__restrict__ out, unsigned long long *__restrict__ nsamp) {
-  int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  int s = blockIdx.y;
+// A block owns ACC_TILE consecutive bins of one state, a warp 32 of them.  Two schedules with
+// the same summation order:
+//   * narrow reach (R <= NARROW_R): each lane walks its own short window;
+//   * wide reach: the warp walks the union window together -- 32 group records are fetched
+//     coalesced, the survivors broadcast one by one, and lane i adds the sample for bin j0+i,
+//     which the polyphase table layout makes one contiguous 128-byte read per group.
+#define NARROW_R 2
+__global__ void __launch_bounds__(ACC_TILE)
+k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, int nrows, int permol, int ntiles,
+             const int32_t *__restrict__ binstart, const int32_t *__restrict__ g_iown,
+             const double *__restrict__ k_in, const uint16_t *__restrict__ pid_in,
+             const int32_t *__restrict__ fbpid, const ProfEntry *__restrict__ ptab,
+             const int32_t *__restrict__ reach, const float *__restrict__ pdata,
+             double *__restrict__ out, unsigned long long *__restrict__ nsamp) {
+  const int s = blockIdx.y;
+  const int lane = threadIdx.x & 31;
+  const int64_t j0 = (int64_t)blockIdx.x * ACC_TILE + (threadIdx.x & ~31);
+  if (j0 >= nwn) return;                       // whole warp
+  const int64_t j = j0 + lane;
+  const bool inb = j < nwn;
+  const int R = reach[s * ntiles + blockIdx.x];
+  const double *ks = k_in + (size_t)s * G;
+  const uint16_t *ps = pid_in + (size_t)s * G;
+  const int32_t *fbs = fbpid + (size_t)s * niso;
   unsigned long long cnt = 0;
-  if (j < nwn) {
-    const int W = psmax[s] / o + 2;
-    int64_t jlo = j - W < 0 ? 0 : j - W;
-    int64_t jhi = j + W + 1 > nwn ? nwn : j + W + 1;
-    const double *ks = k_in + (size_t)s * G;
-    const uint8_t *ps = pidx + (size_t)s * G;
-    const int64_t oj = (int64_t)o * j;
-    double acc = 0.0;
-    for (int row = 0; row < nrows; row++) {
-      const int32_t *bs = binstart + (size_t)row * nwn;
-      int p0 = bs[jlo], p1 = bs[jhi];
-      for (int p = p0; p < p1; p++) {
-        double k = ks[p];
-        if (k < 0) continue;
-        int iso = g_iso[p];
-        int id = ps[p];
-        if (id == FB_IDOP) id = fb[s * niso + iso];
-        ProfEntry pe = ptab[((size_t)s * niso + iso) * nDop + id];
-        int64_t idx = oj - g_iown[p] + pe.psize;
-        if (idx >= 0 && idx <= 2 * (int64_t)pe.psize) {
-          acc = fma(k, (double)pdata[pe.off + idx], acc);
-          cnt++;
+  double acc = 0.0;
+  for (int row = 0; row < nrows; row++) {
+    const int32_t *bs = binstart + (size_t)row * nwn;
+    if (R <= NARROW_R) {
+      if (inb) {
+        const int64_t jlo = j - R < 0 ? 0 : j - R;
+        const int64_t jhi = j + R + 1 > nwn ? nwn : j + R + 1;
+        const int p1 = bs[jhi];
+        const int oj = (int)(o * j);
+        for (int p = bs[jlo]; p < p1; p++) {
+          unsigned pid = ps[p];
+          if (pid == PID_SKIP) continue;
+          if (pid >= PID_FB) pid = fbs[pid - PID_FB];
+          const ProfEntry pe = ptab[pid];
+          const int idx = oj - g_iown[p] + pe.psize;
+          if (idx >= 0 && idx <= 2 * pe.psize) {
+            const int a = pe.nk == 1 ? idx : (idx % o) * pe.nk + idx / o;
+            acc = fma(ks[p], (double)pdata[pe.off + a], acc);
+            cnt++;
+          }
         }
       }
-      if (permol) {
-        out[((size_t)s * nrows + row) * nwn + j] = acc;
-        acc = 0.0;
+    } else {
+      const int64_t ulo = j0 - R < 0 ? 0 : j0 - R;
+      const int64_t uhi = j0 + 32 + R > nwn ? nwn : j0 + 32 + R;
+      const int p0 = bs[ulo], p1 = bs[uhi];
+      const int oj0 = (int)(o * j0);
+      for (int base = p0; base < p1; base += 32) {
+        const int p = base + lane;
+        unsigned pid = p < p1 ? ps[p] : PID_SKIP;
+        double kk = 0.0;
+        int addr0 = 0, lanes = 0;     // lanes = lo | hi << 8 (valid lane range, empty when lo > hi)
+        bool alive = pid != PID_SKIP;
+        if (alive) {
+          if (pid >= PID_FB) pid = fbs[pid - PID_FB];
+          const ProfEntry pe = ptab[pid];
+          const int idx0 = oj0 - g_iown[p] + pe.psize;           // sample index for lane 0
+          // lanes with 0 <= idx0 + lane*o <= 2*psize
+          int lo = idx0 >= 0 ? 0 : (-idx0 + o - 1) / o;
+          int hi = 2 * pe.psize - idx0;
+          hi = hi < 0 ? -1 : hi / o;
+          if (hi > 31) hi = 31;
+          if (lo > hi) alive = false;
+          else {
+            const int first = idx0 + lo * o;                     // >= 0
+            addr0 = pe.off + (first % o) * pe.nk + first / o - lo;
+            lanes = lo | (hi << 8);
+            kk = ks[p];
+          }
+        }
+        unsigned m = __ballot_sync(0xffffffffu, alive);
+        while (m) {
+          const int src = __ffs(m) - 1;
+          m &= m - 1;
+          const double kb = __shfl_sync(0xffffffffu, kk, src);
+          const int ab = __shfl_sync(0xffffffffu, addr0, src);
+          const int lb = __shfl_sync(0xffffffffu, lanes, src);
+          if (lane >= (lb & 255) && lane <= (lb >> 8) && inb) {
+            acc = fma(kb, (double)pdata[ab + lane], acc);
+            cnt++;
+          }
+        }
       }
     }
-    if (!permol) out[(size_t)s * nwn + j] = acc;
+    if (permol) {
+      if (inb) out[((size_t)s * nrows + row) * nwn + j] = acc;
+      acc = 0.0;
+    }
   }
+  if (!permol && inb) out[(size_t)s * nwn + j] = acc;
   // sample counter (the benchmark's unit of work): integer atomics only
   for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
-  if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(&nsamp[s], cnt);
+  if (lane == 0 && cnt) atomicAdd(&nsamp[s], cnt);
 }
 
 // ------------------------------------------------------------------ host driver
@@ -503,29 +632,33 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
                   double ethresh, int permol, double *d_out_rows, double *h_out) {
   TB_REQUIRE(c->have_lines && c->have_prof, TB_ERR_STATE,
              "tb_upload_lines and tb_build_profiles must precede the line sum");
-  TB_REQUIRE(c->nDop < FB_IDOP, TB_ERR_ARG, "nDop must be < %d", FB_IDOP);
+  TB_REQUIRE(c->niso < (int)(PID_SKIP - PID_FB), TB_ERR_ARG, "too many isotopes (%d)", c->niso);
   TB_CUDA(cudaSetDevice(c->device));
   cudaStream_t st = c->stream;
   const int niso = c->niso, nmol = c->nmol, nrows = c->nrows;
   const int nout = permol ? nrows : 1;
   const int64_t G = c->G, M = c->M, nwn = c->nwn;
+  const int ntiles = (int)((nwn + ACC_TILE - 1) / ACC_TILE);
   c->last_ns = ns;
   c->last_permol = permol;
   // chunk the states so the per-(state, group) scratch stays below ~12 GB
   int chunk = ns;
-  const size_t per_state = (size_t)G * 9 + (size_t)nout * nwn * 8 + 64;
+  const size_t per_state = (size_t)G * 10 + (size_t)nout * nwn * 8 + 64;
   const size_t budget = (size_t)12 << 30;
   if (per_state * chunk > budget) chunk = (int)(budget / per_state);
   if (chunk < 1) chunk = 1;
+  if (chunk > 65535) chunk = 65535;            // gridDim.y
   TB_TRY(c->s_T.ensure(chunk)); TB_TRY(c->s_dens.ensure((size_t)chunk * nmol));
   TB_TRY(c->s_Z.ensure((size_t)chunk * (niso ? niso : 1)));
   TB_TRY(c->s_alphal.ensure((size_t)chunk * niso + 1)); TB_TRY(c->s_alphad.ensure((size_t)chunk * niso + 1));
   TB_TRY(c->s_ilor.ensure((size_t)chunk * niso + 1)); TB_TRY(c->s_idop0.ensure((size_t)chunk * niso + 1));
   TB_TRY(c->s_lastq.ensure((size_t)chunk * niso + 1)); TB_TRY(c->s_fb.ensure((size_t)chunk * niso + 1));
-  TB_TRY(c->s_psmax.ensure(chunk)); TB_TRY(c->s_kmax.ensure((size_t)chunk * nrows + 1));
+  TB_TRY(c->s_fbpid.ensure((size_t)chunk * niso + 1)); TB_TRY(c->s_fbmax.ensure(chunk));
+  TB_TRY(c->s_wtile.ensure((size_t)chunk * ntiles)); TB_TRY(c->s_reach.ensure((size_t)chunk * ntiles));
+  TB_TRY(c->s_hasfb.ensure((size_t)chunk * ntiles));
+  TB_TRY(c->s_kmax.ensure((size_t)chunk * nrows + 1));
   TB_TRY(c->s_nsamp.ensure(ns));
-  TB_TRY(c->s_ptab.ensure((size_t)chunk * niso * c->nDop + 1));
-  TB_TRY(c->s_k.ensure((size_t)chunk * G + 1)); TB_TRY(c->s_pidx.ensure((size_t)chunk * G + 1));
+  TB_TRY(c->s_k.ensure((size_t)chunk * G + 1)); TB_TRY(c->s_pid.ensure((size_t)chunk * G + 1));
   double *d_out = d_out_rows;
   if (!d_out) {
     TB_TRY(c->s_out.ensure((size_t)chunk * nout * nwn));
@@ -545,11 +678,12 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
     double *dst = d_out_rows ? d_out + (size_t)s0 * nout * nwn : d_out;
     int nset = cs * (niso > nrows ? niso : nrows);
     if (nset < cs) nset = cs;
+    TB_CUDA(cudaMemsetAsync(c->s_fbmax.p, 0, cs * sizeof(int32_t), st));
     k_state_setup<<<nblk(nset, 128), 128, 0, st>>>(
         cs, niso, nmol, c->s_T.p, c->s_dens.p, c->d_mol_mass.p, c->d_mol_radius.p, c->d_iso_mass.p,
         c->d_iso_imol.p, c->d_aDop.p, c->nDop, c->d_aLor.p, c->nLor, c->wn_i, c->s_alphal.p,
-        c->s_alphad.p, c->s_ilor.p, c->s_idop0.p, c->s_lastq.p, c->s_psmax.p, c->s_kmax.p, nrows,
-        c->s_nsamp.p + s0);
+        c->s_alphad.p, c->s_ilor.p, c->s_idop0.p, c->s_lastq.p, c->s_kmax.p, nrows,
+        c->s_nsamp.p + s0, c->s_wtile.p, c->s_hasfb.p, ntiles);
     TB_LAUNCHED(c);
     if (G > 0) {
       dim3 g2(nblk(M, Tn), (cs + SB - 1) / SB);
@@ -561,24 +695,26 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       dim3 g3(nblk(G, Tn), (cs + SB - 1) / SB);
       tb_timer_begin(c, "strength");
       k_strength<SB><<<g3, Tn, 0, st>>>(
-          G, cs, niso, c->g_start.p, c->g_iso.p, c->g_orig.p, c->g_wavn.p, c->m_wavn.p, c->m_elow.p,
-          c->m_gf.p, c->s_T.p, c->s_Z.p, c->s_dens.p, nmol, c->d_iso_mass.p, c->d_iso_ratio.p,
-          c->d_iso_imol.p, c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
-          c->nDop, c->d_psize.p, c->nLor, c->efct, ethresh, permol, nrows, c->s_kmax.p, c->s_k.p,
-          c->s_pidx.p, c->s_lastq.p, c->s_psmax.p);
+          G, cs, niso, c->g_start.p, c->g_iso.p, c->g_orig.p, c->g_idwn.p, c->g_wavn.p, c->m_wavn.p,
+          c->m_elow.p, c->m_gf.p, c->s_T.p, c->s_Z.p, c->s_dens.p, nmol, c->d_iso_mass.p,
+          c->d_iso_ratio.p, c->d_iso_imol.p, c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ilor.p,
+          c->d_aDop.p, c->nDop, c->d_ptab.p, c->nLor, c->efct, ethresh, permol, nrows, c->s_kmax.p,
+          c->s_k.p, c->s_pid.p, c->s_lastq.p, c->s_wtile.p, c->s_hasfb.p, ntiles);
       tb_timer_end(c, "strength");
       k_fallback<<<nblk(cs * niso, 128), 128, 0, st>>>(
           cs, niso, c->s_lastq.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
-          c->nDop, c->nLor, c->d_psize.p, c->d_poff.p, c->s_fb.p, c->s_ptab.p, c->s_psmax.p);
+          c->nDop, c->nLor, c->d_ptab.p, c->s_fb.p, c->s_fbpid.p, c->s_fbmax.p);
       c->launches += 3;
     }
-    dim3 g4(nblk(nwn, 128), cs);
+    k_reach<<<nblk((int64_t)cs * ntiles, 128), 128, 0, st>>>(cs, ntiles, c->o, c->s_wtile.p, c->s_hasfb.p,
+                                                             c->s_fbmax.p, c->s_reach.p);
+    dim3 g4(ntiles, cs);
     tb_timer_begin(c, "accumulate");
-    k_accumulate<<<g4, 128, 0, st>>>(nwn, G, cs, niso, c->nDop, c->o, nrows, permol, c->binstart.p,
-                                     c->g_iown.p, c->g_iso.p, c->s_k.p, c->s_pidx.p, c->s_fb.p,
-                                     c->s_ptab.p, c->s_psmax.p, c->d_pdata.p, dst, c->s_nsamp.p + s0);
+    k_accumulate<<<g4, ACC_TILE, 0, st>>>(nwn, G, cs, niso, c->o, nrows, permol, ntiles, c->binstart.p,
+                                          c->g_iown.p, c->s_k.p, c->s_pid.p, c->s_fbpid.p, c->d_ptab.p,
+                                          c->s_reach.p, c->d_pdata2.p, dst, c->s_nsamp.p + s0);
     tb_timer_end(c, "accumulate");
-    TB_LAUNCHED(c);
+    c->launches += 2;
     TB_CUDA(cudaGetLastError());
     if (h_out)
       TB_CUDA(cudaMemcpyAsync(h_out + (size_t)s0 * nout * nwn, dst, (size_t)cs * nout * nwn * sizeof(double),
@@ -627,7 +763,7 @@ extern "C" int tb_get_sample_counts(tb_ctx *c, int64_t *nsamples, int ns) {
 __global__ void k_trace(int64_t n, int64_t G, int s_local, int niso, const uint8_t *__restrict__ flag,
                         const int32_t *__restrict__ l_iown, const int32_t *__restrict__ l_gpos,
                         const int32_t *__restrict__ g_idwn, const int16_t *__restrict__ g_iso,
-                        const double *__restrict__ k_in, const uint8_t *__restrict__ pidx,
+                        const double *__restrict__ k_in, const uint16_t *__restrict__ pidv, int nLor,
                         const int32_t *__restrict__ fb, int32_t *__restrict__ iown,
                         int32_t *__restrict__ idwn, int32_t *__restrict__ idop, int8_t *__restrict__ status) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -639,12 +775,11 @@ __global__ void k_trace(int64_t n, int64_t G, int s_local, int niso, const uint8
     int32_t p = l_gpos[i];
     io = l_iown[i];
     id = g_idwn[p];
-    double k = k_in[(size_t)s_local * G + p];
-    if (k < 0) st = 3;
+    const unsigned pid = pidv[(size_t)s_local * G + p];
+    if (pid == PID_SKIP) st = 3;
     else {
       st = 1;
-      dp = pidx[(size_t)s_local * G + p];
-      if (dp == FB_IDOP) dp = fb[s_local * niso + g_iso[p]];
+      dp = pid >= PID_FB ? fb[s_local * niso + g_iso[p]] : (int)pid / nLor;
     }
   } else if (!(f & 2)) st = 2;     // visited only as a co-added member
   iown[i] = io; idwn[i] = id; idop[i] = dp; status[i] = st;
@@ -664,7 +799,7 @@ extern "C" int tb_get_line_trace(tb_ctx *c, int s, int32_t *iown, int32_t *idwn,
   TB_TRY(a.ensure(n)); TB_TRY(b.ensure(n)); TB_TRY(d.ensure(n)); TB_TRY(e.ensure(n));
   k_trace<<<nblk(n, 256), 256, 0, c->stream>>>(n, c->G, s, c->niso, c->l_flag.p, c->l_iown.p,
                                                c->l_gpos.p, c->g_idwn.p, c->g_iso.p, c->s_k.p,
-                                               c->s_pidx.p, c->s_fb.p, a.p, b.p, d.p, e.p);
+                                               c->s_pid.p, c->nLor, c->s_fb.p, a.p, b.p, d.p, e.p);
   TB_CUDA(cudaMemcpyAsync(iown, a.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
   TB_CUDA(cudaMemcpyAsync(idwn, b.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
   TB_CUDA(cudaMemcpyAsync(idop, d.p, n * 4, cudaMemcpyDeviceToHost, c->stream));

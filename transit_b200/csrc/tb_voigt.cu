@@ -108,6 +108,21 @@ __global__ void k_voigt_table(const ProfDesc *__restrict__ desc, int nprof, floa
   out[d.off + k] = res;
 }
 
+// reference layout -> polyphase layout (see ProfEntry)
+__global__ void k_polyphase(const ProfDesc *__restrict__ desc, const int32_t *__restrict__ off2,
+                            int nprof, int o, const float *__restrict__ in, float *__restrict__ out) {
+  int lo = 0, hi = nprof - 1;
+  while (lo < hi) {
+    int mid = (lo + hi + 1) >> 1;
+    if (desc[mid].blk0 <= (int64_t)blockIdx.x) lo = mid; else hi = mid - 1;
+  }
+  const ProfDesc d = desc[lo];
+  const int64_t k = ((int64_t)blockIdx.x - d.blk0) * blockDim.x + threadIdx.x;
+  if (k >= d.nwn) return;
+  const int nk = (d.nwn - 1) / o + 1;
+  out[off2[lo] + (k % o) * (int64_t)nk + k / o] = in[d.off + k];
+}
+
 // getprofile's size rule (extinction.c:21-35) with the reference's float narrowing of the widths
 static int64_t prof_half_size(double dwn, float dop, float lor, float ta, int64_t nwave) {
   double bigalpha = dop;
@@ -122,7 +137,7 @@ static int64_t prof_half_size(double dwn, float dop, float lor, float ta, int64_
 extern "C" int tb_build_profiles(tb_ctx *c, int nDop, int nLor, float dmin, float dmax, float lmin,
                                  float lmax, float nwidth) {
   TB_REQUIRE(c->have_grid, TB_ERR_STATE, "tb_set_wn_grid must precede tb_build_profiles");
-  TB_REQUIRE(nDop >= 2 && nLor >= 2 && nDop < 255, TB_ERR_ARG, "need 2 <= nDop < 255 and nLor >= 2");
+  TB_REQUIRE(nDop >= 2 && nLor >= 2 && (int64_t)nDop * nLor < 32768, TB_ERR_ARG, "need nDop, nLor >= 2 and nDop*nLor < 32768");
   TB_REQUIRE(dmin > 0 && dmax > dmin && lmin > 0 && lmax > lmin && nwidth > 0, TB_ERR_ARG,
              "bad width ranges");
   TB_CUDA(cudaSetDevice(c->device));
@@ -190,13 +205,39 @@ extern "C" int tb_build_profiles(tb_ctx *c, int nDop, int nLor, float dmin, floa
       blocks += (d.nwn + TPB - 1) / TPB;
     }
   c->ndata = total;
+  // polyphase copy: min(o, n) phases of nk = (n-1)/o + 1 samples each per unique profile
+  std::vector<int32_t> off2(desc.size());
+  std::vector<ProfEntry> ptab((size_t)nDop * nLor);
+  int64_t total2 = 0;
+  {
+    std::map<int64_t, size_t> by_off;
+    for (size_t k = 0; k < desc.size(); k++) {
+      const int64_t n = desc[k].nwn, nk = (n - 1) / c->o + 1, nph = n < c->o ? n : c->o;
+      TB_REQUIRE(total2 < 2000000000LL, TB_ERR_ARG, "Voigt table too large for 32-bit offsets");
+      off2[k] = (int32_t)total2;
+      by_off[desc[k].off] = k;
+      total2 += nk * nph;
+    }
+    TB_REQUIRE(total2 < 2000000000LL, TB_ERR_ARG, "Voigt table too large for 32-bit offsets");
+    for (size_t cell = 0; cell < ptab.size(); cell++) {
+      const size_t k = by_off[c->poff[cell]];
+      ptab[cell].off = off2[k];
+      ptab[cell].psize = (int32_t)c->psize[cell];
+      ptab[cell].nk = (int32_t)((2 * c->psize[cell]) / c->o + 1);
+      ptab[cell].pad = 0;
+    }
+  }
   TB_REQUIRE(blocks < 2147483647LL, TB_ERR_ARG, "Voigt table too large for one launch");
   std::vector<int32_t> ps32(c->psize.begin(), c->psize.end());
   TB_TRY(c->d_aDop.ensure(nDop + 1)); TB_TRY(c->d_aLor.ensure(nLor + 1));
   TB_TRY(c->d_psize.ensure(ps32.size())); TB_TRY(c->d_poff.ensure(c->poff.size()));
   TB_TRY(c->d_pdata.ensure(total));
+  TB_TRY(c->d_pdata2.ensure(total2 + 32));
+  TB_TRY(c->d_ptab.ensure(ptab.size()));
   DevBuf<ProfDesc> d_desc;
+  DevBuf<int32_t> d_off2;
   TB_TRY(d_desc.ensure(desc.size()));
+  TB_TRY(d_off2.ensure(off2.size()));
   cudaStream_t st = c->stream;
   TB_CUDA(cudaMemcpyToSymbolAsync(c_ferf, h_ferf, sizeof(h_ferf), 0, cudaMemcpyHostToDevice, st));
   TB_CUDA(cudaMemcpyAsync(c->d_aDop.p, c->aDop.data(), (nDop + 1) * sizeof(double), cudaMemcpyHostToDevice, st));
@@ -204,13 +245,19 @@ extern "C" int tb_build_profiles(tb_ctx *c, int nDop, int nLor, float dmin, floa
   TB_CUDA(cudaMemcpyAsync(c->d_psize.p, ps32.data(), ps32.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
   TB_CUDA(cudaMemcpyAsync(c->d_poff.p, c->poff.data(), c->poff.size() * sizeof(int64_t), cudaMemcpyHostToDevice, st));
   TB_CUDA(cudaMemcpyAsync(d_desc.p, desc.data(), desc.size() * sizeof(ProfDesc), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(d_off2.p, off2.data(), off2.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(c->d_ptab.p, ptab.data(), ptab.size() * sizeof(ProfEntry), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemsetAsync(c->d_pdata2.p, 0, (total2 + 32) * sizeof(float), st));
   tb_timer_begin(c, "voigt");
   k_voigt_table<<<(unsigned)blocks, TPB, 0, st>>>(d_desc.p, (int)desc.size(), c->d_pdata.p);
   tb_timer_end(c, "voigt");
-  TB_LAUNCHED(c);
+  k_polyphase<<<(unsigned)blocks, TPB, 0, st>>>(d_desc.p, d_off2.p, (int)desc.size(), c->o, c->d_pdata.p,
+                                                c->d_pdata2.p);
+  c->launches += 2;
   TB_CUDA(cudaGetLastError());
   TB_CUDA(cudaStreamSynchronize(st));
   d_desc.release();
+  d_off2.release();
   c->aDop.resize(nDop);
   c->aLor.resize(nLor);
   c->have_prof = true;
