@@ -150,7 +150,7 @@ struct tb_ctx {
   DevBuf<int32_t> d_psize;
   DevBuf<int64_t> d_poff;
   DevBuf<float> d_pdata;      // reference layout (test tap)
-  DevBuf<float> d_pdata2;     // polyphase layout (line sum)
+  DevBuf<double> d_pdata2;    // polyphase layout, widened to double (line sum)
   DevBuf<ProfEntry> d_ptab;   // [nDop*nLor]
 
   // ---- atmosphere
@@ -162,7 +162,8 @@ struct tb_ctx {
 
   // ---- state batch scratch (tb_lines.cu)
   DevBuf<double> s_T, s_dens, s_Z, s_alphal, s_alphad, s_kmax, s_k;
-  DevBuf<int32_t> s_ilor, s_idop0, s_lastq, s_fb, s_fbpid, s_wtile, s_reach, s_fbmax;
+  DevBuf<int32_t> s_ilor, s_idop0, s_lastq, s_fb, s_fbpid, s_wtile, s_reach, s_reachP, s_fbmax;
+  DevBuf<double> s_facz, s_rtemp;
   DevBuf<uint16_t> s_pid;     // [state][group] profile cell, PID_SKIP, or PID_FB + isotope
   DevBuf<uint8_t> s_hasfb;    // [state][tile]
   DevBuf<unsigned long long> s_nsamp;

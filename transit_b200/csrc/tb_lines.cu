@@ -82,15 +82,17 @@ __global__ void k_leader_flags(const uint8_t *__restrict__ flag, int64_t n, uint
 // per group (original order): sort key and size; also the sortedness check
 __global__ void k_group_keys(const int32_t *__restrict__ lead, int64_t G, const double *__restrict__ wavn,
                              const int16_t *__restrict__ iso, const int32_t *__restrict__ next,
-                             const int *__restrict__ iso_row, double wn_i, double dwn, int64_t nwn,
-                             int32_t *__restrict__ key, int32_t *__restrict__ size,
-                             double *__restrict__ go_wavn, int32_t *__restrict__ err) {
+                             const int *__restrict__ iso_row, const int32_t *__restrict__ iown,
+                             double wn_i, double dwn, int64_t onwn,
+                             uint64_t *__restrict__ key, int32_t *__restrict__ idwn_out,
+                             int32_t *__restrict__ size, double *__restrict__ go_wavn,
+                             int32_t *__restrict__ err) {
   int64_t g = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (g >= G) return;
   int32_t L = lead[g];
   double w = wavn[L];
-  int32_t idwn = (int32_t)__ddiv_rn(__dsub_rn(w, wn_i), dwn);   // extinction.c:476
-  key[g] = iso_row[iso[L]] * (int32_t)nwn + idwn;
+  idwn_out[g] = (int32_t)__ddiv_rn(__dsub_rn(w, wn_i), dwn);    // extinction.c:476
+  key[g] = (uint64_t)iso_row[iso[L]] * (uint64_t)onwn + (uint64_t)iown[L];
   size[g] = next[L] - L;
   go_wavn[g] = w;
   if (g + 1 < G) {
@@ -100,7 +102,7 @@ __global__ void k_group_keys(const int32_t *__restrict__ lead, int64_t G, const 
 }
 
 // scatter groups and their member lines into bin-sorted order
-__global__ void k_group_fill(const int32_t *__restrict__ order, const int32_t *__restrict__ key_sorted,
+__global__ void k_group_fill(const int32_t *__restrict__ order, const int32_t *__restrict__ idwn_orig,
                              const int32_t *__restrict__ gstart, int64_t G,
                              const int32_t *__restrict__ lead, const int32_t *__restrict__ next,
                              const double *__restrict__ wavn, const double *__restrict__ elow,
@@ -116,7 +118,7 @@ __global__ void k_group_fill(const int32_t *__restrict__ order, const int32_t *_
   if (p >= G) return;
   int32_t g = order[p], L = lead[g], E = next[L], s = gstart[p];
   g_iown[p] = iown[L];
-  g_idwn[p] = key_sorted[p] % (int32_t)nwn;
+  g_idwn[p] = idwn_orig[g];
   g_orig[p] = g;
   g_iso[p] = iso[L];
   g_wavn[p] = wavn[L];
@@ -130,15 +132,17 @@ __global__ void k_group_fill(const int32_t *__restrict__ order, const int32_t *_
   }
 }
 
-// binstart[row][j] = first sorted group with key >= row*nwn + j
-__global__ void k_binstart(const int32_t *__restrict__ key_sorted, int64_t G, int64_t nkeys,
-                           int32_t *__restrict__ binstart) {
+// binstart[row][j] = first sorted group of `row` whose fine bin is >= o*j (groups are sorted by
+// (row, fine bin), so the groups centred in coarse cell j are binstart[row][j] .. [j+1])
+__global__ void k_binstart(const uint64_t *__restrict__ key_sorted, int64_t G, int64_t nkeys, int64_t nwn,
+                           int64_t onwn, int o, int32_t *__restrict__ binstart) {
   int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (k > nkeys) return;
+  const uint64_t want = (uint64_t)(k / nwn) * (uint64_t)onwn + (uint64_t)(k % nwn) * (uint64_t)o;
   int64_t lo = 0, hi = G;
   while (lo < hi) {
     int64_t mid = (lo + hi) >> 1;
-    if (key_sorted[mid] < k) lo = mid + 1; else hi = mid;
+    if (key_sorted[mid] < want) lo = mid + 1; else hi = mid;
   }
   binstart[k] = (int32_t)lo;
 }
@@ -168,7 +172,8 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
   }
   DevBuf<double> d_wl, d_wavn, d_elow, d_gf;
   DevBuf<int16_t> d_iso;
-  DevBuf<int32_t> nxt, jA, jB, lead, key, key_s, ord, ord_s, size, size_s, ngrp;
+  DevBuf<int32_t> nxt, jA, jB, lead, idw, ord, ord_s, size, size_s, ngrp;
+  DevBuf<uint64_t> key, key_s;
   DevBuf<uint8_t> isl;
   TB_TRY(d_wl.ensure(n)); TB_TRY(d_wavn.ensure(n)); TB_TRY(d_elow.ensure(n)); TB_TRY(d_gf.ensure(n));
   TB_TRY(d_iso.ensure(n)); TB_TRY(nxt.ensure(n)); TB_TRY(jA.ensure(n)); TB_TRY(jB.ensure(n));
@@ -218,14 +223,15 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
     c->have_lines = true;
     return TB_OK;
   }
-  TB_TRY(key.ensure(G)); TB_TRY(key_s.ensure(G)); TB_TRY(ord.ensure(G)); TB_TRY(ord_s.ensure(G));
+  TB_TRY(key.ensure(G)); TB_TRY(key_s.ensure(G)); TB_TRY(ord.ensure(G)); TB_TRY(ord_s.ensure(G)); TB_TRY(idw.ensure(G));
   TB_TRY(size.ensure(G)); TB_TRY(size_s.ensure(G)); TB_TRY(c->go_wavn.ensure(G));
-  k_group_keys<<<nblk(G, T), T, 0, st>>>(lead.p, G, d_wavn.p, d_iso.p, nxt.p, c->d_iso_row.p, c->wn_i,
-                                         c->wn_d, c->nwn, key.p, size.p, c->go_wavn.p, c->d_err.p);
+  k_group_keys<<<nblk(G, T), T, 0, st>>>(lead.p, G, d_wavn.p, d_iso.p, nxt.p, c->d_iso_row.p, c->l_iown.p,
+                                         c->wn_i, c->wn_d, c->onwn, key.p, idw.p, size.p, c->go_wavn.p,
+                                         c->d_err.p);
   // stable sort of (key, original group index): equal keys keep the reference's line order
   k_iota<<<nblk(G, T), T, 0, st>>>(ord.p, G);
   int end_bit = 1;
-  while ((1LL << end_bit) < nkeys + 1 && end_bit < 31) end_bit++;
+  while (end_bit < 63 && (1ULL << end_bit) < (uint64_t)c->nrows * (uint64_t)c->onwn + 1) end_bit++;
   tmpb = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, tmpb, key.p, key_s.p, ord.p, ord_s.p, (int)G, 0, end_bit, st);
   TB_TRY(c->cub_tmp.ensure(tmpb));
@@ -256,17 +262,17 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
   TB_TRY(c->m_iso.ensure(M)); TB_TRY(c->m_inr.ensure(M));
   TB_TRY(c->g_iown.ensure(G)); TB_TRY(c->g_idwn.ensure(G)); TB_TRY(c->g_orig.ensure(G));
   TB_TRY(c->g_iso.ensure(G)); TB_TRY(c->g_wavn.ensure(G));
-  k_group_fill<<<nblk(G, T), T, 0, st>>>(ord_s.p, key_s.p, c->g_start.p, G, lead.p, nxt.p, d_wavn.p,
+  k_group_fill<<<nblk(G, T), T, 0, st>>>(ord_s.p, idw.p, c->g_start.p, G, lead.p, nxt.p, d_wavn.p,
                                          d_elow.p, d_gf.p, d_iso.p, c->l_iown.p, c->l_flag.p, c->nwn,
                                          c->g_iown.p, c->g_idwn.p, c->g_orig.p, c->g_iso.p,
                                          c->g_wavn.p, c->m_wavn.p, c->m_elow.p, c->m_gf.p, c->m_iso.p,
                                          c->m_inr.p, c->l_gpos.p);
-  k_binstart<<<nblk(nkeys + 1, T), T, 0, st>>>(key_s.p, G, nkeys, c->binstart.p);
+  k_binstart<<<nblk(nkeys + 1, T), T, 0, st>>>(key_s.p, G, nkeys, c->nwn, c->onwn, c->o, c->binstart.p);
   c->launches += 8;
   TB_CUDA(cudaStreamSynchronize(st));
   d_wl.release(); d_wavn.release(); d_elow.release(); d_gf.release(); d_iso.release();
   nxt.release(); jA.release(); jB.release(); lead.release(); key.release(); key_s.release();
-  ord.release(); ord_s.release(); size.release(); size_s.release(); ngrp.release(); isl.release();
+  ord.release(); ord_s.release(); idw.release(); size.release(); size_s.release(); ngrp.release(); isl.release();
   c->have_lines = true;
   return TB_OK;
 }
@@ -278,6 +284,15 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
 #define ACC_TILE 128       // output bins per block of k_accumulate (4 warps x 32 bins)
 #define MAXISO_SH 128      // isotopes handled with shared-memory maxima in k_strength
 
+// exact x / d for 0 <= x < 2^32 by one 64x64->high multiply (d fixed per context)
+struct FastDiv {
+  uint64_t M;
+  int d;
+};
+__device__ __forceinline__ int fd_div(int x, const FastDiv f) {
+  return f.d == 1 ? x : (int)__umul64hi((uint64_t)(unsigned)x, f.M);
+}
+
 // extinction.c:364-395: Lorentz/Doppler widths and their table indices per (state, isotope)
 __global__ void k_state_setup(int ns, int niso, int nmol, const double *__restrict__ T,
                               const double *__restrict__ dens, const double *__restrict__ mol_mass,
@@ -288,10 +303,12 @@ __global__ void k_state_setup(int ns, int niso, int nmol, const double *__restri
                               int32_t *__restrict__ ilor, int32_t *__restrict__ idop0,
                               int32_t *__restrict__ lastq, double *__restrict__ kmax, int nrows,
                               unsigned long long *__restrict__ nsamp, int32_t *__restrict__ wtile,
-                              uint8_t *__restrict__ hasfb, int ntiles) {
+                              uint8_t *__restrict__ hasfb, int ntiles, const double *__restrict__ Z,
+                              const double *__restrict__ iso_ratio, double *__restrict__ facz,
+                              double *__restrict__ rtemp) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < ns * nrows) kmax[t] = 0.0;
-  if (t < ns) nsamp[t] = 0ULL;   // nsamp already points at this chunk
+  if (t < ns) { nsamp[t] = 0ULL; rtemp[t] = 1.0 / T[t]; }   // nsamp already points at this chunk
   for (int i = t; i < ns * ntiles; i += gridDim.x * blockDim.x) { wtile[i] = -1; hasfb[i] = 0; }
   if (t >= ns * niso) return;
   int s = t / niso, i = t % niso;
@@ -313,6 +330,8 @@ __global__ void k_state_setup(int ns, int niso, int nmol, const double *__restri
   idop0[t] = tb_binsearchapprox(aDop, __dmul_rn(ad, wn0), 0, nDop);
   ilor[t] = tb_binsearchapprox(aLor, al, 0, nLor);
   lastq[t] = -1;
+  // the state- and isotope-dependent factor of extinction.c:464-465
+  facz[t] = __dmul_rn(TB_SIGCTE, iso_ratio[i]) / __dmul_rn(iso_mass[i], Z[t]);
 }
 
 __device__ __forceinline__ void atomicMaxPosDouble(double *addr, double v) {
@@ -320,57 +339,71 @@ __device__ __forceinline__ void atomicMaxPosDouble(double *addr, double v) {
   atomicMax((unsigned long long *)addr, (unsigned long long)__double_as_longlong(v));
 }
 
-// extinction.c:399-427: per-line strength (reference operation order) and its maximum per
-// output row.  One thread per member line, SB states per thread so the 26 B line record is
-// read once per SB states.  A line whose strength bound g/m/Z (both exponential factors are
-// <= 1 and every rounding is monotone) cannot raise the maximum found so far skips its two
-// exp(): the maximum stays exact, only the amount of work depends on the visiting order.
+// extinction.c:399-427: per-line strength and its maximum per output row.  One thread per
+// member line, SB states per thread so the 26 B line record is read once per SB states.  A line
+// whose strength bound g/m/Z (both exponential factors are <= 1 and every rounding is
+// monotone) cannot raise the maximum found so far skips its two exp(): the maximum stays
+// exact, only the amount of work depends on the visiting order.
+#define KMAX_ROWS 16   // output rows reduced in shared memory (more rows: straight to global)
 template <int SB>
 __global__ void k_kmax(int64_t M, int ns, int niso, const double *__restrict__ m_wavn,
                        const double *__restrict__ m_elow, const double *__restrict__ m_gf,
                        const int16_t *__restrict__ m_iso, const uint8_t *__restrict__ m_inr,
-                       const double *__restrict__ T, const double *__restrict__ Z,
+                       const double *__restrict__ rtemp, const double *__restrict__ Z,
                        const double *__restrict__ iso_mass, const double *__restrict__ iso_ratio,
                        const int *__restrict__ iso_row, double efct, int permol, int nrows,
                        double *kmax) {
+  // the running maxima are read once per block (not per warp: every warp of the chip asking
+  // one L2 slice for the same sector serialises there) and merged back once per block
+  __shared__ unsigned long long sh_cur[SB][KMAX_ROWS], sh_new[SB][KMAX_ROWS];
+  const int s0 = blockIdx.y * SB;
+  const bool use_sh = nrows <= KMAX_ROWS;
+  if (use_sh) {
+    for (int i = threadIdx.x; i < SB * nrows; i += blockDim.x) {
+      const int k = i / nrows, r = i % nrows, s = s0 + k;
+      const unsigned long long v = s < ns ? __ldcg((const unsigned long long *)&kmax[s * nrows + r]) : 0ULL;
+      sh_cur[k][r] = v;
+      sh_new[k][r] = v;
+    }
+    __syncthreads();
+  }
   int64_t l = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  int s0 = blockIdx.y * SB;
   bool act = l < M && m_inr[l];
   int iso = 0, row = 0;
-  double wavn = 0, a = 0, g = 0, mass = 1;
+  double a = 0, w = 0, g = 0, mass = 1;
   if (act) {
     iso = m_iso[l];
-    wavn = m_wavn[l];
+    w = __dmul_rn(-TB_EXPCTE, m_wavn[l]);
     a = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
     g = __dmul_rn(__dmul_rn(iso_ratio[iso], TB_SIGCTE), m_gf[l]);
     mass = iso_mass[iso];
     row = permol ? iso_row[iso] : 0;
   }
+  if (act) {
 #pragma unroll
-  for (int k = 0; k < SB; k++) {
-    int s = s0 + k;
-    if (s >= ns) break;
-    double v = 0.0;
-    if (act) {
+    for (int k = 0; k < SB; k++) {
+      const int s = s0 + k;
+      if (s >= ns) break;
+      const double cur = use_sh ? __longlong_as_double((long long)sh_cur[k][row]) : __ldcg(&kmax[s * nrows + row]);
       const double z = Z[s * niso + iso];
-      const double cur = __ldcg(&kmax[s * nrows + row]);      // any stale value is a valid lower bound
-      if (a > 0 || g / mass / z > cur) {
-        double temp = T[s];
-        v = g * exp(a / temp) * (1 - exp(__dmul_rn(-TB_EXPCTE, wavn) / temp)) / mass / z;
-        if (v <= cur) v = 0.0;
+      // g/mass/z <= cur  <=  g < (1-1e-10)*cur*mass*z: no division on the (usual) skip path
+      if (a > 0 || !(g < 0.9999999999 * cur * mass * z)) {
+        const double rT = rtemp[s];
+        const double v = g * exp(a * rT) * (1 - exp(w * rT)) / mass / z;
+        if (v > cur) {
+          if (use_sh) atomicMax(&sh_new[k][row], (unsigned long long)__double_as_longlong(v));
+          else atomicMaxPosDouble(&kmax[s * nrows + row], v);
+        }
       }
     }
-    // rows differ between lanes, so reduce per row only when a warp is uniform; otherwise go
-    // straight to the (exact) atomic maximum
-    unsigned mask = __activemask();
-    if (!__any_sync(mask, v > 0)) continue;
-    int row0 = __shfl_sync(mask, row, __ffs(__ballot_sync(mask, act)) - 1);
-    bool uni = __all_sync(mask, (!act) || row == row0);
-    if (uni) {
-      for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(mask, v, o));
-      if ((threadIdx.x & 31) == 0 && v > 0) atomicMaxPosDouble(&kmax[s * nrows + row0], v);
-    } else if (act && v > 0)
-      atomicMaxPosDouble(&kmax[s * nrows + row], v);
+  }
+  if (use_sh) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < SB * nrows; i += blockDim.x) {
+      const int k = i / nrows, r = i % nrows, s = s0 + k;
+      if (s < ns && sh_new[k][r] > sh_cur[k][r])
+        atomicMax((unsigned long long *)&kmax[s * nrows + r], sh_new[k][r]);
+    }
   }
 }
 
@@ -379,14 +412,14 @@ __global__ void k_kmax(int64_t M, int ns, int niso, const double *__restrict__ m
 // and a 16-bit profile id.  The carried-index and tile-reach maxima are reduced in shared
 // memory first: a handful of global integer atomics per block instead of one per group.
 template <int SB>
-__global__ void k_strength(int64_t G, int ns, int niso, const int32_t *__restrict__ g_start,
+__global__ void k_strength(int64_t G, int ns, int niso, int o, FastDiv fd_tile,
+                           const int32_t *__restrict__ g_start,
                            const int16_t *__restrict__ g_iso, const int32_t *__restrict__ g_orig,
-                           const int32_t *__restrict__ g_idwn,
+                           const int32_t *__restrict__ g_iown,
                            const double *__restrict__ g_wavn, const double *__restrict__ m_wavn,
                            const double *__restrict__ m_elow, const double *__restrict__ m_gf,
-                           const double *__restrict__ T, const double *__restrict__ Z,
+                           const double *__restrict__ rtemp, const double *__restrict__ facz,
                            const double *__restrict__ dens, int nmol,
-                           const double *__restrict__ iso_mass, const double *__restrict__ iso_ratio,
                            const int *__restrict__ iso_imol, const int *__restrict__ iso_row,
                            const double *__restrict__ alphal, const double *__restrict__ alphad,
                            const int32_t *__restrict__ ilor, const double *__restrict__ aDop, int nDop,
@@ -396,28 +429,33 @@ __global__ void k_strength(int64_t G, int ns, int niso, const int32_t *__restric
                            int32_t *__restrict__ lastq, int32_t *__restrict__ wtile,
                            uint8_t *__restrict__ hasfb, int ntiles) {
   __shared__ int32_t sh_lastq[SB][MAXISO_SH];
+  __shared__ double sh_aDop[256];
   const bool use_sh = niso <= MAXISO_SH;
-  if (use_sh) {
+  if (use_sh)
     for (int i = threadIdx.x; i < SB * MAXISO_SH; i += blockDim.x) (&sh_lastq[0][0])[i] = -1;
-    __syncthreads();
-  }
+  for (int i = threadIdx.x; i <= nDop; i += blockDim.x) sh_aDop[i] = aDop[i];   // [nDop] = +inf sentinel
+  __syncthreads();
   int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   const int s0 = blockIdx.y * SB;
   const bool act = p < G;
   int iso = 0, b = 0, e = 0, row = 0, imol = 0, tile = 0, orig = 0;
-  double wlead = 0, fac0 = 0, mass = 1;
+  double wlead = 0, a0 = 0, w0 = 0, g0 = 0;
   if (act) {
     iso = g_iso[p];
     b = g_start[p]; e = g_start[p + 1];
     wlead = g_wavn[p];
     row = permol ? iso_row[iso] : 0;
-    fac0 = __dmul_rn(TB_SIGCTE, iso_ratio[iso]);
-    mass = iso_mass[iso];
     imol = iso_imol[iso];
-    tile = g_idwn[p] / ACC_TILE;
+    tile = fd_div(g_iown[p], fd_tile);          // fine bin / (o * ACC_TILE)
     orig = g_orig[p];
+    a0 = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[b]);
+    w0 = __dmul_rn(-TB_EXPCTE, m_wavn[b]);
+    g0 = m_gf[b];
   }
   const unsigned lane = threadIdx.x & 31;
+  const unsigned full = 0xffffffffu;
+  const int t0 = __shfl_sync(full, tile, 0);
+  const bool uni = __all_sync(full, !act || tile == t0);
 #pragma unroll 1
   for (int k = 0; k < SB; k++) {
     const int s = s0 + k;
@@ -425,40 +463,43 @@ __global__ void k_strength(int64_t G, int ns, int niso, const int32_t *__restric
     int ps = -1;          // psize of the profile this group will use, when known here
     bool fbk = false;     // group uses the carried index
     if (act) {
-      const double temp = T[s];
-      double acc = 0.0;
-      for (int l = b; l < e; l++) {
-        double a = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
-        double term = __dmul_rn(__dmul_rn(m_gf[l], exp(a / temp)),
-                                (1 - exp(__dmul_rn(-TB_EXPCTE, m_wavn[l]) / temp)));
-        acc = (l == b) ? term : __dadd_rn(acc, term);
+      const double rT = rtemp[s];
+      double acc = __dmul_rn(__dmul_rn(g0, exp(a0 * rT)), (1 - exp(w0 * rT)));
+      for (int l = b + 1; l < e; l++) {                        // co-added members (extinction.c:449-462)
+        const double a = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
+        const double term = __dmul_rn(__dmul_rn(m_gf[l], exp(a * rT)),
+                                      (1 - exp(__dmul_rn(-TB_EXPCTE, m_wavn[l]) * rT)));
+        acc = __dadd_rn(acc, term);
       }
-      double kk = __dmul_rn(acc, fac0 / __dmul_rn(mass, Z[s * niso + iso]));
-      const size_t o = (size_t)s * G + p;
-      if (kk < __dmul_rn(ethresh, kmax[s * nrows + row])) {   // extinction.c:467-470
-        pid_out[o] = (uint16_t)PID_SKIP;
-      } else {
+      const int si = s * niso + iso;
+      double kk = __dmul_rn(acc, facz[si]);
+      const size_t oo = (size_t)s * G + p;
+      unsigned pid = PID_SKIP;
+      if (!(kk < __dmul_rn(ethresh, kmax[s * nrows + row]))) {   // extinction.c:467-470
         if (!permol) kk = __dmul_rn(kk, dens[s * nmol + imol]);
-        k_out[o] = kk;
-        const double ad = alphad[s * niso + iso], al = alphal[s * niso + iso];
-        if (__dmul_rn(ad, wlead) / al >= 1e-1) {                 // extinction.c:480-483
-          const int id = tb_binsearchapprox(aDop, __dmul_rn(ad, wlead), 0, nDop);
-          const int cell = id * nLor + ilor[s * niso + iso];
-          pid_out[o] = (uint16_t)cell;
-          ps = ptab[cell].psize;
+        const double al = alphal[si], adw = __dmul_rn(alphad[si], wlead);
+        // extinction.c:480-483: alphad*wavn/alphal >= 0.1, decided by the exact quotient
+        if (adw / al >= 1e-1) {
+          int lo = 0, hi = nDop;                                  // binsearchapprox (iomisc.c:1088-1108)
+          while (hi - lo > 1) {
+            const int mid = (hi + lo) >> 1;
+            if (sh_aDop[mid] > adw) hi = mid; else lo = mid;
+          }
+          const int id = (fabs(sh_aDop[hi] - adw) < fabs(sh_aDop[lo] - adw)) ? hi : lo;
+          pid = id * nLor + ilor[si];
+          ps = ptab[pid].psize;
           if (use_sh) atomicMax(&sh_lastq[k][iso], orig);
-          else atomicMax(&lastq[s * niso + iso], orig);
+          else atomicMax(&lastq[si], orig);
         } else {
-          pid_out[o] = (uint16_t)(PID_FB + iso);
+          pid = PID_FB + iso;
           fbk = true;
         }
-      }
+      } else kk = 0.0;
+      k_out[oo] = kk;                 // written for skipped groups too: whole sectors, no fill reads
+      pid_out[oo] = (uint16_t)pid;
     }
     // widest profile per (state, tile of output bins): one atomic per warp when the warp sits
-    // in one tile (the usual case: groups are sorted by bin)
-    const unsigned full = 0xffffffffu;
-    const int t0 = __shfl_sync(full, tile, 0);
-    const bool uni = __all_sync(full, !act || tile == t0);
+    // in one tile (the usual case: groups are sorted by fine bin)
     if (uni) {
       int m = ps;
       for (int d = 16; d > 0; d >>= 1) m = max(m, __shfl_xor_sync(full, m, d));
@@ -501,74 +542,101 @@ __global__ void k_fallback(int ns, int niso, const int32_t *__restrict__ lastq,
   atomicMax(&fbmax[s], ptab[cell].psize);
 }
 
-// reach[s][t]: how many bins to either side an output bin of tile t must look for contributing
-// groups.  A group in coarse bin d with half-size psize touches bins d-(psize+1)/o .. d+1+psize/o.
+// reach[s][t] / reachP[s][t]: how many coarse bins (and fine bins) to either side an output bin
+// of tile t must look for contributing groups.  A group whose fine bin lies in coarse cell d and
+// whose profile half-size is psize touches bins d - psize/o .. d + 1 + psize/o.
 __global__ void k_reach(int ns, int ntiles, int o, const int32_t *__restrict__ wtile,
                         const uint8_t *__restrict__ hasfb, const int32_t *__restrict__ fbmax,
-                        int32_t *__restrict__ reach) {
+                        int32_t *__restrict__ reach, int32_t *__restrict__ reachP) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= ns * ntiles) return;
   const int s = i / ntiles, t = i % ntiles;
-  int R = 0;
+  int R = 0, P = -1;
   for (int u = 0; u < ntiles; u++) {
     int ps = wtile[s * ntiles + u];
     if (hasfb[s * ntiles + u]) ps = max(ps, fbmax[s]);
     if (ps < 0) continue;
-    const int w = 1 + (ps + 1) / o;
+    const int w = 1 + ps / o;
     const int du = u > t ? u - t : t - u;
     const int gap = du == 0 ? 0 : (du - 1) * ACC_TILE + 1;   // closest pair of bins of the two tiles
-    if (w >= gap) R = max(R, w);
+    if (w >= gap) { R = max(R, w); P = max(P, ps); }
   }
   reach[i] = R;
+  reachP[i] = P;
 }
 
 // extinction.c:486-509 turned inside out: every output bin gathers its contributing groups
-// from the bin-sorted windows [j-R, j+R] of each molecule row, always in sorted order: a fixed
+// from the windows of each molecule row, always in sorted (row, fine bin) order: a fixed
 // summation order, no floating-point atomics.
 //   contributes  <=>  0 <= o*j - (iown - psize) <= 2*psize   (same test as the reference loop)
 // A block owns ACC_TILE consecutive bins of one state, a warp 32 of them.  Two schedules with
 // the same summation order:
-//   * narrow reach (R <= NARROW_R): each lane walks its own short window;
+//   * narrow reach (R <= NARROW_R bins): each lane bisects the fine-bin-sorted groups for its
+//     own window [o*j - P, o*j + P] (P = widest half-size that can reach the tile) and walks it;
 //   * wide reach: the warp walks the union window together -- 32 group records are fetched
-//     coalesced, the survivors broadcast one by one, and lane i adds the sample for bin j0+i,
-//     which the polyphase table layout makes one contiguous 128-byte read per group.
+//     coalesced, the survivors compacted into shared memory and broadcast one by one; lane i
+//     adds the sample for bin j0+i, which the polyphase table layout makes one contiguous
+//     256-byte read per group.
 #define NARROW_R 2
+struct AccRec {
+  double k;
+  int addr0;   // table address of lane 0's sample
+  int lanes;   // lo | hi << 8: lanes (bins j0+lo .. j0+hi) the profile covers
+};
+
 __global__ void __launch_bounds__(ACC_TILE)
-k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, int nrows, int permol, int ntiles,
+k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nrows, int permol, int ntiles,
              const int32_t *__restrict__ binstart, const int32_t *__restrict__ g_iown,
              const double *__restrict__ k_in, const uint16_t *__restrict__ pid_in,
              const int32_t *__restrict__ fbpid, const ProfEntry *__restrict__ ptab,
-             const int32_t *__restrict__ reach, const float *__restrict__ pdata,
-             double *__restrict__ out, unsigned long long *__restrict__ nsamp) {
+             const int32_t *__restrict__ reach, const int32_t *__restrict__ reachP,
+             const double *__restrict__ pdata, double *__restrict__ out,
+             unsigned long long *__restrict__ nsamp) {
+  __shared__ AccRec sh_rec[ACC_TILE / 32][32];
   const int s = blockIdx.y;
-  const int lane = threadIdx.x & 31;
-  const int64_t j0 = (int64_t)blockIdx.x * ACC_TILE + (threadIdx.x & ~31);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t j0 = (int64_t)blockIdx.x * ACC_TILE + warp * 32;
   if (j0 >= nwn) return;                       // whole warp
   const int64_t j = j0 + lane;
   const bool inb = j < nwn;
   const int R = reach[s * ntiles + blockIdx.x];
+  const int P = reachP[s * ntiles + blockIdx.x];
   const double *ks = k_in + (size_t)s * G;
   const uint16_t *ps = pid_in + (size_t)s * G;
   const int32_t *fbs = fbpid + (size_t)s * niso;
+  const int maxlane = (int)(nwn - 1 - j0 < 31 ? nwn - 1 - j0 : 31);
   unsigned long long cnt = 0;
   double acc = 0.0;
   for (int row = 0; row < nrows; row++) {
     const int32_t *bs = binstart + (size_t)row * nwn;
     if (R <= NARROW_R) {
-      if (inb) {
+      if (inb && P >= 0) {
         const int64_t jlo = j - R < 0 ? 0 : j - R;
         const int64_t jhi = j + R + 1 > nwn ? nwn : j + R + 1;
-        const int p1 = bs[jhi];
         const int oj = (int)(o * j);
-        for (int p = bs[jlo]; p < p1; p++) {
+        const int lo_f = oj - P, hi_f = oj + P;
+        int a = bs[jlo];
+        const int p1 = bs[jhi];
+        int b = p1;
+        while (a < b) {                          // first group with fine bin >= lo_f
+          const int mid = (a + b) >> 1;
+          if (g_iown[mid] < lo_f) a = mid + 1; else b = mid;
+        }
+        for (int p = a; p < p1; p++) {
+          const int io = g_iown[p];
+          if (io > hi_f) break;
           unsigned pid = ps[p];
           if (pid == PID_SKIP) continue;
           if (pid >= PID_FB) pid = fbs[pid - PID_FB];
           const ProfEntry pe = ptab[pid];
-          const int idx = oj - g_iown[p] + pe.psize;
+          const int idx = oj - io + pe.psize;
           if (idx >= 0 && idx <= 2 * pe.psize) {
-            const int a = pe.nk == 1 ? idx : (idx % o) * pe.nk + idx / o;
-            acc = fma(ks[p], (double)pdata[pe.off + a], acc);
+            int ad = idx;
+            if (pe.nk != 1) {
+              const int q = fd_div(idx, fd);
+              ad = (idx - q * o) * pe.nk + q;
+            }
+            acc = fma(ks[p], pdata[pe.off + ad], acc);
             cnt++;
           }
         }
@@ -581,38 +649,37 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, int nrows, int per
       for (int base = p0; base < p1; base += 32) {
         const int p = base + lane;
         unsigned pid = p < p1 ? ps[p] : PID_SKIP;
-        double kk = 0.0;
-        int addr0 = 0, lanes = 0;     // lanes = lo | hi << 8 (valid lane range, empty when lo > hi)
         bool alive = pid != PID_SKIP;
+        AccRec rec;
         if (alive) {
           if (pid >= PID_FB) pid = fbs[pid - PID_FB];
           const ProfEntry pe = ptab[pid];
           const int idx0 = oj0 - g_iown[p] + pe.psize;           // sample index for lane 0
           // lanes with 0 <= idx0 + lane*o <= 2*psize
-          int lo = idx0 >= 0 ? 0 : (-idx0 + o - 1) / o;
+          const int lo = idx0 >= 0 ? 0 : fd_div(-idx0 + o - 1, fd);
           int hi = 2 * pe.psize - idx0;
-          hi = hi < 0 ? -1 : hi / o;
-          if (hi > 31) hi = 31;
+          hi = hi < 0 ? -1 : fd_div(hi, fd);
+          if (hi > maxlane) hi = maxlane;
           if (lo > hi) alive = false;
           else {
             const int first = idx0 + lo * o;                     // >= 0
-            addr0 = pe.off + (first % o) * pe.nk + first / o - lo;
-            lanes = lo | (hi << 8);
-            kk = ks[p];
+            const int q = fd_div(first, fd);
+            rec.addr0 = pe.off + (first - q * o) * pe.nk + q - lo;
+            rec.lanes = lo | (hi << 8);
+            rec.k = ks[p];
+            cnt += hi - lo + 1;
           }
         }
-        unsigned m = __ballot_sync(0xffffffffu, alive);
-        while (m) {
-          const int src = __ffs(m) - 1;
-          m &= m - 1;
-          const double kb = __shfl_sync(0xffffffffu, kk, src);
-          const int ab = __shfl_sync(0xffffffffu, addr0, src);
-          const int lb = __shfl_sync(0xffffffffu, lanes, src);
-          if (lane >= (lb & 255) && lane <= (lb >> 8) && inb) {
-            acc = fma(kb, (double)pdata[ab + lane], acc);
-            cnt++;
-          }
+        const unsigned m = __ballot_sync(0xffffffffu, alive);
+        if (alive) sh_rec[warp][__popc(m & ((1u << lane) - 1))] = rec;
+        __syncwarp();
+        const int n = __popc(m);
+#pragma unroll 4
+        for (int i = 0; i < n; i++) {
+          const AccRec r = sh_rec[warp][i];
+          if (lane >= (r.lanes & 255) && lane <= (r.lanes >> 8)) acc = fma(r.k, pdata[r.addr0 + lane], acc);
         }
+        __syncwarp();
       }
     }
     if (permol) {
@@ -655,6 +722,8 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   TB_TRY(c->s_lastq.ensure((size_t)chunk * niso + 1)); TB_TRY(c->s_fb.ensure((size_t)chunk * niso + 1));
   TB_TRY(c->s_fbpid.ensure((size_t)chunk * niso + 1)); TB_TRY(c->s_fbmax.ensure(chunk));
   TB_TRY(c->s_wtile.ensure((size_t)chunk * ntiles)); TB_TRY(c->s_reach.ensure((size_t)chunk * ntiles));
+  TB_TRY(c->s_reachP.ensure((size_t)chunk * ntiles));
+  TB_TRY(c->s_facz.ensure((size_t)chunk * niso + 1)); TB_TRY(c->s_rtemp.ensure(chunk));
   TB_TRY(c->s_hasfb.ensure((size_t)chunk * ntiles));
   TB_TRY(c->s_kmax.ensure((size_t)chunk * nrows + 1));
   TB_TRY(c->s_nsamp.ensure(ns));
@@ -666,6 +735,14 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   }
   const int Tn = 256;
   constexpr int SB = 4;
+  auto fastdiv = [](int64_t d) {
+    FastDiv f;
+    f.d = (int)d;
+    f.M = d == 1 ? 0 : (~0ULL) / (uint64_t)d + 1;
+    return f;
+  };
+  const FastDiv fd_o = fastdiv(c->o), fd_tile = fastdiv((int64_t)c->o * ACC_TILE);
+  TB_REQUIRE(c->nDop < 255, TB_ERR_ARG, "nDop must be < 255");
   tb_timer_begin(c, "molext");
   for (int s0 = 0; s0 < ns; s0 += chunk) {
     const int cs = (ns - s0 < chunk) ? ns - s0 : chunk;
@@ -683,21 +760,22 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
         cs, niso, nmol, c->s_T.p, c->s_dens.p, c->d_mol_mass.p, c->d_mol_radius.p, c->d_iso_mass.p,
         c->d_iso_imol.p, c->d_aDop.p, c->nDop, c->d_aLor.p, c->nLor, c->wn_i, c->s_alphal.p,
         c->s_alphad.p, c->s_ilor.p, c->s_idop0.p, c->s_lastq.p, c->s_kmax.p, nrows,
-        c->s_nsamp.p + s0, c->s_wtile.p, c->s_hasfb.p, ntiles);
+        c->s_nsamp.p + s0, c->s_wtile.p, c->s_hasfb.p, ntiles, c->s_Z.p, c->d_iso_ratio.p, c->s_facz.p,
+        c->s_rtemp.p);
     TB_LAUNCHED(c);
     if (G > 0) {
       dim3 g2(nblk(M, Tn), (cs + SB - 1) / SB);
       tb_timer_begin(c, "kmax");
       k_kmax<SB><<<g2, Tn, 0, st>>>(M, cs, niso, c->m_wavn.p, c->m_elow.p, c->m_gf.p, c->m_iso.p,
-                                    c->m_inr.p, c->s_T.p, c->s_Z.p, c->d_iso_mass.p, c->d_iso_ratio.p,
+                                    c->m_inr.p, c->s_rtemp.p, c->s_Z.p, c->d_iso_mass.p, c->d_iso_ratio.p,
                                     c->d_iso_row.p, c->efct, permol, nrows, c->s_kmax.p);
       tb_timer_end(c, "kmax");
       dim3 g3(nblk(G, Tn), (cs + SB - 1) / SB);
       tb_timer_begin(c, "strength");
       k_strength<SB><<<g3, Tn, 0, st>>>(
-          G, cs, niso, c->g_start.p, c->g_iso.p, c->g_orig.p, c->g_idwn.p, c->g_wavn.p, c->m_wavn.p,
-          c->m_elow.p, c->m_gf.p, c->s_T.p, c->s_Z.p, c->s_dens.p, nmol, c->d_iso_mass.p,
-          c->d_iso_ratio.p, c->d_iso_imol.p, c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ilor.p,
+          G, cs, niso, c->o, fd_tile, c->g_start.p, c->g_iso.p, c->g_orig.p, c->g_iown.p, c->g_wavn.p,
+          c->m_wavn.p, c->m_elow.p, c->m_gf.p, c->s_rtemp.p, c->s_facz.p, c->s_dens.p, nmol,
+          c->d_iso_imol.p, c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ilor.p,
           c->d_aDop.p, c->nDop, c->d_ptab.p, c->nLor, c->efct, ethresh, permol, nrows, c->s_kmax.p,
           c->s_k.p, c->s_pid.p, c->s_lastq.p, c->s_wtile.p, c->s_hasfb.p, ntiles);
       tb_timer_end(c, "strength");
@@ -707,12 +785,13 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       c->launches += 3;
     }
     k_reach<<<nblk((int64_t)cs * ntiles, 128), 128, 0, st>>>(cs, ntiles, c->o, c->s_wtile.p, c->s_hasfb.p,
-                                                             c->s_fbmax.p, c->s_reach.p);
+                                                             c->s_fbmax.p, c->s_reach.p, c->s_reachP.p);
     dim3 g4(ntiles, cs);
     tb_timer_begin(c, "accumulate");
-    k_accumulate<<<g4, ACC_TILE, 0, st>>>(nwn, G, cs, niso, c->o, nrows, permol, ntiles, c->binstart.p,
+    k_accumulate<<<g4, ACC_TILE, 0, st>>>(nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, c->binstart.p,
                                           c->g_iown.p, c->s_k.p, c->s_pid.p, c->s_fbpid.p, c->d_ptab.p,
-                                          c->s_reach.p, c->d_pdata2.p, dst, c->s_nsamp.p + s0);
+                                          c->s_reach.p, c->s_reachP.p, c->d_pdata2.p, dst,
+                                          c->s_nsamp.p + s0);
     tb_timer_end(c, "accumulate");
     c->launches += 2;
     TB_CUDA(cudaGetLastError());

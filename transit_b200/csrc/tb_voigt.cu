@@ -110,7 +110,7 @@ __global__ void k_voigt_table(const ProfDesc *__restrict__ desc, int nprof, floa
 
 // reference layout -> polyphase layout (see ProfEntry)
 __global__ void k_polyphase(const ProfDesc *__restrict__ desc, const int32_t *__restrict__ off2,
-                            int nprof, int o, const float *__restrict__ in, float *__restrict__ out) {
+                            int nprof, int o, const float *__restrict__ in, double *__restrict__ out) {
   int lo = 0, hi = nprof - 1;
   while (lo < hi) {
     int mid = (lo + hi + 1) >> 1;
@@ -120,7 +120,7 @@ __global__ void k_polyphase(const ProfDesc *__restrict__ desc, const int32_t *__
   const int64_t k = ((int64_t)blockIdx.x - d.blk0) * blockDim.x + threadIdx.x;
   if (k >= d.nwn) return;
   const int nk = (d.nwn - 1) / o + 1;
-  out[off2[lo] + (k % o) * (int64_t)nk + k / o] = in[d.off + k];
+  out[off2[lo] + (k % o) * (int64_t)nk + k / o] = (double)in[d.off + k];
 }
 
 // getprofile's size rule (extinction.c:21-35) with the reference's float narrowing of the widths
@@ -247,7 +247,7 @@ extern "C" int tb_build_profiles(tb_ctx *c, int nDop, int nLor, float dmin, floa
   TB_CUDA(cudaMemcpyAsync(d_desc.p, desc.data(), desc.size() * sizeof(ProfDesc), cudaMemcpyHostToDevice, st));
   TB_CUDA(cudaMemcpyAsync(d_off2.p, off2.data(), off2.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
   TB_CUDA(cudaMemcpyAsync(c->d_ptab.p, ptab.data(), ptab.size() * sizeof(ProfEntry), cudaMemcpyHostToDevice, st));
-  TB_CUDA(cudaMemsetAsync(c->d_pdata2.p, 0, (total2 + 32) * sizeof(float), st));
+  TB_CUDA(cudaMemsetAsync(c->d_pdata2.p, 0, (total2 + 32) * sizeof(double), st));
   tb_timer_begin(c, "voigt");
   k_voigt_table<<<(unsigned)blocks, TPB, 0, st>>>(d_desc.p, (int)desc.size(), c->d_pdata.p);
   tb_timer_end(c, "voigt");
