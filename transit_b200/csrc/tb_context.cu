@@ -98,14 +98,13 @@ extern "C" void tb_destroy(tb_ctx *c) {
   REL(g_iso); REL(g_wavn); REL(go_wavn); REL(binstart); REL(d_aDop); REL(d_aLor); REL(d_psize);
   REL(d_poff); REL(d_pdata); REL(d_rad); REL(d_p); REL(d_t); REL(d_dens); REL(s_T); REL(s_dens);
   REL(s_Z); REL(s_alphal); REL(s_alphad); REL(s_kmax); REL(s_k); REL(s_ilor); REL(s_idop0);
-  REL(s_lastq); REL(s_fb); REL(s_fbpid); REL(s_wtile); REL(s_reach); REL(s_reachP); REL(s_fbmax); REL(s_facz); REL(s_rtemp); REL(s_pid); REL(s_hasfb);
+  REL(s_lastq); REL(s_fb); REL(s_fbpid); REL(s_wtile); REL(s_reach); REL(s_reachP); REL(s_fbmax); REL(s_facz); REL(s_rtemp); REL(s_ral); REL(s_xterm); REL(x_line); REL(q_g); REL(q_a); REL(q_w); REL(q_iso); REL(s_pid); REL(s_hasfb);
   REL(s_nsamp); REL(s_out); REL(d_pdata2); REL(d_ptab);
   REL(d_e); REL(d_ecs); REL(d_tau); REL(d_intens); REL(d_out); REL(d_last); REL(d_err);
-  REL(r_coef); REL(r_par); REL(r_meta); REL(d_grid); REL(c_f2); REL(c_z2); REL(c_scr);
-  REL(c_densfac); REL(d_es_aux); REL(cub_tmp);
+  REL(r_coef); REL(r_par); REL(r_h); REL(r_s); REL(r_ip); REL(r_ang); REL(r_meta); REL(d_grid); REL(c_stage); REL(d_es_aux); REL(cub_tmp);
 #undef REL
   for (CiaTable *t : c->cia) {
-    t->d_wn.release(); t->d_temp.release(); t->d_tab.release();
+    t->release();
     delete t;
   }
   for (auto &kv : c->timers) {
@@ -140,6 +139,7 @@ extern "C" int tb_set_wn_grid(tb_ctx *c, double wn_i, double wn_d, int wnosamp, 
   c->odwn = wn_d / (double)wnosamp;
   c->own_last = wn_i + (double)(onwn - 1) * c->odwn;  // owns.v[onwn-1], mul then add
   c->have_grid = true;
+  c->grid_version++;
   c->have_lines = c->have_prof = false;  // both depend on the grid
   return TB_OK;
 }

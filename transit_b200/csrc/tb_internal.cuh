@@ -92,6 +92,15 @@ struct CiaTable {
   int mol[2] = {0, 0};
   std::vector<double> wn, temp, tab;
   DevBuf<double> d_wn, d_temp, d_tab;
+  DevBuf<double> d_zt, d_h, d_u, d_rh, d_r, d_ru;   // table-only spline parts (see tb_radiative.cu)
+  DevBuf<double> d_f2, d_z2, d_v;     // per-spectrum scratch, [row][layer]
+  DevBuf<int32_t> d_widx;             // table interval of every grid wavenumber
+  int64_t fi = 0, li = 0;             // grid range inside the table (no extrapolation)
+  int grid_version = -1;
+  void release() {
+    d_wn.release(); d_temp.release(); d_tab.release(); d_zt.release(); d_h.release(); d_u.release(); d_rh.release(); d_r.release(); d_ru.release();
+    d_f2.release(); d_z2.release(); d_v.release(); d_widx.release();
+  }
 };
 
 struct KernelTimer {
@@ -109,6 +118,7 @@ struct tb_ctx {
 
   // ---- wavenumber grids (a2)
   bool have_grid = false;
+  int grid_version = 0;
   double wn_i = 0, wn_d = 0, odwn = 0, own_last = 0, wn_fct = 1;
   int o = 1;
   int64_t nwn = 0, onwn = 0;
@@ -132,6 +142,10 @@ struct tb_ctx {
   DevBuf<double> m_wavn, m_elow, m_gf;
   DevBuf<int16_t> m_iso;
   DevBuf<uint8_t> m_inr;
+  DevBuf<double> q_g, q_a, q_w;   // in-range member lines, strongest (g/m) first, for k_kmax
+  DevBuf<int16_t> q_iso;
+  int64_t Mq = 0;
+  DevBuf<int32_t> x_line;      // member positions of the co-added (non-leading) lines
   // bin-sorted groups
   DevBuf<int32_t> g_start, g_iown, g_idwn, g_orig;
   DevBuf<int16_t> g_iso;
@@ -144,6 +158,7 @@ struct tb_ctx {
   int nDop = 0, nLor = 0;
   float nwidth = 20.f;
   std::vector<double> aDop, aLor;
+  double dop_lmin = 0, dop_rstep = 0;   // aDop[i] = 10^(dop_lmin + i/dop_rstep)
   std::vector<int64_t> psize, poff;
   int64_t ndata = 0;
   DevBuf<double> d_aDop, d_aLor;
@@ -163,7 +178,7 @@ struct tb_ctx {
   // ---- state batch scratch (tb_lines.cu)
   DevBuf<double> s_T, s_dens, s_Z, s_alphal, s_alphad, s_kmax, s_k;
   DevBuf<int32_t> s_ilor, s_idop0, s_lastq, s_fb, s_fbpid, s_wtile, s_reach, s_reachP, s_fbmax;
-  DevBuf<double> s_facz, s_rtemp;
+  DevBuf<double> s_facz, s_rtemp, s_ral, s_xterm;
   DevBuf<uint16_t> s_pid;     // [state][group] profile cell, PID_SKIP, or PID_FB + isotope
   DevBuf<uint8_t> s_hasfb;    // [state][tile]
   DevBuf<unsigned long long> s_nsamp;
@@ -182,7 +197,7 @@ struct tb_ctx {
   double hfct = 1;
 
   // ---- ray geometry scratch
-  DevBuf<double> r_coef, r_par;
+  DevBuf<double> r_coef, r_par, r_h, r_s, r_ip, r_ang;
   DevBuf<int32_t> r_meta;
 
   // ---- opacity grid (a6-a8)
@@ -194,7 +209,7 @@ struct tb_ctx {
 
   // ---- CIA
   std::vector<CiaTable *> cia;
-  DevBuf<double> c_f2, c_z2, c_scr, c_densfac;
+  DevBuf<double> c_stage;     // [layer temperatures | density factor per table]
 
   // ---- scattering / clouds
   int sc_flag = 0;
@@ -236,4 +251,5 @@ __device__ __forceinline__ int tb_binsearchapprox(const double *__restrict__ a, 
 int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const double *Z,
                   double ethresh, int permol, double *d_out_rows, double *h_out);
 int tb_cia_run(tb_ctx *c);
+int tb_check_errors(tb_ctx *c);
 int tb_interp_run(tb_ctx *c);

@@ -113,7 +113,7 @@ __global__ void k_group_fill(const int32_t *__restrict__ order, const int32_t *_
                              double *__restrict__ g_wavn, double *__restrict__ m_wavn,
                              double *__restrict__ m_elow, double *__restrict__ m_gf,
                              int16_t *__restrict__ m_iso, uint8_t *__restrict__ m_inr,
-                             int32_t *__restrict__ l_gpos) {
+                             int32_t *__restrict__ l_gpos, int32_t *__restrict__ x_line) {
   int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (p >= G) return;
   int32_t g = order[p], L = lead[g], E = next[L], s = gstart[p];
@@ -129,7 +129,39 @@ __global__ void k_group_fill(const int32_t *__restrict__ order, const int32_t *_
     m_gf[s] = gf[l];
     m_iso[s] = iso[l];
     m_inr[s] = flag[l] & 1;
+    if (l != L) x_line[s - p - 1] = s;     // co-added member: the (s-p-1)-th non-leading member
   }
+}
+
+// the strength-maximum pass wants the lines with the largest state-independent factor first
+__global__ void k_q_keys(int64_t M, const double *__restrict__ m_gf, const int16_t *__restrict__ m_iso,
+                         const uint8_t *__restrict__ m_inr, const double *__restrict__ iso_mass,
+                         const double *__restrict__ iso_ratio, double *__restrict__ key,
+                         int32_t *__restrict__ idx) {
+  int64_t l = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (l >= M) return;
+  const int iso = m_iso[l];
+  key[l] = m_inr[l] ? __dmul_rn(__dmul_rn(iso_ratio[iso], TB_SIGCTE), m_gf[l]) / iso_mass[iso] : -1.0;
+  idx[l] = (int32_t)l;
+}
+__global__ void k_q_fill(int64_t Mq, const int32_t *__restrict__ idx, const double *__restrict__ m_wavn,
+                         const double *__restrict__ m_elow, const double *__restrict__ m_gf,
+                         const int16_t *__restrict__ m_iso, const double *__restrict__ iso_ratio, double efct,
+                         double *__restrict__ q_g, double *__restrict__ q_a, double *__restrict__ q_w,
+                         int16_t *__restrict__ q_iso) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= Mq) return;
+  const int l = idx[i], iso = m_iso[l];
+  q_g[i] = __dmul_rn(__dmul_rn(iso_ratio[iso], TB_SIGCTE), m_gf[l]);          // extinction.c:419-421
+  q_a[i] = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
+  q_w[i] = __dmul_rn(-TB_EXPCTE, m_wavn[l]);
+  q_iso[i] = (int16_t)iso;
+}
+__global__ void k_count_pos(int64_t M, const double *__restrict__ key_sorted_desc, int32_t *__restrict__ n) {
+  int64_t l = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (l >= M) return;
+  // keys are sorted descending: the boundary between in-range (>= 0) and out-of-range (-1) lines
+  if (key_sorted_desc[l] >= 0 && (l + 1 == M || key_sorted_desc[l + 1] < 0)) *n = (int32_t)(l + 1);
 }
 
 // binstart[row][j] = first sorted group of `row` whose fine bin is >= o*j (groups are sorted by
@@ -162,7 +194,7 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
   cudaStream_t st = c->stream;
   c->nlines = n; c->wfct = wfct; c->efct = efct;
   c->have_lines = false;
-  c->G = c->M = 0;
+  c->G = c->M = c->Mq = 0;
   const int64_t nkeys = (int64_t)c->nrows * c->nwn;
   TB_TRY(c->binstart.ensure(nkeys + 1));
   if (n == 0) {
@@ -259,16 +291,41 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
   c->M = M;
   TB_CUDA(cudaMemcpyAsync(c->g_start.p + G, &M, 4, cudaMemcpyHostToDevice, st));
   TB_TRY(c->m_wavn.ensure(M)); TB_TRY(c->m_elow.ensure(M)); TB_TRY(c->m_gf.ensure(M));
-  TB_TRY(c->m_iso.ensure(M)); TB_TRY(c->m_inr.ensure(M));
+  TB_TRY(c->m_iso.ensure(M)); TB_TRY(c->m_inr.ensure(M)); TB_TRY(c->x_line.ensure(M - G + 1));
   TB_TRY(c->g_iown.ensure(G)); TB_TRY(c->g_idwn.ensure(G)); TB_TRY(c->g_orig.ensure(G));
   TB_TRY(c->g_iso.ensure(G)); TB_TRY(c->g_wavn.ensure(G));
   k_group_fill<<<nblk(G, T), T, 0, st>>>(ord_s.p, idw.p, c->g_start.p, G, lead.p, nxt.p, d_wavn.p,
                                          d_elow.p, d_gf.p, d_iso.p, c->l_iown.p, c->l_flag.p, c->nwn,
                                          c->g_iown.p, c->g_idwn.p, c->g_orig.p, c->g_iso.p,
                                          c->g_wavn.p, c->m_wavn.p, c->m_elow.p, c->m_gf.p, c->m_iso.p,
-                                         c->m_inr.p, c->l_gpos.p);
+                                         c->m_inr.p, c->l_gpos.p, c->x_line.p);
   k_binstart<<<nblk(nkeys + 1, T), T, 0, st>>>(key_s.p, G, nkeys, c->nwn, c->onwn, c->o, c->binstart.p);
   c->launches += 8;
+  {  // strength-ordered copy of the in-range member lines for k_kmax
+    DevBuf<double> qk, qk_s;
+    DevBuf<int32_t> qi, qi_s;
+    TB_TRY(qk.ensure(M)); TB_TRY(qk_s.ensure(M)); TB_TRY(qi.ensure(M)); TB_TRY(qi_s.ensure(M));
+    k_q_keys<<<nblk(M, T), T, 0, st>>>(M, c->m_gf.p, c->m_iso.p, c->m_inr.p, c->d_iso_mass.p, c->d_iso_ratio.p,
+                                       qk.p, qi.p);
+    tmpb = 0;
+    cub::DeviceRadixSort::SortPairsDescending(nullptr, tmpb, qk.p, qk_s.p, qi.p, qi_s.p, (int)M, 0, 64, st);
+    TB_TRY(c->cub_tmp.ensure(tmpb));
+    cub::DeviceRadixSort::SortPairsDescending(c->cub_tmp.p, tmpb, qk.p, qk_s.p, qi.p, qi_s.p, (int)M, 0, 64, st);
+    TB_CUDA(cudaMemsetAsync(ngrp.p, 0, sizeof(int32_t), st));
+    k_count_pos<<<nblk(M, T), T, 0, st>>>(M, qk_s.p, ngrp.p);
+    int32_t Mq = 0;
+    TB_CUDA(cudaMemcpyAsync(&Mq, ngrp.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    TB_CUDA(cudaStreamSynchronize(st));
+    c->Mq = Mq;
+    TB_TRY(c->q_g.ensure(Mq + 1)); TB_TRY(c->q_a.ensure(Mq + 1)); TB_TRY(c->q_w.ensure(Mq + 1));
+    TB_TRY(c->q_iso.ensure(Mq + 1));
+    if (Mq > 0)
+      k_q_fill<<<nblk(Mq, T), T, 0, st>>>(Mq, qi_s.p, c->m_wavn.p, c->m_elow.p, c->m_gf.p, c->m_iso.p,
+                                          c->d_iso_ratio.p, efct, c->q_g.p, c->q_a.p, c->q_w.p, c->q_iso.p);
+    c->launches += 5;
+    TB_CUDA(cudaStreamSynchronize(st));
+    qk.release(); qk_s.release(); qi.release(); qi_s.release();
+  }
   TB_CUDA(cudaStreamSynchronize(st));
   d_wl.release(); d_wavn.release(); d_elow.release(); d_gf.release(); d_iso.release();
   nxt.release(); jA.release(); jB.release(); lead.release(); key.release(); key_s.release();
@@ -305,7 +362,7 @@ __global__ void k_state_setup(int ns, int niso, int nmol, const double *__restri
                               unsigned long long *__restrict__ nsamp, int32_t *__restrict__ wtile,
                               uint8_t *__restrict__ hasfb, int ntiles, const double *__restrict__ Z,
                               const double *__restrict__ iso_ratio, double *__restrict__ facz,
-                              double *__restrict__ rtemp) {
+                              double *__restrict__ rtemp, double *__restrict__ ral) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < ns * nrows) kmax[t] = 0.0;
   if (t < ns) { nsamp[t] = 0ULL; rtemp[t] = 1.0 / T[t]; }   // nsamp already points at this chunk
@@ -332,6 +389,7 @@ __global__ void k_state_setup(int ns, int niso, int nmol, const double *__restri
   lastq[t] = -1;
   // the state- and isotope-dependent factor of extinction.c:464-465
   facz[t] = __dmul_rn(TB_SIGCTE, iso_ratio[i]) / __dmul_rn(iso_mass[i], Z[t]);
+  ral[t] = 1.0 / al;
 }
 
 __device__ __forceinline__ void atomicMaxPosDouble(double *addr, double v) {
@@ -345,14 +403,13 @@ __device__ __forceinline__ void atomicMaxPosDouble(double *addr, double v) {
 // monotone) cannot raise the maximum found so far skips its two exp(): the maximum stays
 // exact, only the amount of work depends on the visiting order.
 #define KMAX_ROWS 16   // output rows reduced in shared memory (more rows: straight to global)
+#define KMAX_LPT 8     // lines per thread
 template <int SB>
-__global__ void k_kmax(int64_t M, int ns, int niso, const double *__restrict__ m_wavn,
-                       const double *__restrict__ m_elow, const double *__restrict__ m_gf,
-                       const int16_t *__restrict__ m_iso, const uint8_t *__restrict__ m_inr,
-                       const double *__restrict__ rtemp, const double *__restrict__ Z,
-                       const double *__restrict__ iso_mass, const double *__restrict__ iso_ratio,
-                       const int *__restrict__ iso_row, double efct, int permol, int nrows,
-                       double *kmax) {
+__global__ void k_kmax(int64_t l0, int64_t l1, int ns, int niso, const double *__restrict__ q_g,
+                       const double *__restrict__ q_a, const double *__restrict__ q_w,
+                       const int16_t *__restrict__ q_iso, const double *__restrict__ rtemp,
+                       const double *__restrict__ Z, const double *__restrict__ iso_mass,
+                       const int *__restrict__ iso_row, int permol, int nrows, double *kmax) {
   // the running maxima are read once per block (not per warp: every warp of the chip asking
   // one L2 slice for the same sector serialises there) and merged back once per block
   __shared__ unsigned long long sh_cur[SB][KMAX_ROWS], sh_new[SB][KMAX_ROWS];
@@ -367,27 +424,25 @@ __global__ void k_kmax(int64_t M, int ns, int niso, const double *__restrict__ m
     }
     __syncthreads();
   }
-  int64_t l = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  bool act = l < M && m_inr[l];
-  int iso = 0, row = 0;
-  double a = 0, w = 0, g = 0, mass = 1;
-  if (act) {
-    iso = m_iso[l];
-    w = __dmul_rn(-TB_EXPCTE, m_wavn[l]);
-    a = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
-    g = __dmul_rn(__dmul_rn(iso_ratio[iso], TB_SIGCTE), m_gf[l]);
-    mass = iso_mass[iso];
-    row = permol ? iso_row[iso] : 0;
-  }
-  if (act) {
+#pragma unroll 1
+  for (int rep = 0; rep < KMAX_LPT; rep++) {
+    const int64_t l = l0 + ((int64_t)blockIdx.x * KMAX_LPT + rep) * blockDim.x + threadIdx.x;
+    if (l >= l1) break;
+    const int iso = q_iso[l];
+    const double g = q_g[l], mass = iso_mass[iso];
+    const int row = permol ? iso_row[iso] : 0;
+    const double a = q_a[l];      // > 0 only for a (bogus) negative lower-state energy: never skipped
+    double w = 0;
+    bool loaded = false;
 #pragma unroll
     for (int k = 0; k < SB; k++) {
       const int s = s0 + k;
       if (s >= ns) break;
       const double cur = use_sh ? __longlong_as_double((long long)sh_cur[k][row]) : __ldcg(&kmax[s * nrows + row]);
       const double z = Z[s * niso + iso];
-      // g/mass/z <= cur  <=  g < (1-1e-10)*cur*mass*z: no division on the (usual) skip path
+      // g/mass/z <= cur  <=  g < (1-1e-10)*cur*mass*z: no division, no further loads on the skip path
       if (a > 0 || !(g < 0.9999999999 * cur * mass * z)) {
+        if (!loaded) { w = q_w[l]; loaded = true; }
         const double rT = rtemp[s];
         const double v = g * exp(a * rT) * (1 - exp(w * rT)) / mass / z;
         if (v > cur) {
@@ -407,6 +462,24 @@ __global__ void k_kmax(int64_t M, int ns, int niso, const double *__restrict__ m
   }
 }
 
+// The co-added (non-leading) members of a group (extinction.c:449-462) are few; their terms
+// gf*exp(-E/T)*(1-exp(-w/T)) are evaluated here, one thread per (member, state), so that
+// k_strength's member loop is loads and adds only (a divergent loop with two exp() in it
+// costs every warp the full price for one busy lane).
+__global__ void k_extra(int64_t X, int ns, const int32_t *__restrict__ x_line,
+                        const double *__restrict__ m_wavn, const double *__restrict__ m_elow,
+                        const double *__restrict__ m_gf, const double *__restrict__ rtemp, double efct,
+                        double *__restrict__ xterm) {
+  const int64_t x = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int s = blockIdx.y;
+  if (x >= X) return;
+  const int l = x_line[x];
+  const double rT = rtemp[s];
+  const double a = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
+  xterm[(size_t)s * X + x] =
+      __dmul_rn(__dmul_rn(m_gf[l], exp(a * rT)), (1 - exp(__dmul_rn(-TB_EXPCTE, m_wavn[l]) * rT)));
+}
+
 // extinction.c:439-483 for one (group, state): co-added strength in member order, scaling,
 // threshold, density factor, Doppler-index decision.  Output per (state, group): the strength
 // and a 16-bit profile id.  The carried-index and tile-reach maxima are reduced in shared
@@ -419,6 +492,8 @@ __global__ void k_strength(int64_t G, int ns, int niso, int o, FastDiv fd_tile,
                            const double *__restrict__ g_wavn, const double *__restrict__ m_wavn,
                            const double *__restrict__ m_elow, const double *__restrict__ m_gf,
                            const double *__restrict__ rtemp, const double *__restrict__ facz,
+                           const double *__restrict__ ral, const double *__restrict__ xterm, int64_t X,
+                           float dop_lmin, float dop_rstep,
                            const double *__restrict__ dens, int nmol,
                            const int *__restrict__ iso_imol, const int *__restrict__ iso_row,
                            const double *__restrict__ alphal, const double *__restrict__ alphad,
@@ -465,12 +540,8 @@ __global__ void k_strength(int64_t G, int ns, int niso, int o, FastDiv fd_tile,
     if (act) {
       const double rT = rtemp[s];
       double acc = __dmul_rn(__dmul_rn(g0, exp(a0 * rT)), (1 - exp(w0 * rT)));
-      for (int l = b + 1; l < e; l++) {                        // co-added members (extinction.c:449-462)
-        const double a = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
-        const double term = __dmul_rn(__dmul_rn(m_gf[l], exp(a * rT)),
-                                      (1 - exp(__dmul_rn(-TB_EXPCTE, m_wavn[l]) * rT)));
-        acc = __dadd_rn(acc, term);
-      }
+      for (int l = b + 1; l < e; l++)                          // co-added members (extinction.c:449-462)
+        acc = __dadd_rn(acc, xterm[(size_t)s * X + (l - (int)p - 1)]);
       const int si = s * niso + iso;
       double kk = __dmul_rn(acc, facz[si]);
       const size_t oo = (size_t)s * G + p;
@@ -478,13 +549,18 @@ __global__ void k_strength(int64_t G, int ns, int niso, int o, FastDiv fd_tile,
       if (!(kk < __dmul_rn(ethresh, kmax[s * nrows + row]))) {   // extinction.c:467-470
         if (!permol) kk = __dmul_rn(kk, dens[s * nmol + imol]);
         const double al = alphal[si], adw = __dmul_rn(alphad[si], wlead);
-        // extinction.c:480-483: alphad*wavn/alphal >= 0.1, decided by the exact quotient
-        if (adw / al >= 1e-1) {
-          int lo = 0, hi = nDop;                                  // binsearchapprox (iomisc.c:1088-1108)
-          while (hi - lo > 1) {
-            const int mid = (hi + lo) >> 1;
-            if (sh_aDop[mid] > adw) hi = mid; else lo = mid;
-          }
+        // extinction.c:480-483: alphad*wavn/alphal >= 0.1, decided by the exact quotient whenever
+        // the reciprocal product is within rounding distance of the boundary
+        const double qa = adw * ral[si];
+        const bool refresh = fabs(qa - 1e-1) > 1e-12 ? qa >= 1e-1 : adw / al >= 1e-1;
+        if (refresh) {
+          // binsearchapprox (iomisc.c:1088-1108) on the log-spaced table: start from the
+          // closed-form cell and settle with exact comparisons: lo = last entry <= adw
+          int lo = (int)((__log2f((float)adw) * 0.30102999566f - dop_lmin) * dop_rstep);
+          lo = lo < 0 ? 0 : (lo > nDop - 1 ? nDop - 1 : lo);
+          while (lo > 0 && sh_aDop[lo] > adw) lo--;
+          while (sh_aDop[lo + 1] <= adw) lo++;                    // [nDop] = +inf stops it
+          const int hi = lo + 1;
           const int id = (fabs(sh_aDop[hi] - adw) < fabs(sh_aDop[lo] - adw)) ? hi : lo;
           pid = id * nLor + ilor[si];
           ps = ptab[pid].psize;
@@ -710,7 +786,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   c->last_permol = permol;
   // chunk the states so the per-(state, group) scratch stays below ~12 GB
   int chunk = ns;
-  const size_t per_state = (size_t)G * 10 + (size_t)nout * nwn * 8 + 64;
+  const size_t per_state = (size_t)G * 10 + (size_t)(M - G) * 8 + (size_t)nout * nwn * 8 + 64;
   const size_t budget = (size_t)12 << 30;
   if (per_state * chunk > budget) chunk = (int)(budget / per_state);
   if (chunk < 1) chunk = 1;
@@ -724,6 +800,9 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   TB_TRY(c->s_wtile.ensure((size_t)chunk * ntiles)); TB_TRY(c->s_reach.ensure((size_t)chunk * ntiles));
   TB_TRY(c->s_reachP.ensure((size_t)chunk * ntiles));
   TB_TRY(c->s_facz.ensure((size_t)chunk * niso + 1)); TB_TRY(c->s_rtemp.ensure(chunk));
+  TB_TRY(c->s_ral.ensure((size_t)chunk * niso + 1));
+  const int64_t X = M - G;
+  TB_TRY(c->s_xterm.ensure((size_t)chunk * X + 1));
   TB_TRY(c->s_hasfb.ensure((size_t)chunk * ntiles));
   TB_TRY(c->s_kmax.ensure((size_t)chunk * nrows + 1));
   TB_TRY(c->s_nsamp.ensure(ns));
@@ -761,20 +840,34 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
         c->d_iso_imol.p, c->d_aDop.p, c->nDop, c->d_aLor.p, c->nLor, c->wn_i, c->s_alphal.p,
         c->s_alphad.p, c->s_ilor.p, c->s_idop0.p, c->s_lastq.p, c->s_kmax.p, nrows,
         c->s_nsamp.p + s0, c->s_wtile.p, c->s_hasfb.p, ntiles, c->s_Z.p, c->d_iso_ratio.p, c->s_facz.p,
-        c->s_rtemp.p);
+        c->s_rtemp.p, c->s_ral.p);
     TB_LAUNCHED(c);
     if (G > 0) {
-      dim3 g2(nblk(M, Tn), (cs + SB - 1) / SB);
+      // lines in descending order of their state-independent factor: a small seed launch finds
+      // (nearly) the maxima, after which the bulk skips both exp() of almost every line
+      const int64_t Mq = c->Mq, seed = Mq < 16384 ? Mq : 16384;
       tb_timer_begin(c, "kmax");
-      k_kmax<SB><<<g2, Tn, 0, st>>>(M, cs, niso, c->m_wavn.p, c->m_elow.p, c->m_gf.p, c->m_iso.p,
-                                    c->m_inr.p, c->s_rtemp.p, c->s_Z.p, c->d_iso_mass.p, c->d_iso_ratio.p,
-                                    c->d_iso_row.p, c->efct, permol, nrows, c->s_kmax.p);
+      if (seed > 0)
+        k_kmax<SB><<<dim3(nblk(seed, Tn * KMAX_LPT), (cs + SB - 1) / SB), Tn, 0, st>>>(
+            0, seed, cs, niso, c->q_g.p, c->q_a.p, c->q_w.p, c->q_iso.p, c->s_rtemp.p, c->s_Z.p, c->d_iso_mass.p,
+            c->d_iso_row.p, permol, nrows, c->s_kmax.p);
+      if (Mq > seed)
+        k_kmax<SB><<<dim3(nblk(Mq - seed, Tn * KMAX_LPT), (cs + SB - 1) / SB), Tn, 0, st>>>(
+            seed, Mq, cs, niso, c->q_g.p, c->q_a.p, c->q_w.p, c->q_iso.p, c->s_rtemp.p, c->s_Z.p, c->d_iso_mass.p,
+            c->d_iso_row.p, permol, nrows, c->s_kmax.p);
+      TB_LAUNCHED(c);
       tb_timer_end(c, "kmax");
       dim3 g3(nblk(G, Tn), (cs + SB - 1) / SB);
       tb_timer_begin(c, "strength");
+      if (X > 0) {
+        k_extra<<<dim3(nblk(X, Tn), cs), Tn, 0, st>>>(X, cs, c->x_line.p, c->m_wavn.p, c->m_elow.p, c->m_gf.p,
+                                                      c->s_rtemp.p, c->efct, c->s_xterm.p);
+        TB_LAUNCHED(c);
+      }
       k_strength<SB><<<g3, Tn, 0, st>>>(
           G, cs, niso, c->o, fd_tile, c->g_start.p, c->g_iso.p, c->g_orig.p, c->g_iown.p, c->g_wavn.p,
-          c->m_wavn.p, c->m_elow.p, c->m_gf.p, c->s_rtemp.p, c->s_facz.p, c->s_dens.p, nmol,
+          c->m_wavn.p, c->m_elow.p, c->m_gf.p, c->s_rtemp.p, c->s_facz.p, c->s_ral.p, c->s_xterm.p, X,
+          (float)c->dop_lmin, (float)c->dop_rstep, c->s_dens.p, nmol,
           c->d_iso_imol.p, c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ilor.p,
           c->d_aDop.p, c->nDop, c->d_ptab.p, c->nLor, c->efct, ethresh, permol, nrows, c->s_kmax.p,
           c->s_k.p, c->s_pid.p, c->s_lastq.p, c->s_wtile.p, c->s_hasfb.p, ntiles);

@@ -48,46 +48,136 @@ __device__ double tb_splinterp_pt(const double *z, int N, const double *x, const
 }
 
 // =============================================================== CIA (a9)
+//
+// bicubicinterpolate (crosssec.c:353-428) is two families of natural cubic splines: along
+// temperature for every table row, then along wavenumber for every layer.  What depends only
+// on the table (second derivatives along T, the tridiagonal pivots u[] of the wavenumber
+// spline, the table interval of every grid wavenumber) is computed once per table/grid; per
+// spectrum there remain one evaluation per (row, layer), two first-order recurrences per
+// layer and one cubic per (wavenumber, layer), all tables summed in one pass.
 
 #define CIA_MAXT 64
-// pass 1 (crosssec.c:407-412): per table row, spline along temperature -> f2[layer][row]
-__global__ void k_cia_temp(const double *__restrict__ tab, const double *__restrict__ ttemp, int ntw,
-                           int ntt, const double *__restrict__ ltemp, int fj, int lj,
+#define CIA_MAXTAB 8
+
+// pass 1 (crosssec.c:407-412): f2[row][layer] = spline along T of table row `row` at the layer T
+__global__ void k_cia_temp(const double *__restrict__ tab, const double *__restrict__ zt,
+                           const double *__restrict__ ttemp, int ntw, int ntt,
+                           const double *__restrict__ ltemp, int nrad, int fj, int lj,
                            double *__restrict__ f2) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= ntw) return;
-  double z[CIA_MAXT], u[CIA_MAXT], v[CIA_MAXT], y[CIA_MAXT], x[CIA_MAXT];
-  for (int k = 0; k < ntt; k++) { y[k] = tab[(size_t)i * ntt + k]; x[k] = ttemp[k]; }
-  tb_spline_init(z, x, y, ntt, u, v);
-  for (int j = fj; j < lj; j++) f2[(size_t)j * ntw + i] = tb_splinterp_pt(z, ntt, x, y, ltemp[j]);
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= ntw * nrad) return;
+  const int i = t / nrad, j = t % nrad;
+  if (j < fj || j >= lj) return;
+  f2[t] = tb_splinterp_pt(zt + (size_t)i * ntt, ntt, ttemp, tab + (size_t)i * ntt, ltemp[j]);
 }
 
-// pass 2a (crosssec.c:415-416): per layer, second derivatives along the table wavenumbers
-__global__ void k_cia_wnspline(const double *__restrict__ twn, int ntw, int fj, int lj,
-                               const double *__restrict__ f2, double *__restrict__ z2,
-                               double *__restrict__ scr) {
-  int j = fj + blockIdx.x * blockDim.x + threadIdx.x;
+// pass 2a (crosssec.c:415-416, spline.c:12-48): second derivatives along the table wavenumbers,
+// one thread per layer, arrays laid out [row][layer] so a warp of layers moves coalesced.
+// Everything that depends only on the table comes precomputed (rh = 1/h, r = h[i-1]/u[i-1],
+// ru = 1/u), which leaves one fused multiply-add per row on each sweep's dependency chain;
+// the column is fetched CH rows at a time so the loads are in flight together.
+#define CIA_CH 16
+__global__ void k_cia_wnspline(const double *__restrict__ h, const double *__restrict__ rh,
+                               const double *__restrict__ r, const double *__restrict__ ru, int ntw,
+                               int nrad, int fj, int lj, const double *__restrict__ f2,
+                               double *__restrict__ v, double *__restrict__ z2) {
+  const int j = fj + blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= lj) return;
-  tb_spline_init(z2 + (size_t)j * ntw, twn, f2 + (size_t)j * ntw, ntw, scr + (size_t)j * 2 * ntw,
-                 scr + (size_t)j * 2 * ntw + ntw);
+  const size_t st = nrad;
+  const double *y = f2 + j;
+  double *vv = v + j, *zz = z2 + j;
+  if (ntw > 2) {
+    double y0 = y[st];
+    double bm = (y0 - y[0]) * rh[0], vprev = 0.0;
+    for (int i0 = 1; i0 < ntw - 1; i0 += CIA_CH) {
+      double yb[CIA_CH];
+#pragma unroll
+      for (int q = 0; q < CIA_CH; q++) yb[q] = (i0 + q < ntw - 1) ? y[(size_t)(i0 + q + 1) * st] : 0.0;
+#pragma unroll
+      for (int q = 0; q < CIA_CH; q++) {
+        const int i = i0 + q;
+        if (i < ntw - 1) {
+          const double bi = (yb[q] - y0) * rh[i];
+          vprev = (i == 1) ? 6 * (bi - bm) : 6 * (bi - bm) - vprev * r[i];
+          vv[(size_t)i * st] = vprev;
+          bm = bi;
+          y0 = yb[q];
+        }
+      }
+    }
+  }
+  zz[0] = 0;
+  zz[(size_t)(ntw - 1) * st] = 0;
+  double znext = 0;
+  for (int i0 = ntw - 2; i0 > 0; i0 -= CIA_CH) {
+    double vb[CIA_CH];
+#pragma unroll
+    for (int q = 0; q < CIA_CH; q++) vb[q] = (i0 - q > 0) ? vv[(size_t)(i0 - q) * st] : 0.0;
+#pragma unroll
+    for (int q = 0; q < CIA_CH; q++) {
+      const int i = i0 - q;
+      if (i > 0) {
+        znext = (vb[q] - h[i] * znext) * ru[i];
+        zz[(size_t)i * st] = znext;
+      }
+    }
+  }
 }
 
-// pass 2b (crosssec.c:417-419) + density scaling and positivity (crosssec.c:321-336)
-__global__ void k_cia_eval(const double *__restrict__ twn, int ntw, const double *__restrict__ f2,
-                           const double *__restrict__ z2, double wn_i, double wn_d, double wn_fct,
-                           int64_t nwn, int64_t fi, int64_t li, int fj, int lj,
-                           const double *__restrict__ densfac, double *__restrict__ ecs) {
-  int64_t w = fi + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  int j = fj + blockIdx.y;
-  if (w >= li || j >= lj) return;
-  double wn = wn_fct * __dadd_rn(wn_i, __dmul_rn((double)w, wn_d));
-  double val = tb_splinterp_pt(z2 + (size_t)j * ntw, ntw, twn, f2 + (size_t)j * ntw, wn);
-  if (val > 0) ecs[(size_t)j * nwn + w] += val * densfac[j];
+struct CiaDev {
+  const double *wn, *f2, *z2, *densfac;
+  const int32_t *widx;
+  int fi, li, fj, lj;
+};
+struct CiaPack {
+  CiaDev t[CIA_MAXTAB];
+  int n;
+};
+
+// interval of every grid wavenumber in the table, as splinterp_pt picks it (spline.c:139-145)
+__global__ void k_cia_widx(const double *__restrict__ twn, int ntw, double wn_i, double wn_d, double wn_fct,
+                           int64_t nwn, int32_t *__restrict__ widx) {
+  const int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (w >= nwn) return;
+  const double x = wn_fct * __dadd_rn(wn_i, __dmul_rn((double)w, wn_d));
+  int idx = tb_binsearchapprox(twn, x, 0, ntw - 1);
+  if (idx == ntw - 1 || x < twn[idx]) idx--;
+  widx[w] = idx < 0 ? 0 : idx;
+}
+
+// pass 2b (crosssec.c:417-419) + density scaling and positivity (crosssec.c:321-336), every
+// table in file order; ecs[layer][wn]
+__global__ void k_cia_eval(CiaPack P, int nrad, double wn_i, double wn_d, double wn_fct, int64_t nwn,
+                           double *__restrict__ ecs) {
+  const int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int j = blockIdx.y;
+  if (w >= nwn) return;
+  const double xout = wn_fct * __dadd_rn(wn_i, __dmul_rn((double)w, wn_d));
+  double acc = 0.0;
+  for (int n = 0; n < P.n; n++) {
+    const CiaDev &T = P.t[n];
+    if (w < T.fi || w >= T.li || j < T.fj || j >= T.lj) continue;
+    const int idx = T.widx[w];
+    const double x_lo = T.wn[idx], x_hi = T.wn[idx + 1];
+    const double y_lo = T.f2[(size_t)idx * nrad + j], y_hi = T.f2[(size_t)(idx + 1) * nrad + j];
+    const double z_lo = T.z2[(size_t)idx * nrad + j], z_hi = T.z2[(size_t)(idx + 1) * nrad + j];
+    const double h = x_hi - x_lo, dy = y_hi - y_lo;
+    double val = 0;
+    if (x_lo == xout) val = y_lo;
+    else if (h > 0) {                                   // splinterp_pt, spline.c:163-180
+      const double dx = xout - x_lo;
+      const double a = (z_hi - z_lo) / (6 * h), b = 0.5 * z_lo;
+      const double cc = dy / h - h / 6 * (z_hi + 2 * z_lo);
+      val = y_lo + dx * (cc + dx * (b + dx * a));
+    }
+    if (val > 0) acc += val * T.densfac[j];
+  }
+  ecs[(size_t)j * nwn + w] = acc;
 }
 
 extern "C" int tb_cia_clear(tb_ctx *c) {
   for (CiaTable *t : c->cia) {
-    t->d_wn.release(); t->d_temp.release(); t->d_tab.release();
+    t->release();
     delete t;
   }
   c->cia.clear();
@@ -100,8 +190,11 @@ extern "C" int tb_cia_add_table(tb_ctx *c, const double *wn, int nwn, const doub
   TB_REQUIRE(nwn >= 3 && ntemp >= 3 && ntemp <= CIA_MAXT, TB_ERR_ARG,
              "CIA table needs >=3 wavenumbers and 3..%d temperatures", CIA_MAXT);
   TB_REQUIRE(nspec >= 1 && nspec <= 2, TB_ERR_ARG, "CIA table has 1 or 2 species (crosssec.c:115-124)");
+  TB_REQUIRE((int)c->cia.size() < CIA_MAXTAB, TB_ERR_ARG, "at most %d CIA tables", CIA_MAXTAB);
   for (int k = 0; k < nspec; k++)
     TB_REQUIRE(mol[k] >= 0 && mol[k] < c->nmol, TB_ERR_ARG, "CIA species index out of range");
+  for (int i = 1; i < nwn; i++)
+    TB_REQUIRE(wn[i] > wn[i - 1], TB_ERR_ARG, "CIA table wavenumbers must increase");
   TB_CUDA(cudaSetDevice(c->device));
   CiaTable *t = new CiaTable();
   t->nw = nwn; t->nt = ntemp; t->nspec = nspec;
@@ -109,15 +202,47 @@ extern "C" int tb_cia_add_table(tb_ctx *c, const double *wn, int nwn, const doub
   t->wn.assign(wn, wn + nwn);
   t->temp.assign(temp, temp + ntemp);
   t->tab.assign(tab, tab + (size_t)nwn * ntemp);
-  if (t->d_wn.ensure(nwn) || t->d_temp.ensure(ntemp) || t->d_tab.ensure((size_t)nwn * ntemp)) {
+  // table-only parts of the two spline families, in the reference's operation order
+  // (tri + spline_init, spline.c:12-48,186-206)
+  std::vector<double> zt((size_t)nwn * ntemp, 0.0), h(nwn, 1.0), u(nwn, 1.0), uu(ntemp), vv(ntemp);
+  std::vector<double> rh(nwn, 1.0), rr(nwn, 0.0), ru(nwn, 1.0);
+  for (int i = 0; i < nwn; i++) {
+    const double *y = tab + (size_t)i * ntemp;
+    double *z = zt.data() + (size_t)i * ntemp;
+    for (int k = 1; k < ntemp - 1; k++) {
+      const double hk = temp[k + 1] - temp[k], hm = temp[k] - temp[k - 1];
+      const double bk = (y[k + 1] - y[k]) / hk, bm = (y[k] - y[k - 1]) / hm;
+      if (k == 1) { uu[k] = 2 * (hk + hm); vv[k] = 6 * (bk - bm); }
+      else { uu[k] = 2 * (hk + hm) - hm * hm / uu[k - 1]; vv[k] = 6 * (bk - bm) - vv[k - 1] * hm / uu[k - 1]; }
+    }
+    z[0] = z[ntemp - 1] = 0;
+    for (int k = ntemp - 2; k > 0; k--) z[k] = (vv[k] - (temp[k + 1] - temp[k]) * z[k + 1]) / uu[k];
+  }
+  for (int i = 0; i < nwn - 1; i++) h[i] = wn[i + 1] - wn[i];
+  for (int i = 1; i < nwn - 1; i++)
+    u[i] = (i == 1) ? 2 * (h[1] + h[0]) : 2 * (h[i] + h[i - 1]) - h[i - 1] * h[i - 1] / u[i - 1];
+  for (int i = 0; i < nwn - 1; i++) rh[i] = 1.0 / h[i];
+  for (int i = 1; i < nwn - 1; i++) { ru[i] = 1.0 / u[i]; if (i > 1) rr[i] = h[i - 1] / u[i - 1]; }
+  if (t->d_wn.ensure(nwn) || t->d_temp.ensure(ntemp) || t->d_tab.ensure((size_t)nwn * ntemp) ||
+      t->d_zt.ensure((size_t)nwn * ntemp) || t->d_h.ensure(nwn) || t->d_u.ensure(nwn) || t->d_rh.ensure(nwn) ||
+      t->d_r.ensure(nwn) || t->d_ru.ensure(nwn)) {
+    t->release();
     delete t;
     return TB_ERR_NOMEM;
   }
-  TB_CUDA(cudaMemcpyAsync(t->d_wn.p, wn, nwn * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  TB_CUDA(cudaMemcpyAsync(t->d_temp.p, temp, ntemp * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  TB_CUDA(cudaMemcpyAsync(t->d_tab.p, tab, (size_t)nwn * ntemp * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  TB_CUDA(cudaStreamSynchronize(c->stream));
+  cudaStream_t st = c->stream;
+  TB_CUDA(cudaMemcpyAsync(t->d_wn.p, wn, nwn * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(t->d_temp.p, temp, ntemp * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(t->d_tab.p, tab, (size_t)nwn * ntemp * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(t->d_zt.p, zt.data(), zt.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(t->d_h.p, h.data(), nwn * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(t->d_u.p, u.data(), nwn * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(t->d_rh.p, rh.data(), nwn * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(t->d_r.p, rr.data(), nwn * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(t->d_ru.p, ru.data(), nwn * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaStreamSynchronize(st));
   c->cia.push_back(t);
+  c->have_ecs = false;
   return TB_OK;
 }
 
@@ -125,56 +250,85 @@ int tb_cia_run(tb_ctx *c) {
   TB_REQUIRE(c->have_atm && c->have_grid, TB_ERR_STATE, "grid and atmosphere must be set before tb_cia_interp");
   TB_CUDA(cudaSetDevice(c->device));
   cudaStream_t st = c->stream;
-  const int nrad = c->nrad;
+  const int nrad = c->nrad, ntab = (int)c->cia.size();
   const int64_t nwn = c->nwn;
   TB_TRY(c->d_ecs.ensure((size_t)nrad * nwn));
-  TB_CUDA(cudaMemsetAsync(c->d_ecs.p, 0, sizeof(double) * nrad * nwn, st));
-  std::vector<double> ltemp(nrad);
+  if (ntab == 0) {
+    TB_CUDA(cudaMemsetAsync(c->d_ecs.p, 0, sizeof(double) * nrad * nwn, st));
+    c->have_ecs = true;
+    return TB_OK;
+  }
+  // host side, O(nrad * ntab): layer temperatures, density factors, layer ranges
+  std::vector<double> stage((size_t)nrad * (1 + ntab));
+  double *ltemp = stage.data();
   for (int i = 0; i < nrad; i++) ltemp[i] = c->t_fct * c->t[i];
-  DevBuf<double> d_lt;
-  TB_TRY(d_lt.ensure(nrad));
-  TB_CUDA(cudaMemcpyAsync(d_lt.p, ltemp.data(), nrad * sizeof(double), cudaMemcpyHostToDevice, st));
-  TB_TRY(c->c_densfac.ensure(nrad));
-  tb_timer_begin(c, "cia");
-  for (CiaTable *t : c->cia) {
-    // bicubicinterpolate's range logic (crosssec.c:366-393), on the host: O(nwn + nrad)
+  TB_TRY(c->c_stage.ensure(stage.size()));
+  CiaPack P;
+  P.n = 0;
+  auto gw = [&](int64_t k) { return c->wn_fct * (c->wn_i + (double)k * c->wn_d); };
+  for (int n = 0; n < ntab; n++) {
+    CiaTable *t = c->cia[n];
+    // bicubicinterpolate's range logic (crosssec.c:366-393)
     const double fx1 = t->wn[0], lx1 = t->wn[t->nw - 1], fx2 = t->temp[0], lx2 = t->temp[t->nt - 1];
-    auto gw = [&](int64_t k) { return c->wn_fct * (c->wn_i + (double)k * c->wn_d); };
-    if (gw(0) > lx1 || gw(nwn - 1) < fx1 || ltemp[0] > lx2 || ltemp[nrad - 1] < fx2) continue;
-    int64_t fi = 0, li = nwn;
-    while (fi < nwn && gw(fi) < fx1) fi++;
-    for (int64_t i = 0; i < li; i++) if (gw(i) > lx1) li = i;
+    if (t->grid_version != c->grid_version) {          // static per (table, grid): wavenumber range + intervals
+      t->fi = 0; t->li = nwn;
+      if (gw(0) > lx1 || gw(nwn - 1) < fx1) t->li = 0;
+      else {
+        while (t->fi < nwn && gw(t->fi) < fx1) t->fi++;
+        for (int64_t i = 0; i < t->li; i++) if (gw(i) > lx1) t->li = i;
+      }
+      TB_TRY(t->d_widx.ensure(nwn));
+      k_cia_widx<<<nblk(nwn, 256), 256, 0, st>>>(t->d_wn.p, t->nw, c->wn_i, c->wn_d, c->wn_fct, nwn, t->d_widx.p);
+      TB_LAUNCHED(c);
+      t->grid_version = c->grid_version;
+    }
+    if (t->fi >= t->li || ltemp[0] > lx2 || ltemp[nrad - 1] < fx2) continue;
     int fj = 0, lj = nrad;
     while (fj < nrad && ltemp[fj] < fx2) fj++;
     for (int j = 0; j < lj; j++) if (ltemp[j] > lx2) lj = j;
-    if (fi >= li || fj >= lj) continue;
-    std::vector<double> df(nrad, 1.0);
-    for (int i = 0; i < nrad; i++)
+    if (fj >= lj) continue;
+    double *df = stage.data() + (size_t)nrad * (1 + n);
+    for (int i = 0; i < nrad; i++) {
+      df[i] = 1.0;
       for (int k = 0; k < t->nspec; k++) {
-        int m = t->mol[k];
+        const int m = t->mol[k];
         df[i] *= c->dens[(size_t)m * nrad + i] / (TB_AMU * c->mol_mass[m] * TB_AMAGAT);
       }
-    TB_CUDA(cudaMemcpyAsync(c->c_densfac.p, df.data(), nrad * sizeof(double), cudaMemcpyHostToDevice, st));
-    TB_TRY(c->c_f2.ensure((size_t)nrad * t->nw));
-    TB_TRY(c->c_z2.ensure((size_t)nrad * t->nw));
-    TB_TRY(c->c_scr.ensure((size_t)nrad * 2 * t->nw));
-    k_cia_temp<<<nblk(t->nw, 64), 64, 0, st>>>(t->d_tab.p, t->d_temp.p, t->nw, t->nt, d_lt.p, fj, lj, c->c_f2.p);
-    k_cia_wnspline<<<nblk(lj - fj, 32), 32, 0, st>>>(t->d_wn.p, t->nw, fj, lj, c->c_f2.p, c->c_z2.p, c->c_scr.p);
-    dim3 g(nblk(li - fi, 128), lj - fj);
-    k_cia_eval<<<g, 128, 0, st>>>(t->d_wn.p, t->nw, c->c_f2.p, c->c_z2.p, c->wn_i, c->wn_d, c->wn_fct, nwn,
-                                  fi, li, fj, lj, c->c_densfac.p, c->d_ecs.p);
-    c->launches += 3;
-    TB_CUDA(cudaStreamSynchronize(st));   // df / densfac are reused by the next table
+    }
+    TB_TRY(t->d_f2.ensure((size_t)nrad * t->nw)); TB_TRY(t->d_z2.ensure((size_t)nrad * t->nw));
+    TB_TRY(t->d_v.ensure((size_t)nrad * t->nw));
+    CiaDev &D = P.t[P.n++];
+    D.wn = t->d_wn.p; D.f2 = t->d_f2.p; D.z2 = t->d_z2.p; D.widx = t->d_widx.p;
+    D.densfac = c->c_stage.p + (size_t)nrad * (1 + n);
+    D.fi = (int)t->fi; D.li = (int)t->li; D.fj = fj; D.lj = lj;
   }
+  TB_CUDA(cudaMemcpyAsync(c->c_stage.p, stage.data(), stage.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+  tb_timer_begin(c, "cia");
+  int k = 0;
+  for (int n = 0; n < ntab && k < P.n; n++) {
+    CiaTable *t = c->cia[n];
+    if (P.t[k].f2 != t->d_f2.p) continue;
+    const CiaDev &D = P.t[k++];
+    k_cia_temp<<<nblk((int64_t)t->nw * nrad, 256), 256, 0, st>>>(t->d_tab.p, t->d_zt.p, t->d_temp.p, t->nw, t->nt,
+                                                               c->c_stage.p, nrad, D.fj, D.lj, t->d_f2.p);
+    k_cia_wnspline<<<nblk(D.lj - D.fj, 32), 32, 0, st>>>(t->d_h.p, t->d_rh.p, t->d_r.p, t->d_ru.p, t->nw, nrad,
+                                                         D.fj, D.lj, t->d_f2.p, t->d_v.p, t->d_z2.p);
+    c->launches += 2;
+  }
+  dim3 g(nblk(nwn, 256), nrad);
+  k_cia_eval<<<g, 256, 0, st>>>(P, nrad, c->wn_i, c->wn_d, c->wn_fct, nwn, c->d_ecs.p);
+  TB_LAUNCHED(c);
   tb_timer_end(c, "cia");
   TB_CUDA(cudaGetLastError());
-  TB_CUDA(cudaStreamSynchronize(st));
-  d_lt.release();
   c->have_ecs = true;
   return TB_OK;
 }
 
-extern "C" int tb_cia_interp(tb_ctx *c) { return tb_cia_run(c); }
+extern "C" int tb_cia_interp(tb_ctx *c) {
+  TB_TRY(tb_cia_run(c));
+  TB_CUDA(cudaStreamSynchronize(c->stream));
+  return TB_OK;
+}
 
 // =============================================================== ray geometry
 
@@ -372,7 +526,115 @@ __global__ void k_tau(TauPar P, const double *__restrict__ e, const double *__re
   last[w] = lst;
 }
 
-extern "C" int tb_tau(tb_ctx *c, int geometry, double toomuch, const double *h, int nh, double hfct) {
+// Transit geometry, the production layout: a block owns 32 wavenumbers (one per lane) and
+// TAU_NW warps share the rays (ray ri -> warp ri % TAU_NW), all reading the block's extinction
+// columns er[layer][lane] from shared memory.  totaltau1 restores what it modifies
+// (slantpath.c:98-99), so rays are independent; the reference's early exit (tau.c:277-287)
+// becomes: each warp stops a lane at its first ray above `toomuch`, the block takes the minimum
+// over warps as last[w] and clears what was written beyond it (the reference leaves zeros there).
+#define TAU_NW 8
+__global__ void __launch_bounds__(32 * TAU_NW)
+k_tau_transit(TauPar P, const double *__restrict__ e, const double *__restrict__ ecs,
+              const double *__restrict__ press, const double *__restrict__ temp,
+              const double *__restrict__ aux, const double *__restrict__ mol_d,
+              const double *__restrict__ mol_pol, const double *__restrict__ mol_mass, int nmol,
+              const int32_t *__restrict__ meta, const double *__restrict__ par,
+              const double *__restrict__ coef, double *__restrict__ tau, int32_t *__restrict__ last) {
+  extern __shared__ double sm[];
+  __shared__ int sh_last[32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t w = blockIdx.x * 32LL + lane;
+  const bool inb = w < P.nwn;
+  const int nrad = P.nrad;
+  if (warp == 0) sh_last[lane] = P.nh;
+  if (inb) {
+    const double wn = P.wn_fct * __dadd_rn(P.wn_i, __dmul_rn((double)w, P.wn_d));
+    double kBP = 0, kFH = 0, refw = 1;
+    int ctop = -1, cbot = -1;   // cloud occupies layers (cbot, ctop]
+    if (P.cl_flag && P.cl_ext != 0) {
+      const double top = pow(10.0, P.cl_top), bot = pow(10.0, P.cl_bot);
+      int i = nrad - 1;
+      for (; i >= 0; i--) if (press[i] >= top) break;
+      ctop = i;
+      for (; i >= 0; i--) if (press[i] >= bot) break;
+      cbot = i;
+      const double x = 2 * TB_PI * P.cl_r * wn;
+      refw = pow(P.cl_refwn, P.cl_gamma);
+      kBP = P.cl_ext * pow(wn, P.cl_gamma);
+      kFH = P.cl_ext / (P.cl_Q * pow(x, -1 * P.cl_gamma) + pow(x, 0.2));
+    }
+    const double wn4 = P.sc_flag == 1 ? pow(wn, 4.0) : 0.0;
+    for (int r = warp; r < nrad; r += TAU_NW) {
+      double es = 0, ec = 0;
+      if (P.sc_flag == 1) es = P.sc_fac * press[r] / temp[r] * wn4;
+      else if (P.sc_flag == 2) {
+        for (int j = 0; j < nmol; j++)
+          es += TB_PI * 8e-32 / 3. * pow(mol_pol[j], 2.0) * pow(2. * TB_PI * wn * TB_MICRON, 4.0) *
+                mol_d[(size_t)j * nrad + r] / mol_mass[j] * TB_NAVOGADRO;
+      }
+      if (r <= ctop && r > cbot) {
+        const double md = aux[nrad + r];
+        switch (P.cl_flag) {
+          case 1: ec = P.cl_ext; break;
+          case 2: ec = P.cl_ext * md; break;
+          case 3: ec = kBP * md; break;
+          case 4: ec = kFH * md; break;
+          case 5: ec = aux[r] * kBP * P.cl_sig / refw * md; break;
+        }
+      }
+      // tau.c:231-232, same left-to-right sum
+      sm[r * 32 + lane] = e[(size_t)r * P.nwn + w] + es + ec + ecs[(size_t)r * P.nwn + w];
+    }
+  }
+  __syncthreads();
+  const double *er = sm + lane;
+  int myfirst = P.nh;                       // first ray of this warp above toomuch (none yet)
+  if (inb) {
+    for (int ri = warp; ri < P.nh; ri += TAU_NW) {
+      const int32_t *mt = meta + ri * 4;
+      const int mode = mt[2];
+      double t = 0.0;
+      if (mode > 0) {
+        const int rs = mt[0], n = mt[1], np = mt[3];
+        const double *pp = par + ri * 4;
+        const double *cf = coef + (size_t)ri * P.stride;
+        if (mode == 2) {
+          const double y0 = tb_parab(pp[0], pp[1], pp[2], er[(rs - 1) * 32], er[rs * 32], er[(rs + 1) * 32]);
+          const double yb = er[(rs + 1) * 32];
+          const double ya = (y0 + yb) / 2.0;
+          t = (y0 * cf[0] + ya * cf[1] + yb * cf[2]) * cf[3] / 6.0;
+        } else {
+          const double y0 = tb_parab(pp[0], pp[1], pp[2], er[rs * 32], er[(rs + 1) * 32], er[(rs + 2) * 32]);
+          const int even = (n % 2 == 0);
+          double res = 0.0;
+          for (int i = 0; i < np; i++) {
+            const int j = 2 * i + even;
+            const double a0 = (j == 0) ? y0 : er[(rs + j) * 32];
+            res += (a0 * cf[4 * i] + er[(rs + j + 1) * 32] * cf[4 * i + 1] +
+                    er[(rs + j + 2) * 32] * cf[4 * i + 2]) * cf[4 * i + 3];
+          }
+          t = res / 6.0;
+          if (even) t += pp[3] * (y0 + er[(rs + 1) * 32]) / 2;
+        }
+        t = P.rfct * (2 * t);
+      }
+      tau[(size_t)ri * P.nwn + w] = t;
+      if (t > P.toomuch) { myfirst = ri; break; }       // tau.c:277-287
+    }
+    atomicMin(&sh_last[lane], myfirst);
+  }
+  __syncthreads();
+  if (inb) {
+    const int lst = sh_last[lane];                       // == nh: never above toomuch
+    if (warp == 0) last[w] = lst < P.nh ? lst : P.nh - 1;
+    // clear what this warp wrote beyond the block-wide first exceed
+    const int upto = myfirst < P.nh ? myfirst : P.nh - 1;
+    for (int ri = warp; ri <= upto; ri += TAU_NW)
+      if (ri > lst) tau[(size_t)ri * P.nwn + w] = 0.0;
+  }
+}
+
+static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, int nh, double hfct, bool sync) {
   TB_REQUIRE(c->have_e && c->have_atm, TB_ERR_STATE, "extinction must be computed before tb_tau");
   TB_REQUIRE(geometry == TB_GEOM_TRANSIT || geometry == TB_GEOM_ECLIPSE, TB_ERR_ARG, "bad geometry");
   TB_CUDA(cudaSetDevice(c->device));
@@ -396,7 +658,7 @@ extern "C" int tb_tau(tb_ctx *c, int geometry, double toomuch, const double *h, 
     c->have_ecs = true;
   }
   const int stride = 4 * ((nrad + 2) / 2 + 1);
-  DevBuf<double> d_h, d_s;
+  DevBuf<double> &d_h = c->r_h, &d_s = c->r_s;
   TB_TRY(d_h.ensure(nh)); TB_TRY(d_s.ensure((size_t)nh * (nrad + 3)));
   TB_TRY(c->r_meta.ensure((size_t)nh * 4)); TB_TRY(c->r_par.ensure((size_t)nh * 4));
   TB_TRY(c->r_coef.ensure((size_t)nh * stride));
@@ -417,23 +679,44 @@ extern "C" int tb_tau(tb_ctx *c, int geometry, double toomuch, const double *h, 
   P.sc_fac = pow(10.0, c->sc_logext) * TB_E0H2;
   P.cl_ext = c->cl_ext; P.cl_top = c->cl_top; P.cl_bot = c->cl_bot; P.cl_gamma = c->cl_gamma;
   P.cl_Q = c->cl_Q; P.cl_r = c->cl_r; P.cl_sig = c->cl_sig; P.cl_refwn = c->cl_refwn;
-  const int TPB = 64;
-  const size_t shm = (size_t)nrad * TPB * sizeof(double);
-  TB_REQUIRE(shm <= 200 * 1024, TB_ERR_ARG, "too many layers (%d) for the tau kernel's shared memory", nrad);
-  TB_CUDA(cudaFuncSetAttribute(k_tau, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
   tb_timer_begin(c, "tau");
-  k_tau<<<nblk(nwn, TPB), TPB, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p, c->d_dens.p,
-                                          c->d_mol_pol.p, c->d_mol_mass.p, c->nmol, c->r_meta.p, c->r_par.p,
-                                          c->r_coef.p, c->d_tau.p, c->d_last.p);
+  if (geometry == TB_GEOM_ECLIPSE) {
+    const int TPB = 64;
+    const size_t shm = (size_t)nrad * TPB * sizeof(double);
+    TB_REQUIRE(shm <= 200 * 1024, TB_ERR_ARG, "too many layers (%d) for the tau kernel's shared memory", nrad);
+    TB_CUDA(cudaFuncSetAttribute(k_tau, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
+    k_tau<<<nblk(nwn, TPB), TPB, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p, c->d_dens.p,
+                                            c->d_mol_pol.p, c->d_mol_mass.p, c->nmol, c->r_meta.p, c->r_par.p,
+                                            c->r_coef.p, c->d_tau.p, c->d_last.p);
+  } else {
+    const size_t shm = (size_t)nrad * 32 * sizeof(double);
+    TB_REQUIRE(shm <= 200 * 1024, TB_ERR_ARG, "too many layers (%d) for the tau kernel's shared memory", nrad);
+    TB_CUDA(cudaFuncSetAttribute(k_tau_transit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
+    k_tau_transit<<<nblk(nwn, 32), 32 * TAU_NW, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p,
+                                                          c->d_dens.p, c->d_mol_pol.p, c->d_mol_mass.p, c->nmol,
+                                                          c->r_meta.p, c->r_par.p, c->r_coef.p, c->d_tau.p,
+                                                          c->d_last.p);
+  }
   tb_timer_end(c, "tau");
   c->launches += 2;
-  int32_t err[4];
-  TB_CUDA(cudaMemcpyAsync(err, c->d_err.p, sizeof(err), cudaMemcpyDeviceToHost, st));
-  TB_CUDA(cudaStreamSynchronize(st));
-  d_h.release(); d_s.release();
-  TB_REQUIRE(err[1] == 0, TB_ERR_DOMAIN, "a ray's closest approach lies below the bottom layer (slantpath.c:40-44)");
+  TB_CUDA(cudaGetLastError());
   c->have_tau = true;
+  if (sync) TB_TRY(tb_check_errors(c));
   return TB_OK;
+}
+
+// device-side error flags (set by k_ray_geometry / k_modulation), read back with one sync
+int tb_check_errors(tb_ctx *c) {
+  int32_t err[4];
+  TB_CUDA(cudaMemcpyAsync(err, c->d_err.p, sizeof(err), cudaMemcpyDeviceToHost, c->stream));
+  TB_CUDA(cudaStreamSynchronize(c->stream));
+  TB_REQUIRE(err[1] == 0, TB_ERR_DOMAIN, "a ray's closest approach lies below the bottom layer (slantpath.c:40-44)");
+  TB_REQUIRE(err[2] == 0, TB_ERR_DOMAIN, "less than 3 items for radial integration (slantpath.c:393-397)");
+  return TB_OK;
+}
+
+extern "C" int tb_tau(tb_ctx *c, int geometry, double toomuch, const double *h, int nh, double hfct) {
+  return tb_tau_run(c, geometry, toomuch, h, nh, hfct, true);
 }
 
 // =============================================================== modulation (a14)
@@ -477,7 +760,7 @@ extern "C" int tb_modulation(tb_ctx *c, double starrad_cm, int transparent, doub
   TB_REQUIRE(c->have_tau && c->geometry == TB_GEOM_TRANSIT, TB_ERR_STATE, "tb_tau (transit) must precede tb_modulation");
   TB_CUDA(cudaSetDevice(c->device));
   cudaStream_t st = c->stream;
-  DevBuf<double> d_ip;
+  DevBuf<double> &d_ip = c->r_ip;
   TB_TRY(d_ip.ensure(c->nh));
   TB_TRY(c->d_out.ensure(c->nwn));
   TB_CUDA(cudaMemcpyAsync(d_ip.p, c->h_h.data(), c->nh * sizeof(double), cudaMemcpyHostToDevice, st));
@@ -486,13 +769,8 @@ extern "C" int tb_modulation(tb_ctx *c, double starrad_cm, int transparent, doub
                                                   starrad_cm, transparent, c->d_out.p, c->d_err.p);
   tb_timer_end(c, "modulation");
   TB_LAUNCHED(c);
-  int32_t err[4];
-  TB_CUDA(cudaMemcpyAsync(err, c->d_err.p, sizeof(err), cudaMemcpyDeviceToHost, st));
   if (out) TB_CUDA(cudaMemcpyAsync(out, c->d_out.p, c->nwn * sizeof(double), cudaMemcpyDeviceToHost, st));
-  TB_CUDA(cudaStreamSynchronize(st));
-  d_ip.release();
-  TB_REQUIRE(err[2] == 0, TB_ERR_DOMAIN, "less than 3 items for radial integration (slantpath.c:393-397)");
-  return TB_OK;
+  return tb_check_errors(c);
 }
 
 // =============================================================== intensity + flux (a15)
@@ -542,7 +820,7 @@ extern "C" int tb_intensity_flux(tb_ctx *c, const double *angles_deg, int nang, 
   grid[nang] = 90.0 * TB_DEGREES;
   for (int i = 1; i < nang; i++) grid[i] = (ang[i - 1] + ang[i]) * TB_DEGREES / 2.0;
   for (int i = 0; i < nang; i++) area[i] = pow(sin(grid[i + 1]), 2.0) - pow(sin(grid[i]), 2.0);
-  DevBuf<double> d_a;
+  DevBuf<double> &d_a = c->r_ang;
   TB_TRY(d_a.ensure(2 * (size_t)nang));
   TB_TRY(c->d_intens.ensure((size_t)nang * c->nwn));
   TB_TRY(c->d_out.ensure(c->nwn));
@@ -555,10 +833,8 @@ extern "C" int tb_intensity_flux(tb_ctx *c, const double *angles_deg, int nang, 
   tb_timer_end(c, "intensity");
   TB_LAUNCHED(c);
   if (out) TB_CUDA(cudaMemcpyAsync(out, c->d_out.p, c->nwn * sizeof(double), cudaMemcpyDeviceToHost, st));
-  TB_CUDA(cudaStreamSynchronize(st));
-  d_a.release();
   c->nang = nang;
-  return TB_OK;
+  return tb_check_errors(c);
 }
 
 // =============================================================== do_transit in one call
@@ -568,7 +844,7 @@ extern "C" int tb_spectrum(tb_ctx *c, int geometry, double toomuch, double ethre
   TB_TRY(tb_cia_run(c));                                   // interpcs, transit.c:147
   if (c->have_grid_o) TB_TRY(tb_interp_run(c));            // interpolmolext (opacity file given)
   else TB_TRY(tb_extinction_lbl(c, ethresh));              // computemolext per layer
-  TB_TRY(tb_tau(c, geometry, toomuch, nullptr, 0, 0));     // tau, transit.c:165,189
+  TB_TRY(tb_tau_run(c, geometry, toomuch, nullptr, 0, 0, false));   // tau, transit.c:165,189
   if (geometry == TB_GEOM_ECLIPSE) return tb_intensity_flux(c, angles_deg, nang, out);
   return tb_modulation(c, starrad_cm, transparent, out);
 }

@@ -151,6 +151,8 @@ extern "C" int tb_build_profiles(tb_ctx *c, int nDop, int nLor, float dmin, floa
     v[n] = INFINITY;
   };
   logspace(dmin, dmax, nDop, c->aDop);
+  c->dop_lmin = log10((double)dmin);
+  c->dop_rstep = (nDop - 1.0) / (log10((double)dmax) - log10((double)dmin));
   logspace(lmin, lmax, nLor, c->aLor);
   c->psize.assign((size_t)nDop * nLor, 0);
   c->poff.assign((size_t)nDop * nLor, 0);
