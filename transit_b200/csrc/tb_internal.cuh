@@ -247,6 +247,35 @@ __device__ __forceinline__ int tb_binsearchapprox(const double *__restrict__ a, 
   return lo;
 }
 
+// exp(x) for the Boltzmann and stimulated-emission factors (extinction.c:409-413,455-458):
+// x <= 0 there.  Cody-Waite reduction x = k ln2 + r, |r| <= ln2/2, degree-13 Taylor polynomial
+// (truncation < 5e-18 relative), scaling by an exponent-field add: < 1 ulp like the library
+// exp() it replaces, in about a quarter of the instructions.  Outside [-690, 690] (results
+// near the denormal range, or the bogus positive arguments of negative energies) it defers
+// to the library.
+__device__ __forceinline__ double tb_exp(double x) {
+  if (!(x > -690.0 && x < 690.0)) return exp(x);
+  const double kf = rint(x * 1.4426950408889634074);
+  double r = fma(kf, -6.93147180369123816490e-01, x);       // ln2 high part
+  r = fma(kf, -1.90821492927058770002e-10, r);              // ln2 low part
+  double p = 1.6059043836821614599e-10;                     // 1/13!
+  p = fma(p, r, 2.0876756987868098979e-9);
+  p = fma(p, r, 2.5052108385441718775e-8);
+  p = fma(p, r, 2.7557319223985890653e-7);
+  p = fma(p, r, 2.7557319223985892511e-6);
+  p = fma(p, r, 2.4801587301587301566e-5);
+  p = fma(p, r, 1.9841269841269841253e-4);
+  p = fma(p, r, 1.3888888888888889419e-3);
+  p = fma(p, r, 8.3333333333333332177e-3);
+  p = fma(p, r, 4.1666666666666664354e-2);
+  p = fma(p, r, 1.6666666666666665741e-1);
+  p = fma(p, r, 0.5);
+  p = fma(p, r, 1.0);
+  p = fma(p, r, 1.0);
+  const int k = (int)kf;
+  return p * __hiloint2double((k + 1023) << 20, 0);
+}
+
 // internal entry points between translation units
 int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const double *Z,
                   double ethresh, int permol, double *d_out_rows, double *h_out);

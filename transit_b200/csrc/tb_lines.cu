@@ -444,7 +444,7 @@ __global__ void k_kmax(int64_t l0, int64_t l1, int ns, int niso, const double *_
       if (a > 0 || !(g < 0.9999999999 * cur * mass * z)) {
         if (!loaded) { w = q_w[l]; loaded = true; }
         const double rT = rtemp[s];
-        const double v = g * exp(a * rT) * (1 - exp(w * rT)) / mass / z;
+        const double v = g * tb_exp(a * rT) * (1 - tb_exp(w * rT)) / mass / z;
         if (v > cur) {
           if (use_sh) atomicMax(&sh_new[k][row], (unsigned long long)__double_as_longlong(v));
           else atomicMaxPosDouble(&kmax[s * nrows + row], v);
@@ -477,7 +477,7 @@ __global__ void k_extra(int64_t X, int ns, const int32_t *__restrict__ x_line,
   const double rT = rtemp[s];
   const double a = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
   xterm[(size_t)s * X + x] =
-      __dmul_rn(__dmul_rn(m_gf[l], exp(a * rT)), (1 - exp(__dmul_rn(-TB_EXPCTE, m_wavn[l]) * rT)));
+      __dmul_rn(__dmul_rn(m_gf[l], tb_exp(a * rT)), (1 - tb_exp(__dmul_rn(-TB_EXPCTE, m_wavn[l]) * rT)));
 }
 
 // extinction.c:439-483 for one (group, state): co-added strength in member order, scaling,
@@ -485,7 +485,7 @@ __global__ void k_extra(int64_t X, int ns, const int32_t *__restrict__ x_line,
 // and a 16-bit profile id.  The carried-index and tile-reach maxima are reduced in shared
 // memory first: a handful of global integer atomics per block instead of one per group.
 template <int SB>
-__global__ void k_strength(int64_t G, int ns, int niso, int o, FastDiv fd_tile,
+__global__ void __launch_bounds__(256, 4) k_strength(int64_t G, int ns, int niso, int o, FastDiv fd_tile,
                            const int32_t *__restrict__ g_start,
                            const int16_t *__restrict__ g_iso, const int32_t *__restrict__ g_orig,
                            const int32_t *__restrict__ g_iown,
@@ -539,14 +539,23 @@ __global__ void k_strength(int64_t G, int ns, int niso, int o, FastDiv fd_tile,
     bool fbk = false;     // group uses the carried index
     if (act) {
       const double rT = rtemp[s];
-      double acc = __dmul_rn(__dmul_rn(g0, exp(a0 * rT)), (1 - exp(w0 * rT)));
-      for (int l = b + 1; l < e; l++)                          // co-added members (extinction.c:449-462)
-        acc = __dadd_rn(acc, xterm[(size_t)s * X + (l - (int)p - 1)]);
       const int si = s * niso + iso;
-      double kk = __dmul_rn(acc, facz[si]);
+      const double fz = facz[si], thr = __dmul_rn(ethresh, kmax[s * nrows + row]);
+      const double ge1 = __dmul_rn(g0, tb_exp(a0 * rT));
+      double kk = 0.0;
+      // a lone line whose strength without the (<= 1) stimulated-emission factor is already
+      // clearly below the threshold is skipped without the second exp()
+      bool below = (e - b == 1) && ge1 * fz < 0.999999 * thr;
+      if (!below) {
+        double acc = __dmul_rn(ge1, (1 - tb_exp(w0 * rT)));
+        for (int l = b + 1; l < e; l++)                        // co-added members (extinction.c:449-462)
+          acc = __dadd_rn(acc, xterm[(size_t)s * X + (l - (int)p - 1)]);
+        kk = __dmul_rn(acc, fz);
+        below = kk < thr;                                      // extinction.c:467-470
+      }
       const size_t oo = (size_t)s * G + p;
       unsigned pid = PID_SKIP;
-      if (!(kk < __dmul_rn(ethresh, kmax[s * nrows + row]))) {   // extinction.c:467-470
+      if (!below) {
         if (!permol) kk = __dmul_rn(kk, dens[s * nmol + imol]);
         const double al = alphal[si], adw = __dmul_rn(alphad[si], wlead);
         // extinction.c:480-483: alphad*wavn/alphal >= 0.1, decided by the exact quotient whenever
@@ -698,10 +707,18 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
           const int mid = (a + b) >> 1;
           if (g_iown[mid] < lo_f) a = mid + 1; else b = mid;
         }
-        for (int p = a; p < p1; p++) {
-          const int io = g_iown[p];
-          if (io > hi_f) break;
-          unsigned pid = ps[p];
+        // software-pipelined walk: the next group's three independent loads are in flight
+        // while the current one is resolved
+        int p = a;
+        int io_n = p < p1 ? g_iown[p] : 0x7fffffff;
+        unsigned pid_n = p < p1 ? ps[p] : PID_SKIP;
+        double k_n = p < p1 ? ks[p] : 0.0;
+        while (p < p1 && io_n <= hi_f) {
+          const int io = io_n;
+          unsigned pid = pid_n;
+          const double kk = k_n;
+          p++;
+          if (p < p1) { io_n = g_iown[p]; pid_n = ps[p]; k_n = ks[p]; }
           if (pid == PID_SKIP) continue;
           if (pid >= PID_FB) pid = fbs[pid - PID_FB];
           const ProfEntry pe = ptab[pid];
@@ -712,7 +729,7 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
               const int q = fd_div(idx, fd);
               ad = (idx - q * o) * pe.nk + q;
             }
-            acc = fma(ks[p], pdata[pe.off + ad], acc);
+            acc = fma(kk, pdata[pe.off + ad], acc);
             cnt++;
           }
         }
@@ -753,7 +770,9 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
 #pragma unroll 4
         for (int i = 0; i < n; i++) {
           const AccRec r = sh_rec[warp][i];
-          if (lane >= (r.lanes & 255) && lane <= (r.lanes >> 8)) acc = fma(r.k, pdata[r.addr0 + lane], acc);
+          const double pv = pdata[r.addr0 + lane];     // unconditional (table is padded): loads overlap
+          const double t = fma(r.k, pv, acc);
+          acc = (lane >= (r.lanes & 255) && lane <= (r.lanes >> 8)) ? t : acc;
         }
         __syncwarp();
       }

@@ -59,75 +59,80 @@ __device__ double tb_splinterp_pt(const double *z, int N, const double *x, const
 #define CIA_MAXT 64
 #define CIA_MAXTAB 8
 
-// pass 1 (crosssec.c:407-412): f2[row][layer] = spline along T of table row `row` at the layer T
+// pass 1 (crosssec.c:407-412): f2[layer][row] = spline along T of table row `row` at the layer T
 __global__ void k_cia_temp(const double *__restrict__ tab, const double *__restrict__ zt,
                            const double *__restrict__ ttemp, int ntw, int ntt,
                            const double *__restrict__ ltemp, int nrad, int fj, int lj,
                            double *__restrict__ f2) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= ntw * nrad) return;
-  const int i = t / nrad, j = t % nrad;
+  const int j = t / ntw, i = t % ntw;
   if (j < fj || j >= lj) return;
   f2[t] = tb_splinterp_pt(zt + (size_t)i * ntt, ntt, ttemp, tab + (size_t)i * ntt, ltemp[j]);
 }
 
-// pass 2a (crosssec.c:415-416, spline.c:12-48): second derivatives along the table wavenumbers,
-// one thread per layer, arrays laid out [row][layer] so a warp of layers moves coalesced.
-// Everything that depends only on the table comes precomputed (rh = 1/h, r = h[i-1]/u[i-1],
-// ru = 1/u), which leaves one fused multiply-add per row on each sweep's dependency chain;
-// the column is fetched CH rows at a time so the loads are in flight together.
-#define CIA_CH 16
+// pass 2a (crosssec.c:415-416, spline.c:12-48): second derivatives along the table wavenumbers.
+// Both sweeps of the tridiagonal solve are first-order linear recurrences
+//     v[i] = c[i] - r[i] v[i-1],     z[i] = (v[i] - h[i] z[i+1]) ru[i]
+// (r = h[i-1]/u[i-1], ru = 1/u: table-only, precomputed).  One warp per layer: every lane
+// composes the affine map of its contiguous segment of rows, the 32 maps are chained through
+// shuffles, and the lane then replays its segment from the right starting value.
 __global__ void k_cia_wnspline(const double *__restrict__ h, const double *__restrict__ rh,
                                const double *__restrict__ r, const double *__restrict__ ru, int ntw,
-                               int nrad, int fj, int lj, const double *__restrict__ f2,
-                               double *__restrict__ v, double *__restrict__ z2) {
-  const int j = fj + blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= lj) return;
-  const size_t st = nrad;
-  const double *y = f2 + j;
-  double *vv = v + j, *zz = z2 + j;
-  if (ntw > 2) {
-    double y0 = y[st];
-    double bm = (y0 - y[0]) * rh[0], vprev = 0.0;
-    for (int i0 = 1; i0 < ntw - 1; i0 += CIA_CH) {
-      double yb[CIA_CH];
-#pragma unroll
-      for (int q = 0; q < CIA_CH; q++) yb[q] = (i0 + q < ntw - 1) ? y[(size_t)(i0 + q + 1) * st] : 0.0;
-#pragma unroll
-      for (int q = 0; q < CIA_CH; q++) {
-        const int i = i0 + q;
-        if (i < ntw - 1) {
-          const double bi = (yb[q] - y0) * rh[i];
-          vprev = (i == 1) ? 6 * (bi - bm) : 6 * (bi - bm) - vprev * r[i];
-          vv[(size_t)i * st] = vprev;
-          bm = bi;
-          y0 = yb[q];
-        }
-      }
-    }
+                               int fj, int lj, const double *__restrict__ f2, double *__restrict__ v,
+                               double *__restrict__ z2) {
+  const int lane = threadIdx.x & 31;
+  const int j = fj + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  if (j >= lj) return;                                   // whole warp
+  const double *y = f2 + (size_t)j * ntw;
+  double *vv = v + (size_t)j * ntw, *zz = z2 + (size_t)j * ntw;
+  const int L = (ntw - 2 + 31) / 32;                      // rows 1 .. ntw-2
+  const int a = 1 + lane * L;
+  const int b = a + L < ntw - 1 ? a + L : ntw - 1;
+  const unsigned full = 0xffffffffu;
+  // ---- forward sweep
+  double A = 1.0, B = 0.0;
+  for (int i = a; i < b; i++) {
+    const double c = 6 * ((y[i + 1] - y[i]) * rh[i] - (y[i] - y[i - 1]) * rh[i - 1]);
+    B = c - r[i] * B;
+    A = -r[i] * A;
   }
-  zz[0] = 0;
-  zz[(size_t)(ntw - 1) * st] = 0;
-  double znext = 0;
-  for (int i0 = ntw - 2; i0 > 0; i0 -= CIA_CH) {
-    double vb[CIA_CH];
-#pragma unroll
-    for (int q = 0; q < CIA_CH; q++) vb[q] = (i0 - q > 0) ? vv[(size_t)(i0 - q) * st] : 0.0;
-#pragma unroll
-    for (int q = 0; q < CIA_CH; q++) {
-      const int i = i0 - q;
-      if (i > 0) {
-        znext = (vb[q] - h[i] * znext) * ru[i];
-        zz[(size_t)i * st] = znext;
-      }
-    }
+  double carry = 0.0, mine = 0.0;
+  for (int l = 0; l < 32; l++) {
+    const double Al = __shfl_sync(full, A, l), Bl = __shfl_sync(full, B, l);
+    if (lane == l) mine = carry;
+    carry = Al * carry + Bl;
   }
+  double vp = mine;
+  for (int i = a; i < b; i++) {
+    const double c = 6 * ((y[i + 1] - y[i]) * rh[i] - (y[i] - y[i - 1]) * rh[i - 1]);
+    vp = c - r[i] * vp;
+    vv[i] = vp;
+  }
+  // ---- backward sweep (each lane reads back only what it wrote)
+  A = 1.0; B = 0.0;
+  for (int i = b - 1; i >= a; i--) {
+    B = (vv[i] - h[i] * B) * ru[i];
+    A = -h[i] * ru[i] * A;
+  }
+  carry = 0.0; mine = 0.0;
+  for (int l = 31; l >= 0; l--) {
+    const double Al = __shfl_sync(full, A, l), Bl = __shfl_sync(full, B, l);
+    if (lane == l) mine = carry;
+    carry = Al * carry + Bl;
+  }
+  double zn = mine;
+  for (int i = b - 1; i >= a; i--) {
+    zn = (vv[i] - h[i] * zn) * ru[i];
+    zz[i] = zn;
+  }
+  if (lane == 0) { zz[0] = 0; zz[ntw - 1] = 0; }
 }
 
 struct CiaDev {
   const double *wn, *f2, *z2, *densfac;
   const int32_t *widx;
-  int fi, li, fj, lj;
+  int fi, li, fj, lj, ntw;
 };
 struct CiaPack {
   CiaDev t[CIA_MAXTAB];
@@ -159,8 +164,8 @@ __global__ void k_cia_eval(CiaPack P, int nrad, double wn_i, double wn_d, double
     if (w < T.fi || w >= T.li || j < T.fj || j >= T.lj) continue;
     const int idx = T.widx[w];
     const double x_lo = T.wn[idx], x_hi = T.wn[idx + 1];
-    const double y_lo = T.f2[(size_t)idx * nrad + j], y_hi = T.f2[(size_t)(idx + 1) * nrad + j];
-    const double z_lo = T.z2[(size_t)idx * nrad + j], z_hi = T.z2[(size_t)(idx + 1) * nrad + j];
+    const double y_lo = T.f2[(size_t)j * T.ntw + idx], y_hi = T.f2[(size_t)j * T.ntw + idx + 1];
+    const double z_lo = T.z2[(size_t)j * T.ntw + idx], z_hi = T.z2[(size_t)j * T.ntw + idx + 1];
     const double h = x_hi - x_lo, dy = y_hi - y_lo;
     double val = 0;
     if (x_lo == xout) val = y_lo;
@@ -300,7 +305,7 @@ int tb_cia_run(tb_ctx *c) {
     CiaDev &D = P.t[P.n++];
     D.wn = t->d_wn.p; D.f2 = t->d_f2.p; D.z2 = t->d_z2.p; D.widx = t->d_widx.p;
     D.densfac = c->c_stage.p + (size_t)nrad * (1 + n);
-    D.fi = (int)t->fi; D.li = (int)t->li; D.fj = fj; D.lj = lj;
+    D.fi = (int)t->fi; D.li = (int)t->li; D.fj = fj; D.lj = lj; D.ntw = t->nw;
   }
   TB_CUDA(cudaMemcpyAsync(c->c_stage.p, stage.data(), stage.size() * sizeof(double), cudaMemcpyHostToDevice, st));
   tb_timer_begin(c, "cia");
@@ -311,8 +316,8 @@ int tb_cia_run(tb_ctx *c) {
     const CiaDev &D = P.t[k++];
     k_cia_temp<<<nblk((int64_t)t->nw * nrad, 256), 256, 0, st>>>(t->d_tab.p, t->d_zt.p, t->d_temp.p, t->nw, t->nt,
                                                                c->c_stage.p, nrad, D.fj, D.lj, t->d_f2.p);
-    k_cia_wnspline<<<nblk(D.lj - D.fj, 32), 32, 0, st>>>(t->d_h.p, t->d_rh.p, t->d_r.p, t->d_ru.p, t->nw, nrad,
-                                                         D.fj, D.lj, t->d_f2.p, t->d_v.p, t->d_z2.p);
+    k_cia_wnspline<<<nblk(D.lj - D.fj, 4), 128, 0, st>>>(t->d_h.p, t->d_rh.p, t->d_r.p, t->d_ru.p, t->nw, D.fj, D.lj,
+                                                         t->d_f2.p, t->d_v.p, t->d_z2.p);
     c->launches += 2;
   }
   dim3 g(nblk(nwn, 256), nrad);

@@ -210,7 +210,7 @@ extern "C" int tb_build_profiles(tb_ctx *c, int nDop, int nLor, float dmin, floa
   // polyphase copy: min(o, n) phases of nk = (n-1)/o + 1 samples each per unique profile
   std::vector<int32_t> off2(desc.size());
   std::vector<ProfEntry> ptab((size_t)nDop * nLor);
-  int64_t total2 = 0;
+  int64_t total2 = 32;     // 32 floats of padding either side: the warp path reads lanes it then discards
   {
     std::map<int64_t, size_t> by_off;
     for (size_t k = 0; k < desc.size(); k++) {
