@@ -36,44 +36,77 @@ CLOCK_Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slo
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    """SM clock / power / throttle reasons sampled DURING the timed region (B200_PROFILING.md): NVML
+    polled every few ms from a thread (the timed region is tens of ms), nvidia-smi as the fallback."""
+
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, index: int):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.stop_flag, self.th, self.how = index, [], False, None, None
 
     def start(self):
         try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(vis.split(",")[self.index]) if vis and vis.split(",")[0].isdigit() else self.index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.nv = pynvml
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.how = "nvml"
+            self.th = threading.Thread(target=self._poll_nvml, daemon=True)
+            self.th.start()
+            return
+        except Exception:
+            pass
+        try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={CLOCK_Q}", "--format=csv,noheader,nounits",
                                           "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            self.how = "nvidia-smi"
+            self.th = threading.Thread(target=self._read_smi, daemon=True)
+            self.th.start()
         except OSError:
-            self.proc = None
-            return
-        self.th = threading.Thread(target=self._read, daemon=True)
-        self.th.start()
+            self.how = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
-
-    def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        self.th.join(timeout=2)
-        sm, mx, reasons, pw = [], [], set(), []
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+    def _poll_nvml(self):
+        nv = self.nv
+        while not self.stop_flag:
             try:
-                sm.append(float(r[1])); mx.append(float(r[2])); pw.append(float(r[3]))
+                sm = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                try:
+                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except AttributeError:
+                    rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.rows.append((sm, self.mx, pw, {n for bit, n in self.REASONS.items() if rs & bit}))
+            except Exception:
+                pass
+            time.sleep(0.004)
+
+    def _read_smi(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.proc.stdout:
+            r = [x.strip() for x in line.split(",")]
+            try:
+                rs = {nm for k, nm in enumerate(names) if len(r) > 4 + k and r[4 + k].lower().startswith("active")}
+                self.rows.append((float(r[1]), float(r[2]), float(r[3]), rs))
             except (ValueError, IndexError):
                 continue
-            for k, nm in enumerate(names):
-                if len(r) > 4 + k and r[4 + k].lower().startswith("active"):
-                    reasons.add(nm)
+
+    def stop(self):
+        if not self.how:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no NVML / nvidia-smi"]}
+        self.stop_flag = True
+        if self.how == "nvidia-smi":
+            self.proc.terminate()
+        self.th.join(timeout=2)
+        sm = [r[0] for r in self.rows]; mx = [r[1] for r in self.rows]; pw = [r[2] for r in self.rows]
+        reasons = set().union(*[r[3] for r in self.rows]) if self.rows else set()
         # "under load" = samples drawing more than half of the highest power seen
-        load = [s for s, p in zip(sm, pw) if pw and p >= 0.5 * max(pw)] or sm
+        load = [s_ for s_, p_ in zip(sm, pw) if pw and p_ >= 0.5 * max(pw)] or sm
         return {"sm_mhz": float(np.median(load)) if load else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "source": self.how,
+                "reasons": sorted(reasons)}
 
 
 def dist_env():
@@ -183,8 +216,8 @@ def run_reference(args):
               f"(process i -> band i mod {nbands}; full {nlines}-line list on disk); value = processes / bands / step time")
     line = {"impl": "reference", "metric": "spectra/s", "value": value, "unit": "spectra/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(prob, args.workload),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(prob, args.workload, args.gpus),
             "cpu_baseline": {"value": value, "unit": "spectra/s", "cores": cores, "kind": "reference", "sample": sample},
             "e2e": {"value": value, "unit": "spectra/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -192,8 +225,10 @@ def run_reference(args):
     return 0
 
 
-def workload_config(prob, name):
-    return {"workload": f"{name}: HAT-P-11b-shape transmission 0.3-5 um, line-by-line" if name == "C2" else name,
+def workload_config(prob, name, world=1):
+    return {"sharding": f"atmospheres x{world} (one spectrum per rank per step, NCCL all-gather of the spectra)"
+            if world > 1 else "none",
+            "workload": f"{name}: HAT-P-11b-shape transmission 0.3-5 um, line-by-line" if name == "C2" else name,
             "nwn": int(prob.nwn), "wnosamp": int(prob.wnosamp), "layers": int(prob.nrad), "lines": int(len(prob.wl)),
             "isotopologues": int(prob.niso), "line_molecules": len(prob.cfg["molecules"]), "cia_tables": len(prob.cia),
             "geometry": "eclipse" if prob.eclipse else "transit", "voigt_table": "60x60", "l2": "flushed between steps"}
@@ -239,13 +274,20 @@ def run_ours(args):
     assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
 
     prob = workloads.make_problem(args.workload, scale=args.scale)
+    # N > 1: batched atmospheres sharded over the ranks (BART's use of the library: many T-P/abundance
+    # profiles through one static problem) -- rank r computes the spectra of its own atmosphere,
+    # no data-path collective; the spectra are gathered with NCCL.  Per-GPU work is fixed: weak scaling.
+    my_prob = prob if rank == 0 else workloads.perturbed(prob, seed=1000 + rank)
     t0 = time.perf_counter()
     tr = sharding.ShardedTransit(local_rank, rank, world)
-    tr.transit_init(prob)
+    stream = torch.cuda.current_stream()
+    tr.ctx.set_stream(stream.cuda_stream)              # kernels, copies and the NCCL gather share one stream
+    tr.transit_init(my_prob)
     tr.ctx.sync()
     init_s = time.perf_counter() - t0
     ctx = tr.ctx
     out = np.zeros(prob.nwn)
+    gathered = torch.zeros(world, prob.nwn, dtype=torch.float64, device="cuda") if world > 1 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
 
     def barrier():
@@ -254,8 +296,13 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
+    def step():
         tr.do_transit(out)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered.view(-1), tr.device_spectrum_tensor())
+
+    for _ in range(args.warmup):
+        step()
     ref_out = out.copy()
 
     # ---- device-timed steps (static inputs resident; L2 flushed between steps)
@@ -264,14 +311,15 @@ def run_ours(args):
     barrier()
     l0 = ctx.launch_count()
     ms_steps, k_ms = [], {}
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for _ in range(args.steps):
         flush.zero_()
         barrier()
-        ctx.timer_start("step")
-        tr.do_transit(out)
-        ctx.timer_stop("step")
-        ctx.sync()
-        ms_steps.append(ctx.kernel_ms("step"))
+        ev0.record(stream)
+        step()
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        ms_steps.append(ev0.elapsed_time(ev1))
         for nm in ("kmax", "strength", "accumulate", "molext", "cia", "tau", "modulation"):
             try:
                 k_ms.setdefault(nm, []).append(ctx.kernel_ms(nm))
@@ -282,13 +330,15 @@ def run_ours(args):
     nsamp = int(tr.sample_counts().sum())                 # this rank's executed profile updates per step
     clocks = sampler.stop()
     assert np.array_equal(out, ref_out), "spectrum changed between steps: the path is not deterministic"
+    if world > 1:
+        assert np.array_equal(gathered[rank].cpu().numpy(), out), "gathered slice differs from the local spectrum"
 
     # ---- end to end through the host mirror with HOST buffers (H2D atmosphere + D2H spectrum per step)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        tr.set_atmosphere(prob)
-        tr.do_transit(out)
+        tr.set_atmosphere(my_prob)
+        step()
     barrier()
     e2e_s = time.perf_counter() - t0
     h2d = 8 * prob.nrad * (3 + prob.nmol + prob.niso)
@@ -310,20 +360,29 @@ def run_ours(args):
     mol_ms = float(np.mean(k_ms["molext"]))
     G, ns, nwn = tr.ngroups(), prob.nrad, tr.band_nwn()
     my_samp = int(tr.sample_counts().sum())
-    acc_bytes = 4.0 * my_samp + 9.0 * G * ns + 8.0 * nwn * ns
+    # algorithmic bytes of the gather kernel: 4 B of Voigt profile per line-sample
+    # (SURVEY.md 8d), 10 B of strength + profile id per (group, layer), 8 B written per (bin, layer)
+    acc_bytes = 4.0 * my_samp + 10.0 * G * ns + 8.0 * nwn * ns
     achieved = acc_bytes / (acc_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            traffic = json.load(f).get("k_accumulate", {}).get("dram_bytes_per_launch")
+    except (OSError, ValueError):
+        pass
     line = {
-        "metric": "spectra/s", "value": args.steps / (dev_ms * 1e-3), "unit": "spectra/s", "n_gpus": world,
+        "metric": "spectra/s", "value": world * args.steps / (dev_ms * 1e-3), "unit": "spectra/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": dict(workload_config(prob, args.workload), sharding=f"wavenumber bands x{world}" if world > 1 else "none"),
-        "e2e": {"value": args.steps / e2e_s, "unit": "spectra/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(prob, args.workload, world),
+        "e2e": {"value": world * args.steps / e2e_s, "unit": "spectra/s", "h2d_bytes_per_step": h2d * world,
+                "d2h_bytes_per_step": d2h * world},
         "gpu_launches": launches,
         "line_sum": {"gsamples_per_s": nsamp / (mol_ms * 1e-3) / 1e9, "samples_per_step": nsamp,
                      "line_layers_per_s": len(prob.wl) * prob.nrad / (mol_ms * 1e-3), "molext_ms": mol_ms},
         "kernel_ms": {k: float(np.mean(v)) for k, v in k_ms.items()},
         "roofline": {"kernel": "k_accumulate", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src, "ms": acc_ms,
+                     "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src, "ms": acc_ms,
                      "algorithmic_bytes": acc_bytes,
                      "fp64_gflops": 2.0 * my_samp / (acc_ms * 1e-3) / 1e9},
         "clocks": clocks, "init_s": init_s,
@@ -341,8 +400,8 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="C2")
     ap.add_argument("--scale", type=float, default=1.0, help="line-count multiplier (debugging only; 1.0 = the named config)")

@@ -136,6 +136,12 @@ int  tb_timer_start(tb_ctx *c, const char *name);
 int  tb_timer_stop(tb_ctx *c, const char *name);
 int64_t tb_launch_count(tb_ctx *c);
 void *tb_stream(tb_ctx *c);          /* cudaStream_t of the context */
+/* run on a caller-owned stream (e.g. the host framework's current stream) from now on;
+ * NULL returns to the context's own stream.  The caller keeps ownership of `stream`.   */
+int  tb_set_stream(tb_ctx *c, void *stream);
+/* device address of the last spectrum (out[nwn], FP64) for device-side consumers such as an
+ * NCCL gather of per-rank spectra; valid until the next call that produces a spectrum.  */
+int  tb_device_spectrum(tb_ctx *c, void **ptr, int64_t *n);
 
 /* device micro-benchmarks used for the roofline denominators (FP64 FMA / exp / copy)   */
 int  tb_microbench(tb_ctx *c, double *dfma_tflops, double *dexp_gops, double *copy_gbs);

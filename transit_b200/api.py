@@ -72,6 +72,8 @@ ABI = {
     "tb_timer_stop": (C.c_int, [C.c_void_p, C.c_char_p]),
     "tb_launch_count": (C.c_int64, [C.c_void_p]),
     "tb_stream": (C.c_void_p, [C.c_void_p]),
+    "tb_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "tb_device_spectrum": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), i64p]),
     "tb_microbench": (C.c_int, [C.c_void_p, f64p, f64p, f64p]),
 }
 
@@ -330,6 +332,16 @@ class Context:
 
     def launch_count(self):
         return int(self.lib.tb_launch_count(self.h))
+
+    def set_stream(self, stream_ptr):
+        """Run on a caller-owned cudaStream_t (integer handle), e.g. torch.cuda.current_stream().cuda_stream."""
+        self._ck(self.lib.tb_set_stream(self.h, C.c_void_p(stream_ptr)), "tb_set_stream")
+
+    def device_spectrum(self):
+        """(device pointer, n) of the last spectrum, for device-side consumers (NCCL gather)."""
+        p, n = C.c_void_p(), C.c_int64()
+        self._ck(self.lib.tb_device_spectrum(self.h, C.byref(p), C.byref(n)), "tb_device_spectrum")
+        return p.value, n.value
 
     def sync(self):
         self._ck(self.lib.tb_sync(self.h), "tb_sync")

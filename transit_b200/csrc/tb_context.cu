@@ -53,6 +53,20 @@ extern "C" int tb_timer_stop(tb_ctx *c, const char *name) {
 extern "C" int64_t tb_launch_count(tb_ctx *c) { return c->launches; }
 extern "C" void *tb_stream(tb_ctx *c) { return (void *)c->stream; }
 
+extern "C" int tb_set_stream(tb_ctx *c, void *stream) {
+  TB_CUDA(cudaSetDevice(c->device));
+  TB_CUDA(cudaStreamSynchronize(c->stream));
+  c->stream = stream ? (cudaStream_t)stream : c->own_stream;
+  return TB_OK;
+}
+
+extern "C" int tb_device_spectrum(tb_ctx *c, void **ptr, int64_t *n) {
+  TB_REQUIRE(c->d_out.p && c->nwn > 0, TB_ERR_STATE, "no spectrum computed yet");
+  *ptr = (void *)c->d_out.p;
+  *n = c->nwn;
+  return TB_OK;
+}
+
 extern "C" int tb_create(int device, tb_ctx **out) {
   TB_REQUIRE(out, TB_ERR_ARG, "tb_create: out is NULL");
   int ndev = 0;
@@ -73,7 +87,8 @@ extern "C" int tb_create(int device, tb_ctx **out) {
   tb_ctx *c = new tb_ctx();
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
-  TB_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  TB_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+  c->stream = c->own_stream;
   TB_TRY(c->d_err.ensure(4));
   TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4 * sizeof(int32_t), c->stream));
   *out = c;
@@ -111,7 +126,7 @@ extern "C" void tb_destroy(tb_ctx *c) {
     if (kv.second.a) cudaEventDestroy(kv.second.a);
     if (kv.second.b) cudaEventDestroy(kv.second.b);
   }
-  cudaStreamDestroy(c->stream);
+  cudaStreamDestroy(c->own_stream);
   delete c;
 }
 

@@ -112,7 +112,7 @@ struct KernelTimer {
 struct tb_ctx {
   int device = 0;
   int sm_count = 148;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr, own_stream = nullptr;
   int64_t launches = 0;
   std::map<std::string, KernelTimer> timers;
 

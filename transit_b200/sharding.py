@@ -16,8 +16,15 @@ class ShardedTransit(api.Transit):
     def __init__(self, device=0, rank=0, world=1):
         super().__init__(device)
         self.rank, self.world = rank, world
-        if world > 1:
-            raise NotImplementedError("band sharding lands with tb_set_band (next milestone)")
+
+    def device_spectrum_tensor(self):
+        """The last spectrum as a torch CUDA tensor aliasing the context's device buffer."""
+        import torch
+        ptr, n = self.ctx.device_spectrum()
+
+        class _Alias:
+            __cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+        return torch.as_tensor(_Alias(), device="cuda")
 
     def set_atmosphere(self, prob):
         self.ctx.set_atmosphere(prob.rad, prob.rad_fct, prob.p, prob.p_fct, prob.t, prob.t_fct, prob.mol_d, prob.iso_z)

@@ -114,6 +114,30 @@ def make_problem(name="C2", scale=1.0, nlayers=None, wn_hi=None, wnosamp=None, s
         atm=atm)
 
 
+def perturbed(prob, seed, dT=60.0, dex=0.3):
+    """Another atmosphere on the same static problem (what BART feeds run_transit): a smooth
+    temperature offset of at most ``dT`` K and log-abundance offsets of at most ``dex`` for the
+    line-list molecules; densities and partition functions follow (stateeqnford, Z(T))."""
+    import copy
+    rng = np.random.default_rng(seed)
+    p = copy.copy(prob)
+    x = np.linspace(0.0, 1.0, prob.nrad)
+    T = prob.t + dT * (rng.uniform(-1, 1) * (1 - x) + rng.uniform(-1, 1) * x) * 0.5
+    T = np.round(np.clip(T, 250.0, 2900.0), 2)
+    q = prob.mol_q.copy()
+    for j, s in enumerate(prob.species_names):
+        if s in prob.cfg["molecules"]:
+            q[j] = q[j] * 10.0 ** rng.uniform(-dex, dex)
+    p.t, p.mol_q = T, q
+    p.mol_d = np.stack([AMU * q[j] * (prob.p * 1e6) / KB / T * prob.mol_mass[j] for j in range(prob.nmol)])
+    iso_mol, iso_k, k = [], [], 0
+    for db in prob.dbs:
+        for kk in range(len(db.iso_names)):
+            iso_mol.append(db.molecule); iso_k.append(kk)
+    p.iso_z = np.stack([partition_function(iso_mol[i], iso_k[i], T) for i in range(prob.niso)])
+    return p
+
+
 def write_reference_inputs(prob, outdir, line_fraction=1.0, molfile=None, band=None, tag="run"):
     """The same problem as files for the unmodified reference binary (bench cpu_baseline)."""
     os.makedirs(outdir, exist_ok=True)
