@@ -1,0 +1,114 @@
+/* th_internal.h -- the C host of the B200 transit path.
+ *
+ * Keeps the reference's process-level face (transit [-c file] [--key value ...], cfg keys,
+ * atmosphere / TLI / molecules.dat / CS / opacity file formats, spectrum output) and its
+ * library-level face (transit_init, run_transit, ... transit/src/transit.i:11-19,95-104), and
+ * hands every array of the hot path to libtransit_b200.so through include/transit_b200.h.
+ * No physics of the hot path is computed here: only I/O, units, and the O(layers)
+ * per-atmosphere setup (densities, hydrostatic radii, partition-function splines).
+ */
+#ifndef TH_INTERNAL_H
+#define TH_INTERNAL_H
+#include <stdint.h>
+#include <stdio.h>
+#include "../include/transit_b200.h"
+
+#define TH_AMU 1.66053886e-24
+#define TH_KB 1.380658e-16
+#define TH_SUNRADIUS 6.957e10
+#define TH_MAXNAME 64
+
+/* transithint (structures_tr.h:300-370): what the option table of argum.c:112-320 fills */
+typedef struct {
+  char *f_atm, *f_line, *f_molfile, *f_outspec, *f_toomuch, *f_outsample, *f_outintens, *f_opa;
+  char *csfiles;                  /* comma-separated */
+  char *solname;
+  char *raygrid, *qmol, *qscale;
+  double rad_d;                   /* raddelt (-1: keep the atmosphere file's layers)          */
+  double wl_i, wl_f, wl_fct;      /* wllow, wlhigh, wlfct                                     */
+  double wn_i, wn_f, wn_d, wn_fct;
+  int wn_o;
+  int nDop, nLor;
+  float dmin, dmax, lmin, lmax, nwidth;
+  double ethresh, toomuch;
+  double tlow, thigh, tempdelt;
+  double starrad;
+  double p0, r0, gsurf, allowq;
+  int transparent, opabreak, verb;
+  int cl_flag;
+  double cl_ext, cl_top, cl_bot, cl_gamma, cl_Q, cl_r, cl_sig, cl_refwn;
+  int sc_flag;
+  double sc_logext;
+} th_hints;
+
+typedef struct {          /* one TLI database (readlineinfo.c:87-244) */
+  char name[TH_MAXNAME], molname[TH_MAXNAME];
+  int nT, niso, first;    /* first: index of its first isotope in the global list */
+  double *T;
+} th_db;
+
+typedef struct {
+  th_hints h;
+  /* wavenumber sampling (makewnsample) */
+  double wn_i, wn_f, wn_d;
+  int wn_o;
+  int64_t nwn, onwn;
+  /* atmosphere file (getatm): bottom layer first */
+  int nlayer, nmol, bymass;
+  double rad_fct, p_fct, t_fct, zerorad;
+  double *rad, *p, *t, *mm;       /* [nlayer] file units */
+  double *q, *d;                  /* [nmol][nlayer] abundance, density g/cm3 */
+  char (*molname)[TH_MAXNAME];
+  int *molID;
+  double *molmass, *molradius, *molpol;
+  /* line database (readtli_bin, readdatarng) */
+  int ndb, niso;
+  th_db *db;
+  double *isomass, *isoratio, *isoZ;   /* isoZ[iso][nT of its db] flattened via isoZoff */
+  int64_t *isoZoff;
+  int *isodb, *isoimol;
+  double tli_tmin, tli_tmax;
+  int64_t nlines;
+  double *wl, *elow, *gf;
+  int16_t *isoid;
+  /* CS files */
+  int ncs;
+  /* sampled state handed to the device (makeradsample) */
+  double *Zlayer;                 /* [niso][nlayer] */
+  /* geometry */
+  int eclipse, nang;
+  double angles[16];
+  /* device */
+  tb_ctx *ctx;
+  int have_grid_file, initialised;
+  double *out;
+} th_state;
+
+/* th_config.c */
+void th_defaults(th_hints *h);
+int  th_parse_args(th_hints *h, int argc, char **argv);
+/* th_inputs.c */
+void th_die(const char *fmt, ...);
+int  th_read_atmosphere(th_state *s);
+int  th_read_tli(th_state *s);
+int  th_read_cs(th_state *s);
+/* th_setup.c */
+void th_spline_init(double *z, const double *x, const double *y, long n);
+double th_splinterp_pt(const double *z, long n, const double *x, const double *y, double xout);
+int  th_make_wn(th_state *s);
+int  th_densities(th_state *s);
+int  th_radpress(th_state *s);
+int  th_make_rad(th_state *s);
+int  th_opacity(th_state *s);
+/* th_api.c: the reference's library interface */
+void transit_init(int argc, char **argv);
+int  get_no_samples(void);
+void get_waveno_arr(double *waveno_arr, int waveno);
+void set_radius(double refradius);
+void set_cloudtop(double cloudtop);
+void set_scattering(int flag, double scattering);
+void run_transit(double *re_input, int transint, double *transit_out, int transit_out_size);
+void do_transit(double *transit_out);
+void free_memory(void);
+void th_write_spectrum(void);
+#endif

@@ -1,0 +1,243 @@
+/* th_setup.c -- host-side set-up around the device path:
+ *   makewnsample / makesample1     transit/src/makesample.c:27-120,308-400
+ *   checkaddmm, stateeqnford       readatm.c:122-159, transit.h:58-69
+ *   radpress                       readatm.c:787-865
+ *   makeradsample (raddelt = -1)   makesample.c:408-549 (natural splines, spline.c:12-48,131-206)
+ *   opacity() driver + file I/O    opacity.c:11-215,281-503
+ */
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#include "th_internal.h"
+
+/* ---- natural cubic spline, pu/src/spline.c:12-48 (tri + spline_init) and :131-183 */
+void th_spline_init(double *z, const double *x, const double *y, long n) {
+  double *u = (double *)calloc(n, sizeof(double)), *v = (double *)calloc(n, sizeof(double));
+  for (long i = 1; i < n - 1; i++) {
+    const double hi = x[i + 1] - x[i], hm = x[i] - x[i - 1];
+    const double bi = (y[i + 1] - y[i]) / hi, bm = (y[i] - y[i - 1]) / hm;
+    if (i == 1) { u[i] = 2 * (hi + hm); v[i] = 6 * (bi - bm); }
+    else { u[i] = 2 * (hi + hm) - hm * hm / u[i - 1]; v[i] = 6 * (bi - bm) - v[i - 1] * hm / u[i - 1]; }
+  }
+  z[0] = z[n - 1] = 0;
+  for (long i = n - 2; i > 0; i--) z[i] = (v[i] - (x[i + 1] - x[i]) * z[i + 1]) / u[i];
+  free(u); free(v);
+}
+
+static long binsearchapprox(const double *a, double v, long lo, long hi) {   /* iomisc.c:1088-1108 */
+  while (hi - lo > 1) {
+    const long mid = (hi + lo) / 2;
+    if (a[mid] > v) hi = mid; else lo = mid;
+  }
+  if (hi - lo == 1) return fabs(a[hi] - v) < fabs(a[lo] - v) ? hi : lo;
+  return lo;
+}
+
+double th_splinterp_pt(const double *z, long n, const double *x, const double *y, double xout) {
+  long idx = binsearchapprox(x, xout, 0, n - 1);
+  if (idx == n - 1 || xout < x[idx]) idx--;
+  if (idx < 0) idx = 0;
+  const double h = x[idx + 1] - x[idx], dy = y[idx + 1] - y[idx];
+  if (x[idx] == xout) return y[idx];
+  if (h > 0) {
+    const double dx = xout - x[idx];
+    const double a = (z[idx + 1] - z[idx]) / (6 * h), b = 0.5 * z[idx];
+    const double c = dy / h - h / 6 * (z[idx + 1] + 2 * z[idx]);
+    return y[idx] + dx * (c + dx * (b + dx * a));
+  }
+  return 0;
+}
+
+static void splinterp(long n, const double *x, const double *y, long nout, const double *xout, double *yout) {
+  if (n < 2) { for (long i = 0; i < nout; i++) yout[i] = y[0]; return; }
+  double *z = (double *)calloc(n, sizeof(double));
+  th_spline_init(z, x, y, n);
+  for (long i = 0; i < nout; i++) yout[i] = th_splinterp_pt(z, n, x, y, xout[i]);
+  free(z);
+}
+
+/* ---- wavenumber sampling */
+int th_make_wn(th_state *s) {
+  const th_hints *h = &s->h;
+  double wi = 0, wf = 0;
+  if (h->wn_i > 0) {
+    if (h->wn_fct <= 0) th_die("User specified wavenumber factor is negative (%g).\n", h->wn_fct);
+    wi = h->wn_i * h->wn_fct;
+  } else if (h->wl_f > 0) {
+    if (h->wl_fct <= 0) th_die("User specified wavelength factor is negative (%g).\n", h->wl_fct);
+    wi = 1.0 / (h->wl_f * h->wl_fct);
+  } else
+    th_die("Initial wavenumber (nor final wavelength) were correctly provided by the user.\n");
+  if (h->wn_f > 0) {
+    if (h->wn_fct < 0) th_die("User specified wavenumber factor is negative (%g).\n", h->wn_fct);
+    wf = h->wn_f * h->wn_fct;
+  } else if (h->wl_i > 0) {
+    if (h->wl_fct < 0) th_die("User specified wavelength factor is negative (%g).\n", h->wl_fct);
+    wf = 1.0 / (h->wl_i * h->wl_fct);
+  } else
+    th_die("Final wavenumber (nor initial wavelength) were correctly provided by the user.\n");
+  if (h->wn_d <= 0) th_die("Incorrect wavenumber spacing (%g), it must be positive.\n", h->wn_d);
+  if (h->wn_o <= 0) th_die("makesample() :: Invalid oversampling (%d).\n", h->wn_o);
+  if (wf < wi) th_die("makewnsample() :: final wavenumber (%g) is smaller than the initial one (%g).\n", wf, wi);
+  s->wn_i = wi; s->wn_f = wf; s->wn_d = h->wn_d; s->wn_o = h->wn_o;
+  s->nwn = tb_grid_count(wi, wf, h->wn_d, 1);
+  s->onwn = tb_grid_count(wi, wf, h->wn_d, h->wn_o);
+  if (s->nwn < 2) th_die("The wavenumber sampling has less than 2 points.\n");
+  return 0;
+}
+
+/* ---- mean molecular mass and densities for every layer of the atmosphere file */
+int th_densities(th_state *s) {
+  const int n = s->nlayer, nmol = s->nmol;
+  for (int r = 0; r < n; r++) {
+    double mm = 0, sumq = 0;
+    for (int i = 0; i < nmol; i++) {
+      const double q = s->q[(size_t)i * n + r];
+      mm += s->bymass ? q / s->molmass[i] : q * s->molmass[i];
+      sumq += q;
+    }
+    if (s->bymass) mm = 1.0 / mm;
+    if (sumq > 1.001) th_die("Sum of abundances of isotopes adds up to more than 1: %g\n", sumq);
+    if (fabs(sumq - 1.0) > s->h.allowq && s->h.verb > 1)
+      fprintf(stderr, "In radius %g (%i: %g in file), abundances don't add up to 1: %.9g\n", s->rad[r], r,
+              s->rad[r] - s->zerorad, sumq);
+    s->mm[r] = mm;
+    const double p = s->p[r] * s->p_fct, t = s->t[r] * s->t_fct;
+    for (int i = 0; i < nmol; i++) {
+      const double rho = TH_AMU * s->q[(size_t)i * n + r] * p / TH_KB / t;
+      s->d[(size_t)i * n + r] = s->bymass ? rho * mm : rho * s->molmass[i];
+    }
+  }
+  return 0;
+}
+
+/* ---- hydrostatic radii from the reference level (p0, r0, gsurf) */
+int th_radpress(th_state *s) {
+  const int n = s->nlayer;
+  const double g0 = s->h.gsurf, p0 = s->h.p0, r0 = s->h.r0, rfct = s->rad_fct;
+  const double *temp = s->t, *mu = s->mm, *pr = s->p;
+  double *radius = s->rad;
+  if (p0 == 0 || r0 == 0 || g0 == 0)
+    th_die("Surface gravity (%g cm s-2), reference pressure (%g) or reference radius (%g) were not defined.\n", g0, p0, r0);
+  double minimum = 1e37, temp0, mu0, g;
+  int i0 = -1;
+  for (int i = 0; i < n; i++)
+    if (fabs(pr[i] - p0) < minimum) { i0 = i; minimum = fabs(pr[i] - p0); }
+  if ((pr[i0] > p0 && i0 + 1 >= n) || (pr[i0] <= p0 && i0 - 1 < 0))
+    th_die("The reference pressure (%g) lies outside the pressure range of the atmosphere file.\n", p0);
+  const double kb_amu = TH_KB / TH_AMU;
+  if (pr[i0] > p0) {
+    temp0 = temp[i0] + ((temp[i0 + 1] - temp[i0]) / log(pr[i0 + 1] / pr[i0])) * log(p0 / pr[i0]);
+    mu0 = mu[i0] + ((mu[i0 + 1] - mu[i0]) / log(pr[i0 + 1] / pr[i0])) * log(p0 / pr[i0]);
+    radius[i0] = r0 + 0.5 * (temp[i0] / mu[i0] + temp0 / mu0) * (kb_amu * log(p0 / pr[i0]) / g0) / rfct;
+  } else {
+    temp0 = temp[i0] + ((temp[i0 - 1] - temp[i0]) / log(pr[i0 - 1] / pr[i0])) * log(p0 / pr[i0]);
+    mu0 = mu[i0] + ((mu[i0 - 1] - mu[i0]) / log(pr[i0 - 1] / pr[i0])) * log(p0 / pr[i0]);
+    radius[i0] = r0 - 0.5 * (temp[i0] / mu[i0] + temp0 / mu0) * (kb_amu * log(pr[i0] / p0) / g0) / rfct;
+  }
+  g = g0 * pow(r0 / radius[i0], 2);
+  for (int i = i0 - 1; i >= 0; i--) {
+    radius[i] = radius[i + 1] - 0.5 * (temp[i] / mu[i] + temp[i + 1] / mu[i + 1]) * (kb_amu * log(pr[i] / pr[i + 1]) / g) / rfct;
+    g = g * pow(radius[i + 1] / radius[i], 2);
+  }
+  g = g0 * pow(r0 / radius[i0], 2);
+  for (int i = i0 + 1; i < n; i++) {
+    radius[i] = radius[i - 1] + 0.5 * (temp[i] / mu[i] + temp[i - 1] / mu[i - 1]) * (kb_amu * log(pr[i - 1] / pr[i]) / g) / rfct;
+    g = g * pow(radius[i - 1] / radius[i], 2);
+  }
+  return 0;
+}
+
+/* ---- makeradsample with raddelt = -1: the atmosphere file's own layers; the partition
+ * function of every isotope is splined in temperature at the layer temperatures, and the
+ * sampled atmosphere goes to the device. */
+int th_make_rad(th_state *s) {
+  if (s->h.rad_d != -1) th_die("raddelt %g: only the atmosphere file's own layers (raddelt -1, the default) are supported.\n", s->h.rad_d);
+  const int n = s->nlayer, niso = s->niso;
+  for (int i = 0; i < n; i++) {
+    if (s->t[i] < s->tli_tmin) th_die("The layer %d in the atmospheric model has a lower temperature (%.1f K) than the lowest allowed TLI temperature (%.1f K).\n", i, s->t[i], s->tli_tmin);
+    if (s->t[i] > s->tli_tmax) th_die("The layer %d in the atmospheric model has a higher temperature (%.1f K) than the highest allowed TLI temperature (%.1f K).\n", i, s->t[i], s->tli_tmax);
+  }
+  free(s->Zlayer);
+  s->Zlayer = (double *)malloc((size_t)(niso ? niso : 1) * n * sizeof(double));
+  for (int i = 0; i < niso; i++) {
+    const th_db *db = s->db + s->isodb[i];
+    splinterp(db->nT, db->T, s->isoZ + s->isoZoff[i], n, s->t, s->Zlayer + (size_t)i * n);   /* makesample.c:534-544 */
+  }
+  if (tb_set_atmosphere(s->ctx, n, s->rad, s->rad_fct, s->p, s->p_fct, s->t, s->t_fct, s->d, niso ? s->Zlayer : NULL))
+    th_die("%s\n", tb_last_error());
+  return 0;
+}
+
+/* ---- opacity(): Voigt table, and the grid: read it, or build + write it, or none */
+static int file_exists(const char *p) {
+  FILE *f = p ? fopen(p, "rb") : NULL;
+  if (!f) return 0;
+  fclose(f);
+  return 1;
+}
+
+int th_opacity(th_state *s) {
+  const th_hints *h = &s->h;
+  s->have_grid_file = 0;
+  if (h->f_opa && file_exists(h->f_opa)) {                       /* readopacity, opacity.c:432-503 */
+    FILE *fp = fopen(h->f_opa, "rb");
+    long dims[4];                                                /* Nmol, Ntemp, Nlayer, Nwave */
+    if (fread(dims, sizeof(long), 4, fp) != 4) th_die("Opacity file '%s' is truncated.\n", h->f_opa);
+    const long Nmol = dims[0], Nt = dims[1], Nl = dims[2], Nw = dims[3];
+    if (Nw != s->nwn || Nl != s->nlayer)
+      th_die("Opacity file '%s' holds %ld layers x %ld wavenumbers; the run needs %d x %lld.\n", h->f_opa, Nl, Nw,
+             s->nlayer, (long long)s->nwn);
+    int *molID = (int *)malloc(Nmol * sizeof(int));
+    double *temp = (double *)malloc(Nt * sizeof(double)), *press = (double *)malloc(Nl * sizeof(double));
+    double *wns = (double *)malloc(Nw * sizeof(double));
+    const size_t ng = (size_t)Nl * Nt * Nmol * Nw;
+    double *grid = (double *)malloc(ng * sizeof(double));
+    if (!grid) th_die("Not enough host memory for the opacity grid (%zu bytes).\n", ng * sizeof(double));
+    if (fread(molID, sizeof(int), Nmol, fp) != (size_t)Nmol || fread(temp, 8, Nt, fp) != (size_t)Nt ||
+        fread(press, 8, Nl, fp) != (size_t)Nl || fread(wns, 8, Nw, fp) != (size_t)Nw || fread(grid, 8, ng, fp) != ng)
+      th_die("Opacity file '%s' is truncated.\n", h->f_opa);
+    fclose(fp);
+    if (tb_opacity_load(s->ctx, Nmol, Nt, Nl, Nw, molID, temp, press, grid)) th_die("%s\n", tb_last_error());
+    free(molID); free(temp); free(press); free(wns); free(grid);
+    s->have_grid_file = 1;
+    return 0;
+  }
+  /* line-by-line: line index + Voigt table (calcprofiles, opacity.c:218-277) */
+  if (tb_upload_lines(s->ctx, s->wl, s->elow, s->gf, s->isoid, s->nlines, 1e-4, 1.0)) th_die("%s\n", tb_last_error());
+  if (tb_build_profiles(s->ctx, h->nDop, h->nLor, h->dmin, h->dmax, h->lmin, h->lmax, h->nwidth)) th_die("%s\n", tb_last_error());
+  if (!h->f_opa) return 0;
+  /* calcopacity (opacity.c:281-427): temperature grid, Z(T) per isotope, grid, file */
+  const long Nt = (long)tb_grid_count(h->tlow, h->thigh, h->tempdelt, 1);   /* maketempsample, makesample.c:614-636 */
+  if (Nt < 2) th_die("The opacity temperature grid needs at least 2 samples (tlow %g, thigh %g, tempdelt %g).\n", h->tlow, h->thigh, h->tempdelt);
+  const int n = s->nlayer, niso = s->niso, nmol = s->nmol;
+  double *temp = (double *)malloc(Nt * sizeof(double)), *ziso = (double *)malloc((size_t)(niso ? niso : 1) * Nt * sizeof(double));
+  for (long t = 0; t < Nt; t++) temp[t] = h->tlow + t * h->tempdelt;
+  if (temp[0] < s->tli_tmin || temp[Nt - 1] > s->tli_tmax)
+    th_die("The opacity temperature grid [%.1f, %.1f] K exceeds the TLI partition-function range [%.1f, %.1f] K.\n",
+           temp[0], temp[Nt - 1], s->tli_tmin, s->tli_tmax);
+  for (int i = 0; i < niso; i++) {
+    const th_db *db = s->db + s->isodb[i];
+    splinterp(db->nT, db->T, s->isoZ + s->isoZoff[i], Nt, temp, ziso + (size_t)i * Nt);
+  }
+  int molID[256], nrows = 0;
+  if (tb_get_line_molIDs(s->ctx, molID, &nrows)) th_die("%s\n", tb_last_error());
+  const size_t ng = (size_t)n * Nt * nrows * s->nwn;
+  double *grid = (double *)malloc(ng * sizeof(double));
+  if (!grid) th_die("Not enough host memory for the opacity grid (%zu bytes).\n", ng * sizeof(double));
+  if (tb_opacity_build(s->ctx, (int)Nt, temp, ziso, s->q, s->mm, s->bymass, h->ethresh, grid)) th_die("%s\n", tb_last_error());
+  FILE *fp = fopen(h->f_opa, "wb");
+  if (!fp) th_die("Opacity filename '%s' cannot be opened for writing.\n", h->f_opa);
+  long dims[4] = {nrows, Nt, n, (long)s->nwn};
+  fwrite(dims, sizeof(long), 4, fp);
+  fwrite(molID, sizeof(int), nrows, fp);
+  fwrite(temp, 8, Nt, fp);
+  for (int r = 0; r < n; r++) { const double pr = s->p[r] * s->p_fct; fwrite(&pr, 8, 1, fp); }
+  for (int64_t w = 0; w < s->nwn; w++) { const double wn = s->wn_i + (double)w * s->wn_d; fwrite(&wn, 8, 1, fp); }
+  fwrite(grid, 8, ng, fp);
+  fclose(fp);
+  free(temp); free(ziso); free(grid);
+  (void)nmol;
+  s->have_grid_file = 1;
+  return 0;
+}
