@@ -9,8 +9,9 @@
 #include "th_internal.h"
 
 static th_state S;
+int th_dry = 0;
 
-#define CK(call) do { if ((call) != TB_OK) th_die("%s\n", tb_last_error()); } while (0)
+#define CK(call) do { if (TH_DEV(call) != TB_OK) th_die("%s\n", tb_last_error()); } while (0)
 
 static void apply_cloud_scattering(void) {
   const th_hints *h = &S.h;
@@ -54,6 +55,7 @@ void transit_init(int argc, char **argv) {
     if (S.nang < 1) th_die("raygrid '%s' holds no angle.\n", h->raygrid);
   }
   int dev = 0;
+  th_dry = getenv("TRANSIT_B200_DRYRUN") != NULL;
   if (getenv("TRANSIT_B200_DEVICE")) dev = atoi(getenv("TRANSIT_B200_DEVICE"));
   CK(tb_create(dev, &S.ctx));
   th_make_wn(&S);                                          /* makewnsample */
@@ -94,6 +96,21 @@ void do_transit(double *transit_out) {
   if (!S.initialised) { printf("Transit init not run, please initialize transit.\n"); return; }
   if (S.h.opabreak) return;                                /* justOpacity */
   const th_hints *h = &S.h;
+  if (th_dry) {                                            /* host-logic tap: the sampled state as doubles */
+    FILE *f = fopen(getenv("TRANSIT_B200_DRYRUN"), "wb");
+    if (!f) th_die("cannot write the dry-run dump\n");
+    const double hdr[8] = {(double)S.nlayer, (double)S.nmol, (double)S.niso, (double)S.nwn, (double)S.onwn,
+                           (double)S.nlines, S.wn_i, S.wn_d};
+    fwrite(hdr, 8, 8, f);
+    fwrite(S.rad, 8, S.nlayer, f); fwrite(S.p, 8, S.nlayer, f); fwrite(S.t, 8, S.nlayer, f);
+    fwrite(S.mm, 8, S.nlayer, f); fwrite(S.d, 8, (size_t)S.nmol * S.nlayer, f);
+    fwrite(S.Zlayer, 8, (size_t)S.niso * S.nlayer, f);
+    fwrite(S.molmass, 8, S.nmol, f); fwrite(S.molradius, 8, S.nmol, f);
+    fwrite(S.isomass, 8, S.niso, f); fwrite(S.isoratio, 8, S.niso, f);
+    if (S.nlines) { fwrite(S.wl, 8, S.nlines, f); fwrite(S.elow, 8, S.nlines, f); fwrite(S.gf, 8, S.nlines, f); }
+    fclose(f);
+    return;
+  }
   CK(tb_spectrum(S.ctx, S.eclipse ? TB_GEOM_ECLIPSE : TB_GEOM_TRANSIT, h->toomuch, h->ethresh,
                  h->starrad * TH_SUNRADIUS, h->transparent, S.eclipse ? S.angles : NULL, S.nang, S.out));
   if (transit_out) memcpy(transit_out, S.out, S.nwn * sizeof(double));

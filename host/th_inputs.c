@@ -311,7 +311,7 @@ int th_read_tli(th_state *s) {
 /* ------------------------------------------------------------------ CS / CIA files */
 int th_read_cs(th_state *s) {
   s->ncs = 0;
-  if (tb_cia_clear(s->ctx)) th_die("%s\n", tb_last_error());
+  if (TH_DEV(tb_cia_clear(s->ctx))) th_die("%s\n", tb_last_error());
   if (!s->h.csfiles || !*s->h.csfiles) return 0;
   char *list = strdup(s->h.csfiles);
   for (char *file = strtok(list, ","); file; file = strtok(NULL, ",")) {
@@ -377,7 +377,7 @@ int th_read_cs(th_state *s) {
     if (wn[0] > w0 || wn[n - 1] < w1)
       th_die("Wavenumber range [%.2f, %.2f] of CS file '%s' does not cover Transit's range [%.2f, %.2f].\n",
              wn[0], wn[n - 1], file, w0, w1);
-    if (tb_cia_add_table(s->ctx, wn, n, temps, nt, a, mol, nspec)) th_die("%s\n", tb_last_error());
+    if (TH_DEV(tb_cia_add_table(s->ctx, wn, n, temps, nt, a, mol, nspec))) th_die("%s\n", tb_last_error());
     free(wn); free(a);
     s->ncs++;
   }

@@ -84,6 +84,11 @@ typedef struct {
   double *out;
 } th_state;
 
+/* Host-logic test hook: with TRANSIT_B200_DRYRUN=<file> no device call is made (th_dry != 0) and
+ * do_transit writes the sampled atmosphere to <file> instead of computing a spectrum.      */
+extern int th_dry;
+#define TH_DEV(call) (th_dry ? 0 : (call))
+
 /* th_config.c */
 void th_defaults(th_hints *h);
 int  th_parse_args(th_hints *h, int argc, char **argv);

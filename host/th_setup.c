@@ -164,7 +164,7 @@ int th_make_rad(th_state *s) {
     const th_db *db = s->db + s->isodb[i];
     splinterp(db->nT, db->T, s->isoZ + s->isoZoff[i], n, s->t, s->Zlayer + (size_t)i * n);   /* makesample.c:534-544 */
   }
-  if (tb_set_atmosphere(s->ctx, n, s->rad, s->rad_fct, s->p, s->p_fct, s->t, s->t_fct, s->d, niso ? s->Zlayer : NULL))
+  if (TH_DEV(tb_set_atmosphere(s->ctx, n, s->rad, s->rad_fct, s->p, s->p_fct, s->t, s->t_fct, s->d, niso ? s->Zlayer : NULL)))
     th_die("%s\n", tb_last_error());
   return 0;
 }
@@ -198,14 +198,14 @@ int th_opacity(th_state *s) {
         fread(press, 8, Nl, fp) != (size_t)Nl || fread(wns, 8, Nw, fp) != (size_t)Nw || fread(grid, 8, ng, fp) != ng)
       th_die("Opacity file '%s' is truncated.\n", h->f_opa);
     fclose(fp);
-    if (tb_opacity_load(s->ctx, Nmol, Nt, Nl, Nw, molID, temp, press, grid)) th_die("%s\n", tb_last_error());
+    if (TH_DEV(tb_opacity_load(s->ctx, Nmol, Nt, Nl, Nw, molID, temp, press, grid))) th_die("%s\n", tb_last_error());
     free(molID); free(temp); free(press); free(wns); free(grid);
     s->have_grid_file = 1;
     return 0;
   }
   /* line-by-line: line index + Voigt table (calcprofiles, opacity.c:218-277) */
-  if (tb_upload_lines(s->ctx, s->wl, s->elow, s->gf, s->isoid, s->nlines, 1e-4, 1.0)) th_die("%s\n", tb_last_error());
-  if (tb_build_profiles(s->ctx, h->nDop, h->nLor, h->dmin, h->dmax, h->lmin, h->lmax, h->nwidth)) th_die("%s\n", tb_last_error());
+  if (TH_DEV(tb_upload_lines(s->ctx, s->wl, s->elow, s->gf, s->isoid, s->nlines, 1e-4, 1.0))) th_die("%s\n", tb_last_error());
+  if (TH_DEV(tb_build_profiles(s->ctx, h->nDop, h->nLor, h->dmin, h->dmax, h->lmin, h->lmax, h->nwidth))) th_die("%s\n", tb_last_error());
   if (!h->f_opa) return 0;
   /* calcopacity (opacity.c:281-427): temperature grid, Z(T) per isotope, grid, file */
   const long Nt = (long)tb_grid_count(h->tlow, h->thigh, h->tempdelt, 1);   /* maketempsample, makesample.c:614-636 */
@@ -225,7 +225,7 @@ int th_opacity(th_state *s) {
   const size_t ng = (size_t)n * Nt * nrows * s->nwn;
   double *grid = (double *)malloc(ng * sizeof(double));
   if (!grid) th_die("Not enough host memory for the opacity grid (%zu bytes).\n", ng * sizeof(double));
-  if (tb_opacity_build(s->ctx, (int)Nt, temp, ziso, s->q, s->mm, s->bymass, h->ethresh, grid)) th_die("%s\n", tb_last_error());
+  if (TH_DEV(tb_opacity_build(s->ctx, (int)Nt, temp, ziso, s->q, s->mm, s->bymass, h->ethresh, grid))) th_die("%s\n", tb_last_error());
   FILE *fp = fopen(h->f_opa, "wb");
   if (!fp) th_die("Opacity filename '%s' cannot be opened for writing.\n", h->f_opa);
   long dims[4] = {nrows, Nt, n, (long)s->nwn};

@@ -21,6 +21,7 @@
 extern struct transit transit;
 void transit_init(int argc, char **argv);
 void run_transit(double *re_input, int transint, double *transit_out, int n);
+int  reloadatm(struct transit *tr, double *input);
 int  computemolext(struct transit *tr, PREC_RES **kiso, PREC_ATM temp,
                    PREC_ATM *density, double *Z, int permol);
 
@@ -246,12 +247,13 @@ static void spectrum_with_taps(struct transit *tr, const char *pfx, int full_ext
 }
 
 int main(int argc, char **argv){
-  int full_ext = 0, a = 2;
+  int full_ext = 0, a = 2, rerun_taps = 0;
   const char *rerun = NULL;
   if(argc < 4){ fprintf(stderr, "usage: ref_dump out.bin [--full-ext] [--rerun f] -- transit-args\n"); return 2; }
   for(; a < argc && strcmp(argv[a], "--"); a++){
     if(!strcmp(argv[a], "--full-ext")) full_ext = 1;
     else if(!strcmp(argv[a], "--rerun")) rerun = argv[++a];
+    else if(!strcmp(argv[a], "--rerun-taps")) rerun_taps = 1;   /* taps of the re-run too (prefix rr_) */
   }
   if(a >= argc) return 2;
   argv[a] = argv[0];                     /* transit's argv[0] */
@@ -277,7 +279,13 @@ int main(int argc, char **argv){
     freemem_extinction(transit.ds.ex, &transit.pi);
     freemem_tau(transit.ds.tau, &transit.pi);
     freemem_outputray(transit.ds.out, &transit.pi);
-    run_transit(in, (int)nin, o, (int)nwn);
+    if(rerun_taps){            /* run_transit = reloadatm + do_transit (transit.c:118-122) */
+      if(reloadatm(&transit, in) < 0) exit(3);
+      spectrum_with_taps(&transit, "rr_", full_ext);
+      memcpy(o, transit.ds.out->o, nwn*sizeof(double));
+    }
+    else
+      run_transit(in, (int)nin, o, (int)nwn);
     rec1("rerun_in", 0, nin, in);
     rec1("rerun_out", 0, nwn, o);
     rec1("rerun_atm_t", 0, transit.rads.n, transit.atm.t);

@@ -609,7 +609,11 @@ int to_tau(int eclipse, const double *e, const double *e_cs, const double *wn,
           }
         }while(h[ri]*hfct < rad[lastr]*rfct);
       }
-      double b = h[ri]*hfct/rfct;
+      /* tau.c:274 as the reference is BUILT: -ffast-math hoists 1/rfct out of the loop (objdump of
+         tau(): movsd 1.0; divsd rfct before the wavenumber loop), so b = (h*hfct)*(1/rfct).  With
+         IEEE division some impact parameters land one ulp below their own layer radius and the ray
+         picks the layer underneath: a 20% change in tau the reference binary never shows. */
+      double b = h[ri]*hfct*(1.0/rfct);
       tw[ri] = rfct*(eclipse ? to_eclipsetau(b, rad, er, nrad)
                              : to_totaltau1(b, rad, 1.0, er, nrad));
       if(tw[ri] > toomuch){ last[wi] = ri; break; }

@@ -347,7 +347,11 @@ __global__ void k_ray_geometry(int eclipse, const double *__restrict__ rad, int 
                                int32_t *__restrict__ err) {
   int ri = blockIdx.x * blockDim.x + threadIdx.x;
   if (ri >= nh) return;
-  const double b = __ddiv_rn(__dmul_rn(h[ri], hfct), rfct);   // tau.c:274
+  // tau.c:274 as the reference is BUILT: gcc -ffast-math hoists 1/rfct out of the loop (objdump of
+  // tau(): movsd 1.0; divsd rfct ahead of the wavenumber loop), so b = (h*hfct)*(1/rfct).  With an
+  // IEEE division some impact parameters land one ulp below their own layer radius, the ray then
+  // starts one layer lower and tau changes by ~20%: something the reference binary never shows.
+  const double b = __dmul_rn(__dmul_rn(h[ri], hfct), __drcp_rn(rfct));
   int rs, mode = 1;
   if (eclipse) {
     rs = tb_binsearchapprox(rad, b, 0, nrad - 1);             // eclipse.c:39
