@@ -287,7 +287,7 @@ def run_ours(args):
     init_s = time.perf_counter() - t0
     ctx = tr.ctx
     out = np.zeros(prob.nwn)
-    gathered = torch.zeros(world, prob.nwn, dtype=torch.float64, device="cuda") if world > 1 else None
+    gathered = [None]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
 
     def barrier():
@@ -298,8 +298,8 @@ def run_ours(args):
 
     def step():
         tr.do_transit(out)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered.view(-1), tr.device_spectrum_tensor())
+        if world > 1:        # natm = world: one atmosphere per rank per step
+            gathered[0] = sharding.gather_spectra(tr.device_spectrum_tensor().view(1, -1), world, rank, world)
 
     for _ in range(args.warmup):
         step()
@@ -331,7 +331,7 @@ def run_ours(args):
     clocks = sampler.stop()
     assert np.array_equal(out, ref_out), "spectrum changed between steps: the path is not deterministic"
     if world > 1:
-        assert np.array_equal(gathered[rank].cpu().numpy(), out), "gathered slice differs from the local spectrum"
+        assert np.array_equal(gathered[0][rank].cpu().numpy(), out), "gathered slice differs from the local spectrum"
 
     # ---- end to end through the host mirror with HOST buffers (H2D atmosphere + D2H spectrum per step)
     barrier()

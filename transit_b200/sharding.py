@@ -1,9 +1,12 @@
-"""Wavenumber-band sharding of one spectrum over the GPUs of a box.
+"""Multi-GPU plumbing: one process per GPU (torchrun), torch.distributed for the exchange.
 
-One process per GPU.  Every rank holds the whole (layer-independent) line index but owns one
-contiguous band of the coarse wavenumber grid; the only exchanges are the per-layer strength
-maxima / carried Doppler indices (exact integer-ordered maxima, so results are bit-identical to
-the single-GPU run) and the final gather of the spectrum slices.
+The path shards over *atmospheres* (BART's use of the library: many
+T-P/abundance profiles through one static problem).  Every rank holds the static problem (line
+index, Voigt table, CIA tables or opacity grid) and computes the spectra of its own atmospheres;
+there is no collective on the data path, only one all-gather of the finished spectra.  The kernels,
+the copies and the gather share one CUDA stream (tb_set_stream / tb_device_spectrum).
+
+`atmosphere_shard` and `gather_spectra` are backend-agnostic (NCCL on GPUs, gloo in the CPU tests).
 """
 from __future__ import annotations
 
@@ -12,7 +15,37 @@ import numpy as np
 from . import api
 
 
+def atmosphere_shard(natm: int, rank: int, world: int):
+    """Contiguous, balanced block of atmosphere indices owned by `rank` (the first natm % world
+    ranks get one more)."""
+    base, extra = divmod(natm, world)
+    lo = rank * base + min(rank, extra)
+    return range(lo, lo + base + (1 if rank < extra else 0))
+
+
+def gather_spectra(local, natm: int, rank: int, world: int, group=None):
+    """All-gather per-rank spectra [n_local, nwn] into [natm, nwn] in atmosphere order on every rank.
+    Blocks may differ by one row between ranks: they are padded to the largest for the collective."""
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return local
+    nmax = -(-natm // world)
+    nwn = local.shape[1]
+    buf = torch.zeros(nmax, nwn, dtype=local.dtype, device=local.device)
+    buf[:local.shape[0]] = local
+    out = torch.empty(world * nmax, nwn, dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, buf, group=group)
+    rows = []
+    for r in range(world):
+        n = len(atmosphere_shard(natm, r, world))
+        rows.append(out[r * nmax:r * nmax + n])
+    return torch.cat(rows, 0)
+
+
 class ShardedTransit(api.Transit):
+    """api.Transit plus what a rank of a multi-GPU run needs."""
+
     def __init__(self, device=0, rank=0, world=1):
         super().__init__(device)
         self.rank, self.world = rank, world
