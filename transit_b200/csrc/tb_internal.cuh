@@ -80,11 +80,20 @@ struct DevBuf {
 // stored "polyphase": sample idx of the reference layout lives at off + (idx % o)*nk + idx/o,
 // so the samples one line contributes to consecutive coarse bins (idx, idx+o, idx+2o, ...)
 // are consecutive floats (one coalesced 128-byte read per warp instead of 32 sectors).
+#define TB_PROF_PAD 128   // doubles of zero padding either side of the polyphase table
 struct ProfEntry {
   int32_t off;      // offset of the profile in the polyphase float table
   int32_t psize;    // half size in fine samples
   int32_t nk;       // coarse samples per phase: 2*psize/o + 1
   int32_t pad;
+};
+
+// What k_strength leaves per (state, group) for k_accumulate: one 16-byte record, so that a
+// visit is one 128-bit read (one sector per two records) instead of three scattered ones.
+struct __align__(16) LineRec {
+  double k;        // strength (0 for skipped groups)
+  int32_t iown;    // fine bin of the group
+  uint32_t pid;    // profile cell, PID_SKIP, PID_NOREACH + cell, or PID_FB + isotope
 };
 
 struct CiaTable {
@@ -150,8 +159,12 @@ struct tb_ctx {
   DevBuf<int32_t> g_start, g_iown, g_idwn, g_orig;
   DevBuf<int16_t> g_iso;
   DevBuf<double> g_wavn;       // leader wavenumber, sorted order
+  DevBuf<double> g_a0, g_gf, g_lg;   // leader: -EXPCTE*efct*elow, gf, log(gf) (+inf for co-add groups)
   DevBuf<double> go_wavn;      // leader wavenumber, original group order
   DevBuf<int32_t> binstart;    // [nrows][nwn+1]
+  DevBuf<int32_t> substart;    // [nrows][nsub]: finer start index for the narrow path (tb_lines.cu)
+  int64_t nsub = 0;
+  int nsube = 1;
 
   // ---- Voigt table (a3/a4)
   bool have_prof = false;
@@ -178,10 +191,10 @@ struct tb_ctx {
   // ---- state batch scratch (tb_lines.cu)
   DevBuf<double> s_T, s_dens, s_Z, s_alphal, s_alphad, s_kmax, s_k;
   DevBuf<int32_t> s_ilor, s_idop0, s_lastq, s_fb, s_fbpid, s_wtile, s_reach, s_reachP, s_fbmax;
-  DevBuf<double> s_facz, s_rtemp, s_ral, s_xterm;
-  DevBuf<uint16_t> s_pid;     // [state][group] profile cell, PID_SKIP, or PID_FB + isotope
+  DevBuf<double> s_facz, s_rtemp, s_ral, s_xterm, s_lcz;
+  DevBuf<LineRec> s_rec;      // [state][group]
   DevBuf<uint8_t> s_hasfb;    // [state][tile]
-  DevBuf<unsigned long long> s_nsamp;
+  DevBuf<unsigned long long> s_nsamp, s_nsamp_part;
   DevBuf<double> s_out;
   int last_ns = 0, last_permol = 0;
   bool nsamp_valid = false;

@@ -16,6 +16,9 @@
 //   k_accumulate  -> Voigt-profile gather per output bin, fixed summation order, no atomics
 //                    on floating-point data (extinction.c:486-509)
 #include <cub/cub.cuh>
+#include <stdlib.h>
+
+#define NSUB 8             // sub-cells per coarse bin in the narrow path's start index
 #include "tb_internal.cuh"
 
 
@@ -113,10 +116,16 @@ __global__ void k_group_fill(const int32_t *__restrict__ order, const int32_t *_
                              double *__restrict__ g_wavn, double *__restrict__ m_wavn,
                              double *__restrict__ m_elow, double *__restrict__ m_gf,
                              int16_t *__restrict__ m_iso, uint8_t *__restrict__ m_inr,
-                             int32_t *__restrict__ l_gpos, int32_t *__restrict__ x_line) {
+                             int32_t *__restrict__ l_gpos, int32_t *__restrict__ x_line, double efct,
+                             double *__restrict__ g_a0, double *__restrict__ g_gf, double *__restrict__ g_lg) {
   int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (p >= G) return;
   int32_t g = order[p], L = lead[g], E = next[L], s = gstart[p];
+  g_a0[p] = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), elow[L]);
+  g_gf[p] = gf[L];
+  // log of the leader's gf: lets k_strength bound a lone line's strength without exp();
+  // co-add groups (and anything not a positive finite gf) always take the exact path
+  g_lg[p] = (E - L == 1 && gf[L] > 0) ? log(gf[L]) : (gf[L] == 0 && E - L == 1 ? -INFINITY : INFINITY);
   g_iown[p] = iown[L];
   g_idwn[p] = idwn_orig[g];
   g_orig[p] = g;
@@ -177,6 +186,25 @@ __global__ void k_binstart(const uint64_t *__restrict__ key_sorted, int64_t G, i
     if (key_sorted[mid] < want) lo = mid + 1; else hi = mid;
   }
   binstart[k] = (int32_t)lo;
+}
+
+// substart[row][u] = first sorted group of `row` whose fine bin is >= ceil(u*o/nsube): the narrow
+// path's start index (nsube sub-cells per coarse bin), so that a bin finds the first record of its
+// window with one read instead of a bisection of dependent reads
+__global__ void k_substart(const uint64_t *__restrict__ key_sorted, int64_t G, int nrows, int64_t nsub,
+                           int64_t onwn, int o, int nsube, int32_t *__restrict__ substart) {
+  int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= (int64_t)nrows * nsub) return;
+  const int64_t row = k / nsub, u = k % nsub;
+  int64_t f = (u * o + nsube - 1) / nsube;
+  if (f > onwn) f = onwn;
+  const uint64_t want = (uint64_t)row * (uint64_t)onwn + (uint64_t)f;
+  int64_t lo = 0, hi = G;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (key_sorted[mid] < want) lo = mid + 1; else hi = mid;
+  }
+  substart[k] = (int32_t)lo;
 }
 
 static inline int nblk(int64_t n, int t) { return (int)((n + t - 1) / t); }
@@ -294,13 +322,21 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
   TB_TRY(c->m_iso.ensure(M)); TB_TRY(c->m_inr.ensure(M)); TB_TRY(c->x_line.ensure(M - G + 1));
   TB_TRY(c->g_iown.ensure(G)); TB_TRY(c->g_idwn.ensure(G)); TB_TRY(c->g_orig.ensure(G));
   TB_TRY(c->g_iso.ensure(G)); TB_TRY(c->g_wavn.ensure(G));
+  TB_TRY(c->g_a0.ensure(G)); TB_TRY(c->g_gf.ensure(G)); TB_TRY(c->g_lg.ensure(G));
   k_group_fill<<<nblk(G, T), T, 0, st>>>(ord_s.p, idw.p, c->g_start.p, G, lead.p, nxt.p, d_wavn.p,
                                          d_elow.p, d_gf.p, d_iso.p, c->l_iown.p, c->l_flag.p, c->nwn,
                                          c->g_iown.p, c->g_idwn.p, c->g_orig.p, c->g_iso.p,
                                          c->g_wavn.p, c->m_wavn.p, c->m_elow.p, c->m_gf.p, c->m_iso.p,
-                                         c->m_inr.p, c->l_gpos.p, c->x_line.p);
+                                         c->m_inr.p, c->l_gpos.p, c->x_line.p, efct, c->g_a0.p, c->g_gf.p,
+                                         c->g_lg.p);
   k_binstart<<<nblk(nkeys + 1, T), T, 0, st>>>(key_s.p, G, nkeys, c->nwn, c->onwn, c->o, c->binstart.p);
-  c->launches += 8;
+  c->nsube = c->o < NSUB ? c->o : NSUB;
+  c->nsub = ((c->onwn - 1) * c->nsube) / c->o + 2;
+  TB_REQUIRE(c->onwn * c->nsube < 4000000000LL, TB_ERR_ARG, "fine grid too large for the 32-bit start index");
+  TB_TRY(c->substart.ensure((size_t)c->nrows * c->nsub));
+  k_substart<<<nblk((int64_t)c->nrows * c->nsub, T), T, 0, st>>>(key_s.p, G, c->nrows, c->nsub, c->onwn, c->o,
+                                                               c->nsube, c->substart.p);
+  c->launches += 9;
   {  // strength-ordered copy of the in-range member lines for k_kmax
     DevBuf<double> qk, qk_s;
     DevBuf<int32_t> qi, qi_s;
@@ -336,8 +372,10 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
 
 // ------------------------------------------------------------------ per-state kernels
 
-#define PID_SKIP 0xFFFFu   // group below the strength threshold (extinction.c:467-470)
+#define PID_SKIP 0x7FFFu   // group below the strength threshold (extinction.c:467-470)
 #define PID_FB   0x8000u   // + isotope: "use the isotope's carried Doppler index"
+#define PID_NOREACH 0x4000u   // + cell: evaluated, but the profile covers no grid point (nothing to add)
+#define PID_DEAD(pid) (((pid) & 0xC000u) == 0x4000u)   // PID_SKIP or PID_NOREACH: the line sum passes over it
 #define ACC_TILE 128       // output bins per block of k_accumulate (4 warps x 32 bins)
 #define MAXISO_SH 128      // isotopes handled with shared-memory maxima in k_strength
 
@@ -480,130 +518,198 @@ __global__ void k_extra(int64_t X, int ns, const int32_t *__restrict__ x_line,
       __dmul_rn(__dmul_rn(m_gf[l], tb_exp(a * rT)), (1 - tb_exp(__dmul_rn(-TB_EXPCTE, m_wavn[l]) * rT)));
 }
 
+// log-domain threshold offsets: lcz[s][iso] = log(facz) - log(ethresh*kmax[s][row(iso)]).  A lone
+// line with  a0/T + log(gf) + lcz < -1e-9  has  gf*exp(a0/T)*facz  (an upper bound of its strength:
+// the stimulated-emission factor is <= 1) below the threshold by a relative 1e-9, ten thousand
+// times the rounding noise of either side: it is below extinction.c:467's threshold whatever the
+// last bits of exp() are.  Everything else takes the exact path.
+__global__ void k_logthr(int ns, int niso, int nrows, int permol, double ethresh,
+                         const int *__restrict__ iso_row, const double *__restrict__ facz,
+                         const double *__restrict__ kmax, double *__restrict__ lcz) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= ns * niso) return;
+  const int s = t / niso, iso = t % niso;
+  const double thr = __dmul_rn(ethresh, kmax[s * nrows + (permol ? iso_row[iso] : 0)]);
+  const double f = facz[t];
+  lcz[t] = (thr > 0 && f > 0 && isfinite(thr) && isfinite(f)) ? log(f) - log(thr) : INFINITY;
+}
+
 // extinction.c:439-483 for one (group, state): co-added strength in member order, scaling,
 // threshold, density factor, Doppler-index decision.  Output per (state, group): the strength
-// and a 16-bit profile id.  The carried-index and tile-reach maxima are reduced in shared
-// memory first: a handful of global integer atomics per block instead of one per group.
+// and a 16-bit profile id.  A block owns 256 consecutive groups and SB states:
+//   phase 1  one thread per group: the log-domain bound above for each of the SB states (one FMA,
+//            no exp); pairs that may pass are appended to a shared-memory list;
+//   phase 2  the list is processed densely, one (group, state) pair per thread: both exp(), the
+//            co-added members, threshold, Doppler cell.  More than half of all pairs are below
+//            the threshold and interleaved with the survivors; without the list every warp would
+//            pay the full price for its busiest lane;
+//   phase 3  strengths and ids leave through shared memory: whole sectors, coalesced.
+// The carried-index and tile-reach maxima are reduced in shared memory first: a handful of
+// global integer atomics per block instead of one per group.
+#define STR_NT 4   // consecutive accumulate tiles a block's reach maxima are kept for in shared memory
 template <int SB>
-__global__ void __launch_bounds__(256, 4) k_strength(int64_t G, int ns, int niso, int o, FastDiv fd_tile,
+__global__ void __launch_bounds__(256) k_strength(int64_t G, int ns, int niso, int o, FastDiv fd_tile, FastDiv fd_o,
                            const int32_t *__restrict__ g_start,
                            const int16_t *__restrict__ g_iso, const int32_t *__restrict__ g_orig,
                            const int32_t *__restrict__ g_iown,
-                           const double *__restrict__ g_wavn, const double *__restrict__ m_wavn,
-                           const double *__restrict__ m_elow, const double *__restrict__ m_gf,
+                           const double *__restrict__ g_wavn, const double *__restrict__ g_a0,
+                           const double *__restrict__ g_gf, const double *__restrict__ g_lg,
                            const double *__restrict__ rtemp, const double *__restrict__ facz,
+                           const double *__restrict__ lcz,
                            const double *__restrict__ ral, const double *__restrict__ xterm, int64_t X,
                            float dop_lmin, float dop_rstep,
                            const double *__restrict__ dens, int nmol,
                            const int *__restrict__ iso_imol, const int *__restrict__ iso_row,
                            const double *__restrict__ alphal, const double *__restrict__ alphad,
                            const int32_t *__restrict__ ilor, const double *__restrict__ aDop, int nDop,
-                           const ProfEntry *__restrict__ ptab, int nLor, double efct, double ethresh,
+                           const ProfEntry *__restrict__ ptab, int nLor, double ethresh,
                            int permol, int nrows, const double *__restrict__ kmax,
-                           double *__restrict__ k_out, uint16_t *__restrict__ pid_out,
+                           LineRec *__restrict__ rec_out,
                            int32_t *__restrict__ lastq, int32_t *__restrict__ wtile,
                            uint8_t *__restrict__ hasfb, int ntiles) {
   __shared__ int32_t sh_lastq[SB][MAXISO_SH];
   __shared__ double sh_aDop[256];
+  __shared__ double sh_k[SB][256];
+  __shared__ uint16_t sh_pid[SB][256];
+  __shared__ uint16_t sh_list[SB * 256];
+  __shared__ int32_t sh_wt[SB][STR_NT];
+  __shared__ int32_t sh_fb[SB][STR_NT];
+  __shared__ int sh_cnt;
   const bool use_sh = niso <= MAXISO_SH;
+  const int tid = threadIdx.x;
   if (use_sh)
-    for (int i = threadIdx.x; i < SB * MAXISO_SH; i += blockDim.x) (&sh_lastq[0][0])[i] = -1;
-  for (int i = threadIdx.x; i <= nDop; i += blockDim.x) sh_aDop[i] = aDop[i];   // [nDop] = +inf sentinel
+    for (int i = tid; i < SB * MAXISO_SH; i += blockDim.x) (&sh_lastq[0][0])[i] = -1;
+  for (int i = tid; i <= nDop; i += blockDim.x) sh_aDop[i] = aDop[i];   // [nDop] = +inf sentinel
+  if (tid < SB * STR_NT) { (&sh_wt[0][0])[tid] = -1; (&sh_fb[0][0])[tid] = 0; }
+  if (tid == 0) sh_cnt = 0;
   __syncthreads();
-  int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t pbase = blockIdx.x * (int64_t)blockDim.x;
+  const int64_t p = pbase + tid;
   const int s0 = blockIdx.y * SB;
   const bool act = p < G;
-  int iso = 0, b = 0, e = 0, row = 0, imol = 0, tile = 0, orig = 0;
-  double wlead = 0, a0 = 0, w0 = 0, g0 = 0;
-  if (act) {
-    iso = g_iso[p];
-    b = g_start[p]; e = g_start[p + 1];
-    wlead = g_wavn[p];
-    row = permol ? iso_row[iso] : 0;
-    imol = iso_imol[iso];
-    tile = fd_div(g_iown[p], fd_tile);          // fine bin / (o * ACC_TILE)
-    orig = g_orig[p];
-    a0 = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[b]);
-    w0 = __dmul_rn(-TB_EXPCTE, m_wavn[b]);
-    g0 = m_gf[b];
-  }
-  const unsigned lane = threadIdx.x & 31;
-  const unsigned full = 0xffffffffu;
-  const int t0 = __shfl_sync(full, tile, 0);
-  const bool uni = __all_sync(full, !act || tile == t0);
-#pragma unroll 1
-  for (int k = 0; k < SB; k++) {
-    const int s = s0 + k;
-    if (s >= ns) break;
-    int ps = -1;          // psize of the profile this group will use, when known here
-    bool fbk = false;     // group uses the carried index
-    if (act) {
-      const double rT = rtemp[s];
-      const int si = s * niso + iso;
-      const double fz = facz[si], thr = __dmul_rn(ethresh, kmax[s * nrows + row]);
-      const double ge1 = __dmul_rn(g0, tb_exp(a0 * rT));
-      double kk = 0.0;
-      // a lone line whose strength without the (<= 1) stimulated-emission factor is already
-      // clearly below the threshold is skipped without the second exp()
-      bool below = (e - b == 1) && ge1 * fz < 0.999999 * thr;
-      if (!below) {
-        double acc = __dmul_rn(ge1, (1 - tb_exp(w0 * rT)));
-        for (int l = b + 1; l < e; l++)                        // co-added members (extinction.c:449-462)
-          acc = __dadd_rn(acc, xterm[(size_t)s * X + (l - (int)p - 1)]);
-        kk = __dmul_rn(acc, fz);
-        below = kk < thr;                                      // extinction.c:467-470
+  const unsigned lane = tid & 31;
+  const int tile0 = fd_div(g_iown[pbase], fd_tile);        // pbase < G always
+  // ---- phase 1
+  {
+    double a0 = 0, lg = 0;
+    int iso = 0;
+    if (act) { a0 = g_a0[p]; lg = g_lg[p]; iso = g_iso[p]; }
+#pragma unroll
+    for (int k = 0; k < SB; k++) {
+      const int s = s0 + k;
+      bool alive = false;
+      if (act && s < ns) alive = !(fma(a0, rtemp[s], lg + lcz[s * niso + iso]) < -1e-9);
+      sh_k[k][tid] = 0.0;
+      sh_pid[k][tid] = (uint16_t)PID_SKIP;
+      const unsigned m = __ballot_sync(0xffffffffu, alive);
+      if (m) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&sh_cnt, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (alive) sh_list[base + __popc(m & ((1u << lane) - 1))] = (uint16_t)(tid | (k << 8));
       }
-      const size_t oo = (size_t)s * G + p;
-      unsigned pid = PID_SKIP;
-      if (!below) {
-        if (!permol) kk = __dmul_rn(kk, dens[s * nmol + imol]);
-        const double al = alphal[si], adw = __dmul_rn(alphad[si], wlead);
-        // extinction.c:480-483: alphad*wavn/alphal >= 0.1, decided by the exact quotient whenever
-        // the reciprocal product is within rounding distance of the boundary
-        const double qa = adw * ral[si];
-        const bool refresh = fabs(qa - 1e-1) > 1e-12 ? qa >= 1e-1 : adw / al >= 1e-1;
-        if (refresh) {
-          // binsearchapprox (iomisc.c:1088-1108) on the log-spaced table: start from the
-          // closed-form cell and settle with exact comparisons: lo = last entry <= adw
-          int lo = (int)((__log2f((float)adw) * 0.30102999566f - dop_lmin) * dop_rstep);
-          lo = lo < 0 ? 0 : (lo > nDop - 1 ? nDop - 1 : lo);
-          while (lo > 0 && sh_aDop[lo] > adw) lo--;
-          while (sh_aDop[lo + 1] <= adw) lo++;                    // [nDop] = +inf stops it
-          const int hi = lo + 1;
-          const int id = (fabs(sh_aDop[hi] - adw) < fabs(sh_aDop[lo] - adw)) ? hi : lo;
-          pid = id * nLor + ilor[si];
-          ps = ptab[pid].psize;
-          if (use_sh) atomicMax(&sh_lastq[k][iso], orig);
-          else atomicMax(&lastq[si], orig);
-        } else {
-          pid = PID_FB + iso;
-          fbk = true;
-        }
-      } else kk = 0.0;
-      k_out[oo] = kk;                 // written for skipped groups too: whole sectors, no fill reads
-      pid_out[oo] = (uint16_t)pid;
     }
-    // widest profile per (state, tile of output bins): one atomic per warp when the warp sits
-    // in one tile (the usual case: groups are sorted by fine bin)
-    if (uni) {
-      int m = ps;
-      for (int d = 16; d > 0; d >>= 1) m = max(m, __shfl_xor_sync(full, m, d));
-      const bool anyfb = __any_sync(full, fbk);
-      if (lane == 0) {
-        if (m >= 0) atomicMax(&wtile[s * ntiles + t0], m);
-        if (anyfb) hasfb[s * ntiles + t0] = 1;
+  }
+  __syncthreads();
+  // ---- phase 2
+  const int cnt = sh_cnt;
+  for (int it = tid; it < cnt; it += blockDim.x) {
+    const int item = sh_list[it];
+    const int pl = item & 255, k = item >> 8;
+    const int64_t q = pbase + pl;
+    const int s = s0 + k;
+    const int iso = g_iso[q];
+    const int b = g_start[q], e = g_start[q + 1];
+    const double wlead = g_wavn[q];
+    const double rT = rtemp[s];
+    const int si = s * niso + iso;
+    const double fz = facz[si], thr = __dmul_rn(ethresh, kmax[s * nrows + (permol ? iso_row[iso] : 0)]);
+    const double ge1 = __dmul_rn(g_gf[q], tb_exp(g_a0[q] * rT));
+    double kk = 0.0;
+    // a lone line whose strength without the (<= 1) stimulated-emission factor is already
+    // clearly below the threshold is skipped without the second exp()
+    bool below = (e - b == 1) && ge1 * fz < 0.999999 * thr;
+    if (!below) {
+      double acc = __dmul_rn(ge1, (1 - tb_exp(__dmul_rn(-TB_EXPCTE, wlead) * rT)));
+      for (int l = b + 1; l < e; l++)                        // co-added members (extinction.c:449-462)
+        acc = __dadd_rn(acc, xterm[(size_t)s * X + (l - (int)q - 1)]);
+      kk = __dmul_rn(acc, fz);
+      below = kk < thr;                                      // extinction.c:467-470
+    }
+    if (below) continue;
+    if (!permol) kk = __dmul_rn(kk, dens[s * nmol + iso_imol[iso]]);
+    const double al = alphal[si], adw = __dmul_rn(alphad[si], wlead);
+    // extinction.c:480-483: alphad*wavn/alphal >= 0.1, decided by the exact quotient whenever
+    // the reciprocal product is within rounding distance of the boundary
+    const double qa = adw * ral[si];
+    const bool refresh = fabs(qa - 1e-1) > 1e-12 ? qa >= 1e-1 : adw / al >= 1e-1;
+    const int iown = g_iown[q];
+    const int tile = fd_div(iown, fd_tile) - tile0;           // fine bin / (o * ACC_TILE)
+    const bool tsh = tile >= 0 && tile < STR_NT;
+    unsigned pid;
+    if (refresh) {
+      // binsearchapprox (iomisc.c:1088-1108) on the log-spaced table: start from the
+      // closed-form cell and settle with exact comparisons: lo = last entry <= adw
+      int lo = (int)((__log2f((float)adw) * 0.30102999566f - dop_lmin) * dop_rstep);
+      lo = lo < 0 ? 0 : (lo > nDop - 1 ? nDop - 1 : lo);
+      while (lo > 0 && sh_aDop[lo] > adw) lo--;
+      while (sh_aDop[lo + 1] <= adw) lo++;                    // [nDop] = +inf stops it
+      const int hi = lo + 1;
+      const int id = (fabs(sh_aDop[hi] - adw) < fabs(sh_aDop[lo] - adw)) ? hi : lo;
+      pid = id * nLor + ilor[si];
+      const int ps = ptab[pid].psize;
+      {  // does the profile cover any grid point at all?  |iown - o*nearest| <= psize
+        const int dist = iown - fd_div(iown + (o >> 1), fd_o) * o;
+        if ((dist < 0 ? -dist : dist) > ps) pid |= PID_NOREACH;
       }
-    } else if (act) {
-      if (ps >= 0) atomicMax(&wtile[s * ntiles + tile], ps);
-      if (fbk) hasfb[s * ntiles + tile] = 1;
+      {  // the maxima rarely move after a block's first records: look before the (conflicting) atomic
+        const int og = g_orig[q];
+        if (use_sh) { if (og > sh_lastq[k][iso]) atomicMax(&sh_lastq[k][iso], og); }
+        else atomicMax(&lastq[si], og);
+      }
+      // widest profile per (state, tile of output bins) among those that reach a bin
+      if (!(pid & PID_NOREACH)) {
+        if (tsh) { if (ps > sh_wt[k][tile]) atomicMax(&sh_wt[k][tile], ps); }
+        else atomicMax(&wtile[s * ntiles + tile + tile0], ps);
+      }
+    } else {
+      pid = PID_FB + iso;
+      if (tsh) sh_fb[k][tile] = 1;
+      else hasfb[s * ntiles + tile + tile0] = 1;
+    }
+    sh_k[k][pl] = kk;
+    sh_pid[k][pl] = (uint16_t)pid;
+  }
+  __syncthreads();
+  // ---- phase 3
+  if (act) {
+    const int io = g_iown[p];
+#pragma unroll
+    for (int k = 0; k < SB; k++) {
+      const int s = s0 + k;
+      if (s < ns) {
+        // written for skipped groups too: whole sectors, no fill reads
+        const double kk = sh_k[k][tid];
+        int4 v;
+        v.x = __double2loint(kk); v.y = __double2hiint(kk); v.z = io; v.w = (int)sh_pid[k][tid];
+        *reinterpret_cast<int4 *>(rec_out + (size_t)s * G + p) = v;
+      }
+    }
+  }
+  if (tid < SB * STR_NT) {
+    const int k = tid / STR_NT, t = tid % STR_NT, s = s0 + k;
+    if (s < ns && tile0 + t < ntiles) {
+      if (sh_wt[k][t] > __ldcg(&wtile[s * ntiles + tile0 + t])) atomicMax(&wtile[s * ntiles + tile0 + t], sh_wt[k][t]);
+      if (sh_fb[k][t]) hasfb[s * ntiles + tile0 + t] = 1;
     }
   }
   if (use_sh) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < SB * niso; i += blockDim.x) {
+    for (int i = tid; i < SB * niso; i += blockDim.x) {
       const int k = i / niso, is = i % niso, s = s0 + k;
       const int v = sh_lastq[k][is];
-      if (s < ns && v >= 0) atomicMax(&lastq[s * niso + is], v);
+      // most blocks cannot raise the maximum (sorted order runs against the original order):
+      // look before paying for an atomic on an address every block of this state shares
+      if (s < ns && v >= 0 && v > __ldcg(&lastq[s * niso + is])) atomicMax(&lastq[s * niso + is], v);
     }
   }
 }
@@ -654,72 +760,72 @@ __global__ void k_reach(int ns, int ntiles, int o, const int32_t *__restrict__ w
 // from the windows of each molecule row, always in sorted (row, fine bin) order: a fixed
 // summation order, no floating-point atomics.
 //   contributes  <=>  0 <= o*j - (iown - psize) <= 2*psize   (same test as the reference loop)
-// A block owns ACC_TILE consecutive bins of one state, a warp 32 of them.  Two schedules with
-// the same summation order:
-//   * narrow reach (R <= NARROW_R bins): each lane bisects the fine-bin-sorted groups for its
-//     own window [o*j - P, o*j + P] (P = widest half-size that can reach the tile) and walks it;
-//   * wide reach: the warp walks the union window together -- 32 group records are fetched
-//     coalesced, the survivors compacted into shared memory and broadcast one by one; lane i
-//     adds the sample for bin j0+i, which the polyphase table layout makes one contiguous
-//     256-byte read per group.
+// A block owns ACC_TILE consecutive bins of one state.  Two schedules, each with a fixed
+// summation order:
+//   * narrow reach (R <= NARROW_R bins): one thread per bin; it starts at the first record of the
+//     sub-cell holding o*j - P (P = widest half-size that can reach the tile; substart[] has NSUB
+//     sub-cells per bin, so no bisection) and walks the fine-bin-sorted records up to o*j + P;
+//   * wide reach: the block walks the union window of its 128 bins once: the window's records are
+//     split into four contiguous runs, one per warp; a warp fetches 32 records coalesced,
+//     resolves them (table address, covered bins by an exact multiply-high division), compacts
+//     the survivors into shared memory and broadcasts them; lane i adds the samples of bins
+//     i, i+32, i+64, i+96 of the tile, each one contiguous 256-byte read of the polyphase
+//     table.  The four partial sums per bin are added in warp order.
 #define NARROW_R 2
 struct AccRec {
   double k;
-  int addr0;   // table address of lane 0's sample
-  int lanes;   // lo | hi << 8: lanes (bins j0+lo .. j0+hi) the profile covers
+  int addr0;   // table address of bin 0's sample
+  int lanes;   // lo | (hi - lo) << 8: bins (tile-relative, lo..hi) the profile covers
+};
+struct WideShared {
+  AccRec rec[ACC_TILE / 32][32];
+  double part[ACC_TILE / 32][ACC_TILE];
 };
 
 __global__ void __launch_bounds__(ACC_TILE)
 k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nrows, int permol, int ntiles,
-             const int32_t *__restrict__ binstart, const int32_t *__restrict__ g_iown,
-             const double *__restrict__ k_in, const uint16_t *__restrict__ pid_in,
+             const int32_t *__restrict__ binstart, const int32_t *__restrict__ substart, int64_t nsub,
+             int nsube, const LineRec *__restrict__ rec_in,
              const int32_t *__restrict__ fbpid, const ProfEntry *__restrict__ ptab,
              const int32_t *__restrict__ reach, const int32_t *__restrict__ reachP,
              const double *__restrict__ pdata, double *__restrict__ out,
              unsigned long long *__restrict__ nsamp) {
-  __shared__ AccRec sh_rec[ACC_TILE / 32][32];
+  __shared__ __align__(16) WideShared sh;
   const int s = blockIdx.y;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t j0 = (int64_t)blockIdx.x * ACC_TILE + warp * 32;
-  if (j0 >= nwn) return;                       // whole warp
-  const int64_t j = j0 + lane;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t jt = (int64_t)blockIdx.x * ACC_TILE;
+  const int64_t j = jt + tid;
   const bool inb = j < nwn;
   const int R = reach[s * ntiles + blockIdx.x];
   const int P = reachP[s * ntiles + blockIdx.x];
-  const double *ks = k_in + (size_t)s * G;
-  const uint16_t *ps = pid_in + (size_t)s * G;
+  const int4 *rs = reinterpret_cast<const int4 *>(rec_in + (size_t)s * G);
   const int32_t *fbs = fbpid + (size_t)s * niso;
-  const int maxlane = (int)(nwn - 1 - j0 < 31 ? nwn - 1 - j0 : 31);
   unsigned long long cnt = 0;
-  double acc = 0.0;
-  for (int row = 0; row < nrows; row++) {
-    const int32_t *bs = binstart + (size_t)row * nwn;
-    if (R <= NARROW_R) {
-      if (inb && P >= 0) {
-        const int64_t jlo = j - R < 0 ? 0 : j - R;
-        const int64_t jhi = j + R + 1 > nwn ? nwn : j + R + 1;
-        const int oj = (int)(o * j);
-        const int lo_f = oj - P, hi_f = oj + P;
-        int a = bs[jlo];
-        const int p1 = bs[jhi];
-        int b = p1;
-        while (a < b) {                          // first group with fine bin >= lo_f
-          const int mid = (a + b) >> 1;
-          if (g_iown[mid] < lo_f) a = mid + 1; else b = mid;
-        }
-        // software-pipelined walk: the next group's three independent loads are in flight
-        // while the current one is resolved
-        int p = a;
-        int io_n = p < p1 ? g_iown[p] : 0x7fffffff;
-        unsigned pid_n = p < p1 ? ps[p] : PID_SKIP;
-        double k_n = p < p1 ? ks[p] : 0.0;
-        while (p < p1 && io_n <= hi_f) {
-          const int io = io_n;
-          unsigned pid = pid_n;
-          const double kk = k_n;
+  if (P < 0) {                                   // nothing reaches this tile
+    for (int row = 0; row < (permol ? nrows : 1); row++)
+      if (inb) out[((size_t)s * (permol ? nrows : 1) + row) * nwn + j] = 0.0;
+    return;
+  }
+  if (R <= NARROW_R) {
+    double acc = 0.0;
+    if (inb) {
+      const int64_t jhi = j + R + 1 > nwn ? nwn : j + R + 1;
+      const int oj = (int)(o * j);
+      const int lo_f = oj - P < 0 ? 0 : oj - P, hi_f = oj + P;
+      const int u = fd_div(lo_f * nsube, fd);      // sub-cell of the window's first fine bin
+      for (int row = 0; row < nrows; row++) {
+        const int p1 = binstart[(size_t)row * nwn + jhi];
+        // software-pipelined walk: the next record (one 128-bit read) is in flight while the
+        // current one is resolved
+        int p = substart[(size_t)row * nsub + u];
+        int4 r_n = p < p1 ? __ldg(rs + p) : make_int4(0, 0, 0x7fffffff, PID_SKIP);
+        while (p < p1 && r_n.z <= hi_f) {
+          const int io = r_n.z;
+          unsigned pid = (unsigned)r_n.w;
+          const double kk = __hiloint2double(r_n.y, r_n.x);
           p++;
-          if (p < p1) { io_n = g_iown[p]; pid_n = ps[p]; k_n = ks[p]; }
-          if (pid == PID_SKIP) continue;
+          if (p < p1) r_n = __ldg(rs + p);
+          if (PID_DEAD(pid)) continue;
           if (pid >= PID_FB) pid = fbs[pid - PID_FB];
           const ProfEntry pe = ptab[pid];
           const int idx = oj - io + pe.psize;
@@ -733,56 +839,83 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
             cnt++;
           }
         }
+        if (permol) {
+          out[((size_t)s * nrows + row) * nwn + j] = acc;
+          acc = 0.0;
+        }
       }
-    } else {
-      const int64_t ulo = j0 - R < 0 ? 0 : j0 - R;
-      const int64_t uhi = j0 + 32 + R > nwn ? nwn : j0 + 32 + R;
+      if (!permol) out[(size_t)s * nwn + j] = acc;
+    }
+  } else {
+    WideShared &w = sh;
+    const int maxbin = (int)(nwn - 1 - jt < ACC_TILE - 1 ? nwn - 1 - jt : ACC_TILE - 1);
+    const int64_t ulo = jt - R < 0 ? 0 : jt - R;
+    const int64_t uhi = jt + ACC_TILE + R > nwn ? nwn : jt + ACC_TILE + R;
+    const int ojt = (int)(o * jt);
+    double acc[ACC_TILE / 32];
+#pragma unroll
+    for (int q = 0; q < ACC_TILE / 32; q++) acc[q] = 0.0;
+    for (int row = 0; row < nrows; row++) {
+      const int32_t *bs = binstart + (size_t)row * nwn;
       const int p0 = bs[ulo], p1 = bs[uhi];
-      const int oj0 = (int)(o * j0);
-      for (int base = p0; base < p1; base += 32) {
+      const int seg = (((p1 - p0 + 3) >> 2) + 31) & ~31;       // records per warp, whole chunks
+      const int pa = p0 + warp * seg;
+      const int pb = pa + seg < p1 ? pa + seg : p1;
+      for (int base = pa; base < pb; base += 32) {
         const int p = base + lane;
-        unsigned pid = p < p1 ? ps[p] : PID_SKIP;
-        bool alive = pid != PID_SKIP;
+        const int4 rr = p < pb ? __ldg(rs + p) : make_int4(0, 0, 0, PID_SKIP);
+        unsigned pid = (unsigned)rr.w;
+        bool alive = !PID_DEAD(pid);
         AccRec rec;
         if (alive) {
           if (pid >= PID_FB) pid = fbs[pid - PID_FB];
           const ProfEntry pe = ptab[pid];
-          const int idx0 = oj0 - g_iown[p] + pe.psize;           // sample index for lane 0
-          // lanes with 0 <= idx0 + lane*o <= 2*psize
+          const int idx0 = ojt - rr.z + pe.psize;                // sample index for bin 0 of the tile
+          // bins with 0 <= idx0 + bin*o <= 2*psize
           const int lo = idx0 >= 0 ? 0 : fd_div(-idx0 + o - 1, fd);
           int hi = 2 * pe.psize - idx0;
           hi = hi < 0 ? -1 : fd_div(hi, fd);
-          if (hi > maxlane) hi = maxlane;
+          if (hi > maxbin) hi = maxbin;
           if (lo > hi) alive = false;
           else {
             const int first = idx0 + lo * o;                     // >= 0
             const int q = fd_div(first, fd);
             rec.addr0 = pe.off + (first - q * o) * pe.nk + q - lo;
-            rec.lanes = lo | (hi << 8);
-            rec.k = ks[p];
+            rec.lanes = lo | ((hi - lo) << 8);
+            rec.k = __hiloint2double(rr.y, rr.x);
             cnt += hi - lo + 1;
           }
         }
         const unsigned m = __ballot_sync(0xffffffffu, alive);
-        if (alive) sh_rec[warp][__popc(m & ((1u << lane) - 1))] = rec;
+        if (alive) w.rec[warp][__popc(m & ((1u << lane) - 1))] = rec;
         __syncwarp();
         const int n = __popc(m);
-#pragma unroll 4
+#pragma unroll 2
         for (int i = 0; i < n; i++) {
-          const AccRec r = sh_rec[warp][i];
-          const double pv = pdata[r.addr0 + lane];     // unconditional (table is padded): loads overlap
-          const double t = fma(r.k, pv, acc);
-          acc = (lane >= (r.lanes & 255) && lane <= (r.lanes >> 8)) ? t : acc;
+          const AccRec r = w.rec[warp][i];
+          const int d = lane - (r.lanes & 255);                  // bin - lo for q = 0
+          const unsigned span = (unsigned)(r.lanes >> 8);        // hi - lo
+          const double *pp = pdata + r.addr0 + lane;
+#pragma unroll
+          for (int q = 0; q < ACC_TILE / 32; q++)
+            if ((unsigned)(d + 32 * q) <= span) acc[q] = fma(r.k, __ldg(pp + 32 * q), acc[q]);
         }
         __syncwarp();
       }
-    }
-    if (permol) {
-      if (inb) out[((size_t)s * nrows + row) * nwn + j] = acc;
-      acc = 0.0;
+      if (permol || row == nrows - 1) {
+#pragma unroll
+        for (int q = 0; q < ACC_TILE / 32; q++) { w.part[warp][lane + 32 * q] = acc[q]; acc[q] = 0.0; }
+        __syncthreads();
+        if (inb) {
+          double v = w.part[0][threadIdx.x];
+#pragma unroll
+          for (int g = 1; g < ACC_TILE / 32; g++) v += w.part[g][threadIdx.x];
+          out[((size_t)s * (permol ? nrows : 1) + (permol ? row : 0)) * nwn + j] = v;
+        }
+        __syncthreads();
+      }
     }
   }
-  if (!permol && inb) out[(size_t)s * nwn + j] = acc;
   // sample counter (the benchmark's unit of work): integer atomics only
   for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
   if (lane == 0 && cnt) atomicAdd(&nsamp[s], cnt);
@@ -794,7 +927,8 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
                   double ethresh, int permol, double *d_out_rows, double *h_out) {
   TB_REQUIRE(c->have_lines && c->have_prof, TB_ERR_STATE,
              "tb_upload_lines and tb_build_profiles must precede the line sum");
-  TB_REQUIRE(c->niso < (int)(PID_SKIP - PID_FB), TB_ERR_ARG, "too many isotopes (%d)", c->niso);
+  TB_REQUIRE(c->niso < 0x7FFF, TB_ERR_ARG, "too many isotopes (%d)", c->niso);
+  TB_REQUIRE(c->nDop * c->nLor < (int)PID_NOREACH, TB_ERR_ARG, "Voigt table has too many cells (%d)", c->nDop * c->nLor);
   TB_CUDA(cudaSetDevice(c->device));
   cudaStream_t st = c->stream;
   const int niso = c->niso, nmol = c->nmol, nrows = c->nrows;
@@ -805,7 +939,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   c->last_permol = permol;
   // chunk the states so the per-(state, group) scratch stays below ~12 GB
   int chunk = ns;
-  const size_t per_state = (size_t)G * 10 + (size_t)(M - G) * 8 + (size_t)nout * nwn * 8 + 64;
+  const size_t per_state = (size_t)G * 16 + (size_t)(M - G) * 8 + (size_t)nout * nwn * 8 + 64;
   const size_t budget = (size_t)12 << 30;
   if (per_state * chunk > budget) chunk = (int)(budget / per_state);
   if (chunk < 1) chunk = 1;
@@ -819,13 +953,13 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   TB_TRY(c->s_wtile.ensure((size_t)chunk * ntiles)); TB_TRY(c->s_reach.ensure((size_t)chunk * ntiles));
   TB_TRY(c->s_reachP.ensure((size_t)chunk * ntiles));
   TB_TRY(c->s_facz.ensure((size_t)chunk * niso + 1)); TB_TRY(c->s_rtemp.ensure(chunk));
-  TB_TRY(c->s_ral.ensure((size_t)chunk * niso + 1));
+  TB_TRY(c->s_ral.ensure((size_t)chunk * niso + 1)); TB_TRY(c->s_lcz.ensure((size_t)chunk * niso + 1));
   const int64_t X = M - G;
   TB_TRY(c->s_xterm.ensure((size_t)chunk * X + 1));
   TB_TRY(c->s_hasfb.ensure((size_t)chunk * ntiles));
   TB_TRY(c->s_kmax.ensure((size_t)chunk * nrows + 1));
   TB_TRY(c->s_nsamp.ensure(ns));
-  TB_TRY(c->s_k.ensure((size_t)chunk * G + 1)); TB_TRY(c->s_pid.ensure((size_t)chunk * G + 1));
+  TB_TRY(c->s_rec.ensure((size_t)chunk * G + 1));
   double *d_out = d_out_rows;
   if (!d_out) {
     TB_TRY(c->s_out.ensure((size_t)chunk * nout * nwn));
@@ -883,13 +1017,16 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
                                                       c->s_rtemp.p, c->efct, c->s_xterm.p);
         TB_LAUNCHED(c);
       }
+      k_logthr<<<nblk((int64_t)cs * niso, 128), 128, 0, st>>>(cs, niso, nrows, permol, ethresh, c->d_iso_row.p,
+                                                              c->s_facz.p, c->s_kmax.p, c->s_lcz.p);
+      TB_LAUNCHED(c);
       k_strength<SB><<<g3, Tn, 0, st>>>(
-          G, cs, niso, c->o, fd_tile, c->g_start.p, c->g_iso.p, c->g_orig.p, c->g_iown.p, c->g_wavn.p,
-          c->m_wavn.p, c->m_elow.p, c->m_gf.p, c->s_rtemp.p, c->s_facz.p, c->s_ral.p, c->s_xterm.p, X,
+          G, cs, niso, c->o, fd_tile, fd_o, c->g_start.p, c->g_iso.p, c->g_orig.p, c->g_iown.p, c->g_wavn.p,
+          c->g_a0.p, c->g_gf.p, c->g_lg.p, c->s_rtemp.p, c->s_facz.p, c->s_lcz.p, c->s_ral.p, c->s_xterm.p, X,
           (float)c->dop_lmin, (float)c->dop_rstep, c->s_dens.p, nmol,
           c->d_iso_imol.p, c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ilor.p,
-          c->d_aDop.p, c->nDop, c->d_ptab.p, c->nLor, c->efct, ethresh, permol, nrows, c->s_kmax.p,
-          c->s_k.p, c->s_pid.p, c->s_lastq.p, c->s_wtile.p, c->s_hasfb.p, ntiles);
+          c->d_aDop.p, c->nDop, c->d_ptab.p, c->nLor, ethresh, permol, nrows, c->s_kmax.p,
+          c->s_rec.p, c->s_lastq.p, c->s_wtile.p, c->s_hasfb.p, ntiles);
       tb_timer_end(c, "strength");
       k_fallback<<<nblk(cs * niso, 128), 128, 0, st>>>(
           cs, niso, c->s_lastq.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
@@ -901,7 +1038,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
     dim3 g4(ntiles, cs);
     tb_timer_begin(c, "accumulate");
     k_accumulate<<<g4, ACC_TILE, 0, st>>>(nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, c->binstart.p,
-                                          c->g_iown.p, c->s_k.p, c->s_pid.p, c->s_fbpid.p, c->d_ptab.p,
+                                          c->substart.p, c->nsub, c->nsube, c->s_rec.p, c->s_fbpid.p, c->d_ptab.p,
                                           c->s_reach.p, c->s_reachP.p, c->d_pdata2.p, dst,
                                           c->s_nsamp.p + s0);
     tb_timer_end(c, "accumulate");
@@ -954,7 +1091,7 @@ extern "C" int tb_get_sample_counts(tb_ctx *c, int64_t *nsamples, int ns) {
 __global__ void k_trace(int64_t n, int64_t G, int s_local, int niso, const uint8_t *__restrict__ flag,
                         const int32_t *__restrict__ l_iown, const int32_t *__restrict__ l_gpos,
                         const int32_t *__restrict__ g_idwn, const int16_t *__restrict__ g_iso,
-                        const double *__restrict__ k_in, const uint16_t *__restrict__ pidv, int nLor,
+                        const LineRec *__restrict__ recs, int nLor,
                         const int32_t *__restrict__ fb, int32_t *__restrict__ iown,
                         int32_t *__restrict__ idwn, int32_t *__restrict__ idop, int8_t *__restrict__ status) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -966,11 +1103,11 @@ __global__ void k_trace(int64_t n, int64_t G, int s_local, int niso, const uint8
     int32_t p = l_gpos[i];
     io = l_iown[i];
     id = g_idwn[p];
-    const unsigned pid = pidv[(size_t)s_local * G + p];
+    const unsigned pid = recs[(size_t)s_local * G + p].pid;
     if (pid == PID_SKIP) st = 3;
     else {
       st = 1;
-      dp = pid >= PID_FB ? fb[s_local * niso + g_iso[p]] : (int)pid / nLor;
+      dp = pid >= PID_FB ? fb[s_local * niso + g_iso[p]] : (int)(pid & (PID_NOREACH - 1)) / nLor;
     }
   } else if (!(f & 2)) st = 2;     // visited only as a co-added member
   iown[i] = io; idwn[i] = id; idop[i] = dp; status[i] = st;
@@ -980,7 +1117,7 @@ extern "C" int tb_get_line_trace(tb_ctx *c, int s, int32_t *iown, int32_t *idwn,
                                  int8_t *status) {
   TB_REQUIRE(c->have_lines && c->last_ns > 0, TB_ERR_STATE, "no line-sum batch has run");
   TB_REQUIRE(s >= 0 && s < c->last_ns, TB_ERR_ARG, "state %d out of range", s);
-  TB_REQUIRE((size_t)c->last_ns * c->G + 1 <= c->s_k.n, TB_ERR_STATE,
+  TB_REQUIRE((size_t)c->last_ns * c->G + 1 <= c->s_rec.n, TB_ERR_STATE,
              "trace is only available when the batch ran as a single chunk");
   TB_CUDA(cudaSetDevice(c->device));
   const int64_t n = c->nlines;
@@ -989,8 +1126,8 @@ extern "C" int tb_get_line_trace(tb_ctx *c, int s, int32_t *iown, int32_t *idwn,
   DevBuf<int8_t> e;
   TB_TRY(a.ensure(n)); TB_TRY(b.ensure(n)); TB_TRY(d.ensure(n)); TB_TRY(e.ensure(n));
   k_trace<<<nblk(n, 256), 256, 0, c->stream>>>(n, c->G, s, c->niso, c->l_flag.p, c->l_iown.p,
-                                               c->l_gpos.p, c->g_idwn.p, c->g_iso.p, c->s_k.p,
-                                               c->s_pid.p, c->nLor, c->s_fb.p, a.p, b.p, d.p, e.p);
+                                               c->l_gpos.p, c->g_idwn.p, c->g_iso.p,
+                                               c->s_rec.p, c->nLor, c->s_fb.p, a.p, b.p, d.p, e.p);
   TB_CUDA(cudaMemcpyAsync(iown, a.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
   TB_CUDA(cudaMemcpyAsync(idwn, b.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
   TB_CUDA(cudaMemcpyAsync(idop, d.p, n * 4, cudaMemcpyDeviceToHost, c->stream));

@@ -210,7 +210,7 @@ extern "C" int tb_build_profiles(tb_ctx *c, int nDop, int nLor, float dmin, floa
   // polyphase copy: min(o, n) phases of nk = (n-1)/o + 1 samples each per unique profile
   std::vector<int32_t> off2(desc.size());
   std::vector<ProfEntry> ptab((size_t)nDop * nLor);
-  int64_t total2 = 32;     // 32 floats of padding either side: the warp path reads lanes it then discards
+  int64_t total2 = TB_PROF_PAD;   // zero padding either side: the warp path reads lanes it then discards
   {
     std::map<int64_t, size_t> by_off;
     for (size_t k = 0; k < desc.size(); k++) {
@@ -234,7 +234,7 @@ extern "C" int tb_build_profiles(tb_ctx *c, int nDop, int nLor, float dmin, floa
   TB_TRY(c->d_aDop.ensure(nDop + 1)); TB_TRY(c->d_aLor.ensure(nLor + 1));
   TB_TRY(c->d_psize.ensure(ps32.size())); TB_TRY(c->d_poff.ensure(c->poff.size()));
   TB_TRY(c->d_pdata.ensure(total));
-  TB_TRY(c->d_pdata2.ensure(total2 + 32));
+  TB_TRY(c->d_pdata2.ensure(total2 + TB_PROF_PAD));
   TB_TRY(c->d_ptab.ensure(ptab.size()));
   DevBuf<ProfDesc> d_desc;
   DevBuf<int32_t> d_off2;
@@ -249,7 +249,7 @@ extern "C" int tb_build_profiles(tb_ctx *c, int nDop, int nLor, float dmin, floa
   TB_CUDA(cudaMemcpyAsync(d_desc.p, desc.data(), desc.size() * sizeof(ProfDesc), cudaMemcpyHostToDevice, st));
   TB_CUDA(cudaMemcpyAsync(d_off2.p, off2.data(), off2.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
   TB_CUDA(cudaMemcpyAsync(c->d_ptab.p, ptab.data(), ptab.size() * sizeof(ProfEntry), cudaMemcpyHostToDevice, st));
-  TB_CUDA(cudaMemsetAsync(c->d_pdata2.p, 0, (total2 + 32) * sizeof(double), st));
+  TB_CUDA(cudaMemsetAsync(c->d_pdata2.p, 0, (total2 + TB_PROF_PAD) * sizeof(double), st));
   tb_timer_begin(c, "voigt");
   k_voigt_table<<<(unsigned)blocks, TPB, 0, st>>>(d_desc.p, (int)desc.size(), c->d_pdata.p);
   tb_timer_end(c, "voigt");
