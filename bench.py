@@ -269,6 +269,8 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device -- the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO"):
+            os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
@@ -277,9 +279,13 @@ def run_ours(args):
     # N > 1: batched atmospheres sharded over the ranks (BART's use of the library: many T-P/abundance
     # profiles through one static problem) -- rank r computes the spectra of its own atmosphere,
     # no data-path collective; the spectra are gathered with NCCL.  Per-GPU work is fixed: weak scaling.
-    my_prob = prob if rank == 0 else workloads.perturbed(prob, seed=1000 + rank)
+    bands_mode = args.sharding == "bands"
+    # --sharding bands: ONE spectrum per step, its wavenumber range split over the ranks (each rank
+    # evaluates the lines that reach its band, two exact all-reduce MAX complete the global
+    # threshold / carried Doppler index, the spectrum slices are all-gathered): strong scaling.
+    my_prob = prob if (rank == 0 or bands_mode) else workloads.perturbed(prob, seed=1000 + rank)
     t0 = time.perf_counter()
-    tr = sharding.ShardedTransit(local_rank, rank, world)
+    tr = (sharding.BandShardedTransit if bands_mode else sharding.ShardedTransit)(local_rank, rank, world)
     stream = torch.cuda.current_stream()
     tr.ctx.set_stream(stream.cuda_stream)              # kernels, copies and the NCCL gather share one stream
     tr.transit_init(my_prob)
@@ -297,13 +303,25 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     def step():
+        if bands_mode:
+            gathered[0] = tr.do_transit_gathered()
+            return
         tr.do_transit(out)
         if world > 1:        # natm = world: one atmosphere per rank per step
             gathered[0] = sharding.gather_spectra(tr.device_spectrum_tensor().view(1, -1), world, rank, world)
 
     for _ in range(args.warmup):
         step()
+    if bands_mode:
+        out[:] = gathered[0].cpu().numpy()
     ref_out = out.copy()
+    verified = None
+    if bands_mode and args.verify and rank == 0:
+        one = api.Transit(local_rank)
+        one.transit_init(prob)
+        verified = bool(np.array_equal(one.do_transit(None), ref_out))
+        one.free_memory()
+        assert verified, "band-sharded spectrum differs from the single-GPU spectrum"
 
     # ---- device-timed steps (static inputs resident; L2 flushed between steps)
     sampler = ClockSampler(local_rank)
@@ -329,8 +347,10 @@ def run_ours(args):
     launches = ctx.launch_count() - l0
     nsamp = int(tr.sample_counts().sum())                 # this rank's executed profile updates per step
     clocks = sampler.stop()
+    if bands_mode:
+        out[:] = gathered[0].cpu().numpy()
     assert np.array_equal(out, ref_out), "spectrum changed between steps: the path is not deterministic"
-    if world > 1:
+    if world > 1 and not bands_mode:
         assert np.array_equal(gathered[0][rank].cpu().numpy(), out), "gathered slice differs from the local spectrum"
 
     # ---- end to end through the host mirror with HOST buffers (H2D atmosphere + D2H spectrum per step)
@@ -355,6 +375,7 @@ def run_ours(args):
             dist.destroy_process_group()
         return 0
 
+    nspec = 1 if bands_mode else world           # spectra finished per step by the whole job
     hbm_peak, peak_src = measured_peaks()
     acc_ms = float(np.mean(k_ms["accumulate"]))
     mol_ms = float(np.mean(k_ms["molext"]))
@@ -371,12 +392,14 @@ def run_ours(args):
     except (OSError, ValueError):
         pass
     line = {
-        "metric": "spectra/s", "value": world * args.steps / (dev_ms * 1e-3), "unit": "spectra/s", "n_gpus": world,
+        "metric": "spectra/s", "value": nspec * args.steps / (dev_ms * 1e-3), "unit": "spectra/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(prob, args.workload, world),
-        "e2e": {"value": world * args.steps / e2e_s, "unit": "spectra/s", "h2d_bytes_per_step": h2d * world,
-                "d2h_bytes_per_step": d2h * world},
+        "scaling": "strong" if bands_mode else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": dict(workload_config(prob, args.workload, world),
+                       **({"sharding": f"wavenumber bands x{world} (one spectrum per step)", "bands": tr.bands}
+                          if bands_mode else {})),
+        "e2e": {"value": nspec * args.steps / e2e_s, "unit": "spectra/s", "h2d_bytes_per_step": h2d * world,
+                "d2h_bytes_per_step": d2h * nspec},
         "gpu_launches": launches,
         "line_sum": {"gsamples_per_s": nsamp / (mol_ms * 1e-3) / 1e9, "samples_per_step": nsamp,
                      "line_layers_per_s": len(prob.wl) * prob.nrad / (mol_ms * 1e-3), "molext_ms": mol_ms},
@@ -387,6 +410,8 @@ def run_ours(args):
                      "fp64_gflops": 2.0 * my_samp / (acc_ms * 1e-3) / 1e9},
         "clocks": clocks, "init_s": init_s,
     }
+    if verified is not None:
+        line["bit_identical_to_single_gpu"] = verified
     if args.microbench:
         line["microbench"] = ctx.microbench()
     if world == 1 and not args.no_cpu_baseline:
@@ -404,6 +429,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="C2")
+    ap.add_argument("--verify", action="store_true",
+                    help="--sharding bands: rank 0 also computes the spectrum unsharded and requires bit-identity")
+    ap.add_argument("--sharding", default="atmospheres", choices=["atmospheres", "bands"],
+                    help="N>1: one atmosphere per rank (weak scaling, default) or one spectrum split into "
+                         "wavenumber bands (strong scaling)")
     ap.add_argument("--scale", type=float, default=1.0, help="line-count multiplier (debugging only; 1.0 = the named config)")
     ap.add_argument("--microbench", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")

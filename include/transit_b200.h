@@ -143,6 +143,22 @@ int  tb_set_stream(tb_ctx *c, void *stream);
  * NCCL gather of per-rank spectra; valid until the next call that produces a spectrum.  */
 int  tb_device_spectrum(tb_ctx *c, void **ptr, int64_t *n);
 
+/* Wavenumber-band shard (the reference's only way to use more cores is N processes
+ * over disjoint wavenumber bands, each re-reading the whole line list).  The context keeps the
+ * whole line index but computes the line sum only for coarse bins [j_lo, j_hi) -- both multiples
+ * of 128 or the grid ends; (0, 0) = the whole grid.  Two quantities of computemolext are global
+ * over the line list: the strength maximum behind the threshold (extinction.c:399-427, 467) and
+ * the Doppler index carried from the last evaluated line (extinction.c:480-483).  With world > 1
+ * the library calls `fn` twice per batch of states for an in-place all-reduce MAX over `count`
+ * elements at `device_ptr` (doubles for TB_EXCH_KMAX, int32 for TB_EXCH_LASTQ), to be enqueued
+ * on the context's stream (e.g. ncclAllReduce, or torch.distributed on the stream given to
+ * tb_set_stream); both maxima are exact, so the banded results are bit-identical to one GPU.
+ * Bins outside the band come back as zero.                                              */
+enum { TB_EXCH_KMAX = 0, TB_EXCH_LASTQ = 1 };
+typedef int (*tb_exchange_fn)(void *user, int what, void *device_ptr, int64_t count);
+int  tb_set_shard(tb_ctx *c, int64_t j_lo, int64_t j_hi, int rank, int world, tb_exchange_fn fn,
+                  void *user);
+
 /* device micro-benchmarks used for the roofline denominators (FP64 FMA / exp / copy)   */
 int  tb_microbench(tb_ctx *c, double *dfma_tflops, double *dexp_gops, double *copy_gbs);
 

@@ -274,3 +274,69 @@ def test_host_mirror_interface(golden):
     out = tr.do_transit()
     assert relerr(out, d["out"]) < SPEC_RTOL
     tr.free_memory()
+
+
+# ------------------------------------------------------------------ wavenumber-band shard (8e)
+
+def test_band_shard_two_ranks_bit_identical_to_one():
+    """Two contexts, each owning a wavenumber band (tb_set_shard), run as two 'ranks' in two threads;
+    the exchange callback completes the two global maxima through host memory.  Extinction stitched
+    from the bands must be BIT-identical to the single-context result, deep (wide) and shallow
+    (narrow) layers alike, and the executed sample counts must add up."""
+    import threading
+    import torch
+    from transit_b200 import sharding
+
+    prob = workloads.make_problem("C2", scale=0.02, nlayers=24, wn_hi=6000.0)
+    ref = setup_ctx(prob)
+    ref.extinction_lbl(prob.ethresh)
+    e_ref = ref.get_extinction()
+    n_ref = ref.sample_counts(prob.nrad)
+    ref.close()
+
+    world = 2
+    bands = sharding.wavenumber_bands(sharding.line_weights(prob), world)
+    assert bands[0][1] % 128 == 0 and 0 < bands[0][1] < prob.nwn
+    barrier = threading.Barrier(world)
+    slots = [None] * world
+    ctxs_, out, cnt, err = [None] * world, [None] * world, [None] * world, []
+
+    def make_exchange(rank):
+        def exchange(what, ptr, count):
+            ctxs_[rank].sync()
+            t = sharding._alias(ptr, count, "<f8" if what == 0 else "<i4")
+            slots[rank] = t.cpu()
+            barrier.wait(timeout=120)
+            m = torch.maximum(slots[0], slots[1])
+            barrier.wait(timeout=120)
+            t.copy_(m.cuda())
+            torch.cuda.synchronize()
+        return exchange
+
+    def run(rank):
+        try:
+            c = setup_ctx(prob)
+            ctxs_[rank] = c
+            c.set_shard(bands[rank][0], bands[rank][1], rank, world, make_exchange(rank))
+            c.extinction_lbl(prob.ethresh)
+            out[rank] = c.get_extinction()
+            cnt[rank] = c.sample_counts(prob.nrad)
+            c.close()
+        except Exception as e:       # noqa: BLE001
+            err.append(e)
+            barrier.abort()
+
+    th = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join(timeout=300)
+    assert not err, err
+    e = np.zeros_like(e_ref)
+    for r, (lo, hi) in enumerate(bands):
+        e[:, lo:hi] = out[r][:, lo:hi]
+        other = np.ones(prob.nwn, bool)
+        other[lo:hi] = False
+        assert not out[r][:, other].any()            # bins outside the band come back as zero
+    assert np.array_equal(e, e_ref)
+    assert np.array_equal(cnt[0] + cnt[1], n_ref)

@@ -75,7 +75,11 @@ ABI = {
     "tb_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "tb_device_spectrum": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), i64p]),
     "tb_microbench": (C.c_int, [C.c_void_p, f64p, f64p, f64p]),
+    "tb_set_shard": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
 }
+
+
+EXCHANGE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int64)
 
 
 class TransitError(RuntimeError):
@@ -342,6 +346,23 @@ class Context:
         p, n = C.c_void_p(), C.c_int64()
         self._ck(self.lib.tb_device_spectrum(self.h, C.byref(p), C.byref(n)), "tb_device_spectrum")
         return p.value, n.value
+
+    def set_shard(self, j_lo, j_hi, rank=0, world=1, exchange=None):
+        """Wavenumber-band shard: line sum only for coarse bins [j_lo, j_hi).  ``exchange(what, ptr, count)``
+        must all-reduce MAX in place on the context's stream (what 0: float64, 1: int32)."""
+        cb = None
+        if exchange is not None:
+            def _cb(user, what, ptr, count):
+                try:
+                    exchange(int(what), int(ptr), int(count))
+                    return 0
+                except Exception as e:       # never let an exception cross the C boundary
+                    print(f"transit_b200: exchange callback failed: {e!r}")
+                    return 1
+            cb = EXCHANGE_FN(_cb)
+        self._exchange_cb = cb               # keep the trampoline alive as long as the context uses it
+        self._ck(self.lib.tb_set_shard(self.h, int(j_lo), int(j_hi), int(rank), int(world),
+                                       C.cast(cb, C.c_void_p) if cb else None, None), "tb_set_shard")
 
     def sync(self):
         self._ck(self.lib.tb_sync(self.h), "tb_sync")

@@ -95,6 +95,23 @@ extern "C" int tb_create(int device, tb_ctx **out) {
   return TB_OK;
 }
 
+extern "C" int tb_set_shard(tb_ctx *c, int64_t j_lo, int64_t j_hi, int rank, int world, tb_exchange_fn fn,
+                            void *user) {
+  TB_REQUIRE(c->have_grid, TB_ERR_STATE, "tb_set_wn_grid must precede tb_set_shard");
+  TB_REQUIRE(world >= 1 && rank >= 0 && rank < world, TB_ERR_ARG, "tb_set_shard: rank %d of %d", rank, world);
+  TB_REQUIRE(world == 1 || fn, TB_ERR_ARG, "tb_set_shard: world > 1 needs an exchange callback");
+  if (j_lo == 0 && j_hi == 0) j_hi = c->nwn;
+  TB_REQUIRE(j_lo >= 0 && j_lo <= j_hi && j_hi <= c->nwn, TB_ERR_ARG, "tb_set_shard: band [%lld, %lld) outside the grid",
+             (long long)j_lo, (long long)j_hi);
+  TB_REQUIRE(j_lo % 128 == 0 && (j_hi % 128 == 0 || j_hi == c->nwn), TB_ERR_ARG,
+             "tb_set_shard: band ends must be multiples of 128 (or the grid end)");
+  c->band_lo = j_lo; c->band_hi = j_hi;
+  if (j_lo == 0 && j_hi == c->nwn) c->band_lo = c->band_hi = 0;
+  c->shard_rank = rank; c->shard_world = world;
+  c->exch = fn; c->exch_user = user;
+  return TB_OK;
+}
+
 extern "C" int tb_sync(tb_ctx *c) {
   TB_CUDA(cudaSetDevice(c->device));
   TB_CUDA(cudaStreamSynchronize(c->stream));

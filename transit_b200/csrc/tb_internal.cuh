@@ -166,6 +166,13 @@ struct tb_ctx {
   int64_t nsub = 0;
   int nsube = 1;
 
+  // ---- wavenumber-band shard (tb_set_shard): line sum only for coarse bins [band_lo, band_hi)
+  int64_t band_lo = 0, band_hi = 0;   // (0, 0) = whole grid
+  int shard_rank = 0, shard_world = 1;
+  tb_exchange_fn exch = nullptr;
+  void *exch_user = nullptr;
+  std::vector<int32_t> h_binstart;    // host copy of binstart (group ranges of a band)
+
   // ---- Voigt table (a3/a4)
   bool have_prof = false;
   int nDop = 0, nLor = 0;

@@ -222,6 +222,7 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
   cudaStream_t st = c->stream;
   c->nlines = n; c->wfct = wfct; c->efct = efct;
   c->have_lines = false;
+  c->h_binstart.clear();
   c->G = c->M = c->Mq = 0;
   const int64_t nkeys = (int64_t)c->nrows * c->nwn;
   TB_TRY(c->binstart.ensure(nkeys + 1));
@@ -548,7 +549,8 @@ __global__ void k_logthr(int ns, int niso, int nrows, int permol, double ethresh
 // global integer atomics per block instead of one per group.
 #define STR_NT 4   // consecutive accumulate tiles a block's reach maxima are kept for in shared memory
 template <int SB>
-__global__ void __launch_bounds__(256) k_strength(int64_t G, int ns, int niso, int o, FastDiv fd_tile, FastDiv fd_o,
+__global__ void __launch_bounds__(256) k_strength(int64_t G, int64_t p_off, int64_t p_end, int ns, int niso, int o,
+                           FastDiv fd_tile, FastDiv fd_o,
                            const int32_t *__restrict__ g_start,
                            const int16_t *__restrict__ g_iso, const int32_t *__restrict__ g_orig,
                            const int32_t *__restrict__ g_iown,
@@ -583,12 +585,12 @@ __global__ void __launch_bounds__(256) k_strength(int64_t G, int ns, int niso, i
   if (tid < SB * STR_NT) { (&sh_wt[0][0])[tid] = -1; (&sh_fb[0][0])[tid] = 0; }
   if (tid == 0) sh_cnt = 0;
   __syncthreads();
-  const int64_t pbase = blockIdx.x * (int64_t)blockDim.x;
+  const int64_t pbase = p_off + blockIdx.x * (int64_t)blockDim.x;     // groups [p_off, p_end) of this launch
   const int64_t p = pbase + tid;
   const int s0 = blockIdx.y * SB;
-  const bool act = p < G;
+  const bool act = p < p_end;
   const unsigned lane = tid & 31;
-  const int tile0 = fd_div(g_iown[pbase], fd_tile);        // pbase < G always
+  const int tile0 = fd_div(g_iown[pbase], fd_tile);        // pbase < p_end always
   // ---- phase 1
   {
     double a0 = 0, lg = 0;
@@ -736,14 +738,15 @@ __global__ void k_fallback(int ns, int niso, const int32_t *__restrict__ lastq,
 // reach[s][t] / reachP[s][t]: how many coarse bins (and fine bins) to either side an output bin
 // of tile t must look for contributing groups.  A group whose fine bin lies in coarse cell d and
 // whose profile half-size is psize touches bins d - psize/o .. d + 1 + psize/o.
-__global__ void k_reach(int ns, int ntiles, int o, const int32_t *__restrict__ wtile,
+__global__ void k_reach(int ns, int ntiles, int o, int utiles, const int32_t *__restrict__ wtile,
                         const uint8_t *__restrict__ hasfb, const int32_t *__restrict__ fbmax,
                         int32_t *__restrict__ reach, int32_t *__restrict__ reachP) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= ns * ntiles) return;
   const int s = i / ntiles, t = i % ntiles;
   int R = 0, P = -1;
-  for (int u = 0; u < ntiles; u++) {
+  const int u0 = t - utiles < 0 ? 0 : t - utiles, u1 = t + utiles + 1 > ntiles ? ntiles : t + utiles + 1;
+  for (int u = u0; u < u1; u++) {      // utiles: how far the widest profile of the table can reach
     int ps = wtile[s * ntiles + u];
     if (hasfb[s * ntiles + u]) ps = max(ps, fbmax[s]);
     if (ps < 0) continue;
@@ -784,7 +787,7 @@ struct WideShared {
 
 __global__ void __launch_bounds__(ACC_TILE)
 k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nrows, int permol, int ntiles,
-             const int32_t *__restrict__ binstart, const int32_t *__restrict__ substart, int64_t nsub,
+             int tile_off, const int32_t *__restrict__ binstart, const int32_t *__restrict__ substart, int64_t nsub,
              int nsube, const LineRec *__restrict__ rec_in,
              const int32_t *__restrict__ fbpid, const ProfEntry *__restrict__ ptab,
              const int32_t *__restrict__ reach, const int32_t *__restrict__ reachP,
@@ -793,11 +796,12 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
   __shared__ __align__(16) WideShared sh;
   const int s = blockIdx.y;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int64_t jt = (int64_t)blockIdx.x * ACC_TILE;
+  const int tile = blockIdx.x + tile_off;          // a band shard launches only its own tiles
+  const int64_t jt = (int64_t)tile * ACC_TILE;
   const int64_t j = jt + tid;
   const bool inb = j < nwn;
-  const int R = reach[s * ntiles + blockIdx.x];
-  const int P = reachP[s * ntiles + blockIdx.x];
+  const int R = reach[s * ntiles + tile];
+  const int P = reachP[s * ntiles + tile];
   const int4 *rs = reinterpret_cast<const int4 *>(rec_in + (size_t)s * G);
   const int32_t *fbs = fbpid + (size_t)s * niso;
   unsigned long long cnt = 0;
@@ -975,6 +979,31 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   };
   const FastDiv fd_o = fastdiv(c->o), fd_tile = fastdiv((int64_t)c->o * ACC_TILE);
   TB_REQUIRE(c->nDop < 255, TB_ERR_ARG, "nDop must be < 255");
+  // widest reach any profile of the table can have, in coarse bins and in accumulate tiles
+  int64_t max_psize = 0;
+  for (size_t i = 0; i < c->psize.size(); i++) max_psize = c->psize[i] > max_psize ? c->psize[i] : max_psize;
+  const int64_t Rmax = 2 + max_psize / c->o;
+  const int utiles = (int)((Rmax + ACC_TILE - 1) / ACC_TILE) + 1;
+  // wavenumber-band shard (tb_set_shard): which tiles this context accumulates and which groups
+  // can reach them
+  const bool banded = c->band_hi > c->band_lo;
+  const int64_t b_lo = banded ? c->band_lo : 0, b_hi = banded ? c->band_hi : nwn;
+  const int tile_lo = (int)(b_lo / ACC_TILE), tile_hi = (int)((b_hi + ACC_TILE - 1) / ACC_TILE);
+  std::vector<int64_t> pa(nrows, 0), pb(nrows, 0);
+  if (banded && G > 0) {
+    if (c->h_binstart.empty()) {
+      c->h_binstart.resize((size_t)nrows * nwn + 1);
+      TB_CUDA(cudaMemcpyAsync(c->h_binstart.data(), c->binstart.p, c->h_binstart.size() * sizeof(int32_t),
+                              cudaMemcpyDeviceToHost, st));
+      TB_CUDA(cudaStreamSynchronize(st));
+    }
+    const int64_t jl = b_lo - Rmax < 0 ? 0 : b_lo - Rmax, jh = b_hi + Rmax > nwn ? nwn : b_hi + Rmax;
+    for (int r = 0; r < nrows; r++) {
+      pa[r] = c->h_binstart[(size_t)r * nwn + jl];
+      pb[r] = c->h_binstart[(size_t)r * nwn + jh];
+    }
+  }
+  TB_REQUIRE(c->shard_world == 1 || c->exch, TB_ERR_STATE, "sharded context without an exchange callback");
   tb_timer_begin(c, "molext");
   for (int s0 = 0; s0 < ns; s0 += chunk) {
     const int cs = (ns - s0 < chunk) ? ns - s0 : chunk;
@@ -1004,13 +1033,19 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
         k_kmax<SB><<<dim3(nblk(seed, Tn * KMAX_LPT), (cs + SB - 1) / SB), Tn, 0, st>>>(
             0, seed, cs, niso, c->q_g.p, c->q_a.p, c->q_w.p, c->q_iso.p, c->s_rtemp.p, c->s_Z.p, c->d_iso_mass.p,
             c->d_iso_row.p, permol, nrows, c->s_kmax.p);
-      if (Mq > seed)
-        k_kmax<SB><<<dim3(nblk(Mq - seed, Tn * KMAX_LPT), (cs + SB - 1) / SB), Tn, 0, st>>>(
-            seed, Mq, cs, niso, c->q_g.p, c->q_a.p, c->q_w.p, c->q_iso.p, c->s_rtemp.p, c->s_Z.p, c->d_iso_mass.p,
+      // the bulk is split over the ranks of a sharded run (every rank ran the seed, so every
+      // rank skips alike); the exact maximum is completed by the all-reduce below
+      const int64_t per = (Mq - seed + c->shard_world - 1) / c->shard_world;
+      const int64_t q0 = seed + per * c->shard_rank, q1 = q0 + per < Mq ? q0 + per : Mq;
+      if (q1 > q0)
+        k_kmax<SB><<<dim3(nblk(q1 - q0, Tn * KMAX_LPT), (cs + SB - 1) / SB), Tn, 0, st>>>(
+            q0, q1, cs, niso, c->q_g.p, c->q_a.p, c->q_w.p, c->q_iso.p, c->s_rtemp.p, c->s_Z.p, c->d_iso_mass.p,
             c->d_iso_row.p, permol, nrows, c->s_kmax.p);
       TB_LAUNCHED(c);
+      if (c->shard_world > 1)
+        TB_REQUIRE(c->exch(c->exch_user, TB_EXCH_KMAX, c->s_kmax.p, (int64_t)cs * nrows) == 0, TB_ERR_STATE,
+                   "exchange callback failed (strength maxima)");
       tb_timer_end(c, "kmax");
-      dim3 g3(nblk(G, Tn), (cs + SB - 1) / SB);
       tb_timer_begin(c, "strength");
       if (X > 0) {
         k_extra<<<dim3(nblk(X, Tn), cs), Tn, 0, st>>>(X, cs, c->x_line.p, c->m_wavn.p, c->m_elow.p, c->m_gf.p,
@@ -1020,24 +1055,35 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       k_logthr<<<nblk((int64_t)cs * niso, 128), 128, 0, st>>>(cs, niso, nrows, permol, ethresh, c->d_iso_row.p,
                                                               c->s_facz.p, c->s_kmax.p, c->s_lcz.p);
       TB_LAUNCHED(c);
+      for (int r = 0; r < (banded ? nrows : 1); r++) {
+        const int64_t p_off = banded ? pa[r] : 0, p_end = banded ? pb[r] : G;
+        if (p_end <= p_off) continue;
+        dim3 g3(nblk(p_end - p_off, Tn), (cs + SB - 1) / SB);
       k_strength<SB><<<g3, Tn, 0, st>>>(
-          G, cs, niso, c->o, fd_tile, fd_o, c->g_start.p, c->g_iso.p, c->g_orig.p, c->g_iown.p, c->g_wavn.p,
+          G, p_off, p_end, cs, niso, c->o, fd_tile, fd_o, c->g_start.p, c->g_iso.p, c->g_orig.p, c->g_iown.p, c->g_wavn.p,
           c->g_a0.p, c->g_gf.p, c->g_lg.p, c->s_rtemp.p, c->s_facz.p, c->s_lcz.p, c->s_ral.p, c->s_xterm.p, X,
           (float)c->dop_lmin, (float)c->dop_rstep, c->s_dens.p, nmol,
           c->d_iso_imol.p, c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ilor.p,
           c->d_aDop.p, c->nDop, c->d_ptab.p, c->nLor, ethresh, permol, nrows, c->s_kmax.p,
           c->s_rec.p, c->s_lastq.p, c->s_wtile.p, c->s_hasfb.p, ntiles);
+      }
+      if (c->shard_world > 1)
+        TB_REQUIRE(c->exch(c->exch_user, TB_EXCH_LASTQ, c->s_lastq.p, (int64_t)cs * niso) == 0, TB_ERR_STATE,
+                   "exchange callback failed (carried Doppler index)");
       tb_timer_end(c, "strength");
       k_fallback<<<nblk(cs * niso, 128), 128, 0, st>>>(
           cs, niso, c->s_lastq.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
           c->nDop, c->nLor, c->d_ptab.p, c->s_fb.p, c->s_fbpid.p, c->s_fbmax.p);
       c->launches += 3;
     }
-    k_reach<<<nblk((int64_t)cs * ntiles, 128), 128, 0, st>>>(cs, ntiles, c->o, c->s_wtile.p, c->s_hasfb.p,
+    k_reach<<<nblk((int64_t)cs * ntiles, 128), 128, 0, st>>>(cs, ntiles, c->o, utiles, c->s_wtile.p, c->s_hasfb.p,
                                                              c->s_fbmax.p, c->s_reach.p, c->s_reachP.p);
-    dim3 g4(ntiles, cs);
+    if (banded)    // bins outside the band come back as zero
+      TB_CUDA(cudaMemsetAsync(dst, 0, (size_t)cs * nout * nwn * sizeof(double), st));
+    dim3 g4(tile_hi - tile_lo, cs);
     tb_timer_begin(c, "accumulate");
-    k_accumulate<<<g4, ACC_TILE, 0, st>>>(nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, c->binstart.p,
+    if (tile_hi > tile_lo)
+    k_accumulate<<<g4, ACC_TILE, 0, st>>>(nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, tile_lo, c->binstart.p,
                                           c->substart.p, c->nsub, c->nsube, c->s_rec.p, c->s_fbpid.p, c->d_ptab.p,
                                           c->s_reach.p, c->s_reachP.p, c->d_pdata2.p, dst,
                                           c->s_nsamp.p + s0);

@@ -70,3 +70,99 @@ class ShardedTransit(api.Transit):
 
     def band_nwn(self):
         return self.ctx.nwn
+
+
+# ---------------------------------------------------------------------------------------------
+# Wavenumber-band sharding (BASELINE.json north_star: "the wavenumber range
+# is sharded across the 8 GPUs").  Every rank keeps the whole line index (the co-add runs of
+# extinction.c:449-462 depend on the whole list) but evaluates strengths only for the lines that can
+# reach its band and gathers only its own bins.  The two quantities of computemolext that are
+# global over the line list -- the strength maximum behind the threshold and the carried Doppler
+# index -- are completed by an exact all-reduce MAX each (tb_set_shard), so a banded run is
+# bit-identical to a single-GPU one.
+
+BAND_ALIGN = 128          # tb_set_shard: band ends are multiples of the accumulate tile
+
+
+def line_weights(prob):
+    """Lines per coarse bin: the balance weight of the band partition (the line sum's cost per bin
+    is lines x profile width, and the width profile is the same for every band)."""
+    wavn = 1.0 / (prob.wl * prob.wfct)
+    j = np.floor((wavn - prob.wn_i) / prob.wn_d).astype(np.int64)
+    j = j[(j >= 0) & (j < prob.nwn)]
+    return np.bincount(j, minlength=prob.nwn).astype(np.float64)
+
+
+def wavenumber_bands(weights, world: int, align: int = BAND_ALIGN):
+    """Contiguous bands [lo, hi) of the coarse grid, one per rank, balanced by cumulative weight,
+    ends on multiples of `align` (the last band ends at the grid end).  Bands may be empty when
+    there are fewer tiles than ranks."""
+    nwn = len(weights)
+    ntile = -(-nwn // align)
+    tw = np.add.reduceat(np.asarray(weights, float) + 1e-9, np.arange(0, nwn, align))
+    cum = np.concatenate([[0.0], np.cumsum(tw)])
+    cuts = [0]
+    for r in range(1, world):
+        t = int(np.searchsorted(cum, cum[-1] * r / world, side="left"))
+        t = min(max(t, cuts[-1]), ntile)
+        cuts.append(t)
+    cuts.append(ntile)
+    return [(min(cuts[r] * align, nwn), min(cuts[r + 1] * align, nwn)) for r in range(world)]
+
+
+def allreduce_max_(t, group=None):
+    """In-place all-reduce MAX (exact for float64 and int32 alike)."""
+    import torch.distributed as dist
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+    return t
+
+
+def _alias(ptr, n, typestr):
+    import torch
+
+    class _A:
+        __cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+    return torch.as_tensor(_A(), device="cuda")
+
+
+def nccl_exchange(group=None):
+    """The callback tb_set_shard wants, on torch.distributed: the device buffer is aliased as a CUDA
+    tensor and all-reduced in place on the current stream (the one given to tb_set_stream)."""
+    def exchange(what, ptr, count):
+        allreduce_max_(_alias(ptr, count, "<f8" if what == 0 else "<i4"), group)
+    return exchange
+
+
+def gather_bands(local, bands, rank: int, world: int, group=None):
+    """All-gather the band slices of a per-rank array [..., nwn] (only columns bands[rank] are valid on
+    each rank) into the full [..., nwn] on every rank.  Slices are padded to the widest band."""
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return local
+    lead = local.shape[:-1]
+    wmax = max(hi - lo for lo, hi in bands)
+    lo, hi = bands[rank]
+    buf = torch.zeros(*lead, wmax, dtype=local.dtype, device=local.device)
+    buf[..., :hi - lo] = local[..., lo:hi]
+    out = torch.empty(world, *lead, wmax, dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, buf.unsqueeze(0).contiguous(), group=group)
+    full = torch.empty_like(local)
+    for r, (a, b) in enumerate(bands):
+        full[..., a:b] = out[r][..., :b - a]
+    return full
+
+
+class BandShardedTransit(ShardedTransit):
+    """One spectrum computed by `world` ranks, each owning a wavenumber band."""
+
+    def transit_init(self, prob, **kw):
+        super().transit_init(prob, **kw)
+        self.bands = wavenumber_bands(line_weights(prob), self.world)
+        lo, hi = self.bands[self.rank]
+        self.ctx.set_shard(lo, hi, self.rank, self.world, nccl_exchange() if self.world > 1 else None)
+
+    def do_transit_gathered(self):
+        """Spectrum [nwn] on every rank as a CUDA tensor: own band computed here, the rest gathered."""
+        self.do_transit(None)
+        return gather_bands(self.device_spectrum_tensor(), self.bands, self.rank, self.world)
