@@ -429,6 +429,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="C2")
+    ap.add_argument("--natm", type=int, default=1024, help="C5: atmospheres in the retrieval batch")
+    ap.add_argument("--batch", type=int, default=32, help="C5: atmospheres per rank per step")
+    ap.add_argument("--block-layers", type=int, default=2, help="C3: layers (x 26 temperatures) per step")
     ap.add_argument("--verify", action="store_true",
                     help="--sharding bands: rank 0 also computes the spectrum unsharded and requires bit-identity")
     ap.add_argument("--sharding", default="atmospheres", choices=["atmospheres", "bands"],
@@ -442,6 +445,10 @@ def main():
     ap.add_argument("--ref-budget-s", type=float, default=150.0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "b200" and args.workload in ("C3", "C4", "C5"):
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_configs
+        return bench_configs.run(sys.modules[__name__], args)
     return run_reference(args) if args.impl == "reference" else run_ours(args)
 
 

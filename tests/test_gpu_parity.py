@@ -340,3 +340,80 @@ def test_band_shard_two_ranks_bit_identical_to_one():
         assert not out[r][:, other].any()            # bins outside the band come back as zero
     assert np.array_equal(e, e_ref)
     assert np.array_equal(cnt[0] + cnt[1], n_ref)
+
+
+# ------------------------------------------------------------------ C5 / C4 shapes
+
+def _oracle_from_grid(pr, grid, gtemp, gmol_rows):
+    """interpolmolext for every layer on the oracle (extinction.c:534-581)."""
+    L = O.lib()
+    g = O.c64(grid)
+    Nl, Nt, Nm, Nw = g.shape
+    e = np.zeros((pr.nrad, pr.nwn))
+    for r in range(pr.nrad):
+        dens = O.c64(pr.mol_d[gmol_rows, r])
+        rc = L.to_interpolmolext(O.p(g), Nt, Nm, Nw, O.p(O.c64(gtemp)), r, pr.t[r] * pr.t_fct, O.p(dens), O.p(e[r]))
+        assert rc == 0
+    return e
+
+
+def test_retrieval_batch_from_grid_vs_oracle():
+    """C5 shape, reduced: a grid built by the line-by-line path, then several perturbed T-P/abundance
+    profiles through interpolation + CIA + tau + modulation; every spectrum against the oracle
+    fed with the same grid, and the grid itself against the oracle's computemolext on a sample."""
+    import sys, os
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import bench_configs as BC
+    prob = workloads.make_problem("C2", scale=0.004, nlayers=16, wn_hi=3500.0, wnosamp=240)
+    c = setup_ctx(prob, nDop=24, nLor=24)
+    gtemp = np.arange(500.0, 1500.1, 100.0)
+    ziso = BC._ziso(prob, gtemp)
+    grid = c.opacity_build(gtemp, ziso, prob.mol_q, BC._mean_mass(prob), 0, prob.ethresh)
+    molID = c.line_molIDs()
+    rows = [list(prob.mol_ID).index(m) for m in molID]
+    # the grid against the oracle's line sum, two (layer, T) states
+    t = c.get_profiles()
+    vt = O.voigt_from_arrays(t["aDop"], t["aLor"], t["psize"], t["off"], t["data"])
+    pr0 = O.Problem(**vars(prob))
+    for (r, it) in ((0, 3), (11, 7)):
+        dens = api.AMU * prob.mol_q[:, r] * (prob.p[r] * prob.p_fct) / api.KB / gtemp[it] * prob.mol_mass
+        o = O.computemolext(pr0, vt, float(gtemp[it]), dens, ziso[:, it], prob.ethresh, permol=1, molID=molID)
+        assert relerr(grid[r, it], o) < EXT_RTOL
+    for seed in (11, 12, 13):
+        a = workloads.perturbed(prob, seed=seed, dT=150.0, dex=1.0)
+        c.set_atmosphere(a.rad, a.rad_fct, a.p, a.p_fct, a.t, a.t_fct, a.mol_d, a.iso_z)
+        out = c.spectrum(api.GEOM_TRANSIT, a.toomuch, a.ethresh, a.starrad, a.transp)
+        pr = O.Problem(**vars(a))
+        e0 = _oracle_from_grid(pr, grid, gtemp, rows)
+        assert relerr(c.get_extinction(), e0) < 1e-13
+        t0, last0, _ = O.tau(pr, e0, O.interpcs(pr), lazy=False)
+        tg, lastg = c.get_tau()
+        assert np.array_equal(lastg, last0)
+        assert relerr(out, O.modulation(pr, t0, last0)) < SPEC_RTOL
+    c.close()
+
+
+def test_high_resolution_eclipse_from_grid_vs_oracle():
+    """C4 shape, reduced: 20 001 samples at 0.01 cm-1, extinction from a resident synthetic grid, CIA,
+    eclipse tau, 5-angle intensity and flux against the oracle."""
+    import sys, os
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import bench_configs as BC
+    prob = BC.c4_problem(nwn=20001, nlayers=30)
+    temps = np.array([800.0, 1000.0, 1200.0, 1400.0, 1600.0, 1800.0])
+    grid = BC.c4_grid(prob, temps)
+    molID = np.array([prob.mol_ID[prob.species_names.index(s)] for s in ("H2O", "CH4")], np.int32)
+    tr = api.Transit(0)
+    tr.transit_init(prob, opacity=dict(molID=molID, temp=temps, press=prob.p * prob.p_fct, grid=grid))
+    out = tr.do_transit()
+    pr = O.Problem(**vars(prob))
+    rows = [list(prob.mol_ID).index(m) for m in molID]
+    e0 = _oracle_from_grid(pr, grid, temps, rows)
+    assert relerr(tr.ctx.get_extinction(), e0) < 1e-13
+    t0, last0, _ = O.tau(pr, e0, O.interpcs(pr), lazy=False)
+    tg, lastg = tr.ctx.get_tau()
+    assert np.array_equal(lastg, last0)
+    intens0, flux0 = O.intensity_flux(pr, t0, last0)
+    assert relerr(tr.ctx.get_intensity(), intens0) < SPEC_RTOL
+    assert relerr(out, flux0) < SPEC_RTOL
+    tr.free_memory()

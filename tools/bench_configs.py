@@ -1,0 +1,353 @@
+"""bench.py --workload C3 | C4 | C5: the other BASELINE.json configurations.
+
+The headline (and the only line the round-end driver reads) is C2 in bench.py itself; these are
+run by hand, their JSON lines are kept under profiles/.  Same timing rules: CUDA events on the
+launching stream, barrier + synchronize on both sides, max over ranks, L2 flushed between steps.
+
+  C3  opacity-grid build (calcopacity, opacity.c:281-427): an ExoMol-scale synthetic line list
+      (10^8 lines at --scale 1) x 26 temperatures x 100 layers.  A step = the grid rows of
+      --block-layers layers (x 26 T = states of the line sum, permol), delivered to HOST memory in
+      file order.  N > 1: wavenumber bands (tb_set_shard), strong scaling.
+  C4  high-resolution eclipse: 10^6 wavenumber samples, extinction interpolated from a resident
+      grid (interpolmolext), CIA, eclipse tau, 5-angle intensity, flux.  A step = one do_transit.
+  C5  BART-style retrieval: --natm perturbed T-P/abundance profiles through grid interpolation +
+      CIA + tau + modulation on the C2 grid (built here by the line-by-line path).  A step = one
+      batch of --batch atmospheres per rank; N > 1 shards the atmospheres (weak scaling).
+"""
+from __future__ import annotations
+
+import json
+import os
+import time
+
+import numpy as np
+
+GRID_TEMPS = np.arange(500.0, 3000.1, 100.0)          # tlow 500 thigh 3000 tempdelt 100: 26 T
+
+
+def _ziso(prob, temps):
+    from transit_b200 import workloads
+    iso_mol, iso_k = [], []
+    for db in prob.dbs:
+        for kk in range(len(db.iso_names)):
+            iso_mol.append(db.molecule); iso_k.append(kk)
+    return np.stack([workloads.partition_function(iso_mol[i], iso_k[i], temps) for i in range(prob.niso)])
+
+
+def _mean_mass(prob):
+    return (prob.mol_q * prob.mol_mass[:, None]).sum(0)
+
+
+def _dist(bench, args):
+    import torch
+    import torch.distributed as dist
+    rank, local_rank, world = bench.dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the B200 path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO"):
+            os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    return torch, dist, rank, local_rank, world
+
+
+class _Timer:
+    """K timed steps: L2 flush, barrier + synchronize, CUDA events on the launching stream."""
+
+    def __init__(self, torch, dist, world, stream):
+        self.torch, self.dist, self.world, self.stream = torch, dist, world, stream
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        self.e0, self.e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def run(self, step, steps, warmup):
+        for i in range(warmup):
+            step(i)
+        ms = []
+        for i in range(steps):
+            self.flush.zero_()
+            self.barrier()
+            self.e0.record(self.stream)
+            step(warmup + i)
+            self.e1.record(self.stream)
+            self.torch.cuda.synchronize()
+            ms.append(self.e0.elapsed_time(self.e1))
+        self.barrier()
+        return float(np.sum(ms))
+
+    def reduce(self, vals):
+        t = self.torch.tensor(vals, dtype=self.torch.float64, device="cuda")
+        if self.world > 1:
+            mx = t.clone(); self.dist.all_reduce(mx, op=self.dist.ReduceOp.MAX)
+            sm = t.clone(); self.dist.all_reduce(sm, op=self.dist.ReduceOp.SUM)
+            return mx.tolist(), sm.tolist()
+        return t.tolist(), t.tolist()
+
+
+def run_c5(bench, args):
+    """1 024 atmospheres (default) through opacity interpolation + CIA + tau + modulation."""
+    from transit_b200 import api, workloads, sharding
+    torch, dist, rank, local_rank, world = _dist(bench, args)
+    prob = workloads.make_problem("C2", scale=args.scale)
+    tr = sharding.ShardedTransit(local_rank, rank, world)
+    stream = torch.cuda.current_stream()
+    tr.ctx.set_stream(stream.cuda_stream)
+    t0 = time.perf_counter()
+    tr.transit_init(prob)                                # line-by-line set-up, used once: to build the grid
+    grid = tr.ctx.opacity_build(GRID_TEMPS, _ziso(prob, GRID_TEMPS), prob.mol_q, _mean_mass(prob), 0, prob.ethresh)
+    tr.ctx.sync()
+    build_s = time.perf_counter() - t0
+    grid_bytes = grid.nbytes
+    del grid                                             # the resident copy serves every atmosphere
+    mine = list(sharding.atmosphere_shard(args.natm, rank, world))
+    batch = min(args.batch, max(1, len(mine)))
+    atms = [workloads.perturbed(prob, seed=5000 + i, dT=150.0, dex=1.0) for i in mine[:batch * 2]]
+    out = np.zeros((batch, prob.nwn))
+    kms = {}
+
+    def step(i):
+        for b in range(batch):
+            a = atms[(i * batch + b) % len(atms)]
+            tr.set_atmosphere(a)                          # H2D: T, p, radii, densities, partition functions
+            tr.do_transit(out[b])                         # D2H: the spectrum
+        for nm in ("interp", "cia", "tau", "modulation"):
+            try:
+                kms.setdefault(nm, []).append(tr.ctx.kernel_ms(nm))
+            except api.TransitError:
+                pass
+
+    tm = _Timer(torch, dist, world, stream)
+    sampler = bench.ClockSampler(local_rank)
+    sampler.start()
+    l0 = tr.ctx.launch_count()
+    dev_ms = tm.run(step, args.steps, args.warmup)
+    launches = tr.ctx.launch_count() - l0
+    clocks = sampler.stop()
+    assert np.isfinite(out).all() and (out > 0).all()
+    tm.barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        step(i)
+    tm.barrier()
+    e2e_s = time.perf_counter() - t0
+    (dev_ms, e2e_s), (_, _) = tm.reduce([dev_ms, e2e_s])
+    if rank == 0:
+        hbm_peak, src = bench.measured_peaks()
+        nspec = world * batch * args.steps
+        interp_ms = float(np.mean(kms["interp"]))
+        nm = len(prob.cfg["molecules"])
+        ibytes = (2 * nm * 8 + 8.0) * prob.nrad * prob.nwn
+        print(json.dumps({
+            "metric": "spectra/s", "value": nspec / (dev_ms * 1e-3), "unit": "spectra/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C5: BART-style retrieval, perturbed T-P/abundance profiles through opacity-grid "
+                                   "interpolation + CIA + tau + modulation (C2 grid)", "natm": args.natm,
+                       "batch_per_rank_per_step": batch, "sharding": f"atmospheres x{world}", "nwn": int(prob.nwn),
+                       "layers": int(prob.nrad), "grid": [int(prob.nrad), len(GRID_TEMPS), nm, int(prob.nwn)],
+                       "grid_gb": grid_bytes / 1e9, "grid_build_s": build_s, "l2": "flushed between steps"},
+            "e2e": {"value": nspec / e2e_s, "unit": "spectra/s",
+                    "h2d_bytes_per_step": 8 * prob.nrad * (3 + prob.nmol + prob.niso) * batch * world,
+                    "d2h_bytes_per_step": 8 * prob.nwn * batch * world},
+            "gpu_launches": launches * world,
+            "kernel_ms": {k: float(np.mean(v)) for k, v in kms.items()},
+            "roofline": {"kernel": "k_grid_interp", "bound": "hbm", "achieved": ibytes / (interp_ms * 1e-3) / 1e9,
+                         "peak": hbm_peak, "unit": "GB/s", "frac": ibytes / (interp_ms * 1e-3) / 1e9 / hbm_peak,
+                         "traffic": None, "peak_source": src, "ms": interp_ms, "algorithmic_bytes": ibytes},
+            "clocks": clocks}))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def c4_problem(nwn=1_000_000, nlayers=100):
+    """C4 static problem: the C1/eclipse atmosphere shape on a 10^6-sample grid; extinction comes from a
+    grid, so there is no line list."""
+    from transit_b200 import workloads
+    cfg = dict(workloads.CONFIGS["C1"])
+    cfg.update(wn_lo=2000.0, wn_hi=2000.0 + (nwn - 1) * 0.01, wndelt=0.01, wnosamp=120, nlayers=nlayers, nlines=0,
+               molecules={"H2O": (1, 0.5), "CH4": (1, 0.5)},
+               species={"H2": 0.85, "He": 0.149, "H2O": 5e-4, "CH4": 4e-4}, cia=[("H2", "H2"), ("H2", "He")],
+               seed=1004, toomuch=10.0)
+    workloads.CONFIGS["C4"] = cfg
+    return workloads.make_problem("C4")
+
+
+def c4_grid(prob, temps, nm=2):
+    """Synthetic opacity grid o[layer][T][molecule][wn] (cm2/g): smooth band structure, rising with T."""
+    w = prob.wn_i + np.arange(prob.nwn) * prob.wn_d
+    base = [1e-1 * np.exp(-((w - 3700.0) / 600.0) ** 2) * (1.2 + np.sin(w * 7.0)) + 1e-4,
+            4e-2 * np.exp(-((w - 3000.0) / 400.0) ** 2) * (1.2 + np.cos(w * 11.0)) + 5e-5][:nm]
+    grid = np.empty((prob.nrad, len(temps), nm, prob.nwn))
+    for r in range(prob.nrad):
+        for t, T in enumerate(temps):
+            for m in range(nm):
+                grid[r, t, m] = base[m] * (T / 1000.0) ** 1.5 * (1.0 + 0.002 * r)
+    return grid
+
+
+def run_c4(bench, args):
+    from transit_b200 import api, sharding
+    torch, dist, rank, local_rank, world = _dist(bench, args)
+    assert world == 1, "C4 is a single-GPU line here (N independent replicas otherwise)"
+    nwn = max(1000, int(1_000_000 * args.scale))
+    prob = c4_problem(nwn)
+    temps = np.array([800.0, 1000.0, 1200.0, 1400.0, 1600.0, 1800.0])
+    grid = c4_grid(prob, temps)
+    tr = sharding.ShardedTransit(local_rank, rank, world)
+    stream = torch.cuda.current_stream()
+    tr.ctx.set_stream(stream.cuda_stream)
+    molID = np.array([prob.mol_ID[prob.species_names.index(s)] for s in ("H2O", "CH4")], np.int32)
+    tr.transit_init(prob, opacity=dict(molID=molID, temp=temps, press=prob.p * prob.p_fct, grid=grid))
+    grid_gb = grid.nbytes / 1e9
+    del grid
+    out = np.zeros(prob.nwn)
+    kms = {}
+
+    def step(i):
+        tr.do_transit(out)
+        for nm in ("interp", "cia", "tau", "intensity"):
+            try:
+                kms.setdefault(nm, []).append(tr.ctx.kernel_ms(nm))
+            except api.TransitError:
+                pass
+
+    tm = _Timer(torch, dist, world, stream)
+    sampler = bench.ClockSampler(local_rank)
+    sampler.start()
+    l0 = tr.ctx.launch_count()
+    dev_ms = tm.run(step, args.steps, args.warmup)
+    launches = tr.ctx.launch_count() - l0
+    clocks = sampler.stop()
+    assert np.isfinite(out).all() and (out > 0).all()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        tr.set_atmosphere(prob)
+        step(i)
+    tm.barrier()
+    e2e_s = time.perf_counter() - t0
+    hbm_peak, src = bench.measured_peaks()
+    nang, nm = len(prob.angles), 2
+    # algorithmic bytes of one step: interpolation (2 planes per molecule in, e out), tau (e and e_cs in,
+    # t out), intensity (t in once per angle, one intensity plane out per angle), CIA (e_cs out)
+    ab = prob.nrad * prob.nwn * 8.0 * ((2 * nm + 1) + 3 + 1 + nang) + prob.nwn * 8.0 * (nang + 1)
+    print(json.dumps({
+        "metric": "spectra/s", "value": args.steps / (dev_ms * 1e-3), "unit": "spectra/s", "n_gpus": 1,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "C4: high-resolution eclipse, extinction interpolated from a resident opacity grid + CIA, "
+                               "eclipse tau, multi-angle intensity, flux", "nwn": int(prob.nwn), "layers": int(prob.nrad),
+                   "angles": [float(a) for a in prob.angles], "grid": [int(prob.nrad), len(temps), nm, int(prob.nwn)],
+                   "grid_gb": grid_gb, "l2": "flushed between steps"},
+        "samples_per_s": prob.nwn * args.steps / (dev_ms * 1e-3),
+        "e2e": {"value": args.steps / e2e_s, "unit": "spectra/s",
+                "h2d_bytes_per_step": 8 * prob.nrad * (3 + prob.nmol + prob.niso), "d2h_bytes_per_step": 8 * prob.nwn},
+        "gpu_launches": launches, "kernel_ms": {k: float(np.mean(v)) for k, v in kms.items()},
+        "roofline": {"kernel": "whole step (interp + CIA + tau + intensity, all HBM streams)", "bound": "hbm",
+                     "achieved": ab / (dev_ms / args.steps * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": ab / (dev_ms / args.steps * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": src,
+                     "algorithmic_bytes": ab},
+        "clocks": clocks}))
+    return 0
+
+
+def c3_problem(scale=1.0):
+    """C3 static problem: the C2 species on an ExoMol-scale line list (10^8 lines at scale 1: flat in
+    wavenumber, steep gf distribution)."""
+    from transit_b200 import workloads
+    cfg = dict(workloads.CONFIGS["C2"])
+    cfg.update(nlines=100_000_000, seed=1003)
+    workloads.CONFIGS["C3"] = cfg
+    return workloads.make_problem("C3", scale=scale)
+
+
+def run_c3(bench, args):
+    """Opacity-grid build: states (layer, T) of the permol line sum, rows delivered to host memory."""
+    from transit_b200 import api, sharding
+    torch, dist, rank, local_rank, world = _dist(bench, args)
+    t0 = time.perf_counter()
+    prob = c3_problem(args.scale)
+    gen_s = time.perf_counter() - t0
+    tr = sharding.ShardedTransit(local_rank, rank, world)
+    stream = torch.cuda.current_stream()
+    tr.ctx.set_stream(stream.cuda_stream)
+    t0 = time.perf_counter()
+    tr.transit_init(prob)
+    tr.ctx.sync()
+    init_s = time.perf_counter() - t0
+    bands = sharding.wavenumber_bands(sharding.line_weights(prob), world)
+    if world > 1:
+        tr.ctx.set_shard(bands[rank][0], bands[rank][1], rank, world, sharding.nccl_exchange())
+    ziso = _ziso(prob, GRID_TEMPS)
+    nt, nl = len(GRID_TEMPS), args.block_layers
+    ns = nt * nl
+
+    def states(block):
+        T, D, Z = [], [], []
+        for r in [(block * nl + k) % prob.nrad for k in range(nl)]:
+            for t, temp in enumerate(GRID_TEMPS):
+                T.append(temp)
+                rho = api.AMU * prob.mol_q[:, r] * (prob.p[r] * prob.p_fct) / api.KB / temp
+                D.append(rho * prob.mol_mass)               # opacity.c:387-403, stateeqnford by number
+                Z.append(ziso[:, t])
+        return np.array(T), np.array(D), np.array(Z)
+
+    kms, samples, rows = {}, [0], [None]
+
+    def step(i):
+        T, D, Z = states(i)
+        rows[0] = tr.ctx.molext_states(T, D, Z, prob.ethresh, permol=1)     # [ns][mol][nwn] on the host
+        samples[0] = int(tr.ctx.sample_counts(ns).sum())
+        for nm in ("kmax", "strength", "accumulate", "molext"):
+            kms.setdefault(nm, []).append(tr.ctx.kernel_ms(nm))
+
+    tm = _Timer(torch, dist, world, stream)
+    sampler = bench.ClockSampler(local_rank)
+    sampler.start()
+    l0 = tr.ctx.launch_count()
+    dev_ms = tm.run(step, args.steps, args.warmup)
+    launches = tr.ctx.launch_count() - l0
+    clocks = sampler.stop()
+    lo, hi = bands[rank]
+    assert np.isfinite(rows[0]).all() and rows[0][..., lo:hi].max() > 0
+    (dev_ms,), (_,) = tm.reduce([dev_ms])
+    _, (nsamp, mol_ms, acc_ms) = tm.reduce([float(samples[0]), float(np.mean(kms["molext"])),
+                                            float(np.mean(kms["accumulate"]))])
+    if rank == 0:
+        hbm_peak, src = bench.measured_peaks()
+        nlines = len(prob.wl)
+        step_s = dev_ms / args.steps * 1e-3
+        print(json.dumps({
+            "metric": "line-sum Glines.samples/s", "value": nsamp / step_s / 1e9, "unit": "G line-samples/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
+            "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C3: opacity-grid build (calcopacity), ExoMol-scale synthetic line list x 26 temperatures "
+                                   "x layers, permol rows delivered to host memory", "lines": int(nlines),
+                       "states_per_step": ns, "block_layers": nl, "temperatures": nt, "nwn": int(prob.nwn),
+                       "wnosamp": int(prob.wnosamp), "line_molecules": len(prob.cfg["molecules"]),
+                       "sharding": f"wavenumber bands x{world}" if world > 1 else "none", "bands": bands,
+                       "l2": "flushed between steps", "line_list_gen_s": gen_s, "init_s": init_s},
+            "line_states_per_s": nlines * ns / step_s, "states_per_s": ns / step_s,
+            "full_grid_s_extrapolated": step_s * prob.nrad / nl,
+            "e2e": {"value": nsamp / step_s / 1e9, "unit": "G line-samples/s",
+                    "h2d_bytes_per_step": 8 * ns * (1 + prob.nmol + prob.niso) * world,
+                    "d2h_bytes_per_step": 8 * ns * len(prob.cfg["molecules"]) * int(prob.nwn) * world,
+                    "note": "the step already ends with the grid rows in host memory (D2H inside the timed region)"},
+            "gpu_launches": int(launches * world),
+            "kernel_ms": {k: float(np.mean(v)) for k, v in kms.items()},
+            "clocks": clocks}))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def run(bench, args):
+    return {"C3": run_c3, "C4": run_c4, "C5": run_c5}[args.workload](bench, args)

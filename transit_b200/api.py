@@ -21,6 +21,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.path.join(ROOT, "transit_b200", "libtransit_b200.so")
 GEOM_TRANSIT, GEOM_ECLIPSE = 0, 1
+AMU, KB = 1.66053886e-24, 1.380658e-16          # constants_tr.h:21,25 (cgs)
 
 f64p = C.POINTER(C.c_double)
 f32p = C.POINTER(C.c_float)

@@ -225,7 +225,8 @@ struct tb_ctx {
   int64_t gNmol = 0, gNtemp = 0, gNlayer = 0, gNwave = 0;
   std::vector<double> gtemp, gpress;
   std::vector<int> gmolID, gmol_idx;
-  DevBuf<double> d_grid;
+  DevBuf<double> d_grid, i_rho;
+  DevBuf<uint8_t> i_stage;    // per-layer interpolation brackets (tb_opacity.cu)
 
   // ---- CIA
   std::vector<CiaTable *> cia;

@@ -941,10 +941,10 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   const int ntiles = (int)((nwn + ACC_TILE - 1) / ACC_TILE);
   c->last_ns = ns;
   c->last_permol = permol;
-  // chunk the states so the per-(state, group) scratch stays below ~12 GB
+  // chunk the states so the per-(state, group) scratch stays below 48 GB of the 180 GB
   int chunk = ns;
   const size_t per_state = (size_t)G * 16 + (size_t)(M - G) * 8 + (size_t)nout * nwn * 8 + 64;
-  const size_t budget = (size_t)12 << 30;
+  const size_t budget = (size_t)48 << 30;
   if (per_state * chunk > budget) chunk = (int)(budget / per_state);
   if (chunk < 1) chunk = 1;
   if (chunk > 65535) chunk = 65535;            // gridDim.y

@@ -81,20 +81,20 @@ int tb_interp_run(tb_ctx *c) {
     L[r].it = it; L[r].t = T; L[r].tlo = c->gtemp[it]; L[r].thi = c->gtemp[it + 1];
     for (int m = 0; m < Nm; m++) rho[(size_t)m * nrad + r] = c->dens[(size_t)c->gmol_idx[m] * nrad + r];
   }
-  DevBuf<InterpLayer> dL;
-  DevBuf<double> drho;
-  TB_TRY(dL.ensure(nrad)); TB_TRY(drho.ensure(rho.size()));
+  // staging buffers live in the context: a retrieval calls this once per atmosphere
+  TB_TRY(c->i_stage.ensure(nrad * sizeof(InterpLayer))); TB_TRY(c->i_rho.ensure(rho.size()));
   TB_TRY(c->d_e.ensure((size_t)nrad * c->nwn));
-  TB_CUDA(cudaMemcpyAsync(dL.p, L.data(), nrad * sizeof(InterpLayer), cudaMemcpyHostToDevice, st));
-  TB_CUDA(cudaMemcpyAsync(drho.p, rho.data(), rho.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+  InterpLayer *dLp = reinterpret_cast<InterpLayer *>(c->i_stage.p);
+  double *drhop = c->i_rho.p;
+  TB_CUDA(cudaMemcpyAsync(dLp, L.data(), nrad * sizeof(InterpLayer), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(drhop, rho.data(), rho.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaStreamSynchronize(st));       // L and rho are stack/heap locals of this call
   dim3 g(nblk(c->nwn, 256), nrad);
   tb_timer_begin(c, "interp");
-  k_grid_interp<<<g, 256, 0, st>>>(c->nwn, nrad, Nt, Nm, c->d_grid.p, dL.p, drho.p, c->d_e.p);
+  k_grid_interp<<<g, 256, 0, st>>>(c->nwn, nrad, Nt, Nm, c->d_grid.p, dLp, drhop, c->d_e.p);
   tb_timer_end(c, "interp");
   TB_LAUNCHED(c);
   TB_CUDA(cudaGetLastError());
-  TB_CUDA(cudaStreamSynchronize(st));
-  dL.release(); drho.release();
   c->have_e = true;
   return TB_OK;
 }
