@@ -445,102 +445,18 @@ __device__ __forceinline__ double tb_parab(double dx, double x0, double xr, doub
   return xr * xr * a + xr * b + cc;
 }
 
-// One thread per wavenumber; its extinction column er[layer] lives in shared memory laid out
-// [layer][thread] (conflict-free).  Rays are walked top-down with the reference's early exit.
-__global__ void k_tau(TauPar P, const double *__restrict__ e, const double *__restrict__ ecs,
-                      const double *__restrict__ press, const double *__restrict__ temp,
-                      const double *__restrict__ aux, const double *__restrict__ mol_d,
-                      const double *__restrict__ mol_pol, const double *__restrict__ mol_mass, int nmol,
-                      const int32_t *__restrict__ meta, const double *__restrict__ par,
-                      const double *__restrict__ coef, double *__restrict__ tau,
-                      int32_t *__restrict__ last) {
-  extern __shared__ double sm[];
-  const int tid = threadIdx.x, nt = blockDim.x;
-  const int64_t w = blockIdx.x * (int64_t)nt + tid;
-  if (w >= P.nwn) return;
-  double *er = sm + tid;
-  const int nrad = P.nrad;
-  const double wn = P.wn_fct * __dadd_rn(P.wn_i, __dmul_rn((double)w, P.wn_d));
-  // scattering (extinction.c:586-624) and clouds (extinction.c:629-693), per layer
-  double kBP = 0, kFH = 0, refw = 1;
-  int ctop = -1, cbot = -1;   // cloud occupies layers (cbot, ctop]
-  if (P.cl_flag && P.cl_ext != 0) {
-    const double top = pow(10.0, P.cl_top), bot = pow(10.0, P.cl_bot);
-    int i = nrad - 1;
-    for (; i >= 0; i--) if (press[i] >= top) break;
-    ctop = i;
-    for (; i >= 0; i--) if (press[i] >= bot) break;
-    cbot = i;
-    const double x = 2 * TB_PI * P.cl_r * wn;
-    refw = pow(P.cl_refwn, P.cl_gamma);
-    kBP = P.cl_ext * pow(wn, P.cl_gamma);
-    kFH = P.cl_ext / (P.cl_Q * pow(x, -1 * P.cl_gamma) + pow(x, 0.2));
-  }
-  const double wn4 = pow(wn, 4.0);
-  for (int r = 0; r < nrad; r++) {
-    double es = 0, ec = 0;
-    if (P.sc_flag == 1) es = P.sc_fac * press[r] / temp[r] * wn4;
-    else if (P.sc_flag == 2) {
-      for (int j = 0; j < nmol; j++)
-        es += TB_PI * 8e-32 / 3. * pow(mol_pol[j], 2.0) * pow(2. * TB_PI * wn * TB_MICRON, 4.0) *
-              mol_d[(size_t)j * nrad + r] / mol_mass[j] * TB_NAVOGADRO;
-    }
-    if (r <= ctop && r > cbot) {
-      const double md = aux[nrad + r];
-      switch (P.cl_flag) {
-        case 1: ec = P.cl_ext; break;
-        case 2: ec = P.cl_ext * md; break;
-        case 3: ec = kBP * md; break;
-        case 4: ec = kFH * md; break;
-        case 5: ec = aux[r] * kBP * P.cl_sig / refw * md; break;
-      }
-    }
-    // tau.c:231-232, same left-to-right sum
-    er[r * nt] = e[(size_t)r * P.nwn + w] + es + ec + ecs[(size_t)r * P.nwn + w];
-  }
-  int lst = P.nh - 1;
-  for (int ri = 0; ri < P.nh; ri++) {
-    const int32_t *mt = meta + ri * 4;
-    const int mode = mt[2];
-    double t = 0.0;
-    if (mode > 0) {
-      const int rs = mt[0], n = mt[1], np = mt[3];
-      const double *pp = par + ri * 4;
-      const double *cf = coef + (size_t)ri * P.stride;
-      double y0, ya, yb;   // sliding window over the ray's samples
-      if (mode == 2) {
-        y0 = tb_parab(pp[0], pp[1], pp[2], er[(rs - 1) * nt], er[rs * nt], er[(rs + 1) * nt]);
-        yb = er[(rs + 1) * nt];
-        ya = (y0 + yb) / 2.0;
-        t = (y0 * cf[0] + ya * cf[1] + yb * cf[2]) * cf[3] / 6.0;   // three points: one Simpson pair
-      } else {
-        y0 = tb_parab(pp[0], pp[1], pp[2], er[rs * nt], er[(rs + 1) * nt], er[(rs + 2) * nt]);
-        if (P.eclipse) er[rs * nt] = y0;          // eclipse.c:66 never restores it
-        const int even = (n % 2 == 0);
-        double res = 0.0;
-        for (int i = 0; i < np; i++) {
-          const int j = 2 * i + even;
-          const double a0 = (j == 0) ? y0 : er[(rs + j) * nt];
-          res += (a0 * cf[4 * i] + er[(rs + j + 1) * nt] * cf[4 * i + 1] +
-                  er[(rs + j + 2) * nt] * cf[4 * i + 2]) * cf[4 * i + 3];
-        }
-        t = res / 6.0;
-        if (even) t += pp[3] * (y0 + er[(rs + 1) * nt]) / 2;
-      }
-      t = P.rfct * (P.eclipse ? t : 2 * t);
-    }
-    tau[(size_t)ri * P.nwn + w] = t;
-    if (t > P.toomuch) { lst = ri; break; }       // tau.c:277-287
-  }
-  last[w] = lst;
-}
-
-// Transit geometry, the production layout: a block owns 32 wavenumbers (one per lane) and
+// The production layout, both geometries: a block owns 32 wavenumbers (one per lane) and
 // TAU_NW warps share the rays (ray ri -> warp ri % TAU_NW), all reading the block's extinction
 // columns er[layer][lane] from shared memory.  totaltau1 restores what it modifies
-// (slantpath.c:98-99), so rays are independent; the reference's early exit (tau.c:277-287)
-// becomes: each warp stops a lane at its first ray above `toomuch`, the block takes the minimum
-// over warps as last[w] and clears what was written beyond it (the reference leaves zeros there).
+// (slantpath.c:98-99), so transit rays are independent.  eclipsetau does NOT restore the
+// extrapolated value it stores at its starting layer (eclipse.c:62-66): ray ri leaves
+// er[rs] = parabola(er[rs], er[rs+1], er[rs+2]) behind for the rays below it.  That chain is
+// O(layers) per wavenumber and touches each layer once, top down, so warp 0 runs it first
+// (the two-point ray next to the top, which reads the not-yet-modified layer below it, is
+// evaluated inside the chain); after that every ray's Simpson sum reads only final values and
+// the rays are independent again.  The reference's early exit (tau.c:277-287) becomes: each warp
+// stops a lane at its first ray above `toomuch`, the block takes the minimum over warps as
+// last[w] and clears what was written beyond it (the reference leaves zeros there).
 #define TAU_NW 8
 __global__ void __launch_bounds__(32 * TAU_NW)
 k_tau_transit(TauPar P, const double *__restrict__ e, const double *__restrict__ ecs,
@@ -596,24 +512,74 @@ k_tau_transit(TauPar P, const double *__restrict__ e, const double *__restrict__
     }
   }
   __syncthreads();
+  __shared__ double sh_t2[32];
+  __shared__ int sh_ri2;
+  if (threadIdx.x == 0) sh_ri2 = -1;
+  if (P.eclipse) {
+    __syncthreads();
+    if (warp == 0 && inb) {
+      double *ew = sm + lane;
+      for (int ri = 0; ri < P.nh; ri++) {
+        const int32_t *mt = meta + ri * 4;
+        const int mode = mt[2], rs = mt[0];
+        const double *pp = par + ri * 4;
+        if (mode == 1) {
+          ew[rs * 32] = tb_parab(pp[0], pp[1], pp[2], ew[rs * 32], ew[(rs + 1) * 32], ew[(rs + 2) * 32]);
+        } else if (mode == 2) {
+          const double *cf = coef + (size_t)ri * P.stride;
+          const double y0 = tb_parab(pp[0], pp[1], pp[2], ew[(rs - 1) * 32], ew[rs * 32], ew[(rs + 1) * 32]);
+          const double yb = ew[(rs + 1) * 32];
+          const double ya = (y0 + yb) / 2.0;
+          sh_t2[lane] = (y0 * cf[0] + ya * cf[1] + yb * cf[2]) * cf[3] / 6.0;
+          if (lane == 0) sh_ri2 = ri;
+        }
+      }
+    }
+    __syncthreads();
+  }
   const double *er = sm + lane;
   int myfirst = P.nh;                       // first ray of this warp above toomuch (none yet)
-  if (inb) {
-    for (int ri = warp; ri < P.nh; ri += TAU_NW) {
-      const int32_t *mt = meta + ri * 4;
-      const int mode = mt[2];
+  // Simpson coefficients of a ray: one row of `coef`, the same for every wavenumber.  Read pair by
+  // pair from global memory they cost an L2 round trip per pair (the rows of all rays do not fit
+  // beside 25 KB of extinction columns in L1); instead the warp fetches the whole row of its NEXT ray
+  // coalesced into registers while it integrates the current one out of shared memory.
+  double *cw = sm + (size_t)nrad * 32 + (size_t)warp * P.stride;
+  constexpr int CFR = 10;                   // registers per lane for one row (stride <= 320)
+  double pre[CFR];
+  auto fetch = [&](int ri) {
+    if (ri < P.nh) {
+      const double *cf = coef + (size_t)ri * P.stride;
+      const int n4 = 4 * meta[ri * 4 + 3];
+#pragma unroll
+      for (int k = 0; k < CFR; k++) pre[k] = (lane + 32 * k < n4) ? cf[lane + 32 * k] : 0.0;
+    }
+  };
+  fetch(warp);
+  for (int ri = warp; ri < P.nh; ri += TAU_NW) {          // whole warp: lanes outside the grid idle
+    const int32_t *mt = meta + ri * 4;
+    const int mode = mt[2];
+    const int n4 = 4 * mt[3];
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < CFR; k++) if (lane + 32 * k < n4) cw[lane + 32 * k] = pre[k];
+    __syncwarp();
+    fetch(ri + TAU_NW);
+    if (inb && myfirst == P.nh) {
       double t = 0.0;
       if (mode > 0) {
         const int rs = mt[0], n = mt[1], np = mt[3];
         const double *pp = par + ri * 4;
-        const double *cf = coef + (size_t)ri * P.stride;
-        if (mode == 2) {
+        const double *cf = cw;
+        if (mode == 2 && P.eclipse) {
+          t = sh_t2[lane];                                   // evaluated inside the chain (see above)
+        } else if (mode == 2) {
           const double y0 = tb_parab(pp[0], pp[1], pp[2], er[(rs - 1) * 32], er[rs * 32], er[(rs + 1) * 32]);
           const double yb = er[(rs + 1) * 32];
           const double ya = (y0 + yb) / 2.0;
           t = (y0 * cf[0] + ya * cf[1] + yb * cf[2]) * cf[3] / 6.0;
         } else {
-          const double y0 = tb_parab(pp[0], pp[1], pp[2], er[rs * 32], er[(rs + 1) * 32], er[(rs + 2) * 32]);
+          const double y0 = P.eclipse ? er[rs * 32]          // the chain left it there
+                                      : tb_parab(pp[0], pp[1], pp[2], er[rs * 32], er[(rs + 1) * 32], er[(rs + 2) * 32]);
           const int even = (n % 2 == 0);
           double res = 0.0;
           for (int i = 0; i < np; i++) {
@@ -625,11 +591,14 @@ k_tau_transit(TauPar P, const double *__restrict__ e, const double *__restrict__
           t = res / 6.0;
           if (even) t += pp[3] * (y0 + er[(rs + 1) * 32]) / 2;
         }
-        t = P.rfct * (2 * t);
+        t = P.rfct * (P.eclipse ? t : 2 * t);
       }
       tau[(size_t)ri * P.nwn + w] = t;
-      if (t > P.toomuch) { myfirst = ri; break; }       // tau.c:277-287
+      if (t > P.toomuch) myfirst = ri;                   // tau.c:277-287: this lane is done
     }
+    if (__all_sync(0xffffffffu, !inb || myfirst != P.nh)) break;
+  }
+  if (inb) {
     atomicMin(&sh_last[lane], myfirst);
   }
   __syncthreads();
@@ -689,16 +658,9 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
   P.cl_ext = c->cl_ext; P.cl_top = c->cl_top; P.cl_bot = c->cl_bot; P.cl_gamma = c->cl_gamma;
   P.cl_Q = c->cl_Q; P.cl_r = c->cl_r; P.cl_sig = c->cl_sig; P.cl_refwn = c->cl_refwn;
   tb_timer_begin(c, "tau");
-  if (geometry == TB_GEOM_ECLIPSE) {
-    const int TPB = 64;
-    const size_t shm = (size_t)nrad * TPB * sizeof(double);
-    TB_REQUIRE(shm <= 200 * 1024, TB_ERR_ARG, "too many layers (%d) for the tau kernel's shared memory", nrad);
-    TB_CUDA(cudaFuncSetAttribute(k_tau, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
-    k_tau<<<nblk(nwn, TPB), TPB, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p, c->d_dens.p,
-                                            c->d_mol_pol.p, c->d_mol_mass.p, c->nmol, c->r_meta.p, c->r_par.p,
-                                            c->r_coef.p, c->d_tau.p, c->d_last.p);
-  } else {
-    const size_t shm = (size_t)nrad * 32 * sizeof(double);
+  {
+    const size_t shm = ((size_t)nrad * 32 + (size_t)TAU_NW * stride) * sizeof(double);
+    TB_REQUIRE(stride <= 320, TB_ERR_ARG, "too many layers (%d) for the tau kernel's coefficient registers", nrad);
     TB_REQUIRE(shm <= 200 * 1024, TB_ERR_ARG, "too many layers (%d) for the tau kernel's shared memory", nrad);
     TB_CUDA(cudaFuncSetAttribute(k_tau_transit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
     k_tau_transit<<<nblk(nwn, 32), 32 * TAU_NW, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p,
