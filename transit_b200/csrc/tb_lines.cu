@@ -970,7 +970,8 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
     d_out = c->s_out.p;
   }
   const int Tn = 256;
-  constexpr int SB = 4;
+  constexpr int SB = 4;      // states per block of k_kmax
+  constexpr int SBS = 8;     // states per block of k_strength (group records are read once per SBS states)
   auto fastdiv = [](int64_t d) {
     FastDiv f;
     f.d = (int)d;
@@ -1058,8 +1059,8 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       for (int r = 0; r < (banded ? nrows : 1); r++) {
         const int64_t p_off = banded ? pa[r] : 0, p_end = banded ? pb[r] : G;
         if (p_end <= p_off) continue;
-        dim3 g3(nblk(p_end - p_off, Tn), (cs + SB - 1) / SB);
-      k_strength<SB><<<g3, Tn, 0, st>>>(
+        dim3 g3(nblk(p_end - p_off, Tn), (cs + SBS - 1) / SBS);
+      k_strength<SBS><<<g3, Tn, 0, st>>>(
           G, p_off, p_end, cs, niso, c->o, fd_tile, fd_o, c->g_start.p, c->g_iso.p, c->g_orig.p, c->g_iown.p, c->g_wavn.p,
           c->g_a0.p, c->g_gf.p, c->g_lg.p, c->s_rtemp.p, c->s_facz.p, c->s_lcz.p, c->s_ral.p, c->s_xterm.p, X,
           (float)c->dop_lmin, (float)c->dop_rstep, c->s_dens.p, nmol,
