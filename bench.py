@@ -286,7 +286,7 @@ def run_ours(args):
     my_prob = prob if (rank == 0 or bands_mode) else workloads.perturbed(prob, seed=1000 + rank)
     t0 = time.perf_counter()
     tr = (sharding.BandShardedTransit if bands_mode else sharding.ShardedTransit)(local_rank, rank, world)
-    stream = torch.cuda.current_stream()
+    stream = sharding.private_stream()         # kernels, copies and NCCL collectives share this stream
     tr.ctx.set_stream(stream.cuda_stream)              # kernels, copies and the NCCL gather share one stream
     tr.transit_init(my_prob)
     tr.ctx.sync()

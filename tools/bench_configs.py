@@ -97,7 +97,7 @@ def run_c5(bench, args):
     torch, dist, rank, local_rank, world = _dist(bench, args)
     prob = workloads.make_problem("C2", scale=args.scale)
     tr = sharding.ShardedTransit(local_rank, rank, world)
-    stream = torch.cuda.current_stream()
+    stream = sharding.private_stream()         # kernels, copies and NCCL collectives share this stream
     tr.ctx.set_stream(stream.cuda_stream)
     t0 = time.perf_counter()
     tr.transit_init(prob)                                # line-by-line set-up, used once: to build the grid
@@ -202,7 +202,7 @@ def run_c4(bench, args):
     temps = np.array([800.0, 1000.0, 1200.0, 1400.0, 1600.0, 1800.0])
     grid = c4_grid(prob, temps)
     tr = sharding.ShardedTransit(local_rank, rank, world)
-    stream = torch.cuda.current_stream()
+    stream = sharding.private_stream()         # kernels, copies and NCCL collectives share this stream
     tr.ctx.set_stream(stream.cuda_stream)
     molID = np.array([prob.mol_ID[prob.species_names.index(s)] for s in ("H2O", "CH4")], np.int32)
     tr.transit_init(prob, opacity=dict(molID=molID, temp=temps, press=prob.p * prob.p_fct, grid=grid))
@@ -276,7 +276,7 @@ def run_c3(bench, args):
     prob = c3_problem(args.scale)
     gen_s = time.perf_counter() - t0
     tr = sharding.ShardedTransit(local_rank, rank, world)
-    stream = torch.cuda.current_stream()
+    stream = sharding.private_stream()         # kernels, copies and NCCL collectives share this stream
     tr.ctx.set_stream(stream.cuda_stream)
     t0 = time.perf_counter()
     tr.transit_init(prob)

@@ -339,7 +339,11 @@ class Context:
         return int(self.lib.tb_launch_count(self.h))
 
     def set_stream(self, stream_ptr):
-        """Run on a caller-owned cudaStream_t (integer handle), e.g. torch.cuda.current_stream().cuda_stream."""
+        """Run on a caller-owned cudaStream_t (integer handle).  Handle 0 (torch's DEFAULT stream) means
+        "back to the context's own stream" to the library: pass a real stream (sharding.private_stream())."""
+        if not stream_ptr:
+            raise TransitError("set_stream(0): the default stream cannot be shared with the context; "
+                               "use transit_b200.sharding.private_stream()")
         self._ck(self.lib.tb_set_stream(self.h, C.c_void_p(stream_ptr)), "tb_set_stream")
 
     def device_spectrum(self):

@@ -547,9 +547,15 @@ __global__ void k_logthr(int ns, int niso, int nrows, int permol, double ethresh
 //   phase 3  strengths and ids leave through shared memory: whole sectors, coalesced.
 // The carried-index and tile-reach maxima are reduced in shared memory first: a handful of
 // global integer atomics per block instead of one per group.
+#define STR_NR 8   // group ranges one launch of k_strength can cover (a band shard: one range per molecule row)
+struct StrRanges {
+  long long p_off[STR_NR], p_end[STR_NR];
+  int blk0[STR_NR + 1];    // first block of each range
+  int n;
+};
 #define STR_NT 4   // consecutive accumulate tiles a block's reach maxima are kept for in shared memory
 template <int SB>
-__global__ void __launch_bounds__(256) k_strength(int64_t G, int64_t p_off, int64_t p_end, int ns, int niso, int o,
+__global__ void __launch_bounds__(256) k_strength(int64_t G, StrRanges rg, int ns, int niso, int o,
                            FastDiv fd_tile, FastDiv fd_o,
                            const int32_t *__restrict__ g_start,
                            const int16_t *__restrict__ g_iso, const int32_t *__restrict__ g_orig,
@@ -585,7 +591,10 @@ __global__ void __launch_bounds__(256) k_strength(int64_t G, int64_t p_off, int6
   if (tid < SB * STR_NT) { (&sh_wt[0][0])[tid] = -1; (&sh_fb[0][0])[tid] = 0; }
   if (tid == 0) sh_cnt = 0;
   __syncthreads();
-  const int64_t pbase = p_off + blockIdx.x * (int64_t)blockDim.x;     // groups [p_off, p_end) of this launch
+  int ir = 0;
+  while (ir + 1 < rg.n && (int)blockIdx.x >= rg.blk0[ir + 1]) ir++;
+  const int64_t p_end = rg.p_end[ir];
+  const int64_t pbase = rg.p_off[ir] + (blockIdx.x - rg.blk0[ir]) * (int64_t)blockDim.x;   // groups [p_off, p_end) of range ir
   const int64_t p = pbase + tid;
   const int s0 = blockIdx.y * SB;
   const bool act = p < p_end;
@@ -780,12 +789,18 @@ struct AccRec {
   int addr0;   // table address of bin 0's sample
   int lanes;   // lo | (hi - lo) << 8: bins (tile-relative, lo..hi) the profile covers
 };
+#define ACC_WW 16                          // warps of a wide-reach block (the window's records are split 16 ways)
 struct WideShared {
-  AccRec rec[ACC_TILE / 32][32];
-  double part[ACC_TILE / 32][ACC_TILE];
+  AccRec rec[ACC_WW][32];
+  double part[ACC_WW][ACC_TILE];
 };
 
-__global__ void __launch_bounds__(ACC_TILE)
+// Two instances over the same (tile, state) grid: WIDE = false runs 128 threads and takes the tiles
+// of narrow reach (and zero-fills the tiles nothing reaches), WIDE = true runs ACC_WW warps and takes
+// the rest; a block whose tile belongs to the other instance leaves at once.  Sixteen warps per wide
+// tile keep the machine full when a band shard (or a small batch of states) leaves few tiles.
+template <bool WIDE>
+__global__ void __launch_bounds__(WIDE ? 32 * ACC_WW : ACC_TILE)
 k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nrows, int permol, int ntiles,
              int tile_off, const int32_t *__restrict__ binstart, const int32_t *__restrict__ substart, int64_t nsub,
              int nsube, const LineRec *__restrict__ rec_in,
@@ -793,24 +808,24 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
              const int32_t *__restrict__ reach, const int32_t *__restrict__ reachP,
              const double *__restrict__ pdata, double *__restrict__ out,
              unsigned long long *__restrict__ nsamp) {
-  __shared__ __align__(16) WideShared sh;
   const int s = blockIdx.y;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x + tile_off;          // a band shard launches only its own tiles
   const int64_t jt = (int64_t)tile * ACC_TILE;
   const int64_t j = jt + tid;
-  const bool inb = j < nwn;
+  const bool inb = j < nwn && tid < ACC_TILE;
   const int R = reach[s * ntiles + tile];
   const int P = reachP[s * ntiles + tile];
   const int4 *rs = reinterpret_cast<const int4 *>(rec_in + (size_t)s * G);
   const int32_t *fbs = fbpid + (size_t)s * niso;
   unsigned long long cnt = 0;
+  if (WIDE != (P >= 0 && R > NARROW_R)) return;  // the other instance's tile
   if (P < 0) {                                   // nothing reaches this tile
     for (int row = 0; row < (permol ? nrows : 1); row++)
       if (inb) out[((size_t)s * (permol ? nrows : 1) + row) * nwn + j] = 0.0;
     return;
   }
-  if (R <= NARROW_R) {
+  if (!WIDE) {
     double acc = 0.0;
     if (inb) {
       const int64_t jhi = j + R + 1 > nwn ? nwn : j + R + 1;
@@ -851,7 +866,7 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
       if (!permol) out[(size_t)s * nwn + j] = acc;
     }
   } else {
-    WideShared &w = sh;
+    __shared__ __align__(16) WideShared w;
     const int maxbin = (int)(nwn - 1 - jt < ACC_TILE - 1 ? nwn - 1 - jt : ACC_TILE - 1);
     const int64_t ulo = jt - R < 0 ? 0 : jt - R;
     const int64_t uhi = jt + ACC_TILE + R > nwn ? nwn : jt + ACC_TILE + R;
@@ -862,7 +877,7 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
     for (int row = 0; row < nrows; row++) {
       const int32_t *bs = binstart + (size_t)row * nwn;
       const int p0 = bs[ulo], p1 = bs[uhi];
-      const int seg = (((p1 - p0 + 3) >> 2) + 31) & ~31;       // records per warp, whole chunks
+      const int seg = (((p1 - p0 + ACC_WW - 1) / ACC_WW) + 31) & ~31;   // records per warp, whole chunks
       const int pa = p0 + warp * seg;
       const int pb = pa + seg < p1 ? pa + seg : p1;
       for (int base = pa; base < pb; base += 32) {
@@ -913,7 +928,7 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
         if (inb) {
           double v = w.part[0][threadIdx.x];
 #pragma unroll
-          for (int g = 1; g < ACC_TILE / 32; g++) v += w.part[g][threadIdx.x];
+          for (int g = 1; g < ACC_WW; g++) v += w.part[g][threadIdx.x];
           out[((size_t)s * (permol ? nrows : 1) + (permol ? row : 0)) * nwn + j] = v;
         }
         __syncthreads();
@@ -1056,12 +1071,20 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       k_logthr<<<nblk((int64_t)cs * niso, 128), 128, 0, st>>>(cs, niso, nrows, permol, ethresh, c->d_iso_row.p,
                                                               c->s_facz.p, c->s_kmax.p, c->s_lcz.p);
       TB_LAUNCHED(c);
-      for (int r = 0; r < (banded ? nrows : 1); r++) {
-        const int64_t p_off = banded ? pa[r] : 0, p_end = banded ? pb[r] : G;
-        if (p_end <= p_off) continue;
-        dim3 g3(nblk(p_end - p_off, Tn), (cs + SBS - 1) / SBS);
+      for (int r0 = 0; r0 < (banded ? nrows : 1); r0 += STR_NR) {
+        StrRanges rg;
+        rg.n = 0; rg.blk0[0] = 0;
+        for (int r = r0; r < (banded ? nrows : 1) && rg.n < STR_NR; r++) {
+          const int64_t p_off = banded ? pa[r] : 0, p_end = banded ? pb[r] : G;
+          if (p_end <= p_off) continue;
+          rg.p_off[rg.n] = p_off; rg.p_end[rg.n] = p_end;
+          rg.blk0[rg.n + 1] = rg.blk0[rg.n] + nblk(p_end - p_off, Tn);
+          rg.n++;
+        }
+        if (rg.n == 0) continue;
+        dim3 g3(rg.blk0[rg.n], (cs + SBS - 1) / SBS);
       k_strength<SBS><<<g3, Tn, 0, st>>>(
-          G, p_off, p_end, cs, niso, c->o, fd_tile, fd_o, c->g_start.p, c->g_iso.p, c->g_orig.p, c->g_iown.p, c->g_wavn.p,
+          G, rg, cs, niso, c->o, fd_tile, fd_o, c->g_start.p, c->g_iso.p, c->g_orig.p, c->g_iown.p, c->g_wavn.p,
           c->g_a0.p, c->g_gf.p, c->g_lg.p, c->s_rtemp.p, c->s_facz.p, c->s_lcz.p, c->s_ral.p, c->s_xterm.p, X,
           (float)c->dop_lmin, (float)c->dop_rstep, c->s_dens.p, nmol,
           c->d_iso_imol.p, c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ilor.p,
@@ -1083,13 +1106,18 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       TB_CUDA(cudaMemsetAsync(dst, 0, (size_t)cs * nout * nwn * sizeof(double), st));
     dim3 g4(tile_hi - tile_lo, cs);
     tb_timer_begin(c, "accumulate");
-    if (tile_hi > tile_lo)
-    k_accumulate<<<g4, ACC_TILE, 0, st>>>(nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, tile_lo, c->binstart.p,
+    if (tile_hi > tile_lo) {
+      k_accumulate<true><<<g4, 32 * ACC_WW, 0, st>>>(nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, tile_lo, c->binstart.p,
                                           c->substart.p, c->nsub, c->nsube, c->s_rec.p, c->s_fbpid.p, c->d_ptab.p,
                                           c->s_reach.p, c->s_reachP.p, c->d_pdata2.p, dst,
                                           c->s_nsamp.p + s0);
+      k_accumulate<false><<<g4, ACC_TILE, 0, st>>>(nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, tile_lo, c->binstart.p,
+                                          c->substart.p, c->nsub, c->nsube, c->s_rec.p, c->s_fbpid.p, c->d_ptab.p,
+                                          c->s_reach.p, c->s_reachP.p, c->d_pdata2.p, dst,
+                                          c->s_nsamp.p + s0);
+    }
     tb_timer_end(c, "accumulate");
-    c->launches += 2;
+    c->launches += 3;
     TB_CUDA(cudaGetLastError());
     if (h_out)
       TB_CUDA(cudaMemcpyAsync(h_out + (size_t)s0 * nout * nwn, dst, (size_t)cs * nout * nwn * sizeof(double),

@@ -15,6 +15,17 @@ import numpy as np
 from . import api
 
 
+def private_stream():
+    """A non-default torch stream made current for this thread, to be handed to tb_set_stream.
+    torch's default stream has the handle 0, which tb_set_stream reads as "back to the context's
+    own stream": the kernels would then run on a stream NCCL knows nothing about, and the
+    collectives (which order themselves against torch's CURRENT stream) would race with them."""
+    import torch
+    st = torch.cuda.Stream()
+    torch.cuda.set_stream(st)
+    return st
+
+
 def atmosphere_shard(natm: int, rank: int, world: int):
     """Contiguous, balanced block of atmosphere indices owned by `rank` (the first natm % world
     ranks get one more)."""
