@@ -144,24 +144,36 @@ def nccl_exchange(group=None):
     return exchange
 
 
+_gather_cache = {}
+
+
 def gather_bands(local, bands, rank: int, world: int, group=None):
     """All-gather the band slices of a per-rank array [..., nwn] (only columns bands[rank] are valid on
-    each rank) into the full [..., nwn] on every rank.  Slices are padded to the widest band."""
+    each rank) into the full [..., nwn] on every rank.  Slices are padded to the widest band; the
+    staging buffers and the index that puts the gathered slices back in grid order are built once per
+    (shape, bands) so that a call is three small device operations: slice copy, all-gather, gather."""
     import torch
     import torch.distributed as dist
     if world == 1:
         return local
-    lead = local.shape[:-1]
-    wmax = max(hi - lo for lo, hi in bands)
+    lead = tuple(local.shape[:-1])
+    nwn = local.shape[-1]
+    key = (lead, nwn, tuple(bands), local.dtype, str(local.device), rank)
+    st = _gather_cache.get(key)
+    if st is None:
+        wmax = max(hi - lo for lo, hi in bands)
+        nlead = int(np.prod(lead)) if lead else 1
+        idx = np.empty((nlead, nwn), np.int64)
+        for r, (a, b) in enumerate(bands):          # element (l, w) of the result <- out[r, l, w - a]
+            idx[:, a:b] = (r * nlead + np.arange(nlead)[:, None]) * wmax + np.arange(b - a)[None, :]
+        st = dict(wmax=wmax, buf=torch.zeros(*lead, wmax, dtype=local.dtype, device=local.device),
+                  out=torch.empty(world, *lead, wmax, dtype=local.dtype, device=local.device),
+                  idx=torch.from_numpy(idx.reshape(-1)).to(local.device))
+        _gather_cache[key] = st
     lo, hi = bands[rank]
-    buf = torch.zeros(*lead, wmax, dtype=local.dtype, device=local.device)
-    buf[..., :hi - lo] = local[..., lo:hi]
-    out = torch.empty(world, *lead, wmax, dtype=local.dtype, device=local.device)
-    dist.all_gather_into_tensor(out, buf.unsqueeze(0).contiguous(), group=group)
-    full = torch.empty_like(local)
-    for r, (a, b) in enumerate(bands):
-        full[..., a:b] = out[r][..., :b - a]
-    return full
+    st["buf"][..., :hi - lo].copy_(local[..., lo:hi])
+    dist.all_gather_into_tensor(st["out"], st["buf"].unsqueeze(0), group=group)
+    return st["out"].reshape(-1).index_select(0, st["idx"]).reshape(*lead, nwn)
 
 
 class BandShardedTransit(ShardedTransit):
