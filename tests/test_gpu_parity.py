@@ -278,16 +278,11 @@ def test_host_mirror_interface(golden):
 
 # ------------------------------------------------------------------ wavenumber-band shard (8e)
 
-def test_band_shard_two_ranks_bit_identical_to_one():
-    """Two contexts, each owning a wavenumber band (tb_set_shard), run as two 'ranks' in two threads;
-    the exchange callback completes the two global maxima through host memory.  Extinction stitched
-    from the bands must be BIT-identical to the single-context result, deep (wide) and shallow
-    (narrow) layers alike, and the executed sample counts must add up."""
+def _band_union_check(prob):
     import threading
     import torch
     from transit_b200 import sharding
 
-    prob = workloads.make_problem("C2", scale=0.02, nlayers=24, wn_hi=6000.0)
     ref = setup_ctx(prob)
     ref.extinction_lbl(prob.ethresh)
     e_ref = ref.get_extinction()
@@ -340,6 +335,46 @@ def test_band_shard_two_ranks_bit_identical_to_one():
         assert not out[r][:, other].any()            # bins outside the band come back as zero
     assert np.array_equal(e, e_ref)
     assert np.array_equal(cnt[0] + cnt[1], n_ref)
+    return e_ref, n_ref
+
+
+def test_band_shard_two_ranks_bit_identical_to_one():
+    """Two contexts, each owning a wavenumber band (tb_set_shard), run as two 'ranks' in two threads;
+    the exchange callback completes the two global maxima through host memory.  Extinction stitched
+    from the bands must be BIT-identical to the single-context result, deep (wide) and shallow
+    (narrow) layers alike, and the executed sample counts must add up."""
+    _band_union_check(workloads.make_problem("C2", scale=0.02, nlayers=24, wn_hi=6000.0))
+
+
+def test_full_size_c2_properties():
+    """BASELINE.json's C2 at FULL size (31 334 wavenumbers, 100 layers, 10^6 lines), where the oracle
+    would take minutes: size-independent properties instead.  (1) band union == whole, bit for bit,
+    and sample counts add up; (2) two runs are bit-identical (fixed summation order, no float
+    atomics); (3) linearity: the per-molecule rows of a layer, weighted by the molecule densities,
+    add up to the layer's total extinction; (4) every executed profile update is inside the grid:
+    the sample count of a layer is bounded by groups x widest profile."""
+    prob = workloads.make_problem("C2")
+    e_ref, n_ref = _band_union_check(prob)
+    c = setup_ctx(prob)
+    c.extinction_lbl(prob.ethresh)
+    assert np.array_equal(c.get_extinction(), e_ref)
+    assert np.array_equal(c.sample_counts(prob.nrad), n_ref)
+    names = list(prob.cfg["molecules"].keys())
+    for r in (0, 37, 99):
+        T = np.array([prob.t[r] * prob.t_fct]); d = prob.mol_d[:, r][None, :]; Z = prob.iso_z[:, r][None, :]
+        rows = c.molext_states(T, d, Z, prob.ethresh, permol=1)[0]          # cm2/g per molecule
+        tot = c.molext_states(T, d, Z, prob.ethresh, permol=0)[0, 0]
+        assert np.array_equal(tot, e_ref[r])
+        molID = c.line_molIDs()
+        dens = np.array([prob.mol_d[list(prob.mol_ID).index(m), r] for m in molID])
+        # permol thresholds are per molecule (extinction.c:467 uses kmax[molecule]), the total's is
+        # global: the weighted rows can only contain MORE weak lines, by at most ethresh of the peak
+        s_ = (rows * dens[:, None]).sum(0)
+        assert np.all(s_ >= tot * (1 - 1e-12))
+        big = tot > 1e-2 * tot.max()
+        assert np.all(s_[big] <= tot[big] * 1.5)
+    assert n_ref.min() > 0 and n_ref.max() <= c.ngroups() * 401
+    c.close()
 
 
 # ------------------------------------------------------------------ C5 / C4 shapes (SURVEY 8d)
