@@ -133,7 +133,7 @@ extern "C" void tb_destroy(tb_ctx *c) {
   REL(s_lastq); REL(s_fb); REL(s_fbpid); REL(s_wtile); REL(s_reach); REL(s_reachP); REL(s_fbmax); REL(s_facz); REL(s_rtemp); REL(s_ral); REL(s_xterm); REL(x_line); REL(q_g); REL(q_a); REL(q_w); REL(q_iso); REL(s_rec); REL(s_hasfb);
   REL(s_nsamp); REL(s_nsamp_part); REL(s_out); REL(d_pdata2); REL(d_ptab);
   REL(d_e); REL(d_ecs); REL(d_tau); REL(d_intens); REL(d_out); REL(d_last); REL(d_err);
-  REL(r_coef); REL(r_par); REL(r_h); REL(r_s); REL(r_ip); REL(r_ang); REL(r_meta); REL(d_grid); REL(c_stage); REL(d_es_aux); REL(cub_tmp);
+  REL(r_coef); REL(r_rcp); REL(r_par); REL(r_h); REL(r_s); REL(r_ip); REL(r_ang); REL(r_meta); REL(d_grid); REL(c_stage); REL(d_es_aux); REL(cub_tmp);
 #undef REL
   for (CiaTable *t : c->cia) {
     t->release();

@@ -217,7 +217,7 @@ struct tb_ctx {
   double hfct = 1;
 
   // ---- ray geometry scratch
-  DevBuf<double> r_coef, r_par, r_h, r_s, r_ip, r_ang;
+  DevBuf<double> r_coef, r_par, r_h, r_s, r_ip, r_ang, r_rcp;
   DevBuf<int32_t> r_meta;
 
   // ---- opacity grid (a6-a8)

@@ -344,7 +344,7 @@ __global__ void k_ray_geometry(int eclipse, const double *__restrict__ rad, int 
                                const double *__restrict__ h, int nh, double hfct, int stride,
                                int32_t *__restrict__ meta, double *__restrict__ par,
                                double *__restrict__ coef, double *__restrict__ sbuf,
-                               int32_t *__restrict__ err) {
+                               double *__restrict__ rcp, int32_t *__restrict__ err) {
   int ri = blockIdx.x * blockDim.x + threadIdx.x;
   if (ri >= nh) return;
   // tau.c:274 as the reference is BUILT: gcc -ffast-math hoists 1/rfct out of the loop (objdump of
@@ -422,6 +422,8 @@ __global__ void k_ray_geometry(int eclipse, const double *__restrict__ rad, int 
     cf[4 * i + 3] = hsum;
   }
   pp[3] = even ? (s[1] - s[0]) : 0.0;
+  rcp[ri * 2] = 1.0 / (2.0 * pp[0] * pp[0]);      // correctly rounded reciprocals for tb_div_r
+  rcp[ri * 2 + 1] = 1.0 / pp[0];
   mt[0] = rs; mt[1] = n; mt[2] = mode; mt[3] = np;
 }
 
@@ -436,11 +438,21 @@ struct TauPar {
   double cl_ext, cl_top, cl_bot, cl_gamma, cl_Q, cl_r, cl_sig, cl_refwn;
 };
 
-// interp_parab (numerical.c:182-195) with the per-ray constants dx, x0 = x[0]/dx
-__device__ __forceinline__ double tb_parab(double dx, double x0, double xr, double y0, double y1, double y2) {
+// RN(x / y) given r = RN(1 / y): quotient estimate, exact remainder by FMA, one correction (Markstein):
+// the same correctly rounded quotient as the division, without recomputing the reciprocal of a
+// per-ray constant for every wavenumber (an FP64 division is ~40 dependent instructions)
+__device__ __forceinline__ double tb_div_r(double x, double y, double r) {
+  const double q = x * r;
+  return fma(fma(-q, y, x), r, q);
+}
+
+// interp_parab (numerical.c:182-195) with the per-ray constants dx, x0 = x[0]/dx and the
+// reciprocals rcp[0] = 1/(2 dx^2), rcp[1] = 1/dx (k_ray_geometry)
+__device__ __forceinline__ double tb_parab(double dx, double x0, double xr, const double *__restrict__ rcp,
+                                           double y0, double y1, double y2) {
   const double my = y0 + y2 - 2 * y1;
-  const double a = my / (2.0 * dx * dx);
-  const double b = (y2 - y1 - (x0 + 1.5) * my) / dx;
+  const double a = tb_div_r(my, 2.0 * dx * dx, rcp[0]);
+  const double b = tb_div_r(y2 - y1 - (x0 + 1.5) * my, dx, rcp[1]);
   const double cc = y0 + x0 * (y2 - 4 * y1 + 3 * y0 + x0 * my) / 2.0;
   return xr * xr * a + xr * b + cc;
 }
@@ -458,13 +470,14 @@ __device__ __forceinline__ double tb_parab(double dx, double x0, double xr, doub
 // stops a lane at its first ray above `toomuch`, the block takes the minimum over warps as
 // last[w] and clears what was written beyond it (the reference leaves zeros there).
 #define TAU_NW 8
-__global__ void __launch_bounds__(32 * TAU_NW)
+__global__ void __launch_bounds__(32 * TAU_NW, 4)
 k_tau_transit(TauPar P, const double *__restrict__ e, const double *__restrict__ ecs,
               const double *__restrict__ press, const double *__restrict__ temp,
               const double *__restrict__ aux, const double *__restrict__ mol_d,
               const double *__restrict__ mol_pol, const double *__restrict__ mol_mass, int nmol,
               const int32_t *__restrict__ meta, const double *__restrict__ par,
-              const double *__restrict__ coef, double *__restrict__ tau, int32_t *__restrict__ last) {
+              const double *__restrict__ coef, const double *__restrict__ rcp, double *__restrict__ tau,
+              int32_t *__restrict__ last) {
   extern __shared__ double sm[];
   __shared__ int sh_last[32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -511,31 +524,34 @@ k_tau_transit(TauPar P, const double *__restrict__ e, const double *__restrict__
       sm[r * 32 + lane] = e[(size_t)r * P.nwn + w] + es + ec + ecs[(size_t)r * P.nwn + w];
     }
   }
-  __syncthreads();
   __shared__ double sh_t2[32];
-  __shared__ int sh_ri2;
-  if (threadIdx.x == 0) sh_ri2 = -1;
-  if (P.eclipse) {
-    __syncthreads();
-    if (warp == 0 && inb) {
-      double *ew = sm + lane;
-      for (int ri = 0; ri < P.nh; ri++) {
+  __shared__ volatile int sh_prog;          // eclipse: rays whose starting layer the chain has passed
+  if (threadIdx.x == 0) sh_prog = 0;
+  __syncthreads();
+  // eclipse: warp 0 is the PRODUCER of the extrapolation chain, warps 1.. consume: ray ri may start as
+  // soon as the chain has stored its starting layer (everything above it is final by then), so the
+  // O(layers) dependent chain overlaps the Simpson sums instead of preceding them
+  const int w0 = P.eclipse ? 1 : 0, nrw = TAU_NW - w0;
+  if (P.eclipse && warp == 0) {
+    double *ew = sm + lane;
+    for (int ri = 0; ri < P.nh; ri++) {
+      if (inb) {
         const int32_t *mt = meta + ri * 4;
         const int mode = mt[2], rs = mt[0];
         const double *pp = par + ri * 4;
         if (mode == 1) {
-          ew[rs * 32] = tb_parab(pp[0], pp[1], pp[2], ew[rs * 32], ew[(rs + 1) * 32], ew[(rs + 2) * 32]);
+          ew[rs * 32] = tb_parab(pp[0], pp[1], pp[2], rcp + ri * 2, ew[rs * 32], ew[(rs + 1) * 32], ew[(rs + 2) * 32]);
         } else if (mode == 2) {
           const double *cf = coef + (size_t)ri * P.stride;
-          const double y0 = tb_parab(pp[0], pp[1], pp[2], ew[(rs - 1) * 32], ew[rs * 32], ew[(rs + 1) * 32]);
+          const double y0 = tb_parab(pp[0], pp[1], pp[2], rcp + ri * 2, ew[(rs - 1) * 32], ew[rs * 32], ew[(rs + 1) * 32]);
           const double yb = ew[(rs + 1) * 32];
           const double ya = (y0 + yb) / 2.0;
           sh_t2[lane] = (y0 * cf[0] + ya * cf[1] + yb * cf[2]) * cf[3] / 6.0;
-          if (lane == 0) sh_ri2 = ri;
         }
       }
+      __syncwarp();
+      if (lane == 0) { __threadfence_block(); sh_prog = ri + 1; }
     }
-    __syncthreads();
   }
   const double *er = sm + lane;
   int myfirst = P.nh;                       // first ray of this warp above toomuch (none yet)
@@ -554,8 +570,8 @@ k_tau_transit(TauPar P, const double *__restrict__ e, const double *__restrict__
       for (int k = 0; k < CFR; k++) pre[k] = (lane + 32 * k < n4) ? cf[lane + 32 * k] : 0.0;
     }
   };
-  fetch(warp);
-  for (int ri = warp; ri < P.nh; ri += TAU_NW) {          // whole warp: lanes outside the grid idle
+  if (warp >= w0) fetch(warp - w0);
+  for (int ri = warp - w0; ri < P.nh && warp >= w0; ri += nrw) {     // whole warp: lanes outside the grid idle
     const int32_t *mt = meta + ri * 4;
     const int mode = mt[2];
     const int n4 = 4 * mt[3];
@@ -563,7 +579,11 @@ k_tau_transit(TauPar P, const double *__restrict__ e, const double *__restrict__
 #pragma unroll
     for (int k = 0; k < CFR; k++) if (lane + 32 * k < n4) cw[lane + 32 * k] = pre[k];
     __syncwarp();
-    fetch(ri + TAU_NW);
+    fetch(ri + nrw);
+    if (P.eclipse) {                          // wait for the chain to have passed this ray's starting layer
+      while (sh_prog <= ri) { }
+      __threadfence_block();
+    }
     if (inb && myfirst == P.nh) {
       double t = 0.0;
       if (mode > 0) {
@@ -573,20 +593,27 @@ k_tau_transit(TauPar P, const double *__restrict__ e, const double *__restrict__
         if (mode == 2 && P.eclipse) {
           t = sh_t2[lane];                                   // evaluated inside the chain (see above)
         } else if (mode == 2) {
-          const double y0 = tb_parab(pp[0], pp[1], pp[2], er[(rs - 1) * 32], er[rs * 32], er[(rs + 1) * 32]);
+          const double y0 = tb_parab(pp[0], pp[1], pp[2], rcp + ri * 2, er[(rs - 1) * 32], er[rs * 32], er[(rs + 1) * 32]);
           const double yb = er[(rs + 1) * 32];
           const double ya = (y0 + yb) / 2.0;
           t = (y0 * cf[0] + ya * cf[1] + yb * cf[2]) * cf[3] / 6.0;
         } else {
           const double y0 = P.eclipse ? er[rs * 32]          // the chain left it there
-                                      : tb_parab(pp[0], pp[1], pp[2], er[rs * 32], er[(rs + 1) * 32], er[(rs + 2) * 32]);
+                                      : tb_parab(pp[0], pp[1], pp[2], rcp + ri * 2, er[rs * 32], er[(rs + 1) * 32], er[(rs + 2) * 32]);
           const int even = (n % 2 == 0);
           double res = 0.0;
+          // same terms in the same order as simpson() (numerical.c:454-525); the third sample of a pair
+          // is the first of the next and stays in a register, the four weights come as two 128-bit reads
+          double a0 = even ? er[(rs + 1) * 32] : y0;
+          const double *ep = er + (rs + even + 1) * 32;
+          const double2 *c2 = reinterpret_cast<const double2 *>(cf);
+#pragma unroll 2
           for (int i = 0; i < np; i++) {
-            const int j = 2 * i + even;
-            const double a0 = (j == 0) ? y0 : er[(rs + j) * 32];
-            res += (a0 * cf[4 * i] + er[(rs + j + 1) * 32] * cf[4 * i + 1] +
-                    er[(rs + j + 2) * 32] * cf[4 * i + 2]) * cf[4 * i + 3];
+            const double2 c01 = c2[2 * i], c23 = c2[2 * i + 1];
+            const double e1 = ep[0], e2 = ep[32];
+            ep += 64;
+            res += (a0 * c01.x + e1 * c01.y + e2 * c23.x) * c23.y;
+            a0 = e2;
           }
           t = res / 6.0;
           if (even) t += pp[3] * (y0 + er[(rs + 1) * 32]) / 2;
@@ -607,7 +634,7 @@ k_tau_transit(TauPar P, const double *__restrict__ e, const double *__restrict__
     if (warp == 0) last[w] = lst < P.nh ? lst : P.nh - 1;
     // clear what this warp wrote beyond the block-wide first exceed
     const int upto = myfirst < P.nh ? myfirst : P.nh - 1;
-    for (int ri = warp; ri <= upto; ri += TAU_NW)
+    for (int ri = warp - w0; ri <= upto && warp >= w0; ri += nrw)
       if (ri > lst) tau[(size_t)ri * P.nwn + w] = 0.0;
   }
 }
@@ -639,7 +666,7 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
   DevBuf<double> &d_h = c->r_h, &d_s = c->r_s;
   TB_TRY(d_h.ensure(nh)); TB_TRY(d_s.ensure((size_t)nh * (nrad + 3)));
   TB_TRY(c->r_meta.ensure((size_t)nh * 4)); TB_TRY(c->r_par.ensure((size_t)nh * 4));
-  TB_TRY(c->r_coef.ensure((size_t)nh * stride));
+  TB_TRY(c->r_coef.ensure((size_t)nh * stride)); TB_TRY(c->r_rcp.ensure((size_t)nh * 2));
   TB_TRY(c->d_tau.ensure((size_t)nh * nwn)); TB_TRY(c->d_last.ensure(nwn));
   TB_TRY(c->d_es_aux.ensure(2 * (size_t)nrad));
   std::vector<double> aux(2 * (size_t)nrad, 0.0);
@@ -649,7 +676,7 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
   TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4 * sizeof(int32_t), st));
   TB_CUDA(cudaMemsetAsync(c->d_tau.p, 0, sizeof(double) * nh * nwn, st));   // calloc, tau.c:34
   k_ray_geometry<<<nblk(nh, 64), 64, 0, st>>>(geometry == TB_GEOM_ECLIPSE, c->d_rad.p, nrad, c->rad_fct, d_h.p, nh,
-                                              hfct, stride, c->r_meta.p, c->r_par.p, c->r_coef.p, d_s.p, c->d_err.p);
+                                              hfct, stride, c->r_meta.p, c->r_par.p, c->r_coef.p, d_s.p, c->r_rcp.p, c->d_err.p);
   TauPar P;
   P.eclipse = geometry == TB_GEOM_ECLIPSE; P.nrad = nrad; P.nh = nh; P.stride = stride; P.nwn = nwn;
   P.rfct = c->rad_fct; P.toomuch = toomuch; P.wn_i = c->wn_i; P.wn_d = c->wn_d; P.wn_fct = c->wn_fct;
@@ -665,7 +692,7 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
     TB_CUDA(cudaFuncSetAttribute(k_tau_transit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
     k_tau_transit<<<nblk(nwn, 32), 32 * TAU_NW, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p,
                                                           c->d_dens.p, c->d_mol_pol.p, c->d_mol_mass.p, c->nmol,
-                                                          c->r_meta.p, c->r_par.p, c->r_coef.p, c->d_tau.p,
+                                                          c->r_meta.p, c->r_par.p, c->r_coef.p, c->r_rcp.p, c->d_tau.p,
                                                           c->d_last.p);
   }
   tb_timer_end(c, "tau");
