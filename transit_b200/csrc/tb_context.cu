@@ -88,6 +88,9 @@ extern "C" int tb_create(int device, tb_ctx **out) {
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
   TB_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+  TB_CUDA(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
+  TB_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+  TB_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
   c->stream = c->own_stream;
   TB_TRY(c->d_err.ensure(4));
   TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4 * sizeof(int32_t), c->stream));
@@ -122,6 +125,7 @@ extern "C" void tb_destroy(tb_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  if (c->aux_stream) cudaStreamSynchronize(c->aux_stream);
   // DevBuf members are released explicitly: the struct is a plain aggregate
 #define REL(x) c->x.release()
   REL(d_mol_mass); REL(d_mol_radius); REL(d_mol_pol); REL(d_iso_mass); REL(d_iso_ratio);
@@ -144,6 +148,9 @@ extern "C" void tb_destroy(tb_ctx *c) {
     if (kv.second.b) cudaEventDestroy(kv.second.b);
   }
   cudaStreamDestroy(c->own_stream);
+  if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
   delete c;
 }
 

@@ -122,6 +122,8 @@ struct tb_ctx {
   int device = 0;
   int sm_count = 148;
   cudaStream_t stream = nullptr, own_stream = nullptr;
+  cudaStream_t aux_stream = nullptr;                 // CIA runs here, beside the line sum (tb_spectrum)
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int64_t launches = 0;
   std::map<std::string, KernelTimer> timers;
 

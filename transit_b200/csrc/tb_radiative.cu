@@ -839,9 +839,22 @@ extern "C" int tb_intensity_flux(tb_ctx *c, const double *angles_deg, int nang, 
 
 extern "C" int tb_spectrum(tb_ctx *c, int geometry, double toomuch, double ethresh, double starrad_cm,
                            int transparent, const double *angles_deg, int nang, double *out) {
-  TB_TRY(tb_cia_run(c));                                   // interpcs, transit.c:147
-  if (c->have_grid_o) TB_TRY(tb_interp_run(c));            // interpolmolext (opacity file given)
-  else TB_TRY(tb_extinction_lbl(c, ethresh));              // computemolext per layer
+  // interpcs (transit.c:147) does not depend on the molecular extinction: its small latency-bound
+  // kernels run on a second stream beside the line sum and join before tau
+  cudaStream_t main_st = c->stream;
+  TB_CUDA(cudaSetDevice(c->device));
+  TB_CUDA(cudaEventRecord(c->ev_fork, main_st));
+  TB_CUDA(cudaStreamWaitEvent(c->aux_stream, c->ev_fork, 0));
+  c->stream = c->aux_stream;
+  const int rc_cia = tb_cia_run(c);
+  c->stream = main_st;
+  TB_TRY(rc_cia);
+  TB_CUDA(cudaEventRecord(c->ev_join, c->aux_stream));
+  int rc_e;
+  if (c->have_grid_o) rc_e = tb_interp_run(c);             // interpolmolext (opacity file given)
+  else rc_e = tb_extinction_lbl(c, ethresh);               // computemolext per layer
+  TB_CUDA(cudaStreamWaitEvent(main_st, c->ev_join, 0));    // also on error: never leave the fork dangling
+  TB_TRY(rc_e);
   TB_TRY(tb_tau_run(c, geometry, toomuch, nullptr, 0, 0, false));   // tau, transit.c:165,189
   if (geometry == TB_GEOM_ECLIPSE) return tb_intensity_flux(c, angles_deg, nang, out);
   return tb_modulation(c, starrad_cm, transparent, out);
