@@ -133,9 +133,9 @@ extern "C" void tb_destroy(tb_ctx *c) {
   REL(m_gf); REL(m_iso); REL(m_inr); REL(g_start); REL(g_iown); REL(g_idwn); REL(g_orig);
   REL(g_iso); REL(g_wavn); REL(g_a0); REL(g_gf); REL(g_lg); REL(s_lcz); REL(go_wavn); REL(binstart); REL(substart); REL(i_rho); REL(i_stage); REL(d_aDop); REL(d_aLor); REL(d_psize);
   REL(d_poff); REL(d_pdata); REL(d_rad); REL(d_p); REL(d_t); REL(d_dens); REL(s_T); REL(s_dens);
-  REL(s_Z); REL(s_alphal); REL(s_alphad); REL(s_kmax); REL(s_k); REL(s_ilor); REL(s_idop0);
+  REL(s_Z); REL(s_alphal); REL(s_alphad); REL(s_kmax); REL(s_ilor); REL(s_idop0);
   REL(s_lastq); REL(s_fb); REL(s_fbpid); REL(s_wtile); REL(s_reach); REL(s_reachP); REL(s_fbmax); REL(s_facz); REL(s_rtemp); REL(s_ral); REL(s_xterm); REL(x_line); REL(q_g); REL(q_a); REL(q_w); REL(q_iso); REL(s_rec); REL(s_hasfb);
-  REL(s_nsamp); REL(s_nsamp_part); REL(s_out); REL(d_pdata2); REL(d_ptab);
+  REL(s_nsamp); REL(s_out); REL(d_pdata2); REL(d_ptab);
   REL(d_e); REL(d_ecs); REL(d_tau); REL(d_intens); REL(d_out); REL(d_last); REL(d_err);
   REL(r_coef); REL(r_rcp); REL(r_par); REL(r_h); REL(r_s); REL(r_ip); REL(r_ang); REL(r_meta); REL(d_grid); REL(c_stage); REL(d_es_aux); REL(cub_tmp);
 #undef REL

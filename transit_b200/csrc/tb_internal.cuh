@@ -198,12 +198,12 @@ struct tb_ctx {
   DevBuf<double> d_rad, d_p, d_t, d_dens;
 
   // ---- state batch scratch (tb_lines.cu)
-  DevBuf<double> s_T, s_dens, s_Z, s_alphal, s_alphad, s_kmax, s_k;
+  DevBuf<double> s_T, s_dens, s_Z, s_alphal, s_alphad, s_kmax;
   DevBuf<int32_t> s_ilor, s_idop0, s_lastq, s_fb, s_fbpid, s_wtile, s_reach, s_reachP, s_fbmax;
   DevBuf<double> s_facz, s_rtemp, s_ral, s_xterm, s_lcz;
   DevBuf<LineRec> s_rec;      // [state][group]
   DevBuf<uint8_t> s_hasfb;    // [state][tile]
-  DevBuf<unsigned long long> s_nsamp, s_nsamp_part;
+  DevBuf<unsigned long long> s_nsamp;
   DevBuf<double> s_out;
   int last_ns = 0, last_permol = 0;
   bool nsamp_valid = false;
