@@ -278,7 +278,7 @@ def test_host_mirror_interface(golden):
 
 # ------------------------------------------------------------------ wavenumber-band shard (8e)
 
-def _band_union_check(prob):
+def _band_union_check(prob, world=2):
     import threading
     import torch
     from transit_b200 import sharding
@@ -289,9 +289,8 @@ def _band_union_check(prob):
     n_ref = ref.sample_counts(prob.nrad)
     ref.close()
 
-    world = 2
     bands = sharding.wavenumber_bands(sharding.line_weights(prob), world)
-    assert bands[0][1] % 128 == 0 and 0 < bands[0][1] < prob.nwn
+    assert bands[0][1] % 128 == 0 and 0 < bands[0][1] <= prob.nwn
     barrier = threading.Barrier(world)
     slots = [None] * world
     ctxs_, out, cnt, err = [None] * world, [None] * world, [None] * world, []
@@ -302,7 +301,9 @@ def _band_union_check(prob):
             t = sharding._alias(ptr, count, "<f8" if what == 0 else "<i4")
             slots[rank] = t.cpu()
             barrier.wait(timeout=120)
-            m = torch.maximum(slots[0], slots[1])
+            m = slots[0]
+            for other in slots[1:]:
+                m = torch.maximum(m, other)
             barrier.wait(timeout=120)
             t.copy_(m.cuda())
             torch.cuda.synchronize()
@@ -334,7 +335,7 @@ def _band_union_check(prob):
         other[lo:hi] = False
         assert not out[r][:, other].any()            # bins outside the band come back as zero
     assert np.array_equal(e, e_ref)
-    assert np.array_equal(cnt[0] + cnt[1], n_ref)
+    assert np.array_equal(sum(cnt), n_ref)
     return e_ref, n_ref
 
 
@@ -344,6 +345,14 @@ def test_band_shard_two_ranks_bit_identical_to_one():
     from the bands must be BIT-identical to the single-context result, deep (wide) and shallow
     (narrow) layers alike, and the executed sample counts must add up."""
     _band_union_check(workloads.make_problem("C2", scale=0.02, nlayers=24, wn_hi=6000.0))
+
+
+def test_band_shard_uneven_and_empty_bands():
+    """Three ranks on a grid of 2 501 bins (20 tiles, the last one ragged) and five ranks on a grid of
+    three tiles, where some ranks own NO bin at all: they still take part in both exchanges and
+    contribute nothing."""
+    _band_union_check(workloads.make_problem("C2", scale=0.01, nlayers=12, wn_hi=4500.0), world=3)
+    _band_union_check(workloads.make_problem("C2", scale=0.002, nlayers=8, wn_hi=2300.0), world=5)
 
 
 def test_full_size_c2_properties():

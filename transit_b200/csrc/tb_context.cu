@@ -109,7 +109,7 @@ extern "C" int tb_set_shard(tb_ctx *c, int64_t j_lo, int64_t j_hi, int rank, int
   TB_REQUIRE(j_lo % 128 == 0 && (j_hi % 128 == 0 || j_hi == c->nwn), TB_ERR_ARG,
              "tb_set_shard: band ends must be multiples of 128 (or the grid end)");
   c->band_lo = j_lo; c->band_hi = j_hi;
-  if (j_lo == 0 && j_hi == c->nwn) c->band_lo = c->band_hi = 0;
+  c->banded = !(j_lo == 0 && j_hi == c->nwn);       // an EMPTY band (j_lo == j_hi > 0) is a valid shard
   c->shard_rank = rank; c->shard_world = world;
   c->exch = fn; c->exch_user = user;
   return TB_OK;

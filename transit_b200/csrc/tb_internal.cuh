@@ -169,7 +169,8 @@ struct tb_ctx {
   int nsube = 1;
 
   // ---- wavenumber-band shard (tb_set_shard): line sum only for coarse bins [band_lo, band_hi)
-  int64_t band_lo = 0, band_hi = 0;   // (0, 0) = whole grid
+  bool banded = false;                // false = whole grid
+  int64_t band_lo = 0, band_hi = 0;   // coarse bins [band_lo, band_hi); may be empty
   int shard_rank = 0, shard_world = 1;
   tb_exchange_fn exch = nullptr;
   void *exch_user = nullptr;

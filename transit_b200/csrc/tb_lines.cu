@@ -1002,7 +1002,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   const int utiles = (int)((Rmax + ACC_TILE - 1) / ACC_TILE) + 1;
   // wavenumber-band shard (tb_set_shard): which tiles this context accumulates and which groups
   // can reach them
-  const bool banded = c->band_hi > c->band_lo;
+  const bool banded = c->banded;
   const int64_t b_lo = banded ? c->band_lo : 0, b_hi = banded ? c->band_hi : nwn;
   const int tile_lo = (int)(b_lo / ACC_TILE), tile_hi = (int)((b_hi + ACC_TILE - 1) / ACC_TILE);
   std::vector<int64_t> pa(nrows, 0), pb(nrows, 0);
@@ -1014,7 +1014,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       TB_CUDA(cudaStreamSynchronize(st));
     }
     const int64_t jl = b_lo - Rmax < 0 ? 0 : b_lo - Rmax, jh = b_hi + Rmax > nwn ? nwn : b_hi + Rmax;
-    for (int r = 0; r < nrows; r++) {
+    for (int r = 0; r < nrows && b_hi > b_lo; r++) {      // an empty band needs no strengths at all
       pa[r] = c->h_binstart[(size_t)r * nwn + jl];
       pb[r] = c->h_binstart[(size_t)r * nwn + jh];
     }
