@@ -403,7 +403,7 @@ def run_ours(args):
         "gpu_launches": launches,
         "line_sum": {"gsamples_per_s": nsamp / (mol_ms * 1e-3) / 1e9, "samples_per_step": nsamp,
                      "line_layers_per_s": len(prob.wl) * prob.nrad / (mol_ms * 1e-3), "molext_ms": mol_ms},
-        "kernel_ms": {k: float(np.mean(v)) for k, v in k_ms.items()},
+        "kernel_ms": {k: float(np.mean(v)) for k, v in k_ms.items() if np.isfinite(np.mean(v))},
         "roofline": {"kernel": "k_accumulate (wide-reach + narrow-reach instances, one timer)", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src, "ms": acc_ms,
                      "algorithmic_bytes": acc_bytes,
