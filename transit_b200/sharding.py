@@ -34,24 +34,34 @@ def atmosphere_shard(natm: int, rank: int, world: int):
     return range(lo, lo + base + (1 if rank < extra else 0))
 
 
+_spectra_cache = {}
+
+
 def gather_spectra(local, natm: int, rank: int, world: int, group=None):
     """All-gather per-rank spectra [n_local, nwn] into [natm, nwn] in atmosphere order on every rank.
-    Blocks may differ by one row between ranks: they are padded to the largest for the collective."""
+    Blocks may differ by one row between ranks: they are padded to the largest for the collective.
+    Staging buffers are kept per (shape, natm, world): a call is a copy, the all-gather and, only when
+    the blocks are uneven, one row gather."""
     import torch
     import torch.distributed as dist
     if world == 1:
         return local
     nmax = -(-natm // world)
     nwn = local.shape[1]
-    buf = torch.zeros(nmax, nwn, dtype=local.dtype, device=local.device)
-    buf[:local.shape[0]] = local
-    out = torch.empty(world * nmax, nwn, dtype=local.dtype, device=local.device)
-    dist.all_gather_into_tensor(out, buf, group=group)
-    rows = []
-    for r in range(world):
-        n = len(atmosphere_shard(natm, r, world))
-        rows.append(out[r * nmax:r * nmax + n])
-    return torch.cat(rows, 0)
+    key = (natm, nwn, world, rank, local.dtype, str(local.device))
+    st = _spectra_cache.get(key)
+    if st is None:
+        rows = []
+        for r in range(world):
+            rows += [r * nmax + i for i in range(len(atmosphere_shard(natm, r, world)))]
+        even = natm == world * nmax
+        st = dict(buf=torch.zeros(nmax, nwn, dtype=local.dtype, device=local.device),
+                  out=torch.empty(world * nmax, nwn, dtype=local.dtype, device=local.device),
+                  rows=None if even else torch.tensor(rows, dtype=torch.int64, device=local.device))
+        _spectra_cache[key] = st
+    st["buf"][:local.shape[0]].copy_(local)
+    dist.all_gather_into_tensor(st["out"], st["buf"], group=group)
+    return st["out"] if st["rows"] is None else st["out"].index_select(0, st["rows"])
 
 
 class ShardedTransit(api.Transit):
