@@ -93,7 +93,8 @@ struct ProfEntry {
 struct __align__(16) LineRec {
   double k;        // strength (0 for skipped groups)
   int32_t iown;    // fine bin of the group
-  uint32_t pid;    // profile cell, PID_SKIP, PID_NOREACH + cell, or PID_FB + isotope
+  uint32_t pid;    // low 16 bits: profile cell, PID_SKIP, PID_NOREACH + cell, or PID_FB + isotope;
+                   // high 16 bits: how many dead records follow this one inside its 256-group block
 };
 
 struct CiaTable {

@@ -579,6 +579,7 @@ __global__ void __launch_bounds__(256) k_strength(int64_t G, StrRanges rg, int n
   __shared__ double sh_aDop[256];
   __shared__ double sh_k[SB][256];
   __shared__ uint16_t sh_pid[SB][256];
+  __shared__ unsigned sh_dead[SB][8];
   __shared__ uint16_t sh_list[SB * 256];
   __shared__ int32_t sh_wt[SB][STR_NT];
   __shared__ int32_t sh_fb[SB][STR_NT];
@@ -693,16 +694,28 @@ __global__ void __launch_bounds__(256) k_strength(int64_t G, StrRanges rg, int n
   }
   __syncthreads();
   // ---- phase 3
+  // dead-record bitmaps per (state, warp): each record carries the length of the dead run after it
+  // (within this block, up to 63 - lane), which the narrow walk of k_accumulate jumps over
+#pragma unroll
+  for (int k = 0; k < SB; k++) {
+    const unsigned m = __ballot_sync(0xffffffffu, act && PID_DEAD((unsigned)sh_pid[k][tid]));
+    if ((tid & 31) == 0) sh_dead[k][tid >> 5] = m;
+  }
+  __syncthreads();
   if (act) {
     const int io = g_iown[p];
+    const int lane = tid & 31, w = tid >> 5;
 #pragma unroll
     for (int k = 0; k < SB; k++) {
       const int s = s0 + k;
       if (s < ns) {
         // written for skipped groups too: whole sectors, no fill reads
         const double kk = sh_k[k][tid];
+        const unsigned long long dm =
+            (((unsigned long long)(w < 7 ? sh_dead[k][w + 1] : 0u) << 32) | sh_dead[k][w]) >> (lane + 1);
+        const int skip = __ffsll((long long)~dm) - 1;
         int4 v;
-        v.x = __double2loint(kk); v.y = __double2hiint(kk); v.z = io; v.w = (int)sh_pid[k][tid];
+        v.x = __double2loint(kk); v.y = __double2hiint(kk); v.z = io; v.w = (int)sh_pid[k][tid] | (skip << 16);
         *reinterpret_cast<int4 *>(rec_out + (size_t)s * G + p) = v;
       }
     }
@@ -840,9 +853,9 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
         int4 r_n = p < p1 ? __ldg(rs + p) : make_int4(0, 0, 0x7fffffff, PID_SKIP);
         while (p < p1 && r_n.z <= hi_f) {
           const int io = r_n.z;
-          unsigned pid = (unsigned)r_n.w;
+          unsigned pid = (unsigned)r_n.w & 0xFFFFu;
           const double kk = __hiloint2double(r_n.y, r_n.x);
-          p++;
+          p += 1 + (int)((unsigned)r_n.w >> 16);   // over the dead records that follow (k_strength counted them)
           if (p < p1) r_n = __ldg(rs + p);
           if (PID_DEAD(pid)) continue;
           if (pid >= PID_FB) pid = fbs[pid - PID_FB];
@@ -883,7 +896,7 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
       for (int base = pa; base < pb; base += 32) {
         const int p = base + lane;
         const int4 rr = p < pb ? __ldg(rs + p) : make_int4(0, 0, 0, PID_SKIP);
-        unsigned pid = (unsigned)rr.w;
+        unsigned pid = (unsigned)rr.w & 0xFFFFu;
         bool alive = !PID_DEAD(pid);
         AccRec rec;
         if (alive) {
@@ -1178,7 +1191,7 @@ __global__ void k_trace(int64_t n, int64_t G, int s_local, int niso, const uint8
     int32_t p = l_gpos[i];
     io = l_iown[i];
     id = g_idwn[p];
-    const unsigned pid = recs[(size_t)s_local * G + p].pid;
+    const unsigned pid = recs[(size_t)s_local * G + p].pid & 0xFFFFu;
     if (pid == PID_SKIP) st = 3;
     else {
       st = 1;
