@@ -555,7 +555,7 @@ struct StrRanges {
 };
 #define STR_NT 4   // consecutive accumulate tiles a block's reach maxima are kept for in shared memory
 template <int SB>
-__global__ void __launch_bounds__(256) k_strength(int64_t G, StrRanges rg, int ns, int niso, int o,
+__global__ void __launch_bounds__(256, 6) k_strength(int64_t G, StrRanges rg, int ns, int niso, int o,
                            FastDiv fd_tile, FastDiv fd_o,
                            const int32_t *__restrict__ g_start,
                            const int16_t *__restrict__ g_iso, const int32_t *__restrict__ g_orig,
