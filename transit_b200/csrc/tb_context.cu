@@ -1,4 +1,5 @@
 // tb_context.cu -- context life cycle, static problem description, taps, micro-benchmarks.
+#include <cstring>
 #include <stdarg.h>
 #include "tb_internal.cuh"
 
@@ -151,6 +152,7 @@ extern "C" void tb_destroy(tb_ctx *c) {
   if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
+  if (c->h_ring) cudaFreeHost(c->h_ring);
   delete c;
 }
 
@@ -183,11 +185,33 @@ extern "C" int tb_set_wn_grid(tb_ctx *c, double wn_i, double wn_d, int wnosamp, 
   return TB_OK;
 }
 
+// host -> device copy of a small array through the context's pinned ring (see tb_ctx::h_ring)
+int tb_upload_small(tb_ctx *c, void *dst, const void *src, size_t bytes, cudaStream_t st) {
+  if (!bytes) return TB_OK;
+  if (bytes > TB_RING_BYTES / 8) {                     // not small: the ordinary staged copy
+    TB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st));
+    return TB_OK;
+  }
+  if (!c->h_ring) TB_CUDA(cudaMallocHost((void **)&c->h_ring, TB_RING_BYTES));
+  const size_t need = (bytes + 63) & ~size_t(63);
+  if (c->ring_pos + need > TB_RING_BYTES) {            // wrap: whatever still reads the ring must have left
+    TB_CUDA(cudaStreamSynchronize(c->stream));
+    TB_CUDA(cudaStreamSynchronize(c->own_stream));
+    TB_CUDA(cudaStreamSynchronize(c->aux_stream));
+    if (st != c->stream) TB_CUDA(cudaStreamSynchronize(st));
+    c->ring_pos = 0;
+  }
+  char *slot = c->h_ring + c->ring_pos;
+  memcpy(slot, src, bytes);
+  TB_CUDA(cudaMemcpyAsync(dst, slot, bytes, cudaMemcpyHostToDevice, st));
+  c->ring_pos += need;
+  return TB_OK;
+}
+
 template <typename T>
 static int upload(tb_ctx *c, DevBuf<T> &b, const T *h, size_t n) {
   TB_TRY(b.ensure(n ? n : 1));
-  if (n) TB_CUDA(cudaMemcpyAsync(b.p, h, n * sizeof(T), cudaMemcpyHostToDevice, c->stream));
-  return TB_OK;
+  return tb_upload_small(c, b.p, h, n * sizeof(T), c->stream);
 }
 
 extern "C" int tb_set_species(tb_ctx *c, int nmol, const double *mol_mass, const double *mol_radius,
@@ -269,7 +293,6 @@ extern "C" int tb_set_atmosphere(tb_ctx *c, int nrad, const double *rad, double 
   TB_TRY(upload(c, c->d_p, c->p.data(), nrad));
   TB_TRY(upload(c, c->d_t, c->t.data(), nrad));
   TB_TRY(upload(c, c->d_dens, c->dens.data(), (size_t)c->nmol * nrad));
-  TB_CUDA(cudaStreamSynchronize(c->stream));
   c->have_atm = true;
   c->have_e = c->have_ecs = c->have_tau = false;
   return TB_OK;

@@ -124,6 +124,12 @@ struct tb_ctx {
   int sm_count = 148;
   cudaStream_t stream = nullptr, own_stream = nullptr;
   cudaStream_t aux_stream = nullptr;                 // CIA runs here, beside the line sum (tb_spectrum)
+  // pinned host ring behind tb_upload_small: cudaMemcpyAsync from PAGEABLE memory first waits for the
+  // stream's earlier work and then stages, so every small per-atmosphere upload used to be a hidden
+  // stream synchronisation; from the ring it is a plain enqueue and the caller's buffer is free at once
+  char *h_ring = nullptr;
+  size_t ring_pos = 0;
+  int tau_shm_set = -1;                              // dynamic shared memory size k_tau_transit was last opted into
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int64_t launches = 0;
   std::map<std::string, KernelTimer> timers;
@@ -306,4 +312,6 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
                   double ethresh, int permol, double *d_out_rows, double *h_out);
 int tb_cia_run(tb_ctx *c);
 int tb_check_errors(tb_ctx *c);
+#define TB_RING_BYTES (size_t(4) << 20)
+int tb_upload_small(tb_ctx *c, void *dst, const void *src, size_t bytes, cudaStream_t st);
 int tb_interp_run(tb_ctx *c);

@@ -1036,12 +1036,9 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   tb_timer_begin(c, "molext");
   for (int s0 = 0; s0 < ns; s0 += chunk) {
     const int cs = (ns - s0 < chunk) ? ns - s0 : chunk;
-    TB_CUDA(cudaMemcpyAsync(c->s_T.p, T + s0, cs * sizeof(double), cudaMemcpyHostToDevice, st));
-    TB_CUDA(cudaMemcpyAsync(c->s_dens.p, dens + (size_t)s0 * nmol, (size_t)cs * nmol * sizeof(double),
-                            cudaMemcpyHostToDevice, st));
-    if (niso)
-      TB_CUDA(cudaMemcpyAsync(c->s_Z.p, Z + (size_t)s0 * niso, (size_t)cs * niso * sizeof(double),
-                              cudaMemcpyHostToDevice, st));
+    TB_TRY(tb_upload_small(c, c->s_T.p, T + s0, cs * sizeof(double), st));
+    TB_TRY(tb_upload_small(c, c->s_dens.p, dens + (size_t)s0 * nmol, (size_t)cs * nmol * sizeof(double), st));
+    if (niso) TB_TRY(tb_upload_small(c, c->s_Z.p, Z + (size_t)s0 * niso, (size_t)cs * niso * sizeof(double), st));
     double *dst = d_out_rows ? d_out + (size_t)s0 * nout * nwn : d_out;
     int nset = cs * (niso > nrows ? niso : nrows);
     if (nset < cs) nset = cs;

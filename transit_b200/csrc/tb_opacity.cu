@@ -51,9 +51,22 @@ __global__ void k_grid_interp(int64_t nwn, int nrad, int Ntemp, int Nmol, const 
   const double *lo = grid + (((size_t)r * Ntemp + l.it) * Nmol) * nwn + w;
   const double *hi = lo + (size_t)Nmol * nwn;
   double acc = 0.0;
-  for (int m = 0; m < Nmol; m++) {
-    double ext = (lo[(size_t)m * nwn] * (l.thi - l.t) + hi[(size_t)m * nwn] * (l.t - l.tlo)) / (l.thi - l.tlo);
-    acc += rho[m * nrad + r] * ext;
+  // the 2 x 4 plane reads of four molecules are issued before the first division depends on one:
+  // same operations in the same order as the loop over m, four times the bytes in flight
+  for (int m0 = 0; m0 < Nmol; m0 += 4) {
+    double vlo[4], vhi[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const bool in = m0 + k < Nmol;
+      vlo[k] = in ? __ldcs(lo + (size_t)(m0 + k) * nwn) : 0.0;   // streamed once per spectrum
+      vhi[k] = in ? __ldcs(hi + (size_t)(m0 + k) * nwn) : 0.0;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+      if (m0 + k < Nmol) {
+        const double ext = (vlo[k] * (l.thi - l.t) + vhi[k] * (l.t - l.tlo)) / (l.thi - l.tlo);
+        acc += rho[(m0 + k) * nrad + r] * ext;
+      }
   }
   e[(size_t)r * nwn + w] = acc;
 }
@@ -86,9 +99,8 @@ int tb_interp_run(tb_ctx *c) {
   TB_TRY(c->d_e.ensure((size_t)nrad * c->nwn));
   InterpLayer *dLp = reinterpret_cast<InterpLayer *>(c->i_stage.p);
   double *drhop = c->i_rho.p;
-  TB_CUDA(cudaMemcpyAsync(dLp, L.data(), nrad * sizeof(InterpLayer), cudaMemcpyHostToDevice, st));
-  TB_CUDA(cudaMemcpyAsync(drhop, rho.data(), rho.size() * sizeof(double), cudaMemcpyHostToDevice, st));
-  TB_CUDA(cudaStreamSynchronize(st));       // L and rho are stack/heap locals of this call
+  TB_TRY(tb_upload_small(c, dLp, L.data(), nrad * sizeof(InterpLayer), st));   // copied into the pinned ring:
+  TB_TRY(tb_upload_small(c, drhop, rho.data(), rho.size() * sizeof(double), st)); // the locals may die
   dim3 g(nblk(c->nwn, 256), nrad);
   tb_timer_begin(c, "interp");
   k_grid_interp<<<g, 256, 0, st>>>(c->nwn, nrad, Nt, Nm, c->d_grid.p, dLp, drhop, c->d_e.p);

@@ -307,7 +307,7 @@ int tb_cia_run(tb_ctx *c) {
     D.densfac = c->c_stage.p + (size_t)nrad * (1 + n);
     D.fi = (int)t->fi; D.li = (int)t->li; D.fj = fj; D.lj = lj; D.ntw = t->nw;
   }
-  TB_CUDA(cudaMemcpyAsync(c->c_stage.p, stage.data(), stage.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_TRY(tb_upload_small(c, c->c_stage.p, stage.data(), stage.size() * sizeof(double), st));
   tb_timer_begin(c, "cia");
   int k = 0;
   for (int n = 0; n < ntab && k < P.n; n++) {
@@ -671,8 +671,8 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
   TB_TRY(c->d_es_aux.ensure(2 * (size_t)nrad));
   std::vector<double> aux(2 * (size_t)nrad, 0.0);
   if ((int)c->nH.size() == nrad) for (int i = 0; i < nrad; i++) { aux[i] = c->nH[i]; aux[nrad + i] = c->mean_dens[i]; }
-  TB_CUDA(cudaMemcpyAsync(c->d_es_aux.p, aux.data(), aux.size() * sizeof(double), cudaMemcpyHostToDevice, st));
-  TB_CUDA(cudaMemcpyAsync(d_h.p, c->h_h.data(), nh * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_TRY(tb_upload_small(c, c->d_es_aux.p, aux.data(), aux.size() * sizeof(double), st));
+  TB_TRY(tb_upload_small(c, d_h.p, c->h_h.data(), nh * sizeof(double), st));
   TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4 * sizeof(int32_t), st));
   TB_CUDA(cudaMemsetAsync(c->d_tau.p, 0, sizeof(double) * nh * nwn, st));   // calloc, tau.c:34
   k_ray_geometry<<<nblk(nh, 64), 64, 0, st>>>(geometry == TB_GEOM_ECLIPSE, c->d_rad.p, nrad, c->rad_fct, d_h.p, nh,
@@ -689,7 +689,10 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
     const size_t shm = ((size_t)nrad * 32 + (size_t)TAU_NW * stride) * sizeof(double);
     TB_REQUIRE(stride <= 320, TB_ERR_ARG, "too many layers (%d) for the tau kernel's coefficient registers", nrad);
     TB_REQUIRE(shm <= 200 * 1024, TB_ERR_ARG, "too many layers (%d) for the tau kernel's shared memory", nrad);
-    TB_CUDA(cudaFuncSetAttribute(k_tau_transit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
+    if (c->tau_shm_set != (int)shm) {
+      TB_CUDA(cudaFuncSetAttribute(k_tau_transit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
+      c->tau_shm_set = (int)shm;
+    }
     k_tau_transit<<<nblk(nwn, 32), 32 * TAU_NW, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p,
                                                           c->d_dens.p, c->d_mol_pol.p, c->d_mol_mass.p, c->nmol,
                                                           c->r_meta.p, c->r_par.p, c->r_coef.p, c->r_rcp.p, c->d_tau.p,
@@ -761,7 +764,7 @@ extern "C" int tb_modulation(tb_ctx *c, double starrad_cm, int transparent, doub
   DevBuf<double> &d_ip = c->r_ip;
   TB_TRY(d_ip.ensure(c->nh));
   TB_TRY(c->d_out.ensure(c->nwn));
-  TB_CUDA(cudaMemcpyAsync(d_ip.p, c->h_h.data(), c->nh * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_TRY(tb_upload_small(c, d_ip.p, c->h_h.data(), c->nh * sizeof(double), st));
   tb_timer_begin(c, "modulation");
   k_modulation<<<nblk(c->nwn, 128), 128, 0, st>>>(c->nwn, c->nh, c->d_tau.p, c->d_last.p, d_ip.p, c->hfct, c->toomuch,
                                                   starrad_cm, transparent, c->d_out.p, c->d_err.p);
@@ -822,8 +825,8 @@ extern "C" int tb_intensity_flux(tb_ctx *c, const double *angles_deg, int nang, 
   TB_TRY(d_a.ensure(2 * (size_t)nang));
   TB_TRY(c->d_intens.ensure((size_t)nang * c->nwn));
   TB_TRY(c->d_out.ensure(c->nwn));
-  TB_CUDA(cudaMemcpyAsync(d_a.p, ang.data(), nang * sizeof(double), cudaMemcpyHostToDevice, st));
-  TB_CUDA(cudaMemcpyAsync(d_a.p + nang, area.data(), nang * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_TRY(tb_upload_small(c, d_a.p, ang.data(), nang * sizeof(double), st));
+  TB_TRY(tb_upload_small(c, d_a.p + nang, area.data(), nang * sizeof(double), st));
   tb_timer_begin(c, "intensity");
   k_intensity_flux<<<nblk(c->nwn, 128), 128, 0, st>>>(c->nwn, c->nrad, c->d_tau.p, c->d_last.p, c->d_t.p, c->wn_i,
                                                       c->wn_d, c->wn_fct, nang, d_a.p, d_a.p + nang, c->d_intens.p,
