@@ -59,16 +59,25 @@ __device__ double tb_splinterp_pt(const double *z, int N, const double *x, const
 #define CIA_MAXT 64
 #define CIA_MAXTAB 8
 
+// per-table arguments of the two per-spectrum spline passes: every table goes in ONE launch
+// (blockIdx.y = table) so that their latency-bound recurrences run side by side
+struct CiaSplineTab {
+  const double *tab, *zt, *ttemp, *h, *rh, *r, *ru;
+  double *f2, *v, *z2;
+  int ntw, ntt, fj, lj;
+};
+struct CiaSplinePack {
+  CiaSplineTab t[CIA_MAXTAB];
+};
+
 // pass 1 (crosssec.c:407-412): f2[layer][row] = spline along T of table row `row` at the layer T
-__global__ void k_cia_temp(const double *__restrict__ tab, const double *__restrict__ zt,
-                           const double *__restrict__ ttemp, int ntw, int ntt,
-                           const double *__restrict__ ltemp, int nrad, int fj, int lj,
-                           double *__restrict__ f2) {
+__global__ void k_cia_temp(CiaSplinePack P, const double *__restrict__ ltemp, int nrad) {
+  const CiaSplineTab &T = P.t[blockIdx.y];
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= ntw * nrad) return;
-  const int j = t / ntw, i = t % ntw;
-  if (j < fj || j >= lj) return;
-  f2[t] = tb_splinterp_pt(zt + (size_t)i * ntt, ntt, ttemp, tab + (size_t)i * ntt, ltemp[j]);
+  if (t >= T.ntw * nrad) return;
+  const int j = t / T.ntw, i = t % T.ntw;
+  if (j < T.fj || j >= T.lj) return;
+  T.f2[t] = tb_splinterp_pt(T.zt + (size_t)i * T.ntt, T.ntt, T.ttemp, T.tab + (size_t)i * T.ntt, ltemp[j]);
 }
 
 // pass 2a (crosssec.c:415-416, spline.c:12-48): second derivatives along the table wavenumbers.
@@ -77,21 +86,24 @@ __global__ void k_cia_temp(const double *__restrict__ tab, const double *__restr
 // (r = h[i-1]/u[i-1], ru = 1/u: table-only, precomputed).  One warp per layer: every lane
 // composes the affine map of its contiguous segment of rows, the 32 maps are chained through
 // shuffles, and the lane then replays its segment from the right starting value.
-__global__ void k_cia_wnspline(const double *__restrict__ h, const double *__restrict__ rh,
-                               const double *__restrict__ r, const double *__restrict__ ru, int ntw,
-                               int fj, int lj, const double *__restrict__ f2, double *__restrict__ v,
-                               double *__restrict__ z2) {
+__global__ void k_cia_wnspline(CiaSplinePack P) {
+  const CiaSplineTab &T = P.t[blockIdx.y];
+  const double *__restrict__ h = T.h, *__restrict__ rh = T.rh, *__restrict__ r = T.r, *__restrict__ ru = T.ru;
+  const int ntw = T.ntw;
   const int lane = threadIdx.x & 31;
-  const int j = fj + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-  if (j >= lj) return;                                   // whole warp
-  const double *y = f2 + (size_t)j * ntw;
-  double *vv = v + (size_t)j * ntw, *zz = z2 + (size_t)j * ntw;
+  const int j = T.fj + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  if (j >= T.lj) return;                                 // whole warp
+  const double *__restrict__ y = T.f2 + (size_t)j * ntw;
+  double *__restrict__ vv = T.v + (size_t)j * ntw, *__restrict__ zz = T.z2 + (size_t)j * ntw;
   const int L = (ntw - 2 + 31) / 32;                      // rows 1 .. ntw-2
   const int a = 1 + lane * L;
   const int b = a + L < ntw - 1 ? a + L : ntw - 1;
   const unsigned full = 0xffffffffu;
+  // the loops below are first-order recurrences fed by loads that do not depend on them: unrolled
+  // by 8 the loads of eight rows are in flight together instead of one L2 round trip per row
   // ---- forward sweep
   double A = 1.0, B = 0.0;
+#pragma unroll 8
   for (int i = a; i < b; i++) {
     const double c = 6 * ((y[i + 1] - y[i]) * rh[i] - (y[i] - y[i - 1]) * rh[i - 1]);
     B = c - r[i] * B;
@@ -104,6 +116,7 @@ __global__ void k_cia_wnspline(const double *__restrict__ h, const double *__res
     carry = Al * carry + Bl;
   }
   double vp = mine;
+#pragma unroll 8
   for (int i = a; i < b; i++) {
     const double c = 6 * ((y[i + 1] - y[i]) * rh[i] - (y[i] - y[i - 1]) * rh[i - 1]);
     vp = c - r[i] * vp;
@@ -111,6 +124,7 @@ __global__ void k_cia_wnspline(const double *__restrict__ h, const double *__res
   }
   // ---- backward sweep (each lane reads back only what it wrote)
   A = 1.0; B = 0.0;
+#pragma unroll 8
   for (int i = b - 1; i >= a; i--) {
     B = (vv[i] - h[i] * B) * ru[i];
     A = -h[i] * ru[i] * A;
@@ -122,6 +136,7 @@ __global__ void k_cia_wnspline(const double *__restrict__ h, const double *__res
     carry = Al * carry + Bl;
   }
   double zn = mine;
+#pragma unroll 8
   for (int i = b - 1; i >= a; i--) {
     zn = (vv[i] - h[i] * zn) * ru[i];
     zz[i] = zn;
@@ -309,15 +324,22 @@ int tb_cia_run(tb_ctx *c) {
   }
   TB_TRY(tb_upload_small(c, c->c_stage.p, stage.data(), stage.size() * sizeof(double), st));
   tb_timer_begin(c, "cia");
-  int k = 0;
-  for (int n = 0; n < ntab && k < P.n; n++) {
-    CiaTable *t = c->cia[n];
-    if (P.t[k].f2 != t->d_f2.p) continue;
-    const CiaDev &D = P.t[k++];
-    k_cia_temp<<<nblk((int64_t)t->nw * nrad, 256), 256, 0, st>>>(t->d_tab.p, t->d_zt.p, t->d_temp.p, t->nw, t->nt,
-                                                               c->c_stage.p, nrad, D.fj, D.lj, t->d_f2.p);
-    k_cia_wnspline<<<nblk(D.lj - D.fj, 4), 128, 0, st>>>(t->d_h.p, t->d_rh.p, t->d_r.p, t->d_ru.p, t->nw, D.fj, D.lj,
-                                                         t->d_f2.p, t->d_v.p, t->d_z2.p);
+  if (P.n > 0) {
+    CiaSplinePack S;
+    int k = 0, maxrows = 0, maxlayers = 0;
+    for (int n = 0; n < ntab && k < P.n; n++) {
+      CiaTable *t = c->cia[n];
+      if (P.t[k].f2 != t->d_f2.p) continue;
+      const CiaDev &D = P.t[k];
+      CiaSplineTab &T = S.t[k++];
+      T.tab = t->d_tab.p; T.zt = t->d_zt.p; T.ttemp = t->d_temp.p; T.h = t->d_h.p; T.rh = t->d_rh.p;
+      T.r = t->d_r.p; T.ru = t->d_ru.p; T.f2 = t->d_f2.p; T.v = t->d_v.p; T.z2 = t->d_z2.p;
+      T.ntw = t->nw; T.ntt = t->nt; T.fj = D.fj; T.lj = D.lj;
+      if (t->nw > maxrows) maxrows = t->nw;
+      if (D.lj - D.fj > maxlayers) maxlayers = D.lj - D.fj;
+    }
+    k_cia_temp<<<dim3(nblk((int64_t)maxrows * nrad, 256), k), 256, 0, st>>>(S, c->c_stage.p, nrad);
+    k_cia_wnspline<<<dim3(nblk(maxlayers, 4), k), 128, 0, st>>>(S);
     c->launches += 2;
   }
   dim3 g(nblk(nwn, 256), nrad);
