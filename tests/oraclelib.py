@@ -87,6 +87,10 @@ def lib():
         L.to_tau.argtypes = [C.c_int, f64p, f64p, f64p, C.c_int64, C.c_double, f64p, C.c_int,
                              C.c_double, f64p, C.c_int, C.c_double, f64p, f64p,
                              C.POINTER(Contrib), C.c_double, C.c_int, f64p, i64p, i16p]
+        L.to_totaltau1.restype = C.c_double
+        L.to_totaltau1.argtypes = [C.c_double, f64p, C.c_double, f64p, C.c_long]
+        L.to_eclipsetau.restype = C.c_double
+        L.to_eclipsetau.argtypes = [C.c_double, f64p, f64p, C.c_long]
         L.to_modulation1.restype = C.c_double
         L.to_modulation1.argtypes = [f64p, C.c_long, C.c_double, f64p, C.c_long, C.c_double,
                                      C.c_double, C.c_int]
