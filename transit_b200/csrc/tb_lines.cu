@@ -442,6 +442,7 @@ __device__ __forceinline__ void atomicMaxPosDouble(double *addr, double v) {
 // monotone) cannot raise the maximum found so far skips its two exp(): the maximum stays
 // exact, only the amount of work depends on the visiting order.
 #define KMAX_ROWS 16   // output rows reduced in shared memory (more rows: straight to global)
+#define KMAX_ISO 64    // isotopes whose skip thresholds are tabulated per block in shared memory
 #define KMAX_LPT 8     // lines per thread
 template <int SB>
 __global__ void k_kmax(int64_t l0, int64_t l1, int ns, int niso, const double *__restrict__ q_g,
@@ -452,8 +453,13 @@ __global__ void k_kmax(int64_t l0, int64_t l1, int ns, int niso, const double *_
   // the running maxima are read once per block (not per warp: every warp of the chip asking
   // one L2 slice for the same sector serialises there) and merged back once per block
   __shared__ unsigned long long sh_cur[SB][KMAX_ROWS], sh_new[SB][KMAX_ROWS];
+  // the skip bound (1-1e-10)*cur*mass*z depends on (state, isotope) only once the block has its
+  // snapshot of the maxima: tabulated, the skip path of a (line, state) pair is one shared-memory
+  // read and one comparison (same products in the same order as the inline form: same decisions)
+  __shared__ double sh_thr[SB][KMAX_ISO];
   const int s0 = blockIdx.y * SB;
   const bool use_sh = nrows <= KMAX_ROWS;
+  const bool use_thr = use_sh && niso <= KMAX_ISO;
   if (use_sh) {
     for (int i = threadIdx.x; i < SB * nrows; i += blockDim.x) {
       const int k = i / nrows, r = i % nrows, s = s0 + k;
@@ -462,26 +468,35 @@ __global__ void k_kmax(int64_t l0, int64_t l1, int ns, int niso, const double *_
       sh_new[k][r] = v;
     }
     __syncthreads();
+    if (use_thr) {
+      for (int i = threadIdx.x; i < SB * niso; i += blockDim.x) {
+        const int k = i / niso, iso = i % niso, s = s0 + k;
+        const double cur = __longlong_as_double((long long)sh_cur[k][permol ? iso_row[iso] : 0]);
+        sh_thr[k][iso] = s < ns ? 0.9999999999 * cur * iso_mass[iso] * Z[s * niso + iso] : 0.0;
+      }
+      __syncthreads();
+    }
   }
 #pragma unroll 1
   for (int rep = 0; rep < KMAX_LPT; rep++) {
     const int64_t l = l0 + ((int64_t)blockIdx.x * KMAX_LPT + rep) * blockDim.x + threadIdx.x;
     if (l >= l1) break;
     const int iso = q_iso[l];
-    const double g = q_g[l], mass = iso_mass[iso];
-    const int row = permol ? iso_row[iso] : 0;
+    const double g = q_g[l];
     const double a = q_a[l];      // > 0 only for a (bogus) negative lower-state energy: never skipped
-    double w = 0;
+    double w = 0, mass = 0;
+    int row = 0;
     bool loaded = false;
 #pragma unroll
     for (int k = 0; k < SB; k++) {
       const int s = s0 + k;
       if (s >= ns) break;
+      // g/mass/z <= cur  <=  g < (1-1e-10)*cur*mass*z: no division, no further loads on the skip path
+      if (use_thr) { if (!(a > 0) && g < sh_thr[k][iso]) continue; }
+      if (!loaded) { w = q_w[l]; mass = iso_mass[iso]; row = permol ? iso_row[iso] : 0; loaded = true; }
       const double cur = use_sh ? __longlong_as_double((long long)sh_cur[k][row]) : __ldcg(&kmax[s * nrows + row]);
       const double z = Z[s * niso + iso];
-      // g/mass/z <= cur  <=  g < (1-1e-10)*cur*mass*z: no division, no further loads on the skip path
       if (a > 0 || !(g < 0.9999999999 * cur * mass * z)) {
-        if (!loaded) { w = q_w[l]; loaded = true; }
         const double rT = rtemp[s];
         const double v = g * tb_exp(a * rT) * (1 - tb_exp(w * rT)) / mass / z;
         if (v > cur) {
@@ -998,7 +1013,8 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
     d_out = c->s_out.p;
   }
   const int Tn = 256;
-  constexpr int SB = 4;      // states per block of k_kmax
+  constexpr int SB = 4;      // states per block of k_kmax's seed launch (few lines: more blocks)
+  constexpr int SBB = 10;    // ... and of the bulk launch (line records read once per SBB states)
   constexpr int SBS = 8;     // states per block of k_strength (group records are read once per SBS states)
   auto fastdiv = [](int64_t d) {
     FastDiv f;
@@ -1064,7 +1080,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       const int64_t per = (Mq - seed + c->shard_world - 1) / c->shard_world;
       const int64_t q0 = seed + per * c->shard_rank, q1 = q0 + per < Mq ? q0 + per : Mq;
       if (q1 > q0)
-        k_kmax<SB><<<dim3(nblk(q1 - q0, Tn * KMAX_LPT), (cs + SB - 1) / SB), Tn, 0, st>>>(
+        k_kmax<SBB><<<dim3(nblk(q1 - q0, Tn * KMAX_LPT), (cs + SBB - 1) / SBB), Tn, 0, st>>>(
             q0, q1, cs, niso, c->q_g.p, c->q_a.p, c->q_w.p, c->q_iso.p, c->s_rtemp.p, c->s_Z.p, c->d_iso_mass.p,
             c->d_iso_row.p, permol, nrows, c->s_kmax.p);
       TB_LAUNCHED(c);

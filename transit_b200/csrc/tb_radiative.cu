@@ -748,6 +748,24 @@ __global__ void k_modulation(int64_t nwn, int nh, const double *__restrict__ tau
                              const int32_t *__restrict__ last, const double *__restrict__ ip, double ipfct,
                              double toomuch, double srad, int transp, double *__restrict__ out,
                              int32_t *__restrict__ err) {
+  // The impact parameters and the non-uniform Simpson weights (geth/simpson, numerical.c:390-525)
+  // are the same for every wavenumber: three FP64 divisions per pair of intervals.  A pair is
+  // identified by its innermost ray r (points r, r-1, r-2 in ascending radius) whatever the
+  // cut-off ray of a wavenumber is, so each block tabulates xs[r] = ip[r]*ipfct and
+  // cf[r] = {2-hratio, hfactor, 2-1/hratio, hsum} once in shared memory.
+  extern __shared__ __align__(16) double smod[];
+  double *xs = smod, *cf = smod + ((nh + 1) & ~1);   // 16-byte aligned rows
+  for (int i = threadIdx.x; i < nh; i += blockDim.x) xs[i] = ip[i] * ipfct;
+  __syncthreads();
+  for (int r = 2 + threadIdx.x; r < nh; r += blockDim.x) {
+    const double h0 = xs[r - 1] - xs[r], h1 = xs[r - 2] - xs[r - 1];
+    const double hsum = h0 + h1, hratio = h1 / h0, hfactor = hsum * hsum / (h0 * h1);
+    cf[4 * r + 0] = 2.0 - hratio;
+    cf[4 * r + 1] = hfactor;
+    cf[4 * r + 2] = 2.0 - 1.0 / hratio;
+    cf[4 * r + 3] = hsum;
+  }
+  __syncthreads();
   int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (w >= nwn) return;
   const int L0 = last[w];
@@ -756,27 +774,29 @@ __global__ void k_modulation(int64_t nwn, int nh, const double *__restrict__ tau
   const int n = L1 + 1;                                 // points handed to simps (slantpath.c:392-408)
   if (n < 3) { atomicExch(err + 2, 1); out[w] = 0; return; }
   // point k (ascending radius) is ray i = n-1-k; integrand exp(-tau_i)*ip_i for i<=L0, else 0
-  auto X = [&](int k) { return ip[n - 1 - k] * ipfct; };
-  auto Y = [&](int k) { int i = n - 1 - k; return (i <= L0) ? exp(-tau[(size_t)i * nwn + w]) * (ip[i] * ipfct) : 0.0; };
+  auto Y = [&](int i) { return (i <= L0) ? exp(-tau[(size_t)i * nwn + w]) * xs[i] : 0.0; };
   const int even = (n % 2 == 0);
   double res = 0.0;
-  for (int i = 0; i < (n - 1) / 2; i++) {
-    const int j = 2 * i + even;
-    const double h0 = X(j + 1) - X(j), h1 = X(j + 2) - X(j + 1);
-    const double hsum = h0 + h1, hratio = h1 / h0, hfactor = hsum * hsum / (h0 * h1);
-    res += (Y(j) * (2.0 - hratio) + Y(j + 1) * hfactor + Y(j + 2) * (2.0 - 1.0 / hratio)) * hsum;
+  int r = n - 1 - even;                                 // innermost ray of the first pair
+  double y0 = Y(r);
+  for (int i = 0; i < (n - 1) / 2; i++, r -= 2) {
+    const double y1 = Y(r - 1), y2 = Y(r - 2);
+    const double2 c01 = *reinterpret_cast<const double2 *>(cf + 4 * r);
+    const double2 c23 = *reinterpret_cast<const double2 *>(cf + 4 * r + 2);
+    res += (y0 * c01.x + y1 * c01.y + y2 * c23.x) * c23.y;
+    y0 = y2;
   }
   double integ = res / 6.0;
-  if (even) integ += (X(1) - X(0)) * (Y(0) + Y(1)) / 2;
-  const double rtop = ip[0] * ipfct;
-  double r = rtop * rtop - 2.0 * integ;
+  if (even) integ += (xs[n - 2] - xs[n - 1]) * (Y(n - 1) + Y(n - 2)) / 2;
+  const double rtop = xs[0];
+  double rr = rtop * rtop - 2.0 * integ;
   if (transp) {
     const double tl = tau[(size_t)L0 * nwn + w];
     const double maxtau = tl > toomuch ? tl : toomuch;
-    const double rb = X(0);
-    r -= exp(-maxtau) * rb * rb;
+    const double rb = xs[n - 1];
+    rr -= exp(-maxtau) * rb * rb;
   }
-  out[w] = r * (1.0 / (srad * srad));
+  out[w] = rr * (1.0 / (srad * srad));
 }
 
 extern "C" int tb_modulation(tb_ctx *c, double starrad_cm, int transparent, double *out) {
@@ -788,7 +808,9 @@ extern "C" int tb_modulation(tb_ctx *c, double starrad_cm, int transparent, doub
   TB_TRY(c->d_out.ensure(c->nwn));
   TB_TRY(tb_upload_small(c, d_ip.p, c->h_h.data(), c->nh * sizeof(double), st));
   tb_timer_begin(c, "modulation");
-  k_modulation<<<nblk(c->nwn, 128), 128, 0, st>>>(c->nwn, c->nh, c->d_tau.p, c->d_last.p, d_ip.p, c->hfct, c->toomuch,
+  const size_t shm = (5 * (size_t)c->nh + 2) * sizeof(double);   // xs[nh] (padded to even) + cf[4*nh]
+  TB_REQUIRE(shm <= 48 * 1024, TB_ERR_ARG, "too many rays (%d) for the modulation kernel's shared memory", c->nh);
+  k_modulation<<<nblk(c->nwn, 128), 128, shm, st>>>(c->nwn, c->nh, c->d_tau.p, c->d_last.p, d_ip.p, c->hfct, c->toomuch,
                                                   starrad_cm, transparent, c->d_out.p, c->d_err.p);
   tb_timer_end(c, "modulation");
   TB_LAUNCHED(c);
