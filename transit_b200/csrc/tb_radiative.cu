@@ -744,6 +744,7 @@ extern "C" int tb_tau(tb_ctx *c, int geometry, double toomuch, const double *h, 
 
 // =============================================================== modulation (a14)
 
+#define MOD_QL 4   // lanes per wavenumber in k_modulation
 __global__ void k_modulation(int64_t nwn, int nh, const double *__restrict__ tau,
                              const int32_t *__restrict__ last, const double *__restrict__ ip, double ipfct,
                              double toomuch, double srad, int transp, double *__restrict__ out,
@@ -766,26 +767,39 @@ __global__ void k_modulation(int64_t nwn, int nh, const double *__restrict__ tau
     cf[4 * r + 3] = hsum;
   }
   __syncthreads();
-  int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (w >= nwn) return;
+  // MOD_QL lanes share a wavenumber: each integrates a contiguous quarter of the pairs (a dependent
+  // exp-and-add chain of ~50 pairs per wavenumber left the machine at 10 % occupancy with one lane
+  // each); the partial sums are added in a fixed butterfly, lane 0 of the quad finishes.
+  const int64_t wq = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / MOD_QL;
+  const int ql = threadIdx.x & (MOD_QL - 1);
+  const bool inb = wq < nwn;
+  const int64_t w = inb ? wq : nwn - 1;
   const int L0 = last[w];
   int L1 = L0 + 1;
   if (L1 > nh - 1) L1 = nh - 1;
   const int n = L1 + 1;                                 // points handed to simps (slantpath.c:392-408)
-  if (n < 3) { atomicExch(err + 2, 1); out[w] = 0; return; }
+  const bool bad = n < 3;
   // point k (ascending radius) is ray i = n-1-k; integrand exp(-tau_i)*ip_i for i<=L0, else 0
   auto Y = [&](int i) { return (i <= L0) ? exp(-tau[(size_t)i * nwn + w]) * xs[i] : 0.0; };
   const int even = (n % 2 == 0);
+  const int np = bad ? 0 : (n - 1) / 2;
+  const int i0 = (np * ql) / MOD_QL, i1 = (np * (ql + 1)) / MOD_QL;
   double res = 0.0;
-  int r = n - 1 - even;                                 // innermost ray of the first pair
-  double y0 = Y(r);
-  for (int i = 0; i < (n - 1) / 2; i++, r -= 2) {
-    const double y1 = Y(r - 1), y2 = Y(r - 2);
-    const double2 c01 = *reinterpret_cast<const double2 *>(cf + 4 * r);
-    const double2 c23 = *reinterpret_cast<const double2 *>(cf + 4 * r + 2);
-    res += (y0 * c01.x + y1 * c01.y + y2 * c23.x) * c23.y;
-    y0 = y2;
+  if (i1 > i0) {
+    int r = n - 1 - even - 2 * i0;                      // innermost ray of this lane's first pair
+    double y0 = Y(r);
+    for (int i = i0; i < i1; i++, r -= 2) {
+      const double y1 = Y(r - 1), y2 = Y(r - 2);
+      const double2 c01 = *reinterpret_cast<const double2 *>(cf + 4 * r);
+      const double2 c23 = *reinterpret_cast<const double2 *>(cf + 4 * r + 2);
+      res += (y0 * c01.x + y1 * c01.y + y2 * c23.x) * c23.y;
+      y0 = y2;
+    }
   }
+#pragma unroll
+  for (int d = 1; d < MOD_QL; d <<= 1) res += __shfl_xor_sync(0xffffffffu, res, d);
+  if (!inb || ql != 0) return;
+  if (bad) { atomicExch(err + 2, 1); out[w] = 0; return; }
   double integ = res / 6.0;
   if (even) integ += (xs[n - 2] - xs[n - 1]) * (Y(n - 1) + Y(n - 2)) / 2;
   const double rtop = xs[0];
@@ -810,7 +824,7 @@ extern "C" int tb_modulation(tb_ctx *c, double starrad_cm, int transparent, doub
   tb_timer_begin(c, "modulation");
   const size_t shm = (5 * (size_t)c->nh + 2) * sizeof(double);   // xs[nh] (padded to even) + cf[4*nh]
   TB_REQUIRE(shm <= 48 * 1024, TB_ERR_ARG, "too many rays (%d) for the modulation kernel's shared memory", c->nh);
-  k_modulation<<<nblk(c->nwn, 128), 128, shm, st>>>(c->nwn, c->nh, c->d_tau.p, c->d_last.p, d_ip.p, c->hfct, c->toomuch,
+  k_modulation<<<nblk(c->nwn * MOD_QL, 128), 128, shm, st>>>(c->nwn, c->nh, c->d_tau.p, c->d_last.p, d_ip.p, c->hfct, c->toomuch,
                                                   starrad_cm, transparent, c->d_out.p, c->d_err.p);
   tb_timer_end(c, "modulation");
   TB_LAUNCHED(c);
