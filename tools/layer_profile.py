@@ -1,6 +1,6 @@
 """Per-layer cost of the line sum on C2: each layer's state replicated NREP times in one batch,
 device time of k_strength / k_accumulate / k_kmax per replica, samples per state.
-usage: python tools/layer_profile.py [NREP] [step] [layer,layer,...]"""
+usage: python tools/layer_profile.py [NREP] [step] [layer,layer,...|-] [config]"""
 import sys, os
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -8,7 +8,7 @@ from transit_b200 import api, workloads
 
 nrep = int(sys.argv[1]) if len(sys.argv) > 1 else 20
 step = int(sys.argv[2]) if len(sys.argv) > 2 else 5
-prob = workloads.make_problem("C2")
+prob = workloads.make_problem(sys.argv[4] if len(sys.argv) > 4 else "C2")
 c = api.Context(0)
 c.set_wn_grid(prob.wn_i, prob.wn_d, prob.wnosamp, prob.nwn, prob.onwn, prob.wn_fct)
 c.set_species(prob.mol_mass, prob.mol_radius, prob.mol_pol, prob.mol_ID, prob.iso_mass, prob.iso_ratio, prob.iso_imol)
@@ -16,7 +16,7 @@ c.upload_lines(prob.wl, prob.elow, prob.gf, prob.isoid, prob.wfct, prob.efct)
 c.build_profiles(60, 60, 1e-3, 0.25, 1e-4, 10.0, prob.nwidth)
 print("layer  p[bar]      T   samples/state   strength_us accumulate_us kmax_us  (per state)")
 tot = {"strength": 0.0, "accumulate": 0.0, "kmax": 0.0}
-layers = [int(x) for x in sys.argv[3].split(",")] if len(sys.argv) > 3 else range(0, prob.nrad, step)
+layers = [int(x) for x in sys.argv[3].split(",")] if len(sys.argv) > 3 and sys.argv[3] != "-" else range(0, prob.nrad, step)
 for r in layers:
     T = np.full(nrep, prob.t[r] * prob.t_fct)
     d = np.tile(prob.mol_d[:, r], (nrep, 1))
