@@ -212,6 +212,8 @@ struct tb_ctx {
   DevBuf<LineRec> s_rec;      // [state][group]
   DevBuf<uint8_t> s_hasfb;    // [state][tile]
   DevBuf<unsigned long long> s_nsamp;
+  DevBuf<double> s_part;      // partial sums of wide-reach tiles shared by several blocks (small grids)
+  DevBuf<unsigned> s_tcnt;    // ... and their arrival counters
   DevBuf<double> s_out;
   int last_ns = 0, last_permol = 0;
   bool nsamp_valid = false;

@@ -821,7 +821,9 @@ struct AccRec {
 struct WideShared {
   AccRec rec[ACC_WW][32];
   double part[ACC_WW][ACC_TILE];
+  unsigned ticket;
 };
+#define ACC_SPLIT_MAX 8                    // blocks that may share one wide-reach tile on a small grid
 
 // Two instances over the same (tile, state) grid: WIDE = false runs 128 threads and takes the tiles
 // of narrow reach (and zero-fills the tiles nothing reaches), WIDE = true runs ACC_WW warps and takes
@@ -835,10 +837,14 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
              const int32_t *__restrict__ fbpid, const ProfEntry *__restrict__ ptab,
              const int32_t *__restrict__ reach, const int32_t *__restrict__ reachP,
              const double *__restrict__ pdata, double *__restrict__ out,
-             unsigned long long *__restrict__ nsamp) {
+             unsigned long long *__restrict__ nsamp, int S, double *__restrict__ part_g,
+             unsigned *__restrict__ tilecnt) {
   const int s = blockIdx.y;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tile = blockIdx.x + tile_off;          // a band shard launches only its own tiles
+  // S > 1 (wide instance on a grid of few tiles): S blocks share a tile, block k of them takes the
+  // segments k*ACC_WW .. k*ACC_WW+ACC_WW-1 of the window's S*ACC_WW record segments
+  const int ksplit = S > 1 ? (int)(blockIdx.x % S) : 0;
+  const int tile = (S > 1 ? (int)(blockIdx.x / S) : (int)blockIdx.x) + tile_off;   // a band shard launches only its own tiles
   const int64_t jt = (int64_t)tile * ACC_TILE;
   const int64_t j = jt + tid;
   const bool inb = j < nwn && tid < ACC_TILE;
@@ -905,8 +911,10 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
     for (int row = 0; row < nrows; row++) {
       const int32_t *bs = binstart + (size_t)row * nwn;
       const int p0 = bs[ulo], p1 = bs[uhi];
-      const int seg = (((p1 - p0 + ACC_WW - 1) / ACC_WW) + 31) & ~31;   // records per warp, whole chunks
-      const int pa = p0 + warp * seg;
+      const int nseg = ACC_WW * S;
+      const int seg = (((p1 - p0 + nseg - 1) / nseg) + 31) & ~31;       // records per warp, whole chunks
+      const int pa0 = p0 + (ksplit * ACC_WW + warp) * seg;
+      const int pa = pa0 < p1 ? pa0 : p1;
       const int pb = pa + seg < p1 ? pa + seg : p1;
       for (int base = pa; base < pb; base += 32) {
         const int p = base + lane;
@@ -953,11 +961,32 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
 #pragma unroll
         for (int q = 0; q < ACC_TILE / 32; q++) { w.part[warp][lane + 32 * q] = acc[q]; acc[q] = 0.0; }
         __syncthreads();
-        if (inb) {
-          double v = w.part[0][threadIdx.x];
+        const size_t orow = (size_t)s * (permol ? nrows : 1) + (permol ? row : 0);
+        double v = 0.0;
+        if (tid < ACC_TILE) {
+          v = w.part[0][tid];
 #pragma unroll
-          for (int g = 1; g < ACC_WW; g++) v += w.part[g][threadIdx.x];
-          out[((size_t)s * (permol ? nrows : 1) + (permol ? row : 0)) * nwn + j] = v;
+          for (int g = 1; g < ACC_WW; g++) v += w.part[g][tid];
+        }
+        if (S == 1) {
+          if (inb) out[orow * nwn + j] = v;
+        } else {
+          // the S partial sums of a tile meet in global memory; the block that arrives last adds
+          // them in split order (a fixed order whichever block that is)
+          double *pt = part_g + ((orow * ntiles + tile) * S) * ACC_TILE;
+          if (tid < ACC_TILE) pt[(size_t)ksplit * ACC_TILE + tid] = v;
+          __threadfence();
+          __syncthreads();
+          if (tid == 0) w.ticket = atomicAdd(&tilecnt[orow * ntiles + tile], 1u);
+          __syncthreads();
+          if (w.ticket == (unsigned)(S - 1)) {
+            __threadfence();
+            if (inb) {
+              double t = __ldcg(pt + tid);
+              for (int k2 = 1; k2 < S; k2++) t += __ldcg(pt + (size_t)k2 * ACC_TILE + tid);
+              out[orow * nwn + j] = t;
+            }
+          }
         }
         __syncthreads();
       }
@@ -1131,16 +1160,32 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
     if (banded)    // bins outside the band come back as zero
       TB_CUDA(cudaMemsetAsync(dst, 0, (size_t)cs * nout * nwn * sizeof(double), st));
     dim3 g4(tile_hi - tile_lo, cs);
+    // A grid of few tiles leaves the wide-reach instance one block per (tile, deep layer): the deepest
+    // layers of C1 (20 tiles) each ran 0.7 ms on 20 SMs.  There S blocks share a tile.  S depends on
+    // the WHOLE grid, the chunk of states and the row count only, never on the band of a shard, so a
+    // banded run adds in the same order as a single GPU.
+    int S = 1;
+    if (ntiles < 128) {
+      S = (256 + ntiles - 1) / ntiles;
+      if (S > ACC_SPLIT_MAX) S = ACC_SPLIT_MAX;
+      if ((size_t)S * chunk * nout * ntiles * ACC_TILE * sizeof(double) > ((size_t)1 << 30)) S = 1;
+    }
+    if (S > 1) {
+      TB_TRY(c->s_part.ensure((size_t)S * chunk * nout * ntiles * ACC_TILE));
+      TB_TRY(c->s_tcnt.ensure((size_t)chunk * nout * ntiles));
+      TB_CUDA(cudaMemsetAsync(c->s_tcnt.p, 0, (size_t)cs * nout * ntiles * sizeof(unsigned), st));
+    }
     tb_timer_begin(c, "accumulate");
     if (tile_hi > tile_lo) {
-      k_accumulate<true><<<g4, 32 * ACC_WW, 0, st>>>(nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, tile_lo, c->binstart.p,
+      k_accumulate<true><<<dim3((tile_hi - tile_lo) * S, cs), 32 * ACC_WW, 0, st>>>(
+                                          nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, tile_lo, c->binstart.p,
                                           c->substart.p, c->nsub, c->nsube, c->s_rec.p, c->s_fbpid.p, c->d_ptab.p,
                                           c->s_reach.p, c->s_reachP.p, c->d_pdata2.p, dst,
-                                          c->s_nsamp.p + s0);
+                                          c->s_nsamp.p + s0, S, c->s_part.p, c->s_tcnt.p);
       k_accumulate<false><<<g4, ACC_TILE, 0, st>>>(nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, tile_lo, c->binstart.p,
                                           c->substart.p, c->nsub, c->nsube, c->s_rec.p, c->s_fbpid.p, c->d_ptab.p,
                                           c->s_reach.p, c->s_reachP.p, c->d_pdata2.p, dst,
-                                          c->s_nsamp.p + s0);
+                                          c->s_nsamp.p + s0, 1, nullptr, nullptr);
     }
     tb_timer_end(c, "accumulate");
     c->launches += 3;
