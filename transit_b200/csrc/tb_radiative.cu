@@ -835,13 +835,20 @@ extern "C" int tb_modulation(tb_ctx *c, double starrad_cm, int transparent, doub
 // =============================================================== intensity + flux (a15)
 
 #define TB_MAXANG 16
+// QL lanes share a wavenumber, each integrating a contiguous part of the layers (a grid of a few
+// thousand wavenumbers leaves one lane per wavenumber a chain of ~600 exp() on a nearly empty
+// machine); the trapezoid partial sums are added in a fixed butterfly, the lane holding the last
+// layer finishes.  QL = 1 is the plain loop (large grids: enough wavenumbers to fill the machine).
+template <int QL>
 __global__ void k_intensity_flux(int64_t nwn, int nrad, const double *__restrict__ tau,
                                  const int32_t *__restrict__ last, const double *__restrict__ temp,
                                  double wn_i, double wn_d, double wn_fct, int nang,
                                  const double *__restrict__ ang, const double *__restrict__ area,
                                  double *__restrict__ intens, double *__restrict__ out) {
-  int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (w >= nwn) return;
+  const int64_t wq = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / QL;
+  const int ql = threadIdx.x & (QL - 1);
+  const bool inb = wq < nwn;
+  const int64_t w = inb ? wq : nwn - 1;
   const int L = last[w];
   const double wv = __dadd_rn(wn_i, __dmul_rn((double)w, wn_d));   // wns.v[w]
   const double ww = wv * wn_fct;
@@ -849,16 +856,26 @@ __global__ void k_intensity_flux(int64_t nwn, int nrad, const double *__restrict
   double icos[TB_MAXANG], dprev[TB_MAXANG], tz[TB_MAXANG];
   for (int a = 0; a < nang; a++) { icos[a] = cos(ang[a] * TB_DEGREES); tz[a] = 0; dprev[a] = 0; }
   double Bprev = 0;
-  for (int i = 0; i <= L; i++) {
+  const int n = L + 1;
+  const int i0 = (n * ql) / QL, i1 = (n * (ql + 1)) / QL;
+  // a lane that does not start at the top first evaluates the point before its part
+  for (int i = (i0 > 0 ? i0 - 1 : 0); i < i1; i++) {
     const double t = tau[(size_t)i * nwn + w];
     const double B = num / (exp(TB_H * ww * TB_LS / (TB_KB * temp[nrad - 1 - i])) - 1.0);
     for (int a = 0; a < nang; a++) {
       const double dt = exp(-t / icos[a]);
-      if (i > 0) tz[a] += (dt - dprev[a]) * (B + Bprev);             // integ_trapz, numerical.c:168-170
+      if (i >= i0 && i > 0) tz[a] += (dt - dprev[a]) * (B + Bprev);  // integ_trapz, numerical.c:168-170
       dprev[a] = dt;
     }
     Bprev = B;
   }
+  if (QL > 1) {
+    for (int a = 0; a < nang; a++) {
+#pragma unroll
+      for (int d = 1; d < QL; d <<= 1) tz[a] += __shfl_xor_sync(0xffffffffu, tz[a], d);
+    }
+  }
+  if (!inb || ql != QL - 1) return;       // the last lane holds the last layer (i1 = n, n >= 1)
   double f = 0;
   for (int a = 0; a < nang; a++) {
     const double I = Bprev * dprev[a] - 0.5 * tz[a];                  // eclipse.c:158
@@ -886,9 +903,14 @@ extern "C" int tb_intensity_flux(tb_ctx *c, const double *angles_deg, int nang, 
   TB_TRY(tb_upload_small(c, d_a.p, ang.data(), nang * sizeof(double), st));
   TB_TRY(tb_upload_small(c, d_a.p + nang, area.data(), nang * sizeof(double), st));
   tb_timer_begin(c, "intensity");
-  k_intensity_flux<<<nblk(c->nwn, 128), 128, 0, st>>>(c->nwn, c->nrad, c->d_tau.p, c->d_last.p, c->d_t.p, c->wn_i,
-                                                      c->wn_d, c->wn_fct, nang, d_a.p, d_a.p + nang, c->d_intens.p,
-                                                      c->d_out.p);
+  if (c->nwn < 100000)
+    k_intensity_flux<8><<<nblk(c->nwn * 8, 128), 128, 0, st>>>(c->nwn, c->nrad, c->d_tau.p, c->d_last.p, c->d_t.p, c->wn_i,
+                                                            c->wn_d, c->wn_fct, nang, d_a.p, d_a.p + nang, c->d_intens.p,
+                                                            c->d_out.p);
+  else
+    k_intensity_flux<1><<<nblk(c->nwn, 128), 128, 0, st>>>(c->nwn, c->nrad, c->d_tau.p, c->d_last.p, c->d_t.p, c->wn_i,
+                                                        c->wn_d, c->wn_fct, nang, d_a.p, d_a.p + nang, c->d_intens.p,
+                                                        c->d_out.p);
   tb_timer_end(c, "intensity");
   TB_LAUNCHED(c);
   if (out) TB_CUDA(cudaMemcpyAsync(out, c->d_out.p, c->nwn * sizeof(double), cudaMemcpyDeviceToHost, st));
