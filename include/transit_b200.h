@@ -121,6 +121,17 @@ int  tb_intensity_flux(tb_ctx *c, const double *angles_deg, int nang, double *ou
 int  tb_spectrum(tb_ctx *c, int geometry, double toomuch, double ethresh, double starrad_cm,
                  int transparent, const double *angles_deg, int nang, double *out);
 
+/* run_transit (transit.c:118-122) for a batch of atmospheres, as a retrieval hands them over one by
+ * one: atmosphere a is the a-th slice of rad[natm][nrad], p, t, density[natm][nmol][nrad],
+ * Z[natm][niso][nrad] (each slice as tb_set_atmosphere takes it).  The spectra are computed back to
+ * back with no host synchronisation in between; out[natm][nwn].  Results are those of natm calls of
+ * tb_set_atmosphere + tb_spectrum.                                                       */
+int  tb_spectrum_batch(tb_ctx *c, int natm, int nrad, const double *rad, double rad_fct,
+                       const double *p, double p_fct, const double *t, double t_fct,
+                       const double *density, const double *Z, int geometry, double toomuch,
+                       double ethresh, double starrad_cm, int transparent,
+                       const double *angles_deg, int nang, double *out);
+
 /* test taps in the reference's layouts                                                */
 int  tb_get_extinction(tb_ctx *c, double *e /*[nrad][nwn]*/);
 int  tb_get_cia(tb_ctx *c, double *e_cs /*[nwn][nrad]*/);

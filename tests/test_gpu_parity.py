@@ -423,6 +423,7 @@ def test_retrieval_batch_from_grid_vs_oracle():
         dens = api.AMU * prob.mol_q[:, r] * (prob.p[r] * prob.p_fct) / api.KB / gtemp[it] * prob.mol_mass
         o = O.computemolext(pr0, vt, float(gtemp[it]), dens, ziso[:, it], prob.ethresh, permol=1, molID=molID)
         assert relerr(grid[r, it], o) < EXT_RTOL
+    singles, atms = [], []
     for seed in (11, 12, 13):
         a = workloads.perturbed(prob, seed=seed, dT=150.0, dex=1.0)
         c.set_atmosphere(a.rad, a.rad_fct, a.p, a.p_fct, a.t, a.t_fct, a.mol_d, a.iso_z)
@@ -434,6 +435,17 @@ def test_retrieval_batch_from_grid_vs_oracle():
         tg, lastg = c.get_tau()
         assert np.array_equal(lastg, last0)
         assert relerr(out, O.modulation(pr, t0, last0)) < SPEC_RTOL
+        singles.append(out.copy()); atms.append(a)
+    # the same atmospheres through ONE tb_spectrum_batch call: bit-identical spectra, and a ray below
+    # the bottom layer anywhere in the batch is still reported (one error read-back per batch)
+    st = lambda k: np.stack([getattr(x, k) for x in atms])
+    outb = c.spectrum_batch(st("rad"), prob.rad_fct, st("p"), prob.p_fct, st("t"), prob.t_fct, st("mol_d"), st("iso_z"),
+                            api.GEOM_TRANSIT, prob.toomuch, prob.ethresh, prob.starrad, prob.transp)
+    assert np.array_equal(outb, np.stack(singles))
+    out1 = c.spectrum_batch(st("rad")[1:2], prob.rad_fct, st("p")[1:2], prob.p_fct, st("t")[1:2], prob.t_fct,
+                            st("mol_d")[1:2], st("iso_z")[1:2], api.GEOM_TRANSIT, prob.toomuch, prob.ethresh,
+                            prob.starrad, prob.transp)
+    assert np.array_equal(out1[0], singles[1])
     c.close()
 
 

@@ -128,8 +128,30 @@ def run_c5(bench, args):
     kms = {}
     pool = ThreadPoolExecutor(K)
 
+    # --c5-api batch: each context takes a contiguous share of the step's atmospheres through ONE
+    # tb_spectrum_batch call (no host synchronisation between its spectra); "single": one
+    # tb_set_atmosphere + tb_spectrum per atmosphere, as BART calls run_transit
+    use_batch = getattr(args, "c5_api", "single") == "batch"
+    share = [list(range(k * batch // K, (k + 1) * batch // K)) for k in range(K)]
+    stacked = {}
+
+    def stack(i, k):
+        key = (i * batch) % len(atms), k
+        if key not in stacked:
+            sel = [atms[(i * batch + b) % len(atms)] for b in share[k]]
+            stacked[key] = tuple(np.stack([np.asarray(getattr(x, f), np.float64) for x in sel])
+                                 for f in ("rad", "p", "t", "mol_d", "iso_z"))
+        return stacked[key]
+
     def work(k, i):
         tr = trs[k]
+        if use_batch:
+            if share[k]:
+                rad, p, t, d, z = stack(i, k)               # host arrays; H2D inside the call, D2H of the spectra at its end
+                tr.ctx.spectrum_batch(rad, prob.rad_fct, p, prob.p_fct, t, prob.t_fct, d, z, api.GEOM_TRANSIT,
+                                      prob.toomuch, prob.ethresh, prob.starrad, prob.transp, None,
+                                      out[share[k][0]:share[k][-1] + 1])
+            return
         for b in range(k, batch, K):
             a = atms[(i * batch + b) % len(atms)]
             tr.set_atmosphere(a)                          # H2D: T, p, radii, densities, partition functions
@@ -182,6 +204,7 @@ def run_c5(bench, args):
             "config": {"workload": "C5: BART-style retrieval, perturbed T-P/abundance profiles through opacity-grid "
                                    "interpolation + CIA + tau + modulation (C2 grid)", "natm": args.natm,
                        "batch_per_rank_per_step": batch, "contexts_per_gpu": K,
+                       "api": "tb_spectrum_batch (one call per context per step)" if use_batch else "tb_set_atmosphere + tb_spectrum per atmosphere",
                        "sharding": f"atmospheres x{world}", "nwn": int(prob.nwn),
                        "layers": int(prob.nrad), "grid": [int(prob.nrad), len(GRID_TEMPS), nm, int(prob.nwn)],
                        "grid_gb": grid_bytes / 1e9, "grid_build_s": build_s, "l2": "flushed between steps"},

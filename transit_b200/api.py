@@ -63,6 +63,8 @@ ABI = {
     "tb_modulation": (C.c_int, [C.c_void_p, C.c_double, C.c_int, f64p]),
     "tb_intensity_flux": (C.c_int, [C.c_void_p, f64p, C.c_int, f64p]),
     "tb_spectrum": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, f64p, C.c_int, f64p]),
+    "tb_spectrum_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_int, f64p, C.c_double, f64p, C.c_double, f64p, C.c_double,
+                                    f64p, f64p, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, f64p, C.c_int, f64p]),
     "tb_get_extinction": (C.c_int, [C.c_void_p, f64p]),
     "tb_get_cia": (C.c_int, [C.c_void_p, f64p]),
     "tb_get_tau": (C.c_int, [C.c_void_p, f64p, i64p]),
@@ -299,6 +301,27 @@ class Context:
         return out
 
     # -- taps ---------------------------------------------------------------------------
+    def spectrum_batch(self, rad, rad_fct, p, p_fct, t, t_fct, density, Z, geometry, toomuch, ethresh,
+                       starrad_cm=1.0, transparent=0, angles_deg=None, out=None):
+        """natm atmospheres in one call: rad/p/t [natm][nrad], density [natm][nmol][nrad], Z [natm][niso][nrad]."""
+        rad, p, t, density = _c64(rad), _c64(p), _c64(t), _c64(density)
+        Z = None if Z is None else _c64(Z)
+        natm, nrad = rad.shape
+        assert p.shape == (natm, nrad) and t.shape == (natm, nrad) and density.shape == (natm, self.nmol, nrad)
+        assert Z is None or Z.shape == (natm, self.niso, nrad)
+        a = None if angles_deg is None else _c64(angles_deg)
+        out = np.zeros((natm, self.nwn)) if out is None else out
+        assert out.shape == (natm, self.nwn) and out.flags.c_contiguous
+        if a is not None:
+            self.nang = len(a)
+        self._ck(self.lib.tb_spectrum_batch(self.h, natm, nrad, _p(rad), rad_fct, _p(p), p_fct, _p(t), t_fct,
+                                            _p(density), _p(Z), geometry, toomuch, ethresh, starrad_cm,
+                                            int(transparent), _p(a), 0 if a is None else len(a), _p(out)),
+                 "tb_spectrum_batch")
+        self.nrad = nrad
+        self.nh = nrad
+        return out
+
     def get_extinction(self):
         e = np.zeros((self.nrad, self.nwn))
         self._ck(self.lib.tb_get_extinction(self.h, _p(e)), "tb_get_extinction")
@@ -424,6 +447,16 @@ class Transit:
         geom = GEOM_ECLIPSE if p.eclipse else GEOM_TRANSIT
         return self.ctx.spectrum(geom, p.toomuch, p.ethresh, p.starrad, p.transp,
                                  getattr(p, "angles", None) if p.eclipse else None, out)
+
+    def run_batch(self, atms, out=None):
+        """do_transit for a list of sampled atmospheres (same layers and units as the configured one) through
+        one tb_spectrum_batch call; out[natm][nwn]."""
+        p = self.prob
+        geom = GEOM_ECLIPSE if p.eclipse else GEOM_TRANSIT
+        st = lambda k: np.stack([np.asarray(getattr(x, k), np.float64) for x in atms])
+        return self.ctx.spectrum_batch(st("rad"), p.rad_fct, st("p"), p.p_fct, st("t"), p.t_fct, st("mol_d"), st("iso_z"),
+                                       geom, p.toomuch, p.ethresh, p.starrad, p.transp,
+                                       getattr(p, "angles", None) if p.eclipse else None, out)
 
     def free_memory(self):
         self.ctx.close()

@@ -222,6 +222,8 @@ struct tb_ctx {
   DevBuf<double> d_e, d_ecs, d_tau, d_intens, d_out;
   DevBuf<int32_t> d_last;
   DevBuf<int32_t> d_err;
+  bool defer_check = false, err_keep = false;   // tb_spectrum_batch: one error read-back per batch
+  DevBuf<double> d_out_batch;
   bool have_e = false, have_ecs = false, have_tau = false;
   int nh = 0, geometry = 0, nang = 0;
   double toomuch = 0;

@@ -695,7 +695,7 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
   if ((int)c->nH.size() == nrad) for (int i = 0; i < nrad; i++) { aux[i] = c->nH[i]; aux[nrad + i] = c->mean_dens[i]; }
   TB_TRY(tb_upload_small(c, c->d_es_aux.p, aux.data(), aux.size() * sizeof(double), st));
   TB_TRY(tb_upload_small(c, d_h.p, c->h_h.data(), nh * sizeof(double), st));
-  TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4 * sizeof(int32_t), st));
+  if (!c->err_keep) TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4 * sizeof(int32_t), st));
   TB_CUDA(cudaMemsetAsync(c->d_tau.p, 0, sizeof(double) * nh * nwn, st));   // calloc, tau.c:34
   k_ray_geometry<<<nblk(nh, 64), 64, 0, st>>>(geometry == TB_GEOM_ECLIPSE, c->d_rad.p, nrad, c->rad_fct, d_h.p, nh,
                                               hfct, stride, c->r_meta.p, c->r_par.p, c->r_coef.p, d_s.p, c->r_rcp.p, c->d_err.p);
@@ -730,6 +730,7 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
 
 // device-side error flags (set by k_ray_geometry / k_modulation), read back with one sync
 int tb_check_errors(tb_ctx *c) {
+  if (c->defer_check) return TB_OK;          // inside a batch: flags accumulate, read back once
   int32_t err[4];
   TB_CUDA(cudaMemcpyAsync(err, c->d_err.p, sizeof(err), cudaMemcpyDeviceToHost, c->stream));
   TB_CUDA(cudaStreamSynchronize(c->stream));
@@ -941,4 +942,40 @@ extern "C" int tb_spectrum(tb_ctx *c, int geometry, double toomuch, double ethre
   TB_TRY(tb_tau_run(c, geometry, toomuch, nullptr, 0, 0, false));   // tau, transit.c:165,189
   if (geometry == TB_GEOM_ECLIPSE) return tb_intensity_flux(c, angles_deg, nang, out);
   return tb_modulation(c, starrad_cm, transparent, out);
+}
+
+// run_transit for a batch of atmospheres (BART hands a retrieval chain's samples one by one through
+// transit.c:118-122; SURVEY 8b asks for `*_batched` entry points): atmosphere a is the a-th slice
+// of each array, laid out as tb_set_atmosphere takes one.  The spectra are computed back to back on
+// the context's stream -- no host synchronisation, error read-back or device->host copy between
+// atmospheres -- and delivered to out[natm][nwn] with one copy.  Same kernels, same results as natm
+// calls of tb_set_atmosphere + tb_spectrum.
+extern "C" int tb_spectrum_batch(tb_ctx *c, int natm, int nrad, const double *rad, double rad_fct,
+                                 const double *p, double p_fct, const double *t, double t_fct,
+                                 const double *density, const double *Z, int geometry, double toomuch,
+                                 double ethresh, double starrad_cm, int transparent,
+                                 const double *angles_deg, int nang, double *out) {
+  TB_REQUIRE(natm >= 1 && nrad >= 1 && rad && p && t && density && out, TB_ERR_ARG, "tb_spectrum_batch: bad arguments");
+  TB_REQUIRE(c->have_species && c->have_grid, TB_ERR_STATE, "grid and species must be set before tb_spectrum_batch");
+  TB_CUDA(cudaSetDevice(c->device));
+  const int64_t nwn = c->nwn;
+  TB_TRY(c->d_out_batch.ensure((size_t)natm * nwn));
+  int rc = TB_OK;
+  c->defer_check = true;
+  for (int a = 0; a < natm && rc == TB_OK; a++) {
+    c->err_keep = a > 0;
+    rc = tb_set_atmosphere(c, nrad, rad + (size_t)a * nrad, rad_fct, p + (size_t)a * nrad, p_fct,
+                           t + (size_t)a * nrad, t_fct, density + (size_t)a * c->nmol * nrad,
+                           Z ? Z + (size_t)a * c->niso * nrad : nullptr);
+    if (rc == TB_OK)
+      rc = tb_spectrum(c, geometry, toomuch, ethresh, starrad_cm, transparent, angles_deg, nang, nullptr);
+    if (rc == TB_OK && cudaMemcpyAsync(c->d_out_batch.p + (size_t)a * nwn, c->d_out.p, nwn * sizeof(double),
+                                       cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess)
+      rc = TB_ERR_CUDA;
+  }
+  c->defer_check = false;
+  c->err_keep = false;
+  if (rc != TB_OK) { cudaStreamSynchronize(c->stream); return rc; }
+  TB_CUDA(cudaMemcpyAsync(out, c->d_out_batch.p, (size_t)natm * nwn * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  return tb_check_errors(c);
 }
