@@ -111,3 +111,87 @@ def test_library_interface_run_transit_matches_reference(tmp_path):
         outs.append(np.load(str(tmp_path) + "/out_" + os.path.basename(lib) + ".npy"))
     assert np.array_equal(outs[0][0], outs[1][0])
     assert np.max(np.abs(outs[0][1] - outs[1][1]) / np.abs(outs[1][1])) < 1e-8
+
+
+def _read_dry(path):
+    """The host's dry-run dump (th_api.c do_transit, TRANSIT_B200_DRYRUN): header of 8 doubles, then the
+    sampled state in the order it is handed to the device."""
+    a = np.fromfile(path, "<f8")
+    nl, nm, ni, nwn, onwn, nlines = (int(x) for x in a[:6])
+    d = dict(nlayer=nl, nmol=nm, niso=ni, nwn=nwn, onwn=onwn, nlines=nlines, wn_i=a[6], wn_d=a[7])
+    pos = 8
+
+    def take(n, shape=None):
+        nonlocal pos
+        v = a[pos:pos + n].copy(); pos += n
+        return v if shape is None else v.reshape(shape)
+    d["rad"], d["p"], d["t"], d["mm"] = take(nl), take(nl), take(nl), take(nl)
+    d["dens"] = take(nm * nl, (nm, nl)); d["Z"] = take(ni * nl, (ni, nl))
+    d["molmass"], d["molradius"] = take(nm), take(nm)
+    d["isomass"], d["isoratio"] = take(ni), take(ni)
+    if nlines:
+        d["wl"], d["elow"], d["gf"] = take(nlines), take(nlines), take(nlines)
+    assert pos == len(a)
+    return d
+
+
+@pytest.mark.parametrize("name,kw,win", [("C2", dict(scale=0.01, nlayers=20, wn_hi=3000.0, wnosamp=120), (2300.0, 2700.5)),
+                                          ("C1", dict(scale=0.02, nlayers=24, wn_hi=2900.0, wnosamp=120), (2600.0, 2800.0))])
+def test_host_inputs_without_gpu(tmp_path, name, kw, win):
+    """Host logic on CPU through the dry-run tap (no device call is made): cfg + atmosphere file + TLI +
+    molecules.dat in, and out come the wavenumber grid (makewnsample), the layers, densities
+    (stateeqnford), per-layer partition functions (makeradsample splines) and the per-isotope
+    wavelength-range selection of the TLI (readdatarng, readlineinfo.c:416-537).  The cfg asks for a
+    window narrower than the database, so both ends of every isotope's block are cut."""
+    _build()
+    import oraclelib as O
+    prob, cfg = _inputs(tmp_path, name, **kw)
+    txt = "".join(l for l in open(cfg) if not l.startswith(("wnlow", "wnhigh")))
+    cfg = str(tmp_path / "window.cfg")
+    open(cfg, "w").write(txt + f"wnlow {win[0]}\nwnhigh {win[1]}\n")
+    dump = tmp_path / "dry.f64"
+    env = dict(os.environ, TRANSIT_B200_DRYRUN=str(dump))
+    r = subprocess.run([HOST, "-c", cfg], capture_output=True, text=True, env=env, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stderr[-800:]
+    d = _read_dry(str(dump))
+    nwn = int(O.lib().to_grid_count(win[0], win[1], prob.wn_d, 1))
+    assert (d["nlayer"], d["nmol"], d["niso"]) == (prob.nrad, prob.nmol, prob.niso)
+    assert (d["nwn"], d["onwn"]) == (nwn, (nwn - 1) * prob.wnosamp + 1)
+    assert d["wn_i"] == win[0] and d["wn_d"] == prob.wn_d
+    rel = lambda a, b: float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)))
+    assert rel(d["rad"], prob.rad) < 1e-6 and rel(d["p"], prob.p) < 1e-6 and rel(d["t"], prob.t) < 1e-6   # file digits
+    assert np.array_equal(d["molmass"], prob.mol_mass) and rel(d["isomass"], prob.iso_mass) == 0
+    assert rel(d["isoratio"], prob.iso_ratio) == 0
+    # densities and partition functions from the values the HOST read (the files carry ~7 digits)
+    AMU, KB = 1.66053886e-24, 1.380658e-16
+    q = prob.mol_q
+    dens = AMU * q * (d["p"] * prob.p_fct)[None, :] / (KB * d["t"][None, :] * prob.t_fct) * prob.mol_mass[:, None]
+    assert rel(d["dens"], dens) < 2e-6
+    assert rel(d["Z"], prob.iso_z) < 1e-5
+    # TLI selection, in file order, bit for bit
+    raw = open(os.path.join(str(tmp_path), "lines.tli"), "rb").read()
+    allw, _ = O.parse_tli(raw, 1.0, 1e7)
+    want, _ = O.parse_tli(raw, win[0], win[1])     # wns.i .. wns.f as hinted, not the last grid point (readlineinfo.c:302-303)
+    assert 0 < len(want["wl"]) < len(allw["wl"])
+    assert d["nlines"] == len(want["wl"])
+    assert np.array_equal(d["wl"], want["wl"]) and np.array_equal(d["elow"], want["elow"])
+    assert np.array_equal(d["gf"], want["gf"])
+    # ... and the same inputs through the UNMODIFIED reference (oracle/_ref/ref_dump, here only): what the host
+    # hands to the device is what the reference's own readers and samplers produce
+    ref_dump = os.path.join(ROOT, "oracle", "_ref", "ref_dump")
+    if os.path.exists(ref_dump):
+        import sys
+        sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+        import make_golden as MG
+        r = subprocess.run([ref_dump, "ref.bin", "--", "-c", cfg], cwd=str(tmp_path), capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout[-500:]
+        g = MG.read_container(os.path.join(str(tmp_path), "ref.bin"))
+        assert int(g["wns_n"].item()) == d["nwn"] and int(g["owns_n"].item()) == d["onwn"]
+        assert np.array_equal(g["line_wl"], d["wl"]) and np.array_equal(g["line_elow"], d["elow"])
+        assert np.array_equal(g["line_gf"], d["gf"])
+        assert np.array_equal(g["rad_v"], d["rad"]) and np.array_equal(g["atm_t"], d["t"])
+        # the reference passes p, densities and abundances through splinterp at the layers' own radii
+        # (makesample.c:508-530), compiled with -ffast-math: the file's values come back within an ulp or two
+        assert rel(d["p"], g["atm_p"]) < 1e-14
+        assert rel(d["dens"], g["mol_d"]) < 1e-14
+        assert rel(d["Z"], g["iso_z"]) < 1e-14
