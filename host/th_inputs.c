@@ -11,6 +11,7 @@
 #include <stdarg.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/mman.h>
 #include "th_internal.h"
 
 void th_die(const char *fmt, ...) {
@@ -190,19 +191,25 @@ static void rd(void *dst, size_t sz, size_t n, FILE *fp, const char *what) {
   if (fread(dst, sz, n, fp) != n) th_die("TLI file ended while reading %s.\n", what);
 }
 
-/* datafileBS (readlineinfo.c:16-77) on an in-memory, ascending segment */
-static int64_t tli_bs(const double *v, int64_t nfields, double target, int up) {
+/* datafileBS (readlineinfo.c:16-77) on an ascending segment of the memory-mapped file; the TLI header
+ * has no alignment, so the doubles are fetched with memcpy */
+static inline double tli_at(const unsigned char *v, int64_t i) {
+  double x;
+  memcpy(&x, v + 8 * i, 8);
+  return x;
+}
+static int64_t tli_bs(const unsigned char *v, int64_t nfields, double target, int up) {
   int64_t lo = 0, hi = nfields - 1, loc;
   do {
     loc = (hi + lo) / 2;
-    if (target > v[loc]) lo = loc; else hi = loc;
+    if (target > tli_at(v, loc)) lo = loc; else hi = loc;
   } while (hi - lo > 1);
   if (up) {
     loc = lo;
-    while (loc < nfields - 1) { if (v[loc + 1] > target) break; loc++; }
+    while (loc < nfields - 1) { if (tli_at(v, loc + 1) > target) break; loc++; }
   } else {
     loc = hi;
-    while (loc > 0) { if (v[loc - 1] < target) break; loc--; }
+    while (loc > 0) { if (tli_at(v, loc - 1) < target) break; loc--; }
   }
   return loc;
 }
@@ -282,27 +289,46 @@ int th_read_tli(th_state *s) {
   rd(&nl, 8, 1, fp, "number of transitions"); rd(&ni, 4, 1, fp, "number of isotopes with lines");
   uint64_t *cnt = (uint64_t *)malloc((ni ? ni : 1) * sizeof(uint64_t));
   rd(cnt, 8, ni, fp, "transitions per isotope");
-  double *wl = (double *)malloc((nl ? nl : 1) * sizeof(double)), *el = (double *)malloc((nl ? nl : 1) * sizeof(double));
-  double *gf = (double *)malloc((nl ? nl : 1) * sizeof(double));
-  int16_t *id = (int16_t *)malloc((nl ? nl : 1) * sizeof(int16_t));
-  rd(wl, 8, nl, fp, "wavelengths"); rd(id, 2, nl, fp, "isotope IDs"); rd(el, 8, nl, fp, "lower-state energies");
-  rd(gf, 8, nl, fp, "gf values");
-  fclose(fp);
-  /* readdatarng (readlineinfo.c:416-537): per isotope keep [1/wn_f, 1/wn_i] (microns) */
+  /* readdatarng (readlineinfo.c:416-537): per isotope keep [1/wn_f, 1/wn_i] (microns).  The four
+   * arrays (wavelength, isotope, E_low, gf; nl entries each) are NOT read: the file is mapped, the
+   * two ends of every isotope's block are found by datafileBS's search in the mapped wavelengths, and
+   * only the selected slices are copied -- an ExoMol-scale TLI (10^8 lines, 2.6 GB) costs what the
+   * requested wavenumber range holds. */
+  const long hdr_end = ftell(fp);
+  fseek(fp, 0, SEEK_END);
+  const long fsize = ftell(fp);
+  if (hdr_end < 0 || fsize < 0 || (uint64_t)(fsize - hdr_end) < nl * 26)
+    th_die("TLI file ended while reading the line transitions.\n");
+  const unsigned char *map = NULL;
+  if (nl) {
+    map = (const unsigned char *)mmap(NULL, (size_t)fsize, PROT_READ, MAP_PRIVATE, fileno(fp), 0);
+    if (map == MAP_FAILED) th_die("Cannot map the line info file '%s'.\n", s->h.f_line);
+  }
+  const unsigned char *m_wl = map + hdr_end, *m_id = m_wl + 8 * nl, *m_el = m_id + 2 * nl, *m_gf = m_el + 8 * nl;
   const double iniw = 1.0 / (s->wn_f * 1.0) / 1e-4, finw = 1.0 / (s->wn_i * 1.0) / 1e-4;
+  int64_t *lo = (int64_t *)malloc((ni ? ni : 1) * sizeof(int64_t)), *cntsel = (int64_t *)calloc(ni ? ni : 1, sizeof(int64_t));
   int64_t off = 0, n = 0;
   for (int i = 0; i < ni; i++) {
     if (cnt[i] > 0) {
-      const int64_t a = tli_bs(wl + off, (int64_t)cnt[i], iniw, 0) + off, b = tli_bs(wl + off, (int64_t)cnt[i], finw, 1) + off;
-      const int64_t nread = b - a + 1;
-      if (nread > 0) {
-        memmove(wl + n, wl + a, nread * sizeof(double)); memmove(el + n, el + a, nread * sizeof(double));
-        memmove(gf + n, gf + a, nread * sizeof(double)); memmove(id + n, id + a, nread * sizeof(int16_t));
-        n += nread;
-      }
+      const int64_t a = tli_bs(m_wl + 8 * off, (int64_t)cnt[i], iniw, 0) + off, b = tli_bs(m_wl + 8 * off, (int64_t)cnt[i], finw, 1) + off;
+      if (b - a + 1 > 0) { lo[i] = a; cntsel[i] = b - a + 1; n += b - a + 1; }
     }
     off += (int64_t)cnt[i];
   }
+  double *wl = (double *)malloc((n ? n : 1) * sizeof(double)), *el = (double *)malloc((n ? n : 1) * sizeof(double));
+  double *gf = (double *)malloc((n ? n : 1) * sizeof(double));
+  int16_t *id = (int16_t *)malloc((n ? n : 1) * sizeof(int16_t));
+  int64_t k = 0;
+  for (int i = 0; i < ni; i++) {
+    const int64_t c = cntsel[i];
+    if (!c) continue;
+    memcpy(wl + k, m_wl + 8 * lo[i], 8 * c); memcpy(el + k, m_el + 8 * lo[i], 8 * c);
+    memcpy(gf + k, m_gf + 8 * lo[i], 8 * c); memcpy(id + k, m_id + 2 * lo[i], 2 * c);
+    k += c;
+  }
+  if (map) munmap((void *)map, (size_t)fsize);
+  fclose(fp);
+  free(lo); free(cntsel);
   free(cnt);
   s->nlines = n; s->wl = wl; s->elow = el; s->gf = gf; s->isoid = id;
   return 0;
