@@ -195,3 +195,46 @@ def test_host_inputs_without_gpu(tmp_path, name, kw, win):
         assert rel(d["p"], g["atm_p"]) < 1e-14
         assert rel(d["dens"], g["mol_d"]) < 1e-14
         assert rel(d["Z"], g["iso_z"]) < 1e-14
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "ref_dump")),
+                    reason="oracle/_ref/ref_dump not built")
+def test_host_run_transit_setup_without_gpu(tmp_path):
+    """run_transit's per-atmosphere setup on CPU (dry-run tap of libtransit_host.so): reloadatm with new
+    temperatures and abundances (readatm.c:722-784), densities, hydrostatic radii from
+    refpress/refradius/gsurf (radpress, readatm.c:787-865) and the per-layer partition functions, against
+    the same call on the UNMODIFIED reference (ref_dump --rerun)."""
+    _build()
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    import make_golden as MG
+    prob = workloads.make_problem("C2", scale=0.004, nlayers=16, wn_hi=2600.0, wnosamp=60)
+    tmp = str(tmp_path)
+    cfg, _ = workloads.write_reference_inputs(prob, tmp)
+    with open(cfg, "a") as f:
+        f.write(f"refpress {prob.p[5]:.6e}\nrefradius {prob.rad[5]:.6f}\ngsurf 2200.0\n")
+    inp = np.concatenate([prob.t * 1.01 + 3.0] + [prob.mol_q[j] for j in range(prob.nmol)])
+    inp.astype("<f8").tofile(os.path.join(tmp, "rerun.f64"))
+    np.save(tmp_path / "inp.npy", inp)
+    r = subprocess.run([os.path.join(ROOT, "oracle", "_ref", "ref_dump"), "ref.bin", "--rerun", "rerun.f64", "--",
+                        "-c", cfg], cwd=tmp, capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-800:]
+    g = MG.read_container(os.path.join(tmp, "ref.bin"))
+    argv = [b"transit", b"-c", cfg.encode()]
+    dump = os.path.join(tmp, "dry.f64")
+    code = (f"import ctypes as C, numpy as np, os\n"
+            f"os.dup2(os.open(os.devnull, os.O_WRONLY), 1)\n"
+            f"L = C.CDLL({HOSTLIB!r}); argv = {argv!r}; arr = (C.c_char_p * len(argv))(*argv)\n"
+            f"L.transit_init(len(argv), arr); L.get_no_samples.restype = C.c_int; n = L.get_no_samples()\n"
+            f"out = np.zeros(n); inp = np.load({str(tmp_path / 'inp.npy')!r}); P = C.POINTER(C.c_double)\n"
+            f"L.run_transit(inp.ctypes.data_as(P), len(inp), out.ctypes.data_as(P), n)\n")
+    r = subprocess.run(["python", "-c", code], capture_output=True, text=True,
+                       env=dict(os.environ, TRANSIT_B200_DRYRUN=dump))
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = _read_dry(dump)
+    rel = lambda a, b: float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)))
+    assert np.array_equal(d["t"], g["rerun_atm_t"])
+    assert rel(d["rad"], g["rerun_rad_v"]) < 1e-13          # log/pow of the -ffast-math build: a few ulp
+    assert np.any(d["rad"] != prob.rad)                      # the radii really are the hydrostatic ones
+    assert rel(d["dens"], g["rerun_mol_d"]) < 1e-13
+    assert rel(d["Z"], g["rerun_iso_z"]) < 1e-13
