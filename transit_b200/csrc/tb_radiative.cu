@@ -367,74 +367,90 @@ __global__ void k_ray_geometry(int eclipse, const double *__restrict__ rad, int 
                                int32_t *__restrict__ meta, double *__restrict__ par,
                                double *__restrict__ coef, double *__restrict__ sbuf,
                                double *__restrict__ rcp, int32_t *__restrict__ err) {
-  int ri = blockIdx.x * blockDim.x + threadIdx.x;
-  if (ri >= nh) return;
-  // tau.c:274 as the reference is BUILT: gcc -ffast-math hoists 1/rfct out of the loop (objdump of
-  // tau(): movsd 1.0; divsd rfct ahead of the wavenumber loop), so b = (h*hfct)*(1/rfct).  With an
-  // IEEE division some impact parameters land one ulp below their own layer radius, the ray then
-  // starts one layer lower and tau changes by ~20%: something the reference binary never shows.
-  const double b = __dmul_rn(__dmul_rn(h[ri], hfct), __drcp_rn(rfct));
-  int rs, mode = 1;
-  if (eclipse) {
-    rs = tb_binsearchapprox(rad, b, 0, nrad - 1);             // eclipse.c:39
-    if (rs == nrad - 1) mode = 0;
-  } else {
-    // binsearchie (numerical.c:16-45)
-    const double r0 = b;                                       // refraction index 1 (slantpath.c:32)
-    if (rad[0] > r0) { mode = -1; rs = 0; }
-    else if (rad[nrad - 1] < r0) { mode = 0; rs = 0; }         // -2: above the top -> 0
-    else if (rad[nrad - 1] == r0) { mode = 0; rs = 0; }        // -5: outermost layer -> 0
-    else {
-      long i = 0, f = nrad - 1;
-      while (f - i > 1) {
-        long m = (f + i) >> 1;
-        if (rad[m] > r0) f = m; else i = m;
-      }
-      rs = (int)i;
-    }
-  }
+  // one block per ray: thread 0 places the ray, then the path coordinates s[i] (one sqrt each) and the
+  // Simpson weights of the pairs (three divisions each) are independent and spread over the block
+  // (one thread per ray ran them as a 27 us serial chain in front of every tau launch)
+  const int ri = blockIdx.x;
+  __shared__ int sh_rs, sh_mode, sh_n;
+  __shared__ double sh_r0;
   int32_t *mt = meta + ri * 4;
   double *pp = par + ri * 4;
-  if (mode <= 0) {
-    if (mode < 0) atomicExch(err + 1, 1);
-    mt[0] = rs; mt[1] = 0; mt[2] = mode; mt[3] = 0;
-    return;
-  }
-  int n = nrad - rs;
-  const double r0 = eclipse ? rad[rs] : b;
   double *s = sbuf + (size_t)ri * (nrad + 3);
-  if (n == 2) {
-    mode = 2;
-    // interp_parab(rad-1, ex-1, r0): parabola through layers rs-1, rs, rs+1
-    const double *x = rad + rs - 1;
-    pp[0] = x[1] - x[0];
-    pp[1] = x[0] / pp[0];
-    pp[2] = r0;
-    // three points: r0, midpoint, rad[rs+1] (slantpath.c:62-74, eclipse.c:68-80)
-    double r3_0 = eclipse ? rad[rs] : r0, r3_2 = rad[rs + 1], r3_1 = (r3_0 + r3_2) / 2.0;
-    s[0] = 0;
-    if (eclipse) { s[1] = s[0] + (r3_1 - r3_0); s[2] = s[1] + (r3_2 - r3_1); }
-    else { s[1] = sqrt(r3_1 * r3_1 - r0 * r0); s[2] = sqrt(r3_2 * r3_2 - r0 * r0); }
-    n = 3;
-  } else {
-    const double *x = rad + rs;
-    pp[0] = x[1] - x[0];
-    pp[1] = x[0] / pp[0];
-    pp[2] = r0;
-    s[0] = 0;
+  if (threadIdx.x == 0) {
+    // tau.c:274 as the reference is BUILT: gcc -ffast-math hoists 1/rfct out of the loop (objdump of
+    // tau(): movsd 1.0; divsd rfct ahead of the wavenumber loop), so b = (h*hfct)*(1/rfct).  With an
+    // IEEE division some impact parameters land one ulp below their own layer radius, the ray then
+    // starts one layer lower and tau changes by ~20%: something the reference binary never shows.
+    const double b = __dmul_rn(__dmul_rn(h[ri], hfct), __drcp_rn(rfct));
+    int rs, mode = 1;
     if (eclipse) {
-      for (int i = 1; i < n; i++) s[i] = s[i - 1] + (rad[rs + i] - rad[rs + i - 1]);
+      rs = tb_binsearchapprox(rad, b, 0, nrad - 1);             // eclipse.c:39
+      if (rs == nrad - 1) mode = 0;
     } else {
-      for (int i = 1; i < n; i++) {
-        double ri_ = rad[rs + i];
-        s[i] = sqrt(__dsub_rn(__dmul_rn(ri_, ri_), __dmul_rn(r0, r0)));
+      // binsearchie (numerical.c:16-45)
+      const double r0 = b;                                       // refraction index 1 (slantpath.c:32)
+      if (rad[0] > r0) { mode = -1; rs = 0; }
+      else if (rad[nrad - 1] < r0) { mode = 0; rs = 0; }         // -2: above the top -> 0
+      else if (rad[nrad - 1] == r0) { mode = 0; rs = 0; }        // -5: outermost layer -> 0
+      else {
+        long i = 0, f = nrad - 1;
+        while (f - i > 1) {
+          long m = (f + i) >> 1;
+          if (rad[m] > r0) f = m; else i = m;
+        }
+        rs = (int)i;
       }
     }
+    int n = 0;
+    double r0 = 0;
+    if (mode <= 0) {
+      if (mode < 0) atomicExch(err + 1, 1);
+      mt[0] = rs; mt[1] = 0; mt[2] = mode; mt[3] = 0;
+    } else {
+      n = nrad - rs;
+      r0 = eclipse ? rad[rs] : b;
+      if (n == 2) {
+        mode = 2;
+        // interp_parab(rad-1, ex-1, r0): parabola through layers rs-1, rs, rs+1
+        const double *x = rad + rs - 1;
+        pp[0] = x[1] - x[0];
+        pp[1] = x[0] / pp[0];
+        pp[2] = r0;
+        // three points: r0, midpoint, rad[rs+1] (slantpath.c:62-74, eclipse.c:68-80)
+        double r3_0 = eclipse ? rad[rs] : r0, r3_2 = rad[rs + 1], r3_1 = (r3_0 + r3_2) / 2.0;
+        s[0] = 0;
+        if (eclipse) { s[1] = s[0] + (r3_1 - r3_0); s[2] = s[1] + (r3_2 - r3_1); }
+        else { s[1] = sqrt(r3_1 * r3_1 - r0 * r0); s[2] = sqrt(r3_2 * r3_2 - r0 * r0); }
+        n = 3;
+      } else {
+        const double *x = rad + rs;
+        pp[0] = x[1] - x[0];
+        pp[1] = x[0] / pp[0];
+        pp[2] = r0;
+        s[0] = 0;
+        if (eclipse)                                             // a running sum: in order
+          for (int i = 1; i < n; i++) s[i] = s[i - 1] + (rad[rs + i] - rad[rs + i - 1]);
+      }
+      rcp[ri * 2] = 1.0 / (2.0 * pp[0] * pp[0]);      // correctly rounded reciprocals for tb_div_r
+      rcp[ri * 2 + 1] = 1.0 / pp[0];
+    }
+    sh_rs = rs; sh_mode = mode; sh_n = n; sh_r0 = r0;
   }
+  __syncthreads();
+  const int mode = sh_mode, n = sh_n, rs = sh_rs;
+  if (mode <= 0) return;
+  if (mode == 1 && !eclipse) {
+    const double r0 = sh_r0;
+    for (int i = 1 + threadIdx.x; i < n; i += blockDim.x) {
+      double ri_ = rad[rs + i];
+      s[i] = sqrt(__dsub_rn(__dmul_rn(ri_, ri_), __dmul_rn(r0, r0)));
+    }
+  }
+  __syncthreads();
   const int even = (n % 2 == 0);
   const int np = (n - 1) / 2;
   double *cf = coef + (size_t)ri * stride;
-  for (int i = 0; i < np; i++) {
+  for (int i = threadIdx.x; i < np; i += blockDim.x) {
     int j = 2 * i + even;
     double h0 = s[j + 1] - s[j], h1 = s[j + 2] - s[j + 1];
     double hsum = h0 + h1, hratio = h1 / h0, hfactor = hsum * hsum / (h0 * h1);
@@ -443,10 +459,10 @@ __global__ void k_ray_geometry(int eclipse, const double *__restrict__ rad, int 
     cf[4 * i + 2] = 2.0 - 1.0 / hratio;
     cf[4 * i + 3] = hsum;
   }
-  pp[3] = even ? (s[1] - s[0]) : 0.0;
-  rcp[ri * 2] = 1.0 / (2.0 * pp[0] * pp[0]);      // correctly rounded reciprocals for tb_div_r
-  rcp[ri * 2 + 1] = 1.0 / pp[0];
-  mt[0] = rs; mt[1] = n; mt[2] = mode; mt[3] = np;
+  if (threadIdx.x == 0) {
+    pp[3] = even ? (s[1] - s[0]) : 0.0;
+    mt[0] = rs; mt[1] = n; mt[2] = mode; mt[3] = np;
+  }
 }
 
 // =============================================================== tau (a10-a13)
@@ -697,7 +713,7 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
   TB_TRY(tb_upload_small(c, d_h.p, c->h_h.data(), nh * sizeof(double), st));
   if (!c->err_keep) TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4 * sizeof(int32_t), st));
   TB_CUDA(cudaMemsetAsync(c->d_tau.p, 0, sizeof(double) * nh * nwn, st));   // calloc, tau.c:34
-  k_ray_geometry<<<nblk(nh, 64), 64, 0, st>>>(geometry == TB_GEOM_ECLIPSE, c->d_rad.p, nrad, c->rad_fct, d_h.p, nh,
+  k_ray_geometry<<<nh, 64, 0, st>>>(geometry == TB_GEOM_ECLIPSE, c->d_rad.p, nrad, c->rad_fct, d_h.p, nh,
                                               hfct, stride, c->r_meta.p, c->r_par.p, c->r_coef.p, d_s.p, c->r_rcp.p, c->d_err.p);
   TauPar P;
   P.eclipse = geometry == TB_GEOM_ECLIPSE; P.nrad = nrad; P.nh = nh; P.stride = stride; P.nwn = nwn;
