@@ -862,6 +862,14 @@ __global__ void k_intensity_flux(int64_t nwn, int nrad, const double *__restrict
                                  double wn_i, double wn_d, double wn_fct, int nang,
                                  const double *__restrict__ ang, const double *__restrict__ area,
                                  double *__restrict__ intens, double *__restrict__ out) {
+  extern __shared__ __align__(16) double sif[];
+  double *skt = sif, *srkt = sif + nrad;                // k_B*T of point i (layer nrad-1-i) and its reciprocal
+  for (int i = threadIdx.x; i < nrad; i += blockDim.x) {
+    const double kt = TB_KB * temp[nrad - 1 - i];
+    skt[i] = kt;
+    srkt[i] = 1.0 / kt;
+  }
+  __syncthreads();
   const int64_t wq = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / QL;
   const int ql = threadIdx.x & (QL - 1);
   const bool inb = wq < nwn;
@@ -870,17 +878,21 @@ __global__ void k_intensity_flux(int64_t nwn, int nrad, const double *__restrict
   const double wv = __dadd_rn(wn_i, __dmul_rn((double)w, wn_d));   // wns.v[w]
   const double ww = wv * wn_fct;
   const double num = 2.0 * TB_H * pow(ww, 3.0) * TB_LS * TB_LS;     // eclipse.c:154
-  double icos[TB_MAXANG], dprev[TB_MAXANG], tz[TB_MAXANG];
-  for (int a = 0; a < nang; a++) { icos[a] = cos(ang[a] * TB_DEGREES); tz[a] = 0; dprev[a] = 0; }
+  // the divisors of the two per-(layer, wavenumber) divisions -- cos(angle) and k_B*T(layer) -- do not
+  // depend on the wavenumber: their reciprocals are formed once and every quotient is completed to the
+  // correctly rounded one by tb_div_r (the value of the division for ~6 instructions instead of ~40)
+  double icos[TB_MAXANG], rcos[TB_MAXANG], dprev[TB_MAXANG], tz[TB_MAXANG];
+  for (int a = 0; a < nang; a++) { icos[a] = cos(ang[a] * TB_DEGREES); rcos[a] = 1.0 / icos[a]; tz[a] = 0; dprev[a] = 0; }
   double Bprev = 0;
+  const double hcw = TB_H * ww * TB_LS;
   const int n = L + 1;
   const int i0 = (n * ql) / QL, i1 = (n * (ql + 1)) / QL;
   // a lane that does not start at the top first evaluates the point before its part
   for (int i = (i0 > 0 ? i0 - 1 : 0); i < i1; i++) {
     const double t = tau[(size_t)i * nwn + w];
-    const double B = num / (exp(TB_H * ww * TB_LS / (TB_KB * temp[nrad - 1 - i])) - 1.0);
+    const double B = num / (exp(tb_div_r(hcw, skt[i], srkt[i])) - 1.0);
     for (int a = 0; a < nang; a++) {
-      const double dt = exp(-t / icos[a]);
+      const double dt = exp(tb_div_r(-t, icos[a], rcos[a]));
       if (i >= i0 && i > 0) tz[a] += (dt - dprev[a]) * (B + Bprev);  // integ_trapz, numerical.c:168-170
       dprev[a] = dt;
     }
@@ -921,11 +933,11 @@ extern "C" int tb_intensity_flux(tb_ctx *c, const double *angles_deg, int nang, 
   TB_TRY(tb_upload_small(c, d_a.p + nang, area.data(), nang * sizeof(double), st));
   tb_timer_begin(c, "intensity");
   if (c->nwn < 100000)
-    k_intensity_flux<8><<<nblk(c->nwn * 8, 128), 128, 0, st>>>(c->nwn, c->nrad, c->d_tau.p, c->d_last.p, c->d_t.p, c->wn_i,
+    k_intensity_flux<8><<<nblk(c->nwn * 8, 128), 128, 2 * (size_t)c->nrad * sizeof(double), st>>>(c->nwn, c->nrad, c->d_tau.p, c->d_last.p, c->d_t.p, c->wn_i,
                                                             c->wn_d, c->wn_fct, nang, d_a.p, d_a.p + nang, c->d_intens.p,
                                                             c->d_out.p);
   else
-    k_intensity_flux<1><<<nblk(c->nwn, 128), 128, 0, st>>>(c->nwn, c->nrad, c->d_tau.p, c->d_last.p, c->d_t.p, c->wn_i,
+    k_intensity_flux<1><<<nblk(c->nwn, 128), 128, 2 * (size_t)c->nrad * sizeof(double), st>>>(c->nwn, c->nrad, c->d_tau.p, c->d_last.p, c->d_t.p, c->wn_i,
                                                         c->wn_d, c->wn_fct, nang, d_a.p, d_a.p + nang, c->d_intens.p,
                                                         c->d_out.p);
   tb_timer_end(c, "intensity");
