@@ -136,7 +136,9 @@ def _read_dry(path):
 
 
 @pytest.mark.parametrize("name,kw,win", [("C2", dict(scale=0.01, nlayers=20, wn_hi=3000.0, wnosamp=120), (2300.0, 2700.5)),
-                                          ("C1", dict(scale=0.02, nlayers=24, wn_hi=2900.0, wnosamp=120), (2600.0, 2800.0))])
+                                          ("C1", dict(scale=0.02, nlayers=24, wn_hi=2900.0, wnosamp=120), (2600.0, 2800.0)),
+                                          # three samples: most isotopologues have no line at all inside
+                                          ("C2", dict(scale=0.01, nlayers=20, wn_hi=3000.0, wnosamp=120), (2500.0, 2502.0))])
 def test_host_inputs_without_gpu(tmp_path, name, kw, win):
     """Host logic on CPU through the dry-run tap (no device call is made): cfg + atmosphere file + TLI +
     molecules.dat in, and out come the wavenumber grid (makewnsample), the layers, densities
