@@ -244,6 +244,108 @@ def measured_peaks():
         return 6650.0, "fallback (B200_PROFILING.md, 6.65 TB/s)"
 
 
+def ncu_traffic(workload, kernel):
+    """DRAM bytes per launch of `kernel` from an ncu --set full capture of THIS workload (profiles/ncu_traffic.json,
+    keyed by workload), else None: a figure captured on another configuration is not reported."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return json.load(f).get(workload, {}).get(kernel, {}).get("dram_bytes_per_launch")
+    except (OSError, ValueError):
+        return None
+
+
+def rooflines(workload, k_ms, nsamp, nline_layers, nwn, nlayers, mb, hbm_peak, peak_src):
+    """SURVEY.md 8d work models, one entry per timed kernel group, each against the peak measured LIVE in
+    this run (tb_microbench: DFMA, exp, copy) or MEASURED_PEAKS.json (HBM).
+      line sum:  2 flop per line-sample + (12 + 2 c_exp) flop per (line, layer); c_exp = DFMA flop/s over exp/s
+      strength:  the (12 + 2 c_exp) N_line.layer part;  accumulate: 2 N_samples (+ 4 B per sample, 8 B per output)
+      tau:       24 B per (layer, wavenumber) against HBM"""
+    dfma = mb["dfma_tflops"]
+    c_exp = dfma * 1e12 / (mb["dexp_gops"] * 1e9)               # flop-equivalents of one exp
+    pair_flop = (12.0 + 2.0 * c_exp) * nline_layers
+    samp_flop = 2.0 * nsamp
+    src_f = "tb_microbench DFMA, measured in this run"
+    out = {}
+
+    def fp64(name, kernel, flop, note=None):
+        if name in k_ms and k_ms[name] > 0:
+            a = flop / (k_ms[name] * 1e-3) / 1e12
+            out[name] = {"kernel": kernel, "bound": "fp64", "achieved": a, "peak": dfma, "unit": "TFLOP/s", "frac": a / dfma,
+                         "ms": k_ms[name], "traffic": ncu_traffic(workload, name), "peak_source": src_f,
+                         "algorithmic_flop": flop, "c_exp_flop": c_exp}
+            if note:
+                out[name]["note"] = note
+
+    def hbm(name, kernel, nbytes):
+        if name in k_ms and k_ms[name] > 0:
+            a = nbytes / (k_ms[name] * 1e-3) / 1e9
+            out[name] = {"kernel": kernel, "bound": "hbm", "achieved": a, "peak": hbm_peak, "unit": "GB/s", "frac": a / hbm_peak,
+                         "ms": k_ms[name], "traffic": ncu_traffic(workload, name), "peak_source": peak_src,
+                         "algorithmic_bytes": nbytes}
+
+    fp64("molext", "line sum, all kernels (k_kmax + k_linesum_fused + k_strength + k_accumulate)", samp_flop + pair_flop)
+    fp64("strength", "k_strength", pair_flop * k_ms.get("_unfused_frac", 1.0),
+         "reference work of the layers this kernel evaluates (2 exp + 12 flop per (line, layer)); the log-domain "
+         "pretest executes far fewer instructions, so this is throughput in reference work, not pipe use")
+    fp64("fused", "k_linesum_fused (strength + gather of the narrow layers in one kernel)",
+         pair_flop * (1.0 - k_ms.get("_unfused_frac", 1.0)) + 2.0 * k_ms.get("_fused_samples", 0.0))
+    fp64("accumulate", "k_accumulate (wide + narrow instances)", 2.0 * k_ms.get("_unfused_samples", nsamp))
+    if "accumulate" in out:
+        b = 4.0 * k_ms.get("_unfused_samples", nsamp) + 8.0 * nwn * nlayers * k_ms.get("_unfused_frac", 1.0)
+        out["accumulate"]["hbm_gbs"] = b / (k_ms["accumulate"] * 1e-3) / 1e9
+        out["accumulate"]["hbm_frac"] = out["accumulate"]["hbm_gbs"] / hbm_peak
+    hbm("tau", "k_tau_transit", 24.0 * nwn * nlayers)
+    return out
+
+
+def ms_stats(ms_steps):
+    a = np.asarray(ms_steps, float)
+    return {"min": float(a.min()), "median": float(np.median(a)), "max": float(a.max()), "mean": float(a.mean())}
+
+
+HOST_SO = os.path.join(ROOT, "host", "libtransit_host.so")
+
+
+class HostLibrary:
+    """The reference's library face as a user (BART) binds it -- transit_init(argv) once, then
+    run_transit(in = [T | q_mol0 | q_mol1 ...], out[nwn]) per atmosphere (transit.i:11-19, transit.c:118-122) --
+    on host/libtransit_host.so: cfg, atmosphere file, TLI and CS files are read from disk, reloadatm / radpress /
+    makeradsample run per call, and the spectrum comes back in the caller's HOST buffer."""
+
+    def __init__(self, prob, device, tag):
+        import ctypes as C
+        from transit_b200 import workloads
+        if not os.path.exists(HOST_SO):
+            raise SystemExit(f"{HOST_SO} is missing: run __graft_entry__.build()")
+        d = os.path.join("/tmp", f"transit_b200_host_{tag}_{os.getpid()}")
+        cfg, _ = workloads.write_reference_inputs(prob, d)
+        k = prob.nrad // 3
+        with open(cfg, "a") as f:        # run_transit needs the hydrostatic reference level (readatm.c:760-767)
+            f.write(f"refpress {prob.p[k]:.6e}\nrefradius {prob.rad[k]:.6f}\ngsurf 1500.0\n")
+        os.environ["TRANSIT_B200_DEVICE"] = str(device)
+        self.C, self.L = C, C.CDLL(HOST_SO)
+        argv = [b"transit", b"-c", cfg.encode()]
+        arr = (C.c_char_p * len(argv))(*argv)
+        so = os.dup(1)
+        os.dup2(os.open(os.devnull, os.O_WRONLY), 1)     # keep stdout to the JSON line
+        try:
+            self.L.transit_init(len(argv), arr)
+        finally:
+            os.dup2(so, 1)
+        self.L.get_no_samples.restype = C.c_int
+        self.n = self.L.get_no_samples()
+        self.inp = np.ascontiguousarray(np.concatenate([prob.t] + [prob.mol_q[j] for j in range(prob.nmol)]))
+        self.out = np.zeros(self.n)
+        self.P = C.POINTER(C.c_double)
+
+    def run_transit(self):
+        self.L.run_transit(self.inp.ctypes.data_as(self.P), self.inp.size, self.out.ctypes.data_as(self.P), self.n)
+        return self.out
+
+    def close(self):
+        self.L.free_memory()
+
+
 def cpu_baseline_leg(args):
     """The unmodified reference on a bounded sample of the same workload: `nb` processes, one
     wavenumber band each (together one whole spectrum)."""
@@ -269,8 +371,8 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device -- the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO"):
-            os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line
+        # NCCL_DEBUG is left as the caller set it (the driver reads NCCL's own init lines to check the
+        # communicator); the JSON line is printed LAST and is the only line of stdout that parses as JSON
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
@@ -353,14 +455,33 @@ def run_ours(args):
     if world > 1 and not bands_mode:
         assert np.array_equal(gathered[0][rank].cpu().numpy(), out), "gathered slice differs from the local spectrum"
 
-    # ---- end to end through the host mirror with HOST buffers (H2D atmosphere + D2H spectrum per step)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        tr.set_atmosphere(my_prob)
-        step()
-    barrier()
-    e2e_s = time.perf_counter() - t0
+    # ---- end to end with HOST buffers, every step: atmosphere in (H2D inside the call), spectrum out (D2H)
+    e2e_api = args.e2e_api if not bands_mode else "mirror"
+    if e2e_api == "host":
+        # the reference's plugin call for this path: run_transit of the C host (reloadatm + radpress +
+        # makeradsample on the host, then tb_set_atmosphere + tb_spectrum), one library instance per rank
+        host = HostLibrary(my_prob, local_rank, f"r{rank}")
+        assert host.n == prob.nwn
+        for _ in range(max(2, args.warmup)):
+            host.run_transit()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            host.run_transit()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        assert np.all(np.isfinite(host.out)) and host.out.max() > 0
+        host.close()
+        e2e_api = "host/libtransit_host.so: run_transit(in=[T|q...], out[nwn]) per step, one instance per rank"
+    else:
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            tr.set_atmosphere(my_prob)
+            step()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        e2e_api = "python mirror: tb_set_atmosphere + tb_spectrum (+ NCCL gather)"
     h2d = 8 * prob.nrad * (3 + prob.nmol + prob.niso)
     d2h = 8 * prob.nwn
 
@@ -377,20 +498,23 @@ def run_ours(args):
 
     nspec = 1 if bands_mode else world           # spectra finished per step by the whole job
     hbm_peak, peak_src = measured_peaks()
-    acc_ms = float(np.mean(k_ms["accumulate"]))
-    mol_ms = float(np.mean(k_ms["molext"]))
-    G, ns, nwn = tr.ngroups(), prob.nrad, tr.band_nwn()
+    kms = {k: float(np.mean(v)) for k, v in k_ms.items() if np.isfinite(np.mean(v))}
+    mol_ms = kms["molext"]
+    ns, nwn = prob.nrad, tr.band_nwn()
     my_samp = int(tr.sample_counts().sum())
-    # algorithmic bytes of the gather kernel: 4 B of Voigt profile per line-sample
-    # (SURVEY.md 8d), 10 B of strength + profile id per (group, layer), 8 B written per (bin, layer)
-    acc_bytes = 4.0 * my_samp + 10.0 * G * ns + 8.0 * nwn * ns
-    achieved = acc_bytes / (acc_ms * 1e-3) / 1e9
-    traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            traffic = json.load(f).get("k_accumulate", {}).get("dram_bytes_per_launch")
-    except (OSError, ValueError):
-        pass
+    # peaks measured in THIS run on this GPU (milliseconds of device time, outside the timed region)
+    mb = ctx.microbench()
+    frac = getattr(tr, "line_fraction", 1.0)               # band shard: the part of the line list this rank evaluates
+    model = dict(kms)
+    fs = ctx.fused_stats() if hasattr(ctx, "fused_stats") else None
+    if fs:
+        model["_unfused_frac"] = 1.0 - fs["fused_states"] / max(1, ns)
+        model["_fused_samples"] = float(fs["fused_samples"])
+        model["_unfused_samples"] = float(my_samp - fs["fused_samples"])
+    rl = rooflines(args.workload, model, my_samp, len(prob.wl) * ns * frac, nwn, ns, mb, hbm_peak, peak_src)
+    # the line's `roofline` is the kernel with the most device time in a step
+    single = {k: v for k, v in rl.items() if k != "molext"}
+    dominant = max(single, key=lambda k: single[k]["ms"]) if single else "molext"
     line = {
         "metric": "spectra/s", "value": nspec * args.steps / (dev_ms * 1e-3), "unit": "spectra/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
@@ -399,40 +523,26 @@ def run_ours(args):
                        **({"sharding": f"wavenumber bands x{world} (one spectrum per step)", "bands": tr.bands}
                           if bands_mode else {})),
         "e2e": {"value": nspec * args.steps / e2e_s, "unit": "spectra/s", "h2d_bytes_per_step": h2d * world,
-                "d2h_bytes_per_step": d2h * nspec},
+                "d2h_bytes_per_step": d2h * nspec, "api": e2e_api},
         "gpu_launches": launches,
+        "ms_step_stats": ms_stats(ms_steps),
         "line_sum": {"gsamples_per_s": nsamp / (mol_ms * 1e-3) / 1e9, "samples_per_step": nsamp,
                      "line_layers_per_s": len(prob.wl) * prob.nrad / (mol_ms * 1e-3), "molext_ms": mol_ms},
-        "kernel_ms": {k: float(np.mean(v)) for k, v in k_ms.items() if np.isfinite(np.mean(v))},
-        "roofline": {"kernel": "k_accumulate (wide-reach + narrow-reach instances, one timer)", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src, "ms": acc_ms,
-                     "algorithmic_bytes": acc_bytes,
-                     "fp64_gflops": 2.0 * my_samp / (acc_ms * 1e-3) / 1e9},
+        "kernel_ms": kms,
+        "roofline": dict(rl[dominant], dominant_of="kernel_ms (largest device time of a step)"),
+        "roofline_line_sum": rl.get("molext"),
+        "rooflines": rl,
+        "microbench": mb,
         "clocks": clocks, "init_s": init_s,
     }
     if verified is not None:
         line["bit_identical_to_single_gpu"] = verified
-    # second kernel of the line sum, against the FP64 pipe (2 exp + ~12 flop per (group, layer);
-    # one exp = dfma_peak / exp_peak FMA-equivalents from tb_microbench: 34.8 TFLOP/s DFMA, 0.81 T exp/s
-    # recorded on this pool's B200s, re-measured with --microbench)
-    mb = ctx.microbench() if args.microbench else None
-    dfma_tf = mb["dfma_tflops"] if mb else 34.8
-    exp_g = mb["dexp_gops"] if mb else 810.0
-    c_exp = dfma_tf * 1e3 / 2.0 / exp_g                  # FMAs one exp is worth
-    str_ms = float(np.mean(k_ms["strength"]))
-    str_flop = (12.0 + 2.0 * 2.0 * c_exp) * G * ns
-    line["roofline_strength"] = {"kernel": "k_strength", "bound": "fp64", "achieved": str_flop / (str_ms * 1e-3) / 1e12,
-                                 "peak": dfma_tf, "unit": "TFLOP/s", "frac": str_flop / (str_ms * 1e-3) / 1e12 / dfma_tf,
-                                 "ms": str_ms, "peak_source": "tb_microbench DFMA" + (" (live)" if mb else " (recorded)"),
-                                 "note": "algorithmic flops of the reference's pass (2 exp + 12 flop per pair); the log-domain "
-                                         "pretest executes far fewer, so this is throughput in reference work, not pipe use"}
-    if mb:
-        line["microbench"] = mb
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_leg(args)
-    print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+    sys.stdout.flush()
+    print(json.dumps(line), flush=True)                   # last line of stdout
     return 0
 
 
@@ -455,7 +565,9 @@ def main():
                     help="N>1: one atmosphere per rank (weak scaling, default) or one spectrum split into "
                          "wavenumber bands (strong scaling)")
     ap.add_argument("--scale", type=float, default=1.0, help="line-count multiplier (debugging only; 1.0 = the named config)")
-    ap.add_argument("--microbench", action="store_true")
+    ap.add_argument("--e2e-api", default="host", choices=["host", "mirror"],
+                    help="e2e leg: run_transit of the C host (host/libtransit_host.so, the reference's plugin call, "
+                         "a16 host work included) or the Python mirror (tb_set_atmosphere + tb_spectrum)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-baseline-s", type=float, default=14.0)
     ap.add_argument("--ref-procs", type=int, default=0)

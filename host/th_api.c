@@ -9,22 +9,30 @@
 #include "th_internal.h"
 
 static th_state S;
+#ifdef TH_TEST_TAPS
 int th_dry = 0;
+#endif
 
 #define CK(call) do { if (TH_DEV(call) != TB_OK) th_die("%s\n", tb_last_error()); } while (0)
 
 static void apply_cloud_scattering(void) {
   const th_hints *h = &S.h;
   CK(tb_set_scattering(S.ctx, h->sc_flag, h->sc_logext));
-  /* tau.c:194-214: mean density and H number density per layer, for the cloud models */
+  /* tau.c:194-214, restated term by term (including the abundance factor the reference carries in
+   * both sums): mean_dens[r] = (sum_j d_j/m_j*q_j) * (sum_j m_j*q_j), and the H2 number density
+   * nH[r] = d_H2/m_H2*q_H2*N_A for the species NAMED "H2" only.  The reference accumulates mean_dens
+   * into an uninitialised stack array (tau.c:129,203); the sum starts from zero here.           */
   const int n = S.nlayer;
   double *nH = (double *)calloc(n, sizeof(double)), *md = (double *)calloc(n, sizeof(double));
   for (int r = 0; r < n; r++) {
-    for (int i = 0; i < S.nmol; i++) {
-      md[r] += S.d[(size_t)i * n + r];
-      if (S.molID[i] == 105) nH[r] += 2 * S.d[(size_t)i * n + r] / (S.molmass[i] * TH_AMU);
-      if (S.molID[i] == 1) nH[r] += S.d[(size_t)i * n + r] / (S.molmass[i] * TH_AMU);
+    double mean_mm = 0;
+    for (int j = 0; j < S.nmol; j++) {
+      const double d = S.d[(size_t)j * n + r], q = S.q[(size_t)j * n + r];
+      md[r] += d / S.molmass[j] * q;
+      if (!strcmp("H2", S.molname[j])) nH[r] = d / S.molmass[j] * q * 6.02214076e23;
+      mean_mm += S.molmass[j] * q;
     }
+    md[r] *= mean_mm;
   }
   CK(tb_set_cloud(S.ctx, h->cl_flag, h->cl_ext, h->cl_top, h->cl_bot, h->cl_gamma, h->cl_Q, h->cl_r, h->cl_sig,
                   h->cl_refwn, nH, md));
@@ -55,7 +63,9 @@ void transit_init(int argc, char **argv) {
     if (S.nang < 1) th_die("raygrid '%s' holds no angle.\n", h->raygrid);
   }
   int dev = 0;
+#ifdef TH_TEST_TAPS
   th_dry = getenv("TRANSIT_B200_DRYRUN") != NULL;
+#endif
   if (getenv("TRANSIT_B200_DEVICE")) dev = atoi(getenv("TRANSIT_B200_DEVICE"));
   CK(tb_create(dev, &S.ctx));
   th_make_wn(&S);                                          /* makewnsample */
@@ -96,6 +106,7 @@ void do_transit(double *transit_out) {
   if (!S.initialised) { printf("Transit init not run, please initialize transit.\n"); return; }
   if (S.h.opabreak) return;                                /* justOpacity */
   const th_hints *h = &S.h;
+#ifdef TH_TEST_TAPS
   if (th_dry) {                                            /* host-logic tap: the sampled state as doubles */
     FILE *f = fopen(getenv("TRANSIT_B200_DRYRUN"), "wb");
     if (!f) th_die("cannot write the dry-run dump\n");
@@ -111,6 +122,7 @@ void do_transit(double *transit_out) {
     fclose(f);
     return;
   }
+#endif
   CK(tb_spectrum(S.ctx, S.eclipse ? TB_GEOM_ECLIPSE : TB_GEOM_TRANSIT, h->toomuch, h->ethresh,
                  h->starrad * TH_SUNRADIUS, h->transparent, S.eclipse ? S.angles : NULL, S.nang, S.out));
   if (transit_out) memcpy(transit_out, S.out, S.nwn * sizeof(double));

@@ -84,10 +84,16 @@ typedef struct {
   double *out;
 } th_state;
 
-/* Host-logic test hook: with TRANSIT_B200_DRYRUN=<file> no device call is made (th_dry != 0) and
- * do_transit writes the sampled atmosphere to <file> instead of computing a spectrum.      */
+/* Host-logic test hook, compiled ONLY into the test build (-DTH_TEST_TAPS: host/transit_b200_taps and
+ * host/libtransit_host_taps.so, used by tests/test_host_cli.py): with TRANSIT_B200_DRYRUN=<file> no
+ * device call is made (th_dry != 0) and do_transit writes the sampled atmosphere to <file> instead of
+ * computing a spectrum.  The shipped host has no such switch: every device call is made.     */
+#ifdef TH_TEST_TAPS
 extern int th_dry;
 #define TH_DEV(call) (th_dry ? 0 : (call))
+#else
+#define TH_DEV(call) (call)
+#endif
 
 /* th_config.c */
 void th_defaults(th_hints *h);

@@ -15,12 +15,15 @@ from transit_b200 import workloads
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HOST = os.path.join(ROOT, "host", "transit_b200")
 HOSTLIB = os.path.join(ROOT, "host", "libtransit_host.so")
+# test builds with the dry-run tap compiled in (-DTH_TEST_TAPS, host/Makefile); the shipped host has none
+HOST_TAPS = os.path.join(ROOT, "host", "transit_b200_taps")
+HOSTLIB_TAPS = os.path.join(ROOT, "host", "libtransit_host_taps.so")
 REF = os.path.join(ROOT, "oracle", "_ref", "transit")
 REFLIB = os.path.join(ROOT, "oracle", "_ref", "libtransit_ref.so")
 
 
 def _build():
-    if not os.path.exists(HOST):
+    if not (os.path.exists(HOST) and os.path.exists(HOST_TAPS) and os.path.exists(HOSTLIB_TAPS)):
         from transit_b200 import api
         api.build_library()
         subprocess.run(["make", "-C", os.path.join(ROOT, "host")], check=True, stdout=subprocess.DEVNULL)
@@ -58,6 +61,15 @@ def test_cfg_prefix_match_and_loud_failure_without_gpu(tmp_path):
         pytest.skip("GPU present: covered by the gpu tests")
     r = subprocess.run([HOST, "-c", str(ok)], capture_output=True, text=True)
     assert r.returncode != 0 and ("CUDA" in r.stderr or "no CPU fallback" in r.stderr)
+
+
+def test_shipped_host_has_no_dry_run_switch(tmp_path):
+    """TRANSIT_B200_DRYRUN is a hook of the TEST build only: the shipped binary and library must not even
+    contain the string, so no environment variable can turn their device calls into no-ops."""
+    _build()
+    for f in (HOST, HOSTLIB):
+        assert b"TRANSIT_B200_DRYRUN" not in open(f, "rb").read(), f
+    assert b"TRANSIT_B200_DRYRUN" in open(HOST_TAPS, "rb").read()
 
 
 def _read_spec(path):
@@ -153,7 +165,7 @@ def test_host_inputs_without_gpu(tmp_path, name, kw, win):
     open(cfg, "w").write(txt + f"wnlow {win[0]}\nwnhigh {win[1]}\n")
     dump = tmp_path / "dry.f64"
     env = dict(os.environ, TRANSIT_B200_DRYRUN=str(dump))
-    r = subprocess.run([HOST, "-c", cfg], capture_output=True, text=True, env=env, cwd=str(tmp_path))
+    r = subprocess.run([HOST_TAPS, "-c", cfg], capture_output=True, text=True, env=env, cwd=str(tmp_path))
     assert r.returncode == 0, r.stderr[-800:]
     d = _read_dry(str(dump))
     nwn = int(O.lib().to_grid_count(win[0], win[1], prob.wn_d, 1))
@@ -202,7 +214,7 @@ def test_host_inputs_without_gpu(tmp_path, name, kw, win):
 @pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "ref_dump")),
                     reason="oracle/_ref/ref_dump not built")
 def test_host_run_transit_setup_without_gpu(tmp_path):
-    """run_transit's per-atmosphere setup on CPU (dry-run tap of libtransit_host.so): reloadatm with new
+    """run_transit's per-atmosphere setup on CPU (dry-run tap of the test build libtransit_host_taps.so): reloadatm with new
     temperatures and abundances (readatm.c:722-784), densities, hydrostatic radii from
     refpress/refradius/gsurf (radpress, readatm.c:787-865) and the per-layer partition functions, against
     the same call on the UNMODIFIED reference (ref_dump --rerun)."""
@@ -226,7 +238,7 @@ def test_host_run_transit_setup_without_gpu(tmp_path):
     dump = os.path.join(tmp, "dry.f64")
     code = (f"import ctypes as C, numpy as np, os\n"
             f"os.dup2(os.open(os.devnull, os.O_WRONLY), 1)\n"
-            f"L = C.CDLL({HOSTLIB!r}); argv = {argv!r}; arr = (C.c_char_p * len(argv))(*argv)\n"
+            f"L = C.CDLL({HOSTLIB_TAPS!r}); argv = {argv!r}; arr = (C.c_char_p * len(argv))(*argv)\n"
             f"L.transit_init(len(argv), arr); L.get_no_samples.restype = C.c_int; n = L.get_no_samples()\n"
             f"out = np.zeros(n); inp = np.load({str(tmp_path / 'inp.npy')!r}); P = C.POINTER(C.c_double)\n"
             f"L.run_transit(inp.ctypes.data_as(P), len(inp), out.ctypes.data_as(P), n)\n")

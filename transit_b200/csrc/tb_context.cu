@@ -68,6 +68,17 @@ extern "C" int tb_device_spectrum(tb_ctx *c, void **ptr, int64_t *n) {
   return TB_OK;
 }
 
+static int tb_create_resources(tb_ctx *c) {
+  TB_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+  c->stream = c->own_stream;
+  TB_CUDA(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
+  TB_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+  TB_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+  TB_TRY(c->d_err.ensure(4));
+  TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4 * sizeof(int32_t), c->stream));
+  return TB_OK;
+}
+
 extern "C" int tb_create(int device, tb_ctx **out) {
   TB_REQUIRE(out, TB_ERR_ARG, "tb_create: out is NULL");
   int ndev = 0;
@@ -88,13 +99,11 @@ extern "C" int tb_create(int device, tb_ctx **out) {
   tb_ctx *c = new tb_ctx();
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
-  TB_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
-  TB_CUDA(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
-  TB_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
-  TB_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
-  c->stream = c->own_stream;
-  TB_TRY(c->d_err.ensure(4));
-  TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4 * sizeof(int32_t), c->stream));
+  const int rc = tb_create_resources(c);
+  if (rc != TB_OK) {           // whatever was created so far goes away with the context
+    tb_destroy(c);
+    return rc;
+  }
   *out = c;
   return TB_OK;
 }
@@ -125,30 +134,16 @@ extern "C" int tb_sync(tb_ctx *c) {
 extern "C" void tb_destroy(tb_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->device);
-  cudaStreamSynchronize(c->stream);
+  if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->aux_stream) cudaStreamSynchronize(c->aux_stream);
-  // DevBuf members are released explicitly: the struct is a plain aggregate
-#define REL(x) c->x.release()
-  REL(d_mol_mass); REL(d_mol_radius); REL(d_mol_pol); REL(d_iso_mass); REL(d_iso_ratio);
-  REL(d_iso_imol); REL(d_iso_row); REL(l_iown); REL(l_gpos); REL(l_flag); REL(m_wavn); REL(m_elow);
-  REL(m_gf); REL(m_iso); REL(m_inr); REL(g_start); REL(g_iown); REL(g_idwn); REL(g_orig);
-  REL(g_iso); REL(g_wavn); REL(g_a0); REL(g_gf); REL(g_lg); REL(s_lcz); REL(go_wavn); REL(binstart); REL(substart); REL(i_rho); REL(i_stage); REL(d_aDop); REL(d_aLor); REL(d_psize);
-  REL(d_poff); REL(d_pdata); REL(d_rad); REL(d_p); REL(d_t); REL(d_dens); REL(s_T); REL(s_dens);
-  REL(s_Z); REL(s_alphal); REL(s_alphad); REL(s_kmax); REL(s_ilor); REL(s_idop0);
-  REL(s_lastq); REL(s_fb); REL(s_fbpid); REL(s_wtile); REL(s_reach); REL(s_reachP); REL(s_fbmax); REL(s_facz); REL(s_rtemp); REL(s_ral); REL(s_xterm); REL(x_line); REL(q_g); REL(q_a); REL(q_w); REL(q_iso); REL(s_rec); REL(s_hasfb);
-  REL(s_nsamp); REL(s_out); REL(d_pdata2); REL(d_ptab);
-  REL(d_e); REL(d_ecs); REL(d_tau); REL(d_intens); REL(d_out); REL(d_last); REL(d_err);
-  REL(r_coef); REL(r_rcp); REL(r_par); REL(r_h); REL(r_s); REL(r_ip); REL(r_ang); REL(r_meta); REL(d_grid); REL(c_stage); REL(d_es_aux); REL(cub_tmp);
-#undef REL
-  for (CiaTable *t : c->cia) {
-    t->release();
-    delete t;
-  }
+  // every DevBuf member frees itself in its destructor (delete c below)
+  for (CiaTable *t : c->cia) delete t;
+  c->cia.clear();
   for (auto &kv : c->timers) {
     if (kv.second.a) cudaEventDestroy(kv.second.a);
     if (kv.second.b) cudaEventDestroy(kv.second.b);
   }
-  cudaStreamDestroy(c->own_stream);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
   if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);

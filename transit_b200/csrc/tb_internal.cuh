@@ -50,11 +50,16 @@ void tb_set_error(const char *fmt, ...);
     }                               \
   } while (0)
 
-// Device buffer that remembers its size; freed by tb_destroy through tb_ctx::bufs.
+// Device buffer that remembers its size.  It frees itself when its owner goes away (tb_destroy sets the
+// device and deletes the context; locals leave scope), so no release list can drift from the struct.
 template <typename T>
 struct DevBuf {
   T *p = nullptr;
   size_t n = 0;
+  DevBuf() = default;
+  DevBuf(const DevBuf &) = delete;
+  DevBuf &operator=(const DevBuf &) = delete;
+  ~DevBuf() { release(); }
   int ensure(size_t want) {
     if (want <= n && p) return TB_OK;
     if (p) cudaFree(p);

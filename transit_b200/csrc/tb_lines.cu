@@ -216,9 +216,19 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
   TB_REQUIRE(n >= 0 && n < 2000000000LL, TB_ERR_ARG, "line count out of range");
   TB_REQUIRE((int64_t)c->nrows * c->nwn < 2000000000LL, TB_ERR_ARG, "nrows*nwn too large");
   TB_CUDA(cudaSetDevice(c->device));
-  for (int64_t i = 0; i < n; i++)
-    TB_REQUIRE(isoid[i] >= 0 && isoid[i] < c->niso, TB_ERR_ARG, "isoid[%lld]=%d out of range",
-               (long long)i, (int)isoid[i]);
+  {  // per isotope the wavelengths must not decrease over the WHOLE list (not just between neighbours:
+     // an isotope split into two runs would get a wrong carried Doppler index, extinction.c:480-483)
+    std::vector<double> lastwl(c->niso > 0 ? c->niso : 1, -INFINITY);
+    for (int64_t i = 0; i < n; i++) {
+      TB_REQUIRE(isoid[i] >= 0 && isoid[i] < c->niso, TB_ERR_ARG, "isoid[%lld]=%d out of range",
+                 (long long)i, (int)isoid[i]);
+      TB_REQUIRE(!(wl[i] < lastwl[isoid[i]]), TB_ERR_UNSORTED,
+                 "line list is not sorted by ascending wavelength within isotope %d (line %lld; "
+                 "pylineread.py:369-383 guarantees it; the Doppler-index carry relies on it)",
+                 (int)isoid[i], (long long)i);
+      lastwl[isoid[i]] = wl[i];
+    }
+  }
   cudaStream_t st = c->stream;
   c->nlines = n; c->wfct = wfct; c->efct = efct;
   c->have_lines = false;

@@ -282,6 +282,22 @@ int tb_cia_run(tb_ctx *c) {
   std::vector<double> stage((size_t)nrad * (1 + ntab));
   double *ltemp = stage.data();
   for (int i = 0; i < nrad; i++) ltemp[i] = c->t_fct * c->t[i];
+  {  // interpcs refuses a layer outside the range common to all tables (crosssec.c:174-176,293-309);
+     // a silently clipped layer would come back with zero CIA and a plausible, wrong spectrum
+    double tmin = 0.0, tmax = 70000.0;
+    for (int n = 0; n < ntab; n++) {
+      tmin = fmax(tmin, c->cia[n]->temp[0]);
+      tmax = fmin(tmax, c->cia[n]->temp[c->cia[n]->nt - 1]);
+    }
+    for (int i = 0; i < nrad; i++) {
+      TB_REQUIRE(!(ltemp[i] < tmin), TB_ERR_DOMAIN,
+                 "The layer %d in the atmospheric model has a lower temperature (%.1f K) than the lowest allowed "
+                 "cross-section temperature (%.1f K).", i, ltemp[i], tmin);
+      TB_REQUIRE(!(ltemp[i] > tmax), TB_ERR_DOMAIN,
+                 "The layer %d in the atmospheric model has a higher temperature (%.1f K) than the highest allowed "
+                 "cross-section temperature (%.1f K).", i, ltemp[i], tmax);
+    }
+  }
   TB_TRY(c->c_stage.ensure(stage.size()));
   CiaPack P;
   P.n = 0;

@@ -137,7 +137,10 @@ static int64_t prof_half_size(double dwn, float dop, float lor, float ta, int64_
 extern "C" int tb_build_profiles(tb_ctx *c, int nDop, int nLor, float dmin, float dmax, float lmin,
                                  float lmax, float nwidth) {
   TB_REQUIRE(c->have_grid, TB_ERR_STATE, "tb_set_wn_grid must precede tb_build_profiles");
-  TB_REQUIRE(nDop >= 2 && nLor >= 2 && (int64_t)nDop * nLor < 32768, TB_ERR_ARG, "need nDop, nLor >= 2 and nDop*nLor < 32768");
+  // the line sum packs a cell into 14 bits of a record and keeps aDop[] in 256 shared doubles: refuse here,
+  // before a table of hundreds of MB is built, what tb_states_run could not use
+  TB_REQUIRE(nDop >= 2 && nLor >= 2 && nDop < 255 && (int64_t)nDop * nLor < 0x4000, TB_ERR_ARG,
+             "need 2 <= nDop < 255, nLor >= 2 and nDop*nLor < 16384 (got %d x %d)", nDop, nLor);
   TB_REQUIRE(dmin > 0 && dmax > dmin && lmin > 0 && lmax > lmin && nwidth > 0, TB_ERR_ARG,
              "bad width ranges");
   TB_CUDA(cudaSetDevice(c->device));
