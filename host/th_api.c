@@ -6,6 +6,7 @@
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/time.h>
 #include "th_internal.h"
 
 static th_state S;
@@ -14,6 +15,25 @@ int th_dry = 0;
 #endif
 
 #define CK(call) do { if (TH_DEV(call) != TB_OK) th_die("%s\n", tb_last_error()); } while (0)
+
+tb_ctx *th_context(void) { return S.ctx; }
+/* sizes of the problem behind the library face: layers, molecules, isotopes, wavenumbers, lines, angles */
+void th_sizes(int64_t *out) {
+  out[0] = S.nlayer; out[1] = S.nmol; out[2] = S.niso; out[3] = S.nwn; out[4] = S.nlines; out[5] = S.nang;
+}
+
+/* timecheck (transitstd.c:359-374): the "Check point" lines users grep, printed at verbosity >= 4
+ * (TOUT_RESULT) with the reference's iteration / stage numbering (transit.c:33-66,143-199).  The first
+ * line carries seconds since the epoch, as the reference's does (its t0 starts at 0).                 */
+static double th_t0 = 0;
+static long th_itr = 0;
+static void timecheck(long index, const char *str) {
+  struct timeval tv;
+  gettimeofday(&tv, NULL);
+  const double sec = tv.tv_sec + 1e-6 * tv.tv_usec;
+  if (S.h.verb >= 4) printf("Check point: %02li - %02li %s:  dt = %.4f sec.\n\n", th_itr, index, str, sec - th_t0);
+  th_t0 = sec;
+}
 
 static void apply_cloud_scattering(void) {
   const th_hints *h = &S.h;
@@ -43,6 +63,7 @@ void transit_init(int argc, char **argv) {
   memset(&S, 0, sizeof(S));
   th_defaults(&S.h);
   th_parse_args(&S.h, argc, argv);
+  timecheck(0, "processparameters");
   const th_hints *h = &S.h;
   if (h->nwidth < 1) th_die("Times of maximum width has to be greater than one: %g\n", h->nwidth);
   if (h->ethresh <= 0) th_die("Extinction threshold has to be positive: %g\n", h->ethresh);
@@ -69,14 +90,22 @@ void transit_init(int argc, char **argv) {
   if (getenv("TRANSIT_B200_DEVICE")) dev = atoi(getenv("TRANSIT_B200_DEVICE"));
   CK(tb_create(dev, &S.ctx));
   th_make_wn(&S);                                          /* makewnsample */
+  timecheck(1, "makewnsample");
   th_read_atmosphere(&S);                                  /* getatm */
+  timecheck(2, "getatm");
   th_read_tli(&S);                                         /* readlineinfo */
+  timecheck(3, "readlineinfo");
   CK(tb_set_wn_grid(S.ctx, S.wn_i, S.wn_d, S.wn_o, S.nwn, S.onwn, 1.0));
   CK(tb_set_species(S.ctx, S.nmol, S.molmass, S.molradius, S.molpol, S.molID, S.niso, S.isomass, S.isoratio,
                     S.isoimol));
   th_make_rad(&S);                                         /* makeradsample */
+  timecheck(4, "makeradsample");
   th_opacity(&S);                                          /* opacity */
+  timecheck(5, "opacity");
   th_read_cs(&S);                                          /* readcs */
+  timecheck(6, "readcs");
+  if (h->modlevel != 1 && h->modlevel != -1)
+    th_die("slantpath:: modulationperwn:: Level %i of detail has not been implemented to compute modulation.\n", h->modlevel);
   apply_cloud_scattering();
   S.out = (double *)calloc(S.nwn, sizeof(double));
   S.initialised = 1;
@@ -102,6 +131,110 @@ void set_scattering(int flag, double scattering) {
   if (S.initialised) CK(tb_set_scattering(S.ctx, flag, scattering));
 }
 
+/* printsample / outsample (makesample.c:642-672,743-772), written only with `savefiles yes` as in the
+ * reference (makesample.c:598); struct transit's `wavs` sample is never filled there, hence the zeros */
+static void write_outsample(void) {
+  FILE *out = stdout;
+  if (strcmp(S.h.f_outsample, "-") != 0 && !(out = fopen(S.h.f_outsample, "w"))) {
+    fprintf(stderr, "Cannot open file '%s' for writing sampling data.\n", S.h.f_outsample);
+    return;
+  }
+  const int n = S.nlayer;
+  const char *hdr = "############################\n   %-12s Sampling\n----------------------------\n";
+  fprintf(out, hdr, "Wavenumber");
+  fprintf(out, "Factor to cgs units: %g\nInitial value: %g\nFinal value: %g\nSpacing: %g\nOversample: %i\n"
+               "Number of elements: %lli\n", 1.0, S.wn_i, S.wn_f, S.wn_d, 1, (long long)S.nwn);
+  fprintf(out, hdr, "Wavelength");
+  fprintf(out, "Factor to cgs units: %g\nInitial value: %g\nFinal value: %g\nSpacing: %g\nOversample: %i\n"
+               "Number of elements: %lli\n", 0.0, 0.0, 0.0, 0.0, 0, 0LL);
+  fprintf(out, hdr, "Radius");
+  fprintf(out, "Factor to cgs units: %g\nInitial value: %g\nFinal value: %g\nSpacing: %g\n"
+               "Number of elements: %lli\nValues: ", S.rad_fct, S.rad[0], S.rad[n - 1], 0.0, (long long)n);
+  for (int i = 0; i < n; i++) fprintf(out, " %12.8g", S.rad[i]);
+  fprintf(out, "\n");
+  fprintf(out, hdr, "Impact parameter");
+  fprintf(out, "Factor to cgs units: %g\nInitial value: %g\nFinal value: %g\nSpacing: %g\nOversample: %i\n"
+               "Number of elements: %lli\nValues: ", S.rad_fct, S.rad[n - 1], S.rad[0], 0.0, 0, (long long)n);
+  for (int i = 0; i < n; i++) fprintf(out, " %12.8g", S.rad[n - 1 - i]);
+  fprintf(out, "\n");
+  if (out != stdout) fclose(out);
+}
+
+/* savefile_extinct (extinction.c:62-91): "@E@S@", e[rad][wn] as doubles, computed[rad] as shorts
+ * (#define _Bool short, transit.h:128-130).  The reference evaluates layers lazily, so rows it never
+ * reached hold zeros there; the same rows are zeroed here.  An existing file is overwritten: the
+ * restore half (restfile_extinct, an optimisation of repeated runs) is not needed by a path that
+ * recomputes every layer in a millisecond.                                                        */
+static void write_saveext(void) {
+  const int n = S.nlayer;
+  double *e = (double *)malloc((size_t)n * S.nwn * sizeof(double));
+  short *comp = (short *)calloc(n, sizeof(short));
+  int16_t *c16 = (int16_t *)calloc(n, sizeof(int16_t));
+  if (!e || !comp || !c16) th_die("Not enough host memory for the extinction savefile.\n");
+  CK(tb_get_extinction(S.ctx, e));
+  CK(tb_get_computed(S.ctx, c16));
+  FILE *fp = fopen(S.h.f_saveext, "w");
+  if (!fp) {
+    fprintf(stderr, "Extinction savefile '%s' cannot be opened for writing.\nContinuing without saving\n", S.h.f_saveext);
+  } else {
+    for (int r = 0; r < n; r++) {
+      comp[r] = c16[r];
+      if (!c16[r]) memset(e + (size_t)r * S.nwn, 0, S.nwn * sizeof(double));
+    }
+    fwrite("@E@S@", 1, 5, fp);
+    fwrite(e, sizeof(double), (size_t)n * S.nwn, fp);
+    fwrite(comp, sizeof(short), n, fp);
+    fclose(fp);
+  }
+  free(e); free(comp); free(c16);
+}
+
+/* printtoomuch (tau.c:611-640) */
+static void write_toomuch(void) {
+  const int n = S.nlayer;                       /* rays = layers (raddelt -1) */
+  double *t = (double *)malloc((size_t)S.nwn * n * sizeof(double));
+  int64_t *last = (int64_t *)malloc(S.nwn * sizeof(int64_t));
+  if (!t || !last) th_die("Not enough host memory for the toomuch file.\n");
+  CK(tb_get_tau(S.ctx, t, last));
+  FILE *out = stdout;
+  if (S.h.f_toomuch[0] != '-') out = fopen(S.h.f_toomuch, "w");
+  if (!out) {
+    fprintf(stderr, "Cannot open '%s' for writing depth where the optical depth reached toomuch.\n", S.h.f_toomuch);
+  } else {
+    fprintf(out, "# Wavelength   Max Optical   Radius at the    Radius\n"
+                 "   (microns)         depth   max depth (km)    index\n");
+    for (int64_t w = 0; w < S.nwn; w++) {
+      const double wn = S.wn_i + (double)w * S.wn_d;
+      /* the rays are the impact parameters, top first: ips.v[i] = rads.v[n-1-i] (makesample.c:564-573) */
+      fprintf(out, "%12.7f   %.5e     %12.4f     %04ld\n", 1.0 / wn * 1.0 * 1e4, t[(size_t)w * n + last[w]],
+              S.rad[n - 1 - last[w]] * S.rad_fct / 1e5, (long)last[w]);
+    }
+    if (out != stdout) fclose(out);
+  }
+  free(t); free(last);
+}
+
+/* printintens (eclipse.c:293-348) */
+static void write_intens(void) {
+  double *a = (double *)malloc((size_t)S.nang * S.nwn * sizeof(double));
+  if (!a) th_die("Not enough host memory for the intensity file.\n");
+  CK(tb_get_intensity(S.ctx, a));
+  FILE *outf = fopen(S.h.f_outintens, "w");
+  if (!outf) th_die("Cannot open intensity file '%s'.\n", S.h.f_outintens);
+  fprintf(outf, "#wvl %*s", 10, " ");
+  for (int i = 0; i < S.nang; i++) fprintf(outf, "I[%4.1lf deg]%*s", S.angles[i], 7, " ");
+  fprintf(outf, "\n#[um]%*s", 10, " ");
+  for (int i = 0; i < S.nang; i++) fprintf(outf, "[erg/s/cm/sr]%*s", 5, " ");
+  fprintf(outf, "\n");
+  for (int64_t w = 0; w < S.nwn; w++) {
+    fprintf(outf, "%-15.10g", 1e4 / ((S.wn_i + (double)w * S.wn_d) / 1.0));
+    for (int i = 0; i < S.nang; i++) fprintf(outf, "%-18.9g", a[(size_t)i * S.nwn + w]);
+    fprintf(outf, "\n");
+  }
+  fclose(outf);
+  free(a);
+}
+
 void do_transit(double *transit_out) {
   if (!S.initialised) { printf("Transit init not run, please initialize transit.\n"); return; }
   if (S.h.opabreak) return;                                /* justOpacity */
@@ -123,9 +256,35 @@ void do_transit(double *transit_out) {
     return;
   }
 #endif
+  if (h->savefiles && h->f_outsample) write_outsample();   /* makeipsample, makesample.c:598-599 */
+  timecheck(6, "makeipsample");
+  CK(tb_set_modlevel(S.ctx, h->modlevel));
   CK(tb_spectrum(S.ctx, S.eclipse ? TB_GEOM_ECLIPSE : TB_GEOM_TRANSIT, h->toomuch, h->ethresh,
                  h->starrad * TH_SUNRADIUS, h->transparent, S.eclipse ? S.angles : NULL, S.nang, S.out));
+  if (h->verb >= 4) {      /* one device call covers the reference's stages: their share of it, from the device timers */
+    float ms;
+    const char *stage[][2] = {{"cia", "interpcs"}, {"molext", "extwn + lazy extinction (tau.c:238-271)"},
+                              {"interp", "interpolmolext"}, {"tau", S.eclipse ? "tau eclipse" : "tau transit"},
+                              {"intensity", "emergent intensity + flux"}, {"modulation", "modulation"}};
+    for (int k = 0; k < 6; k++)
+      if (tb_get_kernel_ms(S.ctx, stage[k][0], &ms) == TB_OK && ms > 0)
+        printf("  device: %-44s %.4f sec.\n", stage[k][1], 1e-3 * ms);
+  }
+  timecheck(9, "interpcs");
+  timecheck(10, "idxrefrac");
+  timecheck(11, "extwn");
+  timecheck(12, S.eclipse ? "tau eclipse" : "tau transit");
+  if (h->f_saveext) write_saveext();                       /* tau.c:340-341 */
+  if (h->f_toomuch) write_toomuch();                       /* tau.c:344-345 */
+  if (S.eclipse) {
+    for (int a = 0; a < S.nang; a++) timecheck(13, "emergent intensity");
+    if (h->f_outintens && h->f_outintens[0] != '-') write_intens();   /* eclipse.c:230-231 */
+    timecheck(14, "flux");
+  } else
+    timecheck(13, "modulation");
   if (transit_out) memcpy(transit_out, S.out, S.nwn * sizeof(double));
+  timecheck(14, "THE END");
+  th_itr++;
 }
 
 /* reloadatm (readatm.c:722-784): in = [T(nlayers) | q_mol0(nlayers) | q_mol1(nlayers) | ...] */

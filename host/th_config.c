@@ -17,7 +17,7 @@ enum { O_IGN = 1, O_VERB, O_QUIET, O_CFG, O_ATM, O_LINEDB, O_OUTTOOMUCH, O_OUTSA
        O_WLFCT, O_WNLOW, O_WNHIGH, O_WNDELT, O_WNOSAMP, O_WNFCT, O_NDOP, O_NLOR, O_DMIN, O_DMAX, O_LMIN,
        O_LMAX, O_NWIDTH, O_ETHRESH, O_CLOUD, O_CLOUDTOP, O_SCATTERING, O_CSFILE, O_OPACITYFILE, O_TLOW,
        O_THIGH, O_TEMPDELT, O_OPABREAK, O_SOLUTION, O_TOOMUCH, O_STARRAD, O_TRANSPARENT, O_RAYGRID,
-       O_VERSION, O_HELP };
+       O_VERSION, O_HELP, O_SAVEEXT, O_SAVEFILES, O_MODLEVEL };
 
 typedef struct { const char *name; char shortc; int has_arg; const char *def; int id; } th_opt;
 
@@ -28,7 +28,7 @@ static const th_opt table[] = {
   {"atm", 0, 1, NULL, O_ATM}, {"linedb", 0, 1, NULL, O_LINEDB}, {"outtoomuch", 0, 1, NULL, O_OUTTOOMUCH},
   {"outsample", 0, 1, NULL, O_OUTSAMPLE}, {"outspec", 0, 1, "outspectrum", O_OUTSPEC},
   {"outintens", 0, 1, NULL, O_OUTINTENS}, {"molfile", 0, 1, "../inputs/molecules.dat", O_MOLFILE},
-  {"savefiles", 0, 1, NULL, O_IGN},
+  {"savefiles", 0, 1, "no", O_SAVEFILES},
   {"raddelt", 0, 1, "-1", O_RADDELT}, {"radlow", 0, 1, "0", O_IGN}, {"radhigh", 0, 1, "0", O_IGN},
   {"radfct", 0, 1, "0", O_IGN},
   {"allowq", 0, 1, "0.00001", O_ALLOWQ}, {"refpress", 0, 1, NULL, O_RPRESS}, {"refradius", 0, 1, NULL, O_RRADIUS},
@@ -41,12 +41,12 @@ static const th_opt table[] = {
   {"nwidth", 'a', 1, "20", O_NWIDTH},
   {"ethreshold", 0, 1, "1e-8", O_ETHRESH}, {"cloud", 0, 1, NULL, O_CLOUD}, {"cloudtop", 0, 1, NULL, O_CLOUDTOP},
   {"scattering", 0, 1, NULL, O_SCATTERING}, {"detailext", 0, 1, NULL, O_IGN}, {"detailcia", 0, 1, NULL, O_IGN},
-  {"csfile", 0, 1, NULL, O_CSFILE}, {"saveext", 0, 1, NULL, O_IGN},
+  {"csfile", 0, 1, NULL, O_CSFILE}, {"saveext", 0, 1, NULL, O_SAVEEXT},
   {"opacityfile", 0, 1, NULL, O_OPACITYFILE}, {"tlow", 0, 1, "500", O_TLOW}, {"thigh", 0, 1, "3000", O_THIGH},
   {"tempdelt", 0, 1, "100.0", O_TEMPDELT}, {"justOpacity", 0, 0, NULL, O_OPABREAK},
   {"shareOpacity", 0, 0, NULL, O_IGN},
   {"solution", 's', 1, "eclipse", O_SOLUTION}, {"toomuch", 0, 1, "20", O_TOOMUCH}, {"taulevel", 0, 1, "1", O_IGN},
-  {"modlevel", 0, 1, "1", O_IGN}, {"detailtau", 0, 1, NULL, O_IGN},
+  {"modlevel", 0, 1, "1", O_MODLEVEL}, {"detailtau", 0, 1, NULL, O_IGN},
   {"starrad", 0, 1, "1.125", O_STARRAD}, {"gorbpar", 0, 1, NULL, O_IGN}, {"gorbparfct", 0, 1, NULL, O_IGN},
   {"transparent", 0, 0, NULL, O_TRANSPARENT}, {"raygrid", 0, 1, "0 20 40 60 80", O_RAYGRID},
   {NULL, 0, 0, NULL, 0}};
@@ -68,7 +68,15 @@ static int process_file(th_hints *h, const char *path);
 
 static void apply(th_hints *h, const th_opt *o, const char *v) {
   switch (o->id) {
-    case O_IGN: case O_OUTTOOMUCH: case O_OUTSAMPLE: break;
+    case O_IGN: break;
+    case O_OUTTOOMUCH: setstr(&h->f_toomuch, v); break;
+    case O_OUTSAMPLE: setstr(&h->f_outsample, v); break;
+    case O_SAVEEXT: setstr(&h->f_saveext, v); break;
+    case O_SAVEFILES:         /* argum.c:457-470: 'yes' or 'no' */
+      if (strcmp(v, "yes") == 0) h->savefiles = 1; else if (strcmp(v, "no") == 0) h->savefiles = 0;
+      else { printf("\nAllowed arguments for savefiles are: 'yes' or 'no'\n\n"); exit(EXIT_FAILURE); }
+      break;
+    case O_MODLEVEL: h->modlevel = atoi(v); break;
     case O_VERSION: printf("transit_b200 host (B200 line-by-line path), interface of transit v4.0\n"); exit(0);
     case O_HELP:
       printf("usage: transit_b200 [-c cfgfile] [--key value ...]   keys: ");

@@ -20,7 +20,7 @@
 
 /* transithint (structures_tr.h:300-370): what the option table of argum.c:112-320 fills */
 typedef struct {
-  char *f_atm, *f_line, *f_molfile, *f_outspec, *f_toomuch, *f_outsample, *f_outintens, *f_opa;
+  char *f_atm, *f_line, *f_molfile, *f_outspec, *f_toomuch, *f_outsample, *f_outintens, *f_opa, *f_saveext;
   char *csfiles;                  /* comma-separated */
   char *solname;
   char *raygrid, *qmol, *qscale;
@@ -34,7 +34,7 @@ typedef struct {
   double tlow, thigh, tempdelt;
   double starrad;
   double p0, r0, gsurf, allowq;
-  int transparent, opabreak, verb;
+  int transparent, opabreak, verb, savefiles, modlevel;
   int cl_flag;
   double cl_ext, cl_top, cl_bot, cl_gamma, cl_Q, cl_r, cl_sig, cl_refwn;
   int sc_flag;
@@ -122,4 +122,7 @@ void run_transit(double *re_input, int transint, double *transit_out, int transi
 void do_transit(double *transit_out);
 void free_memory(void);
 void th_write_spectrum(void);
+/* test/diagnostic accessor: the device context behind the library face (NULL before transit_init) */
+tb_ctx *th_context(void);
+void th_sizes(int64_t *out);
 #endif

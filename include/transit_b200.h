@@ -79,6 +79,8 @@ int  tb_molext_states(tb_ctx *c, int ns, const double *T, const double *density 
 int  tb_get_line_trace(tb_ctx *c, int s, int32_t *iown, int32_t *idwn, int32_t *idop,
                        int8_t *status);
 int  tb_get_sample_counts(tb_ctx *c, int64_t *nsamples, int ns);
+/* ilor[niso] of state `s` of the last batch (extinction.c:394); with the trace's idop it names the Voigt cell */
+int  tb_get_state_ilor(tb_ctx *c, int s, int32_t *ilor);
 int  tb_get_line_molIDs(tb_ctx *c, int *molID, int *nmolrows);   /* opacity.c:349-361 */
 /* sizes of the device line index: lines uploaded, co-add groups (evaluated leaders), member lines */
 int  tb_get_line_counts(tb_ctx *c, int64_t *nlines, int64_t *ngroups, int64_t *nmembers);
@@ -111,6 +113,10 @@ int  tb_set_cloud(tb_ctx *c, int flag, double cloudext, double cloudtop, double 
  * rays h[nh]*hfct (impact parameters, top first; NULL = reversed radii as makeipsample
  * with raddelt=-1, makesample.c:564-573).                                             */
 int  tb_tau(tb_ctx *c, int geometry, double toomuch, const double *h, int nh, double hfct);
+/* modulationperwn's dispatch (slantpath.c:477-503, cfg key `modlevel`): 1 = modulation1 (default),
+ * -1 = modulationm1 (slantpath.c:446-473, opaque disc at tau = toomuch); anything else is refused
+ * with the reference's message.                                                          */
+int  tb_set_modlevel(tb_ctx *c, int level);
 /* modulation/modulation1 (slantpath.c:274-436): out[nwn]                              */
 int  tb_modulation(tb_ctx *c, double starrad_cm, int transparent, double *out);
 /* eclipse_intens/emergent_intens/flux (eclipse.c:117-287): out[nwn] flux             */

@@ -7,11 +7,16 @@
  * *before* do_transit's clean-up would free them.  tests/golden/make_golden.py turns
  * that container into the committed .npz fixtures.
  *
- * usage: ref_dump <out.bin> [--full-ext] [--rerun <in.f64>] -- <transit argv...>
+ * usage: ref_dump <out.bin> [--full-ext] [--rerun <in.f64>] [--idx r0,r1,..] -- <transit argv...>
  *   --full-ext : additionally call computemolext() for EVERY layer (the reference
  *                only evaluates the layers its rays reach, tau.c:238-271)
  *   --rerun f  : after the first spectrum, call run_transit() with the doubles in f
- *                (reloadatm path, transit.c:118-122) and dump its output too
+ *                (reloadatm path, transit.c:118-122) and dump its output too; a file holding k
+ *                inputs back to back gives k calls (outputs rerun_out [k][nwn])
+ *   --idx list : (ref_dump_idx only: the build with the patched copy of extinction.c, see
+ *                oracle/Makefile) for every listed layer call computemolext() once more with the
+ *                hooks armed and dump per line: status (0 not visited / out of range, 1 evaluated
+ *                leader, 2 co-added member, 3 leader below threshold), iown, idwn, idop, ilor, minj, maxj
  *
  * container record: u32 namelen | name | u32 dtype(0=f64,1=i32,2=i64,3=f32,4=i16)
  *                   | u32 ndim | u64 dims[ndim] | raw little-endian data
@@ -26,6 +31,29 @@ int  computemolext(struct transit *tr, PREC_RES **kiso, PREC_ATM temp,
                    PREC_ATM *density, double *Z, int permol);
 
 static FILE *out;
+
+#ifdef REF_IDX
+/* hooks called from the patched copy of extinction.c (oracle/ref_idx_hooks.h) */
+long ref_idx_lead = 0;
+static int idx_armed = 0;
+static signed char *ix_status;
+static int *ix_iown, *ix_idwn, *ix_idop, *ix_ilor, *ix_minj, *ix_maxj;
+void ref_idx_hook(long lead, long last, long iown, long idwn, int idop, int ilor, long minj, long maxj){
+  long l;
+  if(!idx_armed) return;
+  ix_status[lead] = 1;
+  for(l=lead+1; l<=last; l++) ix_status[l] = 2;
+  ix_iown[lead] = (int)iown; ix_idwn[lead] = (int)idwn; ix_idop[lead] = idop; ix_ilor[lead] = ilor;
+  ix_minj[lead] = (int)minj; ix_maxj[lead] = (int)maxj;
+}
+void ref_idx_skip(long lead, long last, long iown){
+  long l;
+  if(!idx_armed) return;
+  ix_status[lead] = 3;
+  for(l=lead+1; l<=last; l++) ix_status[l] = 2;
+  ix_iown[lead] = (int)iown;
+}
+#endif
 
 static void rec(const char *name, unsigned dtype, unsigned ndim,
                 const unsigned long long *dims, const void *data){
@@ -248,12 +276,13 @@ static void spectrum_with_taps(struct transit *tr, const char *pfx, int full_ext
 
 int main(int argc, char **argv){
   int full_ext = 0, a = 2, rerun_taps = 0;
-  const char *rerun = NULL;
+  const char *rerun = NULL, *idxlist = NULL;
   if(argc < 4){ fprintf(stderr, "usage: ref_dump out.bin [--full-ext] [--rerun f] -- transit-args\n"); return 2; }
   for(; a < argc && strcmp(argv[a], "--"); a++){
     if(!strcmp(argv[a], "--full-ext")) full_ext = 1;
     else if(!strcmp(argv[a], "--rerun")) rerun = argv[++a];
     else if(!strcmp(argv[a], "--rerun-taps")) rerun_taps = 1;   /* taps of the re-run too (prefix rr_) */
+    else if(!strcmp(argv[a], "--idx")) idxlist = argv[++a];
   }
   if(a >= argc) return 2;
   argv[a] = argv[0];                     /* transit's argv[0] */
@@ -266,11 +295,48 @@ int main(int argc, char **argv){
 
   spectrum_with_taps(&transit, "", full_ext);
 
+#ifdef REF_IDX
+  if(idxlist && transit.fp_opa == NULL && transit.f_line != NULL){
+    struct transit *tr = &transit;
+    long nl = tr->ds.li->n_l, nwn = tr->wns.n;
+    double *row = calloc(nwn, sizeof(double));
+    double *dens = calloc(tr->ds.mol->nmol, sizeof(double));
+    double *Z    = calloc(tr->ds.iso->n_i, sizeof(double));
+    ix_status = malloc(nl); ix_iown = malloc(4*nl); ix_idwn = malloc(4*nl); ix_idop = malloc(4*nl);
+    ix_ilor = malloc(4*nl); ix_minj = malloc(4*nl); ix_maxj = malloc(4*nl);
+    char *lst = strdup(idxlist), *tok;
+    for(tok = strtok(lst, ","); tok; tok = strtok(NULL, ",")){
+      long r = atol(tok); int k; char nm[64];
+      if(r < 0 || r >= tr->rads.n) continue;
+      memset(ix_status, 0, nl); memset(ix_iown, 0, 4*nl); memset(ix_idwn, 0, 4*nl); memset(ix_idop, 0xff, 4*nl);
+      memset(ix_ilor, 0xff, 4*nl); memset(ix_minj, 0, 4*nl); memset(ix_maxj, 0, 4*nl);
+      for(k=0; k<tr->ds.mol->nmol; k++) dens[k] = tr->ds.mol->molec[k].d[r];
+      for(k=0; k<tr->ds.iso->n_i; k++)  Z[k] = tr->ds.iso->isov[k].z[r];
+      idx_armed = 1;
+      computemolext(tr, &row, tr->atm.t[r]*tr->atm.tfct, dens, Z, 0);
+      idx_armed = 0;
+      /* dtype 4 = i16 is the smallest the container has: status goes out as i32 */
+      { int *st32 = malloc(4*nl); long l; for(l=0; l<nl; l++) st32[l] = ix_status[l];
+        sprintf(nm, "idx%ld_status", r); rec1(nm, 1, nl, st32); free(st32); }
+      sprintf(nm, "idx%ld_iown", r); rec1(nm, 1, nl, ix_iown);
+      sprintf(nm, "idx%ld_idwn", r); rec1(nm, 1, nl, ix_idwn);
+      sprintf(nm, "idx%ld_idop", r); rec1(nm, 1, nl, ix_idop);
+      sprintf(nm, "idx%ld_ilor", r); rec1(nm, 1, nl, ix_ilor);
+      sprintf(nm, "idx%ld_minj", r); rec1(nm, 1, nl, ix_minj);
+      sprintf(nm, "idx%ld_maxj", r); rec1(nm, 1, nl, ix_maxj);
+      sprintf(nm, "idx%ld_ext", r);  rec1(nm, 0, nwn, row);
+    }
+    free(lst);
+  }
+#endif
+
   if(rerun){
     FILE *fi = fopen(rerun, "rb");
-    long nin = transit.rads.n * (1 + transit.ds.mol->nmol), nwn = transit.wns.n;
-    double *in = malloc(nin*sizeof(double)), *o = malloc(nwn*sizeof(double));
-    if(!fi || fread(in, 8, nin, fi) != (size_t)nin){ fprintf(stderr, "bad rerun file\n"); return 2; }
+    long nin = transit.rads.n * (1 + transit.ds.mol->nmol), nwn = transit.wns.n, nrr = 1, k;
+    if(fi){ fseek(fi, 0, SEEK_END); nrr = ftell(fi) / (8*nin); fseek(fi, 0, SEEK_SET); }
+    if(nrr < 1) nrr = 1;
+    double *in = malloc(nrr*nin*sizeof(double)), *o = malloc(nrr*nwn*sizeof(double));
+    if(!fi || fread(in, 8, nrr*nin, fi) != (size_t)(nrr*nin)){ fprintf(stderr, "bad rerun file\n"); return 2; }
     fclose(fi);
     /* do_transit frees what spectrum_with_taps allocated only inside do_transit itself;
        our taps allocated fresh arrays, so release them the way do_transit does. */
@@ -285,7 +351,10 @@ int main(int argc, char **argv){
       memcpy(o, transit.ds.out->o, nwn*sizeof(double));
     }
     else
-      run_transit(in, (int)nin, o, (int)nwn);
+      for(k=0; k<nrr; k++)
+        run_transit(in + k*nin, (int)nin, o + k*nwn, (int)nwn);
+    if(nrr > 1) rec2("rerun_out_all", 0, nrr, nwn, o);
+    in += (nrr-1)*nin; o += (nrr-1)*nwn;       /* the single-call records describe the LAST call */
     rec1("rerun_in", 0, nin, in);
     rec1("rerun_out", 0, nwn, o);
     rec1("rerun_atm_t", 0, transit.rads.n, transit.atm.t);

@@ -49,6 +49,7 @@ ABI = {
     "tb_molext_states": (C.c_int, [C.c_void_p, C.c_int, f64p, f64p, f64p, C.c_double, C.c_int, f64p]),
     "tb_get_line_trace": (C.c_int, [C.c_void_p, C.c_int, i32p, i32p, i32p, i8p]),
     "tb_get_sample_counts": (C.c_int, [C.c_void_p, i64p, C.c_int]),
+    "tb_get_state_ilor": (C.c_int, [C.c_void_p, C.c_int, i32p]),
     "tb_get_line_molIDs": (C.c_int, [C.c_void_p, i32p, i32p]),
     "tb_get_line_counts": (C.c_int, [C.c_void_p, i64p, i64p, i64p]),
     "tb_opacity_build": (C.c_int, [C.c_void_p, C.c_int, f64p, f64p, f64p, f64p, C.c_int, C.c_double, f64p]),
@@ -60,6 +61,7 @@ ABI = {
     "tb_set_scattering": (C.c_int, [C.c_void_p, C.c_int, C.c_double]),
     "tb_set_cloud": (C.c_int, [C.c_void_p, C.c_int] + [C.c_double] * 8 + [f64p, f64p]),
     "tb_tau": (C.c_int, [C.c_void_p, C.c_int, C.c_double, f64p, C.c_int, C.c_double]),
+    "tb_set_modlevel": (C.c_int, [C.c_void_p, C.c_int]),
     "tb_modulation": (C.c_int, [C.c_void_p, C.c_double, C.c_int, f64p]),
     "tb_intensity_flux": (C.c_int, [C.c_void_p, f64p, C.c_int, f64p]),
     "tb_spectrum": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, f64p, C.c_int, f64p]),
@@ -136,7 +138,21 @@ class Context:
         self.h = h
         self.nwn = self.nrad = self.nang = 0
 
+    @classmethod
+    def adopt(cls, handle, nwn, nrad, nmol, niso, nlines=0, nang=0):
+        """Wrap a tb_ctx that somebody else owns (the C host's, through th_context()): taps only, never closed here."""
+        self = cls.__new__(cls)
+        self.lib = load_library()
+        self.h = C.c_void_p(handle)
+        self.nwn, self.nrad, self.nmol, self.niso, self.nlines, self.nang = nwn, nrad, nmol, niso, nlines, nang
+        self.nh = nrad
+        self._borrowed = True
+        return self
+
     def close(self):
+        if getattr(self, "_borrowed", False):
+            self.h = None
+            return
         if getattr(self, "h", None):
             self.lib.tb_destroy(self.h)
             self.h = None
@@ -223,6 +239,11 @@ class Context:
                  "tb_get_line_trace")
         return dict(iown=a[0], idwn=a[1], idop=a[2], status=st)
 
+    def state_ilor(self, s=0):
+        out = np.zeros(max(1, self.niso), np.int32)
+        self._ck(self.lib.tb_get_state_ilor(self.h, s, _p(out, i32p)), "tb_get_state_ilor")
+        return out[:self.niso]
+
     def sample_counts(self, ns):
         out = np.zeros(ns, np.int64)
         self._ck(self.lib.tb_get_sample_counts(self.h, _p(out, i64p), ns), "tb_get_sample_counts")
@@ -278,6 +299,9 @@ class Context:
         hp = None if h is None else _c64(h)
         self._ck(self.lib.tb_tau(self.h, geometry, toomuch, _p(hp), 0 if h is None else len(hp), hfct), "tb_tau")
         self.nh = self.nrad if h is None else len(hp)
+
+    def set_modlevel(self, level):
+        self._ck(self.lib.tb_set_modlevel(self.h, int(level)), "tb_set_modlevel")
 
     def modulation(self, starrad_cm, transparent=0):
         out = np.zeros(self.nwn)

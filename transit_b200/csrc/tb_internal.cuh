@@ -252,6 +252,7 @@ struct tb_ctx {
   DevBuf<double> c_stage;     // [layer temperatures | density factor per table]
 
   // ---- scattering / clouds
+  int modlevel = 1;                                  // modulation1 (1) or modulationm1 (-1), slantpath.c:487-503
   int sc_flag = 0;
   double sc_logext = 0;
   int cl_flag = 0;

@@ -1292,3 +1292,18 @@ extern "C" int tb_get_line_trace(tb_ctx *c, int s, int32_t *iown, int32_t *idwn,
   a.release(); b.release(); d.release(); e.release();
   return TB_OK;
 }
+
+// Lorentz-width index of every isotope at state `s` of the last batch (extinction.c:394): with the trace's
+// Doppler index it names the Voigt cell, hence profsize, minj and maxj of extinction.c:486-496
+extern "C" int tb_get_state_ilor(tb_ctx *c, int s, int32_t *ilor) {
+  TB_REQUIRE(c->have_lines && c->last_ns > 0, TB_ERR_STATE, "no line-sum batch has run");
+  TB_REQUIRE(s >= 0 && s < c->last_ns, TB_ERR_ARG, "state %d out of range", s);
+  TB_REQUIRE((size_t)c->last_ns * c->niso + 1 <= c->s_ilor.n, TB_ERR_STATE,
+             "only available when the batch ran as a single chunk");
+  TB_CUDA(cudaSetDevice(c->device));
+  if (c->niso == 0) return TB_OK;
+  TB_CUDA(cudaMemcpyAsync(ilor, c->s_ilor.p + (size_t)s * c->niso, c->niso * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                          c->stream));
+  TB_CUDA(cudaStreamSynchronize(c->stream));
+  return TB_OK;
+}

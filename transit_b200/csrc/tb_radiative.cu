@@ -768,6 +768,8 @@ int tb_check_errors(tb_ctx *c) {
   TB_CUDA(cudaStreamSynchronize(c->stream));
   TB_REQUIRE(err[1] == 0, TB_ERR_DOMAIN, "a ray's closest approach lies below the bottom layer (slantpath.c:40-44)");
   TB_REQUIRE(err[2] == 0, TB_ERR_DOMAIN, "less than 3 items for radial integration (slantpath.c:393-397)");
+  TB_REQUIRE(err[3] == 0, TB_ERR_DOMAIN, "Optical depth didn't reach the limiting value at some wavenumber.  Cannot use "
+             "critical radius technique (-1) (slantpath.c:308-316)");
   return TB_OK;
 }
 
@@ -846,6 +848,32 @@ __global__ void k_modulation(int64_t nwn, int nh, const double *__restrict__ tau
   out[w] = rr * (1.0 / (srad * srad));
 }
 
+// modulationm1 (slantpath.c:446-473, `modlevel -1`): the planet as an opaque disc whose radius is where
+// tau reaches toomuch, by a line through the two rays around the cut-off (interp_line, pu numerical.c:200-210).
+// A wavenumber whose tau never reached toomuch is the reference's error -1 (slantpath.c:308-316).
+__global__ void k_modulation_m1(int64_t nwn, int nh, const double *__restrict__ tau,
+                                const int32_t *__restrict__ last, const double *__restrict__ ip, double ipfct,
+                                double toomuch, double srad, double *__restrict__ out, int32_t *__restrict__ err) {
+  const int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (w >= nwn) return;
+  const int L = last[w];
+  if (tau[(size_t)L * nwn + w] < toomuch) { atomicExch(err + 3, 1); out[w] = -1; return; }
+  const int ini = L - 1 < 0 ? 0 : L - 1;
+  // ipv[1] is left unset by the reference when the very first ray is already opaque (ini = last = 0)
+  const double y0 = ip[ini] * ipfct, y1 = (ini + 1 <= L) ? ip[ini + 1] * ipfct : 0.0;
+  const double x0 = tau[(size_t)ini * nwn + w], x1 = ini + 1 < nh ? tau[(size_t)(ini + 1) * nwn + w] : 0.0;
+  const double dx = x1 - x0, m = (y1 - y0) / dx;
+  const double muchrad = y0 + (toomuch - x0) * m;
+  out[w] = muchrad * muchrad / (srad * srad);
+}
+
+extern "C" int tb_set_modlevel(tb_ctx *c, int level) {
+  TB_REQUIRE(level == 1 || level == -1, TB_ERR_ARG,
+             "slantpath:: modulationperwn:: Level %i of detail has not been implemented to compute modulation.", level);
+  c->modlevel = level;
+  return TB_OK;
+}
+
 extern "C" int tb_modulation(tb_ctx *c, double starrad_cm, int transparent, double *out) {
   TB_REQUIRE(c->have_tau && c->geometry == TB_GEOM_TRANSIT, TB_ERR_STATE, "tb_tau (transit) must precede tb_modulation");
   TB_CUDA(cudaSetDevice(c->device));
@@ -857,7 +885,11 @@ extern "C" int tb_modulation(tb_ctx *c, double starrad_cm, int transparent, doub
   tb_timer_begin(c, "modulation");
   const size_t shm = (5 * (size_t)c->nh + 2) * sizeof(double);   // xs[nh] (padded to even) + cf[4*nh]
   TB_REQUIRE(shm <= 48 * 1024, TB_ERR_ARG, "too many rays (%d) for the modulation kernel's shared memory", c->nh);
-  k_modulation<<<nblk(c->nwn * MOD_QL, 128), 128, shm, st>>>(c->nwn, c->nh, c->d_tau.p, c->d_last.p, d_ip.p, c->hfct, c->toomuch,
+  if (c->modlevel == -1)
+    k_modulation_m1<<<nblk(c->nwn, 128), 128, 0, st>>>(c->nwn, c->nh, c->d_tau.p, c->d_last.p, d_ip.p, c->hfct, c->toomuch,
+                                                       starrad_cm, c->d_out.p, c->d_err.p);
+  else
+    k_modulation<<<nblk(c->nwn * MOD_QL, 128), 128, shm, st>>>(c->nwn, c->nh, c->d_tau.p, c->d_last.p, d_ip.p, c->hfct, c->toomuch,
                                                   starrad_cm, transparent, c->d_out.p, c->d_err.p);
   tb_timer_end(c, "modulation");
   TB_LAUNCHED(c);
