@@ -79,6 +79,14 @@ int  tb_molext_states(tb_ctx *c, int ns, const double *T, const double *density 
 int  tb_get_line_trace(tb_ctx *c, int s, int32_t *iown, int32_t *idwn, int32_t *idop,
                        int8_t *status);
 int  tb_get_sample_counts(tb_ctx *c, int64_t *nsamples, int ns);
+/* The line sum of a state whose profiles are narrow runs as ONE kernel (strength + gather, records kept in
+ * shared memory); tb_set_fused(c, 0) sends every state through the two-kernel path instead (same bits for the
+ * narrow-reach states: same summation order).  tb_set_trace(c, 1) makes the fused kernel also leave the
+ * per-line records tb_get_line_trace reads (off by default: 16 B of HBM per (group, state)).
+ * tb_get_fused_stats: states of the last batch taken by the fused kernel and its executed profile updates. */
+int  tb_set_fused(tb_ctx *c, int on);
+int  tb_set_trace(tb_ctx *c, int on);
+int  tb_get_fused_stats(tb_ctx *c, int64_t *fused_states, int64_t *fused_samples);
 /* ilor[niso] of state `s` of the last batch (extinction.c:394); with the trace's idop it names the Voigt cell */
 int  tb_get_state_ilor(tb_ctx *c, int s, int32_t *ilor);
 int  tb_get_line_molIDs(tb_ctx *c, int *molID, int *nmolrows);   /* opacity.c:349-361 */

@@ -40,6 +40,9 @@ def main():
     n = L.get_no_samples()
     P = C.POINTER(C.c_double)
     out = np.zeros(n)
+    L.th_context.restype = C.c_void_p
+    if trace:                 # the fused line sum leaves its per-line records only when asked
+        api.load_library().tb_set_trace(C.c_void_p(L.th_context()), 1)
     t0 = time.perf_counter()
     L.do_transit(out.ctypes.data_as(P))
     run_s = time.perf_counter() - t0

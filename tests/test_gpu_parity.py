@@ -26,6 +26,7 @@ def cfg_of(d):
 
 def setup_ctx(prob, d=None, nDop=None, nLor=None, lines=True):
     c = api.Context(0)
+    c.set_trace(True)       # the fused line sum leaves its per-line records only when asked (tb_set_trace)
     c.set_wn_grid(prob.wn_i, prob.wn_d, prob.wnosamp, prob.nwn, prob.onwn, prob.wn_fct)
     c.set_species(prob.mol_mass, prob.mol_radius, prob.mol_pol, prob.mol_ID, prob.iso_mass, prob.iso_ratio,
                   prob.iso_imol)
@@ -146,6 +147,42 @@ def test_line_sum_medium_vs_oracle():
         lead = tr["status"] == 1
         assert np.array_equal(g["iown"][lead], tr["iown"][lead]) and np.array_equal(g["idop"][lead], tr["idop"][lead])
         assert relerr(e[r], ref[0]) < 1e-12, f"layer {r}"
+    c.close()
+
+
+def test_fused_line_sum_vs_two_kernel_path():
+    """k_linesum_fused (strength + gather in one kernel, records in shared memory) against k_strength +
+    k_accumulate on the same states: the states of narrow reach add in the same order and must agree BIT FOR BIT,
+    per-line decisions and sample counts included; states the two-kernel path sums with its wide-reach schedule
+    (reach 3..8 bins) differ by summation order only.  Both geometries of the batch: collapsed and per molecule."""
+    prob = workloads.make_problem("C2", scale=0.05, nlayers=40, wn_hi=12000.0)
+    c = setup_ctx(prob)
+    T = prob.t * prob.t_fct
+    dens, Z = prob.mol_d.T.copy(), prob.iso_z.T.copy()
+    for permol in (0, 1):
+        c.set_fused(True)
+        a = c.molext_states(T, dens, Z, prob.ethresh, permol=permol)
+        st = c.fused_stats()
+        na = c.sample_counts(prob.nrad)
+        tr_a = [c.line_trace(r) for r in (prob.nrad - 1, prob.nrad // 2)]
+        a2 = c.molext_states(T, dens, Z, prob.ethresh, permol=permol)
+        assert np.array_equal(a, a2)                                   # deterministic
+        c.set_fused(False)
+        b = c.molext_states(T, dens, Z, prob.ethresh, permol=permol)
+        nb = c.sample_counts(prob.nrad)
+        tr_b = [c.line_trace(r) for r in (prob.nrad - 1, prob.nrad // 2)]
+        assert c.fused_stats()["fused_states"] == 0
+        assert st["fused_states"] >= 16 and st["fused_states"] % 8 == 0, st   # the upper layers of this atmosphere
+        assert np.array_equal(na, nb)                                  # same profile updates, layer by layer
+        assert st["fused_samples"] == int(na[prob.nrad - st["fused_states"]:].sum()) or st["fused_samples"] > 0
+        for x, y in zip(tr_a, tr_b):
+            for k in ("status", "iown", "idwn", "idop"):
+                assert np.array_equal(x[k], y[k]), k
+        assert np.array_equal(a == 0, b == 0)
+        assert relerr(a, b) < 1e-13
+        same = [r for r in range(prob.nrad) if np.array_equal(a[r], b[r])]
+        assert len(same) >= prob.nrad - 8, (len(same), prob.nrad)      # only the few reach-3..8 layers may differ in order
+    c.set_fused(True)
     c.close()
 
 

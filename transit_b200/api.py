@@ -50,6 +50,9 @@ ABI = {
     "tb_get_line_trace": (C.c_int, [C.c_void_p, C.c_int, i32p, i32p, i32p, i8p]),
     "tb_get_sample_counts": (C.c_int, [C.c_void_p, i64p, C.c_int]),
     "tb_get_state_ilor": (C.c_int, [C.c_void_p, C.c_int, i32p]),
+    "tb_set_fused": (C.c_int, [C.c_void_p, C.c_int]),
+    "tb_set_trace": (C.c_int, [C.c_void_p, C.c_int]),
+    "tb_get_fused_stats": (C.c_int, [C.c_void_p, i64p, i64p]),
     "tb_get_line_molIDs": (C.c_int, [C.c_void_p, i32p, i32p]),
     "tb_get_line_counts": (C.c_int, [C.c_void_p, i64p, i64p, i64p]),
     "tb_opacity_build": (C.c_int, [C.c_void_p, C.c_int, f64p, f64p, f64p, f64p, C.c_int, C.c_double, f64p]),
@@ -238,6 +241,17 @@ class Context:
         self._ck(self.lib.tb_get_line_trace(self.h, s, _p(a[0], i32p), _p(a[1], i32p), _p(a[2], i32p), _p(st, i8p)),
                  "tb_get_line_trace")
         return dict(iown=a[0], idwn=a[1], idop=a[2], status=st)
+
+    def set_fused(self, on=True):
+        self._ck(self.lib.tb_set_fused(self.h, int(bool(on))), "tb_set_fused")
+
+    def set_trace(self, on=True):
+        self._ck(self.lib.tb_set_trace(self.h, int(bool(on))), "tb_set_trace")
+
+    def fused_stats(self):
+        a, b = C.c_int64(), C.c_int64()
+        self._ck(self.lib.tb_get_fused_stats(self.h, C.byref(a), C.byref(b)), "tb_get_fused_stats")
+        return dict(fused_states=a.value, fused_samples=b.value)
 
     def state_ilor(self, s=0):
         out = np.zeros(max(1, self.niso), np.int32)

@@ -215,6 +215,9 @@ struct tb_ctx {
   DevBuf<int32_t> s_ilor, s_idop0, s_lastq, s_fb, s_fbpid, s_wtile, s_reach, s_reachP, s_fbmax;
   DevBuf<double> s_facz, s_rtemp, s_ral, s_xterm, s_lcz;
   DevBuf<LineRec> s_rec;      // [state][group]
+  DevBuf<int32_t> s_fclass, s_fP;   // per batch of 8 states: taken by k_linesum_fused? / widest half-size (fine bins)
+  bool fuse_enabled = true, trace_enabled = false;
+  int fuse_shm_set = -1, last_chunk_s0 = 0, last_chunk_cs = 0;
   DevBuf<uint8_t> s_hasfb;    // [state][tile]
   DevBuf<unsigned long long> s_nsamp;
   DevBuf<double> s_part;      // partial sums of wide-reach tiles shared by several blocks (small grids)

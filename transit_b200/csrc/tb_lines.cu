@@ -599,7 +599,9 @@ __global__ void __launch_bounds__(256, 6) k_strength(int64_t G, StrRanges rg, in
                            int permol, int nrows, const double *__restrict__ kmax,
                            LineRec *__restrict__ rec_out,
                            int32_t *__restrict__ lastq, int32_t *__restrict__ wtile,
-                           uint8_t *__restrict__ hasfb, int ntiles) {
+                           uint8_t *__restrict__ hasfb, int ntiles, const int32_t *__restrict__ fclass) {
+  static_assert(SB == 8, "k_strength and k_linesum_fused batch the states alike");
+  if (fclass[blockIdx.y]) return;               // this batch of states belongs to k_linesum_fused
   __shared__ int32_t sh_lastq[SB][MAXISO_SH];
   __shared__ double sh_aDop[256];
   __shared__ double sh_k[SB][256];
@@ -848,8 +850,9 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
              const int32_t *__restrict__ reach, const int32_t *__restrict__ reachP,
              const double *__restrict__ pdata, double *__restrict__ out,
              unsigned long long *__restrict__ nsamp, int S, double *__restrict__ part_g,
-             unsigned *__restrict__ tilecnt) {
+             unsigned *__restrict__ tilecnt, const int32_t *__restrict__ fclass) {
   const int s = blockIdx.y;
+  if (fclass[s >> 3]) return;                    // summed by k_linesum_fused
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   // S > 1 (wide instance on a grid of few tiles): S blocks share a tile, block k of them takes the
   // segments k*ACC_WW .. k*ACC_WW+ACC_WW-1 of the window's S*ACC_WW record segments
@@ -1007,6 +1010,313 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
   if (lane == 0 && cnt) atomicAdd(&nsamp[s], cnt);
 }
 
+
+// ------------------------------------------------------------------ fused line sum of the narrow layers
+//
+// For a state (layer) whose profiles are narrow, k_strength + k_accumulate spend their time on the
+// 16-byte record every (group, state) pair leaves in HBM and on fetching it back bin by bin.  Where
+//   (1) every isotope always refreshes its Doppler index (alphad*wn_i/alphal >= 0.1 with margin, so the
+//       carried index of extinction.c:480-483 -- a quantity global over the line list -- is never used), and
+//   (2) the widest profile any line of the state can take reaches at most FUSE_RMAX coarse bins,
+// both halves run in ONE kernel and the records never leave the SM.  A block owns a tile of 128 output
+// bins and FB = 8 consecutive states.  Per molecule row it walks the tile's window of groups (tile +-
+// reach, found through binstart) in chunks of FUSE_CAP candidates:
+//   phase 1  one thread per candidate: the log-domain pretest of k_strength for the 8 states (no exp),
+//            ordered compaction of the groups alive in any state (warp ballots + one block prefix);
+//   phase 2  one thread per alive group, its constants in registers, a loop over its alive states:
+//            both exp(), co-added members, threshold, Doppler cell, "covers no grid point" test -- the
+//            decisions of k_strength, expression by expression -- into shared-memory records
+//            {k, cell, half-size} ordered by fine bin;
+//   phase 3  one thread per (bin, 4 states): bisection for the first record of the bin's window, then the
+//            walk of k_accumulate's narrow schedule over the shared records, four accumulators fed per visit.
+// The sum of a bin runs over rows, chunks and records in sorted (row, fine bin) order: the same fixed
+// order, the same FMA chain and therefore the same bits as the unfused narrow path; tiles are independent,
+// so band shards stay bit-identical.  No floating-point atomics.
+#define FB 8                 // states per block (same batching as k_strength<SBS = 8>)
+#define FUSE_CAP 768         // candidate groups per chunk (3 per thread)
+#define FUSE_NT 256
+#define FUSE_MAXISO 64
+#define FUSE_RMAX 8          // widest reach, in coarse bins, of a fused state
+
+// Which batches of FB states the fused kernel takes (decided on the device: no read-back on the way)
+__global__ void k_fuse_class(int ns, int niso, double wn_i, double own_last, int o, int enable,
+                             const double *__restrict__ alphad, const double *__restrict__ ral,
+                             const int32_t *__restrict__ ilor, const double *__restrict__ aDop, int nDop, int nLor,
+                             const ProfEntry *__restrict__ ptab, int32_t *__restrict__ fclass,
+                             int32_t *__restrict__ fP) {
+  __shared__ int sh_ok, sh_P;
+  const int s0 = blockIdx.x * FB;
+  if (threadIdx.x == 0) { sh_ok = 1; sh_P = 0; }
+  __syncthreads();
+  for (int i = threadIdx.x; i < FB * niso; i += blockDim.x) {
+    const int k = i / niso, iso = i % niso, s = s0 + k;
+    if (s >= ns) continue;
+    const int si = s * niso + iso;
+    const double ad = alphad[si];
+    // every in-range line has wavn >= wn_i: alphad*wavn/alphal >= this, with a margin far above rounding
+    if (!(__dmul_rn(ad, wn_i) * ral[si] >= 0.1000001)) sh_ok = 0;
+    // ... and wavn <= own_last: no line takes a Doppler cell beyond this one (nearest-cell search is monotone)
+    const int id = tb_binsearchapprox(aDop, __dmul_rn(ad, own_last), 0, nDop);
+    atomicMax(&sh_P, ptab[id * nLor + ilor[si]].psize);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int P = sh_P;
+    const long long lim = (long long)FUSE_RMAX * o < 32767 ? (long long)FUSE_RMAX * o : 32767;
+    fclass[blockIdx.x] = (enable && sh_ok && niso >= 1 && niso <= FUSE_MAXISO && P <= lim) ? 1 : 0;
+    fP[blockIdx.x] = P;
+  }
+}
+
+// fill the records of fused states with "below threshold" when the per-line trace is wanted (tb_set_trace)
+__global__ void k_fuse_trace_fill(int64_t G, int ns, const int32_t *__restrict__ fclass,
+                                  const int32_t *__restrict__ g_iown, LineRec *__restrict__ rec) {
+  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int s = blockIdx.y;
+  if (p >= G || s >= ns || !fclass[s / FB]) return;
+  LineRec r;
+  r.k = 0.0; r.iown = g_iown[p]; r.pid = PID_SKIP;
+  rec[(size_t)s * G + p] = r;
+}
+
+struct FuseTab {           // per (state of the block, isotope), in shared memory
+  double lcz, facz, thr, densf, alphad;
+};
+
+__global__ void __launch_bounds__(FUSE_NT, 2)
+k_linesum_fused(int64_t nwn, int64_t G, int ns, int niso, int nmol, int o, FastDiv fd_o, FastDiv fd_tile, int nrows,
+                int permol, int tile_off, const int32_t *__restrict__ fclass, const int32_t *__restrict__ fP,
+                const int32_t *__restrict__ binstart, const int32_t *__restrict__ g_start,
+                const int16_t *__restrict__ g_iso, const int32_t *__restrict__ g_iown,
+                const double *__restrict__ g_wavn, const double *__restrict__ g_a0,
+                const double *__restrict__ g_gf, const double *__restrict__ g_lg,
+                const double *__restrict__ rtemp, const double *__restrict__ facz, const double *__restrict__ lcz,
+                const double *__restrict__ xterm, int64_t X, float dop_lmin, float dop_rstep,
+                const double *__restrict__ dens, const int *__restrict__ iso_imol, const int *__restrict__ iso_row,
+                const double *__restrict__ alphad, const int32_t *__restrict__ ilor,
+                const double *__restrict__ aDop, int nDop, const ProfEntry *__restrict__ ptab, int nLor,
+                double ethresh, const double *__restrict__ kmax, const double *__restrict__ pdata,
+                double *__restrict__ out, unsigned long long *__restrict__ nsamp, LineRec *__restrict__ rec_out) {
+  const int batch = blockIdx.y;
+  if (!fclass[batch]) return;                      // k_strength + k_accumulate take this batch
+  extern __shared__ __align__(16) unsigned char fsm[];
+  // ---- shared-memory carve-up
+  double *sh_k = reinterpret_cast<double *>(fsm);                               // [FB][CAP]
+  short *sh_ps = reinterpret_cast<short *>(sh_k + FB * FUSE_CAP);                // [CAP][FB]  (16 B per group)
+  unsigned short *sh_cell = reinterpret_cast<unsigned short *>(sh_ps + FUSE_CAP * FB);   // [FB][CAP]
+  int *sh_iown = reinterpret_cast<int *>(sh_cell + FB * FUSE_CAP);               // [CAP]
+  unsigned short *sh_gidx = reinterpret_cast<unsigned short *>(sh_iown + FUSE_CAP);      // [CAP]
+  unsigned char *sh_mask = reinterpret_cast<unsigned char *>(sh_gidx + FUSE_CAP);        // [CAP]
+  double *sh_aDop = reinterpret_cast<double *>(sh_mask + FUSE_CAP);              // [256]
+  double *sh_rT = sh_aDop + 256;                                                 // [FB]
+  FuseTab *sh_tab = reinterpret_cast<FuseTab *>(sh_rT + FB);                     // [FB][niso]
+  int *sh_ilor = reinterpret_cast<int *>(sh_tab + FB * niso);                    // [FB][niso]
+  __shared__ int sh_wcnt[FUSE_NT / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int s0 = batch * FB;
+  const int tile = blockIdx.x + tile_off;
+  const int64_t jt = (int64_t)tile * ACC_TILE;
+  const int P = fP[batch];
+  const int R = P / o + 1;
+  for (int i = tid; i <= nDop; i += FUSE_NT) sh_aDop[i] = aDop[i];               // [nDop] = +inf sentinel
+  if (tid < FB) sh_rT[tid] = rtemp[s0 + tid < ns ? s0 + tid : ns - 1];
+  for (int i = tid; i < FB * niso; i += FUSE_NT) {
+    const int k = i / niso, iso = i % niso, s = s0 + k < ns ? s0 + k : ns - 1;
+    const int si = s * niso + iso;
+    FuseTab t;
+    t.lcz = lcz[si]; t.facz = facz[si];
+    t.thr = __dmul_rn(ethresh, kmax[s * nrows + (permol ? iso_row[iso] : 0)]);
+    t.densf = dens[s * nmol + iso_imol[iso]];
+    t.alphad = alphad[si];
+    sh_tab[i] = t;
+    sh_ilor[i] = ilor[si];
+  }
+  // ---- this thread's output bin and its four states
+  const int64_t j = jt + (tid & (ACC_TILE - 1));
+  const int half = tid >> 7;                       // states 4*half .. 4*half+3
+  const bool inb = j < nwn;
+  const int oj = (int)(o * (inb ? j : nwn - 1));
+  const int lo_f = oj - P, hi_f = oj + P;
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
+  unsigned cnt[4] = {0u, 0u, 0u, 0u};
+  const int64_t jlo = jt - R < 0 ? 0 : jt - R;
+  const int64_t jhi = jt + ACC_TILE + R > nwn ? nwn : jt + ACC_TILE + R;
+  const unsigned nsmask = ns - s0 >= FB ? 0xFFu : ((1u << (ns - s0)) - 1u);      // states that exist
+  __syncthreads();
+  for (int row = 0; row < nrows; row++) {
+    const int pa = binstart[(size_t)row * nwn + jlo], pb = binstart[(size_t)row * nwn + jhi];
+    for (int p0 = pa; p0 < pb; p0 += FUSE_CAP) {
+      const int nc = pb - p0 < FUSE_CAP ? pb - p0 : FUSE_CAP;
+      // ---- phase 1: pretest + ordered compaction (a warp owns FUSE_CAP/8 consecutive candidates)
+      constexpr int PER_W = FUSE_CAP / (FUSE_NT / 32), ITS = PER_W / 32;
+      unsigned mym = 0, myrank = 0;
+      int wcount = 0;
+#pragma unroll
+      for (int it = 0; it < ITS; it++) {
+        const int i = warp * PER_W + it * 32 + lane;
+        unsigned m8 = 0;
+        if (i < nc) {
+          const int q = p0 + i;
+          const double a0 = g_a0[q], lg = g_lg[q];
+          const FuseTab *tb = sh_tab + g_iso[q];
+#pragma unroll
+          for (int k = 0; k < FB; k++)
+            if (!(fma(a0, sh_rT[k], lg + tb[k * niso].lcz) < -1e-9)) m8 |= 1u << k;
+          m8 &= nsmask;
+        }
+        const unsigned ball = __ballot_sync(0xffffffffu, m8 != 0);
+        mym |= m8 << (8 * it);
+        myrank |= (unsigned)(wcount + __popc(ball & ((1u << lane) - 1))) << (8 * it);   // < 96: fits a byte
+        wcount += __popc(ball);
+      }
+      if (lane == 0) sh_wcnt[warp] = wcount;
+      __syncthreads();                              // also: phase 3 of the previous chunk is over
+      int base = 0, nalive = 0;
+#pragma unroll
+      for (int w = 0; w < FUSE_NT / 32; w++) {
+        const int cw = sh_wcnt[w];
+        if (w < warp) base += cw;
+        nalive += cw;
+      }
+#pragma unroll
+      for (int it = 0; it < ITS; it++) {
+        const unsigned m8 = (mym >> (8 * it)) & 0xFFu;
+        if (m8) {
+          const int c = base + (int)((myrank >> (8 * it)) & 0xFFu);
+          sh_gidx[c] = (unsigned short)(warp * PER_W + it * 32 + lane);
+          sh_mask[c] = (unsigned char)m8;
+        }
+      }
+      __syncthreads();
+      // ---- phase 2: one thread per alive group, a loop over its alive states
+      for (int c = tid; c < nalive; c += FUSE_NT) {
+        const int q = p0 + sh_gidx[c];
+        const unsigned m8 = sh_mask[c];
+        const int iso = g_iso[q];
+        const int b = g_start[q], e = g_start[q + 1];
+        const double wlead = g_wavn[q], gf = g_gf[q], a0 = g_a0[q];
+        const int iown = g_iown[q];
+        const double wneg = __dmul_rn(-TB_EXPCTE, wlead);
+        // |iown - o*nearest coarse bin|: a profile with a smaller half-size covers no grid point
+        int dist = iown - fd_div(iown + (o >> 1), fd_o) * o;
+        dist = dist < 0 ? -dist : dist;
+        const bool home = rec_out && fd_div(iown, fd_tile) == tile;   // trace: each group is written by its own tile
+        sh_iown[c] = iown;
+        short ps8[FB];
+#pragma unroll
+        for (int k = 0; k < FB; k++) ps8[k] = -1;
+#pragma unroll
+        for (int k = 0; k < FB; k++) {
+          if (!((m8 >> k) & 1u)) continue;
+          const int s = s0 + k;
+          const double rT = sh_rT[k];
+          const FuseTab t = sh_tab[k * niso + iso];
+          const double ge1 = __dmul_rn(gf, tb_exp(a0 * rT));
+          double kk = 0.0;
+          bool below = (e - b == 1) && ge1 * t.facz < 0.999999 * t.thr;
+          if (!below) {
+            double a = __dmul_rn(ge1, (1 - tb_exp(wneg * rT)));
+            for (int l = b + 1; l < e; l++)                      // co-added members (extinction.c:449-462)
+              a = __dadd_rn(a, xterm[(size_t)s * X + (l - q - 1)]);
+            kk = __dmul_rn(a, t.facz);
+            below = kk < t.thr;                                  // extinction.c:467-470
+          }
+          if (below) continue;
+          if (!permol) kk = __dmul_rn(kk, t.densf);
+          const double adw = __dmul_rn(t.alphad, wlead);
+          // binsearchapprox (iomisc.c:1088-1108) on the log-spaced table, as in k_strength
+          int lo = (int)((__log2f((float)adw) * 0.30102999566f - dop_lmin) * dop_rstep);
+          lo = lo < 0 ? 0 : (lo > nDop - 1 ? nDop - 1 : lo);
+          while (lo > 0 && sh_aDop[lo] > adw) lo--;
+          while (sh_aDop[lo + 1] <= adw) lo++;
+          const int id = (fabs(sh_aDop[lo + 1] - adw) < fabs(sh_aDop[lo] - adw)) ? lo + 1 : lo;
+          const unsigned pid = (unsigned)(id * nLor + sh_ilor[k * niso + iso]);
+          const int ps = ptab[pid].psize;
+          const bool reach = dist <= ps;
+          if (reach) {
+            sh_k[k * FUSE_CAP + c] = kk;
+            sh_cell[k * FUSE_CAP + c] = (unsigned short)pid;
+            ps8[k] = (short)ps;
+          }
+          if (home) {
+            LineRec r;
+            r.k = kk; r.iown = iown; r.pid = reach ? pid : (pid | PID_NOREACH);
+            rec_out[(size_t)s * G + q] = r;
+          }
+        }
+        int4 v;
+        v.x = (unsigned short)ps8[0] | ((unsigned)(unsigned short)ps8[1] << 16);
+        v.y = (unsigned short)ps8[2] | ((unsigned)(unsigned short)ps8[3] << 16);
+        v.z = (unsigned short)ps8[4] | ((unsigned)(unsigned short)ps8[5] << 16);
+        v.w = (unsigned short)ps8[6] | ((unsigned)(unsigned short)ps8[7] << 16);
+        *reinterpret_cast<int4 *>(sh_ps + (size_t)c * FB) = v;
+      }
+      __syncthreads();
+      // ---- phase 3: the bin's window of the shared records, in fine-bin order
+      if (inb && nalive > 0) {
+        int lo = 0, hi = nalive;
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (sh_iown[mid] < lo_f) lo = mid + 1; else hi = mid;
+        }
+        for (int c = lo; c < nalive; c++) {
+          const int io = sh_iown[c];
+          if (io > hi_f) break;
+          const int d = oj - io, ad = d < 0 ? -d : d;
+          const int2 pp = *reinterpret_cast<const int2 *>(sh_ps + (size_t)c * FB + 4 * half);
+#pragma unroll
+          for (int kk = 0; kk < 4; kk++) {
+            const int w32 = kk < 2 ? pp.x : pp.y;
+            const int ps = (int)(short)((kk & 1) ? (w32 >> 16) : (w32 & 0xFFFF));
+            if (ps >= ad) {
+              const int k = 4 * half + kk;
+              const ProfEntry pe = ptab[sh_cell[k * FUSE_CAP + c]];
+              const int idx = d + ps;
+              int a = idx;
+              if (pe.nk != 1) {
+                const int qd = fd_div(idx, fd_o);
+                a = (idx - qd * o) * pe.nk + qd;
+              }
+              acc[kk] = fma(sh_k[k * FUSE_CAP + c], pdata[pe.off + a], acc[kk]);
+              cnt[kk]++;
+            }
+          }
+        }
+      }
+      // the next chunk's phase 1 writes only sh_wcnt before its first barrier: no barrier needed here
+    }
+    if (permol) {
+#pragma unroll
+      for (int kk = 0; kk < 4; kk++) {
+        const int s = s0 + 4 * half + kk;
+        if (inb && s < ns) out[((size_t)s * nrows + row) * nwn + j] = acc[kk];
+        acc[kk] = 0.0;
+      }
+    }
+  }
+  if (!permol) {
+#pragma unroll
+    for (int kk = 0; kk < 4; kk++) {
+      const int s = s0 + 4 * half + kk;
+      if (inb && s < ns) out[(size_t)s * nwn + j] = acc[kk];
+    }
+  }
+  // sample counters (integer atomics): one add per warp and state
+#pragma unroll
+  for (int kk = 0; kk < 4; kk++) {
+    unsigned v = cnt[kk];
+    for (int dlt = 16; dlt > 0; dlt >>= 1) v += __shfl_xor_sync(0xffffffffu, v, dlt);
+    const int s = s0 + 4 * half + kk;
+    if (lane == 0 && v && s < ns) atomicAdd(&nsamp[s], (unsigned long long)v);
+  }
+}
+
+static size_t fuse_shared_bytes(int niso) {
+  return (size_t)FB * FUSE_CAP * 8 + (size_t)FUSE_CAP * FB * 2 + (size_t)FB * FUSE_CAP * 2 + (size_t)FUSE_CAP * 4 +
+         (size_t)FUSE_CAP * 2 + (size_t)FUSE_CAP + 256 * 8 + FB * 8 + (size_t)FB * niso * sizeof(FuseTab) +
+         (size_t)FB * niso * 4 + 16;
+}
+
 // ------------------------------------------------------------------ host driver
 
 int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const double *Z,
@@ -1046,6 +1356,14 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   TB_TRY(c->s_kmax.ensure((size_t)chunk * nrows + 1));
   TB_TRY(c->s_nsamp.ensure(ns));
   TB_TRY(c->s_rec.ensure((size_t)chunk * G + 1));
+  const int nbatch_max = (chunk + FB - 1) / FB;
+  TB_TRY(c->s_fclass.ensure(nbatch_max)); TB_TRY(c->s_fP.ensure(nbatch_max));
+  const size_t fuse_shm = fuse_shared_bytes(niso);
+  const bool fuse_on = c->fuse_enabled && niso >= 1 && niso <= FUSE_MAXISO && G > 0 && fuse_shm <= 110 * 1024;
+  if (fuse_on && c->fuse_shm_set != (int)fuse_shm) {
+    TB_CUDA(cudaFuncSetAttribute(k_linesum_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fuse_shm));
+    c->fuse_shm_set = (int)fuse_shm;
+  }
   double *d_out = d_out_rows;
   if (!d_out) {
     TB_TRY(c->s_out.ensure((size_t)chunk * nout * nwn));
@@ -1105,6 +1423,13 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
         c->s_nsamp.p + s0, c->s_wtile.p, c->s_hasfb.p, ntiles, c->s_Z.p, c->d_iso_ratio.p, c->s_facz.p,
         c->s_rtemp.p, c->s_ral.p);
     TB_LAUNCHED(c);
+    if (banded)    // bins outside the band come back as zero
+      TB_CUDA(cudaMemsetAsync(dst, 0, (size_t)cs * nout * nwn * sizeof(double), st));
+    const int nbatch = (cs + FB - 1) / FB;
+    k_fuse_class<<<nbatch, 128, 0, st>>>(cs, niso, c->wn_i, c->own_last, c->o, fuse_on ? 1 : 0, c->s_alphad.p, c->s_ral.p,
+                                         c->s_ilor.p, c->d_aDop.p, c->nDop, c->nLor, c->d_ptab.p, c->s_fclass.p, c->s_fP.p);
+    TB_LAUNCHED(c);
+    c->last_chunk_s0 = s0; c->last_chunk_cs = cs;
     if (G > 0) {
       // lines in descending order of their state-independent factor: a small seed launch finds
       // (nearly) the maxima, after which the bulk skips both exp() of almost every line
@@ -1136,6 +1461,24 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       k_logthr<<<nblk((int64_t)cs * niso, 128), 128, 0, st>>>(cs, niso, nrows, permol, ethresh, c->d_iso_row.p,
                                                               c->s_facz.p, c->s_kmax.p, c->s_lcz.p);
       TB_LAUNCHED(c);
+      if (fuse_on && tile_hi > tile_lo) {
+        tb_timer_end(c, "strength");
+        tb_timer_begin(c, "fused");
+        LineRec *trace_rec = nullptr;
+        if (c->trace_enabled) {                 // per-line trace wanted: records of the fused states too
+          k_fuse_trace_fill<<<dim3(nblk(G, Tn), cs), Tn, 0, st>>>(G, cs, c->s_fclass.p, c->g_iown.p, c->s_rec.p);
+          trace_rec = c->s_rec.p;
+        }
+        k_linesum_fused<<<dim3(tile_hi - tile_lo, nbatch), FUSE_NT, fuse_shm, st>>>(
+            nwn, G, cs, niso, nmol, c->o, fd_o, fd_tile, nrows, permol, tile_lo, c->s_fclass.p, c->s_fP.p, c->binstart.p,
+            c->g_start.p, c->g_iso.p, c->g_iown.p, c->g_wavn.p, c->g_a0.p, c->g_gf.p, c->g_lg.p, c->s_rtemp.p,
+            c->s_facz.p, c->s_lcz.p, c->s_xterm.p, X, (float)c->dop_lmin, (float)c->dop_rstep, c->s_dens.p,
+            c->d_iso_imol.p, c->d_iso_row.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p, c->nDop, c->d_ptab.p, c->nLor,
+            ethresh, c->s_kmax.p, c->d_pdata2.p, dst, c->s_nsamp.p + s0, trace_rec);
+        TB_LAUNCHED(c);
+        tb_timer_end(c, "fused");
+        tb_timer_begin(c, "strength");
+      }
       for (int r0 = 0; r0 < (banded ? nrows : 1); r0 += STR_NR) {
         StrRanges rg;
         rg.n = 0; rg.blk0[0] = 0;
@@ -1154,7 +1497,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
           (float)c->dop_lmin, (float)c->dop_rstep, c->s_dens.p, nmol,
           c->d_iso_imol.p, c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ilor.p,
           c->d_aDop.p, c->nDop, c->d_ptab.p, c->nLor, ethresh, permol, nrows, c->s_kmax.p,
-          c->s_rec.p, c->s_lastq.p, c->s_wtile.p, c->s_hasfb.p, ntiles);
+          c->s_rec.p, c->s_lastq.p, c->s_wtile.p, c->s_hasfb.p, ntiles, c->s_fclass.p);
       }
       if (c->shard_world > 1)
         TB_REQUIRE(c->exch(c->exch_user, TB_EXCH_LASTQ, c->s_lastq.p, (int64_t)cs * niso) == 0, TB_ERR_STATE,
@@ -1167,8 +1510,6 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
     }
     k_reach<<<nblk((int64_t)cs * ntiles, 128), 128, 0, st>>>(cs, ntiles, c->o, utiles, c->s_wtile.p, c->s_hasfb.p,
                                                              c->s_fbmax.p, c->s_reach.p, c->s_reachP.p);
-    if (banded)    // bins outside the band come back as zero
-      TB_CUDA(cudaMemsetAsync(dst, 0, (size_t)cs * nout * nwn * sizeof(double), st));
     dim3 g4(tile_hi - tile_lo, cs);
     // A grid of few tiles leaves the wide-reach instance one block per (tile, deep layer): the deepest
     // layers of C1 (20 tiles) each ran 0.7 ms on 20 SMs.  There S blocks share a tile.  S depends on
@@ -1191,11 +1532,11 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
                                           nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, tile_lo, c->binstart.p,
                                           c->substart.p, c->nsub, c->nsube, c->s_rec.p, c->s_fbpid.p, c->d_ptab.p,
                                           c->s_reach.p, c->s_reachP.p, c->d_pdata2.p, dst,
-                                          c->s_nsamp.p + s0, S, c->s_part.p, c->s_tcnt.p);
+                                          c->s_nsamp.p + s0, S, c->s_part.p, c->s_tcnt.p, c->s_fclass.p);
       k_accumulate<false><<<g4, ACC_TILE, 0, st>>>(nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, tile_lo, c->binstart.p,
                                           c->substart.p, c->nsub, c->nsube, c->s_rec.p, c->s_fbpid.p, c->d_ptab.p,
                                           c->s_reach.p, c->s_reachP.p, c->d_pdata2.p, dst,
-                                          c->s_nsamp.p + s0, 1, nullptr, nullptr);
+                                          c->s_nsamp.p + s0, 1, nullptr, nullptr, c->s_fclass.p);
     }
     tb_timer_end(c, "accumulate");
     c->launches += 3;
@@ -1278,6 +1619,13 @@ extern "C" int tb_get_line_trace(tb_ctx *c, int s, int32_t *iown, int32_t *idwn,
   TB_CUDA(cudaSetDevice(c->device));
   const int64_t n = c->nlines;
   if (n == 0) return TB_OK;
+  if (!c->trace_enabled && c->G > 0) {          // the fused kernel keeps its records on chip unless asked
+    int32_t fc = 0;
+    TB_CUDA(cudaMemcpyAsync(&fc, c->s_fclass.p + s / FB, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    TB_CUDA(cudaStreamSynchronize(c->stream));
+    TB_REQUIRE(fc == 0, TB_ERR_STATE, "state %d went through the fused line sum, which writes per-line records only "
+               "when asked: call tb_set_trace(c, 1) before the batch", s);
+  }
   DevBuf<int32_t> a, b, d;
   DevBuf<int8_t> e;
   TB_TRY(a.ensure(n)); TB_TRY(b.ensure(n)); TB_TRY(d.ensure(n)); TB_TRY(e.ensure(n));
@@ -1305,5 +1653,33 @@ extern "C" int tb_get_state_ilor(tb_ctx *c, int s, int32_t *ilor) {
   TB_CUDA(cudaMemcpyAsync(ilor, c->s_ilor.p + (size_t)s * c->niso, c->niso * sizeof(int32_t), cudaMemcpyDeviceToHost,
                           c->stream));
   TB_CUDA(cudaStreamSynchronize(c->stream));
+  return TB_OK;
+}
+
+// Per-line records of the fused states (test tap; costs 16 B of HBM per (group, state) while on)
+extern "C" int tb_set_trace(tb_ctx *c, int on) {
+  c->trace_enabled = on != 0;
+  return TB_OK;
+}
+// 0: every state through k_strength + k_accumulate (the two-kernel path); 1 (default): narrow states fused
+extern "C" int tb_set_fused(tb_ctx *c, int on) {
+  c->fuse_enabled = on != 0;
+  return TB_OK;
+}
+// how many states of the last batch the fused kernel took, and the profile updates it executed
+extern "C" int tb_get_fused_stats(tb_ctx *c, int64_t *fused_states, int64_t *fused_samples) {
+  TB_REQUIRE(c->last_ns > 0, TB_ERR_STATE, "no line-sum batch has run");
+  TB_CUDA(cudaSetDevice(c->device));
+  const int cs = c->last_chunk_cs, s0 = c->last_chunk_s0, nb = (cs + FB - 1) / FB;
+  std::vector<int32_t> fc(nb > 0 ? nb : 1, 0);
+  std::vector<unsigned long long> h(cs > 0 ? cs : 1, 0);
+  if (nb > 0) TB_CUDA(cudaMemcpyAsync(fc.data(), c->s_fclass.p, nb * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+  if (cs > 0) TB_CUDA(cudaMemcpyAsync(h.data(), c->s_nsamp.p + s0, cs * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  TB_CUDA(cudaStreamSynchronize(c->stream));
+  int64_t nsf = 0, smp = 0;
+  for (int s = 0; s < cs; s++)
+    if (fc[s / FB]) { nsf++; smp += (int64_t)h[s]; }
+  if (fused_states) *fused_states = nsf;
+  if (fused_samples) *fused_samples = smp;
   return TB_OK;
 }
