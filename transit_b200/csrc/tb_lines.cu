@@ -1020,20 +1020,21 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
 //   (2) the widest profile any line of the state can take reaches at most FUSE_RMAX coarse bins,
 // both halves run in ONE kernel and the records never leave the SM.  A block owns a tile of 128 output
 // bins and FB = 8 consecutive states.  Per molecule row it walks the tile's window of groups (tile +-
-// reach, found through binstart) in chunks of FUSE_CAP candidates:
-//   phase 1  one thread per candidate: the log-domain pretest of k_strength for the 8 states (no exp),
-//            ordered compaction of the groups alive in any state (warp ballots + one block prefix);
+// the widest profile of that row near the tile, found through binstart) in chunks of up to FUSE_CAPA alive groups:
+//   phase 1  one thread per candidate, 256 at a time: the log-domain pretest of k_strength for the 8 states
+//            (no exp), ordered compaction of the groups alive in any state (warp ballots + one block prefix);
 //   phase 2  one thread per alive group, its constants in registers, a loop over its alive states:
 //            both exp(), co-added members, threshold, Doppler cell, "covers no grid point" test -- the
-//            decisions of k_strength, expression by expression -- into shared-memory records
-//            {k, cell, half-size} ordered by fine bin;
+//            decisions of k_strength, expression by expression -- into 16-byte shared-memory records
+//            {k, table address of the tile's bin 0, first and last covered bin} ordered by fine bin;
 //   phase 3  one thread per (bin, 4 states): bisection for the first record of the bin's window, then the
-//            walk of k_accumulate's narrow schedule over the shared records, four accumulators fed per visit.
+//            walk of k_accumulate's narrow schedule over the shared records: one 128-bit shared read, two
+//            comparisons and, on a hit, one table read + FMA per (record, state).
 // The sum of a bin runs over rows, chunks and records in sorted (row, fine bin) order: the same fixed
 // order, the same FMA chain and therefore the same bits as the unfused narrow path; tiles are independent,
 // so band shards stay bit-identical.  No floating-point atomics.
 #define FB 8                 // states per block (same batching as k_strength<SBS = 8>)
-#define FUSE_CAP 768         // candidate groups per chunk (3 per thread)
+#define FUSE_CAPA 512        // alive groups per chunk (two full passes of phase 2)
 #define FUSE_NT 256
 #define FUSE_MAXISO 64
 #define FUSE_RMAX 8          // widest reach, in coarse bins, of a fused state
@@ -1082,10 +1083,20 @@ __global__ void k_fuse_trace_fill(int64_t G, int ns, const int32_t *__restrict__
 struct FuseTab {           // per (state of the block, isotope), in shared memory
   double lcz, facz, thr, densf, alphad;
 };
+// What phase 2 leaves per (alive group, state) for phase 3: the strength and everything the gather needs
+// as one 128-bit shared-memory read.  The profile sample bin j of the tile takes is pdata[A + j]:
+//   idx = o*j - iown + psize = o*(j - q + m) + rho   (iown = o*q + r, psize - r = o*m + rho, 0 <= rho < o)
+//   polyphase address = off + rho*nk + (j - q + m)   =>   A = off + rho*nk + m - q + jt  (j tile-relative)
+struct __align__(16) FuseRec {
+  double k;
+  int A;
+  short jl, jh;            // tile-relative bins the profile covers (jl > jh: none)
+};
 
 __global__ void __launch_bounds__(FUSE_NT, 2)
-k_linesum_fused(int64_t nwn, int64_t G, int ns, int niso, int nmol, int o, FastDiv fd_o, FastDiv fd_tile, int nrows,
-                int permol, int tile_off, const int32_t *__restrict__ fclass, const int32_t *__restrict__ fP,
+k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol, int o, FastDiv fd_o, FastDiv fd_tile,
+                int nrows, int permol, int tile_off, double wn_i, double odwn,
+                const int32_t *__restrict__ fclass, const int32_t *__restrict__ fP,
                 const int32_t *__restrict__ binstart, const int32_t *__restrict__ g_start,
                 const int16_t *__restrict__ g_iso, const int32_t *__restrict__ g_iown,
                 const double *__restrict__ g_wavn, const double *__restrict__ g_a0,
@@ -1101,25 +1112,24 @@ k_linesum_fused(int64_t nwn, int64_t G, int ns, int niso, int nmol, int o, FastD
   if (!fclass[batch]) return;                      // k_strength + k_accumulate take this batch
   extern __shared__ __align__(16) unsigned char fsm[];
   // ---- shared-memory carve-up
-  double *sh_k = reinterpret_cast<double *>(fsm);                               // [FB][CAP]
-  short *sh_ps = reinterpret_cast<short *>(sh_k + FB * FUSE_CAP);                // [CAP][FB]  (16 B per group)
-  unsigned short *sh_cell = reinterpret_cast<unsigned short *>(sh_ps + FUSE_CAP * FB);   // [FB][CAP]
-  int *sh_iown = reinterpret_cast<int *>(sh_cell + FB * FUSE_CAP);               // [CAP]
-  unsigned short *sh_gidx = reinterpret_cast<unsigned short *>(sh_iown + FUSE_CAP);      // [CAP]
-  unsigned char *sh_mask = reinterpret_cast<unsigned char *>(sh_gidx + FUSE_CAP);        // [CAP]
-  double *sh_aDop = reinterpret_cast<double *>(sh_mask + FUSE_CAP);              // [256]
+  FuseRec *sh_rec = reinterpret_cast<FuseRec *>(fsm);                            // [FB][CAPA]
+  int *sh_iown = reinterpret_cast<int *>(sh_rec + FB * FUSE_CAPA);               // [CAPA]
+  int *sh_gidx = sh_iown + FUSE_CAPA;                                            // [CAPA]
+  double *sh_aDop = reinterpret_cast<double *>(sh_gidx + FUSE_CAPA);             // [256]
   double *sh_rT = sh_aDop + 256;                                                 // [FB]
   FuseTab *sh_tab = reinterpret_cast<FuseTab *>(sh_rT + FB);                     // [FB][niso]
   int *sh_ilor = reinterpret_cast<int *>(sh_tab + FB * niso);                    // [FB][niso]
-  __shared__ int sh_wcnt[FUSE_NT / 32];
+  unsigned char *sh_mask = reinterpret_cast<unsigned char *>(sh_ilor + FB * niso);   // [CAPA]
+  __shared__ int sh_wcnt[2][FUSE_NT / 32];
+  __shared__ int sh_Prow[16];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int s0 = batch * FB;
   const int tile = blockIdx.x + tile_off;
   const int64_t jt = (int64_t)tile * ACC_TILE;
-  const int P = fP[batch];
-  const int R = P / o + 1;
+  const int Pb = fP[batch];
   for (int i = tid; i <= nDop; i += FUSE_NT) sh_aDop[i] = aDop[i];               // [nDop] = +inf sentinel
   if (tid < FB) sh_rT[tid] = rtemp[s0 + tid < ns ? s0 + tid : ns - 1];
+  if (tid < 16) sh_Prow[tid] = 0;
   for (int i = tid; i < FB * niso; i += FUSE_NT) {
     const int k = i / niso, iso = i % niso, s = s0 + k < ns ? s0 + k : ns - 1;
     const int si = s * niso + iso;
@@ -1131,32 +1141,50 @@ k_linesum_fused(int64_t nwn, int64_t G, int ns, int niso, int nmol, int o, FastD
     sh_tab[i] = t;
     sh_ilor[i] = ilor[si];
   }
+  __syncthreads();
+  // ---- the widest profile a line of each molecule row can take in THIS tile: nothing that reaches the tile
+  // has its centre above fine bin o*(jt+127) + Pb, the Doppler cell grows with the wavenumber and the half-size
+  // with the cell, so the cell of that wavenumber bounds every line of (state, isotope) near the tile
+  {
+    int64_t ftop = (int64_t)o * (jt + ACC_TILE - 1) + Pb + 1;
+    if (ftop > onwn - 1) ftop = onwn - 1;
+    const double wtop = tb_fine_wn(wn_i, odwn, ftop);
+    for (int i = tid; i < FB * niso; i += FUSE_NT) {
+      const int k = i / niso, iso = i % niso;
+      if (s0 + k >= ns) continue;
+      const int id = tb_binsearchapprox(sh_aDop, __dmul_rn(sh_tab[i].alphad, wtop), 0, nDop);
+      const int row = nrows <= 16 ? iso_row[iso] : 0;
+      atomicMax(&sh_Prow[row], ptab[id * nLor + sh_ilor[i]].psize);
+    }
+  }
   // ---- this thread's output bin and its four states
-  const int64_t j = jt + (tid & (ACC_TILE - 1));
+  const int jr = tid & (ACC_TILE - 1);
+  const int64_t j = jt + jr;
   const int half = tid >> 7;                       // states 4*half .. 4*half+3
   const bool inb = j < nwn;
   const int oj = (int)(o * (inb ? j : nwn - 1));
-  const int lo_f = oj - P, hi_f = oj + P;
   double acc[4] = {0.0, 0.0, 0.0, 0.0};
   unsigned cnt[4] = {0u, 0u, 0u, 0u};
-  const int64_t jlo = jt - R < 0 ? 0 : jt - R;
-  const int64_t jhi = jt + ACC_TILE + R > nwn ? nwn : jt + ACC_TILE + R;
   const unsigned nsmask = ns - s0 >= FB ? 0xFFu : ((1u << (ns - s0)) - 1u);      // states that exist
+  int buf = 0;
   __syncthreads();
   for (int row = 0; row < nrows; row++) {
+    const int P = nrows <= 16 ? sh_Prow[row] : Pb;   // more than 16 line-list molecules: the batch-wide bound
+    const int R = P / o + 1;
+    const int64_t jlo = jt - R < 0 ? 0 : jt - R;
+    const int64_t jhi = jt + ACC_TILE + R > nwn ? nwn : jt + ACC_TILE + R;
     const int pa = binstart[(size_t)row * nwn + jlo], pb = binstart[(size_t)row * nwn + jhi];
-    for (int p0 = pa; p0 < pb; p0 += FUSE_CAP) {
-      const int nc = pb - p0 < FUSE_CAP ? pb - p0 : FUSE_CAP;
-      // ---- phase 1: pretest + ordered compaction (a warp owns FUSE_CAP/8 consecutive candidates)
-      constexpr int PER_W = FUSE_CAP / (FUSE_NT / 32), ITS = PER_W / 32;
-      unsigned mym = 0, myrank = 0;
-      int wcount = 0;
-#pragma unroll
-      for (int it = 0; it < ITS; it++) {
-        const int i = warp * PER_W + it * 32 + lane;
+    const int lo_f = oj - P, hi_f = oj + P;
+    int p = pa;
+    while (p < pb) {
+      // ---- phase 1: candidates 256 at a time through the log-domain pretest, the groups alive in any state
+      // appended IN ORDER to the chunk's list until it is (nearly) full
+      const int chunk0 = p;
+      int nalive = 0;
+      while (p < pb && nalive <= FUSE_CAPA - FUSE_NT) {
+        const int q = p + tid;
         unsigned m8 = 0;
-        if (i < nc) {
-          const int q = p0 + i;
+        if (q < pb) {
           const double a0 = g_a0[q], lg = g_lg[q];
           const FuseTab *tb = sh_tab + g_iso[q];
 #pragma unroll
@@ -1165,91 +1193,92 @@ k_linesum_fused(int64_t nwn, int64_t G, int ns, int niso, int nmol, int o, FastD
           m8 &= nsmask;
         }
         const unsigned ball = __ballot_sync(0xffffffffu, m8 != 0);
-        mym |= m8 << (8 * it);
-        myrank |= (unsigned)(wcount + __popc(ball & ((1u << lane) - 1))) << (8 * it);   // < 96: fits a byte
-        wcount += __popc(ball);
-      }
-      if (lane == 0) sh_wcnt[warp] = wcount;
-      __syncthreads();                              // also: phase 3 of the previous chunk is over
-      int base = 0, nalive = 0;
+        if (lane == 0) sh_wcnt[buf][warp] = __popc(ball);
+        __syncthreads();
+        int base = nalive, tot = 0;
 #pragma unroll
-      for (int w = 0; w < FUSE_NT / 32; w++) {
-        const int cw = sh_wcnt[w];
-        if (w < warp) base += cw;
-        nalive += cw;
-      }
-#pragma unroll
-      for (int it = 0; it < ITS; it++) {
-        const unsigned m8 = (mym >> (8 * it)) & 0xFFu;
+        for (int w = 0; w < FUSE_NT / 32; w++) {
+          const int cw = sh_wcnt[buf][w];
+          if (w < warp) base += cw;
+          tot += cw;
+        }
         if (m8) {
-          const int c = base + (int)((myrank >> (8 * it)) & 0xFFu);
-          sh_gidx[c] = (unsigned short)(warp * PER_W + it * 32 + lane);
+          const int c = base + __popc(ball & ((1u << lane) - 1));
+          sh_gidx[c] = q - chunk0;
           sh_mask[c] = (unsigned char)m8;
         }
+        nalive += tot;
+        p += FUSE_NT;
+        buf ^= 1;
       }
       __syncthreads();
       // ---- phase 2: one thread per alive group, a loop over its alive states
       for (int c = tid; c < nalive; c += FUSE_NT) {
-        const int q = p0 + sh_gidx[c];
+        const int q = chunk0 + sh_gidx[c];
         const unsigned m8 = sh_mask[c];
         const int iso = g_iso[q];
         const int b = g_start[q], e = g_start[q + 1];
         const double wlead = g_wavn[q], gf = g_gf[q], a0 = g_a0[q];
         const int iown = g_iown[q];
         const double wneg = __dmul_rn(-TB_EXPCTE, wlead);
-        // |iown - o*nearest coarse bin|: a profile with a smaller half-size covers no grid point
-        int dist = iown - fd_div(iown + (o >> 1), fd_o) * o;
-        dist = dist < 0 ? -dist : dist;
+        const int qi = fd_div(iown, fd_o), ri = iown - qi * o;       // iown = o*qi + ri
         const bool home = rec_out && fd_div(iown, fd_tile) == tile;   // trace: each group is written by its own tile
         sh_iown[c] = iown;
-        short ps8[FB];
-#pragma unroll
-        for (int k = 0; k < FB; k++) ps8[k] = -1;
 #pragma unroll
         for (int k = 0; k < FB; k++) {
-          if (!((m8 >> k) & 1u)) continue;
-          const int s = s0 + k;
-          const double rT = sh_rT[k];
-          const FuseTab t = sh_tab[k * niso + iso];
-          const double ge1 = __dmul_rn(gf, tb_exp(a0 * rT));
-          double kk = 0.0;
-          bool below = (e - b == 1) && ge1 * t.facz < 0.999999 * t.thr;
-          if (!below) {
-            double a = __dmul_rn(ge1, (1 - tb_exp(wneg * rT)));
-            for (int l = b + 1; l < e; l++)                      // co-added members (extinction.c:449-462)
-              a = __dadd_rn(a, xterm[(size_t)s * X + (l - q - 1)]);
-            kk = __dmul_rn(a, t.facz);
-            below = kk < t.thr;                                  // extinction.c:467-470
+          FuseRec rr;
+          rr.k = 0.0; rr.A = 0; rr.jl = 1; rr.jh = 0;                // dead unless proven otherwise
+          if ((m8 >> k) & 1u) {
+            const int s = s0 + k;
+            const double rT = sh_rT[k];
+            const FuseTab t = sh_tab[k * niso + iso];
+            const double ge1 = __dmul_rn(gf, tb_exp(a0 * rT));
+            double kk = 0.0;
+            bool below = (e - b == 1) && ge1 * t.facz < 0.999999 * t.thr;
+            if (!below) {
+              double a = __dmul_rn(ge1, (1 - tb_exp(wneg * rT)));
+              for (int l = b + 1; l < e; l++)                      // co-added members (extinction.c:449-462)
+                a = __dadd_rn(a, xterm[(size_t)s * X + (l - q - 1)]);
+              kk = __dmul_rn(a, t.facz);
+              below = kk < t.thr;                                  // extinction.c:467-470
+            }
+            if (!below) {
+              if (!permol) kk = __dmul_rn(kk, t.densf);
+              const double adw = __dmul_rn(t.alphad, wlead);
+              // binsearchapprox (iomisc.c:1088-1108) on the log-spaced table, as in k_strength
+              int lo = (int)((__log2f((float)adw) * 0.30102999566f - dop_lmin) * dop_rstep);
+              lo = lo < 0 ? 0 : (lo > nDop - 1 ? nDop - 1 : lo);
+              while (lo > 0 && sh_aDop[lo] > adw) lo--;
+              while (sh_aDop[lo + 1] <= adw) lo++;
+              const int id = (fabs(sh_aDop[lo + 1] - adw) < fabs(sh_aDop[lo] - adw)) ? lo + 1 : lo;
+              const unsigned pid = (unsigned)(id * nLor + sh_ilor[k * niso + iso]);
+              const ProfEntry pe = ptab[pid];
+              const int ps = pe.psize;
+              // bins with |o*j - iown| <= ps: ceil((iown-ps)/o) .. floor((iown+ps)/o), on the grid
+              const int lof = iown - ps;
+              int jl = lof <= 0 ? 0 : fd_div(lof + o - 1, fd_o);
+              int jh = fd_div(iown + ps, fd_o);
+              if (jh > (int)(nwn - 1)) jh = (int)(nwn - 1);
+              const bool reach = jl <= jh;                          // else: covers no grid point (nothing to add)
+              if (reach) {
+                // ps - ri = o*m + rho with 0 <= rho < o (ps - ri > -o)
+                const int t0 = ps - ri + o;
+                const int m1 = fd_div(t0, fd_o), rho = t0 - m1 * o;
+                jl -= (int)jt; jh -= (int)jt;
+                rr.k = kk;
+                rr.A = pe.off + rho * pe.nk + (m1 - 1) - qi + (int)jt;
+                rr.jl = (short)(jl < 0 ? 0 : jl);
+                rr.jh = (short)(jh > ACC_TILE - 1 ? ACC_TILE - 1 : jh);
+              }
+              if (home) {
+                LineRec r;
+                r.k = kk; r.iown = iown; r.pid = reach ? pid : (pid | PID_NOREACH);
+                rec_out[(size_t)s * G + q] = r;
+              }
+            }
           }
-          if (below) continue;
-          if (!permol) kk = __dmul_rn(kk, t.densf);
-          const double adw = __dmul_rn(t.alphad, wlead);
-          // binsearchapprox (iomisc.c:1088-1108) on the log-spaced table, as in k_strength
-          int lo = (int)((__log2f((float)adw) * 0.30102999566f - dop_lmin) * dop_rstep);
-          lo = lo < 0 ? 0 : (lo > nDop - 1 ? nDop - 1 : lo);
-          while (lo > 0 && sh_aDop[lo] > adw) lo--;
-          while (sh_aDop[lo + 1] <= adw) lo++;
-          const int id = (fabs(sh_aDop[lo + 1] - adw) < fabs(sh_aDop[lo] - adw)) ? lo + 1 : lo;
-          const unsigned pid = (unsigned)(id * nLor + sh_ilor[k * niso + iso]);
-          const int ps = ptab[pid].psize;
-          const bool reach = dist <= ps;
-          if (reach) {
-            sh_k[k * FUSE_CAP + c] = kk;
-            sh_cell[k * FUSE_CAP + c] = (unsigned short)pid;
-            ps8[k] = (short)ps;
-          }
-          if (home) {
-            LineRec r;
-            r.k = kk; r.iown = iown; r.pid = reach ? pid : (pid | PID_NOREACH);
-            rec_out[(size_t)s * G + q] = r;
-          }
+          sh_rec[k * FUSE_CAPA + c] = rr;
         }
-        int4 v;
-        v.x = (unsigned short)ps8[0] | ((unsigned)(unsigned short)ps8[1] << 16);
-        v.y = (unsigned short)ps8[2] | ((unsigned)(unsigned short)ps8[3] << 16);
-        v.z = (unsigned short)ps8[4] | ((unsigned)(unsigned short)ps8[5] << 16);
-        v.w = (unsigned short)ps8[6] | ((unsigned)(unsigned short)ps8[7] << 16);
-        *reinterpret_cast<int4 *>(sh_ps + (size_t)c * FB) = v;
       }
       __syncthreads();
       // ---- phase 3: the bin's window of the shared records, in fine-bin order
@@ -1259,31 +1288,20 @@ k_linesum_fused(int64_t nwn, int64_t G, int ns, int niso, int nmol, int o, FastD
           const int mid = (lo + hi) >> 1;
           if (sh_iown[mid] < lo_f) lo = mid + 1; else hi = mid;
         }
-        for (int c = lo; c < nalive; c++) {
-          const int io = sh_iown[c];
-          if (io > hi_f) break;
-          const int d = oj - io, ad = d < 0 ? -d : d;
-          const int2 pp = *reinterpret_cast<const int2 *>(sh_ps + (size_t)c * FB + 4 * half);
+        const FuseRec *rp = sh_rec + (size_t)(4 * half) * FUSE_CAPA;
+        for (int c = lo; c < nalive && sh_iown[c] <= hi_f; c++) {
 #pragma unroll
           for (int kk = 0; kk < 4; kk++) {
-            const int w32 = kk < 2 ? pp.x : pp.y;
-            const int ps = (int)(short)((kk & 1) ? (w32 >> 16) : (w32 & 0xFFFF));
-            if (ps >= ad) {
-              const int k = 4 * half + kk;
-              const ProfEntry pe = ptab[sh_cell[k * FUSE_CAP + c]];
-              const int idx = d + ps;
-              int a = idx;
-              if (pe.nk != 1) {
-                const int qd = fd_div(idx, fd_o);
-                a = (idx - qd * o) * pe.nk + qd;
-              }
-              acc[kk] = fma(sh_k[k * FUSE_CAP + c], pdata[pe.off + a], acc[kk]);
+            const int4 v = *reinterpret_cast<const int4 *>(rp + kk * FUSE_CAPA + c);
+            const int jl = (int)(short)(v.w & 0xFFFF), jh = v.w >> 16;
+            if (jr >= jl && jr <= jh) {
+              acc[kk] = fma(__hiloint2double(v.y, v.x), pdata[v.z + jr], acc[kk]);
               cnt[kk]++;
             }
           }
         }
       }
-      // the next chunk's phase 1 writes only sh_wcnt before its first barrier: no barrier needed here
+      // the next chunk's phase 1 passes at least one barrier before its phase 2 rewrites the records
     }
     if (permol) {
 #pragma unroll
@@ -1312,9 +1330,8 @@ k_linesum_fused(int64_t nwn, int64_t G, int ns, int niso, int nmol, int o, FastD
 }
 
 static size_t fuse_shared_bytes(int niso) {
-  return (size_t)FB * FUSE_CAP * 8 + (size_t)FUSE_CAP * FB * 2 + (size_t)FB * FUSE_CAP * 2 + (size_t)FUSE_CAP * 4 +
-         (size_t)FUSE_CAP * 2 + (size_t)FUSE_CAP + 256 * 8 + FB * 8 + (size_t)FB * niso * sizeof(FuseTab) +
-         (size_t)FB * niso * 4 + 16;
+  return (size_t)FB * FUSE_CAPA * sizeof(FuseRec) + (size_t)FUSE_CAPA * 4 * 2 + 256 * 8 + FB * 8 +
+         (size_t)FB * niso * sizeof(FuseTab) + (size_t)FB * niso * 4 + FUSE_CAPA + 16;
 }
 
 // ------------------------------------------------------------------ host driver
@@ -1470,7 +1487,8 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
           trace_rec = c->s_rec.p;
         }
         k_linesum_fused<<<dim3(tile_hi - tile_lo, nbatch), FUSE_NT, fuse_shm, st>>>(
-            nwn, G, cs, niso, nmol, c->o, fd_o, fd_tile, nrows, permol, tile_lo, c->s_fclass.p, c->s_fP.p, c->binstart.p,
+            nwn, c->onwn, G, cs, niso, nmol, c->o, fd_o, fd_tile, nrows, permol, tile_lo, c->wn_i, c->odwn,
+            c->s_fclass.p, c->s_fP.p, c->binstart.p,
             c->g_start.p, c->g_iso.p, c->g_iown.p, c->g_wavn.p, c->g_a0.p, c->g_gf.p, c->g_lg.p, c->s_rtemp.p,
             c->s_facz.p, c->s_lcz.p, c->s_xterm.p, X, (float)c->dop_lmin, (float)c->dop_rstep, c->s_dens.p,
             c->d_iso_imol.p, c->d_iso_row.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p, c->nDop, c->d_ptab.p, c->nLor,
