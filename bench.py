@@ -440,7 +440,7 @@ def run_ours(args):
         ev1.record(stream)
         torch.cuda.synchronize()
         ms_steps.append(ev0.elapsed_time(ev1))
-        for nm in ("kmax", "strength", "accumulate", "molext", "cia", "tau", "modulation"):
+        for nm in ("kmax", "strength", "fused", "accumulate", "molext", "cia", "tau", "modulation"):
             try:
                 k_ms.setdefault(nm, []).append(ctx.kernel_ms(nm))
             except api.TransitError:

@@ -121,6 +121,10 @@ int  tb_set_cloud(tb_ctx *c, int flag, double cloudext, double cloudtop, double 
  * rays h[nh]*hfct (impact parameters, top first; NULL = reversed radii as makeipsample
  * with raddelt=-1, makesample.c:564-573).                                             */
 int  tb_tau(tb_ctx *c, int geometry, double toomuch, const double *h, int nh, double hfct);
+/* eclipse geometry: 1 (default) = the O(layers)-per-wavenumber streaming kernel (every ray's Simpson pairs end
+ * at the top layer, so ray ri adds one pair to the sum of the rays above it); 0 = the general kernel that
+ * integrates every ray on its own.  Same terms, pairs associated top down instead of bottom up.            */
+int  tb_set_tau_streaming(tb_ctx *c, int on);
 /* modulationperwn's dispatch (slantpath.c:477-503, cfg key `modlevel`): 1 = modulation1 (default),
  * -1 = modulationm1 (slantpath.c:446-473, opaque disc at tau = toomuch); anything else is refused
  * with the reference's message.                                                          */

@@ -509,4 +509,13 @@ def test_high_resolution_eclipse_from_grid_vs_oracle():
     intens0, flux0 = O.intensity_flux(pr, t0, last0)
     assert relerr(tr.ctx.get_intensity(), intens0) < SPEC_RTOL
     assert relerr(out, flux0) < SPEC_RTOL
+    assert np.array_equal(tg == 0, t0 == 0) and relerr(tg[t0 != 0], t0[t0 != 0]) < 1e-9
+    # the O(layers) streaming kernel (default) against the general kernel that integrates every ray on its own:
+    # same last[], same zero tail, optical depths equal to the association of the pair sums
+    tr.ctx.set_tau_streaming(False)
+    out2 = tr.do_transit()
+    tg2, lastg2 = tr.ctx.get_tau()
+    tr.ctx.set_tau_streaming(True)
+    assert np.array_equal(lastg2, lastg) and np.array_equal(tg2 == 0, tg == 0)
+    assert relerr(tg[tg2 != 0], tg2[tg2 != 0]) < 1e-12 and relerr(out, out2) < 1e-12
     tr.free_memory()

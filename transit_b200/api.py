@@ -65,6 +65,7 @@ ABI = {
     "tb_set_cloud": (C.c_int, [C.c_void_p, C.c_int] + [C.c_double] * 8 + [f64p, f64p]),
     "tb_tau": (C.c_int, [C.c_void_p, C.c_int, C.c_double, f64p, C.c_int, C.c_double]),
     "tb_set_modlevel": (C.c_int, [C.c_void_p, C.c_int]),
+    "tb_set_tau_streaming": (C.c_int, [C.c_void_p, C.c_int]),
     "tb_modulation": (C.c_int, [C.c_void_p, C.c_double, C.c_int, f64p]),
     "tb_intensity_flux": (C.c_int, [C.c_void_p, f64p, C.c_int, f64p]),
     "tb_spectrum": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, f64p, C.c_int, f64p]),
@@ -313,6 +314,9 @@ class Context:
         hp = None if h is None else _c64(h)
         self._ck(self.lib.tb_tau(self.h, geometry, toomuch, _p(hp), 0 if h is None else len(hp), hfct), "tb_tau")
         self.nh = self.nrad if h is None else len(hp)
+
+    def set_tau_streaming(self, on=True):
+        self._ck(self.lib.tb_set_tau_streaming(self.h, int(bool(on))), "tb_set_tau_streaming")
 
     def set_modlevel(self, level):
         self._ck(self.lib.tb_set_modlevel(self.h, int(level)), "tb_set_modlevel")

@@ -240,6 +240,8 @@ struct tb_ctx {
 
   // ---- ray geometry scratch
   DevBuf<double> r_coef, r_par, r_h, r_s, r_ip, r_ang, r_rcp;
+  DevBuf<uint8_t> r_ecl;               // per-ray constants of the streaming eclipse kernel (tb_radiative.cu)
+  bool tau_stream_ecl = true;          // eclipse tau in O(layers) per wavenumber (false: the general kernel)
   DevBuf<int32_t> r_meta;
 
   // ---- opacity grid (a6-a8)

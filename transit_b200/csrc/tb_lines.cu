@@ -1033,7 +1033,10 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
 // The sum of a bin runs over rows, chunks and records in sorted (row, fine bin) order: the same fixed
 // order, the same FMA chain and therefore the same bits as the unfused narrow path; tiles are independent,
 // so band shards stay bit-identical.  No floating-point atomics.
-#define FB 8                 // states per block (same batching as k_strength<SBS = 8>)
+#define FB 8                 // states per classification batch (same batching as k_strength<SBS = 8>)
+#define FBK 4                // states per block of the fused kernel
+#define FPT (FBK / 2)        // states per thread in phase 3 (two threads per bin)
+#define FUSE_BLOCKS 4        // resident blocks per SM the kernel is compiled for (64 registers)
 #define FUSE_CAPA 512        // alive groups per chunk (two full passes of phase 2)
 #define FUSE_NT 256
 #define FUSE_MAXISO 64
@@ -1093,7 +1096,7 @@ struct __align__(16) FuseRec {
   short jl, jh;            // tile-relative bins the profile covers (jl > jh: none)
 };
 
-__global__ void __launch_bounds__(FUSE_NT, 2)
+__global__ void __launch_bounds__(FUSE_NT, FUSE_BLOCKS)
 k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol, int o, FastDiv fd_o, FastDiv fd_tile,
                 int nrows, int permol, int tile_off, double wn_i, double odwn,
                 const int32_t *__restrict__ fclass, const int32_t *__restrict__ fP,
@@ -1108,29 +1111,29 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
                 const double *__restrict__ aDop, int nDop, const ProfEntry *__restrict__ ptab, int nLor,
                 double ethresh, const double *__restrict__ kmax, const double *__restrict__ pdata,
                 double *__restrict__ out, unsigned long long *__restrict__ nsamp, LineRec *__restrict__ rec_out) {
-  const int batch = blockIdx.y;
+  const int batch = blockIdx.y / (FB / FBK);       // classification is per batch of FB states (as k_strength)
   if (!fclass[batch]) return;                      // k_strength + k_accumulate take this batch
   extern __shared__ __align__(16) unsigned char fsm[];
   // ---- shared-memory carve-up
-  FuseRec *sh_rec = reinterpret_cast<FuseRec *>(fsm);                            // [FB][CAPA]
-  int *sh_iown = reinterpret_cast<int *>(sh_rec + FB * FUSE_CAPA);               // [CAPA]
+  FuseRec *sh_rec = reinterpret_cast<FuseRec *>(fsm);                            // [FBK][CAPA]
+  int *sh_iown = reinterpret_cast<int *>(sh_rec + FBK * FUSE_CAPA);               // [CAPA]
   int *sh_gidx = sh_iown + FUSE_CAPA;                                            // [CAPA]
   double *sh_aDop = reinterpret_cast<double *>(sh_gidx + FUSE_CAPA);             // [256]
-  double *sh_rT = sh_aDop + 256;                                                 // [FB]
-  FuseTab *sh_tab = reinterpret_cast<FuseTab *>(sh_rT + FB);                     // [FB][niso]
-  int *sh_ilor = reinterpret_cast<int *>(sh_tab + FB * niso);                    // [FB][niso]
-  unsigned char *sh_mask = reinterpret_cast<unsigned char *>(sh_ilor + FB * niso);   // [CAPA]
+  double *sh_rT = sh_aDop + 256;                                                 // [FBK]
+  FuseTab *sh_tab = reinterpret_cast<FuseTab *>(sh_rT + FBK);                    // [FBK][niso]
+  int *sh_ilor = reinterpret_cast<int *>(sh_tab + FBK * niso);                   // [FBK][niso]
+  unsigned char *sh_mask = reinterpret_cast<unsigned char *>(sh_ilor + FBK * niso);  // [CAPA]
   __shared__ int sh_wcnt[2][FUSE_NT / 32];
   __shared__ int sh_Prow[16];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int s0 = batch * FB;
+  const int s0 = blockIdx.y * FBK;
   const int tile = blockIdx.x + tile_off;
   const int64_t jt = (int64_t)tile * ACC_TILE;
   const int Pb = fP[batch];
   for (int i = tid; i <= nDop; i += FUSE_NT) sh_aDop[i] = aDop[i];               // [nDop] = +inf sentinel
-  if (tid < FB) sh_rT[tid] = rtemp[s0 + tid < ns ? s0 + tid : ns - 1];
+  if (tid < FBK) sh_rT[tid] = rtemp[s0 + tid < ns ? s0 + tid : ns - 1];
   if (tid < 16) sh_Prow[tid] = 0;
-  for (int i = tid; i < FB * niso; i += FUSE_NT) {
+  for (int i = tid; i < FBK * niso; i += FUSE_NT) {
     const int k = i / niso, iso = i % niso, s = s0 + k < ns ? s0 + k : ns - 1;
     const int si = s * niso + iso;
     FuseTab t;
@@ -1149,7 +1152,7 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
     int64_t ftop = (int64_t)o * (jt + ACC_TILE - 1) + Pb + 1;
     if (ftop > onwn - 1) ftop = onwn - 1;
     const double wtop = tb_fine_wn(wn_i, odwn, ftop);
-    for (int i = tid; i < FB * niso; i += FUSE_NT) {
+    for (int i = tid; i < FBK * niso; i += FUSE_NT) {
       const int k = i / niso, iso = i % niso;
       if (s0 + k >= ns) continue;
       const int id = tb_binsearchapprox(sh_aDop, __dmul_rn(sh_tab[i].alphad, wtop), 0, nDop);
@@ -1160,12 +1163,14 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
   // ---- this thread's output bin and its four states
   const int jr = tid & (ACC_TILE - 1);
   const int64_t j = jt + jr;
-  const int half = tid >> 7;                       // states 4*half .. 4*half+3
+  const int half = tid >> 7;                       // states FPT*half .. FPT*half+FPT-1
   const bool inb = j < nwn;
   const int oj = (int)(o * (inb ? j : nwn - 1));
-  double acc[4] = {0.0, 0.0, 0.0, 0.0};
-  unsigned cnt[4] = {0u, 0u, 0u, 0u};
-  const unsigned nsmask = ns - s0 >= FB ? 0xFFu : ((1u << (ns - s0)) - 1u);      // states that exist
+  double acc[FPT];
+  unsigned cnt[FPT];
+#pragma unroll
+  for (int kk = 0; kk < FPT; kk++) { acc[kk] = 0.0; cnt[kk] = 0u; }
+  const unsigned nsmask = ns - s0 >= FBK ? (1u << FBK) - 1u : (ns - s0 > 0 ? (1u << (ns - s0)) - 1u : 0u);      // states that exist
   int buf = 0;
   __syncthreads();
   for (int row = 0; row < nrows; row++) {
@@ -1188,7 +1193,7 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
           const double a0 = g_a0[q], lg = g_lg[q];
           const FuseTab *tb = sh_tab + g_iso[q];
 #pragma unroll
-          for (int k = 0; k < FB; k++)
+          for (int k = 0; k < FBK; k++)
             if (!(fma(a0, sh_rT[k], lg + tb[k * niso].lcz) < -1e-9)) m8 |= 1u << k;
           m8 &= nsmask;
         }
@@ -1221,11 +1226,11 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
         const double wlead = g_wavn[q], gf = g_gf[q], a0 = g_a0[q];
         const int iown = g_iown[q];
         const double wneg = __dmul_rn(-TB_EXPCTE, wlead);
-        const int qi = fd_div(iown, fd_o), ri = iown - qi * o;       // iown = o*qi + ri
         const bool home = rec_out && fd_div(iown, fd_tile) == tile;   // trace: each group is written by its own tile
         sh_iown[c] = iown;
-#pragma unroll
-        for (int k = 0; k < FB; k++) {
+        int lo = -1;                                               // Doppler cell of the previous state: the search resumes there
+#pragma unroll 1
+        for (int k = 0; k < FBK; k++) {
           FuseRec rr;
           rr.k = 0.0; rr.A = 0; rr.jl = 1; rr.jh = 0;                // dead unless proven otherwise
           if ((m8 >> k) & 1u) {
@@ -1246,8 +1251,10 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
               if (!permol) kk = __dmul_rn(kk, t.densf);
               const double adw = __dmul_rn(t.alphad, wlead);
               // binsearchapprox (iomisc.c:1088-1108) on the log-spaced table, as in k_strength
-              int lo = (int)((__log2f((float)adw) * 0.30102999566f - dop_lmin) * dop_rstep);
-              lo = lo < 0 ? 0 : (lo > nDop - 1 ? nDop - 1 : lo);
+              if (lo < 0) {
+                lo = (int)((__log2f((float)adw) * 0.30102999566f - dop_lmin) * dop_rstep);
+                lo = lo < 0 ? 0 : (lo > nDop - 1 ? nDop - 1 : lo);
+              }
               while (lo > 0 && sh_aDop[lo] > adw) lo--;
               while (sh_aDop[lo + 1] <= adw) lo++;
               const int id = (fabs(sh_aDop[lo + 1] - adw) < fabs(sh_aDop[lo] - adw)) ? lo + 1 : lo;
@@ -1261,12 +1268,13 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
               if (jh > (int)(nwn - 1)) jh = (int)(nwn - 1);
               const bool reach = jl <= jh;                          // else: covers no grid point (nothing to add)
               if (reach) {
-                // ps - ri = o*m + rho with 0 <= rho < o (ps - ri > -o)
-                const int t0 = ps - ri + o;
-                const int m1 = fd_div(t0, fd_o), rho = t0 - m1 * o;
+                // sample index of bin jl: i0 = o*jl - iown + ps, in [0, o) unless jl was clamped to the grid start;
+                // bin j then reads sample i0 + o*(j - jl): polyphase address off + (i0 % o)*nk + i0/o + (j - jl)
+                int i0 = o * jl - lof, m = 0;
+                if (i0 >= o) { m = fd_div(i0, fd_o); i0 -= m * o; }
                 jl -= (int)jt; jh -= (int)jt;
                 rr.k = kk;
-                rr.A = pe.off + rho * pe.nk + (m1 - 1) - qi + (int)jt;
+                rr.A = pe.off + i0 * pe.nk + m - jl;                // + tile-relative bin
                 rr.jl = (short)(jl < 0 ? 0 : jl);
                 rr.jh = (short)(jh > ACC_TILE - 1 ? ACC_TILE - 1 : jh);
               }
@@ -1288,10 +1296,10 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
           const int mid = (lo + hi) >> 1;
           if (sh_iown[mid] < lo_f) lo = mid + 1; else hi = mid;
         }
-        const FuseRec *rp = sh_rec + (size_t)(4 * half) * FUSE_CAPA;
+        const FuseRec *rp = sh_rec + (size_t)(FPT * half) * FUSE_CAPA;
         for (int c = lo; c < nalive && sh_iown[c] <= hi_f; c++) {
 #pragma unroll
-          for (int kk = 0; kk < 4; kk++) {
+          for (int kk = 0; kk < FPT; kk++) {
             const int4 v = *reinterpret_cast<const int4 *>(rp + kk * FUSE_CAPA + c);
             const int jl = (int)(short)(v.w & 0xFFFF), jh = v.w >> 16;
             if (jr >= jl && jr <= jh) {
@@ -1305,8 +1313,8 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
     }
     if (permol) {
 #pragma unroll
-      for (int kk = 0; kk < 4; kk++) {
-        const int s = s0 + 4 * half + kk;
+      for (int kk = 0; kk < FPT; kk++) {
+        const int s = s0 + FPT * half + kk;
         if (inb && s < ns) out[((size_t)s * nrows + row) * nwn + j] = acc[kk];
         acc[kk] = 0.0;
       }
@@ -1314,24 +1322,24 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
   }
   if (!permol) {
 #pragma unroll
-    for (int kk = 0; kk < 4; kk++) {
-      const int s = s0 + 4 * half + kk;
+    for (int kk = 0; kk < FPT; kk++) {
+      const int s = s0 + FPT * half + kk;
       if (inb && s < ns) out[(size_t)s * nwn + j] = acc[kk];
     }
   }
   // sample counters (integer atomics): one add per warp and state
 #pragma unroll
-  for (int kk = 0; kk < 4; kk++) {
+  for (int kk = 0; kk < FPT; kk++) {
     unsigned v = cnt[kk];
     for (int dlt = 16; dlt > 0; dlt >>= 1) v += __shfl_xor_sync(0xffffffffu, v, dlt);
-    const int s = s0 + 4 * half + kk;
+    const int s = s0 + FPT * half + kk;
     if (lane == 0 && v && s < ns) atomicAdd(&nsamp[s], (unsigned long long)v);
   }
 }
 
 static size_t fuse_shared_bytes(int niso) {
-  return (size_t)FB * FUSE_CAPA * sizeof(FuseRec) + (size_t)FUSE_CAPA * 4 * 2 + 256 * 8 + FB * 8 +
-         (size_t)FB * niso * sizeof(FuseTab) + (size_t)FB * niso * 4 + FUSE_CAPA + 16;
+  return (size_t)FBK * FUSE_CAPA * sizeof(FuseRec) + (size_t)FUSE_CAPA * 4 * 2 + 256 * 8 + FBK * 8 +
+         (size_t)FBK * niso * sizeof(FuseTab) + (size_t)FBK * niso * 4 + FUSE_CAPA + 16;
 }
 
 // ------------------------------------------------------------------ host driver
@@ -1376,7 +1384,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   const int nbatch_max = (chunk + FB - 1) / FB;
   TB_TRY(c->s_fclass.ensure(nbatch_max)); TB_TRY(c->s_fP.ensure(nbatch_max));
   const size_t fuse_shm = fuse_shared_bytes(niso);
-  const bool fuse_on = c->fuse_enabled && niso >= 1 && niso <= FUSE_MAXISO && G > 0 && fuse_shm <= 110 * 1024;
+  const bool fuse_on = c->fuse_enabled && niso >= 1 && niso <= FUSE_MAXISO && G > 0 && fuse_shm <= 100 * 1024;
   if (fuse_on && c->fuse_shm_set != (int)fuse_shm) {
     TB_CUDA(cudaFuncSetAttribute(k_linesum_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fuse_shm));
     c->fuse_shm_set = (int)fuse_shm;
@@ -1486,7 +1494,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
           k_fuse_trace_fill<<<dim3(nblk(G, Tn), cs), Tn, 0, st>>>(G, cs, c->s_fclass.p, c->g_iown.p, c->s_rec.p);
           trace_rec = c->s_rec.p;
         }
-        k_linesum_fused<<<dim3(tile_hi - tile_lo, nbatch), FUSE_NT, fuse_shm, st>>>(
+        k_linesum_fused<<<dim3(tile_hi - tile_lo, nbatch * (FB / FBK)), FUSE_NT, fuse_shm, st>>>(
             nwn, c->onwn, G, cs, niso, nmol, c->o, fd_o, fd_tile, nrows, permol, tile_lo, c->wn_i, c->odwn,
             c->s_fclass.p, c->s_fP.p, c->binstart.p,
             c->g_start.p, c->g_iso.p, c->g_iown.p, c->g_wavn.p, c->g_a0.p, c->g_gf.p, c->g_lg.p, c->s_rtemp.p,

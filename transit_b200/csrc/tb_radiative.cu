@@ -693,6 +693,153 @@ k_tau_transit(TauPar P, const double *__restrict__ e, const double *__restrict__
   }
 }
 
+
+// ---- eclipse geometry in O(layers) per wavenumber --------------------------------------------------
+// eclipsetau (eclipse.c:28-105) integrates along the VERTICAL: the path coordinate of ray ri is a running
+// sum of layer spacings, whichever layer the ray starts from, so the Simpson weights of the pair of
+// intervals (a, a+1, a+2) are the same for every ray that contains it (to rounding of the running sums),
+// every ray's pairs end at the top layer, and the rays take their starting layers top down, one layer
+// each.  The O(layers^2) work of the general kernel therefore collapses: walking the rays top down,
+//   * the unrestored extrapolation chain stores er[rs] = parabola(er[rs], er[rs+1], er[rs+2]) (eclipse.c:62-66);
+//   * a ray with an odd number of points adds ONE new pair -- its own first pair, with its own
+//     coefficients (k_ray_geometry) -- to the running sum S of the pairs above it;
+//   * a ray with an even number of points has exactly the pairs of the ray above it plus the trapezoid of
+//     its first interval (numerical.c:454-525).
+// One thread per wavenumber, no shared extinction columns, the inputs streamed once: 24 B per (layer,
+// wavenumber), the HBM figure of SURVEY 8d.  The pairs of a ray are summed from the top down instead of
+// the reference's bottom up: same terms, a different association (tau within 1e-9: tested).
+struct EclRay {           // per ray, wavenumber-independent (from k_ray_geometry's tables)
+  double dx, x0, xr, rcp0, rcp1;      // interp_parab constants of the ray's starting layer
+  double c0, c1, c2, c3;              // its first pair of intervals
+  double h0;                          // first interval (trapezoid of an even point count)
+  int mode, n;
+  int pad0, pad1;
+};
+
+__global__ void k_ecl_rays(int nh, int nrad, int stride, const int32_t *__restrict__ meta,
+                           const double *__restrict__ par, const double *__restrict__ coef,
+                           const double *__restrict__ rcp, EclRay *__restrict__ rays, int32_t *__restrict__ err) {
+  const int ri = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ri >= nh) return;
+  const int32_t *mt = meta + ri * 4;
+  EclRay r;
+  r.mode = mt[2]; r.n = mt[1];
+  r.dx = par[ri * 4]; r.x0 = par[ri * 4 + 1]; r.xr = par[ri * 4 + 2]; r.h0 = par[ri * 4 + 3];
+  r.rcp0 = rcp[ri * 2]; r.rcp1 = rcp[ri * 2 + 1];
+  const double *cf = coef + (size_t)ri * stride;
+  r.c0 = cf[0]; r.c1 = cf[1]; r.c2 = cf[2]; r.c3 = cf[3];
+  r.pad0 = r.pad1 = 0;
+  // the streaming kernel relies on ray ri starting at layer nrad-1-ri (the rays ARE the layers, tau.c:92-98)
+  if (r.mode > 0 && mt[0] != nrad - 1 - ri) atomicExch(err, 1);
+  if (r.mode == 0 && ri != 0) atomicExch(err, 1);
+  rays[ri] = r;
+}
+
+__device__ __forceinline__ double tb_extra_ext(const TauPar &P, int r, double wn, double wn4, double kBP, double kFH,
+                                               double refw, int ctop, int cbot, const double *__restrict__ press,
+                                               const double *__restrict__ temp, const double *__restrict__ aux,
+                                               const double *__restrict__ mol_d, const double *__restrict__ mol_pol,
+                                               const double *__restrict__ mol_mass, int nmol, double &ec_out) {
+  double es = 0, ec = 0;
+  const int nrad = P.nrad;
+  if (P.sc_flag == 1) es = P.sc_fac * press[r] / temp[r] * wn4;
+  else if (P.sc_flag == 2) {
+    for (int j = 0; j < nmol; j++)
+      es += TB_PI * 8e-32 / 3. * pow(mol_pol[j], 2.0) * pow(2. * TB_PI * wn * TB_MICRON, 4.0) *
+            mol_d[(size_t)j * nrad + r] / mol_mass[j] * TB_NAVOGADRO;
+  }
+  if (r <= ctop && r > cbot) {
+    const double md = aux[nrad + r];
+    switch (P.cl_flag) {
+      case 1: ec = P.cl_ext; break;
+      case 2: ec = P.cl_ext * md; break;
+      case 3: ec = kBP * md; break;
+      case 4: ec = kFH * md; break;
+      case 5: ec = aux[r] * kBP * P.cl_sig / refw * md; break;
+    }
+  }
+  ec_out = ec;
+  return es;
+}
+
+__global__ void __launch_bounds__(128)
+k_tau_eclipse(TauPar P, const double *__restrict__ e, const double *__restrict__ ecs,
+              const double *__restrict__ press, const double *__restrict__ temp,
+              const double *__restrict__ aux, const double *__restrict__ mol_d,
+              const double *__restrict__ mol_pol, const double *__restrict__ mol_mass, int nmol,
+              const EclRay *__restrict__ rays, double *__restrict__ tau, int32_t *__restrict__ last) {
+  extern __shared__ __align__(16) unsigned char esm[];
+  EclRay *sr = reinterpret_cast<EclRay *>(esm);
+  for (int i = threadIdx.x; i < P.nh * (int)(sizeof(EclRay) / 8); i += blockDim.x)
+    reinterpret_cast<double *>(sr)[i] = reinterpret_cast<const double *>(rays)[i];
+  __syncthreads();
+  const int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (w >= P.nwn) return;
+  const int nrad = P.nrad;
+  const double wn = P.wn_fct * __dadd_rn(P.wn_i, __dmul_rn((double)w, P.wn_d));
+  double kBP = 0, kFH = 0, refw = 1;
+  int ctop = -1, cbot = -1;
+  if (P.cl_flag && P.cl_ext != 0) {
+    const double top = pow(10.0, P.cl_top), bot = pow(10.0, P.cl_bot);
+    int i = nrad - 1;
+    for (; i >= 0; i--) if (press[i] >= top) break;
+    ctop = i;
+    for (; i >= 0; i--) if (press[i] >= bot) break;
+    cbot = i;
+    const double x = 2 * TB_PI * P.cl_r * wn;
+    refw = pow(P.cl_refwn, P.cl_gamma);
+    kBP = P.cl_ext * pow(wn, P.cl_gamma);
+    kFH = P.cl_ext / (P.cl_Q * pow(x, -1 * P.cl_gamma) + pow(x, 0.2));
+  }
+  const double wn4 = P.sc_flag == 1 ? pow(wn, 4.0) : 0.0;
+  const bool extra = P.sc_flag != 0 || (P.cl_flag && P.cl_ext != 0);
+  // tau.c:231-232, same left-to-right sum
+  auto load = [&](int r) -> double {
+    double es = 0, ec = 0;
+    if (extra) es = tb_extra_ext(P, r, wn, wn4, kBP, kFH, refw, ctop, cbot, press, temp, aux, mol_d, mol_pol, mol_mass, nmol, ec);
+    return __ldcs(e + (size_t)r * P.nwn + w) + es + ec + __ldcs(ecs + (size_t)r * P.nwn + w);
+  };
+  // ray 0 is the top layer itself: tau = 0 (eclipse.c:46-47)
+  tau[w] = 0.0;
+  int lst = P.nh - 1;
+  if (0.0 > P.toomuch) { last[w] = 0; return; }
+  if (P.nh == 1) { last[w] = 0; return; }
+  // sliding window of the column, top down: e1 = er[rs+1], e2 = er[rs+2] (final values), er[rs] loaded ahead
+  double e2 = 0.0, e1 = load(nrad - 1);
+  double cur = load(nrad - 2);                     // er[rs] of ray 1
+  double nxt = nrad >= 3 ? load(nrad - 3) : 0.0;   // the layer below, still unmodified: ray 1's parabola reads it
+  // three more layers in flight: one coalesced 256-byte request per warp and array every iteration, issued
+  // four rays before its value is needed
+  double n2 = nrad >= 4 ? load(nrad - 4) : 0.0, n3 = nrad >= 5 ? load(nrad - 5) : 0.0, n4 = nrad >= 6 ? load(nrad - 6) : 0.0;
+  double S = 0.0;                                  // running sum of the pairs above, (f0 c0 + f1 c1 + f2 c2) c3
+  for (int ri = 1; ri < P.nh; ri++) {
+    const EclRay &R = sr[ri];
+    const int rs = nrad - 1 - ri;
+    double t;
+    if (R.mode == 2) {
+      // two points: parabola through layers rs-1, rs, rs+1 at rad[rs], midpoint construction, value restored
+      const double rc[2] = {R.rcp0, R.rcp1};
+      const double y0 = tb_parab(R.dx, R.x0, R.xr, rc, nxt, cur, e1);
+      const double yb = e1, ya = (y0 + yb) / 2.0;
+      t = (y0 * R.c0 + ya * R.c1 + yb * R.c2) * R.c3 / 6.0;
+    } else {
+      const double rc[2] = {R.rcp0, R.rcp1};
+      cur = tb_parab(R.dx, R.x0, R.xr, rc, cur, e1, e2);          // stays modified for the rays below
+      if ((R.n & 1) != 0) {                                        // odd point count: one new pair, then the ones above
+        S = (cur * R.c0 + e1 * R.c1 + e2 * R.c2) * R.c3 + S;
+        t = S / 6.0;
+      } else
+        t = S / 6.0 + R.h0 * (cur + e1) / 2;
+    }
+    t = P.rfct * t;
+    tau[(size_t)ri * P.nwn + w] = t;
+    if (t > P.toomuch) { lst = ri; break; }                        // tau.c:277-287
+    e2 = e1; e1 = cur; cur = nxt; nxt = n2; n2 = n3; n3 = n4;
+    n4 = rs - 5 >= 0 ? load(rs - 5) : 0.0;
+  }
+  last[w] = lst;
+}
+
 static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, int nh, double hfct, bool sync) {
   TB_REQUIRE(c->have_e && c->have_atm, TB_ERR_STATE, "extinction must be computed before tb_tau");
   TB_REQUIRE(geometry == TB_GEOM_TRANSIT || geometry == TB_GEOM_ECLIPSE, TB_ERR_ARG, "bad geometry");
@@ -739,7 +886,16 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
   P.cl_ext = c->cl_ext; P.cl_top = c->cl_top; P.cl_bot = c->cl_bot; P.cl_gamma = c->cl_gamma;
   P.cl_Q = c->cl_Q; P.cl_r = c->cl_r; P.cl_sig = c->cl_sig; P.cl_refwn = c->cl_refwn;
   tb_timer_begin(c, "tau");
-  {
+  if (geometry == TB_GEOM_ECLIPSE && c->tau_stream_ecl && nh == nrad && nrad >= 3 &&
+      (size_t)nh * sizeof(EclRay) <= 48 * 1024) {
+    TB_TRY(c->r_ecl.ensure((size_t)nh * sizeof(EclRay)));
+    k_ecl_rays<<<nblk(nh, 128), 128, 0, st>>>(nh, nrad, stride, c->r_meta.p, c->r_par.p, c->r_coef.p, c->r_rcp.p,
+                                              reinterpret_cast<EclRay *>(c->r_ecl.p), c->d_err.p);
+    k_tau_eclipse<<<nblk(nwn, 128), 128, (size_t)nh * sizeof(EclRay), st>>>(
+        P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p, c->d_dens.p, c->d_mol_pol.p, c->d_mol_mass.p,
+        c->nmol, reinterpret_cast<const EclRay *>(c->r_ecl.p), c->d_tau.p, c->d_last.p);
+    TB_LAUNCHED(c);
+  } else {
     const size_t shm = ((size_t)nrad * 32 + (size_t)TAU_NW * stride) * sizeof(double);
     TB_REQUIRE(stride <= 320, TB_ERR_ARG, "too many layers (%d) for the tau kernel's coefficient registers", nrad);
     TB_REQUIRE(shm <= 200 * 1024, TB_ERR_ARG, "too many layers (%d) for the tau kernel's shared memory", nrad);
@@ -766,10 +922,17 @@ int tb_check_errors(tb_ctx *c) {
   int32_t err[4];
   TB_CUDA(cudaMemcpyAsync(err, c->d_err.p, sizeof(err), cudaMemcpyDeviceToHost, c->stream));
   TB_CUDA(cudaStreamSynchronize(c->stream));
+  TB_REQUIRE(err[0] == 0, TB_ERR_STATE, "eclipse rays are not the layers taken top down (tau.c:92-98): internal error");
   TB_REQUIRE(err[1] == 0, TB_ERR_DOMAIN, "a ray's closest approach lies below the bottom layer (slantpath.c:40-44)");
   TB_REQUIRE(err[2] == 0, TB_ERR_DOMAIN, "less than 3 items for radial integration (slantpath.c:393-397)");
   TB_REQUIRE(err[3] == 0, TB_ERR_DOMAIN, "Optical depth didn't reach the limiting value at some wavenumber.  Cannot use "
              "critical radius technique (-1) (slantpath.c:308-316)");
+  return TB_OK;
+}
+
+// 1 (default): eclipse tau by the O(layers) streaming kernel; 0: the general O(layers^2) kernel (comparison tap)
+extern "C" int tb_set_tau_streaming(tb_ctx *c, int on) {
+  c->tau_stream_ecl = on != 0;
   return TB_OK;
 }
 
