@@ -80,7 +80,8 @@ int  tb_get_line_trace(tb_ctx *c, int s, int32_t *iown, int32_t *idwn, int32_t *
                        int8_t *status);
 int  tb_get_sample_counts(tb_ctx *c, int64_t *nsamples, int ns);
 /* The line sum of a state whose profiles are narrow runs as ONE kernel (strength + gather, records kept in
- * shared memory); tb_set_fused(c, 0) sends every state through the two-kernel path instead (same bits for the
+ * shared memory) on grids of at least 96 tiles of 128 bins; tb_set_fused(c, 0) sends every state through the
+ * two-kernel path instead, tb_set_fused(c, 2) fuses on small grids too (same bits for the
  * narrow-reach states: same summation order).  tb_set_trace(c, 1) makes the fused kernel also leave the
  * per-line records tb_get_line_trace reads (off by default: 16 B of HBM per (group, state)).
  * tb_get_fused_stats: states of the last batch taken by the fused kernel and its executed profile updates. */

@@ -27,6 +27,7 @@ def cfg_of(d):
 def setup_ctx(prob, d=None, nDop=None, nLor=None, lines=True):
     c = api.Context(0)
     c.set_trace(True)       # the fused line sum leaves its per-line records only when asked (tb_set_trace)
+    c.set_fused(2)          # ... and is used on these small grids too, so that every parity test covers it
     c.set_wn_grid(prob.wn_i, prob.wn_d, prob.wnosamp, prob.nwn, prob.onwn, prob.wn_fct)
     c.set_species(prob.mol_mass, prob.mol_radius, prob.mol_pol, prob.mol_ID, prob.iso_mass, prob.iso_ratio,
                   prob.iso_imol)
@@ -160,7 +161,7 @@ def test_fused_line_sum_vs_two_kernel_path():
     T = prob.t * prob.t_fct
     dens, Z = prob.mol_d.T.copy(), prob.iso_z.T.copy()
     for permol in (0, 1):
-        c.set_fused(True)
+        c.set_fused(2)                     # 2: fused whatever the size of the grid
         a = c.molext_states(T, dens, Z, prob.ethresh, permol=permol)
         st = c.fused_stats()
         na = c.sample_counts(prob.nrad)
@@ -182,7 +183,7 @@ def test_fused_line_sum_vs_two_kernel_path():
         assert relerr(a, b) < 1e-13
         same = [r for r in range(prob.nrad) if np.array_equal(a[r], b[r])]
         assert len(same) >= prob.nrad - 8, (len(same), prob.nrad)      # only the few reach-3..8 layers may differ in order
-    c.set_fused(True)
+    c.set_fused(1)
     c.close()
 
 

@@ -243,8 +243,9 @@ class Context:
                  "tb_get_line_trace")
         return dict(iown=a[0], idwn=a[1], idop=a[2], status=st)
 
-    def set_fused(self, on=True):
-        self._ck(self.lib.tb_set_fused(self.h, int(bool(on))), "tb_set_fused")
+    def set_fused(self, on=1):
+        """0: two-kernel path; 1/True: fused where the grid has >= 96 tiles; 2: fused on small grids too."""
+        self._ck(self.lib.tb_set_fused(self.h, int(on)), "tb_set_fused")
 
     def set_trace(self, on=True):
         self._ck(self.lib.tb_set_trace(self.h, int(bool(on))), "tb_set_trace")

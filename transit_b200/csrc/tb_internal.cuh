@@ -216,7 +216,8 @@ struct tb_ctx {
   DevBuf<double> s_facz, s_rtemp, s_ral, s_xterm, s_lcz;
   DevBuf<LineRec> s_rec;      // [state][group]
   DevBuf<int32_t> s_fclass, s_fP;   // per batch of 8 states: taken by k_linesum_fused? / widest half-size (fine bins)
-  bool fuse_enabled = true, trace_enabled = false;
+  int fuse_enabled = 1;          // 0 off, 1 on where the grid has enough tiles, 2 always (tests)
+  bool trace_enabled = false;
   int fuse_shm_set = -1, last_chunk_s0 = 0, last_chunk_cs = 0;
   DevBuf<uint8_t> s_hasfb;    // [state][tile]
   DevBuf<unsigned long long> s_nsamp;

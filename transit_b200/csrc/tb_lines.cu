@@ -1041,6 +1041,7 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
 #define FUSE_NT 256
 #define FUSE_MAXISO 64
 #define FUSE_RMAX 8          // widest reach, in coarse bins, of a fused state
+#define FUSE_MIN_TILES 96     // grids with fewer 128-bin tiles keep the two-kernel path (tb_set_fused(c, 2) forces fusion)
 
 // Which batches of FB states the fused kernel takes (decided on the device: no read-back on the way)
 __global__ void k_fuse_class(int ns, int niso, double wn_i, double own_last, int o, int enable,
@@ -1237,13 +1238,18 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
             const int s = s0 + k;
             const double rT = sh_rT[k];
             const FuseTab t = sh_tab[k * niso + iso];
+            // the first co-added member's term is requested before the two exp(): its L2 round trip hides behind them
+            const double *xt = xterm + (size_t)s * X + (b - q);     // member l of the group: xt[l - b - 1]
+            const double x1 = e - b > 1 ? __ldg(xt) : 0.0;
             const double ge1 = __dmul_rn(gf, tb_exp(a0 * rT));
             double kk = 0.0;
             bool below = (e - b == 1) && ge1 * t.facz < 0.999999 * t.thr;
             if (!below) {
               double a = __dmul_rn(ge1, (1 - tb_exp(wneg * rT)));
-              for (int l = b + 1; l < e; l++)                      // co-added members (extinction.c:449-462)
-                a = __dadd_rn(a, xterm[(size_t)s * X + (l - q - 1)]);
+              if (e - b > 1) {                                      // co-added members, in order (extinction.c:449-462)
+                a = __dadd_rn(a, x1);
+                for (int l = b + 2; l < e; l++) a = __dadd_rn(a, xt[l - b - 1]);
+              }
               kk = __dmul_rn(a, t.facz);
               below = kk < t.thr;                                  // extinction.c:467-470
             }
@@ -1342,6 +1348,7 @@ static size_t fuse_shared_bytes(int niso) {
          (size_t)FBK * niso * sizeof(FuseTab) + (size_t)FBK * niso * 4 + FUSE_CAPA + 16;
 }
 
+
 // ------------------------------------------------------------------ host driver
 
 int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const double *Z,
@@ -1384,7 +1391,10 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   const int nbatch_max = (chunk + FB - 1) / FB;
   TB_TRY(c->s_fclass.ensure(nbatch_max)); TB_TRY(c->s_fP.ensure(nbatch_max));
   const size_t fuse_shm = fuse_shared_bytes(niso);
-  const bool fuse_on = c->fuse_enabled && niso >= 1 && niso <= FUSE_MAXISO && G > 0 && fuse_shm <= 100 * 1024;
+  // a tile of 128 bins x 4 states is the fused kernel's unit of parallelism: a grid of a few dozen tiles (C1: 20)
+  // cannot fill 148 SMs with it (measured: C1 1.29 -> 2.9 ms per step), so small grids keep the two-kernel path
+  const bool fuse_on = c->fuse_enabled && niso >= 1 && niso <= FUSE_MAXISO && G > 0 && fuse_shm <= 100 * 1024 &&
+                       (ntiles >= FUSE_MIN_TILES || c->fuse_enabled > 1);
   if (fuse_on && c->fuse_shm_set != (int)fuse_shm) {
     TB_CUDA(cudaFuncSetAttribute(k_linesum_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fuse_shm));
     c->fuse_shm_set = (int)fuse_shm;
@@ -1689,7 +1699,7 @@ extern "C" int tb_set_trace(tb_ctx *c, int on) {
 }
 // 0: every state through k_strength + k_accumulate (the two-kernel path); 1 (default): narrow states fused
 extern "C" int tb_set_fused(tb_ctx *c, int on) {
-  c->fuse_enabled = on != 0;
+  c->fuse_enabled = on < 0 ? 0 : (on > 2 ? 2 : on);     // 2: also on grids of fewer than FUSE_MIN_TILES tiles
   return TB_OK;
 }
 // how many states of the last batch the fused kernel took, and the profile updates it executed
@@ -1709,3 +1719,4 @@ extern "C" int tb_get_fused_stats(tb_ctx *c, int64_t *fused_states, int64_t *fus
   if (fused_samples) *fused_samples = smp;
   return TB_OK;
 }
+
