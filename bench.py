@@ -361,6 +361,50 @@ def cpu_baseline_leg(args):
                       f"do_transit), split into {nb} wavenumber bands on {nb} processes/cores: {sec:.1f} s"}
 
 
+def bands_leg(args, prob, ref_out, one_gpu_ms, local_rank, rank, world, stream, flush):
+    """Strong scaling of ONE spectrum: the wavenumber range of the same C2 problem cut into `world` bands, one per
+    rank (north_star's first sharding).  Exchange inside the library: two ncclAllReduce(MAX) in the line sum, one
+    ncclAllGather of the band slices; every rank ends each step with the whole spectrum.  Timed like the headline
+    (CUDA events on the launching stream, L2 flushed between steps, max over ranks); no per-step barrier -- the
+    collectives are what couples the ranks."""
+    import torch
+    import torch.distributed as dist
+    from transit_b200 import sharding
+    tb = sharding.BandShardedTransit(local_rank, rank, world)
+    tb.ctx.set_stream(stream.cuda_stream)
+    tb.transit_init(prob)
+    for _ in range(max(3, args.warmup)):
+        g = tb.do_transit_gathered()
+    same = bool(np.array_equal(g.cpu().numpy(), ref_out)) if rank == 0 else True
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ms, kms = [], {}
+    for _ in range(args.steps):
+        flush.zero_()
+        torch.cuda.synchronize()
+        ev0.record(stream)
+        tb.do_transit_gathered()
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        ms.append(ev0.elapsed_time(ev1))
+        for nm in ("kmax", "strength", "fused", "accumulate", "molext", "cia", "tau", "modulation", "gather"):
+            try:
+                kms.setdefault(nm, []).append(tb.ctx.kernel_ms(nm))
+            except Exception:
+                pass
+    torch.cuda.synchronize(); dist.barrier()
+    t = torch.tensor([float(np.sum(ms)), 0.0 if same else 1.0], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    tb.free_memory()
+    step_ms = float(t[0]) / args.steps
+    return {"what": f"one {args.workload} spectrum per step, wavenumber range in {world} bands (strong scaling)",
+            "ms_per_step": step_ms, "spectra_per_s": 1e3 / step_ms, "one_gpu_ms_per_step": one_gpu_ms,
+            "speedup_vs_one_gpu": one_gpu_ms / step_ms, "efficiency": one_gpu_ms / step_ms / world,
+            "bit_identical_to_single_gpu": bool(float(t[1]) == 0.0), "bands": tb.bands,
+            "exchange": "in-library NCCL: 2 x ncclAllReduce(MAX) + 1 x ncclAllGather per spectrum, on the context stream",
+            "rank0_kernel_ms": {k: float(np.mean(v)) for k, v in kms.items()}, "ms_step_stats": ms_stats(ms)}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -455,6 +499,12 @@ def run_ours(args):
     if world > 1 and not bands_mode:
         assert np.array_equal(gathered[0][rank].cpu().numpy(), out), "gathered slice differs from the local spectrum"
 
+    # ---- N > 1: the other sharding of north_star beside the headline -- one spectrum over N wavenumber bands
+    bands = None
+    if world > 1 and not bands_mode and not args.no_bands_leg:
+        ref0 = [ref_out if rank == 0 else None]           # rank 0 ran the unperturbed problem: the single-GPU spectrum
+        bands = bands_leg(args, prob, ref0[0], float(np.mean(ms_steps)), local_rank, rank, world, stream, flush)
+
     # ---- end to end with HOST buffers, every step: atmosphere in (H2D inside the call), spectrum out (D2H)
     e2e_api = args.e2e_api if not bands_mode else "mirror"
     if e2e_api == "host":
@@ -537,6 +587,8 @@ def run_ours(args):
     }
     if verified is not None:
         line["bit_identical_to_single_gpu"] = verified
+    if bands is not None:
+        line["bands"] = bands
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_leg(args)
     if world > 1:
@@ -565,6 +617,7 @@ def main():
                     help="N>1: one atmosphere per rank (weak scaling, default) or one spectrum split into "
                          "wavenumber bands (strong scaling)")
     ap.add_argument("--scale", type=float, default=1.0, help="line-count multiplier (debugging only; 1.0 = the named config)")
+    ap.add_argument("--no-bands-leg", action="store_true", help="N>1: skip the wavenumber-band strong-scaling leg")
     ap.add_argument("--e2e-api", default="host", choices=["host", "mirror"],
                     help="e2e leg: run_transit of the C host (host/libtransit_host.so, the reference's plugin call, "
                          "a16 host work included) or the Python mirror (tb_set_atmosphere + tb_spectrum)")

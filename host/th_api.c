@@ -7,9 +7,11 @@
 #include <stdlib.h>
 #include <string.h>
 #include <sys/time.h>
+#include <unistd.h>
 #include "th_internal.h"
 
 static th_state S;
+int th_rank = 0, th_world = 1, th_idfd[64];
 #ifdef TH_TEST_TAPS
 int th_dry = 0;
 #endif
@@ -83,7 +85,7 @@ void transit_init(int argc, char **argv) {
     free(g);
     if (S.nang < 1) th_die("raygrid '%s' holds no angle.\n", h->raygrid);
   }
-  int dev = 0;
+  int dev = th_rank;                                       /* one process per GPU: rank r drives device r */
 #ifdef TH_TEST_TAPS
   th_dry = getenv("TRANSIT_B200_DRYRUN") != NULL;
 #endif
@@ -100,6 +102,19 @@ void transit_init(int argc, char **argv) {
                     S.isoimol));
   th_make_rad(&S);                                         /* makeradsample */
   timecheck(4, "makeradsample");
+  S.band_lo = 0; S.band_hi = S.nwn;
+  if (th_world > 1) {
+    /* wavenumber-band sharding over the GPUs of the box: rank 0 makes the NCCL id and passes it
+     * down the pipes th_main.c opened before forking; every rank joins the communicator */
+    char id[128];
+    if (th_rank == 0) {
+      CK(tb_comm_unique_id(id));
+      for (int r = 1; r < th_world; r++)
+        if (write(th_idfd[r], id, 128) != 128) th_die("cannot hand the communicator id to rank %d\n", r);
+    } else if (read(th_idfd[th_rank], id, 128) != 128)
+      th_die("rank %d: no communicator id from rank 0\n", th_rank);
+    CK(tb_comm_init(S.ctx, th_rank, th_world, id));
+  }
   th_opacity(&S);                                          /* opacity */
   timecheck(5, "opacity");
   th_read_cs(&S);                                          /* readcs */

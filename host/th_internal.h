@@ -81,6 +81,7 @@ typedef struct {
   /* device */
   tb_ctx *ctx;
   int have_grid_file, initialised;
+  int64_t band_lo, band_hi;       /* this rank's wavenumber band (whole grid when world = 1) */
   double *out;
 } th_state;
 
@@ -123,6 +124,9 @@ void do_transit(double *transit_out);
 void free_memory(void);
 void th_write_spectrum(void);
 /* test/diagnostic accessor: the device context behind the library face (NULL before transit_init) */
+/* multi-GPU: rank / world of this process and the pipe ends the 128-byte communicator id travels through
+ * (set by th_main.c before transit_init; world 1 = single GPU) */
+extern int th_rank, th_world, th_idfd[64];
 tb_ctx *th_context(void);
 void th_sizes(int64_t *out);
 #endif

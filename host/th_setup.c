@@ -5,10 +5,21 @@
  *   makeradsample (raddelt = -1)   makesample.c:408-549 (natural splines, spline.c:12-48,131-206)
  *   opacity() driver + file I/O    opacity.c:11-215,281-503
  */
+#include <fcntl.h>
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
 #include "th_internal.h"
+
+/* multi-GPU run: this rank's wavenumber band, once the grid (and, line by line, the line index) is on the device */
+static void set_bands(th_state *s) {
+  if (th_world <= 1) return;
+  int64_t edges[65];
+  if (TH_DEV(tb_balanced_bands(s->ctx, th_world, edges)) || TH_DEV(tb_set_bands(s->ctx, th_world, edges, th_rank)))
+    th_die("%s\n", tb_last_error());
+  s->band_lo = edges[th_rank]; s->band_hi = edges[th_rank + 1];
+}
 
 /* ---- natural cubic spline, pu/src/spline.c:12-48 (tri + spline_init) and :131-183 */
 void th_spline_init(double *z, const double *x, const double *y, long n) {
@@ -201,11 +212,13 @@ int th_opacity(th_state *s) {
     if (TH_DEV(tb_opacity_load(s->ctx, Nmol, Nt, Nl, Nw, molID, temp, press, grid))) th_die("%s\n", tb_last_error());
     free(molID); free(temp); free(press); free(wns); free(grid);
     s->have_grid_file = 1;
+    set_bands(s);
     return 0;
   }
   /* line-by-line: line index + Voigt table (calcprofiles, opacity.c:218-277) */
   if (TH_DEV(tb_upload_lines(s->ctx, s->wl, s->elow, s->gf, s->isoid, s->nlines, 1e-4, 1.0))) th_die("%s\n", tb_last_error());
   if (TH_DEV(tb_build_profiles(s->ctx, h->nDop, h->nLor, h->dmin, h->dmax, h->lmin, h->lmax, h->nwidth))) th_die("%s\n", tb_last_error());
+  set_bands(s);
   if (!h->f_opa) return 0;
   /* calcopacity (opacity.c:281-427): temperature grid, Z(T) per isotope, grid, file */
   const long Nt = (long)tb_grid_count(h->tlow, h->thigh, h->tempdelt, 1);   /* maketempsample, makesample.c:614-636 */
@@ -226,16 +239,35 @@ int th_opacity(th_state *s) {
   double *grid = (double *)malloc(ng * sizeof(double));
   if (!grid) th_die("Not enough host memory for the opacity grid (%zu bytes).\n", ng * sizeof(double));
   if (TH_DEV(tb_opacity_build(s->ctx, (int)Nt, temp, ziso, s->q, s->mm, s->bymass, h->ethresh, grid))) th_die("%s\n", tb_last_error());
-  FILE *fp = fopen(h->f_opa, "wb");
-  if (!fp) th_die("Opacity filename '%s' cannot be opened for writing.\n", h->f_opa);
-  long dims[4] = {nrows, Nt, n, (long)s->nwn};
-  fwrite(dims, sizeof(long), 4, fp);
-  fwrite(molID, sizeof(int), nrows, fp);
-  fwrite(temp, 8, Nt, fp);
-  for (int r = 0; r < n; r++) { const double pr = s->p[r] * s->p_fct; fwrite(&pr, 8, 1, fp); }
-  for (int64_t w = 0; w < s->nwn; w++) { const double wn = s->wn_i + (double)w * s->wn_d; fwrite(&wn, 8, 1, fp); }
-  fwrite(grid, 8, ng, fp);
-  fclose(fp);
+  /* the file (opacity.c:405-423).  A band-sharded build computed only this rank's columns of every row
+   * o[r][t][m][.]: rank 0 writes the header, every rank writes its own column slices in place (file order has
+   * the wavenumber innermost), and nobody goes on before all have written. */
+  const long dims[4] = {nrows, Nt, n, (long)s->nwn};
+  const off_t hdr = 4 * sizeof(long) + (off_t)nrows * sizeof(int) + 8 * ((off_t)Nt + n + s->nwn);
+  if (th_rank == 0) {
+    FILE *fp = fopen(h->f_opa, "wb");
+    if (!fp) th_die("Opacity filename '%s' cannot be opened for writing.\n", h->f_opa);
+    fwrite(dims, sizeof(long), 4, fp);
+    fwrite(molID, sizeof(int), nrows, fp);
+    fwrite(temp, 8, Nt, fp);
+    for (int r = 0; r < n; r++) { const double pr = s->p[r] * s->p_fct; fwrite(&pr, 8, 1, fp); }
+    for (int64_t w = 0; w < s->nwn; w++) { const double wn = s->wn_i + (double)w * s->wn_d; fwrite(&wn, 8, 1, fp); }
+    if (th_world == 1) fwrite(grid, 8, ng, fp);
+    fclose(fp);
+  }
+  if (th_world > 1) {
+    if (TH_DEV(tb_comm_barrier(s->ctx))) th_die("%s\n", tb_last_error());      /* the header is there */
+    const int fd = open(h->f_opa, O_WRONLY);
+    if (fd < 0) th_die("Opacity filename '%s' cannot be opened for writing.\n", h->f_opa);
+    const size_t nrow = (size_t)n * Nt * nrows, bw = (size_t)(s->band_hi - s->band_lo);
+    for (size_t k = 0; k < nrow && bw; k++) {
+      const off_t at = hdr + 8 * ((off_t)k * s->nwn + s->band_lo);
+      if (pwrite(fd, grid + k * s->nwn + s->band_lo, 8 * bw, at) != (ssize_t)(8 * bw))
+        th_die("Short write to opacity file '%s'.\n", h->f_opa);
+    }
+    close(fd);
+    if (TH_DEV(tb_comm_barrier(s->ctx))) th_die("%s\n", tb_last_error());      /* the file is complete */
+  }
   free(temp); free(ziso); free(grid);
   (void)nmol;
   s->have_grid_file = 1;

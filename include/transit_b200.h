@@ -179,7 +179,8 @@ int  tb_device_spectrum(tb_ctx *c, void **ptr, int64_t *n);
  * of 128 or the grid ends; (0, 0) = the whole grid.  Two quantities of computemolext are global
  * over the line list: the strength maximum behind the threshold (extinction.c:399-427, 467) and
  * the Doppler index carried from the last evaluated line (extinction.c:480-483).  With world > 1
- * the library calls `fn` twice per batch of states for an in-place all-reduce MAX over `count`
+ * the library calls `fn` (or, when fn is NULL and tb_comm_init has run, ncclAllReduce itself) twice per batch
+ * of states for an in-place all-reduce MAX over `count`
  * elements at `device_ptr` (doubles for TB_EXCH_KMAX, int32 for TB_EXCH_LASTQ), to be enqueued
  * on the context's stream (e.g. ncclAllReduce, or torch.distributed on the stream given to
  * tb_set_stream); both maxima are exact, so the banded results are bit-identical to one GPU.
@@ -188,6 +189,22 @@ enum { TB_EXCH_KMAX = 0, TB_EXCH_LASTQ = 1 };
 typedef int (*tb_exchange_fn)(void *user, int what, void *device_ptr, int64_t count);
 int  tb_set_shard(tb_ctx *c, int64_t j_lo, int64_t j_hi, int rank, int world, tb_exchange_fn fn,
                   void *user);
+
+/* In-library exchange of a band-sharded run (one process per GPU; NCCL bound at run time with dlopen, so a
+ * single-GPU user needs none).  Rank 0 makes the 128-byte id (tb_comm_unique_id = ncclGetUniqueId) and the host
+ * hands it to the other ranks by whatever it has (a pipe between forked ranks, MPI, torch.distributed, a file);
+ * every rank then calls tb_comm_init (ncclCommInitRank on the context's device).  tb_balanced_bands cuts the
+ * coarse grid into `world` contiguous bands balanced by line groups per bin (ends on multiples of 128; the same
+ * table on every rank); tb_set_bands makes this context rank `rank` of that table.  From then on tb_spectrum
+ * evaluates only its band -- line sum, CIA evaluation, tau, modulation / intensities -- completes the two global
+ * maxima of computemolext with ncclAllReduce(MAX) on the context's stream, and ends with an ncclAllGather of the
+ * band slices, so that EVERY rank returns the whole spectrum, bit-identical to a single-GPU run.            */
+int  tb_comm_unique_id(char *id128);
+int  tb_comm_init(tb_ctx *c, int rank, int world, const char *id128);
+int  tb_comm_destroy(tb_ctx *c);
+int  tb_comm_barrier(tb_ctx *c);     /* all ranks have finished what they enqueued (tiny all-reduce + stream sync) */
+int  tb_balanced_bands(tb_ctx *c, int world, int64_t *edges /*[world+1]*/);
+int  tb_set_bands(tb_ctx *c, int world, const int64_t *edges /*[world+1]*/, int rank);
 
 /* device micro-benchmarks used for the roofline denominators (FP64 FMA / exp / copy)   */
 int  tb_microbench(tb_ctx *c, double *dfma_tflops, double *dexp_gops, double *copy_gbs);

@@ -84,6 +84,12 @@ ABI = {
     "tb_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "tb_device_spectrum": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), i64p]),
     "tb_microbench": (C.c_int, [C.c_void_p, f64p, f64p, f64p]),
+    "tb_comm_unique_id": (C.c_int, [C.c_char_p]),
+    "tb_comm_init": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p]),
+    "tb_comm_destroy": (C.c_int, [C.c_void_p]),
+    "tb_comm_barrier": (C.c_int, [C.c_void_p]),
+    "tb_balanced_bands": (C.c_int, [C.c_void_p, C.c_int, i64p]),
+    "tb_set_bands": (C.c_int, [C.c_void_p, C.c_int, i64p, C.c_int]),
     "tb_set_shard": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
 }
 
@@ -434,6 +440,27 @@ class Context:
         self._exchange_cb = cb               # keep the trampoline alive as long as the context uses it
         self._ck(self.lib.tb_set_shard(self.h, int(j_lo), int(j_hi), int(rank), int(world),
                                        C.cast(cb, C.c_void_p) if cb else None, None), "tb_set_shard")
+
+    # -- in-library NCCL exchange of a band-sharded run ------------------------------------
+    @staticmethod
+    def comm_unique_id():
+        buf = C.create_string_buffer(128)
+        lib = load_library()
+        if lib.tb_comm_unique_id(buf) != 0:
+            raise TransitError(f"tb_comm_unique_id failed: {lib.tb_last_error().decode()}")
+        return buf.raw
+
+    def comm_init(self, rank, world, id128):
+        self._ck(self.lib.tb_comm_init(self.h, int(rank), int(world), C.c_char_p(bytes(id128))), "tb_comm_init")
+
+    def balanced_bands(self, world):
+        e = np.zeros(world + 1, np.int64)
+        self._ck(self.lib.tb_balanced_bands(self.h, int(world), _p(e, i64p)), "tb_balanced_bands")
+        return e
+
+    def set_bands(self, edges, rank):
+        e = np.ascontiguousarray(edges, np.int64)
+        self._ck(self.lib.tb_set_bands(self.h, len(e) - 1, _p(e, i64p), int(rank)), "tb_set_bands")
 
     def sync(self):
         self._ck(self.lib.tb_sync(self.h), "tb_sync")

@@ -112,7 +112,8 @@ extern "C" int tb_set_shard(tb_ctx *c, int64_t j_lo, int64_t j_hi, int rank, int
                             void *user) {
   TB_REQUIRE(c->have_grid, TB_ERR_STATE, "tb_set_wn_grid must precede tb_set_shard");
   TB_REQUIRE(world >= 1 && rank >= 0 && rank < world, TB_ERR_ARG, "tb_set_shard: rank %d of %d", rank, world);
-  TB_REQUIRE(world == 1 || fn, TB_ERR_ARG, "tb_set_shard: world > 1 needs an exchange callback");
+  TB_REQUIRE(world == 1 || fn || (c->comm && c->comm_world == world && c->comm_rank == rank), TB_ERR_ARG,
+             "tb_set_shard: world > 1 needs an exchange callback or a communicator of that size (tb_comm_init)");
   if (j_lo == 0 && j_hi == 0) j_hi = c->nwn;
   TB_REQUIRE(j_lo >= 0 && j_lo <= j_hi && j_hi <= c->nwn, TB_ERR_ARG, "tb_set_shard: band [%lld, %lld) outside the grid",
              (long long)j_lo, (long long)j_hi);
@@ -136,6 +137,7 @@ extern "C" void tb_destroy(tb_ctx *c) {
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->aux_stream) cudaStreamSynchronize(c->aux_stream);
+  tb_comm_destroy(c);
   // every DevBuf member frees itself in its destructor (delete c below)
   for (CiaTable *t : c->cia) delete t;
   c->cia.clear();

@@ -187,6 +187,13 @@ struct tb_ctx {
   tb_exchange_fn exch = nullptr;
   void *exch_user = nullptr;
   std::vector<int32_t> h_binstart;    // host copy of binstart (group ranges of a band)
+  // in-library exchange of a band-sharded run (tb_comm.cu): NCCL communicator, band table, gather staging
+  void *comm = nullptr;
+  int comm_rank = 0, comm_world = 1;
+  std::vector<int64_t> band_edges;    // [world + 1]
+  DevBuf<double> g_send, g_recv;
+  DevBuf<int64_t> g_edges;
+  int g_edges_world = 0;
 
   // ---- Voigt table (a3/a4)
   bool have_prof = false;
@@ -331,3 +338,13 @@ int tb_check_errors(tb_ctx *c);
 #define TB_RING_BYTES (size_t(4) << 20)
 int tb_upload_small(tb_ctx *c, void *dst, const void *src, size_t bytes, cudaStream_t st);
 int tb_interp_run(tb_ctx *c);
+int tb_comm_allreduce_max(tb_ctx *c, int what, void *device_ptr, int64_t count);
+int tb_comm_gather_spectrum(tb_ctx *c);
+extern "C" int tb_comm_destroy(tb_ctx *c);
+// columns [w0, w1) the per-wavenumber stages (CIA evaluation, tau, modulation, intensities) compute: the band of a
+// sharded run that gathers its spectrum in the library, else the whole grid
+static inline void tb_band_columns(const tb_ctx *c, int64_t *w0, int64_t *w1) {
+  const bool cut = c->banded && c->comm && c->shard_world > 1 && !c->band_edges.empty();
+  *w0 = cut ? c->band_lo : 0;
+  *w1 = cut ? c->band_hi : c->nwn;
+}

@@ -1440,7 +1440,8 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       pb[r] = c->h_binstart[(size_t)r * nwn + jh];
     }
   }
-  TB_REQUIRE(c->shard_world == 1 || c->exch, TB_ERR_STATE, "sharded context without an exchange callback");
+  TB_REQUIRE(c->shard_world == 1 || c->exch || c->comm, TB_ERR_STATE,
+             "sharded context without an exchange callback or a communicator (tb_comm_init)");
   tb_timer_begin(c, "molext");
   for (int s0 = 0; s0 < ns; s0 += chunk) {
     const int cs = (ns - s0 < chunk) ? ns - s0 : chunk;
@@ -1483,9 +1484,12 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
             q0, q1, cs, niso, c->q_g.p, c->q_a.p, c->q_w.p, c->q_iso.p, c->s_rtemp.p, c->s_Z.p, c->d_iso_mass.p,
             c->d_iso_row.p, permol, nrows, c->s_kmax.p);
       TB_LAUNCHED(c);
-      if (c->shard_world > 1)
-        TB_REQUIRE(c->exch(c->exch_user, TB_EXCH_KMAX, c->s_kmax.p, (int64_t)cs * nrows) == 0, TB_ERR_STATE,
-                   "exchange callback failed (strength maxima)");
+      if (c->shard_world > 1) {
+        if (c->exch)
+          TB_REQUIRE(c->exch(c->exch_user, TB_EXCH_KMAX, c->s_kmax.p, (int64_t)cs * nrows) == 0, TB_ERR_STATE,
+                     "exchange callback failed (strength maxima)");
+        else TB_TRY(tb_comm_allreduce_max(c, TB_EXCH_KMAX, c->s_kmax.p, (int64_t)cs * nrows));
+      }
       tb_timer_end(c, "kmax");
       tb_timer_begin(c, "strength");
       if (X > 0) {
@@ -1535,9 +1539,12 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
           c->d_aDop.p, c->nDop, c->d_ptab.p, c->nLor, ethresh, permol, nrows, c->s_kmax.p,
           c->s_rec.p, c->s_lastq.p, c->s_wtile.p, c->s_hasfb.p, ntiles, c->s_fclass.p);
       }
-      if (c->shard_world > 1)
-        TB_REQUIRE(c->exch(c->exch_user, TB_EXCH_LASTQ, c->s_lastq.p, (int64_t)cs * niso) == 0, TB_ERR_STATE,
-                   "exchange callback failed (carried Doppler index)");
+      if (c->shard_world > 1) {
+        if (c->exch)
+          TB_REQUIRE(c->exch(c->exch_user, TB_EXCH_LASTQ, c->s_lastq.p, (int64_t)cs * niso) == 0, TB_ERR_STATE,
+                     "exchange callback failed (carried Doppler index)");
+        else TB_TRY(tb_comm_allreduce_max(c, TB_EXCH_LASTQ, c->s_lastq.p, (int64_t)cs * niso));
+      }
       tb_timer_end(c, "strength");
       k_fallback<<<nblk(cs * niso, 128), 128, 0, st>>>(
           cs, niso, c->s_lastq.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,

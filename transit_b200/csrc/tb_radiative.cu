@@ -167,11 +167,11 @@ __global__ void k_cia_widx(const double *__restrict__ twn, int ntw, double wn_i,
 
 // pass 2b (crosssec.c:417-419) + density scaling and positivity (crosssec.c:321-336), every
 // table in file order; ecs[layer][wn]
-__global__ void k_cia_eval(CiaPack P, int nrad, double wn_i, double wn_d, double wn_fct, int64_t nwn,
-                           double *__restrict__ ecs) {
-  const int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+__global__ void k_cia_eval(CiaPack P, int nrad, double wn_i, double wn_d, double wn_fct, int64_t nwn, int64_t w0,
+                           int64_t w1, double *__restrict__ ecs) {
+  const int64_t w = w0 + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;      // columns [w0, w1): the band of a shard
   const int j = blockIdx.y;
-  if (w >= nwn) return;
+  if (w >= w1) return;
   const double xout = wn_fct * __dadd_rn(wn_i, __dmul_rn((double)w, wn_d));
   double acc = 0.0;
   for (int n = 0; n < P.n; n++) {
@@ -358,9 +358,13 @@ int tb_cia_run(tb_ctx *c) {
     k_cia_wnspline<<<dim3(nblk(maxlayers, 4), k), 128, 0, st>>>(S);
     c->launches += 2;
   }
-  dim3 g(nblk(nwn, 256), nrad);
-  k_cia_eval<<<g, 256, 0, st>>>(P, nrad, c->wn_i, c->wn_d, c->wn_fct, nwn, c->d_ecs.p);
-  TB_LAUNCHED(c);
+  int64_t w0, w1;
+  tb_band_columns(c, &w0, &w1);
+  if (w1 > w0) {
+    dim3 g(nblk(w1 - w0, 256), nrad);
+    k_cia_eval<<<g, 256, 0, st>>>(P, nrad, c->wn_i, c->wn_d, c->wn_fct, nwn, w0, w1, c->d_ecs.p);
+    TB_LAUNCHED(c);
+  }
   tb_timer_end(c, "cia");
   TB_CUDA(cudaGetLastError());
   c->have_ecs = true;
@@ -485,7 +489,7 @@ __global__ void k_ray_geometry(int eclipse, const double *__restrict__ rad, int 
 
 struct TauPar {
   int eclipse, nrad, nh, stride;
-  int64_t nwn;
+  int64_t nwn, w0, w1;                 // columns [w0, w1) are computed (the band of a shard, else the grid)
   double rfct, toomuch, wn_i, wn_d, wn_fct;
   int sc_flag, cl_flag;
   double sc_fac;                       // pow(10, logext) * E0H2
@@ -535,8 +539,8 @@ k_tau_transit(TauPar P, const double *__restrict__ e, const double *__restrict__
   extern __shared__ double sm[];
   __shared__ int sh_last[32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t w = blockIdx.x * 32LL + lane;
-  const bool inb = w < P.nwn;
+  const int64_t w = P.w0 + blockIdx.x * 32LL + lane;
+  const bool inb = w < P.w1;
   const int nrad = P.nrad;
   if (warp == 0) sh_last[lane] = P.nh;
   if (inb) {
@@ -773,8 +777,8 @@ k_tau_eclipse(TauPar P, const double *__restrict__ e, const double *__restrict__
   for (int i = threadIdx.x; i < P.nh * (int)(sizeof(EclRay) / 8); i += blockDim.x)
     reinterpret_cast<double *>(sr)[i] = reinterpret_cast<const double *>(rays)[i];
   __syncthreads();
-  const int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (w >= P.nwn) return;
+  const int64_t w = P.w0 + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (w >= P.w1) return;
   const int nrad = P.nrad;
   const double wn = P.wn_fct * __dadd_rn(P.wn_i, __dmul_rn((double)w, P.wn_d));
   double kBP = 0, kFH = 0, refw = 1;
@@ -880,18 +884,22 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
                                               hfct, stride, c->r_meta.p, c->r_par.p, c->r_coef.p, d_s.p, c->r_rcp.p, c->d_err.p);
   TauPar P;
   P.eclipse = geometry == TB_GEOM_ECLIPSE; P.nrad = nrad; P.nh = nh; P.stride = stride; P.nwn = nwn;
+  tb_band_columns(c, &P.w0, &P.w1);
+  const int64_t ncol = P.w1 - P.w0;
   P.rfct = c->rad_fct; P.toomuch = toomuch; P.wn_i = c->wn_i; P.wn_d = c->wn_d; P.wn_fct = c->wn_fct;
   P.sc_flag = c->sc_flag; P.cl_flag = c->cl_flag;
   P.sc_fac = pow(10.0, c->sc_logext) * TB_E0H2;
   P.cl_ext = c->cl_ext; P.cl_top = c->cl_top; P.cl_bot = c->cl_bot; P.cl_gamma = c->cl_gamma;
   P.cl_Q = c->cl_Q; P.cl_r = c->cl_r; P.cl_sig = c->cl_sig; P.cl_refwn = c->cl_refwn;
   tb_timer_begin(c, "tau");
-  if (geometry == TB_GEOM_ECLIPSE && c->tau_stream_ecl && nh == nrad && nrad >= 3 &&
-      (size_t)nh * sizeof(EclRay) <= 48 * 1024) {
+  if (ncol <= 0) {
+    // an empty band: nothing to integrate
+  } else if (geometry == TB_GEOM_ECLIPSE && c->tau_stream_ecl && nh == nrad && nrad >= 3 &&
+             (size_t)nh * sizeof(EclRay) <= 48 * 1024) {
     TB_TRY(c->r_ecl.ensure((size_t)nh * sizeof(EclRay)));
     k_ecl_rays<<<nblk(nh, 128), 128, 0, st>>>(nh, nrad, stride, c->r_meta.p, c->r_par.p, c->r_coef.p, c->r_rcp.p,
                                               reinterpret_cast<EclRay *>(c->r_ecl.p), c->d_err.p);
-    k_tau_eclipse<<<nblk(nwn, 128), 128, (size_t)nh * sizeof(EclRay), st>>>(
+    k_tau_eclipse<<<nblk(ncol, 128), 128, (size_t)nh * sizeof(EclRay), st>>>(
         P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p, c->d_dens.p, c->d_mol_pol.p, c->d_mol_mass.p,
         c->nmol, reinterpret_cast<const EclRay *>(c->r_ecl.p), c->d_tau.p, c->d_last.p);
     TB_LAUNCHED(c);
@@ -903,7 +911,7 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
       TB_CUDA(cudaFuncSetAttribute(k_tau_transit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
       c->tau_shm_set = (int)shm;
     }
-    k_tau_transit<<<nblk(nwn, 32), 32 * TAU_NW, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p,
+    k_tau_transit<<<nblk(ncol, 32), 32 * TAU_NW, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p,
                                                           c->d_dens.p, c->d_mol_pol.p, c->d_mol_mass.p, c->nmol,
                                                           c->r_meta.p, c->r_par.p, c->r_coef.p, c->r_rcp.p, c->d_tau.p,
                                                           c->d_last.p);
@@ -943,7 +951,7 @@ extern "C" int tb_tau(tb_ctx *c, int geometry, double toomuch, const double *h, 
 // =============================================================== modulation (a14)
 
 #define MOD_QL 4   // lanes per wavenumber in k_modulation
-__global__ void k_modulation(int64_t nwn, int nh, const double *__restrict__ tau,
+__global__ void k_modulation(int64_t nwn, int64_t w0, int64_t w1, int nh, const double *__restrict__ tau,
                              const int32_t *__restrict__ last, const double *__restrict__ ip, double ipfct,
                              double toomuch, double srad, int transp, double *__restrict__ out,
                              int32_t *__restrict__ err) {
@@ -968,10 +976,10 @@ __global__ void k_modulation(int64_t nwn, int nh, const double *__restrict__ tau
   // MOD_QL lanes share a wavenumber: each integrates a contiguous quarter of the pairs (a dependent
   // exp-and-add chain of ~50 pairs per wavenumber left the machine at 10 % occupancy with one lane
   // each); the partial sums are added in a fixed butterfly, lane 0 of the quad finishes.
-  const int64_t wq = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / MOD_QL;
+  const int64_t wq = w0 + (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / MOD_QL;   // columns [w0, w1)
   const int ql = threadIdx.x & (MOD_QL - 1);
-  const bool inb = wq < nwn;
-  const int64_t w = inb ? wq : nwn - 1;
+  const bool inb = wq < w1;
+  const int64_t w = inb ? wq : w1 - 1;
   const int L0 = last[w];
   int L1 = L0 + 1;
   if (L1 > nh - 1) L1 = nh - 1;
@@ -1014,11 +1022,11 @@ __global__ void k_modulation(int64_t nwn, int nh, const double *__restrict__ tau
 // modulationm1 (slantpath.c:446-473, `modlevel -1`): the planet as an opaque disc whose radius is where
 // tau reaches toomuch, by a line through the two rays around the cut-off (interp_line, pu numerical.c:200-210).
 // A wavenumber whose tau never reached toomuch is the reference's error -1 (slantpath.c:308-316).
-__global__ void k_modulation_m1(int64_t nwn, int nh, const double *__restrict__ tau,
+__global__ void k_modulation_m1(int64_t nwn, int64_t w0, int64_t w1, int nh, const double *__restrict__ tau,
                                 const int32_t *__restrict__ last, const double *__restrict__ ip, double ipfct,
                                 double toomuch, double srad, double *__restrict__ out, int32_t *__restrict__ err) {
-  const int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (w >= nwn) return;
+  const int64_t w = w0 + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (w >= w1) return;
   const int L = last[w];
   if (tau[(size_t)L * nwn + w] < toomuch) { atomicExch(err + 3, 1); out[w] = -1; return; }
   const int ini = L - 1 < 0 ? 0 : L - 1;
@@ -1048,14 +1056,19 @@ extern "C" int tb_modulation(tb_ctx *c, double starrad_cm, int transparent, doub
   tb_timer_begin(c, "modulation");
   const size_t shm = (5 * (size_t)c->nh + 2) * sizeof(double);   // xs[nh] (padded to even) + cf[4*nh]
   TB_REQUIRE(shm <= 48 * 1024, TB_ERR_ARG, "too many rays (%d) for the modulation kernel's shared memory", c->nh);
-  if (c->modlevel == -1)
-    k_modulation_m1<<<nblk(c->nwn, 128), 128, 0, st>>>(c->nwn, c->nh, c->d_tau.p, c->d_last.p, d_ip.p, c->hfct, c->toomuch,
-                                                       starrad_cm, c->d_out.p, c->d_err.p);
+  int64_t w0, w1;
+  tb_band_columns(c, &w0, &w1);
+  if (w1 <= w0) {
+    // an empty band
+  } else if (c->modlevel == -1)
+    k_modulation_m1<<<nblk(w1 - w0, 128), 128, 0, st>>>(c->nwn, w0, w1, c->nh, c->d_tau.p, c->d_last.p, d_ip.p, c->hfct,
+                                                        c->toomuch, starrad_cm, c->d_out.p, c->d_err.p);
   else
-    k_modulation<<<nblk(c->nwn * MOD_QL, 128), 128, shm, st>>>(c->nwn, c->nh, c->d_tau.p, c->d_last.p, d_ip.p, c->hfct, c->toomuch,
-                                                  starrad_cm, transparent, c->d_out.p, c->d_err.p);
+    k_modulation<<<nblk((w1 - w0) * MOD_QL, 128), 128, shm, st>>>(c->nwn, w0, w1, c->nh, c->d_tau.p, c->d_last.p, d_ip.p, c->hfct,
+                                                  c->toomuch, starrad_cm, transparent, c->d_out.p, c->d_err.p);
   tb_timer_end(c, "modulation");
   TB_LAUNCHED(c);
+  TB_TRY(tb_comm_gather_spectrum(c));         // band shard: every rank gets the whole spectrum (NCCL all-gather)
   if (out) TB_CUDA(cudaMemcpyAsync(out, c->d_out.p, c->nwn * sizeof(double), cudaMemcpyDeviceToHost, st));
   return tb_check_errors(c);
 }
@@ -1068,7 +1081,7 @@ extern "C" int tb_modulation(tb_ctx *c, double starrad_cm, int transparent, doub
 // machine); the trapezoid partial sums are added in a fixed butterfly, the lane holding the last
 // layer finishes.  QL = 1 is the plain loop (large grids: enough wavenumbers to fill the machine).
 template <int QL>
-__global__ void k_intensity_flux(int64_t nwn, int nrad, const double *__restrict__ tau,
+__global__ void k_intensity_flux(int64_t nwn, int64_t w0, int64_t w1, int nrad, const double *__restrict__ tau,
                                  const int32_t *__restrict__ last, const double *__restrict__ temp,
                                  double wn_i, double wn_d, double wn_fct, int nang,
                                  const double *__restrict__ ang, const double *__restrict__ area,
@@ -1081,10 +1094,10 @@ __global__ void k_intensity_flux(int64_t nwn, int nrad, const double *__restrict
     srkt[i] = 1.0 / kt;
   }
   __syncthreads();
-  const int64_t wq = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / QL;
+  const int64_t wq = w0 + (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / QL;        // columns [w0, w1)
   const int ql = threadIdx.x & (QL - 1);
-  const bool inb = wq < nwn;
-  const int64_t w = inb ? wq : nwn - 1;
+  const bool inb = wq < w1;
+  const int64_t w = inb ? wq : w1 - 1;
   const int L = last[w];
   const double wv = __dadd_rn(wn_i, __dmul_rn((double)w, wn_d));   // wns.v[w]
   const double ww = wv * wn_fct;
@@ -1142,17 +1155,22 @@ extern "C" int tb_intensity_flux(tb_ctx *c, const double *angles_deg, int nang, 
   TB_TRY(c->d_out.ensure(c->nwn));
   TB_TRY(tb_upload_small(c, d_a.p, ang.data(), nang * sizeof(double), st));
   TB_TRY(tb_upload_small(c, d_a.p + nang, area.data(), nang * sizeof(double), st));
+  int64_t w0, w1;
+  tb_band_columns(c, &w0, &w1);
   tb_timer_begin(c, "intensity");
-  if (c->nwn < 100000)
-    k_intensity_flux<8><<<nblk(c->nwn * 8, 128), 128, 2 * (size_t)c->nrad * sizeof(double), st>>>(c->nwn, c->nrad, c->d_tau.p, c->d_last.p, c->d_t.p, c->wn_i,
+  if (w1 <= w0) {
+    // an empty band
+  } else if (c->nwn < 100000)
+    k_intensity_flux<8><<<nblk((w1 - w0) * 8, 128), 128, 2 * (size_t)c->nrad * sizeof(double), st>>>(c->nwn, w0, w1, c->nrad, c->d_tau.p, c->d_last.p, c->d_t.p, c->wn_i,
                                                             c->wn_d, c->wn_fct, nang, d_a.p, d_a.p + nang, c->d_intens.p,
                                                             c->d_out.p);
   else
-    k_intensity_flux<1><<<nblk(c->nwn, 128), 128, 2 * (size_t)c->nrad * sizeof(double), st>>>(c->nwn, c->nrad, c->d_tau.p, c->d_last.p, c->d_t.p, c->wn_i,
+    k_intensity_flux<1><<<nblk(w1 - w0, 128), 128, 2 * (size_t)c->nrad * sizeof(double), st>>>(c->nwn, w0, w1, c->nrad, c->d_tau.p, c->d_last.p, c->d_t.p, c->wn_i,
                                                         c->wn_d, c->wn_fct, nang, d_a.p, d_a.p + nang, c->d_intens.p,
                                                         c->d_out.p);
   tb_timer_end(c, "intensity");
   TB_LAUNCHED(c);
+  TB_TRY(tb_comm_gather_spectrum(c));         // band shard: every rank gets the whole flux spectrum
   if (out) TB_CUDA(cudaMemcpyAsync(out, c->d_out.p, c->nwn * sizeof(double), cudaMemcpyDeviceToHost, st));
   c->nang = nang;
   return tb_check_errors(c);

@@ -186,16 +186,43 @@ def gather_bands(local, bands, rank: int, world: int, group=None):
     return st["out"].reshape(-1).index_select(0, st["idx"]).reshape(*lead, nwn)
 
 
+def broadcast_comm_id(rank, world, group=None):
+    """The 128-byte id of the library's own NCCL communicator (tb_comm_unique_id), made by rank 0 and handed to the
+    other ranks through torch.distributed (any backend: it is a host-side byte string)."""
+    import torch.distributed as dist
+    box = [api.Context.comm_unique_id() if rank == 0 else None]
+    if world > 1:
+        dist.broadcast_object_list(box, src=0, group=group)
+    return box[0]
+
+
 class BandShardedTransit(ShardedTransit):
-    """One spectrum computed by `world` ranks, each owning a wavenumber band."""
+    """One spectrum computed by `world` ranks, each owning a wavenumber band.  The exchange lives in the library
+    (tb_comm_init / tb_set_bands: two exact ncclAllReduce(MAX) inside the line sum and one ncclAllGather of the
+    band slices at the end of tb_spectrum, all on the context's stream): every rank's do_transit returns the
+    whole spectrum.  ``exchange="callback"`` keeps the older route -- a host callback into torch.distributed for
+    the two maxima and a torch all-gather of the slices -- for comparison and for the gloo tests."""
+
+    def __init__(self, device=0, rank=0, world=1, exchange="library"):
+        super().__init__(device, rank, world)
+        self.exchange = exchange
 
     def transit_init(self, prob, **kw):
         super().transit_init(prob, **kw)
-        self.bands = wavenumber_bands(line_weights(prob), self.world)
-        lo, hi = self.bands[self.rank]
-        self.ctx.set_shard(lo, hi, self.rank, self.world, nccl_exchange() if self.world > 1 else None)
+        if self.exchange == "library":
+            if self.world > 1:
+                self.ctx.comm_init(self.rank, self.world, broadcast_comm_id(self.rank, self.world))
+            edges = self.ctx.balanced_bands(self.world)
+            self.bands = [(int(edges[r]), int(edges[r + 1])) for r in range(self.world)]
+            self.ctx.set_bands(edges, self.rank)
+        else:
+            self.bands = wavenumber_bands(line_weights(prob), self.world)
+            lo, hi = self.bands[self.rank]
+            self.ctx.set_shard(lo, hi, self.rank, self.world, nccl_exchange() if self.world > 1 else None)
 
     def do_transit_gathered(self):
         """Spectrum [nwn] on every rank as a CUDA tensor: own band computed here, the rest gathered."""
         self.do_transit(None)
+        if self.exchange == "library":
+            return self.device_spectrum_tensor()
         return gather_bands(self.device_spectrum_tensor(), self.bands, self.rank, self.world)
