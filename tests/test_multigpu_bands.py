@@ -49,7 +49,7 @@ def test_c_host_on_two_gpus_writes_the_same_files(tmp_path):
     for g in (1, 2):
         opa = tmp_path / f"grid{g}.opa"
         env = dict(os.environ, TRANSIT_B200_GPUS=str(g))
-        r = subprocess.run([HOST, "-c", cfg, "--opacityfile", str(opa), "--tlow", "700", "--thigh", "1100", "--tempdelt",
+        r = subprocess.run([HOST, "-c", cfg, "--opacityfile", str(opa), "--tlow", "600", "--thigh", "1200", "--tempdelt",
                             "100", "--outspec", str(tmp_path / f"gs{g}.dat")], capture_output=True, text=True, env=env, timeout=600)
         assert r.returncode == 0, r.stderr[-2000:]
         grids[g] = open(opa, "rb").read()
