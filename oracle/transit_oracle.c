@@ -648,6 +648,27 @@ double to_modulation1(const double *tau, long last, double toomuch, const double
   return res;
 }
 
+/* modulationm1, slantpath.c:446-473 (interp_line: pu/src/numerical.c:200-210): the planet as an opaque disc
+ * whose radius is where tau reaches toomuch.  Returns -1 if toomuch was not reached (slantpath.c:308-316).
+ * When the first ray is already opaque the reference leaves ipv[1] unset; zero stands in for it here. */
+double to_modulationm1(const double *tau, long last, double toomuch, const double *ip,
+                       long ipn, double ipfct, double srad){
+  long i, ini;
+  double ipv[2] = {0.0, 0.0};
+  (void)ipn;
+  if(tau[last] < toomuch) return -1;
+  ini = ++last - 2;
+  if(ini < 0) ini = 0;
+  for(i=ini; i<last; i++) ipv[i-ini] = ip[i]*ipfct;
+  {
+    const double *x = tau + ini;
+    const double dx = x[1] - x[0];
+    const double m = (ipv[1] - ipv[0]) / dx;
+    const double muchrad = ipv[0] + (toomuch - x[0]) * m;
+    return muchrad*muchrad/(srad*srad);
+  }
+}
+
 /* eclipse.c:117-160 (+ integ_trapz numerical.c:154-172) */
 double to_eclipse_intens(const double *tau, double w, double wfct, long last,
                          const double *temp, long rnn, double angle_deg){

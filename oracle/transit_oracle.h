@@ -105,6 +105,8 @@ int to_tau(int eclipse, const double *e, const double *e_cs, const double *wn,
            double *t, int64_t *last, int16_t *computed);
 
 /* slantpath.c:350-436 */
+double to_modulationm1(const double *tau, long last, double toomuch, const double *ipv,
+                       long ipn, double ipfct, double srad);
 double to_modulation1(const double *tau, long last, double toomuch, const double *ipv,
                       long ipn, double ipfct, double srad, int transp);
 /* eclipse.c:117-160 */

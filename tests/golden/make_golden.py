@@ -14,6 +14,7 @@ CUDA path.  Fixtures store float64 arrays exactly (np.savez_compressed is lossle
 """
 from __future__ import annotations
 
+import json
 import os
 import struct
 import subprocess
@@ -157,10 +158,70 @@ def case_tiny_grid(tmp):
                                 opa="grid.opa"))
 
 
+CLOUD_VARIANTS = {
+    # name -> extra reference CLI arguments (argum.c:636-715: --cloud type,ext,top,bot[,gamma[,Q,r | sig,refwn]];
+    # --scattering <log ext> | polar; --cloudtop <log bar>)
+    "none": [],
+    "sc1": ["--scattering", "0.5"],
+    "sc2": ["--scattering", "polar"],
+    "cl1": ["--cloud", "ext,3e-9,-4.0,-1.0"],
+    "cl2": ["--cloud", "opa,2e-3,-4.0,-1.0"],
+    "cl3": ["--cloud", "B17,4e-19,-4.0,-1.0,4.0"],
+    "cl4": ["--cloud", "F18,2e-3,-4.0,-1.0,4.0,40.0,1e-4"],
+    "cl5": ["--cloud", "P19,1e5,-4.0,-1.0,4.0,1e-27,2857.0"],
+    "cloudtop": ["--cloudtop", "-2.5"],
+    "sc1_cl2": ["--scattering", "0.5", "--cloud", "opa,2e-3,-4.0,-1.0"],
+    "transparent": ["--transparent"],
+    "modm1": ["--modlevel", "-1", "--toomuch", "1.0"],
+}
+
+
+def make_tiny_cloud():
+    """a10 / a14 fixtures: ONE small transit problem through the unmodified reference once per scattering / cloud /
+    modulation variant (computeextscat, computeextcloud, set_cloudtop's fields, --transparent, modlevel -1);
+    the static inputs are kept once, tau / last / spectrum per variant."""
+    with tempfile.TemporaryDirectory() as tmp:
+        _common(tmp, 1010, 4000.0, 4080.0, 1500, 24,
+                {"H2O": (3, 0.6), "CO2": (3, 0.4)},
+                {"H2": 0.85, "He": 0.1485, "H2O": 9e-4, "CO2": 6e-4}, p_top_bar=1e-6, p_bot_bar=1e1)
+        wn = np.arange(20.0, 6000.1, 20.0)
+        temps = np.array([200., 400., 600., 800., 1000., 1500., 2000., 3000.])
+        synth.write_cia(os.path.join(tmp, "cia_h2h2.dat"), "H2", "H2", wn, temps, 1e-7, 1)
+        cfg = dict(atm="atm.dat", linedb="lines.tli", molfile=f"{REF_INPUTS}/molecules.dat", csfile="cia_h2h2.dat",
+                   wnlow=4000.0, wnhigh=4080.0, wndelt=1.0, wnosamp=120, wnfct=1.0, wlfct=1e-4,
+                   solution="transit", toomuch=10, ethreshold=1e-8, starrad=0.75,
+                   nwidth=20, ndop=10, nlor=12, verb=0, outspec="spec.dat")
+        cfgp = os.path.join(tmp, "case.cfg")
+        synth.write_cfg(cfgp, **cfg)
+        out = {}
+        for name, extra in CLOUD_VARIANTS.items():
+            outp = os.path.join(tmp, f"dump_{name}.bin")
+            subprocess.run([REF_DUMP, outp] + (["--full-ext"] if name == "none" else []) + ["--", "-c", cfgp] + extra,
+                           cwd=tmp, check=True, stdout=subprocess.DEVNULL)
+            d = read_container(outp)
+            if name == "none":
+                out.update({k: v for k, v in d.items() if not k.startswith(("prof_", "profsize"))})
+            for k in ("tau", "last", "out", "computed"):
+                out[f"{name}__{k}"] = d[k]
+            for k in ("sc_flag", "sc_logext", "cl_flag", "cl_ext", "cl_top", "cl_bot", "cl_gamma", "cl_Q", "cl_r", "cl_sig",
+                      "cl_refwn", "transpplanet", "toomuch"):
+                out[f"{name}__{k}"] = d[k]
+        out["cfg_text"] = np.frombuffer(open(cfgp, "rb").read(), np.uint8)
+        out["variants"] = np.frombuffer(json.dumps(CLOUD_VARIANTS).encode(), np.uint8)
+        for key, fn in dict(tli="lines.tli", atm="atm.dat", cia0="cia_h2h2.dat").items():
+            out["file_" + key] = np.frombuffer(open(os.path.join(tmp, fn), "rb").read(), np.uint8)
+    path = os.path.join(HERE, "tiny_cloud.npz")
+    np.savez_compressed(path, **out)
+    print(f"tiny_cloud: {len(out)} arrays, {os.path.getsize(path) / 1024:.0f} KiB")
+
+
 CASES = dict(tiny_ecl=case_tiny_ecl, tiny_tra=case_tiny_tra, tiny_grid=case_tiny_grid)
 
 if __name__ == "__main__":
     if not os.path.exists(REF_DUMP):
         sys.exit("oracle/_ref/ref_dump missing: run `make -C oracle ref` first")
-    for nm in (sys.argv[1:] or CASES):
-        run_case(nm, CASES[nm])
+    for nm in (sys.argv[1:] or list(CASES) + ["tiny_cloud"]):
+        if nm == "tiny_cloud":
+            make_tiny_cloud()
+        else:
+            run_case(nm, CASES[nm])

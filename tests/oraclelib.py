@@ -91,6 +91,8 @@ def lib():
         L.to_totaltau1.argtypes = [C.c_double, f64p, C.c_double, f64p, C.c_long]
         L.to_eclipsetau.restype = C.c_double
         L.to_eclipsetau.argtypes = [C.c_double, f64p, f64p, C.c_long]
+        L.to_modulationm1.restype = C.c_double
+        L.to_modulationm1.argtypes = [f64p, C.c_long, C.c_double, f64p, C.c_long, C.c_double, C.c_double]
         L.to_modulation1.restype = C.c_double
         L.to_modulation1.argtypes = [f64p, C.c_long, C.c_double, f64p, C.c_long, C.c_double,
                                      C.c_double, C.c_int]
@@ -266,9 +268,23 @@ def interpcs(prob, temp=None, mol_d=None):
     return e_cs
 
 
+def cloud_aux(prob, mol_names):
+    """tau.c:194-214: mean_dens[r] = (sum_j d_j/m_j*q_j) * (sum_j m_j*q_j) and, for the species named "H2",
+    nH[r] = d/m*q*N_A (the reference accumulates mean_dens into an uninitialised stack array; from zero here)."""
+    NAVOGADRO = 6.02214076e23
+    md = np.zeros(prob.nrad); nH = np.zeros(prob.nrad); mm = np.zeros(prob.nrad)
+    for j, nm in enumerate(mol_names):
+        md = md + prob.mol_d[j] / prob.mol_mass[j] * prob.mol_q[j]
+        if nm == "H2":
+            nH = prob.mol_d[j] / prob.mol_mass[j] * prob.mol_q[j] * NAVOGADRO
+        mm = mm + prob.mol_mass[j] * prob.mol_q[j]
+    return nH, md * mm
+
+
 def contrib(prob, sc_flag=0, sc_logext=0.0, cl_flag=0, cl_ext=0.0, cl_top=0.0, cl_bot=0.0,
-            cl_gamma=0.0, cl_Q=0.0, cl_r=0.0, cl_sig=0.0, cl_refwn=0.0):
-    nH = np.zeros(prob.nrad); md = np.zeros(prob.nrad)
+            cl_gamma=0.0, cl_Q=0.0, cl_r=0.0, cl_sig=0.0, cl_refwn=0.0, nH=None, md=None):
+    nH = np.zeros(prob.nrad) if nH is None else c64(nH).copy()
+    md = np.zeros(prob.nrad) if md is None else c64(md).copy()
     cb = Contrib(sc_flag, sc_logext, cl_flag, cl_ext, cl_top, cl_bot, cl_gamma, cl_Q, cl_r,
                  cl_sig, cl_refwn, p(nH), p(md), prob.nmol, p(prob.mol_pol), p(prob.mol_d),
                  p(prob.mol_mass))
@@ -276,9 +292,10 @@ def contrib(prob, sc_flag=0, sc_logext=0.0, cl_flag=0, cl_ext=0.0, cl_top=0.0, c
     return cb
 
 
-def tau(prob, e, e_cs, cb=None, lazy=True, rad=None):
+def tau(prob, e, e_cs, cb=None, lazy=True, rad=None, toomuch=None):
     L = lib()
     cb = cb or contrib(prob)
+    toomuch = prob.toomuch if toomuch is None else toomuch
     rad = c64(prob.rad if rad is None else rad).copy()
     nrad = prob.nrad
     h = c64(rad[::-1])                       # makeipsample raddelt=-1 / tau.c:92-98
@@ -288,19 +305,24 @@ def tau(prob, e, e_cs, cb=None, lazy=True, rad=None):
     e = c64(e); e_cs = c64(e_cs)
     L.to_tau(int(prob.eclipse), p(e), p(e_cs), p(prob.wn), prob.nwn, prob.wn_fct, p(rad), nrad,
              prob.rad_fct, p(h), nh, prob.rad_fct, p(prob.p), p(prob.t), C.byref(cb),
-             prob.toomuch, int(lazy), p(t), p(last, i64p), p(comp, i16p))
+             toomuch, int(lazy), p(t), p(last, i64p), p(comp, i16p))
     return t, last, comp
 
 
-def modulation(prob, t, last, rad=None):
+def modulation(prob, t, last, rad=None, transp=None, modlevel=1, toomuch=None):
     L = lib()
     rad = prob.rad if rad is None else rad
     ip = c64(rad[::-1])
     out = np.zeros(prob.nwn)
+    transp = prob.transp if transp is None else transp
+    toomuch = prob.toomuch if toomuch is None else toomuch
     for w in range(prob.nwn):
         row = c64(t[w])
-        out[w] = L.to_modulation1(p(row), int(last[w]), prob.toomuch, p(ip), len(ip),
-                                  prob.rad_fct, prob.starrad, prob.transp)
+        if modlevel == -1:
+            out[w] = L.to_modulationm1(p(row), int(last[w]), toomuch, p(ip), len(ip), prob.rad_fct, prob.starrad)
+        else:
+            out[w] = L.to_modulation1(p(row), int(last[w]), toomuch, p(ip), len(ip),
+                                      prob.rad_fct, prob.starrad, int(transp))
     return out
 
 
@@ -358,3 +380,15 @@ def parse_tli(raw: bytes, wn_lo: float, wn_hi: float):
     sel = np.concatenate(sel)
     return dict(wl=c64(wl[sel]), elow=c64(el[sel]), gf=c64(gf[sel]),
                 isoid=np.ascontiguousarray(iso[sel], np.int16), wfct=1e-4, efct=1.0), dbs
+
+
+def cloud_variant(d, name):
+    """Parameters of one variant of tests/golden/tiny_cloud.npz as keyword arguments of contrib()."""
+    g = lambda k: d[f"{name}__{k}"].item()
+    return dict(sc_flag=int(g("sc_flag")), sc_logext=g("sc_logext"), cl_flag=int(g("cl_flag")), cl_ext=g("cl_ext"),
+                cl_top=g("cl_top"), cl_bot=g("cl_bot"), cl_gamma=g("cl_gamma"), cl_Q=g("cl_Q"), cl_r=g("cl_r"),
+                cl_sig=g("cl_sig"), cl_refwn=g("cl_refwn"))
+
+
+def golden_mol_names(d):
+    return d["mol_names"].tobytes().decode().strip("\x00").split()

@@ -2,6 +2,8 @@
 (a) the committed golden vectors produced by the UNMODIFIED reference and (b) the CPU
 oracle on seeded synthetic inputs.  Integer/index work is compared bit-exactly; extinction
 to 1e-10 relative and spectra to 1e-8 relative (BASELINE.json north_star)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -261,6 +263,66 @@ def test_scattering_and_cloud_vs_oracle(ctxs):
 
 
 # ------------------------------------------------------------------ opacity grid (a6-a8)
+
+def test_scattering_cloud_modulation_variants_vs_reference(golden, tmp_path):
+    """a10 / a14 against the UNMODIFIED reference (tests/golden/tiny_cloud.npz): Rayleigh flags 1 and 2, cloud models
+    1-5, the --cloudtop deck (set_cloudtop), --transparent and modlevel -1, each through the library interface
+    (Transit.set_scattering / set_cloud / set_cloudtop) AND through the C host's command line."""
+    import json
+    import subprocess
+    d = golden("tiny_cloud")
+    prob = O.Problem.from_golden(d)
+    prob.species_names = O.golden_mol_names(d)
+    cfg = cfg_of(d)
+    variants = json.loads(bytes(d["variants"]).decode())
+    # the same inputs as files for the C host (the fixture carries them)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for key, fn in (("tli", "lines.tli"), ("atm", "atm.dat"), ("cia0", "cia_h2h2.dat")):
+        open(tmp_path / fn, "wb").write(bytes(d["file_" + key]))
+    txt = bytes(d["cfg_text"]).decode().replace("/root/reference/inputs/molecules.dat",
+                                                os.path.join(root, "oracle", "_ref", "inputs", "molecules.dat"))
+    open(tmp_path / "case.cfg", "w").write(txt)
+    host = os.path.join(root, "host", "transit_b200")
+    have_host = os.path.exists(host) and os.path.exists(os.path.join(root, "oracle", "_ref", "inputs", "molecules.dat"))
+    tr = api.Transit(0)
+    tr.ctx.set_fused(2)
+    tr.transit_init(prob, int(cfg["ndop"]), int(cfg["nlor"]))
+    worst = {}
+    for name, extra in variants.items():
+        kw = O.cloud_variant(d, name)
+        p2 = type(prob)(**vars(prob))
+        p2.toomuch = d[f"{name}__toomuch"].item()
+        p2.transp = int(d[f"{name}__transpplanet"].item())
+        p2.starrad = prob.starrad
+        tr.prob = p2
+        tr.set_scattering(kw["sc_flag"], kw["sc_logext"])
+        if name == "cloudtop":
+            tr.set_cloudtop(kw["cl_top"])                 # BART's entry (transit.c:103-109)
+        else:
+            tr.set_cloud(kw["cl_flag"], kw["cl_ext"], kw["cl_top"], kw["cl_bot"], kw["cl_gamma"], kw["cl_Q"], kw["cl_r"],
+                         kw["cl_sig"], kw["cl_refwn"])
+        tr.ctx.set_modlevel(-1 if name == "modm1" else 1)
+        out = tr.do_transit()
+        t, last = tr.ctx.get_tau()
+        assert np.array_equal(last, d[f"{name}__last"]), name
+        assert np.array_equal(tr.ctx.get_computed(), d[f"{name}__computed"]), name
+        assert np.array_equal(t == 0, d[f"{name}__tau"] == 0), name
+        nz = d[f"{name}__tau"] != 0
+        assert relerr(t[nz], d[f"{name}__tau"][nz]) < 1e-9, name
+        worst[name] = relerr(out, d[f"{name}__out"])
+        assert worst[name] < SPEC_RTOL, (name, worst[name])
+        if have_host:
+            spec = tmp_path / f"spec_{name}.dat"
+            r = subprocess.run([host, "-c", str(tmp_path / "case.cfg"), "--outspec", str(spec)] + list(extra),
+                               capture_output=True, text=True, cwd=str(tmp_path))
+            assert r.returncode == 0, (name, r.stderr[-800:])
+            a = np.loadtxt(spec, comments="#")
+            want = np.array([float(f"{v:.9g}") for v in d[f"{name}__out"]])     # the file carries 9 digits
+            assert np.max(np.abs(a[:, 1] - want) / np.abs(want)) < 1e-8, name
+    tr.ctx.set_modlevel(1)
+    tr.free_memory()
+    print("\n[parity a10/a14 variants] worst spectrum rel:", json.dumps(worst))
+
 
 def test_opacity_grid_build_and_interp_vs_reference(golden):
     d = golden("tiny_grid")

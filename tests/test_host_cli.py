@@ -125,6 +125,104 @@ def test_library_interface_run_transit_matches_reference(tmp_path):
     assert np.max(np.abs(outs[0][1] - outs[1][1]) / np.abs(outs[1][1])) < 1e-8
 
 
+def _golden_files(tmp_path, case):
+    """Input files a golden fixture carries + its cfg with the molecules file repointed to the shipped copy."""
+    d = np.load(os.path.join(ROOT, "tests", "golden", case + ".npz"))
+    names = {"tli": "lines.tli", "atm": "atm.dat", "cia0": "cia_h2h2.dat", "cia1": "cia_h2he.dat", "opa": "ref.opa"}
+    for k in d.files:
+        if k.startswith("file_"):
+            open(tmp_path / names[k[5:]], "wb").write(bytes(d[k]))
+    txt = bytes(d["cfg_text"]).decode().replace("/root/reference/inputs/", os.path.join(ROOT, "oracle", "_ref", "inputs") + "/")
+    return d, txt
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "inputs", "molecules.dat")),
+                    reason="oracle/_ref/inputs not built")
+def test_opacity_file_face_across_implementations(tmp_path):
+    """a6 / a7 as FILES (opacity.c:405-423 writer, :432-503 reader): (1) the host builds a grid with --opacityfile
+    and its file has the reference file's header byte for byte and its grid within 1e-10; (2) the host reads the file
+    the REFERENCE wrote (tests/golden/tiny_grid.npz:file_opa) and reproduces the reference's spectrum; (3) the
+    unmodified reference binary reads the file the HOST wrote and prints the spectrum it prints from its own file."""
+    _build()
+    d, txt = _golden_files(tmp_path, "tiny_grid")
+    base = "".join(l + "\n" for l in txt.splitlines() if not l.startswith(("opacityfile", "outspec")))
+    def run(binary, opa, spec, extra=()):
+        cfg = tmp_path / f"c_{os.path.basename(spec)}.cfg"
+        cfg.write_text(base + f"opacityfile {opa}\noutspec {spec}\n")
+        r = subprocess.run([binary, "-c", str(cfg)] + list(extra), capture_output=True, text=True, cwd=str(tmp_path))
+        assert r.returncode == 0, (binary, r.stdout[-1500:], r.stderr[-1500:])
+    # (1) build with the host
+    run(HOST, tmp_path / "ours.opa", tmp_path / "s_build.dat")
+    ref_b, our_b = open(tmp_path / "ref.opa", "rb").read(), open(tmp_path / "ours.opa", "rb").read()
+    assert len(ref_b) == len(our_b)
+    Nmol, Nt, Nl, Nw = np.frombuffer(ref_b[:32], "<i8")
+    hdr = 32 + 4 * Nmol + 8 * (Nt + Nl + Nw)
+    assert ref_b[:hdr] == our_b[:hdr], "opacity file header (sizes, molID, temperatures, pressures, wavenumbers) differs"
+    g_ref, g_our = np.frombuffer(ref_b[hdr:], "<f8"), np.frombuffer(our_b[hdr:], "<f8")
+    assert g_ref.size == Nmol * Nt * Nl * Nw and np.array_equal(g_ref == 0, g_our == 0)
+    nz = g_ref != 0
+    assert np.max(np.abs(g_our[nz] - g_ref[nz]) / np.abs(g_ref[nz])) < 1e-10
+    # (2) the host on the reference's file
+    run(HOST, tmp_path / "ref.opa", tmp_path / "s_ours_on_ref.dat")
+    a = _read_spec(str(tmp_path / "s_ours_on_ref.dat"))
+    want = np.array([float(f"{v:.9g}") for v in d["out"]])
+    assert a.shape[0] == want.size and np.max(np.abs(a[:, 1] - want) / np.abs(want)) < 1e-8
+    # (3) the reference on the host's file, against the reference on its own file
+    run(REF, tmp_path / "ours.opa", tmp_path / "s_ref_on_ours.dat")
+    run(REF, tmp_path / "ref.opa", tmp_path / "s_ref_on_ref.dat")
+    b, c = _read_spec(str(tmp_path / "s_ref_on_ours.dat")), _read_spec(str(tmp_path / "s_ref_on_ref.dat"))
+    assert np.array_equal(b[:, 0], c[:, 0]) and np.max(np.abs(b[:, 1] - c[:, 1]) / np.abs(c[:, 1])) < 1e-8
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "inputs", "molecules.dat")),
+                    reason="oracle/_ref/inputs not built")
+@pytest.mark.parametrize("case", ["tiny_ecl", "tiny_tra"])
+def test_side_files_match_reference(tmp_path, case):
+    """a17: outtoomuch (printtoomuch, tau.c:611-640), outintens (printintens, eclipse.c:293-348), outsample with
+    `savefiles yes` (makesample.c:598,743-772) and saveext (extinction.c:62-91) as the host writes them, against the
+    files the unmodified reference writes from the same cfg: text files equal to the printed digits, the extinction
+    savefile's magic and computed[] exact and its values within 1e-10."""
+    _build()
+    d, txt = _golden_files(tmp_path, case)
+    base = "".join(l + "\n" for l in txt.splitlines() if not l.startswith("outspec"))
+    res = {}
+    for who, binary in (("ours", HOST), ("ref", REF)):
+        sub = tmp_path / who
+        sub.mkdir()
+        cfg = tmp_path / f"{who}.cfg"
+        cfg.write_text(base + f"outspec {sub}/spec.dat\nouttoomuch {sub}/toomuch.dat\noutsample {sub}/sample.dat\n"
+                              f"outintens {sub}/intens.dat\nsaveext {sub}/ext.sav\nsavefiles yes\n")
+        r = subprocess.run([binary, "-c", str(cfg)], capture_output=True, text=True, cwd=str(tmp_path))
+        assert r.returncode == 0, (who, r.stdout[-1500:], r.stderr[-1500:])
+        res[who] = sub
+    def numbers(path):
+        return [l.split() for l in open(path) if not l.startswith("#") and l.strip()]
+    # sampling file: identical text
+    assert open(res["ours"] / "sample.dat").read() == open(res["ref"] / "sample.dat").read()
+    # toomuch: same header, same radius index and radius, optical depth to its 6 printed digits
+    o, r = open(res["ours"] / "toomuch.dat").read().splitlines(), open(res["ref"] / "toomuch.dat").read().splitlines()
+    assert o[:2] == r[:2] and len(o) == len(r)
+    for lo, lr in zip(o[2:], r[2:]):
+        fo, fr = lo.split(), lr.split()
+        assert fo[0] == fr[0] and fo[2:] == fr[2:], (lo, lr)
+        assert abs(float(fo[1]) - float(fr[1])) <= 2e-5 * abs(float(fr[1])), (lo, lr)
+    # extinction savefile
+    bo, br = open(res["ours"] / "ext.sav", "rb").read(), open(res["ref"] / "ext.sav", "rb").read()
+    assert len(bo) == len(br) and bo[:5] == br[:5] == b"@E@S@"
+    nrad, nwn = int(d["nrad"].item()), int(d["wns_n"].item())
+    eo, er = np.frombuffer(bo[5:5 + 8 * nrad * nwn], "<f8"), np.frombuffer(br[5:5 + 8 * nrad * nwn], "<f8")
+    assert bo[5 + 8 * nrad * nwn:] == br[5 + 8 * nrad * nwn:], "computed[] (shorts) differ"
+    assert np.array_equal(eo == 0, er == 0)
+    assert np.max(np.abs(eo[er != 0] - er[er != 0]) / np.abs(er[er != 0])) < 1e-10
+    if case == "tiny_ecl":      # intensities per angle: header lines identical, values to the printed digits
+        o, r = open(res["ours"] / "intens.dat").read().splitlines(), open(res["ref"] / "intens.dat").read().splitlines()
+        assert o[:2] == r[:2] and len(o) == len(r)
+        a, b = np.array([[float(x) for x in l.split()] for l in o[2:]]), np.array([[float(x) for x in l.split()] for l in r[2:]])
+        assert np.array_equal(a[:, 0], b[:, 0]) and np.max(np.abs(a[:, 1:] - b[:, 1:]) / np.abs(b[:, 1:])) < 1e-8
+
+
 def _read_dry(path):
     """The host's dry-run dump (th_api.c do_transit, TRANSIT_B200_DRYRUN): header of 8 doubles, then the
     sampled state in the order it is handed to the device."""

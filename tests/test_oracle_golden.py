@@ -124,3 +124,32 @@ def test_interpolmolext_spectrum_from_grid(golden):
     assert np.array_equal(comp2, d["computed"]) and np.array_equal(last, d["last"])
     assert relerr(t, d["tau"]) < 1e-9
     assert relerr(O.modulation(prob, t, last), d["out"]) < 1e-11
+
+
+def test_scattering_clouds_and_modulation_variants(golden):
+    """a10 / a14 pinned to the UNMODIFIED reference (tests/golden/tiny_cloud.npz: one problem through the reference
+    once per variant): computeextscat flags 1 and 2, computeextcloud models 1-5, the --cloudtop deck
+    (set_cloudtop's fields), --transparent and modlevel -1 -- tau, last[], the lazily evaluated layer set and the
+    spectrum of every variant."""
+    import json
+    d = golden("tiny_cloud")
+    prob = O.Problem.from_golden(d)
+    names = O.golden_mol_names(d)
+    assert names[:2] == ["H2", "He"]
+    nH, md = O.cloud_aux(prob, names)
+    variants = json.loads(bytes(d["variants"]).decode())
+    assert set(variants) >= {"sc1", "sc2", "cl1", "cl2", "cl3", "cl4", "cl5", "cloudtop", "transparent", "modm1"}
+    base_out = d["none__out"]
+    for name in variants:
+        kw = O.cloud_variant(d, name)
+        toomuch = d[f"{name}__toomuch"].item()
+        cb = O.contrib(prob, nH=nH, md=md, **kw)
+        t, last, comp = O.tau(prob, d["ext_full"], d["e_cs"], cb, lazy=True, toomuch=toomuch)
+        assert np.array_equal(last, d[f"{name}__last"]), name
+        assert np.array_equal(comp, d[f"{name}__computed"]), name
+        assert relerr(t, d[f"{name}__tau"]) < 1e-9, (name, relerr(t, d[f"{name}__tau"]))
+        out = O.modulation(prob, d[f"{name}__tau"], d[f"{name}__last"], transp=int(d[f"{name}__transpplanet"].item()),
+                           modlevel=-1 if name == "modm1" else 1, toomuch=toomuch)
+        assert relerr(out, d[f"{name}__out"]) < 1e-11, (name, relerr(out, d[f"{name}__out"]))
+        if name not in ("none",):
+            assert not np.array_equal(d[f"{name}__out"], base_out), f"variant {name} does not change the spectrum"

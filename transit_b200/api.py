@@ -508,6 +508,24 @@ class Transit:
     def set_scattering(self, flag, logext):
         self.ctx.set_scattering(flag, logext)
 
+    def cloud_aux(self):
+        """tau.c:194-214: per layer the H2 number density nH = d/m*q*N_A of the species NAMED "H2" and the mean
+        mass density (sum_j d_j/m_j*q_j)*(sum_j m_j*q_j), what cloud models 2-5 scale with."""
+        p = self.prob
+        names = list(getattr(p, "species_names", []))
+        md = np.zeros(p.nrad); nH = np.zeros(p.nrad); mm = np.zeros(p.nrad)
+        for j in range(p.nmol):
+            md = md + p.mol_d[j] / p.mol_mass[j] * p.mol_q[j]
+            if j < len(names) and names[j] == "H2":
+                nH = p.mol_d[j] / p.mol_mass[j] * p.mol_q[j] * 6.02214076e23
+            mm = mm + p.mol_mass[j] * p.mol_q[j]
+        return nH, md * mm
+
+    def set_cloud(self, flag, ext, top, bot, gamma=1.0, Q=1.0, r=1.0, sig=1.0, refwn=1.0):
+        """--cloud type,ext,top,bot[,gamma[,Q,r | sig,refwn]] (argum.c:636-715; extinction.c:629-693)."""
+        nH, md = self.cloud_aux()
+        self.ctx.set_cloud(flag, ext, top, bot, gamma, Q, r, sig, refwn, nH, md)
+
     def set_cloudtop(self, cloudtop):
         """transit.c:103-109: constant-extinction cloud deck between cloudtop and cloudtop+10 (log p)."""
         self.ctx.set_cloud(1, 100.0, cloudtop, cloudtop + 10)
