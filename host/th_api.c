@@ -122,6 +122,8 @@ void transit_init(int argc, char **argv) {
   if (h->modlevel != 1 && h->modlevel != -1)
     th_die("slantpath:: modulationperwn:: Level %i of detail has not been implemented to compute modulation.\n", h->modlevel);
   apply_cloud_scattering();
+  if (S.have_grid_file && h->p0 != 0 && h->r0 != 0 && h->gsurf != 0)      /* what run_transit_batch needs */
+    CK(tb_set_atmosphere_model(S.ctx, S.nlayer, S.p, S.p_fct, S.t_fct, S.rad_fct, S.bymass, h->p0, h->r0, h->gsurf));
   S.out = (double *)calloc(S.nwn, sizeof(double));
   S.initialised = 1;
 }
@@ -314,6 +316,20 @@ void run_transit(double *re_input, int transint, double *transit_out, int transi
   th_make_rad(&S);
   apply_cloud_scattering();
   do_transit(transit_out);
+}
+
+/* run_transit for natm atmospheres at once: re_input[natm][nlayers*(1+nmol)], transit_out[natm][nwn].  From a
+ * resident opacity grid in transit geometry the whole batch goes through the device in one pass (reloadatm's
+ * densities and hydrostatic radii included, tb_run_transit_batch); any other configuration is a loop of
+ * run_transit.  An extension of the reference's interface (it has no batched call), same input layout. */
+void run_transit_batch(double *re_input, int natm, double *transit_out) {
+  const int nin = S.nlayer * (1 + S.nmol);
+  if (!S.initialised) { printf("Transit init not run, please initialize transit.\n"); return; }
+  if (S.have_grid_file && !S.eclipse && S.h.modlevel == 1 && S.h.p0 != 0 && S.h.r0 != 0 && S.h.gsurf != 0 && th_world == 1) {
+    CK(tb_run_transit_batch(S.ctx, natm, re_input, S.h.toomuch, S.h.starrad * TH_SUNRADIUS, S.h.transparent, transit_out));
+    return;
+  }
+  for (int a = 0; a < natm; a++) run_transit(re_input + (size_t)a * nin, nin, transit_out + (size_t)a * S.nwn, (int)S.nwn);
 }
 
 void free_memory(void) {

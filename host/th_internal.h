@@ -121,6 +121,7 @@ void set_cloudtop(double cloudtop);
 void set_scattering(int flag, double scattering);
 void run_transit(double *re_input, int transint, double *transit_out, int transit_out_size);
 void do_transit(double *transit_out);
+void run_transit_batch(double *re_input, int natm, double *transit_out);
 void free_memory(void);
 void th_write_spectrum(void);
 /* test/diagnostic accessor: the device context behind the library face (NULL before transit_init) */

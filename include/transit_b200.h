@@ -151,6 +151,19 @@ int  tb_spectrum_batch(tb_ctx *c, int natm, int nrad, const double *rad, double 
                        double ethresh, double starrad_cm, int transparent,
                        const double *angles_deg, int nang, double *out);
 
+/* run_transit for a BATCH of atmospheres exactly as BART hands them over (readatm.c:735-744):
+ * in[natm][nlayers*(1+nmol)] = [T(nlayers) | q_mol0(nlayers) | q_mol1(nlayers) ...] per atmosphere, spectra
+ * out[natm][nwn].  The per-atmosphere set-up of reloadatm (readatm.c:722-784: checkaddmm, stateeqnford, radpress)
+ * runs ON THE DEVICE, and every stage -- grid interpolation, CIA, tau, modulation -- is launched once per batch of
+ * up to 32 atmospheres.  Needs a resident opacity grid (tb_opacity_load), transit geometry, modlevel 1, and the
+ * static part of the atmosphere model: the file's pressures (file units), the unit factors, `q number|mass`, and the
+ * hydrostatic reference level refpress / refradius / gsurf (argum.c).  H2 (for the cloud model P19) is the
+ * molecule with ID 105, as in the shipped molecules.dat.                                                       */
+int  tb_set_atmosphere_model(tb_ctx *c, int nrad, const double *p, double p_fct, double t_fct, double rad_fct,
+                             int bymass, double p0, double r0, double gsurf);
+int  tb_run_transit_batch(tb_ctx *c, int natm, const double *in, double toomuch, double starrad_cm,
+                          int transparent, double *out);
+
 /* test taps in the reference's layouts                                                */
 int  tb_get_extinction(tb_ctx *c, double *e /*[nrad][nwn]*/);
 int  tb_get_cia(tb_ctx *c, double *e_cs /*[nwn][nrad]*/);

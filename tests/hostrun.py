@@ -4,7 +4,7 @@ the per-line index trace of chosen layers -- through the host's own context (th_
 Executed as a subprocess by tests/test_fullsize_parity.py (the host has one global state and exits on errors,
 like the reference it mirrors).
 
-    python tests/hostrun.py <cfg> <out.npz> [--trace r0,r1,..] [--rerun file.f64] [--no-taps] [-- extra transit args]
+    python tests/hostrun.py <cfg> <out.npz> [--trace r0,r1,..] [--rerun file.f64 [--batch]] [--no-taps] [-- extra transit args]
 """
 import ctypes as C
 import os
@@ -82,6 +82,15 @@ def main():
         d["rerun_s"] = time.perf_counter() - t0
         os.dup2(so, 1)
         d["rerun_out_all"] = outs
+        if "--batch" in rest:          # the same inputs through ONE run_transit_batch call
+            b = np.zeros((k, n))
+            x = np.ascontiguousarray(inp[:k * nin])
+            os.dup2(os.open(os.devnull, os.O_WRONLY), 1)
+            t0 = time.perf_counter()
+            L.run_transit_batch(x.ctypes.data_as(P), k, b.ctypes.data_as(P))
+            d["batch_s"] = time.perf_counter() - t0
+            os.dup2(so, 1)
+            d["batch_out_all"] = b
     np.savez(outp, **d)
     L.free_memory()
 

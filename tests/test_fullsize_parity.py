@@ -172,3 +172,94 @@ def test_c2_full_size(tmp_path):
     w["reference_s"] = ref_s
     w["ours_run_s"] = float(o["run_s"])
     report("C2 full size", w)
+
+
+def _rerun_inputs(prob, k, seed0=7000, dT=150.0, dex=1.0):
+    """k run_transit inputs [T | q_mol...] (readatm.c:735-744): seeded perturbations of the base profile."""
+    rows = []
+    for i in range(k):
+        a = workloads.perturbed(prob, seed=seed0 + i, dT=dT, dex=dex)
+        rows.append(np.concatenate([a.t] + [a.mol_q[j] for j in range(prob.nmol)]))
+    return np.stack(rows)
+
+
+def test_c5_shape_retrieval_from_c2_grid(tmp_path):
+    """C5 shape at the C2 grid's full size: the host BUILDS the 2.6 GB opacity grid (100 layers x 26 temperatures x 4
+    molecules x 31 334 wavenumbers) with --opacityfile, the UNMODIFIED reference reads that file and serves the base
+    spectrum + 4 run_transit calls (perturbed T-P / abundance profiles, hydrostatic radii from refpress / refradius /
+    gsurf); the host serves the same calls one by one AND as one run_transit_batch (set-up on the device)."""
+    tmp = str(tmp_path)
+    prob = workloads.make_problem("C2")
+    cfg, _ = workloads.write_reference_inputs(prob, tmp)
+    k = prob.nrad // 3
+    with open(cfg, "a") as f:
+        f.write(f"refpress {prob.p[k]:.6e}\nrefradius {prob.rad[k]:.6f}\ngsurf 1500.0\nopacityfile {tmp}/grid.opa\n")
+    inp = _rerun_inputs(prob, 4)
+    inp.astype("<f8").tofile(os.path.join(tmp, "rerun.f64"))
+    # the host first (it builds and writes the grid), then the reference on the host's file
+    ours = os.path.join(tmp, "ours.npz")
+    t0 = time.perf_counter()
+    r = subprocess.run([sys.executable, HOSTRUN, cfg, ours, "--rerun", os.path.join(tmp, "rerun.f64"), "--batch", "--no-taps"],
+                       cwd=tmp, capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-3000:])
+    build_s = time.perf_counter() - t0
+    assert os.path.getsize(os.path.join(tmp, "grid.opa")) > 2.5e9
+    refbin = os.path.join(tmp, "ref.bin")
+    t0 = time.perf_counter()
+    r = subprocess.run([os.path.join(REFDIR, "ref_dump"), refbin, "--rerun", os.path.join(tmp, "rerun.f64"), "--", "-c", cfg],
+                       cwd=tmp, capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    ref_s = time.perf_counter() - t0
+    g, o = MG.read_container(refbin), np.load(ours)
+    assert int(g["op_Ntemp"].item()) == 26 and int(g["op_Nmol"].item()) == 4 and int(g["op_Nwave"].item()) == 31334
+    w = dict(nwn=31334, layers=100, grid_temperatures=26, atmospheres=4)
+    w["spectrum_rel"] = rel(o["out"], g["out"])
+    w["run_transit_rel"] = rel(o["rerun_out_all"], g["rerun_out_all"])
+    w["batch_vs_loop_rel"] = rel(o["batch_out_all"], o["rerun_out_all"])
+    w["batch_vs_reference_rel"] = rel(o["batch_out_all"], g["rerun_out_all"])
+    assert w["spectrum_rel"] < 1e-8 and w["run_transit_rel"] < 1e-8 and w["batch_vs_reference_rel"] < 1e-8
+    assert w["batch_vs_loop_rel"] < 1e-11
+    w["reference_s"] = ref_s
+    w["ours_total_s_including_grid_build_and_file"] = build_s
+    w["ours_loop_s"], w["ours_batch_s"] = float(o["rerun_s"]), float(o["batch_s"])
+    report("C5 shape: run_transit x4 from the full-size C2 grid", w)
+
+
+def test_c4_shape_high_resolution_eclipse(tmp_path):
+    """C4 shape at a tenth of its wavenumbers (1e5 samples at 0.01 cm-1, 100 layers, 6 grid temperatures x 2
+    molecules: a 0.96 GB opacity file both sides read), eclipse geometry, 5 angles: the largest size the reference
+    serves in under two minutes."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import bench_configs as BC
+    tmp = str(tmp_path)
+    prob = BC.c4_problem(nwn=100001)
+    temps = np.array([800.0, 1000.0, 1200.0, 1400.0, 1600.0, 1800.0])
+    grid = BC.c4_grid(prob, temps)
+    cfg, _ = workloads.write_reference_inputs(prob, tmp)
+    molID = np.array([prob.mol_ID[prob.species_names.index(s)] for s in ("H2O", "CH4")], np.int32)
+    with open(os.path.join(tmp, "grid.opa"), "wb") as f:          # opacity.c:405-421
+        np.array([2, len(temps), prob.nrad, prob.nwn], "<i8").tofile(f)
+        molID.astype("<i4").tofile(f); temps.astype("<f8").tofile(f)
+        (prob.p * prob.p_fct).astype("<f8").tofile(f)
+        (prob.wn_i + np.arange(prob.nwn) * prob.wn_d).astype("<f8").tofile(f)
+        grid.astype("<f8").tofile(f)
+    del grid
+    with open(cfg, "a") as f:
+        f.write(f"opacityfile {tmp}/grid.opa\n")
+    g, o, ref_s = run_both(tmp, cfg, [], timeout=1500)
+    assert int(g["wns_n"].item()) == 100001 and int(g["nrad"].item()) == 100
+    assert np.array_equal(o["last"], g["last"]) and np.array_equal(o["computed"], g["computed"].astype(np.int16))
+    comp = g["computed"].astype(bool)
+    w = dict(nwn=100001, layers=100, angles=5)
+    w["ext_rel"] = rel(o["ext"][comp], g["ext"][comp])
+    w["cia_rel"] = rel(o["e_cs"][g["e_cs"] > 0], g["e_cs"][g["e_cs"] > 0])
+    nz = g["tau"] != 0
+    assert np.array_equal(o["tau"] == 0, g["tau"] == 0)
+    w["tau_rel"] = rel(o["tau"][nz], g["tau"][nz])
+    w["intens_rel"] = rel(o["intens"], g["intens"])
+    w["spectrum_rel"] = rel(o["out"], g["out"])
+    assert w["ext_rel"] < 1e-10 and w["cia_rel"] < 1e-12 and w["tau_rel"] < 1e-9
+    assert w["intens_rel"] < 1e-8 and w["spectrum_rel"] < 1e-8
+    w["reference_s"] = ref_s
+    w["ours_run_s"] = float(o["run_s"])
+    report("C4 shape: 1e5 wavenumbers, eclipse from a grid", w)

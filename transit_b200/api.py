@@ -71,6 +71,9 @@ ABI = {
     "tb_spectrum": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, f64p, C.c_int, f64p]),
     "tb_spectrum_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_int, f64p, C.c_double, f64p, C.c_double, f64p, C.c_double,
                                     f64p, f64p, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, f64p, C.c_int, f64p]),
+    "tb_set_atmosphere_model": (C.c_int, [C.c_void_p, C.c_int, f64p, C.c_double, C.c_double, C.c_double, C.c_int,
+                                          C.c_double, C.c_double, C.c_double]),
+    "tb_run_transit_batch": (C.c_int, [C.c_void_p, C.c_int, f64p, C.c_double, C.c_double, C.c_int, f64p]),
     "tb_get_extinction": (C.c_int, [C.c_void_p, f64p]),
     "tb_get_cia": (C.c_int, [C.c_void_p, f64p]),
     "tb_get_tau": (C.c_int, [C.c_void_p, f64p, i64p]),
@@ -369,6 +372,20 @@ class Context:
                  "tb_spectrum_batch")
         self.nrad = nrad
         self.nh = nrad
+        return out
+
+    def set_atmosphere_model(self, p, p_fct, t_fct, rad_fct, bymass, p0, r0, gsurf):
+        p = _c64(p)
+        self._ck(self.lib.tb_set_atmosphere_model(self.h, len(p), _p(p), p_fct, t_fct, rad_fct, int(bymass), p0, r0, gsurf),
+                 "tb_set_atmosphere_model")
+
+    def run_transit_batch(self, inputs, toomuch, starrad_cm, transparent=0, out=None):
+        """inputs[natm][nlayers*(1+nmol)] as BART hands them to run_transit; out[natm][nwn]."""
+        x = _c64(inputs)
+        natm = x.shape[0]
+        out = np.zeros((natm, self.nwn)) if out is None else out
+        self._ck(self.lib.tb_run_transit_batch(self.h, natm, _p(x), toomuch, starrad_cm, int(transparent), _p(out)),
+                 "tb_run_transit_batch")
         return out
 
     def get_extinction(self):

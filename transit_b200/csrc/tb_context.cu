@@ -74,8 +74,8 @@ static int tb_create_resources(tb_ctx *c) {
   TB_CUDA(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
   TB_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
   TB_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
-  TB_TRY(c->d_err.ensure(4));
-  TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4 * sizeof(int32_t), c->stream));
+  TB_TRY(c->d_err.ensure(8));
+  TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 8 * sizeof(int32_t), c->stream));
   return TB_OK;
 }
 

@@ -102,6 +102,11 @@ struct __align__(16) LineRec {
                    // high 16 bits: how many dead records follow this one inside its 256-group block
 };
 
+struct InterpLayer {   // per layer of an interpolated spectrum: lower grid-temperature index and the weights' ingredients
+  int it;
+  double t, tlo, thi;
+};
+
 struct CiaTable {
   int nw = 0, nt = 0, nspec = 0;
   int mol[2] = {0, 0};
@@ -237,7 +242,7 @@ struct tb_ctx {
   // ---- results
   DevBuf<double> d_e, d_ecs, d_tau, d_intens, d_out;
   DevBuf<int32_t> d_last;
-  DevBuf<int32_t> d_err;
+  DevBuf<int32_t> d_err;      // [8] device-side error flags
   bool defer_check = false, err_keep = false;   // tb_spectrum_batch: one error read-back per batch
   DevBuf<double> d_out_batch;
   bool have_e = false, have_ecs = false, have_tau = false;
@@ -272,6 +277,15 @@ struct tb_ctx {
   double cl_ext = 0, cl_top = 0, cl_bot = 0, cl_gamma = 0, cl_Q = 0, cl_r = 0, cl_sig = 0, cl_refwn = 0;
   std::vector<double> nH, mean_dens;
   DevBuf<double> d_es_aux;  // [nH | mean_dens]
+
+  // ---- batched retrieval (tb_radiative.cu: tb_set_atmosphere_model / tb_run_transit_batch)
+  int am_nrad = 0, am_bymass = 0, am_ih2 = -1, b_static_version = -1;
+  double am_pfct = 1, am_tfct = 1, am_rfct = 1, am_p0 = 0, am_r0 = 0, am_gsurf = 0;
+  std::vector<double> am_p;
+  DevBuf<double> b_p, b_in, b_ltemp, b_traw, b_dens, b_rad, b_ip, b_rho, b_densfac, b_aux, b_e, b_ecs, b_tau, b_out, b_gtemp;
+  DevBuf<uint8_t> b_L;
+  DevBuf<int32_t> b_last;
+  DevBuf<int> b_gmol;
 
   // CUB temp storage
   DevBuf<uint8_t> cub_tmp;
@@ -338,6 +352,7 @@ int tb_check_errors(tb_ctx *c);
 #define TB_RING_BYTES (size_t(4) << 20)
 int tb_upload_small(tb_ctx *c, void *dst, const void *src, size_t bytes, cudaStream_t st);
 int tb_interp_run(tb_ctx *c);
+int tb_interp_launch(tb_ctx *c, int nvl, int ngrid, const InterpLayer *dL, const double *drho, double *e);
 int tb_comm_allreduce_max(tb_ctx *c, int what, void *device_ptr, int64_t count);
 int tb_comm_gather_spectrum(tb_ctx *c);
 extern "C" int tb_comm_destroy(tb_ctx *c);

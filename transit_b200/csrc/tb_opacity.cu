@@ -35,20 +35,18 @@ extern "C" int tb_opacity_load(tb_ctx *c, int64_t Nmol, int64_t Ntemp, int64_t N
   return TB_OK;
 }
 
-struct InterpLayer {   // per layer: lower temperature index and the two weights' ingredients
-  int it;
-  double t, tlo, thi;
-};
 
 // extinction.c:568-578: e[r][w] = sum_m rho_m[r] * (o_lo*(T+ - T) + o_hi*(T - T-))/(T+ - T-)
-__global__ void k_grid_interp(int64_t nwn, int nrad, int Ntemp, int Nmol, const double *__restrict__ grid,
+// A batch of atmospheres (tb_batch.cu) is nrad*natm "virtual layers": virtual layer v = a*ngrid + r reads the grid
+// planes of layer r = v % ngrid with its own temperature bracket and densities; rho[Nmol][nrad], e[nrad][nwn].
+__global__ void k_grid_interp(int64_t nwn, int nrad, int ngrid, int Ntemp, int Nmol, const double *__restrict__ grid,
                               const InterpLayer *__restrict__ L, const double *__restrict__ rho /*[Nmol][nrad]*/,
                               double *__restrict__ e) {
   int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  int r = blockIdx.y;
-  if (w >= nwn) return;
+  int r = blockIdx.y + blockIdx.z * gridDim.y;
+  if (w >= nwn || r >= nrad) return;
   const InterpLayer l = L[r];
-  const double *lo = grid + (((size_t)r * Ntemp + l.it) * Nmol) * nwn + w;
+  const double *lo = grid + (((size_t)(r % ngrid) * Ntemp + l.it) * Nmol) * nwn + w;
   const double *hi = lo + (size_t)Nmol * nwn;
   double acc = 0.0;
   // the 2 x 4 plane reads of four molecules are issued before the first division depends on one:
@@ -103,11 +101,22 @@ int tb_interp_run(tb_ctx *c) {
   TB_TRY(tb_upload_small(c, drhop, rho.data(), rho.size() * sizeof(double), st)); // the locals may die
   dim3 g(nblk(c->nwn, 256), nrad);
   tb_timer_begin(c, "interp");
-  k_grid_interp<<<g, 256, 0, st>>>(c->nwn, nrad, Nt, Nm, c->d_grid.p, dLp, drhop, c->d_e.p);
+  k_grid_interp<<<g, 256, 0, st>>>(c->nwn, nrad, nrad, Nt, Nm, c->d_grid.p, dLp, drhop, c->d_e.p);
   tb_timer_end(c, "interp");
   TB_LAUNCHED(c);
   TB_CUDA(cudaGetLastError());
   c->have_e = true;
+  return TB_OK;
+}
+
+// the same kernel over nvl virtual layers of a batch of atmospheres (tb_run_transit_batch)
+int tb_interp_launch(tb_ctx *c, int nvl, int ngrid, const InterpLayer *dL, const double *drho, double *e) {
+  const int ny = nvl < 32768 ? nvl : 32768;
+  dim3 g(nblk(c->nwn, 256), ny, (nvl + ny - 1) / ny);
+  tb_timer_begin(c, "interp");
+  k_grid_interp<<<g, 256, 0, c->stream>>>(c->nwn, nvl, ngrid, (int)c->gNtemp, (int)c->gNmol, c->d_grid.p, dL, drho, e);
+  tb_timer_end(c, "interp");
+  TB_LAUNCHED(c);
   return TB_OK;
 }
 

@@ -266,6 +266,25 @@ extern "C" int tb_cia_add_table(tb_ctx *c, const double *wn, int nwn, const doub
   return TB_OK;
 }
 
+// static per (table, grid): the table's wavenumber range on the grid and the table interval of every grid point
+static int tb_cia_table_grid(tb_ctx *c, CiaTable *t) {
+  if (t->grid_version == c->grid_version) return TB_OK;
+  const int64_t nwn = c->nwn;
+  auto gw = [&](int64_t k) { return c->wn_fct * (c->wn_i + (double)k * c->wn_d); };
+  const double fx1 = t->wn[0], lx1 = t->wn[t->nw - 1];
+  t->fi = 0; t->li = nwn;
+  if (gw(0) > lx1 || gw(nwn - 1) < fx1) t->li = 0;
+  else {
+    while (t->fi < nwn && gw(t->fi) < fx1) t->fi++;
+    for (int64_t i = 0; i < t->li; i++) if (gw(i) > lx1) t->li = i;
+  }
+  TB_TRY(t->d_widx.ensure(nwn));
+  k_cia_widx<<<nblk(nwn, 256), 256, 0, c->stream>>>(t->d_wn.p, t->nw, c->wn_i, c->wn_d, c->wn_fct, nwn, t->d_widx.p);
+  TB_LAUNCHED(c);
+  t->grid_version = c->grid_version;
+  return TB_OK;
+}
+
 int tb_cia_run(tb_ctx *c) {
   TB_REQUIRE(c->have_atm && c->have_grid, TB_ERR_STATE, "grid and atmosphere must be set before tb_cia_interp");
   TB_CUDA(cudaSetDevice(c->device));
@@ -306,18 +325,7 @@ int tb_cia_run(tb_ctx *c) {
     CiaTable *t = c->cia[n];
     // bicubicinterpolate's range logic (crosssec.c:366-393)
     const double fx1 = t->wn[0], lx1 = t->wn[t->nw - 1], fx2 = t->temp[0], lx2 = t->temp[t->nt - 1];
-    if (t->grid_version != c->grid_version) {          // static per (table, grid): wavenumber range + intervals
-      t->fi = 0; t->li = nwn;
-      if (gw(0) > lx1 || gw(nwn - 1) < fx1) t->li = 0;
-      else {
-        while (t->fi < nwn && gw(t->fi) < fx1) t->fi++;
-        for (int64_t i = 0; i < t->li; i++) if (gw(i) > lx1) t->li = i;
-      }
-      TB_TRY(t->d_widx.ensure(nwn));
-      k_cia_widx<<<nblk(nwn, 256), 256, 0, st>>>(t->d_wn.p, t->nw, c->wn_i, c->wn_d, c->wn_fct, nwn, t->d_widx.p);
-      TB_LAUNCHED(c);
-      t->grid_version = c->grid_version;
-    }
+    TB_TRY(tb_cia_table_grid(c, t));
     if (t->fi >= t->li || ltemp[0] > lx2 || ltemp[nrad - 1] < fx2) continue;
     int fj = 0, lj = nrad;
     while (fj < nrad && ltemp[fj] < fx2) fj++;
@@ -390,7 +398,10 @@ __global__ void k_ray_geometry(int eclipse, const double *__restrict__ rad, int 
   // one block per ray: thread 0 places the ray, then the path coordinates s[i] (one sqrt each) and the
   // Simpson weights of the pairs (three divisions each) are independent and spread over the block
   // (one thread per ray ran them as a 27 us serial chain in front of every tau launch)
+  // a batch of atmospheres (tb_batch.cu) launches natm*nh blocks: block a*nh + ri is ray ri of atmosphere a, whose
+  // radii and impact parameters are the a-th slices; every output is indexed by the block
   const int ri = blockIdx.x;
+  rad += (size_t)(ri / nh) * nrad;                             // h[natm][nh] is indexed by the block as it is
   __shared__ int sh_rs, sh_mode, sh_n;
   __shared__ double sh_r0;
   int32_t *mt = meta + ri * 4;
@@ -539,6 +550,12 @@ k_tau_transit(TauPar P, const double *__restrict__ e, const double *__restrict__
   extern __shared__ double sm[];
   __shared__ int sh_last[32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  {  // a batch of atmospheres (tb_batch.cu): blockIdx.y selects the atmosphere's slices
+    const size_t a = blockIdx.y;
+    e += a * P.nrad * P.nwn; ecs += a * P.nrad * P.nwn; temp += a * P.nrad; aux += a * 2 * P.nrad;
+    mol_d += a * (size_t)nmol * P.nrad; meta += a * P.nh * 4; par += a * P.nh * 4; coef += a * (size_t)P.nh * P.stride;
+    rcp += a * P.nh * 2; tau += a * P.nh * P.nwn; last += a * P.nwn;
+  }
   const int64_t w = P.w0 + blockIdx.x * 32LL + lane;
   const bool inb = w < P.w1;
   const int nrad = P.nrad;
@@ -962,6 +979,10 @@ __global__ void k_modulation(int64_t nwn, int64_t w0, int64_t w1, int nh, const 
   // cf[r] = {2-hratio, hfactor, 2-1/hratio, hsum} once in shared memory.
   extern __shared__ __align__(16) double smod[];
   double *xs = smod, *cf = smod + ((nh + 1) & ~1);   // 16-byte aligned rows
+  {  // a batch of atmospheres (tb_batch.cu): blockIdx.y selects the atmosphere's slices
+    const size_t a = blockIdx.y;
+    tau += a * nh * nwn; last += a * nwn; ip += a * nh; out += a * nwn;
+  }
   for (int i = threadIdx.x; i < nh; i += blockDim.x) xs[i] = ip[i] * ipfct;
   __syncthreads();
   for (int r = 2 + threadIdx.x; r < nh; r += blockDim.x) {
@@ -1235,4 +1256,267 @@ extern "C" int tb_spectrum_batch(tb_ctx *c, int natm, int nrad, const double *ra
   if (rc != TB_OK) { cudaStreamSynchronize(c->stream); return rc; }
   TB_CUDA(cudaMemcpyAsync(out, c->d_out_batch.p, (size_t)natm * nwn * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   return tb_check_errors(c);
+}
+
+// =============================================================== batched retrieval (a16 on the device, C5)
+//
+// BART hands run_transit one atmosphere at a time: in = [T(nlayers) | q_mol0(nlayers) | ...] (readatm.c:735-744).
+// From the opacity grid a spectrum is a chain of small latency-bound kernels (~0.37 ms of which ~0.1 ms is
+// arithmetic), so a batch of atmospheres goes through EVERY stage in one launch each:
+//   k_atm_setup    reloadatm + checkaddmm + stateeqnford + radpress (readatm.c:122-159,722-865, transit.h:58-69)
+//                  per atmosphere on the device: densities, mean molecular mass, hydrostatic radii, impact
+//                  parameters, the grid's temperature brackets, the CIA density factors, cloud densities;
+//   k_grid_interp  over natm*nlayers virtual layers (every grid plane a batch touches is read while it is in L2);
+//   k_cia_*        the two spline families over natm*nlayers layers;
+//   k_ray_geometry, k_tau_transit, k_modulation with the atmosphere as a grid dimension.
+// One upload of the inputs, one read-back of the spectra and one error check per batch.
+struct BatchPar {
+  int nrad, nmol, bymass, ih2, Nt, Nm, ntab;
+  double p_fct, t_fct, rad_fct, p0, r0, gsurf;
+  double cia_tmin, cia_tmax;
+  int tab_mol[CIA_MAXTAB][2], tab_nspec[CIA_MAXTAB];
+};
+
+#define ATM_MAXLAYERS 1024
+__global__ void k_atm_setup(BatchPar B, int natm, const double *__restrict__ in, const double *__restrict__ p,
+                            const double *__restrict__ mol_mass, const double *__restrict__ gtemp,
+                            const int *__restrict__ gmol_idx, double *__restrict__ ltemp /*[natm][nrad] kelvin*/,
+                            double *__restrict__ traw /*[natm][nrad] file units*/, double *__restrict__ dens /*[natm][nmol][nrad]*/,
+                            double *__restrict__ rad /*[natm][nrad]*/, double *__restrict__ ip /*[natm][nrad]*/,
+                            InterpLayer *__restrict__ L /*[natm*nrad]*/, double *__restrict__ rho_g /*[Nm][natm*nrad]*/,
+                            double *__restrict__ densfac /*[ntab][natm*nrad]*/, double *__restrict__ aux /*[natm][2][nrad]*/,
+                            int32_t *__restrict__ err) {
+  __shared__ double sh_t[ATM_MAXLAYERS], sh_mm[ATM_MAXLAYERS], sh_rad[ATM_MAXLAYERS];
+  const int a = blockIdx.x, n = B.nrad, nmol = B.nmol, nvl = natm * n;
+  const double *x = in + (size_t)a * n * (1 + nmol);
+  for (int r = threadIdx.x; r < n; r += blockDim.x) {
+    const double T = x[r];
+    double mm = 0, sumq = 0;
+    for (int i = 0; i < nmol; i++) {                       // checkaddmm (readatm.c:122-159)
+      const double q = x[(size_t)n * (i + 1) + r];
+      mm += B.bymass ? q / mol_mass[i] : q * mol_mass[i];
+      sumq += q;
+    }
+    if (B.bymass) mm = 1.0 / mm;
+    if (sumq > 1.001) atomicExch(err + 4, 1);
+    sh_t[r] = T; sh_mm[r] = mm;
+    const double pr = p[r] * B.p_fct, tk = T * B.t_fct;
+    double md = 0, nH = 0, mean_mm = 0;
+    for (int i = 0; i < nmol; i++) {                       // stateeqnford (transit.h:58-69)
+      const double q = x[(size_t)n * (i + 1) + r];
+      const double rho = TB_AMU * q * pr / TB_KB / tk;
+      const double d = B.bymass ? rho * mm : rho * mol_mass[i];
+      dens[((size_t)a * nmol + i) * n + r] = d;
+      md += d / mol_mass[i] * q;                           // tau.c:194-214
+      if (i == B.ih2) nH = d / mol_mass[i] * q * TB_NAVOGADRO;
+      mean_mm += mol_mass[i] * q;
+    }
+    aux[(size_t)a * 2 * n + r] = nH;
+    aux[(size_t)a * 2 * n + n + r] = md * mean_mm;
+    ltemp[(size_t)a * n + r] = tk;
+    traw[(size_t)a * n + r] = T;
+    if (tk < B.cia_tmin || tk > B.cia_tmax) atomicExch(err + 5, 1);   // interpcs exits (crosssec.c:293-309)
+    // interpolmolext's temperature bracket (extinction.c:562-564)
+    int lo = 0, hi = B.Nt;
+    while (hi - lo > 1) {
+      const int mid = (hi + lo) / 2;
+      if (gtemp[mid] > tk) hi = mid; else lo = mid;
+    }
+    int it = (fabs(gtemp[hi] - tk) < fabs(gtemp[lo] - tk)) ? hi : lo;
+    if (tk < gtemp[it]) it--;
+    if (it < 0 || it + 1 >= B.Nt) { atomicExch(err + 6, 1); it = it < 0 ? 0 : B.Nt - 2; }
+    InterpLayer l;
+    l.it = it; l.t = tk; l.tlo = gtemp[it]; l.thi = gtemp[it + 1];
+    L[(size_t)a * n + r] = l;
+    for (int m = 0; m < B.Nm; m++) rho_g[(size_t)m * nvl + (size_t)a * n + r] = dens[((size_t)a * nmol + gmol_idx[m]) * n + r];
+    for (int k = 0; k < B.ntab; k++) {                      // crosssec.c:321-326
+      double f = 1.0;
+      for (int q2 = 0; q2 < B.tab_nspec[k]; q2++) {
+        const int m = B.tab_mol[k][q2];
+        f *= dens[((size_t)a * nmol + m) * n + r] / (TB_AMU * mol_mass[m] * TB_AMAGAT);
+      }
+      densfac[(size_t)k * nvl + (size_t)a * n + r] = f;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {                                  // radpress (readatm.c:787-865): a recurrence over the layers
+    const double g0 = B.gsurf, p0 = B.p0, r0 = B.r0, rfct = B.rad_fct;
+    const double *temp = sh_t, *mu = sh_mm, *pr = p;
+    double *radius = sh_rad;
+    double minimum = 1e37, temp0, mu0, g;
+    int i0 = -1;
+    for (int i = 0; i < n; i++)
+      if (fabs(pr[i] - p0) < minimum) { i0 = i; minimum = fabs(pr[i] - p0); }
+    const double kb_amu = TB_KB / TB_AMU;
+    if ((pr[i0] > p0 && i0 + 1 >= n) || (pr[i0] <= p0 && i0 - 1 < 0)) { atomicExch(err + 7, 1); i0 = i0 + 1 >= n ? n - 2 : 1; }
+    if (pr[i0] > p0) {
+      temp0 = temp[i0] + ((temp[i0 + 1] - temp[i0]) / log(pr[i0 + 1] / pr[i0])) * log(p0 / pr[i0]);
+      mu0 = mu[i0] + ((mu[i0 + 1] - mu[i0]) / log(pr[i0 + 1] / pr[i0])) * log(p0 / pr[i0]);
+      radius[i0] = r0 + 0.5 * (temp[i0] / mu[i0] + temp0 / mu0) * (kb_amu * log(p0 / pr[i0]) / g0) / rfct;
+    } else {
+      temp0 = temp[i0] + ((temp[i0 - 1] - temp[i0]) / log(pr[i0 - 1] / pr[i0])) * log(p0 / pr[i0]);
+      mu0 = mu[i0] + ((mu[i0 - 1] - mu[i0]) / log(pr[i0 - 1] / pr[i0])) * log(p0 / pr[i0]);
+      radius[i0] = r0 - 0.5 * (temp[i0] / mu[i0] + temp0 / mu0) * (kb_amu * log(pr[i0] / p0) / g0) / rfct;
+    }
+    g = g0 * pow(r0 / radius[i0], 2.0);
+    for (int i = i0 - 1; i >= 0; i--) {
+      radius[i] = radius[i + 1] - 0.5 * (temp[i] / mu[i] + temp[i + 1] / mu[i + 1]) * (kb_amu * log(pr[i] / pr[i + 1]) / g) / rfct;
+      g = g * pow(radius[i + 1] / radius[i], 2.0);
+    }
+    g = g0 * pow(r0 / radius[i0], 2.0);
+    for (int i = i0 + 1; i < n; i++) {
+      radius[i] = radius[i - 1] + 0.5 * (temp[i] / mu[i] + temp[i - 1] / mu[i - 1]) * (kb_amu * log(pr[i - 1] / pr[i]) / g) / rfct;
+      g = g * pow(radius[i - 1] / radius[i], 2.0);
+    }
+  }
+  __syncthreads();
+  for (int r = threadIdx.x; r < n; r += blockDim.x) {
+    rad[(size_t)a * n + r] = sh_rad[r];
+    ip[(size_t)a * n + r] = sh_rad[n - 1 - r];              // makeipsample with raddelt = -1 (makesample.c:564-573)
+    if (r > 0 && !(sh_rad[r] > sh_rad[r - 1])) atomicExch(err + 7, 1);
+  }
+}
+
+extern "C" int tb_set_atmosphere_model(tb_ctx *c, int nrad, const double *p, double p_fct, double t_fct, double rad_fct,
+                                       int bymass, double p0, double r0, double gsurf) {
+  TB_REQUIRE(nrad >= 3 && nrad <= ATM_MAXLAYERS && p, TB_ERR_ARG, "tb_set_atmosphere_model: 3..%d layers", ATM_MAXLAYERS);
+  TB_REQUIRE(p0 != 0 && r0 != 0 && gsurf != 0, TB_ERR_ARG,
+             "Surface gravity (%g) or reference pressure (%g) or radius (%g) were not defined.", gsurf, p0, r0);
+  TB_CUDA(cudaSetDevice(c->device));
+  c->am_nrad = nrad; c->am_p.assign(p, p + nrad);
+  c->am_pfct = p_fct; c->am_tfct = t_fct; c->am_rfct = rad_fct; c->am_bymass = bymass;
+  c->am_p0 = p0; c->am_r0 = r0; c->am_gsurf = gsurf;
+  c->am_ih2 = -1;                       // tau.c:207 looks H2 up by NAME; molecules.dat gives it the ID 105
+  for (int i = 0; i < c->nmol; i++) if (c->mol_ID[i] == 105) c->am_ih2 = i;
+  TB_TRY(c->b_p.ensure(nrad));
+  TB_CUDA(cudaMemcpyAsync(c->b_p.p, p, nrad * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  TB_CUDA(cudaStreamSynchronize(c->stream));
+  return TB_OK;
+}
+
+extern "C" int tb_run_transit_batch(tb_ctx *c, int natm, const double *in, double toomuch, double starrad_cm,
+                                    int transparent, double *out) {
+  TB_REQUIRE(natm >= 1 && in && out, TB_ERR_ARG, "tb_run_transit_batch: bad arguments");
+  TB_REQUIRE(c->am_nrad > 0, TB_ERR_STATE, "tb_set_atmosphere_model must precede tb_run_transit_batch");
+  TB_REQUIRE(c->have_grid_o, TB_ERR_STATE, "tb_run_transit_batch serves spectra from a resident opacity grid (tb_opacity_load)");
+  TB_REQUIRE(c->modlevel == 1, TB_ERR_STATE, "tb_run_transit_batch: modlevel 1 only");
+  TB_REQUIRE(!(c->banded && c->shard_world > 1), TB_ERR_STATE, "a retrieval batch shards over atmospheres, not bands");
+  const int nrad = c->am_nrad, nmol = c->nmol, nh = nrad, ntab = (int)c->cia.size();
+  TB_REQUIRE(c->gNlayer == nrad, TB_ERR_ARG, "opacity grid has %lld layers, the atmosphere model %d", (long long)c->gNlayer, nrad);
+  TB_CUDA(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const int64_t nwn = c->nwn;
+  const int Bmax = natm < 32 ? natm : 32;
+  const int Nt = (int)c->gNtemp, Nm = (int)c->gNmol;
+  const int stride = 4 * ((nrad + 2) / 2 + 1);
+  const size_t shm_tau = ((size_t)nrad * 32 + (size_t)TAU_NW * stride) * sizeof(double);
+  TB_REQUIRE(stride <= 320 && shm_tau <= 200 * 1024, TB_ERR_ARG, "too many layers (%d) for the tau kernel", nrad);
+  const size_t nin = (size_t)nrad * (1 + nmol), nvl_max = (size_t)Bmax * nrad;
+  // ---- batch buffers
+  TB_TRY(c->b_in.ensure(Bmax * nin)); TB_TRY(c->b_ltemp.ensure(nvl_max)); TB_TRY(c->b_traw.ensure(nvl_max));
+  TB_TRY(c->b_dens.ensure(nvl_max * nmol)); TB_TRY(c->b_rad.ensure(nvl_max)); TB_TRY(c->b_ip.ensure(nvl_max));
+  TB_TRY(c->b_L.ensure(nvl_max * sizeof(InterpLayer))); TB_TRY(c->b_rho.ensure(nvl_max * Nm));
+  TB_TRY(c->b_densfac.ensure(nvl_max * (ntab ? ntab : 1))); TB_TRY(c->b_aux.ensure(2 * nvl_max));
+  TB_TRY(c->b_e.ensure(nvl_max * nwn)); TB_TRY(c->b_ecs.ensure(nvl_max * nwn)); TB_TRY(c->b_tau.ensure(nvl_max * nwn));
+  TB_TRY(c->b_last.ensure((size_t)Bmax * nwn)); TB_TRY(c->b_out.ensure((size_t)Bmax * nwn));
+  TB_TRY(c->r_meta.ensure(nvl_max * 4)); TB_TRY(c->r_par.ensure(nvl_max * 4)); TB_TRY(c->r_coef.ensure(nvl_max * stride));
+  TB_TRY(c->r_rcp.ensure(nvl_max * 2)); TB_TRY(c->r_s.ensure(nvl_max * (nrad + 3)));
+  if (c->b_static_version != c->grid_version || c->b_gtemp.n < (size_t)Nt + 1) {
+    TB_TRY(c->b_gtemp.ensure(Nt + 1)); TB_TRY(c->b_gmol.ensure(Nm));
+    TB_CUDA(cudaMemcpyAsync(c->b_gtemp.p, c->gtemp.data(), (Nt + 1) * sizeof(double), cudaMemcpyHostToDevice, st));
+    TB_CUDA(cudaMemcpyAsync(c->b_gmol.p, c->gmol_idx.data(), Nm * sizeof(int), cudaMemcpyHostToDevice, st));
+    TB_CUDA(cudaStreamSynchronize(st));
+    c->b_static_version = c->grid_version;
+  }
+  BatchPar B;
+  B.nrad = nrad; B.nmol = nmol; B.bymass = c->am_bymass; B.Nt = Nt; B.Nm = Nm; B.ntab = ntab;
+  B.p_fct = c->am_pfct; B.t_fct = c->am_tfct; B.rad_fct = c->am_rfct; B.p0 = c->am_p0; B.r0 = c->am_r0; B.gsurf = c->am_gsurf;
+  B.ih2 = c->am_ih2;
+  B.cia_tmin = 0.0; B.cia_tmax = 70000.0;
+  for (int n = 0; n < ntab; n++) {
+    CiaTable *t = c->cia[n];
+    TB_TRY(tb_cia_table_grid(c, t));
+    B.cia_tmin = fmax(B.cia_tmin, t->temp[0]); B.cia_tmax = fmin(B.cia_tmax, t->temp[t->nt - 1]);
+    B.tab_nspec[n] = t->nspec; B.tab_mol[n][0] = t->mol[0]; B.tab_mol[n][1] = t->mol[1];
+    TB_TRY(t->d_f2.ensure(nvl_max * t->nw)); TB_TRY(t->d_z2.ensure(nvl_max * t->nw)); TB_TRY(t->d_v.ensure(nvl_max * t->nw));
+  }
+  if (c->tau_shm_set != (int)shm_tau) {
+    TB_CUDA(cudaFuncSetAttribute(k_tau_transit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm_tau));
+    c->tau_shm_set = (int)shm_tau;
+  }
+  TauPar P;
+  P.eclipse = 0; P.nrad = nrad; P.nh = nh; P.stride = stride; P.nwn = nwn; P.w0 = 0; P.w1 = nwn;
+  P.rfct = c->am_rfct; P.toomuch = toomuch; P.wn_i = c->wn_i; P.wn_d = c->wn_d; P.wn_fct = c->wn_fct;
+  P.sc_flag = c->sc_flag; P.cl_flag = c->cl_flag;
+  P.sc_fac = pow(10.0, c->sc_logext) * TB_E0H2;
+  P.cl_ext = c->cl_ext; P.cl_top = c->cl_top; P.cl_bot = c->cl_bot; P.cl_gamma = c->cl_gamma;
+  P.cl_Q = c->cl_Q; P.cl_r = c->cl_r; P.cl_sig = c->cl_sig; P.cl_refwn = c->cl_refwn;
+  const size_t shm_mod = (5 * (size_t)nh + 2) * sizeof(double);
+  TB_REQUIRE(shm_mod <= 48 * 1024, TB_ERR_ARG, "too many rays (%d) for the modulation kernel's shared memory", nh);
+  TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 8 * sizeof(int32_t), st));
+  c->toomuch = toomuch;
+  tb_timer_begin(c, "batch");
+  for (int a0 = 0; a0 < natm; a0 += Bmax) {
+    const int nb = natm - a0 < Bmax ? natm - a0 : Bmax;
+    const int nvl = nb * nrad;
+    TB_CUDA(cudaMemcpyAsync(c->b_in.p, in + (size_t)a0 * nin, nb * nin * sizeof(double), cudaMemcpyHostToDevice, st));
+    k_atm_setup<<<nb, 128, 0, st>>>(B, nb, c->b_in.p, c->b_p.p, c->d_mol_mass.p, c->b_gtemp.p, c->b_gmol.p, c->b_ltemp.p,
+                                    c->b_traw.p, c->b_dens.p, c->b_rad.p, c->b_ip.p, reinterpret_cast<InterpLayer *>(c->b_L.p),
+                                    c->b_rho.p, c->b_densfac.p, c->b_aux.p, c->d_err.p);
+    TB_TRY(tb_interp_launch(c, nvl, nrad, reinterpret_cast<const InterpLayer *>(c->b_L.p), c->b_rho.p, c->b_e.p));
+    // ---- CIA over nvl layers (every layer is inside every table's range: k_atm_setup flags the others)
+    if (ntab > 0) {
+      CiaPack CP;
+      CiaSplinePack SP;
+      int k = 0, maxrows = 0;
+      for (int n = 0; n < ntab; n++) {
+        CiaTable *t = c->cia[n];
+        if (t->fi >= t->li) continue;
+        CiaDev &D = CP.t[k];
+        D.wn = t->d_wn.p; D.f2 = t->d_f2.p; D.z2 = t->d_z2.p; D.widx = t->d_widx.p;
+        D.densfac = c->b_densfac.p + (size_t)n * nvl;
+        D.fi = (int)t->fi; D.li = (int)t->li; D.fj = 0; D.lj = nvl; D.ntw = t->nw;
+        CiaSplineTab &T = SP.t[k];
+        T.tab = t->d_tab.p; T.zt = t->d_zt.p; T.ttemp = t->d_temp.p; T.h = t->d_h.p; T.rh = t->d_rh.p;
+        T.r = t->d_r.p; T.ru = t->d_ru.p; T.f2 = t->d_f2.p; T.v = t->d_v.p; T.z2 = t->d_z2.p;
+        T.ntw = t->nw; T.ntt = t->nt; T.fj = 0; T.lj = nvl;
+        if (t->nw > maxrows) maxrows = t->nw;
+        k++;
+      }
+      CP.n = k;
+      if (k > 0) {
+        k_cia_temp<<<dim3(nblk((int64_t)maxrows * nvl, 256), k), 256, 0, st>>>(SP, c->b_ltemp.p, nvl);
+        k_cia_wnspline<<<dim3(nblk(nvl, 4), k), 128, 0, st>>>(SP);
+      }
+      k_cia_eval<<<dim3(nblk(nwn, 256), nvl), 256, 0, st>>>(CP, nvl, c->wn_i, c->wn_d, c->wn_fct, nwn, 0, nwn, c->b_ecs.p);
+      c->launches += 3;
+    } else
+      TB_CUDA(cudaMemsetAsync(c->b_ecs.p, 0, sizeof(double) * nvl * nwn, st));
+    // ---- tau + modulation, the atmosphere as a grid dimension
+    TB_CUDA(cudaMemsetAsync(c->b_tau.p, 0, sizeof(double) * nvl * nwn, st));
+    k_ray_geometry<<<nb * nh, 64, 0, st>>>(0, c->b_rad.p, nrad, c->am_rfct, c->b_ip.p, nh, c->am_rfct, stride, c->r_meta.p,
+                                           c->r_par.p, c->r_coef.p, c->r_s.p, c->r_rcp.p, c->d_err.p);
+    k_tau_transit<<<dim3(nblk(nwn, 32), nb), 32 * TAU_NW, shm_tau, st>>>(P, c->b_e.p, c->b_ecs.p, c->b_p.p, c->b_traw.p, c->b_aux.p,
+                                                                        c->b_dens.p, c->d_mol_pol.p, c->d_mol_mass.p, nmol,
+                                                                        c->r_meta.p, c->r_par.p, c->r_coef.p, c->r_rcp.p,
+                                                                        c->b_tau.p, c->b_last.p);
+    k_modulation<<<dim3(nblk(nwn * MOD_QL, 128), nb), 128, shm_mod, st>>>(nwn, 0, nwn, nh, c->b_tau.p, c->b_last.p, c->b_ip.p,
+                                                                         c->am_rfct, toomuch, starrad_cm, transparent,
+                                                                         c->b_out.p, c->d_err.p);
+    c->launches += 5;
+    TB_CUDA(cudaMemcpyAsync(out + (size_t)a0 * nwn, c->b_out.p, (size_t)nb * nwn * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (a0 + Bmax < natm) TB_CUDA(cudaStreamSynchronize(st));   // the batch buffers are reused
+  }
+  tb_timer_end(c, "batch");
+  TB_CUDA(cudaGetLastError());
+  int32_t err[8];
+  TB_CUDA(cudaMemcpyAsync(err, c->d_err.p, sizeof(err), cudaMemcpyDeviceToHost, st));
+  TB_CUDA(cudaStreamSynchronize(st));
+  TB_REQUIRE(err[4] == 0, TB_ERR_DOMAIN, "Sum of abundances of isotopes adds up to more than 1 in some layer of the batch");
+  TB_REQUIRE(err[5] == 0, TB_ERR_DOMAIN, "A layer of the batch has a temperature outside the cross-section tables' range (crosssec.c:293-309)");
+  TB_REQUIRE(err[6] == 0, TB_ERR_DOMAIN, "A layer of the batch has a temperature outside the opacity grid");
+  TB_REQUIRE(err[7] == 0, TB_ERR_DOMAIN, "The reference pressure lies outside the atmosphere, or the hydrostatic radii do not increase");
+  TB_REQUIRE(err[1] == 0, TB_ERR_DOMAIN, "a ray's closest approach lies below the bottom layer (slantpath.c:40-44)");
+  TB_REQUIRE(err[2] == 0, TB_ERR_DOMAIN, "less than 3 items for radial integration (slantpath.c:393-397)");
+  return TB_OK;
 }
