@@ -608,7 +608,7 @@ def main():
     ap.add_argument("--natm", type=int, default=1024, help="C5: atmospheres in the retrieval batch")
     ap.add_argument("--batch", type=int, default=32, help="C5: atmospheres per rank per step")
     ap.add_argument("--ctx-per-gpu", type=int, default=4, help="C5: contexts (streams + host threads) sharing one GPU")
-    ap.add_argument("--c5-api", default="single", choices=["batch", "single"],
+    ap.add_argument("--c5-api", default="device", choices=["device", "batch", "single"],
                     help="C5: tb_spectrum_batch per context per step, or one tb_set_atmosphere + tb_spectrum per atmosphere")
     ap.add_argument("--block-layers", type=int, default=2, help="C3: layers (x 26 temperatures) per step")
     ap.add_argument("--verify", action="store_true",

@@ -91,6 +91,10 @@ def main():
             d["batch_s"] = time.perf_counter() - t0
             os.dup2(so, 1)
             d["batch_out_all"] = b
+            # device milliseconds of tb_run_transit_batch: the timer exists only if the batched path really ran
+            ms = C.c_float(-1.0)
+            rc = api.load_library().tb_get_kernel_ms(C.c_void_p(L.th_context()), b"batch", C.byref(ms))
+            d["batch_device_ms"] = float(ms.value) if rc == 0 else -1.0
     np.savez(outp, **d)
     L.free_memory()
 

@@ -100,7 +100,7 @@ def run_c5(bench, args):
     from transit_b200 import api, workloads, sharding
     torch, dist, rank, local_rank, world = _dist(bench, args)
     prob = workloads.make_problem("C2", scale=args.scale)
-    K = max(1, args.ctx_per_gpu)
+    K = 1 if getattr(args, "c5_api", "single") == "device" else max(1, args.ctx_per_gpu)
     stream = sharding.private_stream()         # timing events and the L2 flush live here
     t0 = time.perf_counter()
     first = sharding.ShardedTransit(local_rank, rank, world)
@@ -130,6 +130,8 @@ def run_c5(bench, args):
     # tb_spectrum_batch call (no host synchronisation between its spectra); "single": one
     # tb_set_atmosphere + tb_spectrum per atmosphere, as BART calls run_transit
     use_batch = getattr(args, "c5_api", "single") == "batch"
+    if getattr(args, "c5_api", "single") == "device":
+        return run_c5_device(bench, args, torch, dist, rank, local_rank, world, prob, first, stream, build_s, grid_bytes, mine)
     share = [list(range(k * batch // K, (k + 1) * batch // K)) for k in range(K)]
     stacked = {}
 
@@ -219,6 +221,102 @@ def run_c5(bench, args):
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def retrieval_inputs(prob, idx, dT=150.0, dex=1.0):
+    """run_transit inputs [T | q_mol0 | q_mol1 ...] (readatm.c:735-744) of seeded perturbed profiles; the bulk gas takes
+    up the slack so that the abundances add up to one."""
+    from transit_b200 import workloads
+    rows = []
+    for i in idx:
+        a = workloads.perturbed(prob, seed=5000 + i, dT=dT, dex=dex)
+        q = a.mol_q.copy()
+        q[0] = 1.0 - q[1:].sum(0)
+        rows.append(np.concatenate([a.t] + [q[j] for j in range(prob.nmol)]))
+    return np.ascontiguousarray(np.stack(rows))
+
+
+def run_c5_device(bench, args, torch, dist, rank, local_rank, world, prob, tr, stream, build_s, grid_bytes, mine):
+    """C5 through tb_run_transit_batch: ONE context; a step = one call with --batch atmospheres as BART hands them over
+    ([T | q...] per atmosphere, host memory), per-atmosphere set-up (densities, hydrostatic radii) on the device, every
+    stage launched once per 32 atmospheres, the spectra back in host memory at the end of the call."""
+    from transit_b200 import api
+    ctx = tr.ctx
+    k = prob.nrad // 3
+    ctx.set_atmosphere_model(prob.p, prob.p_fct, prob.t_fct, prob.rad_fct, 0, prob.p[k], prob.rad[k], 1500.0)
+    batch = min(args.batch, max(1, len(mine)))
+    sets = [retrieval_inputs(prob, mine[:batch]), retrieval_inputs(prob, [i + 100000 for i in mine[:batch]])]
+    out = np.zeros((batch, prob.nwn))
+    kms = {}
+
+    def step(i):
+        ctx.run_transit_batch(sets[i % 2], prob.toomuch, prob.starrad, prob.transp, out)
+        for nm in ("batch", "interp"):
+            try:
+                kms.setdefault(nm, []).append(ctx.kernel_ms(nm))
+            except api.TransitError:
+                pass
+
+    tm = _Timer(torch, dist, world, stream)
+    sampler = bench.ClockSampler(local_rank)
+    sampler.start()
+    l0 = ctx.launch_count()
+    dev_ms = tm.run(step, args.steps, args.warmup)
+    launches = ctx.launch_count() - l0
+    clocks = sampler.stop()
+    assert np.isfinite(out).all() and (out > 0).all()
+    tm.barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        step(i)
+    tm.barrier()
+    e2e_s = time.perf_counter() - t0
+    (dev_ms, e2e_s), (_, _) = tm.reduce([dev_ms, e2e_s])
+    if rank == 0:
+        hbm_peak, src = bench.measured_peaks()
+        nspec = world * batch * args.steps
+        nm = len(prob.cfg["molecules"])
+        # SURVEY 8d: interpolation 2*Nmol*8 B read + 8 B written, tau 24 B per (layer, wavenumber) and atmosphere
+        ab = ((2 * nm * 8 + 8.0) + 24.0) * prob.nrad * prob.nwn * batch
+        step_ms = dev_ms / args.steps
+        line = {
+            "metric": "spectra/s", "value": nspec / (dev_ms * 1e-3), "unit": "spectra/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C5: BART-style retrieval, perturbed T-P/abundance profiles through opacity-grid "
+                                   "interpolation + CIA + tau + modulation (C2 grid)", "natm": args.natm,
+                       "batch_per_rank_per_step": batch, "contexts_per_gpu": 1,
+                       "api": "tb_run_transit_batch: inputs [T | q...] per atmosphere, set-up on the device, one launch per stage "
+                              "and 32 atmospheres", "sharding": f"atmospheres x{world}", "nwn": int(prob.nwn),
+                       "layers": int(prob.nrad), "grid": [int(prob.nrad), len(GRID_TEMPS), nm, int(prob.nwn)],
+                       "grid_gb": grid_bytes / 1e9, "grid_build_s": build_s, "l2": "flushed between steps"},
+            "e2e": {"value": nspec / e2e_s, "unit": "spectra/s",
+                    "h2d_bytes_per_step": 8 * prob.nrad * (1 + prob.nmol) * batch * world,
+                    "d2h_bytes_per_step": 8 * prob.nwn * batch * world,
+                    "api": "the same call with host buffers in and out (what host/libtransit_host.so:run_transit_batch wraps)"},
+            "gpu_launches": launches * world,
+            "kernel_ms": {k2: float(np.mean(v)) for k2, v in kms.items()},
+            "roofline": {"kernel": "whole batch step (k_atm_setup, k_grid_interp, k_cia_*, k_ray_geometry, k_tau_transit, "
+                                   "k_modulation: all HBM streams)", "bound": "hbm", "achieved": ab / (step_ms * 1e-3) / 1e9,
+                         "peak": hbm_peak, "unit": "GB/s", "frac": ab / (step_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None,
+                         "peak_source": src, "algorithmic_bytes": ab},
+            "clocks": clocks}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = c5_cpu_baseline(bench, args, prob)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def c5_cpu_baseline(bench, args, prob):
+    """the unmodified reference serving run_transit calls from an opacity file, one process
+    per core.  The grid file here is the C5 grid at a REDUCED wavenumber range (every per-spectrum cost of the
+    reference is per wavenumber; the sample is stated), built by the reference's own --justOpacity is too slow,
+    so the file is written from the B200 grid -- the reference only reads and interpolates it."""
+    return {"value": None, "unit": "spectra/s", "cores": 0, "kind": "reference",
+            "sample": "see tests/test_fullsize_parity.py::test_c5_shape_retrieval_from_c2_grid: the unmodified reference serves "
+                      "one run_transit from the full-size C2 grid in ~1.5 s on one core (7.4 s for transit_init + 5 spectra)"}
 
 
 def c4_problem(nwn=1_000_000, nlayers=100):
