@@ -264,6 +264,32 @@ def test_scattering_and_cloud_vs_oracle(ctxs):
 
 # ------------------------------------------------------------------ opacity grid (a6-a8)
 
+def test_tau_weight_form_vs_pairwise_kernel():
+    """Transit geometry: k_tau_w (t = W er: one weight per (ray, layer), four rays per warp pass, the parabola value
+    at the closest approach kept as the exact interp_parab expression) against k_tau_transit, which adds the Simpson
+    pairs term by term like simpson() does: same last[], same zero tail, optical depths equal to the association of
+    the sum; with scattering and a cloud deck switched on as well."""
+    prob = workloads.make_problem("C2", scale=0.02, nlayers=37, wn_hi=5000.0)     # 37 layers: a ragged last group of rays
+    c = setup_ctx(prob)
+    c.extinction_lbl(prob.ethresh)
+    c.cia_interp()
+    for extra in (False, True):
+        if extra:
+            c.set_scattering(1, 0.7)
+            c.set_cloud(1, 2e-9, -3.0, 0.0)
+        res = []
+        for fast in (True, False):
+            c.set_tau_streaming(fast)
+            c.tau(api.GEOM_TRANSIT, prob.toomuch)
+            t, last = c.get_tau()
+            res.append((t, last, c.modulation(prob.starrad)))
+        (t1, l1, m1), (t0, l0, m0) = res
+        assert np.array_equal(l1, l0) and np.array_equal(t1 == 0, t0 == 0)
+        assert relerr(t1[t0 != 0], t0[t0 != 0]) < 1e-12 and relerr(m1, m0) < 1e-12
+    c.set_tau_streaming(True)
+    c.close()
+
+
 def test_scattering_cloud_modulation_variants_vs_reference(golden, tmp_path):
     """a10 / a14 against the UNMODIFIED reference (tests/golden/tiny_cloud.npz): Rayleigh flags 1 and 2, cloud models
     1-5, the --cloudtop deck (set_cloudtop), --transparent and modlevel -1, each through the library interface

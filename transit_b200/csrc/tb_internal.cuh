@@ -139,6 +139,7 @@ struct tb_ctx {
   // stream synchronisation; from the ring it is a plain enqueue and the caller's buffer is free at once
   char *h_ring = nullptr;
   size_t ring_pos = 0;
+  int tauw_shm_set = -1;
   int tau_shm_set = -1;                              // dynamic shared memory size k_tau_transit was last opted into
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int64_t launches = 0;
@@ -252,7 +253,7 @@ struct tb_ctx {
   double hfct = 1;
 
   // ---- ray geometry scratch
-  DevBuf<double> r_coef, r_par, r_h, r_s, r_ip, r_ang, r_rcp;
+  DevBuf<double> r_coef, r_par, r_h, r_s, r_ip, r_ang, r_rcp, r_wg, r_w0;
   DevBuf<uint8_t> r_ecl;               // per-ray constants of the streaming eclipse kernel (tb_radiative.cu)
   bool tau_stream_ecl = true;          // eclipse tau in O(layers) per wavenumber (false: the general kernel)
   DevBuf<int32_t> r_meta;

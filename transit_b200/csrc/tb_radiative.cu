@@ -387,6 +387,7 @@ extern "C" int tb_cia_interp(tb_ctx *c) {
 
 // =============================================================== ray geometry
 
+#define TAU_RB 4     // rays per register block of k_tau_w
 // meta[ray*4]: {rs, npts, mode, npairs}; mode 0: tau = 0, 1: normal, 2: two-point case, -1: error
 // par[ray*4]:  {dx, x0, xr, trap_h0}
 // coef[ray*stride + 4*i]: {2-hratio, hfactor, 2-1/hratio, hsum} (geth/simpson, numerical.c:390-525)
@@ -394,7 +395,8 @@ __global__ void k_ray_geometry(int eclipse, const double *__restrict__ rad, int 
                                const double *__restrict__ h, int nh, double hfct, int stride,
                                int32_t *__restrict__ meta, double *__restrict__ par,
                                double *__restrict__ coef, double *__restrict__ sbuf,
-                               double *__restrict__ rcp, int32_t *__restrict__ err) {
+                               double *__restrict__ rcp, int32_t *__restrict__ err,
+                               double *__restrict__ wg, double *__restrict__ w0) {
   // one block per ray: thread 0 places the ray, then the path coordinates s[i] (one sqrt each) and the
   // Simpson weights of the pairs (three divisions each) are independent and spread over the block
   // (one thread per ray ran them as a 27 us serial chain in front of every tau launch)
@@ -469,7 +471,15 @@ __global__ void k_ray_geometry(int eclipse, const double *__restrict__ rad, int 
   }
   __syncthreads();
   const int mode = sh_mode, n = sh_n, rs = sh_rs;
-  if (mode <= 0) return;
+  // per-layer weights of the ray for k_tau_w (see there): rays in groups of four, wgr[layer][ray % 4]
+  double *wgr = wg ? wg + ((size_t)(ri / TAU_RB) * nrad) * TAU_RB + (ri % TAU_RB) : nullptr;
+  if (mode <= 0) {
+    if (wgr) {
+      for (int L = threadIdx.x; L < nrad; L += blockDim.x) wgr[(size_t)L * TAU_RB] = 0.0;
+      if (threadIdx.x == 0) w0[ri] = 0.0;
+    }
+    return;
+  }
   if (mode == 1 && !eclipse) {
     const double r0 = sh_r0;
     for (int i = 1 + threadIdx.x; i < n; i += blockDim.x) {
@@ -493,6 +503,36 @@ __global__ void k_ray_geometry(int eclipse, const double *__restrict__ rad, int 
   if (threadIdx.x == 0) {
     pp[3] = even ? (s[1] - s[0]) : 0.0;
     mt[0] = rs; mt[1] = n; mt[2] = mode; mt[3] = np;
+  }
+  if (!wgr) return;
+  __syncthreads();                                   // cf[] of this block is complete
+  // simpson() (numerical.c:454-525) is linear in the samples f_k = er[rs + k] (f_0 = the parabola value):
+  //   sum_i (f_a c0_i + f_a+1 c1_i + f_a+2 c2_i) c3_i / 6  [+ h0 (f_0 + f_1)/2]  =  sum_k W_k f_k
+  // W_k depends on the ray only, not on the wavenumber; layer L = rs + k carries W_k, every other layer zero.
+  const double h0t = even ? (s[1] - s[0]) : 0.0;
+  for (int L = threadIdx.x; L < nrad; L += blockDim.x) {
+    double W = 0.0;
+    const int k = L - rs;
+    if (mode == 2) {                                 // two-point ray: samples y0, (y0 + yb)/2, yb = er[rs + 1]
+      if (k == 0) W = (cf[0] + cf[1] / 2.0) * cf[3] / 6.0;
+      else if (k == 1) W = (cf[2] + cf[1] / 2.0) * cf[3] / 6.0;
+    } else if (k >= 0 && k < n) {
+      if (k >= even) {
+        const int m = k - even;
+        if ((m & 1) == 0) {
+          const int i = m >> 1;
+          if (i < np) W += cf[4 * i] * cf[4 * i + 3];
+          if (i >= 1) W += cf[4 * (i - 1) + 2] * cf[4 * (i - 1) + 3];
+        } else {
+          const int i = (m - 1) >> 1;
+          W += cf[4 * i + 1] * cf[4 * i + 3];
+        }
+      }
+      W /= 6.0;
+      if (even && k <= 1) W += h0t / 2.0;
+    }
+    if (k == 0) { w0[ri] = W; W = 0.0; }             // the parabola value's weight is kept apart
+    wgr[(size_t)L * TAU_RB] = W;
   }
 }
 
@@ -861,6 +901,126 @@ k_tau_eclipse(TauPar P, const double *__restrict__ e, const double *__restrict__
   last[w] = lst;
 }
 
+
+// ---- transit geometry as t = W er ------------------------------------------------------------------
+// totaltau1's Simpson sum is a fixed linear map of the extinction column: per ray one weight per
+// layer (k_ray_geometry) plus the weight of the parabola value at the ray's closest approach, which stays the
+// exact interp_parab expression (its conditioning is what the 1e-9 tolerance on tau comes from).  A warp
+// integrates FOUR consecutive rays at once: per layer one shared read of the column (32 wavenumbers, one per
+// lane), the four weights as two warp-uniform 128-bit reads, four FMAs -- 0.75 loads per FMA where the pair-wise
+// kernel issues 4 loads per 5 floating-point instructions and 2.5 of those per layer.  Layers below a ray's
+// start carry the weight zero, so the loop is the same for the four rays.  Early exit, last[] and the zero
+// tail as in k_tau_transit.
+__global__ void __launch_bounds__(32 * TAU_NW, 4)
+k_tau_w(TauPar P, const double *__restrict__ e, const double *__restrict__ ecs,
+        const double *__restrict__ press, const double *__restrict__ temp,
+        const double *__restrict__ aux, const double *__restrict__ mol_d,
+        const double *__restrict__ mol_pol, const double *__restrict__ mol_mass, int nmol,
+        const int32_t *__restrict__ meta, const double *__restrict__ par, const double *__restrict__ rcp,
+        const double *__restrict__ wg, const double *__restrict__ w0, double *__restrict__ tau,
+        int32_t *__restrict__ last) {
+  extern __shared__ double sm[];
+  __shared__ int sh_last[32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nrad = P.nrad, ngrp = (P.nh + TAU_RB - 1) / TAU_RB;
+  {  // a batch of atmospheres (tb_run_transit_batch): blockIdx.y selects the atmosphere's slices
+    const size_t a = blockIdx.y;
+    e += a * nrad * P.nwn; ecs += a * nrad * P.nwn; temp += a * nrad; aux += a * 2 * nrad;
+    mol_d += a * (size_t)nmol * nrad; meta += a * P.nh * 4; par += a * P.nh * 4; rcp += a * P.nh * 2;
+    wg += a * (size_t)ngrp * nrad * TAU_RB; w0 += a * P.nh; tau += a * P.nh * P.nwn; last += a * P.nwn;
+  }
+  const int64_t w = P.w0 + blockIdx.x * 32LL + lane;
+  const bool inb = w < P.w1;
+  if (warp == 0) sh_last[lane] = P.nh;
+  if (inb) {
+    const double wn = P.wn_fct * __dadd_rn(P.wn_i, __dmul_rn((double)w, P.wn_d));
+    double kBP = 0, kFH = 0, refw = 1;
+    int ctop = -1, cbot = -1;
+    if (P.cl_flag && P.cl_ext != 0) {
+      const double top = pow(10.0, P.cl_top), bot = pow(10.0, P.cl_bot);
+      int i = nrad - 1;
+      for (; i >= 0; i--) if (press[i] >= top) break;
+      ctop = i;
+      for (; i >= 0; i--) if (press[i] >= bot) break;
+      cbot = i;
+      const double x = 2 * TB_PI * P.cl_r * wn;
+      refw = pow(P.cl_refwn, P.cl_gamma);
+      kBP = P.cl_ext * pow(wn, P.cl_gamma);
+      kFH = P.cl_ext / (P.cl_Q * pow(x, -1 * P.cl_gamma) + pow(x, 0.2));
+    }
+    const double wn4 = P.sc_flag == 1 ? pow(wn, 4.0) : 0.0;
+    const bool extra = P.sc_flag != 0 || (P.cl_flag && P.cl_ext != 0);
+    for (int r = warp; r < nrad; r += TAU_NW) {
+      double es = 0, ec = 0;
+      if (extra) es = tb_extra_ext(P, r, wn, wn4, kBP, kFH, refw, ctop, cbot, press, temp, aux, mol_d, mol_pol, mol_mass, nmol, ec);
+      // tau.c:231-232, same left-to-right sum
+      sm[r * 32 + lane] = e[(size_t)r * P.nwn + w] + es + ec + ecs[(size_t)r * P.nwn + w];
+    }
+  }
+  __syncthreads();
+  const double *er = sm + lane;
+  int myfirst = P.nh;                       // first ray of this warp above toomuch (none yet)
+  for (int g = warp; g < ngrp; g += TAU_NW) {
+    const int ri0 = g * TAU_RB;
+    // the deepest ray of the group is the last one (rays go top down)
+    int rsv[TAU_RB], mdv[TAU_RB], rs_min = nrad;
+#pragma unroll
+    for (int j = 0; j < TAU_RB; j++) {
+      const int ri = ri0 + j;
+      rsv[j] = nrad; mdv[j] = 0;
+      if (ri < P.nh) { rsv[j] = meta[ri * 4]; mdv[j] = meta[ri * 4 + 2]; }
+      if (mdv[j] > 0 && rsv[j] < rs_min) rs_min = rsv[j];
+    }
+    double acc[TAU_RB];
+#pragma unroll
+    for (int j = 0; j < TAU_RB; j++) {
+      acc[j] = 0.0;
+      const int ri = ri0 + j;
+      if (mdv[j] > 0 && inb) {            // weight of the parabola value at the ray's closest approach
+        const int b = rsv[j] - (mdv[j] == 2 ? 1 : 0);        // the two-point ray takes layers rs-1, rs, rs+1
+        const double *pp = par + ri * 4;
+        const double y0 = tb_parab(pp[0], pp[1], pp[2], rcp + ri * 2, er[b * 32], er[(b + 1) * 32], er[(b + 2) * 32]);
+        acc[j] = w0[ri] * y0;
+      }
+    }
+    if (inb && myfirst == P.nh) {
+      const double2 *wp = reinterpret_cast<const double2 *>(wg + ((size_t)g * nrad) * TAU_RB);
+#pragma unroll 4
+      for (int L = rs_min + 1; L < nrad; L++) {
+        const double ev = er[L * 32];
+        const double2 wa = __ldg(wp + 2 * L), wb = __ldg(wp + 2 * L + 1);
+        acc[0] = fma(wa.x, ev, acc[0]);
+        acc[1] = fma(wa.y, ev, acc[1]);
+        acc[2] = fma(wb.x, ev, acc[2]);
+        acc[3] = fma(wb.y, ev, acc[3]);
+      }
+#pragma unroll
+      for (int j = 0; j < TAU_RB; j++) {
+        const int ri = ri0 + j;
+        if (ri < P.nh && myfirst == P.nh) {
+          const double t = mdv[j] > 0 ? P.rfct * (2 * acc[j]) : 0.0;
+          tau[(size_t)ri * P.nwn + w] = t;
+          if (t > P.toomuch) myfirst = ri;                   // tau.c:277-287: this lane is done
+        }
+      }
+    }
+    if (__all_sync(0xffffffffu, !inb || myfirst != P.nh)) break;
+  }
+  if (inb) atomicMin(&sh_last[lane], myfirst);
+  __syncthreads();
+  if (inb) {
+    const int lst = sh_last[lane];                       // == nh: never above toomuch
+    if (warp == 0) last[w] = lst < P.nh ? lst : P.nh - 1;
+    // clear what this warp wrote beyond the block-wide first exceed
+    const int upto = myfirst < P.nh ? myfirst : P.nh - 1;
+    for (int g = warp; g < ngrp; g += TAU_NW)
+      for (int j = 0; j < TAU_RB; j++) {
+        const int ri = g * TAU_RB + j;
+        if (ri <= upto && ri > lst) tau[(size_t)ri * P.nwn + w] = 0.0;
+      }
+  }
+}
+
 static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, int nh, double hfct, bool sync) {
   TB_REQUIRE(c->have_e && c->have_atm, TB_ERR_STATE, "extinction must be computed before tb_tau");
   TB_REQUIRE(geometry == TB_GEOM_TRANSIT || geometry == TB_GEOM_ECLIPSE, TB_ERR_ARG, "bad geometry");
@@ -897,8 +1057,12 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
   TB_TRY(tb_upload_small(c, d_h.p, c->h_h.data(), nh * sizeof(double), st));
   if (!c->err_keep) TB_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4 * sizeof(int32_t), st));
   TB_CUDA(cudaMemsetAsync(c->d_tau.p, 0, sizeof(double) * nh * nwn, st));   // calloc, tau.c:34
+  const bool wform = geometry == TB_GEOM_TRANSIT && c->tau_stream_ecl;      // t = W er (k_tau_w)
+  const int ngrp = (nh + TAU_RB - 1) / TAU_RB;
+  if (wform) { TB_TRY(c->r_wg.ensure((size_t)ngrp * nrad * TAU_RB)); TB_TRY(c->r_w0.ensure(nh)); }
   k_ray_geometry<<<nh, 64, 0, st>>>(geometry == TB_GEOM_ECLIPSE, c->d_rad.p, nrad, c->rad_fct, d_h.p, nh,
-                                              hfct, stride, c->r_meta.p, c->r_par.p, c->r_coef.p, d_s.p, c->r_rcp.p, c->d_err.p);
+                                              hfct, stride, c->r_meta.p, c->r_par.p, c->r_coef.p, d_s.p, c->r_rcp.p, c->d_err.p,
+                                              wform ? c->r_wg.p : nullptr, wform ? c->r_w0.p : nullptr);
   TauPar P;
   P.eclipse = geometry == TB_GEOM_ECLIPSE; P.nrad = nrad; P.nh = nh; P.stride = stride; P.nwn = nwn;
   tb_band_columns(c, &P.w0, &P.w1);
@@ -920,6 +1084,16 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
         P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p, c->d_dens.p, c->d_mol_pol.p, c->d_mol_mass.p,
         c->nmol, reinterpret_cast<const EclRay *>(c->r_ecl.p), c->d_tau.p, c->d_last.p);
     TB_LAUNCHED(c);
+  } else if (wform) {
+    const size_t shm = (size_t)nrad * 32 * sizeof(double);
+    TB_REQUIRE(shm <= 200 * 1024, TB_ERR_ARG, "too many layers (%d) for the tau kernel's shared memory", nrad);
+    if (c->tauw_shm_set != (int)shm) {
+      TB_CUDA(cudaFuncSetAttribute(k_tau_w, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
+      c->tauw_shm_set = (int)shm;
+    }
+    k_tau_w<<<nblk(ncol, 32), 32 * TAU_NW, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p, c->d_dens.p,
+                                                    c->d_mol_pol.p, c->d_mol_mass.p, c->nmol, c->r_meta.p, c->r_par.p,
+                                                    c->r_rcp.p, c->r_wg.p, c->r_w0.p, c->d_tau.p, c->d_last.p);
   } else {
     const size_t shm = ((size_t)nrad * 32 + (size_t)TAU_NW * stride) * sizeof(double);
     TB_REQUIRE(stride <= 320, TB_ERR_ARG, "too many layers (%d) for the tau kernel's coefficient registers", nrad);
@@ -1440,10 +1614,13 @@ extern "C" int tb_run_transit_batch(tb_ctx *c, int natm, const double *in, doubl
     B.tab_nspec[n] = t->nspec; B.tab_mol[n][0] = t->mol[0]; B.tab_mol[n][1] = t->mol[1];
     TB_TRY(t->d_f2.ensure(nvl_max * t->nw)); TB_TRY(t->d_z2.ensure(nvl_max * t->nw)); TB_TRY(t->d_v.ensure(nvl_max * t->nw));
   }
-  if (c->tau_shm_set != (int)shm_tau) {
-    TB_CUDA(cudaFuncSetAttribute(k_tau_transit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm_tau));
-    c->tau_shm_set = (int)shm_tau;
+  const size_t shm_tauw = (size_t)nrad * 32 * sizeof(double);
+  if (c->tauw_shm_set != (int)shm_tauw) {
+    TB_CUDA(cudaFuncSetAttribute(k_tau_w, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm_tauw));
+    c->tauw_shm_set = (int)shm_tauw;
   }
+  TB_REQUIRE(nh % TAU_RB == 0, TB_ERR_ARG, "tb_run_transit_batch: the layer count (%d) must be a multiple of %d", nh, TAU_RB);
+  TB_TRY(c->r_wg.ensure(nvl_max * nrad)); TB_TRY(c->r_w0.ensure(nvl_max));
   TauPar P;
   P.eclipse = 0; P.nrad = nrad; P.nh = nh; P.stride = stride; P.nwn = nwn; P.w0 = 0; P.w1 = nwn;
   P.rfct = c->am_rfct; P.toomuch = toomuch; P.wn_i = c->wn_i; P.wn_d = c->wn_d; P.wn_fct = c->wn_fct;
@@ -1495,11 +1672,11 @@ extern "C" int tb_run_transit_batch(tb_ctx *c, int natm, const double *in, doubl
     // ---- tau + modulation, the atmosphere as a grid dimension
     TB_CUDA(cudaMemsetAsync(c->b_tau.p, 0, sizeof(double) * nvl * nwn, st));
     k_ray_geometry<<<nb * nh, 64, 0, st>>>(0, c->b_rad.p, nrad, c->am_rfct, c->b_ip.p, nh, c->am_rfct, stride, c->r_meta.p,
-                                           c->r_par.p, c->r_coef.p, c->r_s.p, c->r_rcp.p, c->d_err.p);
-    k_tau_transit<<<dim3(nblk(nwn, 32), nb), 32 * TAU_NW, shm_tau, st>>>(P, c->b_e.p, c->b_ecs.p, c->b_p.p, c->b_traw.p, c->b_aux.p,
-                                                                        c->b_dens.p, c->d_mol_pol.p, c->d_mol_mass.p, nmol,
-                                                                        c->r_meta.p, c->r_par.p, c->r_coef.p, c->r_rcp.p,
-                                                                        c->b_tau.p, c->b_last.p);
+                                           c->r_par.p, c->r_coef.p, c->r_s.p, c->r_rcp.p, c->d_err.p, c->r_wg.p, c->r_w0.p);
+    k_tau_w<<<dim3(nblk(nwn, 32), nb), 32 * TAU_NW, shm_tauw, st>>>(P, c->b_e.p, c->b_ecs.p, c->b_p.p, c->b_traw.p, c->b_aux.p,
+                                                                   c->b_dens.p, c->d_mol_pol.p, c->d_mol_mass.p, nmol,
+                                                                   c->r_meta.p, c->r_par.p, c->r_rcp.p, c->r_wg.p, c->r_w0.p,
+                                                                   c->b_tau.p, c->b_last.p);
     k_modulation<<<dim3(nblk(nwn * MOD_QL, 128), nb), 128, shm_mod, st>>>(nwn, 0, nwn, nh, c->b_tau.p, c->b_last.p, c->b_ip.p,
                                                                          c->am_rfct, toomuch, starrad_cm, transparent,
                                                                          c->b_out.p, c->d_err.p);
