@@ -86,6 +86,7 @@ int  tb_get_sample_counts(tb_ctx *c, int64_t *nsamples, int ns);
  * per-line records tb_get_line_trace reads (off by default: 16 B of HBM per (group, state)).
  * tb_get_fused_stats: states of the last batch taken by the fused kernel and its executed profile updates. */
 int  tb_set_fused(tb_ctx *c, int on);
+int  tb_set_fused_reach(tb_ctx *c, int rmax);   /* widest reach (coarse bins) of a fused state; default 8 */
 int  tb_set_trace(tb_ctx *c, int on);
 int  tb_get_fused_stats(tb_ctx *c, int64_t *fused_states, int64_t *fused_samples);
 /* ilor[niso] of state `s` of the last batch (extinction.c:394); with the trace's idop it names the Voigt cell */

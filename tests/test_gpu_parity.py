@@ -157,25 +157,31 @@ def test_fused_line_sum_vs_two_kernel_path():
     """k_linesum_fused (strength + gather in one kernel, records in shared memory) against k_strength +
     k_accumulate on the same states: the states of narrow reach add in the same order and must agree BIT FOR BIT,
     per-line decisions and sample counts included; states the two-kernel path sums with its wide-reach schedule
-    (reach 3..8 bins) differ by summation order only.  Both geometries of the batch: collapsed and per molecule."""
+    differ by summation order only.  The fused states include layers whose lines partly keep a CARRIED Doppler index
+    (extinction.c:480-483), found there by k_lastq_scan instead of k_strength's maxima: same per-line indices.
+    Both geometries of the batch: collapsed and per molecule; and with every layer fused (reach limit lifted)."""
     prob = workloads.make_problem("C2", scale=0.05, nlayers=40, wn_hi=12000.0)
     c = setup_ctx(prob)
     T = prob.t * prob.t_fct
     dens, Z = prob.mol_d.T.copy(), prob.iso_z.T.copy()
-    for permol in (0, 1):
+    for permol, rmax in ((0, 8), (1, 8), (0, 4096)):
         c.set_fused(2)                     # 2: fused whatever the size of the grid
+        c.set_fused_reach(rmax)
         a = c.molext_states(T, dens, Z, prob.ethresh, permol=permol)
         st = c.fused_stats()
         na = c.sample_counts(prob.nrad)
-        tr_a = [c.line_trace(r) for r in (prob.nrad - 1, prob.nrad // 2)]
+        tr_layers = (prob.nrad - 1, prob.nrad // 2, 12, 8, 0)
+        tr_a = [c.line_trace(r) for r in tr_layers]
         a2 = c.molext_states(T, dens, Z, prob.ethresh, permol=permol)
         assert np.array_equal(a, a2)                                   # deterministic
         c.set_fused(False)
         b = c.molext_states(T, dens, Z, prob.ethresh, permol=permol)
         nb = c.sample_counts(prob.nrad)
-        tr_b = [c.line_trace(r) for r in (prob.nrad - 1, prob.nrad // 2)]
+        tr_b = [c.line_trace(r) for r in tr_layers]
         assert c.fused_stats()["fused_states"] == 0
         assert st["fused_states"] >= 16 and st["fused_states"] % 8 == 0, st   # the upper layers of this atmosphere
+        if rmax == 4096:
+            assert st["fused_states"] == prob.nrad, st
         assert np.array_equal(na, nb)                                  # same profile updates, layer by layer
         assert st["fused_samples"] == int(na[prob.nrad - st["fused_states"]:].sum()) or st["fused_samples"] > 0
         for x, y in zip(tr_a, tr_b):
@@ -184,8 +190,8 @@ def test_fused_line_sum_vs_two_kernel_path():
         assert np.array_equal(a == 0, b == 0)
         assert relerr(a, b) < 1e-13
         same = [r for r in range(prob.nrad) if np.array_equal(a[r], b[r])]
-        assert len(same) >= prob.nrad - 8, (len(same), prob.nrad)      # only the few reach-3..8 layers may differ in order
-    c.set_fused(1)
+        assert len(same) >= prob.nrad // 2, (len(same), prob.nrad)     # only the layers of reach > 2 bins may differ in order
+    c.set_fused(1); c.set_fused_reach(8)
     c.close()
 
 

@@ -181,6 +181,9 @@ struct tb_ctx {
   DevBuf<double> g_wavn;       // leader wavenumber, sorted order
   DevBuf<double> g_a0, g_gf, g_lg;   // leader: -EXPCTE*efct*elow, gf, log(gf) (+inf for co-add groups)
   DevBuf<double> go_wavn;      // leader wavenumber, original group order
+  DevBuf<int32_t> go_pos;      // sorted position of every original group
+  DevBuf<int32_t> iso_og0, iso_og1;   // [niso] range of original groups of each isotope (one run each: og_contig)
+  bool og_contig = true;
   DevBuf<int32_t> binstart;    // [nrows][nwn+1]
   DevBuf<int32_t> substart;    // [nrows][nsub]: finer start index for the narrow path (tb_lines.cu)
   int64_t nsub = 0;
@@ -228,7 +231,8 @@ struct tb_ctx {
   DevBuf<int32_t> s_ilor, s_idop0, s_lastq, s_fb, s_fbpid, s_wtile, s_reach, s_reachP, s_fbmax;
   DevBuf<double> s_facz, s_rtemp, s_ral, s_xterm, s_lcz;
   DevBuf<LineRec> s_rec;      // [state][group]
-  DevBuf<int32_t> s_fclass, s_fP;   // per batch of 8 states: taken by k_linesum_fused? / widest half-size (fine bins)
+  DevBuf<int32_t> s_fclass, s_fP, s_lastq2;   // s_lastq2: carried-index source of the fused states (k_lastq_scan)
+  int fuse_rmax = 8;   // per batch of 8 states: taken by k_linesum_fused? / widest half-size (fine bins)
   int fuse_enabled = 1;          // 0 off, 1 on where the grid has enough tiles, 2 always (tests)
   bool trace_enabled = false;
   int fuse_shm_set = -1, last_chunk_s0 = 0, last_chunk_cs = 0;

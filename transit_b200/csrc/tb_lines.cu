@@ -142,6 +142,21 @@ __global__ void k_group_fill(const int32_t *__restrict__ order, const int32_t *_
   }
 }
 
+// position of every group (original, i.e. file order) in the sorted order, and the contiguous range of original
+// groups each isotope occupies (TLI order: by isotope, then ascending wavelength) -- what k_lastq_scan walks
+__global__ void k_group_pos(int64_t G, const int32_t *__restrict__ g_orig, int32_t *__restrict__ go_pos) {
+  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (p < G) go_pos[g_orig[p]] = (int32_t)p;
+}
+__global__ void k_iso_ranges(int64_t G, const int32_t *__restrict__ go_pos, const int16_t *__restrict__ g_iso,
+                             int32_t *__restrict__ og0, int32_t *__restrict__ og1, int32_t *__restrict__ nruns) {
+  const int64_t og = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (og >= G) return;
+  const int iso = g_iso[go_pos[og]];
+  if (og == 0 || g_iso[go_pos[og - 1]] != iso) { og0[iso] = (int32_t)og; atomicAdd(&nruns[iso], 1); }
+  if (og == G - 1 || g_iso[go_pos[og + 1]] != iso) og1[iso] = (int32_t)og + 1;
+}
+
 // the strength-maximum pass wants the lines with the largest state-independent factor first
 __global__ void k_q_keys(int64_t M, const double *__restrict__ m_gf, const int16_t *__restrict__ m_iso,
                          const uint8_t *__restrict__ m_inr, const double *__restrict__ iso_mass,
@@ -292,6 +307,7 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
   if (G == 0) {
     TB_CUDA(cudaMemsetAsync(c->binstart.p, 0, (nkeys + 1) * sizeof(int32_t), st));
     c->have_lines = true;
+    c->og_contig = true;
     return TB_OK;
   }
   TB_TRY(key.ensure(G)); TB_TRY(key_s.ensure(G)); TB_TRY(ord.ensure(G)); TB_TRY(ord_s.ensure(G)); TB_TRY(idw.ensure(G));
@@ -347,7 +363,22 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
   TB_TRY(c->substart.ensure((size_t)c->nrows * c->nsub));
   k_substart<<<nblk((int64_t)c->nrows * c->nsub, T), T, 0, st>>>(key_s.p, G, c->nrows, c->nsub, c->onwn, c->o,
                                                                c->nsube, c->substart.p);
-  c->launches += 9;
+  {  // original (file) order -> sorted position, isotope ranges in file order (k_lastq_scan)
+    TB_TRY(c->go_pos.ensure(G)); TB_TRY(c->iso_og0.ensure(c->niso + 1)); TB_TRY(c->iso_og1.ensure(c->niso + 1));
+    DevBuf<int32_t> nruns;
+    TB_TRY(nruns.ensure(c->niso + 1));
+    TB_CUDA(cudaMemsetAsync(c->iso_og0.p, 0, (c->niso + 1) * sizeof(int32_t), st));
+    TB_CUDA(cudaMemsetAsync(c->iso_og1.p, 0, (c->niso + 1) * sizeof(int32_t), st));
+    TB_CUDA(cudaMemsetAsync(nruns.p, 0, (c->niso + 1) * sizeof(int32_t), st));
+    k_group_pos<<<nblk(G, T), T, 0, st>>>(G, c->g_orig.p, c->go_pos.p);
+    k_iso_ranges<<<nblk(G, T), T, 0, st>>>(G, c->go_pos.p, c->g_iso.p, c->iso_og0.p, c->iso_og1.p, nruns.p);
+    std::vector<int32_t> h(c->niso + 1, 0);
+    TB_CUDA(cudaMemcpyAsync(h.data(), nruns.p, (c->niso + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    TB_CUDA(cudaStreamSynchronize(st));
+    c->og_contig = true;                 // every isotope's lines form ONE run of the list (the TLI order)
+    for (int i = 0; i < c->niso; i++) if (h[i] > 1) c->og_contig = false;
+  }
+  c->launches += 11;
   {  // strength-ordered copy of the in-range member lines for k_kmax
     DevBuf<double> qk, qk_s;
     DevBuf<int32_t> qi, qi_s;
@@ -388,6 +419,7 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
 #define PID_NOREACH 0x4000u   // + cell: evaluated, but the profile covers no grid point (nothing to add)
 #define PID_DEAD(pid) (((pid) & 0xC000u) == 0x4000u)   // PID_SKIP or PID_NOREACH: the line sum passes over it
 #define ACC_TILE 128       // output bins per block of k_accumulate (4 warps x 32 bins)
+#define FB 8               // states per batch: k_strength<8>'s block, the unit the fused / two-kernel choice is made for
 #define MAXISO_SH 128      // isotopes handled with shared-memory maxima in k_strength
 
 // exact x / d for 0 <= x < 2^32 by one 64x64->high multiply (d fixed per context)
@@ -767,7 +799,7 @@ __global__ void __launch_bounds__(256, 6) k_strength(int64_t G, StrRanges rg, in
 
 // carried Doppler index per (state, isotope): the index left by the last evaluated line that
 // refreshed it, else the one computed at wn[0] (extinction.c:393,480-483).
-__global__ void k_fallback(int ns, int niso, const int32_t *__restrict__ lastq,
+__global__ void k_fallback(int ns, int niso, const int32_t *__restrict__ fclass, int which, const int32_t *__restrict__ lastq,
                            const int32_t *__restrict__ idop0, const double *__restrict__ go_wavn,
                            const double *__restrict__ alphad, const int32_t *__restrict__ ilor,
                            const double *__restrict__ aDop, int nDop, int nLor,
@@ -776,6 +808,7 @@ __global__ void k_fallback(int ns, int niso, const int32_t *__restrict__ lastq,
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= ns * niso) return;
   int s = t / niso;
+  if ((fclass[s / FB] != 0) != (which != 0)) return;    // which = 1: the fused states (lastq from k_lastq_scan), 0: the others
   int q = lastq[t];
   int id = (q < 0) ? idop0[t] : tb_binsearchapprox(aDop, __dmul_rn(alphad[t], go_wavn[q]), 0, nDop);
   fb[t] = id;
@@ -1033,18 +1066,17 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
 // The sum of a bin runs over rows, chunks and records in sorted (row, fine bin) order: the same fixed
 // order, the same FMA chain and therefore the same bits as the unfused narrow path; tiles are independent,
 // so band shards stay bit-identical.  No floating-point atomics.
-#define FB 8                 // states per classification batch (same batching as k_strength<SBS = 8>)
 #define FBK 4                // states per block of the fused kernel
 #define FPT (FBK / 2)        // states per thread in phase 3 (two threads per bin)
 #define FUSE_BLOCKS 4        // resident blocks per SM the kernel is compiled for (64 registers)
 #define FUSE_CAPA 512        // alive groups per chunk (two full passes of phase 2)
 #define FUSE_NT 256
 #define FUSE_MAXISO 64
-#define FUSE_RMAX 8          // widest reach, in coarse bins, of a fused state
+#define FUSE_RMAX 8          // default widest reach, in coarse bins, of a fused state (tb_set_fused_reach)
 #define FUSE_MIN_TILES 96     // grids with fewer 128-bin tiles keep the two-kernel path (tb_set_fused(c, 2) forces fusion)
 
 // Which batches of FB states the fused kernel takes (decided on the device: no read-back on the way)
-__global__ void k_fuse_class(int ns, int niso, double wn_i, double own_last, int o, int enable,
+__global__ void k_fuse_class(int ns, int niso, double wn_i, double own_last, int o, int enable, int need_refresh, int rmax,
                              const double *__restrict__ alphad, const double *__restrict__ ral,
                              const int32_t *__restrict__ ilor, const double *__restrict__ aDop, int nDop, int nLor,
                              const ProfEntry *__restrict__ ptab, int32_t *__restrict__ fclass,
@@ -1059,7 +1091,7 @@ __global__ void k_fuse_class(int ns, int niso, double wn_i, double own_last, int
     const int si = s * niso + iso;
     const double ad = alphad[si];
     // every in-range line has wavn >= wn_i: alphad*wavn/alphal >= this, with a margin far above rounding
-    if (!(__dmul_rn(ad, wn_i) * ral[si] >= 0.1000001)) sh_ok = 0;
+    if (need_refresh && !(__dmul_rn(ad, wn_i) * ral[si] >= 0.1000001)) sh_ok = 0;
     // ... and wavn <= own_last: no line takes a Doppler cell beyond this one (nearest-cell search is monotone)
     const int id = tb_binsearchapprox(aDop, __dmul_rn(ad, own_last), 0, nDop);
     atomicMax(&sh_P, ptab[id * nLor + ilor[si]].psize);
@@ -1067,7 +1099,7 @@ __global__ void k_fuse_class(int ns, int niso, double wn_i, double own_last, int
   __syncthreads();
   if (threadIdx.x == 0) {
     const int P = sh_P;
-    const long long lim = (long long)FUSE_RMAX * o < 32767 ? (long long)FUSE_RMAX * o : 32767;
+    const long long lim = (long long)rmax * o < 0x3fffffff ? (long long)rmax * o : 0x3fffffff;
     fclass[blockIdx.x] = (enable && sh_ok && niso >= 1 && niso <= FUSE_MAXISO && P <= lim) ? 1 : 0;
     fP[blockIdx.x] = P;
   }
@@ -1084,8 +1116,68 @@ __global__ void k_fuse_trace_fill(int64_t G, int ns, const int32_t *__restrict__
   rec[(size_t)s * G + p] = r;
 }
 
+
+// extinction.c:480-483 as k_strength decides it: refresh the isotope's Doppler index at this line?
+__device__ __forceinline__ bool tb_refresh(double adw, double al, double ral) {
+  const double qa = adw * ral;
+  return fabs(qa - 1e-1) > 1e-12 ? qa >= 1e-1 : adw / al >= 1e-1;
+}
+
+// Is group q evaluated at state s (extinction.c:439-470)?  The expressions of k_strength / k_linesum_fused.
+__device__ __forceinline__ bool tb_group_evaluated(int q, size_t sX, double rT, double fz, double thr,
+                                                   const int32_t *__restrict__ g_start, const double *__restrict__ g_gf,
+                                                   const double *__restrict__ g_a0, const double *__restrict__ g_wavn,
+                                                   const double *__restrict__ xterm) {
+  const int b = g_start[q], e = g_start[q + 1];
+  const double ge1 = __dmul_rn(g_gf[q], tb_exp(g_a0[q] * rT));
+  if ((e - b == 1) && ge1 * fz < 0.999999 * thr) return false;
+  double a = __dmul_rn(ge1, (1 - tb_exp(__dmul_rn(-TB_EXPCTE, g_wavn[q]) * rT)));
+  for (int l = b + 1; l < e; l++) a = __dadd_rn(a, xterm[sX + (l - q - 1)]);
+  return !(__dmul_rn(a, fz) < thr);
+}
+
+// The carried Doppler index without walking the list (extinction.c:480-483): per (state, isotope) the reference
+// leaves, for the lines that do not refresh it, the index of the LAST line in file order that did refresh it and
+// was evaluated.  An isotope's lines come in one run of descending wavenumber, and "refreshes" is monotone in the
+// wavenumber, so the refreshing lines are a prefix of the run: bisect its end, then scan backwards, 32 groups per
+// step, for the first evaluated one.  One warp per (state, isotope); nothing here depends on a band shard.
+__global__ void k_lastq_scan(int ns, int niso, int nrows, int permol, double ethresh,
+                             const int32_t *__restrict__ iso_og0, const int32_t *__restrict__ iso_og1,
+                             const int32_t *__restrict__ go_pos, const double *__restrict__ go_wavn,
+                             const int32_t *__restrict__ g_start, const double *__restrict__ g_gf,
+                             const double *__restrict__ g_a0, const double *__restrict__ g_wavn,
+                             const double *__restrict__ rtemp, const double *__restrict__ facz,
+                             const double *__restrict__ kmax, const int *__restrict__ iso_row,
+                             const double *__restrict__ alphal, const double *__restrict__ alphad,
+                             const double *__restrict__ ral, const double *__restrict__ xterm, int64_t X,
+                             const int32_t *__restrict__ fclass, int32_t *__restrict__ lastq) {
+  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (wid >= ns * niso) return;
+  const int s = wid / niso, iso = wid % niso;
+  if (!fclass[s / FB]) return;                   // k_strength finds it for the states it evaluates
+  const int og0 = iso_og0[iso], og1 = iso_og1[iso];
+  int res = -1;
+  if (og1 > og0) {
+    const double al = alphal[wid], ad = alphad[wid], rl = ral[wid];
+    int l = og0, h = og1;                          // first group of the run that does NOT refresh
+    while (l < h) {
+      const int mid = (l + h) >> 1;
+      if (tb_refresh(__dmul_rn(ad, go_wavn[mid]), al, rl)) l = mid + 1; else h = mid;
+    }
+    const double rT = rtemp[s], fz = facz[wid];
+    const double thr = __dmul_rn(ethresh, kmax[s * nrows + (permol ? iso_row[iso] : 0)]);
+    for (int base = l - 1; base >= og0; base -= 32) {
+      const int og = base - lane;
+      const bool ok = og >= og0 && tb_group_evaluated(go_pos[og], (size_t)s * X, rT, fz, thr, g_start, g_gf, g_a0, g_wavn, xterm);
+      const unsigned ball = __ballot_sync(0xffffffffu, ok);
+      if (ball) { res = base - (__ffs(ball) - 1); break; }
+    }
+  }
+  if (lane == 0) lastq[wid] = res;
+}
+
 struct FuseTab {           // per (state of the block, isotope), in shared memory
-  double lcz, facz, thr, densf, alphad;
+  double lcz, facz, thr, densf, alphad, alphal, ral;
 };
 // What phase 2 leaves per (alive group, state) for phase 3: the strength and everything the gather needs
 // as one 128-bit shared-memory read.  The profile sample bin j of the tile takes is pdata[A + j]:
@@ -1109,6 +1201,7 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
                 const double *__restrict__ xterm, int64_t X, float dop_lmin, float dop_rstep,
                 const double *__restrict__ dens, const int *__restrict__ iso_imol, const int *__restrict__ iso_row,
                 const double *__restrict__ alphad, const int32_t *__restrict__ ilor,
+                const double *__restrict__ alphal, const double *__restrict__ ral, const int32_t *__restrict__ fbpid,
                 const double *__restrict__ aDop, int nDop, const ProfEntry *__restrict__ ptab, int nLor,
                 double ethresh, const double *__restrict__ kmax, const double *__restrict__ pdata,
                 double *__restrict__ out, unsigned long long *__restrict__ nsamp, LineRec *__restrict__ rec_out) {
@@ -1123,7 +1216,8 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
   double *sh_rT = sh_aDop + 256;                                                 // [FBK]
   FuseTab *sh_tab = reinterpret_cast<FuseTab *>(sh_rT + FBK);                    // [FBK][niso]
   int *sh_ilor = reinterpret_cast<int *>(sh_tab + FBK * niso);                   // [FBK][niso]
-  unsigned char *sh_mask = reinterpret_cast<unsigned char *>(sh_ilor + FBK * niso);  // [CAPA]
+  int *sh_fbpid = sh_ilor + FBK * niso;                                          // [FBK][niso] carried cell
+  unsigned char *sh_mask = reinterpret_cast<unsigned char *>(sh_fbpid + FBK * niso);  // [CAPA]
   __shared__ int sh_wcnt[2][FUSE_NT / 32];
   __shared__ int sh_Prow[16];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -1141,9 +1235,10 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
     t.lcz = lcz[si]; t.facz = facz[si];
     t.thr = __dmul_rn(ethresh, kmax[s * nrows + (permol ? iso_row[iso] : 0)]);
     t.densf = dens[s * nmol + iso_imol[iso]];
-    t.alphad = alphad[si];
+    t.alphad = alphad[si]; t.alphal = alphal[si]; t.ral = ral[si];
     sh_tab[i] = t;
     sh_ilor[i] = ilor[si];
+    sh_fbpid[i] = fbpid[si];
   }
   __syncthreads();
   // ---- the widest profile a line of each molecule row can take in THIS tile: nothing that reaches the tile
@@ -1158,7 +1253,9 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
       if (s0 + k >= ns) continue;
       const int id = tb_binsearchapprox(sh_aDop, __dmul_rn(sh_tab[i].alphad, wtop), 0, nDop);
       const int row = nrows <= 16 ? iso_row[iso] : 0;
-      atomicMax(&sh_Prow[row], ptab[id * nLor + sh_ilor[i]].psize);
+      // ... and the lines that do not refresh the Doppler index take the carried cell (extinction.c:480-483)
+      const int pc = ptab[sh_fbpid[i]].psize, pr_ = ptab[id * nLor + sh_ilor[i]].psize;
+      atomicMax(&sh_Prow[row], pc > pr_ ? pc : pr_);
     }
   }
   // ---- this thread's output bin and its four states
@@ -1256,15 +1353,19 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
             if (!below) {
               if (!permol) kk = __dmul_rn(kk, t.densf);
               const double adw = __dmul_rn(t.alphad, wlead);
-              // binsearchapprox (iomisc.c:1088-1108) on the log-spaced table, as in k_strength
-              if (lo < 0) {
-                lo = (int)((__log2f((float)adw) * 0.30102999566f - dop_lmin) * dop_rstep);
-                lo = lo < 0 ? 0 : (lo > nDop - 1 ? nDop - 1 : lo);
-              }
-              while (lo > 0 && sh_aDop[lo] > adw) lo--;
-              while (sh_aDop[lo + 1] <= adw) lo++;
-              const int id = (fabs(sh_aDop[lo + 1] - adw) < fabs(sh_aDop[lo] - adw)) ? lo + 1 : lo;
-              const unsigned pid = (unsigned)(id * nLor + sh_ilor[k * niso + iso]);
+              unsigned pid;
+              if (tb_refresh(adw, t.alphal, t.ral)) {               // extinction.c:480-483
+                // binsearchapprox (iomisc.c:1088-1108) on the log-spaced table, as in k_strength
+                if (lo < 0) {
+                  lo = (int)((__log2f((float)adw) * 0.30102999566f - dop_lmin) * dop_rstep);
+                  lo = lo < 0 ? 0 : (lo > nDop - 1 ? nDop - 1 : lo);
+                }
+                while (lo > 0 && sh_aDop[lo] > adw) lo--;
+                while (sh_aDop[lo + 1] <= adw) lo++;
+                const int id = (fabs(sh_aDop[lo + 1] - adw) < fabs(sh_aDop[lo] - adw)) ? lo + 1 : lo;
+                pid = (unsigned)(id * nLor + sh_ilor[k * niso + iso]);
+              } else
+                pid = (unsigned)sh_fbpid[k * niso + iso];          // the index carried from the last line that refreshed it
               const ProfEntry pe = ptab[pid];
               const int ps = pe.psize;
               // bins with |o*j - iown| <= ps: ceil((iown-ps)/o) .. floor((iown+ps)/o), on the grid
@@ -1345,7 +1446,7 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
 
 static size_t fuse_shared_bytes(int niso) {
   return (size_t)FBK * FUSE_CAPA * sizeof(FuseRec) + (size_t)FUSE_CAPA * 4 * 2 + 256 * 8 + FBK * 8 +
-         (size_t)FBK * niso * sizeof(FuseTab) + (size_t)FBK * niso * 4 + FUSE_CAPA + 16;
+         (size_t)FBK * niso * sizeof(FuseTab) + (size_t)FBK * niso * 8 + FUSE_CAPA + 16;
 }
 
 
@@ -1462,7 +1563,8 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
     if (banded)    // bins outside the band come back as zero
       TB_CUDA(cudaMemsetAsync(dst, 0, (size_t)cs * nout * nwn * sizeof(double), st));
     const int nbatch = (cs + FB - 1) / FB;
-    k_fuse_class<<<nbatch, 128, 0, st>>>(cs, niso, c->wn_i, c->own_last, c->o, fuse_on ? 1 : 0, c->s_alphad.p, c->s_ral.p,
+    k_fuse_class<<<nbatch, 128, 0, st>>>(cs, niso, c->wn_i, c->own_last, c->o, fuse_on ? 1 : 0, c->og_contig ? 0 : 1, c->fuse_rmax,
+                                         c->s_alphad.p, c->s_ral.p,
                                          c->s_ilor.p, c->d_aDop.p, c->nDop, c->nLor, c->d_ptab.p, c->s_fclass.p, c->s_fP.p);
     TB_LAUNCHED(c);
     c->last_chunk_s0 = s0; c->last_chunk_cs = cs;
@@ -1503,6 +1605,19 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       if (fuse_on && tile_hi > tile_lo) {
         tb_timer_end(c, "strength");
         tb_timer_begin(c, "fused");
+        // carried Doppler index of the fused states: found by bisection + a short backward scan of the file order
+        TB_TRY(c->s_lastq2.ensure((size_t)chunk * niso + 1));
+        if (c->og_contig)
+          k_lastq_scan<<<nblk((int64_t)cs * niso * 32, 128), 128, 0, st>>>(
+              cs, niso, nrows, permol, ethresh, c->iso_og0.p, c->iso_og1.p, c->go_pos.p, c->go_wavn.p, c->g_start.p,
+              c->g_gf.p, c->g_a0.p, c->g_wavn.p, c->s_rtemp.p, c->s_facz.p, c->s_kmax.p, c->d_iso_row.p, c->s_alphal.p,
+              c->s_alphad.p, c->s_ral.p, c->s_xterm.p, X, c->s_fclass.p, c->s_lastq2.p);
+        else     // (isotopes in several runs: only always-refreshing states are fused, their carried index is never read)
+          TB_CUDA(cudaMemsetAsync(c->s_lastq2.p, 0xff, (size_t)cs * niso * sizeof(int32_t), st));
+        k_fallback<<<nblk(cs * niso, 128), 128, 0, st>>>(
+            cs, niso, c->s_fclass.p, 1, c->s_lastq2.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
+            c->nDop, c->nLor, c->d_ptab.p, c->s_fb.p, c->s_fbpid.p, c->s_fbmax.p);
+        c->launches += 2;
         LineRec *trace_rec = nullptr;
         if (c->trace_enabled) {                 // per-line trace wanted: records of the fused states too
           k_fuse_trace_fill<<<dim3(nblk(G, Tn), cs), Tn, 0, st>>>(G, cs, c->s_fclass.p, c->g_iown.p, c->s_rec.p);
@@ -1513,7 +1628,8 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
             c->s_fclass.p, c->s_fP.p, c->binstart.p,
             c->g_start.p, c->g_iso.p, c->g_iown.p, c->g_wavn.p, c->g_a0.p, c->g_gf.p, c->g_lg.p, c->s_rtemp.p,
             c->s_facz.p, c->s_lcz.p, c->s_xterm.p, X, (float)c->dop_lmin, (float)c->dop_rstep, c->s_dens.p,
-            c->d_iso_imol.p, c->d_iso_row.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p, c->nDop, c->d_ptab.p, c->nLor,
+            c->d_iso_imol.p, c->d_iso_row.p, c->s_alphad.p, c->s_ilor.p, c->s_alphal.p, c->s_ral.p, c->s_fbpid.p,
+            c->d_aDop.p, c->nDop, c->d_ptab.p, c->nLor,
             ethresh, c->s_kmax.p, c->d_pdata2.p, dst, c->s_nsamp.p + s0, trace_rec);
         TB_LAUNCHED(c);
         tb_timer_end(c, "fused");
@@ -1547,7 +1663,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       }
       tb_timer_end(c, "strength");
       k_fallback<<<nblk(cs * niso, 128), 128, 0, st>>>(
-          cs, niso, c->s_lastq.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
+          cs, niso, c->s_fclass.p, 0, c->s_lastq.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
           c->nDop, c->nLor, c->d_ptab.p, c->s_fb.p, c->s_fbpid.p, c->s_fbmax.p);
       c->launches += 3;
     }
@@ -1727,3 +1843,10 @@ extern "C" int tb_get_fused_stats(tb_ctx *c, int64_t *fused_states, int64_t *fus
   return TB_OK;
 }
 
+
+// widest reach (coarse bins) of a state the fused kernel takes (default FUSE_RMAX; a tuning / comparison tap)
+extern "C" int tb_set_fused_reach(tb_ctx *c, int rmax) {
+  TB_REQUIRE(rmax >= 1 && rmax <= 4096, TB_ERR_ARG, "tb_set_fused_reach: 1..4096 coarse bins");
+  c->fuse_rmax = rmax;
+  return TB_OK;
+}
