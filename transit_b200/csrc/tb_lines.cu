@@ -1138,42 +1138,61 @@ __device__ __forceinline__ bool tb_group_evaluated(int q, size_t sX, double rT, 
 
 // The carried Doppler index without walking the list (extinction.c:480-483): per (state, isotope) the reference
 // leaves, for the lines that do not refresh it, the index of the LAST line in file order that did refresh it and
-// was evaluated.  An isotope's lines come in one run of descending wavenumber, and "refreshes" is monotone in the
-// wavenumber, so the refreshing lines are a prefix of the run: bisect its end, then scan backwards, 32 groups per
-// step, for the first evaluated one.  One warp per (state, isotope); nothing here depends on a band shard.
-__global__ void k_lastq_scan(int ns, int niso, int nrows, int permol, double ethresh,
-                             const int32_t *__restrict__ iso_og0, const int32_t *__restrict__ iso_og1,
-                             const int32_t *__restrict__ go_pos, const double *__restrict__ go_wavn,
-                             const int32_t *__restrict__ g_start, const double *__restrict__ g_gf,
-                             const double *__restrict__ g_a0, const double *__restrict__ g_wavn,
-                             const double *__restrict__ rtemp, const double *__restrict__ facz,
-                             const double *__restrict__ kmax, const int *__restrict__ iso_row,
-                             const double *__restrict__ alphal, const double *__restrict__ alphad,
-                             const double *__restrict__ ral, const double *__restrict__ xterm, int64_t X,
-                             const int32_t *__restrict__ fclass, int32_t *__restrict__ lastq) {
-  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (wid >= ns * niso) return;
-  const int s = wid / niso, iso = wid % niso;
+// was evaluated.  An isotope's lines come in one run of descending wavenumber and "refreshes" is monotone in the
+// wavenumber, so the refreshing lines are a prefix of the run: its end is bisected, and the run is searched
+// backwards from there for the first evaluated group -- in chunks of 256 groups dealt to LASTQ_NB blocks per
+// (state, isotope), each chunk through the log-domain pretest first (an isotopologue whose lines are all below the
+// threshold costs one cheap pass, not a serial walk), hits merged by an integer atomicMax, a chunk skipped as soon
+// as a hit nearer the end of the prefix is known.  A pair whose lines ALL refresh never reads the carried index
+// and is left alone.  Nothing here depends on a band shard: every rank finds the same index.
+#define LASTQ_NB 64
+__global__ void __launch_bounds__(256)
+k_lastq_scan(int ns, int niso, int nrows, int permol, double ethresh, double wn_i,
+             const int32_t *__restrict__ iso_og0, const int32_t *__restrict__ iso_og1,
+             const int32_t *__restrict__ go_pos, const double *__restrict__ go_wavn,
+             const int32_t *__restrict__ g_start, const double *__restrict__ g_gf,
+             const double *__restrict__ g_a0, const double *__restrict__ g_lg, const double *__restrict__ g_wavn,
+             const double *__restrict__ rtemp, const double *__restrict__ facz, const double *__restrict__ lcz,
+             const double *__restrict__ kmax, const int *__restrict__ iso_row,
+             const double *__restrict__ alphal, const double *__restrict__ alphad,
+             const double *__restrict__ ral, const double *__restrict__ xterm, int64_t X,
+             const int32_t *__restrict__ fclass, int32_t *lastq /* preset to -1 */) {
+  const int pair = blockIdx.y, s = pair / niso, iso = pair % niso;
   if (!fclass[s / FB]) return;                   // k_strength finds it for the states it evaluates
   const int og0 = iso_og0[iso], og1 = iso_og1[iso];
-  int res = -1;
-  if (og1 > og0) {
-    const double al = alphal[wid], ad = alphad[wid], rl = ral[wid];
-    int l = og0, h = og1;                          // first group of the run that does NOT refresh
-    while (l < h) {
-      const int mid = (l + h) >> 1;
-      if (tb_refresh(__dmul_rn(ad, go_wavn[mid]), al, rl)) l = mid + 1; else h = mid;
+  if (og1 <= og0) return;
+  const double al = alphal[pair], ad = alphad[pair], rl = ral[pair];
+  if (tb_refresh(__dmul_rn(ad, wn_i), al, rl)) return;      // every in-range line refreshes: the carried index is never read
+  __shared__ int sh_best;
+  int l = og0, h = og1;                          // first group of the run that does NOT refresh
+  while (l < h) {
+    const int mid = (l + h) >> 1;
+    if (tb_refresh(__dmul_rn(ad, go_wavn[mid]), al, rl)) l = mid + 1; else h = mid;
+  }
+  const int ogb = l - 1;
+  const double rT = rtemp[s], fz = facz[pair], lz = lcz[pair];
+  const double thr = __dmul_rn(ethresh, kmax[s * nrows + (permol ? iso_row[iso] : 0)]);
+  for (int j = blockIdx.x;; j += LASTQ_NB) {
+    const int hi = ogb - 256 * j;
+    if (hi < og0) break;
+    if (__ldcg(lastq + pair) >= hi) break;       // a hit nearer the end of the prefix: nothing here can beat it
+    if (threadIdx.x == 0) sh_best = -1;
+    __syncthreads();
+    const int og = hi - (int)threadIdx.x;
+    if (og >= og0) {
+      const int q = go_pos[og];
+      if (!(fma(g_a0[q], rT, g_lg[q] + lz) < -1e-9) &&
+          tb_group_evaluated(q, (size_t)s * X, rT, fz, thr, g_start, g_gf, g_a0, g_wavn, xterm))
+        atomicMax(&sh_best, og);
     }
-    const double rT = rtemp[s], fz = facz[wid];
-    const double thr = __dmul_rn(ethresh, kmax[s * nrows + (permol ? iso_row[iso] : 0)]);
-    for (int base = l - 1; base >= og0; base -= 32) {
-      const int og = base - lane;
-      const bool ok = og >= og0 && tb_group_evaluated(go_pos[og], (size_t)s * X, rT, fz, thr, g_start, g_gf, g_a0, g_wavn, xterm);
-      const unsigned ball = __ballot_sync(0xffffffffu, ok);
-      if (ball) { res = base - (__ffs(ball) - 1); break; }
+    __syncthreads();
+    const int best = sh_best;
+    __syncthreads();
+    if (best >= 0) {
+      if (threadIdx.x == 0) atomicMax(lastq + pair, best);
+      break;
     }
   }
-  if (lane == 0) lastq[wid] = res;
 }
 
 struct FuseTab {           // per (state of the block, isotope), in shared memory
@@ -1607,13 +1626,12 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
         tb_timer_begin(c, "fused");
         // carried Doppler index of the fused states: found by bisection + a short backward scan of the file order
         TB_TRY(c->s_lastq2.ensure((size_t)chunk * niso + 1));
-        if (c->og_contig)
-          k_lastq_scan<<<nblk((int64_t)cs * niso * 32, 128), 128, 0, st>>>(
-              cs, niso, nrows, permol, ethresh, c->iso_og0.p, c->iso_og1.p, c->go_pos.p, c->go_wavn.p, c->g_start.p,
-              c->g_gf.p, c->g_a0.p, c->g_wavn.p, c->s_rtemp.p, c->s_facz.p, c->s_kmax.p, c->d_iso_row.p, c->s_alphal.p,
-              c->s_alphad.p, c->s_ral.p, c->s_xterm.p, X, c->s_fclass.p, c->s_lastq2.p);
-        else     // (isotopes in several runs: only always-refreshing states are fused, their carried index is never read)
-          TB_CUDA(cudaMemsetAsync(c->s_lastq2.p, 0xff, (size_t)cs * niso * sizeof(int32_t), st));
+        TB_CUDA(cudaMemsetAsync(c->s_lastq2.p, 0xff, (size_t)cs * niso * sizeof(int32_t), st));
+        if (c->og_contig)   // (isotopes in several runs: only always-refreshing states are fused, their carried index is never read)
+          k_lastq_scan<<<dim3(LASTQ_NB, cs * niso), 256, 0, st>>>(
+              cs, niso, nrows, permol, ethresh, c->wn_i, c->iso_og0.p, c->iso_og1.p, c->go_pos.p, c->go_wavn.p, c->g_start.p,
+              c->g_gf.p, c->g_a0.p, c->g_lg.p, c->g_wavn.p, c->s_rtemp.p, c->s_facz.p, c->s_lcz.p, c->s_kmax.p,
+              c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ral.p, c->s_xterm.p, X, c->s_fclass.p, c->s_lastq2.p);
         k_fallback<<<nblk(cs * niso, 128), 128, 0, st>>>(
             cs, niso, c->s_fclass.p, 1, c->s_lastq2.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
             c->nDop, c->nLor, c->d_ptab.p, c->s_fb.p, c->s_fbpid.p, c->s_fbmax.p);
