@@ -439,7 +439,7 @@ def run_ours(args):
     init_s = time.perf_counter() - t0
     ctx = tr.ctx
     if args.fuse_rmax:
-        ctx.set_fused_reach(args.fuse_rmax)
+        ctx.set_fused_reach(args.fuse_rmax, True)
     out = np.zeros(prob.nwn)
     gathered = [None]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2

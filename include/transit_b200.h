@@ -86,7 +86,10 @@ int  tb_get_sample_counts(tb_ctx *c, int64_t *nsamples, int ns);
  * per-line records tb_get_line_trace reads (off by default: 16 B of HBM per (group, state)).
  * tb_get_fused_stats: states of the last batch taken by the fused kernel and its executed profile updates. */
 int  tb_set_fused(tb_ctx *c, int on);
-int  tb_set_fused_reach(tb_ctx *c, int rmax);   /* widest reach (coarse bins) of a fused state; default 8 */
+/* which states are fused: widest reach in coarse bins (default 8) and whether states whose lines partly keep a
+ * carried Doppler index (extinction.c:480-483; found by a bisection + backward scan instead of the list walk) are
+ * fused as well (default 0: only states where every line refreshes its index) */
+int  tb_set_fused_reach(tb_ctx *c, int rmax, int carried);
 int  tb_set_trace(tb_ctx *c, int on);
 int  tb_get_fused_stats(tb_ctx *c, int64_t *fused_states, int64_t *fused_samples);
 /* ilor[niso] of state `s` of the last batch (extinction.c:394); with the trace's idop it names the Voigt cell */

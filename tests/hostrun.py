@@ -43,6 +43,9 @@ def main():
     L.th_context.restype = C.c_void_p
     if trace:                 # the fused line sum leaves its per-line records only when asked
         api.load_library().tb_set_trace(C.c_void_p(L.th_context()), 1)
+    if "--fuse-all" in rest:  # every state through the fused kernel, carried Doppler indices by k_lastq_scan
+        api.load_library().tb_set_fused(C.c_void_p(L.th_context()), 2)
+        api.load_library().tb_set_fused_reach(C.c_void_p(L.th_context()), 4096, 1)
     t0 = time.perf_counter()
     L.do_transit(out.ctypes.data_as(P))
     run_s = time.perf_counter() - t0

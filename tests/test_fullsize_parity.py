@@ -159,19 +159,22 @@ def test_c1_demo_cfg_verbatim(tmp_path):
     report("C1 transit_demo.cfg verbatim", w)
 
 
-def test_c2_full_size(tmp_path):
+@pytest.mark.parametrize("mode", ["default", "fuse-all"])
+def test_c2_full_size(tmp_path, mode):
     """C2 as BASELINE.json names it: 31 334 wavenumbers x 100 layers x 1e6 lines, 60x60 table at wnosamp 2160,
-    ONE whole-spectrum reference process (~30 core-seconds)."""
+    ONE whole-spectrum reference process (~30 core-seconds).  Twice: with the production split (narrow layers fused,
+    the rest through k_strength + k_accumulate) and with EVERY layer through the fused kernel, the carried Doppler
+    indices of the deep layers found by k_lastq_scan -- the per-line index tap covers both."""
     tmp = str(tmp_path)
     prob = workloads.make_problem("C2")
     cfg, nlines = workloads.write_reference_inputs(prob, tmp)
     idx = [0, 6, 12, 16, 19, 20, 21, 30, 60, 99]
-    g, o, ref_s = run_both(tmp, cfg, idx, timeout=1500)
+    g, o, ref_s = run_both(tmp, cfg, idx, timeout=1500, extra_host=["--fuse-all"] if mode == "fuse-all" else [])
     assert int(g["wns_n"].item()) == 31334 and int(g["nrad"].item()) == 100 and int(g["nlines"].item()) >= 990000
     w = compare_lbl("C2", g, o, idx, eclipse=False)
     w["reference_s"] = ref_s
     w["ours_run_s"] = float(o["run_s"])
-    report("C2 full size", w)
+    report("C2 full size" + ("" if mode == "default" else " (every layer fused, carried indices by k_lastq_scan)"), w)
 
 
 def _rerun_inputs(prob, k, seed0=7000, dT=150.0, dex=1.0):

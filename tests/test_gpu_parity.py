@@ -166,7 +166,7 @@ def test_fused_line_sum_vs_two_kernel_path():
     dens, Z = prob.mol_d.T.copy(), prob.iso_z.T.copy()
     for permol, rmax in ((0, 8), (1, 8), (0, 4096)):
         c.set_fused(2)                     # 2: fused whatever the size of the grid
-        c.set_fused_reach(rmax)
+        c.set_fused_reach(rmax, carried=True)
         a = c.molext_states(T, dens, Z, prob.ethresh, permol=permol)
         st = c.fused_stats()
         na = c.sample_counts(prob.nrad)
@@ -191,7 +191,7 @@ def test_fused_line_sum_vs_two_kernel_path():
         assert relerr(a, b) < 1e-13
         same = [r for r in range(prob.nrad) if np.array_equal(a[r], b[r])]
         assert len(same) >= prob.nrad // 2, (len(same), prob.nrad)     # only the layers of reach > 2 bins may differ in order
-    c.set_fused(1); c.set_fused_reach(8)
+    c.set_fused(1); c.set_fused_reach(8, False)
     c.close()
 
 

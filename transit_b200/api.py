@@ -51,7 +51,7 @@ ABI = {
     "tb_get_sample_counts": (C.c_int, [C.c_void_p, i64p, C.c_int]),
     "tb_get_state_ilor": (C.c_int, [C.c_void_p, C.c_int, i32p]),
     "tb_set_fused": (C.c_int, [C.c_void_p, C.c_int]),
-    "tb_set_fused_reach": (C.c_int, [C.c_void_p, C.c_int]),
+    "tb_set_fused_reach": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "tb_set_trace": (C.c_int, [C.c_void_p, C.c_int]),
     "tb_get_fused_stats": (C.c_int, [C.c_void_p, i64p, i64p]),
     "tb_get_line_molIDs": (C.c_int, [C.c_void_p, i32p, i32p]),
@@ -257,8 +257,8 @@ class Context:
         """0: two-kernel path; 1/True: fused where the grid has >= 96 tiles; 2: fused on small grids too."""
         self._ck(self.lib.tb_set_fused(self.h, int(on)), "tb_set_fused")
 
-    def set_fused_reach(self, rmax):
-        self._ck(self.lib.tb_set_fused_reach(self.h, int(rmax)), "tb_set_fused_reach")
+    def set_fused_reach(self, rmax, carried=False):
+        self._ck(self.lib.tb_set_fused_reach(self.h, int(rmax), int(bool(carried))), "tb_set_fused_reach")
 
     def set_trace(self, on=True):
         self._ck(self.lib.tb_set_trace(self.h, int(bool(on))), "tb_set_trace")

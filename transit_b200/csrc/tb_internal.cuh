@@ -232,7 +232,8 @@ struct tb_ctx {
   DevBuf<double> s_facz, s_rtemp, s_ral, s_xterm, s_lcz;
   DevBuf<LineRec> s_rec;      // [state][group]
   DevBuf<int32_t> s_fclass, s_fP, s_lastq2;   // s_lastq2: carried-index source of the fused states (k_lastq_scan)
-  int fuse_rmax = 8;   // per batch of 8 states: taken by k_linesum_fused? / widest half-size (fine bins)
+  int fuse_rmax = 8;
+  bool fuse_carried = false;     // fuse states whose lines partly keep a carried Doppler index (k_lastq_scan)   // per batch of 8 states: taken by k_linesum_fused? / widest half-size (fine bins)
   int fuse_enabled = 1;          // 0 off, 1 on where the grid has enough tiles, 2 always (tests)
   bool trace_enabled = false;
   int fuse_shm_set = -1, last_chunk_s0 = 0, last_chunk_cs = 0;

@@ -1140,12 +1140,12 @@ __device__ __forceinline__ bool tb_group_evaluated(int q, size_t sX, double rT, 
 // leaves, for the lines that do not refresh it, the index of the LAST line in file order that did refresh it and
 // was evaluated.  An isotope's lines come in one run of descending wavenumber and "refreshes" is monotone in the
 // wavenumber, so the refreshing lines are a prefix of the run: its end is bisected, and the run is searched
-// backwards from there for the first evaluated group -- in chunks of 256 groups dealt to LASTQ_NB blocks per
+// backwards from there for the first evaluated group -- in chunks of 256 groups dealt to LASTQ_NB = 8 blocks per
 // (state, isotope), each chunk through the log-domain pretest first (an isotopologue whose lines are all below the
 // threshold costs one cheap pass, not a serial walk), hits merged by an integer atomicMax, a chunk skipped as soon
 // as a hit nearer the end of the prefix is known.  A pair whose lines ALL refresh never reads the carried index
 // and is left alone.  Nothing here depends on a band shard: every rank finds the same index.
-#define LASTQ_NB 64
+#define LASTQ_NB 8
 __global__ void __launch_bounds__(256)
 k_lastq_scan(int ns, int niso, int nrows, int permol, double ethresh, double wn_i,
              const int32_t *__restrict__ iso_og0, const int32_t *__restrict__ iso_og1,
@@ -1157,7 +1157,7 @@ k_lastq_scan(int ns, int niso, int nrows, int permol, double ethresh, double wn_
              const double *__restrict__ alphal, const double *__restrict__ alphad,
              const double *__restrict__ ral, const double *__restrict__ xterm, int64_t X,
              const int32_t *__restrict__ fclass, int32_t *lastq /* preset to -1 */) {
-  const int pair = blockIdx.y, s = pair / niso, iso = pair % niso;
+  const int pair = blockIdx.x, s = pair / niso, iso = pair % niso;      // (x: up to 2^31 pairs; y: the chunk dealer)
   if (!fclass[s / FB]) return;                   // k_strength finds it for the states it evaluates
   const int og0 = iso_og0[iso], og1 = iso_og1[iso];
   if (og1 <= og0) return;
@@ -1172,7 +1172,7 @@ k_lastq_scan(int ns, int niso, int nrows, int permol, double ethresh, double wn_
   const int ogb = l - 1;
   const double rT = rtemp[s], fz = facz[pair], lz = lcz[pair];
   const double thr = __dmul_rn(ethresh, kmax[s * nrows + (permol ? iso_row[iso] : 0)]);
-  for (int j = blockIdx.x;; j += LASTQ_NB) {
+  for (int j = blockIdx.y;; j += LASTQ_NB) {
     const int hi = ogb - 256 * j;
     if (hi < og0) break;
     if (__ldcg(lastq + pair) >= hi) break;       // a hit nearer the end of the prefix: nothing here can beat it
@@ -1582,7 +1582,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
     if (banded)    // bins outside the band come back as zero
       TB_CUDA(cudaMemsetAsync(dst, 0, (size_t)cs * nout * nwn * sizeof(double), st));
     const int nbatch = (cs + FB - 1) / FB;
-    k_fuse_class<<<nbatch, 128, 0, st>>>(cs, niso, c->wn_i, c->own_last, c->o, fuse_on ? 1 : 0, c->og_contig ? 0 : 1, c->fuse_rmax,
+    k_fuse_class<<<nbatch, 128, 0, st>>>(cs, niso, c->wn_i, c->own_last, c->o, fuse_on ? 1 : 0, (c->fuse_carried && c->og_contig) ? 0 : 1, c->fuse_rmax,
                                          c->s_alphad.p, c->s_ral.p,
                                          c->s_ilor.p, c->d_aDop.p, c->nDop, c->nLor, c->d_ptab.p, c->s_fclass.p, c->s_fP.p);
     TB_LAUNCHED(c);
@@ -1627,8 +1627,8 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
         // carried Doppler index of the fused states: found by bisection + a short backward scan of the file order
         TB_TRY(c->s_lastq2.ensure((size_t)chunk * niso + 1));
         TB_CUDA(cudaMemsetAsync(c->s_lastq2.p, 0xff, (size_t)cs * niso * sizeof(int32_t), st));
-        if (c->og_contig)   // (isotopes in several runs: only always-refreshing states are fused, their carried index is never read)
-          k_lastq_scan<<<dim3(LASTQ_NB, cs * niso), 256, 0, st>>>(
+        if (c->fuse_carried && c->og_contig)   // (else only always-refreshing states are fused: their carried index is never read)
+          k_lastq_scan<<<dim3(cs * niso, LASTQ_NB), 256, 0, st>>>(
               cs, niso, nrows, permol, ethresh, c->wn_i, c->iso_og0.p, c->iso_og1.p, c->go_pos.p, c->go_wavn.p, c->g_start.p,
               c->g_gf.p, c->g_a0.p, c->g_lg.p, c->g_wavn.p, c->s_rtemp.p, c->s_facz.p, c->s_lcz.p, c->s_kmax.p,
               c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ral.p, c->s_xterm.p, X, c->s_fclass.p, c->s_lastq2.p);
@@ -1862,9 +1862,12 @@ extern "C" int tb_get_fused_stats(tb_ctx *c, int64_t *fused_states, int64_t *fus
 }
 
 
-// widest reach (coarse bins) of a state the fused kernel takes (default FUSE_RMAX; a tuning / comparison tap)
-extern "C" int tb_set_fused_reach(tb_ctx *c, int rmax) {
+// Which states the fused kernel takes (tuning / comparison tap): widest reach in coarse bins (default FUSE_RMAX) and
+// whether states whose lines partly keep a CARRIED Doppler index are fused too (default no: measured on C2, the
+// two-kernel path is as fast on those layers -- 25 us against 30 us per layer -- and k_lastq_scan costs 35 us).
+extern "C" int tb_set_fused_reach(tb_ctx *c, int rmax, int carried) {
   TB_REQUIRE(rmax >= 1 && rmax <= 4096, TB_ERR_ARG, "tb_set_fused_reach: 1..4096 coarse bins");
   c->fuse_rmax = rmax;
+  c->fuse_carried = carried != 0;
   return TB_OK;
 }
