@@ -112,13 +112,13 @@ struct CiaTable {
   int mol[2] = {0, 0};
   std::vector<double> wn, temp, tab;
   DevBuf<double> d_wn, d_temp, d_tab;
-  DevBuf<double> d_zt, d_h, d_u, d_rh, d_r, d_ru;   // table-only spline parts (see tb_radiative.cu)
+  DevBuf<double> d_zt, d_h, d_u, d_rh, d_r, d_ru, d_r6h, d_h6;   // table-only spline parts (see tb_radiative.cu)
   DevBuf<double> d_f2, d_z2, d_v;     // per-spectrum scratch, [row][layer]
   DevBuf<int32_t> d_widx;             // table interval of every grid wavenumber
   int64_t fi = 0, li = 0;             // grid range inside the table (no extrapolation)
   int grid_version = -1;
   void release() {
-    d_wn.release(); d_temp.release(); d_tab.release(); d_zt.release(); d_h.release(); d_u.release(); d_rh.release(); d_r.release(); d_ru.release();
+    d_wn.release(); d_temp.release(); d_tab.release(); d_zt.release(); d_h.release(); d_u.release(); d_rh.release(); d_r.release(); d_ru.release(); d_r6h.release(); d_h6.release();
     d_f2.release(); d_z2.release(); d_v.release(); d_widx.release();
   }
 };

@@ -1208,6 +1208,7 @@ struct __align__(16) FuseRec {
   short jl, jh;            // tile-relative bins the profile covers (jl > jh: none)
 };
 
+template <bool CARRIED>      // CARRIED: some lines keep the isotope's carried Doppler index (fbpid) instead of their own
 __global__ void __launch_bounds__(FUSE_NT, FUSE_BLOCKS)
 k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol, int o, FastDiv fd_o, FastDiv fd_tile,
                 int nrows, int permol, int tile_off, double wn_i, double odwn,
@@ -1257,7 +1258,7 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
     t.alphad = alphad[si]; t.alphal = alphal[si]; t.ral = ral[si];
     sh_tab[i] = t;
     sh_ilor[i] = ilor[si];
-    sh_fbpid[i] = fbpid[si];
+    sh_fbpid[i] = CARRIED ? fbpid[si] : 0;
   }
   __syncthreads();
   // ---- the widest profile a line of each molecule row can take in THIS tile: nothing that reaches the tile
@@ -1273,7 +1274,7 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
       const int id = tb_binsearchapprox(sh_aDop, __dmul_rn(sh_tab[i].alphad, wtop), 0, nDop);
       const int row = nrows <= 16 ? iso_row[iso] : 0;
       // ... and the lines that do not refresh the Doppler index take the carried cell (extinction.c:480-483)
-      const int pc = ptab[sh_fbpid[i]].psize, pr_ = ptab[id * nLor + sh_ilor[i]].psize;
+      const int pc = CARRIED ? ptab[sh_fbpid[i]].psize : 0, pr_ = ptab[id * nLor + sh_ilor[i]].psize;
       atomicMax(&sh_Prow[row], pc > pr_ ? pc : pr_);
     }
   }
@@ -1373,7 +1374,7 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
               if (!permol) kk = __dmul_rn(kk, t.densf);
               const double adw = __dmul_rn(t.alphad, wlead);
               unsigned pid;
-              if (tb_refresh(adw, t.alphal, t.ral)) {               // extinction.c:480-483
+              if (!CARRIED || tb_refresh(adw, t.alphal, t.ral)) {   // extinction.c:480-483
                 // binsearchapprox (iomisc.c:1088-1108) on the log-spaced table, as in k_strength
                 if (lo < 0) {
                   lo = (int)((__log2f((float)adw) * 0.30102999566f - dop_lmin) * dop_rstep);
@@ -1516,7 +1517,8 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   const bool fuse_on = c->fuse_enabled && niso >= 1 && niso <= FUSE_MAXISO && G > 0 && fuse_shm <= 100 * 1024 &&
                        (ntiles >= FUSE_MIN_TILES || c->fuse_enabled > 1);
   if (fuse_on && c->fuse_shm_set != (int)fuse_shm) {
-    TB_CUDA(cudaFuncSetAttribute(k_linesum_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fuse_shm));
+    TB_CUDA(cudaFuncSetAttribute(k_linesum_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fuse_shm));
+    TB_CUDA(cudaFuncSetAttribute(k_linesum_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fuse_shm));
     c->fuse_shm_set = (int)fuse_shm;
   }
   double *d_out = d_out_rows;
@@ -1626,22 +1628,25 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
         tb_timer_begin(c, "fused");
         // carried Doppler index of the fused states: found by bisection + a short backward scan of the file order
         TB_TRY(c->s_lastq2.ensure((size_t)chunk * niso + 1));
-        TB_CUDA(cudaMemsetAsync(c->s_lastq2.p, 0xff, (size_t)cs * niso * sizeof(int32_t), st));
-        if (c->fuse_carried && c->og_contig)   // (else only always-refreshing states are fused: their carried index is never read)
+        if (c->fuse_carried && c->og_contig) {   // (else only always-refreshing states are fused: their carried index is never read)
+          TB_CUDA(cudaMemsetAsync(c->s_lastq2.p, 0xff, (size_t)cs * niso * sizeof(int32_t), st));
           k_lastq_scan<<<dim3(cs * niso, LASTQ_NB), 256, 0, st>>>(
               cs, niso, nrows, permol, ethresh, c->wn_i, c->iso_og0.p, c->iso_og1.p, c->go_pos.p, c->go_wavn.p, c->g_start.p,
               c->g_gf.p, c->g_a0.p, c->g_lg.p, c->g_wavn.p, c->s_rtemp.p, c->s_facz.p, c->s_lcz.p, c->s_kmax.p,
               c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ral.p, c->s_xterm.p, X, c->s_fclass.p, c->s_lastq2.p);
-        k_fallback<<<nblk(cs * niso, 128), 128, 0, st>>>(
-            cs, niso, c->s_fclass.p, 1, c->s_lastq2.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
-            c->nDop, c->nLor, c->d_ptab.p, c->s_fb.p, c->s_fbpid.p, c->s_fbmax.p);
-        c->launches += 2;
+          k_fallback<<<nblk(cs * niso, 128), 128, 0, st>>>(
+              cs, niso, c->s_fclass.p, 1, c->s_lastq2.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
+              c->nDop, c->nLor, c->d_ptab.p, c->s_fb.p, c->s_fbpid.p, c->s_fbmax.p);
+          c->launches += 2;
+        }
         LineRec *trace_rec = nullptr;
         if (c->trace_enabled) {                 // per-line trace wanted: records of the fused states too
           k_fuse_trace_fill<<<dim3(nblk(G, Tn), cs), Tn, 0, st>>>(G, cs, c->s_fclass.p, c->g_iown.p, c->s_rec.p);
           trace_rec = c->s_rec.p;
         }
-        k_linesum_fused<<<dim3(tile_hi - tile_lo, nbatch * (FB / FBK)), FUSE_NT, fuse_shm, st>>>(
+        const bool carried = c->fuse_carried && c->og_contig;
+        auto fused_kernel = carried ? k_linesum_fused<true> : k_linesum_fused<false>;
+        fused_kernel<<<dim3(tile_hi - tile_lo, nbatch * (FB / FBK)), FUSE_NT, fuse_shm, st>>>(
             nwn, c->onwn, G, cs, niso, nmol, c->o, fd_o, fd_tile, nrows, permol, tile_lo, c->wn_i, c->odwn,
             c->s_fclass.p, c->s_fP.p, c->binstart.p,
             c->g_start.p, c->g_iso.p, c->g_iown.p, c->g_wavn.p, c->g_a0.p, c->g_gf.p, c->g_lg.p, c->s_rtemp.p,

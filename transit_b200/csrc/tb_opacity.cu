@@ -45,6 +45,11 @@ __global__ void k_grid_interp(int64_t nwn, int nrad, int ngrid, int Ntemp, int N
   int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   int r = blockIdx.y + blockIdx.z * gridDim.y;
   if (w >= nwn || r >= nrad) return;
+  {  // blocks are dealt layer-major, atmosphere fastest: the atmospheres of a batch that bracket a layer's temperature
+     // alike read the same grid planes while those are in L2 (2 MB per (atmosphere, layer), 126 MB of L2)
+    const int natm = nrad / ngrid;
+    r = (r % natm) * ngrid + r / natm;
+  }
   const InterpLayer l = L[r];
   const double *lo = grid + (((size_t)(r % ngrid) * Ntemp + l.it) * Nmol) * nwn + w;
   const double *hi = lo + (size_t)Nmol * nwn;

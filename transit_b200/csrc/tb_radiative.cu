@@ -145,7 +145,7 @@ __global__ void k_cia_wnspline(CiaSplinePack P) {
 }
 
 struct CiaDev {
-  const double *wn, *f2, *z2, *densfac;
+  const double *wn, *f2, *z2, *densfac, *rh, *r6h, *h6;   // rh = 1/h, r6h = 1/(6h), h6 = h/6 per table interval
   const int32_t *widx;
   int fi, li, fj, lj, ntw;
 };
@@ -185,9 +185,12 @@ __global__ void k_cia_eval(CiaPack P, int nrad, double wn_i, double wn_d, double
     double val = 0;
     if (x_lo == xout) val = y_lo;
     else if (h > 0) {                                   // splinterp_pt, spline.c:163-180
+      // its three divisions have divisors that depend on the table interval only: 1/(6h), 1/h and h/6 are formed
+      // once per table (correctly rounded), so the per-point cubic is multiplications -- each quotient within one
+      // ulp of the reference's, the cross-section within a few 1e-16 (tolerance 1e-12)
       const double dx = xout - x_lo;
-      const double a = (z_hi - z_lo) / (6 * h), b = 0.5 * z_lo;
-      const double cc = dy / h - h / 6 * (z_hi + 2 * z_lo);
+      const double a = (z_hi - z_lo) * T.r6h[idx], b = 0.5 * z_lo;
+      const double cc = dy * T.rh[idx] - T.h6[idx] * (z_hi + 2 * z_lo);
       val = y_lo + dx * (cc + dx * (b + dx * a));
     }
     if (val > 0) acc += val * T.densfac[j];
@@ -241,11 +244,12 @@ extern "C" int tb_cia_add_table(tb_ctx *c, const double *wn, int nwn, const doub
   for (int i = 0; i < nwn - 1; i++) h[i] = wn[i + 1] - wn[i];
   for (int i = 1; i < nwn - 1; i++)
     u[i] = (i == 1) ? 2 * (h[1] + h[0]) : 2 * (h[i] + h[i - 1]) - h[i - 1] * h[i - 1] / u[i - 1];
-  for (int i = 0; i < nwn - 1; i++) rh[i] = 1.0 / h[i];
+  std::vector<double> r6h(nwn, 0.0), h6(nwn, 0.0);
+  for (int i = 0; i < nwn - 1; i++) { rh[i] = 1.0 / h[i]; r6h[i] = 1.0 / (6 * h[i]); h6[i] = h[i] / 6; }
   for (int i = 1; i < nwn - 1; i++) { ru[i] = 1.0 / u[i]; if (i > 1) rr[i] = h[i - 1] / u[i - 1]; }
   if (t->d_wn.ensure(nwn) || t->d_temp.ensure(ntemp) || t->d_tab.ensure((size_t)nwn * ntemp) ||
       t->d_zt.ensure((size_t)nwn * ntemp) || t->d_h.ensure(nwn) || t->d_u.ensure(nwn) || t->d_rh.ensure(nwn) ||
-      t->d_r.ensure(nwn) || t->d_ru.ensure(nwn)) {
+      t->d_r.ensure(nwn) || t->d_ru.ensure(nwn) || t->d_r6h.ensure(nwn) || t->d_h6.ensure(nwn)) {
     t->release();
     delete t;
     return TB_ERR_NOMEM;
@@ -260,6 +264,8 @@ extern "C" int tb_cia_add_table(tb_ctx *c, const double *wn, int nwn, const doub
   TB_CUDA(cudaMemcpyAsync(t->d_rh.p, rh.data(), nwn * sizeof(double), cudaMemcpyHostToDevice, st));
   TB_CUDA(cudaMemcpyAsync(t->d_r.p, rr.data(), nwn * sizeof(double), cudaMemcpyHostToDevice, st));
   TB_CUDA(cudaMemcpyAsync(t->d_ru.p, ru.data(), nwn * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(t->d_r6h.p, r6h.data(), nwn * sizeof(double), cudaMemcpyHostToDevice, st));
+  TB_CUDA(cudaMemcpyAsync(t->d_h6.p, h6.data(), nwn * sizeof(double), cudaMemcpyHostToDevice, st));
   TB_CUDA(cudaStreamSynchronize(st));
   c->cia.push_back(t);
   c->have_ecs = false;
@@ -343,6 +349,7 @@ int tb_cia_run(tb_ctx *c) {
     TB_TRY(t->d_v.ensure((size_t)nrad * t->nw));
     CiaDev &D = P.t[P.n++];
     D.wn = t->d_wn.p; D.f2 = t->d_f2.p; D.z2 = t->d_z2.p; D.widx = t->d_widx.p;
+    D.rh = t->d_rh.p; D.r6h = t->d_r6h.p; D.h6 = t->d_h6.p;
     D.densfac = c->c_stage.p + (size_t)nrad * (1 + n);
     D.fi = (int)t->fi; D.li = (int)t->li; D.fj = fj; D.lj = lj; D.ntw = t->nw;
   }
@@ -911,7 +918,8 @@ k_tau_eclipse(TauPar P, const double *__restrict__ e, const double *__restrict__
 // kernel issues 4 loads per 5 floating-point instructions and 2.5 of those per layer.  Layers below a ray's
 // start carry the weight zero, so the loop is the same for the four rays.  Early exit, last[] and the zero
 // tail as in k_tau_transit.
-__global__ void __launch_bounds__(32 * TAU_NW, 4)
+#define TAU_WL 2      // wavenumbers per lane of k_tau_w (a block owns 32 * TAU_WL columns)
+__global__ void __launch_bounds__(32 * TAU_NW, 3)
 k_tau_w(TauPar P, const double *__restrict__ e, const double *__restrict__ ecs,
         const double *__restrict__ press, const double *__restrict__ temp,
         const double *__restrict__ aux, const double *__restrict__ mol_d,
@@ -919,8 +927,8 @@ k_tau_w(TauPar P, const double *__restrict__ e, const double *__restrict__ ecs,
         const int32_t *__restrict__ meta, const double *__restrict__ par, const double *__restrict__ rcp,
         const double *__restrict__ wg, const double *__restrict__ w0, double *__restrict__ tau,
         int32_t *__restrict__ last) {
-  extern __shared__ double sm[];
-  __shared__ int sh_last[32];
+  extern __shared__ __align__(16) double sm[];          // er[layer][32 lanes][TAU_WL]
+  __shared__ int sh_last[32 * TAU_WL];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nrad = P.nrad, ngrp = (P.nh + TAU_RB - 1) / TAU_RB;
   {  // a batch of atmospheres (tb_run_transit_batch): blockIdx.y selects the atmosphere's slices
@@ -929,40 +937,53 @@ k_tau_w(TauPar P, const double *__restrict__ e, const double *__restrict__ ecs,
     mol_d += a * (size_t)nmol * nrad; meta += a * P.nh * 4; par += a * P.nh * 4; rcp += a * P.nh * 2;
     wg += a * (size_t)ngrp * nrad * TAU_RB; w0 += a * P.nh; tau += a * P.nh * P.nwn; last += a * P.nwn;
   }
-  const int64_t w = P.w0 + blockIdx.x * 32LL + lane;
-  const bool inb = w < P.w1;
-  if (warp == 0) sh_last[lane] = P.nh;
-  if (inb) {
-    const double wn = P.wn_fct * __dadd_rn(P.wn_i, __dmul_rn((double)w, P.wn_d));
-    double kBP = 0, kFH = 0, refw = 1;
-    int ctop = -1, cbot = -1;
-    if (P.cl_flag && P.cl_ext != 0) {
-      const double top = pow(10.0, P.cl_top), bot = pow(10.0, P.cl_bot);
-      int i = nrad - 1;
-      for (; i >= 0; i--) if (press[i] >= top) break;
-      ctop = i;
-      for (; i >= 0; i--) if (press[i] >= bot) break;
-      cbot = i;
-      const double x = 2 * TB_PI * P.cl_r * wn;
-      refw = pow(P.cl_refwn, P.cl_gamma);
-      kBP = P.cl_ext * pow(wn, P.cl_gamma);
-      kFH = P.cl_ext / (P.cl_Q * pow(x, -1 * P.cl_gamma) + pow(x, 0.2));
+  const int64_t wbase = P.w0 + blockIdx.x * (32LL * TAU_WL) + lane * TAU_WL;    // this lane's first column
+  bool inb[TAU_WL];
+  bool any = false;
+#pragma unroll
+  for (int u = 0; u < TAU_WL; u++) { inb[u] = wbase + u < P.w1; any |= inb[u]; }
+  if (warp == 0)
+    for (int u = 0; u < TAU_WL; u++) sh_last[lane * TAU_WL + u] = P.nh;
+  const bool extra = P.sc_flag != 0 || (P.cl_flag && P.cl_ext != 0);
+#pragma unroll
+  for (int u = 0; u < TAU_WL; u++) {
+    const int64_t w = wbase + u;
+    if (!inb[u]) {
+      for (int r = warp; r < nrad; r += TAU_NW) sm[(r * 32 + lane) * TAU_WL + u] = 0.0;
+      continue;
     }
-    const double wn4 = P.sc_flag == 1 ? pow(wn, 4.0) : 0.0;
-    const bool extra = P.sc_flag != 0 || (P.cl_flag && P.cl_ext != 0);
+    const double wn = P.wn_fct * __dadd_rn(P.wn_i, __dmul_rn((double)w, P.wn_d));
+    double kBP = 0, kFH = 0, refw = 1, wn4 = 0;
+    int ctop = -1, cbot = -1;
+    if (extra) {
+      if (P.cl_flag && P.cl_ext != 0) {
+        const double top = pow(10.0, P.cl_top), bot = pow(10.0, P.cl_bot);
+        int i = nrad - 1;
+        for (; i >= 0; i--) if (press[i] >= top) break;
+        ctop = i;
+        for (; i >= 0; i--) if (press[i] >= bot) break;
+        cbot = i;
+        const double x = 2 * TB_PI * P.cl_r * wn;
+        refw = pow(P.cl_refwn, P.cl_gamma);
+        kBP = P.cl_ext * pow(wn, P.cl_gamma);
+        kFH = P.cl_ext / (P.cl_Q * pow(x, -1 * P.cl_gamma) + pow(x, 0.2));
+      }
+      wn4 = P.sc_flag == 1 ? pow(wn, 4.0) : 0.0;
+    }
     for (int r = warp; r < nrad; r += TAU_NW) {
       double es = 0, ec = 0;
       if (extra) es = tb_extra_ext(P, r, wn, wn4, kBP, kFH, refw, ctop, cbot, press, temp, aux, mol_d, mol_pol, mol_mass, nmol, ec);
       // tau.c:231-232, same left-to-right sum
-      sm[r * 32 + lane] = e[(size_t)r * P.nwn + w] + es + ec + ecs[(size_t)r * P.nwn + w];
+      sm[(r * 32 + lane) * TAU_WL + u] = e[(size_t)r * P.nwn + w] + es + ec + ecs[(size_t)r * P.nwn + w];
     }
   }
   __syncthreads();
-  const double *er = sm + lane;
-  int myfirst = P.nh;                       // first ray of this warp above toomuch (none yet)
+  const double2 *er = reinterpret_cast<const double2 *>(sm) + lane;       // er[L * 32] = this lane's two columns of layer L
+  int myfirst[TAU_WL];                      // first ray of this warp above toomuch (none yet), per column
+#pragma unroll
+  for (int u = 0; u < TAU_WL; u++) myfirst[u] = P.nh;
   for (int g = warp; g < ngrp; g += TAU_NW) {
     const int ri0 = g * TAU_RB;
-    // the deepest ray of the group is the last one (rays go top down)
     int rsv[TAU_RB], mdv[TAU_RB], rs_min = nrad;
 #pragma unroll
     for (int j = 0; j < TAU_RB; j++) {
@@ -971,48 +992,62 @@ k_tau_w(TauPar P, const double *__restrict__ e, const double *__restrict__ ecs,
       if (ri < P.nh) { rsv[j] = meta[ri * 4]; mdv[j] = meta[ri * 4 + 2]; }
       if (mdv[j] > 0 && rsv[j] < rs_min) rs_min = rsv[j];
     }
-    double acc[TAU_RB];
+    double ax[TAU_RB], ay[TAU_RB];
 #pragma unroll
     for (int j = 0; j < TAU_RB; j++) {
-      acc[j] = 0.0;
+      ax[j] = 0.0; ay[j] = 0.0;
       const int ri = ri0 + j;
-      if (mdv[j] > 0 && inb) {            // weight of the parabola value at the ray's closest approach
+      if (mdv[j] > 0 && any) {            // weight of the parabola value at the ray's closest approach
         const int b = rsv[j] - (mdv[j] == 2 ? 1 : 0);        // the two-point ray takes layers rs-1, rs, rs+1
         const double *pp = par + ri * 4;
-        const double y0 = tb_parab(pp[0], pp[1], pp[2], rcp + ri * 2, er[b * 32], er[(b + 1) * 32], er[(b + 2) * 32]);
-        acc[j] = w0[ri] * y0;
+        const double2 f0 = er[b * 32], f1 = er[(b + 1) * 32], f2 = er[(b + 2) * 32];
+        const double wq = w0[ri];
+        ax[j] = wq * tb_parab(pp[0], pp[1], pp[2], rcp + ri * 2, f0.x, f1.x, f2.x);
+        ay[j] = wq * tb_parab(pp[0], pp[1], pp[2], rcp + ri * 2, f0.y, f1.y, f2.y);
       }
     }
-    if (inb && myfirst == P.nh) {
+    if (any && (myfirst[0] == P.nh || myfirst[1] == P.nh)) {
       const double2 *wp = reinterpret_cast<const double2 *>(wg + ((size_t)g * nrad) * TAU_RB);
 #pragma unroll 4
       for (int L = rs_min + 1; L < nrad; L++) {
-        const double ev = er[L * 32];
+        const double2 ev = er[L * 32];
         const double2 wa = __ldg(wp + 2 * L), wb = __ldg(wp + 2 * L + 1);
-        acc[0] = fma(wa.x, ev, acc[0]);
-        acc[1] = fma(wa.y, ev, acc[1]);
-        acc[2] = fma(wb.x, ev, acc[2]);
-        acc[3] = fma(wb.y, ev, acc[3]);
+        ax[0] = fma(wa.x, ev.x, ax[0]); ay[0] = fma(wa.x, ev.y, ay[0]);
+        ax[1] = fma(wa.y, ev.x, ax[1]); ay[1] = fma(wa.y, ev.y, ay[1]);
+        ax[2] = fma(wb.x, ev.x, ax[2]); ay[2] = fma(wb.x, ev.y, ay[2]);
+        ax[3] = fma(wb.y, ev.x, ax[3]); ay[3] = fma(wb.y, ev.y, ay[3]);
       }
 #pragma unroll
       for (int j = 0; j < TAU_RB; j++) {
         const int ri = ri0 + j;
-        if (ri < P.nh && myfirst == P.nh) {
-          const double t = mdv[j] > 0 ? P.rfct * (2 * acc[j]) : 0.0;
-          tau[(size_t)ri * P.nwn + w] = t;
-          if (t > P.toomuch) myfirst = ri;                   // tau.c:277-287: this lane is done
+        if (ri >= P.nh) continue;
+#pragma unroll
+        for (int u = 0; u < TAU_WL; u++) {
+          if (inb[u] && myfirst[u] == P.nh) {
+            const double t = mdv[j] > 0 ? P.rfct * (2 * (u == 0 ? ax[j] : ay[j])) : 0.0;
+            tau[(size_t)ri * P.nwn + wbase + u] = t;
+            if (t > P.toomuch) myfirst[u] = ri;              // tau.c:277-287: this column is done
+          }
         }
       }
     }
-    if (__all_sync(0xffffffffu, !inb || myfirst != P.nh)) break;
+    bool done = true;
+#pragma unroll
+    for (int u = 0; u < TAU_WL; u++) done &= (!inb[u] || myfirst[u] != P.nh);
+    if (__all_sync(0xffffffffu, done)) break;
   }
-  if (inb) atomicMin(&sh_last[lane], myfirst);
+#pragma unroll
+  for (int u = 0; u < TAU_WL; u++)
+    if (inb[u]) atomicMin(&sh_last[lane * TAU_WL + u], myfirst[u]);
   __syncthreads();
-  if (inb) {
-    const int lst = sh_last[lane];                       // == nh: never above toomuch
+#pragma unroll
+  for (int u = 0; u < TAU_WL; u++) {
+    if (!inb[u]) continue;
+    const int64_t w = wbase + u;
+    const int lst = sh_last[lane * TAU_WL + u];          // == nh: never above toomuch
     if (warp == 0) last[w] = lst < P.nh ? lst : P.nh - 1;
     // clear what this warp wrote beyond the block-wide first exceed
-    const int upto = myfirst < P.nh ? myfirst : P.nh - 1;
+    const int upto = myfirst[u] < P.nh ? myfirst[u] : P.nh - 1;
     for (int g = warp; g < ngrp; g += TAU_NW)
       for (int j = 0; j < TAU_RB; j++) {
         const int ri = g * TAU_RB + j;
@@ -1085,13 +1120,13 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
         c->nmol, reinterpret_cast<const EclRay *>(c->r_ecl.p), c->d_tau.p, c->d_last.p);
     TB_LAUNCHED(c);
   } else if (wform) {
-    const size_t shm = (size_t)nrad * 32 * sizeof(double);
+    const size_t shm = (size_t)nrad * 32 * TAU_WL * sizeof(double);
     TB_REQUIRE(shm <= 200 * 1024, TB_ERR_ARG, "too many layers (%d) for the tau kernel's shared memory", nrad);
     if (c->tauw_shm_set != (int)shm) {
       TB_CUDA(cudaFuncSetAttribute(k_tau_w, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
       c->tauw_shm_set = (int)shm;
     }
-    k_tau_w<<<nblk(ncol, 32), 32 * TAU_NW, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p, c->d_dens.p,
+    k_tau_w<<<nblk(ncol, 32 * TAU_WL), 32 * TAU_NW, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p, c->d_dens.p,
                                                     c->d_mol_pol.p, c->d_mol_mass.p, c->nmol, c->r_meta.p, c->r_par.p,
                                                     c->r_rcp.p, c->r_wg.p, c->r_w0.p, c->d_tau.p, c->d_last.p);
   } else {
@@ -1614,7 +1649,7 @@ extern "C" int tb_run_transit_batch(tb_ctx *c, int natm, const double *in, doubl
     B.tab_nspec[n] = t->nspec; B.tab_mol[n][0] = t->mol[0]; B.tab_mol[n][1] = t->mol[1];
     TB_TRY(t->d_f2.ensure(nvl_max * t->nw)); TB_TRY(t->d_z2.ensure(nvl_max * t->nw)); TB_TRY(t->d_v.ensure(nvl_max * t->nw));
   }
-  const size_t shm_tauw = (size_t)nrad * 32 * sizeof(double);
+  const size_t shm_tauw = (size_t)nrad * 32 * TAU_WL * sizeof(double);
   if (c->tauw_shm_set != (int)shm_tauw) {
     TB_CUDA(cudaFuncSetAttribute(k_tau_w, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm_tauw));
     c->tauw_shm_set = (int)shm_tauw;
@@ -1651,6 +1686,7 @@ extern "C" int tb_run_transit_batch(tb_ctx *c, int natm, const double *in, doubl
         if (t->fi >= t->li) continue;
         CiaDev &D = CP.t[k];
         D.wn = t->d_wn.p; D.f2 = t->d_f2.p; D.z2 = t->d_z2.p; D.widx = t->d_widx.p;
+        D.rh = t->d_rh.p; D.r6h = t->d_r6h.p; D.h6 = t->d_h6.p;
         D.densfac = c->b_densfac.p + (size_t)n * nvl;
         D.fi = (int)t->fi; D.li = (int)t->li; D.fj = 0; D.lj = nvl; D.ntw = t->nw;
         CiaSplineTab &T = SP.t[k];
@@ -1673,7 +1709,7 @@ extern "C" int tb_run_transit_batch(tb_ctx *c, int natm, const double *in, doubl
     TB_CUDA(cudaMemsetAsync(c->b_tau.p, 0, sizeof(double) * nvl * nwn, st));
     k_ray_geometry<<<nb * nh, 64, 0, st>>>(0, c->b_rad.p, nrad, c->am_rfct, c->b_ip.p, nh, c->am_rfct, stride, c->r_meta.p,
                                            c->r_par.p, c->r_coef.p, c->r_s.p, c->r_rcp.p, c->d_err.p, c->r_wg.p, c->r_w0.p);
-    k_tau_w<<<dim3(nblk(nwn, 32), nb), 32 * TAU_NW, shm_tauw, st>>>(P, c->b_e.p, c->b_ecs.p, c->b_p.p, c->b_traw.p, c->b_aux.p,
+    k_tau_w<<<dim3(nblk(nwn, 32 * TAU_WL), nb), 32 * TAU_NW, shm_tauw, st>>>(P, c->b_e.p, c->b_ecs.p, c->b_p.p, c->b_traw.p, c->b_aux.p,
                                                                    c->b_dens.p, c->d_mol_pol.p, c->d_mol_mass.p, nmol,
                                                                    c->r_meta.p, c->r_par.p, c->r_rcp.p, c->r_wg.p, c->r_w0.p,
                                                                    c->b_tau.p, c->b_last.p);
