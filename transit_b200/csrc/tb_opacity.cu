@@ -45,11 +45,10 @@ __global__ void k_grid_interp(int64_t nwn, int nrad, int ngrid, int Ntemp, int N
   int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   int r = blockIdx.y + blockIdx.z * gridDim.y;
   if (w >= nwn || r >= nrad) return;
-  {  // blocks are dealt layer-major, atmosphere fastest: the atmospheres of a batch that bracket a layer's temperature
-     // alike read the same grid planes while those are in L2 (2 MB per (atmosphere, layer), 126 MB of L2)
-    const int natm = nrad / ngrid;
-    r = (r % natm) * ngrid + r / natm;
-  }
+  // blocks are dealt layer-major, atmosphere fastest: the atmospheres of a batch that bracket a layer's temperature
+  // alike read the same grid planes while those are in L2 (2 MB per (atmosphere, layer), 126 MB of L2)
+  const int natm = nrad / ngrid;
+  r = (r % natm) * ngrid + r / natm;
   const InterpLayer l = L[r];
   const double *lo = grid + (((size_t)(r % ngrid) * Ntemp + l.it) * Nmol) * nwn + w;
   const double *hi = lo + (size_t)Nmol * nwn;
@@ -61,8 +60,9 @@ __global__ void k_grid_interp(int64_t nwn, int nrad, int ngrid, int Ntemp, int N
 #pragma unroll
     for (int k = 0; k < 4; k++) {
       const bool in = m0 + k < Nmol;
-      vlo[k] = in ? __ldcs(lo + (size_t)(m0 + k) * nwn) : 0.0;   // streamed once per spectrum
-      vhi[k] = in ? __ldcs(hi + (size_t)(m0 + k) * nwn) : 0.0;
+      // one atmosphere: every plane is read once (streaming hint); a batch: the planes are shared through L2
+      vlo[k] = !in ? 0.0 : (natm == 1 ? __ldcs(lo + (size_t)(m0 + k) * nwn) : __ldg(lo + (size_t)(m0 + k) * nwn));
+      vhi[k] = !in ? 0.0 : (natm == 1 ? __ldcs(hi + (size_t)(m0 + k) * nwn) : __ldg(hi + (size_t)(m0 + k) * nwn));
     }
 #pragma unroll
     for (int k = 0; k < 4; k++)
@@ -114,12 +114,62 @@ int tb_interp_run(tb_ctx *c) {
   return TB_OK;
 }
 
-// the same kernel over nvl virtual layers of a batch of atmospheres (tb_run_transit_batch)
+// interpolmolext for a BATCH of atmospheres (tb_run_transit_batch): a block owns 256 wavenumbers of ONE grid layer
+// and serves every atmosphere from it.  The atmospheres of a retrieval bracket a layer's temperature with a handful
+// of neighbouring grid temperatures, so the block walks those brackets upwards -- the upper planes of one bracket
+// stay in registers as the lower planes of the next -- and every grid plane is read ONCE per batch instead of once
+// per atmosphere (2 MB per (atmosphere, layer) otherwise: 6.4 GB per 32 atmospheres of C5).  Per atmosphere the
+// operations and their order are those of k_grid_interp: same bits.
+#define GI_MAXMOL 8
+__global__ void k_grid_interp_batch(int64_t nwn, int natm, int ngrid, int Ntemp, int Nmol, const double *__restrict__ grid,
+                                    const InterpLayer *__restrict__ L /*[natm*ngrid]*/,
+                                    const double *__restrict__ rho /*[Nmol][natm*ngrid]*/, double *__restrict__ e) {
+  const int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int r = blockIdx.y, nvl = natm * ngrid;
+  __shared__ int sh_it[64];
+  int lo_it = Ntemp, hi_it = -1;
+  for (int a0 = 0; a0 < natm; a0 += 64) {              // (warp-uniform: every thread scans the same brackets)
+    __syncthreads();
+    if (threadIdx.x < 64 && a0 + threadIdx.x < natm) sh_it[threadIdx.x] = L[(size_t)(a0 + threadIdx.x) * ngrid + r].it;
+    __syncthreads();
+    for (int k = 0; k < 64 && a0 + k < natm; k++) { lo_it = min(lo_it, sh_it[k]); hi_it = max(hi_it, sh_it[k]); }
+  }
+  if (w >= nwn) return;
+  const double *pl = grid + (((size_t)r * Ntemp) * Nmol) * nwn + w;
+  double vlo[GI_MAXMOL], vhi[GI_MAXMOL];
+#pragma unroll
+  for (int m = 0; m < GI_MAXMOL; m++) vlo[m] = m < Nmol ? __ldcs(pl + ((size_t)lo_it * Nmol + m) * nwn) : 0.0;
+  for (int it = lo_it; it <= hi_it; it++) {
+#pragma unroll
+    for (int m = 0; m < GI_MAXMOL; m++) vhi[m] = m < Nmol ? __ldcs(pl + ((size_t)(it + 1) * Nmol + m) * nwn) : 0.0;
+    for (int a = 0; a < natm; a++) {
+      const int v = a * ngrid + r;
+      const InterpLayer l = L[v];
+      if (l.it != it) continue;
+      double acc = 0.0;
+#pragma unroll
+      for (int m = 0; m < GI_MAXMOL; m++)
+        if (m < Nmol) {
+          const double ext = (vlo[m] * (l.thi - l.t) + vhi[m] * (l.t - l.tlo)) / (l.thi - l.tlo);
+          acc += rho[(size_t)m * nvl + v] * ext;
+        }
+      e[(size_t)v * nwn + w] = acc;
+    }
+#pragma unroll
+    for (int m = 0; m < GI_MAXMOL; m++) vlo[m] = vhi[m];
+  }
+}
+
 int tb_interp_launch(tb_ctx *c, int nvl, int ngrid, const InterpLayer *dL, const double *drho, double *e) {
-  const int ny = nvl < 32768 ? nvl : 32768;
-  dim3 g(nblk(c->nwn, 256), ny, (nvl + ny - 1) / ny);
   tb_timer_begin(c, "interp");
-  k_grid_interp<<<g, 256, 0, c->stream>>>(c->nwn, nvl, ngrid, (int)c->gNtemp, (int)c->gNmol, c->d_grid.p, dL, drho, e);
+  if (c->gNmol <= GI_MAXMOL && nvl > ngrid) {
+    k_grid_interp_batch<<<dim3(nblk(c->nwn, 256), ngrid), 256, 0, c->stream>>>(c->nwn, nvl / ngrid, ngrid, (int)c->gNtemp,
+                                                                              (int)c->gNmol, c->d_grid.p, dL, drho, e);
+  } else {       // one atmosphere, or more molecules than the batch kernel keeps in registers: a virtual layer per block row
+    const int ny = nvl < 32768 ? nvl : 32768;
+    dim3 g(nblk(c->nwn, 256), ny, (nvl + ny - 1) / ny);
+    k_grid_interp<<<g, 256, 0, c->stream>>>(c->nwn, nvl, ngrid, (int)c->gNtemp, (int)c->gNmol, c->d_grid.p, dL, drho, e);
+  }
   tb_timer_end(c, "interp");
   TB_LAUNCHED(c);
   return TB_OK;

@@ -1495,9 +1495,10 @@ __global__ void k_atm_setup(BatchPar B, int natm, const double *__restrict__ in,
                             InterpLayer *__restrict__ L /*[natm*nrad]*/, double *__restrict__ rho_g /*[Nm][natm*nrad]*/,
                             double *__restrict__ densfac /*[ntab][natm*nrad]*/, double *__restrict__ aux /*[natm][2][nrad]*/,
                             int32_t *__restrict__ err) {
-  __shared__ double sh_t[ATM_MAXLAYERS], sh_mm[ATM_MAXLAYERS], sh_rad[ATM_MAXLAYERS];
+  __shared__ double sh_t[ATM_MAXLAYERS], sh_mm[ATM_MAXLAYERS], sh_rad[ATM_MAXLAYERS], sh_lp[ATM_MAXLAYERS];
   const int a = blockIdx.x, n = B.nrad, nmol = B.nmol, nvl = natm * n;
   const double *x = in + (size_t)a * n * (1 + nmol);
+  for (int r = threadIdx.x; r + 1 < n; r += blockDim.x) sh_lp[r] = log(p[r] / p[r + 1]);   // radpress: log(pr[i]/pr[i+1])
   for (int r = threadIdx.x; r < n; r += blockDim.x) {
     const double T = x[r];
     double mm = 0, sumq = 0;
@@ -1567,15 +1568,20 @@ __global__ void k_atm_setup(BatchPar B, int natm, const double *__restrict__ in,
       mu0 = mu[i0] + ((mu[i0 - 1] - mu[i0]) / log(pr[i0 - 1] / pr[i0])) * log(p0 / pr[i0]);
       radius[i0] = r0 - 0.5 * (temp[i0] / mu[i0] + temp0 / mu0) * (kb_amu * log(pr[i0] / p0) / g0) / rfct;
     }
-    g = g0 * pow(r0 / radius[i0], 2.0);
+    // (pow(x, 2) of a correctly rounded libm is the rounded product x*x; the logarithms of the layers' pressure
+    // ratios do not depend on the atmosphere and were formed by the whole block: the chain below is ~10 operations
+    // per layer instead of a log and a pow)
+    { const double q = r0 / radius[i0]; g = g0 * (q * q); }
     for (int i = i0 - 1; i >= 0; i--) {
-      radius[i] = radius[i + 1] - 0.5 * (temp[i] / mu[i] + temp[i + 1] / mu[i + 1]) * (kb_amu * log(pr[i] / pr[i + 1]) / g) / rfct;
-      g = g * pow(radius[i + 1] / radius[i], 2.0);
+      radius[i] = radius[i + 1] - 0.5 * (temp[i] / mu[i] + temp[i + 1] / mu[i + 1]) * (kb_amu * sh_lp[i] / g) / rfct;
+      const double q = radius[i + 1] / radius[i];
+      g = g * (q * q);
     }
-    g = g0 * pow(r0 / radius[i0], 2.0);
+    { const double q = r0 / radius[i0]; g = g0 * (q * q); }
     for (int i = i0 + 1; i < n; i++) {
-      radius[i] = radius[i - 1] + 0.5 * (temp[i] / mu[i] + temp[i - 1] / mu[i - 1]) * (kb_amu * log(pr[i - 1] / pr[i]) / g) / rfct;
-      g = g * pow(radius[i - 1] / radius[i], 2.0);
+      radius[i] = radius[i - 1] + 0.5 * (temp[i] / mu[i] + temp[i - 1] / mu[i - 1]) * (kb_amu * sh_lp[i - 1] / g) / rfct;
+      const double q = radius[i - 1] / radius[i];
+      g = g * (q * q);
     }
   }
   __syncthreads();
