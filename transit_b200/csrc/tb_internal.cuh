@@ -104,7 +104,7 @@ struct __align__(16) LineRec {
 
 struct InterpLayer {   // per layer of an interpolated spectrum: lower grid-temperature index and the weights' ingredients
   int it;
-  double t, tlo, thi;
+  double t, tlo, thi, rdt;   // rdt = RN(1 / (thi - tlo))
 };
 
 struct CiaTable {
@@ -348,6 +348,14 @@ __device__ __forceinline__ double tb_exp(double x) {
   p = fma(p, r, 1.0);
   const int k = (int)kf;
   return p * __hiloint2double((k + 1023) << 20, 0);
+}
+
+// RN(x / y) given r = RN(1 / y): quotient estimate, exact remainder by FMA, one correction (Markstein):
+// the same correctly rounded quotient as the division, without recomputing the reciprocal of a
+// constant divisor for every element (an FP64 division is ~40 dependent instructions)
+__device__ __forceinline__ double tb_div_r(double x, double y, double r) {
+  const double q = x * r;
+  return fma(fma(-q, y, x), r, q);
 }
 
 // internal entry points between translation units

@@ -67,7 +67,9 @@ __global__ void k_grid_interp(int64_t nwn, int nrad, int ngrid, int Ntemp, int N
 #pragma unroll
     for (int k = 0; k < 4; k++)
       if (m0 + k < Nmol) {
-        const double ext = (vlo[k] * (l.thi - l.t) + vhi[k] * (l.t - l.tlo)) / (l.thi - l.tlo);
+        // the divisor depends on the layer only: its reciprocal comes with the layer, the quotient is completed to
+        // the correctly rounded one (tb_div_r)
+        const double ext = tb_div_r(vlo[k] * (l.thi - l.t) + vhi[k] * (l.t - l.tlo), l.thi - l.tlo, l.rdt);
         acc += rho[(m0 + k) * nrad + r] * ext;
       }
   }
@@ -95,6 +97,7 @@ int tb_interp_run(tb_ctx *c) {
     TB_REQUIRE(it >= 0 && it + 1 < Nt, TB_ERR_DOMAIN,
                "layer %d temperature %.2f K is outside the opacity grid [%.1f, %.1f] K", r, T, c->gtemp[0], c->gtemp[Nt - 1]);
     L[r].it = it; L[r].t = T; L[r].tlo = c->gtemp[it]; L[r].thi = c->gtemp[it + 1];
+    L[r].rdt = 1.0 / (L[r].thi - L[r].tlo);
     for (int m = 0; m < Nm; m++) rho[(size_t)m * nrad + r] = c->dens[(size_t)c->gmol_idx[m] * nrad + r];
   }
   // staging buffers live in the context: a retrieval calls this once per atmosphere
@@ -150,7 +153,7 @@ __global__ void k_grid_interp_batch(int64_t nwn, int natm, int ngrid, int Ntemp,
 #pragma unroll
       for (int m = 0; m < GI_MAXMOL; m++)
         if (m < Nmol) {
-          const double ext = (vlo[m] * (l.thi - l.t) + vhi[m] * (l.t - l.tlo)) / (l.thi - l.tlo);
+          const double ext = tb_div_r(vlo[m] * (l.thi - l.t) + vhi[m] * (l.t - l.tlo), l.thi - l.tlo, l.rdt);
           acc += rho[(size_t)m * nvl + v] * ext;
         }
       e[(size_t)v * nwn + w] = acc;

@@ -554,13 +554,6 @@ struct TauPar {
   double cl_ext, cl_top, cl_bot, cl_gamma, cl_Q, cl_r, cl_sig, cl_refwn;
 };
 
-// RN(x / y) given r = RN(1 / y): quotient estimate, exact remainder by FMA, one correction (Markstein):
-// the same correctly rounded quotient as the division, without recomputing the reciprocal of a
-// per-ray constant for every wavenumber (an FP64 division is ~40 dependent instructions)
-__device__ __forceinline__ double tb_div_r(double x, double y, double r) {
-  const double q = x * r;
-  return fma(fma(-q, y, x), r, q);
-}
 
 // interp_parab (numerical.c:182-195) with the per-ray constants dx, x0 = x[0]/dx and the
 // reciprocals rcp[0] = 1/(2 dx^2), rcp[1] = 1/dx (k_ray_geometry)
@@ -1536,7 +1529,7 @@ __global__ void k_atm_setup(BatchPar B, int natm, const double *__restrict__ in,
     if (tk < gtemp[it]) it--;
     if (it < 0 || it + 1 >= B.Nt) { atomicExch(err + 6, 1); it = it < 0 ? 0 : B.Nt - 2; }
     InterpLayer l;
-    l.it = it; l.t = tk; l.tlo = gtemp[it]; l.thi = gtemp[it + 1];
+    l.it = it; l.t = tk; l.tlo = gtemp[it]; l.thi = gtemp[it + 1]; l.rdt = 1.0 / (l.thi - l.tlo);
     L[(size_t)a * n + r] = l;
     for (int m = 0; m < B.Nm; m++) rho_g[(size_t)m * nvl + (size_t)a * n + r] = dens[((size_t)a * nmol + gmol_idx[m]) * n + r];
     for (int k = 0; k < B.ntab; k++) {                      // crosssec.c:321-326
