@@ -373,6 +373,8 @@ def bands_leg(args, prob, ref_out, one_gpu_ms, local_rank, rank, world, stream, 
     tb = sharding.BandShardedTransit(local_rank, rank, world)
     tb.ctx.set_stream(stream.cuda_stream)
     tb.transit_init(prob)
+    first_cut = list(tb.bands)
+    tb.rebalance(rounds=2)                    # measured rebalancing: cost per line group differs from band to band
     for _ in range(max(3, args.warmup)):
         g = tb.do_transit_gathered()
     same = bool(np.array_equal(g.cpu().numpy(), ref_out)) if rank == 0 else True
@@ -395,14 +397,22 @@ def bands_leg(args, prob, ref_out, one_gpu_ms, local_rank, rank, world, stream, 
     torch.cuda.synchronize(); dist.barrier()
     t = torch.tensor([float(np.sum(ms)), 0.0 if same else 1.0], dtype=torch.float64, device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    names = ("molext", "kmax", "strength", "fused", "accumulate", "tau", "cia", "gather")
+    mine = torch.tensor([float(np.median(kms.get(nm, [0.0]))) for nm in names] + [float(np.median(ms))],
+                        dtype=torch.float64, device="cuda")
+    allr = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(allr, mine)
+    per_rank = {nm: [round(float(a[i]), 4) for a in allr] for i, nm in enumerate(names + ("step",))}
     tb.free_memory()
     step_ms = float(t[0]) / args.steps
     return {"what": f"one {args.workload} spectrum per step, wavenumber range in {world} bands (strong scaling)",
             "ms_per_step": step_ms, "spectra_per_s": 1e3 / step_ms, "one_gpu_ms_per_step": one_gpu_ms,
             "speedup_vs_one_gpu": one_gpu_ms / step_ms, "efficiency": one_gpu_ms / step_ms / world,
             "bit_identical_to_single_gpu": bool(float(t[1]) == 0.0), "bands": tb.bands,
+            "bands_before_rebalancing": first_cut,
             "exchange": "in-library NCCL: 2 x ncclAllReduce(MAX) + 1 x ncclAllGather per spectrum, on the context stream",
-            "rank0_kernel_ms": {k: float(np.mean(v)) for k, v in kms.items()}, "ms_step_stats": ms_stats(ms)}
+            "rank0_kernel_ms": {k: float(np.mean(v)) for k, v in kms.items()}, "ms_step_stats": ms_stats(ms),
+            "per_rank_median_ms": per_rank}
 
 
 def run_ours(args):

@@ -276,6 +276,12 @@ void do_transit(double *transit_out) {
   if (h->savefiles && h->f_outsample) write_outsample();   /* makeipsample, makesample.c:598-599 */
   timecheck(6, "makeipsample");
   CK(tb_set_modlevel(S.ctx, h->modlevel));
+  if (th_world > 1 && !S.rebalanced) {     /* one spectrum to measure the bands, cut again by measured cost, then the real one */
+    CK(tb_spectrum(S.ctx, S.eclipse ? TB_GEOM_ECLIPSE : TB_GEOM_TRANSIT, h->toomuch, h->ethresh,
+                   h->starrad * TH_SUNRADIUS, h->transparent, S.eclipse ? S.angles : NULL, S.nang, S.out));
+    if (!S.have_grid_file) CK(tb_rebalance_bands(S.ctx));
+    S.rebalanced = 1;
+  }
   CK(tb_spectrum(S.ctx, S.eclipse ? TB_GEOM_ECLIPSE : TB_GEOM_TRANSIT, h->toomuch, h->ethresh,
                  h->starrad * TH_SUNRADIUS, h->transparent, S.eclipse ? S.angles : NULL, S.nang, S.out));
   if (h->verb >= 4) {      /* one device call covers the reference's stages: their share of it, from the device timers */

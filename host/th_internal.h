@@ -80,7 +80,7 @@ typedef struct {
   double angles[16];
   /* device */
   tb_ctx *ctx;
-  int have_grid_file, initialised;
+  int have_grid_file, initialised, rebalanced;
   int64_t band_lo, band_hi;       /* this rank's wavenumber band (whole grid when world = 1) */
   double *out;
 } th_state;

@@ -222,6 +222,10 @@ int  tb_comm_destroy(tb_ctx *c);
 int  tb_comm_barrier(tb_ctx *c);     /* all ranks have finished what they enqueued (tiny all-reduce + stream sync) */
 int  tb_balanced_bands(tb_ctx *c, int world, int64_t *edges /*[world+1]*/);
 int  tb_set_bands(tb_ctx *c, int world, const int64_t *edges /*[world+1]*/, int rank);
+/* after a first spectrum: all ranks exchange the device time of their line sum, re-weight each band's line groups
+ * by the cost per group measured there and cut the grid again (a collective call; same result on every rank) */
+int  tb_rebalance_bands(tb_ctx *c);
+int  tb_get_bands(tb_ctx *c, int64_t *edges /*[world+1]*/);
 
 /* device micro-benchmarks used for the roofline denominators (FP64 FMA / exp / copy)   */
 int  tb_microbench(tb_ctx *c, double *dfma_tflops, double *dexp_gops, double *copy_gbs);

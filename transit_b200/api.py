@@ -94,6 +94,8 @@ ABI = {
     "tb_comm_barrier": (C.c_int, [C.c_void_p]),
     "tb_balanced_bands": (C.c_int, [C.c_void_p, C.c_int, i64p]),
     "tb_set_bands": (C.c_int, [C.c_void_p, C.c_int, i64p, C.c_int]),
+    "tb_rebalance_bands": (C.c_int, [C.c_void_p]),
+    "tb_get_bands": (C.c_int, [C.c_void_p, i64p]),
     "tb_set_shard": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
 }
 
@@ -477,6 +479,12 @@ class Context:
     def balanced_bands(self, world):
         e = np.zeros(world + 1, np.int64)
         self._ck(self.lib.tb_balanced_bands(self.h, int(world), _p(e, i64p)), "tb_balanced_bands")
+        return e
+
+    def rebalance_bands(self, world):
+        self._ck(self.lib.tb_rebalance_bands(self.h), "tb_rebalance_bands")
+        e = np.zeros(world + 1, np.int64)
+        self._ck(self.lib.tb_get_bands(self.h, _p(e, i64p)), "tb_get_bands")
         return e
 
     def set_bands(self, edges, rank):

@@ -102,8 +102,56 @@ int tb_comm_allreduce_max(tb_ctx *c, int what, void *device_ptr, int64_t count) 
 // (the line sum's cost per bin is groups x profile width, and the width profile is the same for every band);
 // ends on multiples of the 128-bin accumulate tile, the last band ends at the grid end, bands may be empty.
 // Every rank computes the same table from the same line index.
+static int tb_cut_bands(tb_ctx *c, int world, const std::vector<double> *scale_per_tile, int64_t *edges);
+
 extern "C" int tb_balanced_bands(tb_ctx *c, int world, int64_t *edges) {
   TB_REQUIRE(c->have_grid && world >= 1 && edges, TB_ERR_STATE, "tb_set_wn_grid must precede tb_balanced_bands");
+  return tb_cut_bands(c, world, nullptr, edges);
+}
+
+// Measured rebalancing: the cost of a band is not proportional to its line groups (profiles widen with the
+// wavenumber, the deep layers' wings cross band ends), so after a first spectrum every rank contributes the device
+// time of its line sum (ncclAllGather of one double), each band's groups are re-weighted by the cost per group
+// measured in it, and the grid is cut again.  The same table on every rank; results do not depend on the cut.
+extern "C" int tb_rebalance_bands(tb_ctx *c) {
+  TB_REQUIRE(c->comm && c->comm_world > 1 && (int)c->band_edges.size() == c->comm_world + 1, TB_ERR_STATE,
+             "tb_rebalance_bands: tb_comm_init and tb_set_bands must come first");
+  const int world = c->comm_world;
+  float ms = 0.f, ms_k = 0.f;
+  TB_TRY(tb_get_kernel_ms(c, "molext", &ms));
+  // the strength-maximum stage ends with the all-reduce, i.e. with waiting for the slowest rank: not this band's cost
+  if (tb_get_kernel_ms(c, "kmax", &ms_k) != TB_OK) ms_k = 0.f;
+  TB_CUDA(cudaSetDevice(c->device));
+  TB_TRY(c->g_send.ensure(1)); TB_TRY(c->g_recv.ensure(world));
+  const double mine = ms - ms_k > 0.01f ? ms - ms_k : 0.01;
+  TB_CUDA(cudaMemcpyAsync(c->g_send.p, &mine, sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  TB_NCCL(g_nccl.AllGather(c->g_send.p, c->g_recv.p, 1, ncclDouble, (ncclComm_t)c->comm, c->stream));
+  std::vector<double> cost(world);
+  TB_CUDA(cudaMemcpyAsync(cost.data(), c->g_recv.p, world * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  TB_CUDA(cudaStreamSynchronize(c->stream));
+  // cost per unit of weight inside each old band, as a scale per 128-bin tile
+  const int64_t ntile = (c->nwn + 127) / 128;
+  std::vector<double> scale(ntile, 1.0);
+  std::vector<int64_t> one(world + 1);
+  std::vector<double> unit(ntile, 1.0);
+  {
+    // weights of the old bands with unit scale
+    std::vector<int64_t> tmp(world + 1);
+    std::vector<double> wsum(world, 0.0);
+    c->tile_weight.clear();
+    TB_TRY(tb_cut_bands(c, world, &unit, tmp.data()));          // fills c->tile_weight
+    for (int r = 0; r < world; r++)
+      for (int64_t t = c->band_edges[r] / 128; t < (c->band_edges[r + 1] + 127) / 128 && t < ntile; t++) wsum[r] += c->tile_weight[t];
+    for (int r = 0; r < world; r++)
+      for (int64_t t = c->band_edges[r] / 128; t < (c->band_edges[r + 1] + 127) / 128 && t < ntile; t++)
+        scale[t] = wsum[r] > 0 && cost[r] > 0 ? cost[r] / wsum[r] : 1.0;
+  }
+  std::vector<int64_t> edges(world + 1);
+  TB_TRY(tb_cut_bands(c, world, &scale, edges.data()));
+  return tb_set_bands(c, world, edges.data(), c->comm_rank);
+}
+
+static int tb_cut_bands(tb_ctx *c, int world, const std::vector<double> *scale_per_tile, int64_t *edges) {
   TB_CUDA(cudaSetDevice(c->device));
   const int64_t nwn = c->nwn;
   const int nrows = c->nrows;
@@ -125,6 +173,11 @@ extern "C" int tb_balanced_bands(tb_ctx *c, int world, int64_t *edges) {
         const size_t a = (size_t)r * nwn + j0, b = (size_t)r * nwn + j1;
         w += (double)(c->h_binstart[b] - c->h_binstart[a]);
       }
+    if (scale_per_tile) {
+      if ((int64_t)c->tile_weight.size() != ntile) c->tile_weight.assign(ntile, 0.0);
+      c->tile_weight[t] = w;
+      w *= (*scale_per_tile)[t];
+    }
     cum[t + 1] = cum[t] + w;
   }
   int64_t prev = 0;
@@ -206,5 +259,11 @@ extern "C" int tb_comm_barrier(tb_ctx *c) {
   TB_CUDA(cudaMemsetAsync(c->g_send.p, 0, sizeof(double), c->stream));
   TB_NCCL(g_nccl.AllReduce(c->g_send.p, c->g_send.p, 1, ncclDouble, ncclMax, (ncclComm_t)c->comm, c->stream));
   TB_CUDA(cudaStreamSynchronize(c->stream));
+  return TB_OK;
+}
+
+extern "C" int tb_get_bands(tb_ctx *c, int64_t *edges) {
+  TB_REQUIRE(!c->band_edges.empty() && edges, TB_ERR_STATE, "tb_set_bands not called");
+  memcpy(edges, c->band_edges.data(), c->band_edges.size() * sizeof(int64_t));
   return TB_OK;
 }

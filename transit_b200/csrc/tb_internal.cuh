@@ -200,6 +200,7 @@ struct tb_ctx {
   void *comm = nullptr;
   int comm_rank = 0, comm_world = 1;
   std::vector<int64_t> band_edges;    // [world + 1]
+  std::vector<double> tile_weight;    // line groups per 128-bin tile (tb_rebalance_bands)
   DevBuf<double> g_send, g_recv;
   DevBuf<int64_t> g_edges;
   int g_edges_world = 0;

@@ -1156,9 +1156,9 @@ k_lastq_scan(int ns, int niso, int nrows, int permol, double ethresh, double wn_
              const double *__restrict__ kmax, const int *__restrict__ iso_row,
              const double *__restrict__ alphal, const double *__restrict__ alphad,
              const double *__restrict__ ral, const double *__restrict__ xterm, int64_t X,
-             const int32_t *__restrict__ fclass, int32_t *lastq /* preset to -1 */) {
+             const int32_t *__restrict__ fclass, int all, int32_t *lastq /* preset to -1 */) {
   const int pair = blockIdx.x, s = pair / niso, iso = pair % niso;      // (x: up to 2^31 pairs; y: the chunk dealer)
-  if (!fclass[s / FB]) return;                   // k_strength finds it for the states it evaluates
+  if (!all && !fclass[s / FB]) return;           // (else) k_strength finds it for the states it evaluates
   const int og0 = iso_og0[iso], og1 = iso_og1[iso];
   if (og1 <= og0) return;
   const double al = alphal[pair], ad = alphad[pair], rl = ral[pair];
@@ -1623,28 +1623,37 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       k_logthr<<<nblk((int64_t)cs * niso, 128), 128, 0, st>>>(cs, niso, nrows, permol, ethresh, c->d_iso_row.p,
                                                               c->s_facz.p, c->s_kmax.p, c->s_lcz.p);
       TB_LAUNCHED(c);
+      // carried Doppler index by bisection + backward scan of the file order (k_lastq_scan) instead of maxima over the
+      // evaluated groups: for the fused states that keep one, and -- in a band-sharded run with the exchange in the
+      // library -- for EVERY state: the scan reads the whole line index, so each rank finds the global index by
+      // itself and the all-reduce of the carried index (one collective, one rendez-vous of the ranks) is not needed
+      const bool scan_all = c->shard_world > 1 && !c->exch && c->og_contig;
+      const bool scan_fused = fuse_on && c->fuse_carried && c->og_contig;
+      if (scan_all || scan_fused) {
+        TB_TRY(c->s_lastq2.ensure((size_t)chunk * niso + 1));
+        TB_CUDA(cudaMemsetAsync(c->s_lastq2.p, 0xff, (size_t)cs * niso * sizeof(int32_t), st));
+        k_lastq_scan<<<dim3(cs * niso, LASTQ_NB), 256, 0, st>>>(
+            cs, niso, nrows, permol, ethresh, c->wn_i, c->iso_og0.p, c->iso_og1.p, c->go_pos.p, c->go_wavn.p, c->g_start.p,
+            c->g_gf.p, c->g_a0.p, c->g_lg.p, c->g_wavn.p, c->s_rtemp.p, c->s_facz.p, c->s_lcz.p, c->s_kmax.p,
+            c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ral.p, c->s_xterm.p, X, c->s_fclass.p, scan_all ? 1 : 0,
+            c->s_lastq2.p);
+        TB_LAUNCHED(c);
+      }
       if (fuse_on && tile_hi > tile_lo) {
         tb_timer_end(c, "strength");
         tb_timer_begin(c, "fused");
-        // carried Doppler index of the fused states: found by bisection + a short backward scan of the file order
-        TB_TRY(c->s_lastq2.ensure((size_t)chunk * niso + 1));
-        if (c->fuse_carried && c->og_contig) {   // (else only always-refreshing states are fused: their carried index is never read)
-          TB_CUDA(cudaMemsetAsync(c->s_lastq2.p, 0xff, (size_t)cs * niso * sizeof(int32_t), st));
-          k_lastq_scan<<<dim3(cs * niso, LASTQ_NB), 256, 0, st>>>(
-              cs, niso, nrows, permol, ethresh, c->wn_i, c->iso_og0.p, c->iso_og1.p, c->go_pos.p, c->go_wavn.p, c->g_start.p,
-              c->g_gf.p, c->g_a0.p, c->g_lg.p, c->g_wavn.p, c->s_rtemp.p, c->s_facz.p, c->s_lcz.p, c->s_kmax.p,
-              c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ral.p, c->s_xterm.p, X, c->s_fclass.p, c->s_lastq2.p);
+        if (scan_fused) {      // (else only always-refreshing states are fused: their carried index is never read)
           k_fallback<<<nblk(cs * niso, 128), 128, 0, st>>>(
               cs, niso, c->s_fclass.p, 1, c->s_lastq2.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
               c->nDop, c->nLor, c->d_ptab.p, c->s_fb.p, c->s_fbpid.p, c->s_fbmax.p);
-          c->launches += 2;
+          TB_LAUNCHED(c);
         }
         LineRec *trace_rec = nullptr;
         if (c->trace_enabled) {                 // per-line trace wanted: records of the fused states too
           k_fuse_trace_fill<<<dim3(nblk(G, Tn), cs), Tn, 0, st>>>(G, cs, c->s_fclass.p, c->g_iown.p, c->s_rec.p);
           trace_rec = c->s_rec.p;
         }
-        const bool carried = c->fuse_carried && c->og_contig;
+        const bool carried = scan_fused;
         auto fused_kernel = carried ? k_linesum_fused<true> : k_linesum_fused<false>;
         fused_kernel<<<dim3(tile_hi - tile_lo, nbatch * (FB / FBK)), FUSE_NT, fuse_shm, st>>>(
             nwn, c->onwn, G, cs, niso, nmol, c->o, fd_o, fd_tile, nrows, permol, tile_lo, c->wn_i, c->odwn,
@@ -1678,7 +1687,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
           c->d_aDop.p, c->nDop, c->d_ptab.p, c->nLor, ethresh, permol, nrows, c->s_kmax.p,
           c->s_rec.p, c->s_lastq.p, c->s_wtile.p, c->s_hasfb.p, ntiles, c->s_fclass.p);
       }
-      if (c->shard_world > 1) {
+      if (c->shard_world > 1 && !scan_all) {
         if (c->exch)
           TB_REQUIRE(c->exch(c->exch_user, TB_EXCH_LASTQ, c->s_lastq.p, (int64_t)cs * niso) == 0, TB_ERR_STATE,
                      "exchange callback failed (carried Doppler index)");
@@ -1686,7 +1695,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       }
       tb_timer_end(c, "strength");
       k_fallback<<<nblk(cs * niso, 128), 128, 0, st>>>(
-          cs, niso, c->s_fclass.p, 0, c->s_lastq.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
+          cs, niso, c->s_fclass.p, 0, scan_all ? c->s_lastq2.p : c->s_lastq.p, c->s_idop0.p, c->go_wavn.p, c->s_alphad.p, c->s_ilor.p, c->d_aDop.p,
           c->nDop, c->nLor, c->d_ptab.p, c->s_fb.p, c->s_fbpid.p, c->s_fbmax.p);
       c->launches += 3;
     }

@@ -220,6 +220,18 @@ class BandShardedTransit(ShardedTransit):
             lo, hi = self.bands[self.rank]
             self.ctx.set_shard(lo, hi, self.rank, self.world, nccl_exchange() if self.world > 1 else None)
 
+    def rebalance(self, rounds=2):
+        """Measured rebalancing (tb_rebalance_bands): one spectrum, then the grid is cut again by the cost per line
+        group measured in every band; a collective call."""
+        if self.exchange != "library" or self.world == 1:
+            return self.bands
+        for _ in range(rounds):
+            self.do_transit(None)
+            self.do_transit(None)
+            edges = self.ctx.rebalance_bands(self.world)
+            self.bands = [(int(edges[r]), int(edges[r + 1])) for r in range(self.world)]
+        return self.bands
+
     def do_transit_gathered(self):
         """Spectrum [nwn] on every rank as a CUDA tensor: own band computed here, the rest gathered."""
         self.do_transit(None)
