@@ -205,6 +205,7 @@ extern "C" int tb_set_bands(tb_ctx *c, int world, const int64_t *edges, int rank
     TB_REQUIRE(edges[r] <= edges[r + 1], TB_ERR_ARG, "tb_set_bands: band edges must not decrease");
   TB_REQUIRE(edges[0] == 0 && edges[world] == c->nwn, TB_ERR_ARG, "tb_set_bands: the bands must cover the grid");
   c->band_edges.assign(edges, edges + world + 1);
+  c->g_edges_world = 0;                 // the device copy of the table (spectrum gather) is stale
   c->exch = nullptr;
   c->exch_user = nullptr;
   if (world == 1) return tb_set_shard(c, 0, 0, 0, 1, nullptr, nullptr);
