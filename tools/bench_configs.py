@@ -118,7 +118,8 @@ def run_c5(bench, args):
         t.ctx.set_stream(ws.cuda_stream)
         t.transit_init(prob, opacity=dict(molID=molID, temp=GRID_TEMPS, press=prob.p * prob.p_fct, grid=grid))
         trs.append(t); wstreams.append(ws)
-    del grid                                             # the resident copies serve every atmosphere
+    if getattr(args, "c5_api", "single") != "device":
+        del grid                                         # the resident copies serve every atmosphere
     mine = list(sharding.atmosphere_shard(args.natm, rank, world))
     batch = min(args.batch, max(1, len(mine)))
     atms = [workloads.perturbed(prob, seed=5000 + i, dT=150.0, dex=1.0) for i in mine[:batch * 2]]
@@ -131,7 +132,7 @@ def run_c5(bench, args):
     # tb_set_atmosphere + tb_spectrum per atmosphere, as BART calls run_transit
     use_batch = getattr(args, "c5_api", "single") == "batch"
     if getattr(args, "c5_api", "single") == "device":
-        return run_c5_device(bench, args, torch, dist, rank, local_rank, world, prob, first, stream, build_s, grid_bytes, mine)
+        return run_c5_device(bench, args, torch, dist, rank, local_rank, world, prob, first, stream, build_s, grid_bytes, mine, grid, molID)
     share = [list(range(k * batch // K, (k + 1) * batch // K)) for k in range(K)]
     stacked = {}
 
@@ -236,7 +237,7 @@ def retrieval_inputs(prob, idx, dT=150.0, dex=1.0):
     return np.ascontiguousarray(np.stack(rows))
 
 
-def run_c5_device(bench, args, torch, dist, rank, local_rank, world, prob, tr, stream, build_s, grid_bytes, mine):
+def run_c5_device(bench, args, torch, dist, rank, local_rank, world, prob, tr, stream, build_s, grid_bytes, mine, grid, molID):
     """C5 through tb_run_transit_batch: ONE context; a step = one call with --batch atmospheres as BART hands them over
     ([T | q...] per atmosphere, host memory), per-atmosphere set-up (densities, hydrostatic radii) on the device, every
     stage launched once per 32 atmospheres, the spectra back in host memory at the end of the call."""
@@ -302,21 +303,167 @@ def run_c5_device(bench, args, torch, dist, rank, local_rank, world, prob, tr, s
                          "peak_source": src, "algorithmic_bytes": ab},
             "clocks": clocks}
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = c5_cpu_baseline(bench, args, prob)
+            line["cpu_baseline"] = c5_cpu_baseline(bench, args, prob, grid, molID)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
-def c5_cpu_baseline(bench, args, prob):
-    """the unmodified reference serving run_transit calls from an opacity file, one process
-    per core.  The grid file here is the C5 grid at a REDUCED wavenumber range (every per-spectrum cost of the
-    reference is per wavenumber; the sample is stated), built by the reference's own --justOpacity is too slow,
-    so the file is written from the B200 grid -- the reference only reads and interpolates it."""
-    return {"value": None, "unit": "spectra/s", "cores": 0, "kind": "reference",
-            "sample": "see tests/test_fullsize_parity.py::test_c5_shape_retrieval_from_c2_grid: the unmodified reference serves "
-                      "one run_transit from the full-size C2 grid in ~1.5 s on one core (7.4 s for transit_init + 5 spectra)"}
+REF_BIN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "transit")
+REF_SO = os.path.join(os.path.dirname(REF_BIN), "libtransit_ref.so")
+
+
+def write_opacity_file(path, molID, temps, press_cgs, wn, grid):
+    """opacity.c:405-421: 4 longs, molID, temperatures, pressures, wavenumbers, o[r][t][m][w]."""
+    Nl, Nt, Nm, Nw = grid.shape
+    with open(path, "wb") as f:
+        np.array([Nm, Nt, Nl, Nw], "<i8").tofile(f)
+        np.asarray(molID, "<i4").tofile(f); np.asarray(temps, "<f8").tofile(f)
+        np.asarray(press_cgs, "<f8").tofile(f); np.asarray(wn, "<f8").tofile(f)
+        np.ascontiguousarray(grid, "<f8").tofile(f)
+
+
+def _ref_retrieval_worker(cfg, inputs, conn):
+    """One process = one instance of the unmodified reference: transit_init once, then run_transit per input."""
+    import ctypes as C
+    os.dup2(os.open(os.devnull, os.O_WRONLY), 1)
+    L = C.CDLL(REF_SO)
+    argv = [b"transit", b"-c", cfg.encode()]
+    arr = (C.c_char_p * len(argv))(*argv)
+    t0 = time.perf_counter()
+    L.transit_init(len(argv), arr)
+    L.get_no_samples.restype = C.c_int
+    n = L.get_no_samples()
+    init_s = time.perf_counter() - t0
+    out = np.zeros(n)
+    P = C.POINTER(C.c_double)
+    conn.send(("ready", init_s))
+    conn.recv()
+    t0 = time.perf_counter()
+    for x in inputs:
+        x = np.ascontiguousarray(x)
+        L.run_transit(x.ctypes.data_as(P), x.size, out.ctypes.data_as(P), n)
+    conn.send((time.perf_counter() - t0, float(out.sum())))
+
+
+def c5_cpu_baseline(bench, args, prob, grid, molID):
+    """the unmodified reference serving run_transit calls from the SAME full-size grid (written
+    here as an opacity file; the reference only reads and interpolates it), one process per core, each process its own
+    atmospheres -- the only parallelism the reference has."""
+    import multiprocessing as mp
+    if not os.path.exists(REF_SO):
+        return {"value": None, "unit": "spectra/s", "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+    from transit_b200 import workloads
+    d = os.path.join("/tmp", f"transit_b200_c5ref_{os.getpid()}")
+    cfg, _ = workloads.write_reference_inputs(prob, d)
+    k = prob.nrad // 3
+    opa = os.path.join(d, "grid.opa")
+    write_opacity_file(opa, molID, GRID_TEMPS, prob.p * prob.p_fct, prob.wn_i + np.arange(prob.nwn) * prob.wn_d, grid)
+    with open(cfg, "a") as f:
+        f.write(f"refpress {prob.p[k]:.6e}\nrefradius {prob.rad[k]:.6f}\ngsurf 1500.0\nopacityfile {opa}\n")
+    nproc = max(1, min(os.cpu_count() or 1, 8))           # 8 x 2.6 GB of grid in host memory
+    per = 3
+    ctx = mp.get_context("fork")
+    pipes, procs = [], []
+    for i in range(nproc):
+        a, b = ctx.Pipe()
+        inputs = retrieval_inputs(prob, [900000 + i * per + j for j in range(per)])
+        p_ = ctx.Process(target=_ref_retrieval_worker, args=(cfg, inputs, b), daemon=True)
+        p_.start(); pipes.append(a); procs.append(p_)
+    inits = []
+    for a in pipes:
+        if not a.poll(900):
+            raise RuntimeError("reference worker did not initialise")
+        inits.append(a.recv()[1])
+    t0 = time.perf_counter()
+    for a in pipes:
+        a.send("go")
+    res = [a.recv() for a in pipes]
+    wall = time.perf_counter() - t0
+    for p_ in procs:
+        p_.join(timeout=5)
+    try:
+        os.remove(opa)
+    except OSError:
+        pass
+    return {"value": nproc * per / wall, "unit": "spectra/s", "cores": nproc, "kind": "reference",
+            "sample": f"{nproc} processes of the unmodified reference (libtransit_ref.so), each transit_init from the full-size C2 grid "
+                      f"file ({grid.nbytes / 1e9:.1f} GB, {np.mean(inits):.1f} s, not counted) and then {per} run_transit calls with "
+                      f"perturbed profiles: {wall:.1f} s for {nproc * per} spectra; one core alone: {np.mean([r[0] for r in res]) / per:.2f} s per spectrum"}
+
+
+def c4_cpu_baseline(bench, args):
+    """The unmodified reference binary on the C4 shape at a TENTH of the wavenumbers (1e5 samples, 0.96 GB grid file);
+    every per-spectrum cost of the reference is per wavenumber, so the full size is 10x (stated in `sample`)."""
+    import subprocess
+    if not os.path.exists(REF_BIN):
+        return {"value": None, "unit": "spectra/s", "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+    from transit_b200 import workloads
+    prob = c4_problem(nwn=100001)
+    temps = np.array([800.0, 1000.0, 1200.0, 1400.0, 1600.0, 1800.0])
+    d = os.path.join("/tmp", f"transit_b200_c4ref_{os.getpid()}")
+    cfg, _ = workloads.write_reference_inputs(prob, d)
+    molID = np.array([prob.mol_ID[prob.species_names.index(s)] for s in ("H2O", "CH4")], np.int32)
+    opa = os.path.join(d, "grid.opa")
+    write_opacity_file(opa, molID, temps, prob.p * prob.p_fct, prob.wn_i + np.arange(prob.nwn) * prob.wn_d, c4_grid(prob, temps))
+    with open(cfg, "a") as f:
+        f.write(f"opacityfile {opa}\n")
+    t0 = time.perf_counter()
+    r = subprocess.run([REF_BIN, "-c", cfg], capture_output=True, text=True, cwd=d)
+    wall = time.perf_counter() - t0
+    os.remove(opa)
+    if r.returncode != 0:
+        return {"value": None, "unit": "spectra/s", "cores": 1, "kind": "reference", "sample": "reference run failed: " + r.stdout[-200:]}
+    return {"value": 1.0 / (10.0 * wall), "unit": "spectra/s", "cores": 1, "kind": "reference",
+            "sample": f"the unmodified reference binary, one process, C4 shape at 100 001 wavenumbers (a tenth): {wall:.1f} s wall "
+                      f"including transit_init and reading the 0.96 GB grid file; value = 1 / (10 x that), a linear extrapolation in the "
+                      f"wavenumber count (labelled: not a measurement at 1e6)"}
+
+
+def c3_cpu_baseline(bench, args, ctx_factory):
+    """the reference's --justOpacity build on a 1e5-line subsample of the C3 line list, 10 layers,
+    at 2 and at 6 grid temperatures; the DIFFERENCE of the two runs is the cost of 40 more (layer, T) states without
+    transit_init (TLI read, Voigt table), and the rate in line-states/s extrapolates linearly in lines x states."""
+    import subprocess
+    if not os.path.exists(REF_BIN):
+        return {"value": None, "unit": "G line-samples/s", "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+    from transit_b200 import workloads
+    c3_problem(1.0)                                        # registers CONFIGS["C3"]
+    prob = workloads.make_problem("C3", scale=1e-3, nlayers=10)
+    d = os.path.join("/tmp", f"transit_b200_c3ref_{os.getpid()}")
+    cfg, nlines = workloads.write_reference_inputs(prob, d)
+    walls = {}
+    for nt, thigh in ((2, 900), (6, 1300)):
+        opa = os.path.join(d, f"g{nt}.opa")
+        t0 = time.perf_counter()
+        r = subprocess.run([REF_BIN, "-c", cfg, "--opacityfile", opa, "--justOpacity", "--tlow", "800", "--thigh", str(thigh),
+                            "--tempdelt", "100"], capture_output=True, text=True, cwd=d)
+        walls[nt] = time.perf_counter() - t0
+        if r.returncode != 0:
+            return {"value": None, "unit": "G line-samples/s", "cores": 1, "kind": "reference", "sample": "reference run failed: " + r.stdout[-200:]}
+        os.remove(opa)
+    dstates = 10 * (6 - 2)
+    dt = max(walls[6] - walls[2], 1e-3)
+    # the same 40 states through the library, for the number of profile updates they execute (the metric's unit)
+    temps = np.arange(1000.0, 1300.1, 100.0)
+    ziso = _ziso(prob, temps)
+    tr = ctx_factory(prob)
+    T, D, Z = [], [], []
+    for r_ in range(prob.nrad):
+        for t, temp in enumerate(temps):
+            T.append(temp)
+            D.append(1.66053886e-24 * prob.mol_q[:, r_] * (prob.p[r_] * prob.p_fct) / 1.380658e-16 / temp * prob.mol_mass)
+            Z.append(ziso[:, t])
+    tr.ctx.molext_states(np.array(T), np.array(D), np.array(Z), prob.ethresh, permol=1)
+    nsamp = int(tr.ctx.sample_counts(len(T)).sum())
+    tr.free_memory()
+    return {"value": nsamp / dt / 1e9, "unit": "G line-samples/s", "cores": 1, "kind": "reference",
+            "line_states_per_s": nlines * dstates / dt,
+            "sample": f"the unmodified reference binary, one process, --justOpacity on a {nlines}-line subsample (scale 1e-3 of C3's "
+                      f"list), 10 layers: {walls[2]:.1f} s with 2 grid temperatures, {walls[6]:.1f} s with 6; the difference is {dstates} "
+                      f"(layer, T) states = {nlines * dstates:.2e} line-states in {dt:.1f} s; the full C3 grid (1e8 lines x 2600 states) "
+                      f"extrapolates to {1e8 * 2600 / (nlines * dstates / dt) / 3600:.0f} core-hours (linear in lines x states, labelled)"}
 
 
 def c4_problem(nwn=1_000_000, nlayers=100):
@@ -390,7 +537,7 @@ def run_c4(bench, args):
     # algorithmic bytes of one step: interpolation (2 planes per molecule in, e out), tau (e and e_cs in,
     # t out), intensity (t in once per angle, one intensity plane out per angle), CIA (e_cs out)
     ab = prob.nrad * prob.nwn * 8.0 * ((2 * nm + 1) + 3 + 1 + nang) + prob.nwn * 8.0 * (nang + 1)
-    print(json.dumps({
+    line = {
         "metric": "spectra/s", "value": args.steps / (dev_ms * 1e-3), "unit": "spectra/s", "n_gpus": 1,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -406,7 +553,10 @@ def run_c4(bench, args):
                      "achieved": ab / (dev_ms / args.steps * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                      "frac": ab / (dev_ms / args.steps * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": src,
                      "algorithmic_bytes": ab},
-        "clocks": clocks}))
+        "clocks": clocks}
+    if not args.no_cpu_baseline:
+        line["cpu_baseline"] = c4_cpu_baseline(bench, args)
+    print(json.dumps(line), flush=True)
     return 0
 
 
@@ -476,7 +626,7 @@ def run_c3(bench, args):
         hbm_peak, src = bench.measured_peaks()
         nlines = len(prob.wl)
         step_s = dev_ms / args.steps * 1e-3
-        print(json.dumps({
+        line = {
             "metric": "line-sum Glines.samples/s", "value": nsamp / step_s / 1e9, "unit": "G line-samples/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
             "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
@@ -495,7 +645,24 @@ def run_c3(bench, args):
                     "note": "the step already ends with the grid rows in host memory (D2H inside the timed region)"},
             "gpu_launches": int(launches * world),
             "kernel_ms": {k: float(np.mean(v)) for k, v in kms.items()},
-            "clocks": clocks}))
+            "clocks": clocks}
+        mb = tr.ctx.microbench()
+        c_exp = mb["dfma_tflops"] * 1e12 / (mb["dexp_gops"] * 1e9)
+        flop = 2.0 * nsamp + (12.0 + 2.0 * c_exp) * nlines * ns            # SURVEY 8d, whole line sum of a step
+        ach = flop / (float(np.mean(kms["molext"])) * 1e-3) / 1e12
+        line["roofline"] = {"kernel": "line sum, all kernels (k_kmax + k_linesum_fused + k_strength + k_accumulate)", "bound": "fp64",
+                            "achieved": ach, "peak": mb["dfma_tflops"], "unit": "TFLOP/s", "frac": ach / mb["dfma_tflops"],
+                            "traffic": None, "peak_source": "tb_microbench DFMA, measured in this run", "ms": float(np.mean(kms["molext"])),
+                            "algorithmic_flop": flop, "c_exp_flop": c_exp}
+        line["microbench"] = mb
+        if world == 1 and not args.no_cpu_baseline:
+            def factory(pr):
+                t2 = sharding.ShardedTransit(local_rank, rank, world)
+                t2.ctx.set_fused(2)
+                t2.transit_init(pr)
+                return t2
+            line["cpu_baseline"] = c3_cpu_baseline(bench, args, factory)
+        print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
