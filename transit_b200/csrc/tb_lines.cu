@@ -486,7 +486,7 @@ __device__ __forceinline__ void atomicMaxPosDouble(double *addr, double v) {
 #define KMAX_ROWS 16   // output rows reduced in shared memory (more rows: straight to global)
 #define KMAX_ISO 64    // isotopes whose skip thresholds are tabulated per block in shared memory
 #define KMAX_LPT 8     // lines per thread
-template <int SB>
+template <int SB, int LPT = KMAX_LPT>
 __global__ void k_kmax(int64_t l0, int64_t l1, int ns, int niso, const double *__restrict__ q_g,
                        const double *__restrict__ q_a, const double *__restrict__ q_w,
                        const int16_t *__restrict__ q_iso, const double *__restrict__ rtemp,
@@ -520,8 +520,8 @@ __global__ void k_kmax(int64_t l0, int64_t l1, int ns, int niso, const double *_
     }
   }
 #pragma unroll 1
-  for (int rep = 0; rep < KMAX_LPT; rep++) {
-    const int64_t l = l0 + ((int64_t)blockIdx.x * KMAX_LPT + rep) * blockDim.x + threadIdx.x;
+  for (int rep = 0; rep < LPT; rep++) {
+    const int64_t l = l0 + ((int64_t)blockIdx.x * LPT + rep) * blockDim.x + threadIdx.x;
     if (l >= l1) break;
     const int iso = q_iso[l];
     const double g = q_g[l];
@@ -1595,7 +1595,8 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       const int64_t Mq = c->Mq, seed = Mq < 16384 ? Mq : 16384;
       tb_timer_begin(c, "kmax");
       if (seed > 0)
-        k_kmax<SB><<<dim3(nblk(seed, Tn * KMAX_LPT), (cs + SB - 1) / SB), Tn, 0, st>>>(
+        // (one line per thread: the seed is 16 384 lines, eight per thread would leave it 200 blocks for 148 SMs)
+        k_kmax<SB, 1><<<dim3(nblk(seed, Tn), (cs + SB - 1) / SB), Tn, 0, st>>>(
             0, seed, cs, niso, c->q_g.p, c->q_a.p, c->q_w.p, c->q_iso.p, c->s_rtemp.p, c->s_Z.p, c->d_iso_mass.p,
             c->d_iso_row.p, permol, nrows, c->s_kmax.p);
       // the bulk is split over the ranks of a sharded run (every rank ran the seed, so every
