@@ -66,6 +66,7 @@ typedef struct {
   th_db *db;
   double *isomass, *isoratio, *isoZ;   /* isoZ[iso][nT of its db] flattened via isoZoff */
   int64_t *isoZoff;
+  double *isoZ2;                  /* second derivatives of each isoZ spline, same layout; filled on first use */
   int *isodb, *isoimol;
   double tli_tmin, tli_tmax;
   int64_t nlines;

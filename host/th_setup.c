@@ -67,6 +67,30 @@ static void splinterp(long n, const double *x, const double *y, long nout, const
   free(z);
 }
 
+/* The same evaluation with the second derivatives z computed once per table, and the interval
+ * found by walking from the previous point's interval.  binsearchapprox + the step back of
+ * th_splinterp_pt select the largest idx with x[idx] <= xout, kept in [0, n-2]; the walk below
+ * lands on that same idx, so every output is the same double. */
+static void splinterp_cached(long n, const double *x, const double *y, const double *z, long nout,
+                             const double *xout, double *yout) {
+  if (n < 2) { for (long i = 0; i < nout; i++) yout[i] = y[0]; return; }
+  long idx = 0;
+  for (long i = 0; i < nout; i++) {
+    const double xo = xout[i];
+    while (idx < n - 2 && x[idx + 1] <= xo) idx++;
+    while (idx > 0 && x[idx] > xo) idx--;
+    const double h = x[idx + 1] - x[idx], dy = y[idx + 1] - y[idx];
+    if (x[idx] == xo) { yout[i] = y[idx]; continue; }
+    if (h > 0) {
+      const double dx = xo - x[idx];
+      const double a = (z[idx + 1] - z[idx]) / (6 * h), b = 0.5 * z[idx];
+      const double c = dy / h - h / 6 * (z[idx + 1] + 2 * z[idx]);
+      yout[i] = y[idx] + dx * (c + dx * (b + dx * a));
+    } else
+      yout[i] = 0;
+  }
+}
+
 /* ---- wavenumber sampling */
 int th_make_wn(th_state *s) {
   const th_hints *h = &s->h;
@@ -169,11 +193,21 @@ int th_make_rad(th_state *s) {
     if (s->t[i] < s->tli_tmin) th_die("The layer %d in the atmospheric model has a lower temperature (%.1f K) than the lowest allowed TLI temperature (%.1f K).\n", i, s->t[i], s->tli_tmin);
     if (s->t[i] > s->tli_tmax) th_die("The layer %d in the atmospheric model has a higher temperature (%.1f K) than the highest allowed TLI temperature (%.1f K).\n", i, s->t[i], s->tli_tmax);
   }
-  free(s->Zlayer);
-  s->Zlayer = (double *)malloc((size_t)(niso ? niso : 1) * n * sizeof(double));
+  if (!s->Zlayer) s->Zlayer = (double *)malloc((size_t)(niso ? niso : 1) * n * sizeof(double));
+  if (!s->isoZ2 && niso) {        /* run_transit comes here once per spectrum: the tridiagonal solves are done once */
+    int64_t zn = 0;
+    for (int i = 0; i < niso; i++)
+      if (s->isoZoff[i] + s->db[s->isodb[i]].nT > zn) zn = s->isoZoff[i] + s->db[s->isodb[i]].nT;
+    s->isoZ2 = (double *)calloc((size_t)zn, sizeof(double));
+    for (int i = 0; i < niso; i++) {
+      const th_db *db = s->db + s->isodb[i];
+      if (db->nT >= 2) th_spline_init(s->isoZ2 + s->isoZoff[i], db->T, s->isoZ + s->isoZoff[i], db->nT);
+    }
+  }
   for (int i = 0; i < niso; i++) {
     const th_db *db = s->db + s->isodb[i];
-    splinterp(db->nT, db->T, s->isoZ + s->isoZoff[i], n, s->t, s->Zlayer + (size_t)i * n);   /* makesample.c:534-544 */
+    splinterp_cached(db->nT, db->T, s->isoZ + s->isoZoff[i], s->isoZ2 + s->isoZoff[i], n, s->t,
+                     s->Zlayer + (size_t)i * n);                                             /* makesample.c:534-544 */
   }
   if (TH_DEV(tb_set_atmosphere(s->ctx, n, s->rad, s->rad_fct, s->p, s->p_fct, s->t, s->t_fct, s->d, niso ? s->Zlayer : NULL)))
     th_die("%s\n", tb_last_error());
