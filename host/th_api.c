@@ -21,7 +21,8 @@ int th_dry = 0;
 tb_ctx *th_context(void) { return S.ctx; }
 /* sizes of the problem behind the library face: layers, molecules, isotopes, wavenumbers, lines, angles */
 void th_sizes(int64_t *out) {
-  out[0] = S.nlayer; out[1] = S.nmol; out[2] = S.niso; out[3] = S.nwn; out[4] = S.nlines; out[5] = S.nang;
+  out[0] = S.resampled ? S.other.n : S.nlayer;    /* layers of the atmosphere file: what run_transit's input holds */
+  out[1] = S.nmol; out[2] = S.niso; out[3] = S.nwn; out[4] = S.nlines; out[5] = S.nang;
 }
 
 /* timecheck (transitstd.c:359-374): the "Check point" lines users grep, printed at verbosity >= 4
@@ -122,7 +123,7 @@ void transit_init(int argc, char **argv) {
   if (h->modlevel != 1 && h->modlevel != -1)
     th_die("slantpath:: modulationperwn:: Level %i of detail has not been implemented to compute modulation.\n", h->modlevel);
   apply_cloud_scattering();
-  if (S.have_grid_file && h->p0 != 0 && h->r0 != 0 && h->gsurf != 0)      /* what run_transit_batch needs */
+  if (S.have_grid_file && !S.resampled && h->p0 != 0 && h->r0 != 0 && h->gsurf != 0)      /* what run_transit_batch needs */
     CK(tb_set_atmosphere_model(S.ctx, S.nlayer, S.p, S.p_fct, S.t_fct, S.rad_fct, S.bymass, h->p0, h->r0, h->gsurf));
   S.out = (double *)calloc(S.nwn, sizeof(double));
   S.initialised = 1;
@@ -166,13 +167,15 @@ static void write_outsample(void) {
                "Number of elements: %lli\n", 0.0, 0.0, 0.0, 0.0, 0, 0LL);
   fprintf(out, hdr, "Radius");
   fprintf(out, "Factor to cgs units: %g\nInitial value: %g\nFinal value: %g\nSpacing: %g\n"
-               "Number of elements: %lli\nValues: ", S.rad_fct, S.rad[0], S.rad[n - 1], 0.0, (long long)n);
+               "Number of elements: %lli\nValues: ", S.rad_fct, S.rad[0], S.resampled ? S.samp_f : S.rad[n - 1],
+          S.resampled ? S.h.rad_d : 0.0, (long long)n);
   for (int i = 0; i < n; i++) fprintf(out, " %12.8g", S.rad[i]);
   fprintf(out, "\n");
   fprintf(out, hdr, "Impact parameter");
   fprintf(out, "Factor to cgs units: %g\nInitial value: %g\nFinal value: %g\nSpacing: %g\nOversample: %i\n"
-               "Number of elements: %lli\nValues: ", S.rad_fct, S.rad[n - 1], S.rad[0], 0.0, 0, (long long)n);
-  for (int i = 0; i < n; i++) fprintf(out, " %12.8g", S.rad[n - 1 - i]);
+               "Number of elements: %lli\nValues: ", S.rad_fct, S.rad[n - 1], S.rad[0], S.resampled ? -S.h.rad_d : 0.0,
+          S.resampled ? 1 : 0, (long long)(S.resampled ? S.nip : n));
+  for (int i = 0; i < (S.resampled ? S.nip : n); i++) fprintf(out, " %12.8g", S.resampled ? S.ips[i] : S.rad[n - 1 - i]);
   fprintf(out, "\n");
   if (out != stdout) fclose(out);
 }
@@ -208,7 +211,7 @@ static void write_saveext(void) {
 
 /* printtoomuch (tau.c:611-640) */
 static void write_toomuch(void) {
-  const int n = S.nlayer;                       /* rays = layers (raddelt -1) */
+  const int n = S.resampled && !S.eclipse ? S.nip : S.nlayer;   /* rays: the layers, or the resampled impact parameters */
   double *t = (double *)malloc((size_t)S.nwn * n * sizeof(double));
   int64_t *last = (int64_t *)malloc(S.nwn * sizeof(int64_t));
   if (!t || !last) th_die("Not enough host memory for the toomuch file.\n");
@@ -224,7 +227,7 @@ static void write_toomuch(void) {
       const double wn = S.wn_i + (double)w * S.wn_d;
       /* the rays are the impact parameters, top first: ips.v[i] = rads.v[n-1-i] (makesample.c:564-573) */
       fprintf(out, "%12.7f   %.5e     %12.4f     %04ld\n", 1.0 / wn * 1.0 * 1e4, t[(size_t)w * n + last[w]],
-              S.rad[n - 1 - last[w]] * S.rad_fct / 1e5, (long)last[w]);
+              (S.resampled ? S.ips[last[w]] : S.rad[n - 1 - last[w]]) * S.rad_fct / 1e5, (long)last[w]);
     }
     if (out != stdout) fclose(out);
   }
@@ -312,6 +315,7 @@ void do_transit(double *transit_out) {
 
 /* reloadatm (readatm.c:722-784): in = [T(nlayers) | q_mol0(nlayers) | q_mol1(nlayers) | ...] */
 void run_transit(double *re_input, int transint, double *transit_out, int transit_out_size) {
+  th_file_layers(&S);                              /* raddelt != -1: reloadatm updates the atmosphere FILE's layers */
   const int n = S.nlayer;
   (void)transint; (void)transit_out_size;
   for (int i = 0; i < n; i++) S.t[i] = re_input[i];
@@ -329,9 +333,9 @@ void run_transit(double *re_input, int transint, double *transit_out, int transi
  * densities and hydrostatic radii included, tb_run_transit_batch); any other configuration is a loop of
  * run_transit.  An extension of the reference's interface (it has no batched call), same input layout. */
 void run_transit_batch(double *re_input, int natm, double *transit_out) {
-  const int nin = S.nlayer * (1 + S.nmol);
+  const int nin = (S.resampled ? S.other.n : S.nlayer) * (1 + S.nmol);
   if (!S.initialised) { printf("Transit init not run, please initialize transit.\n"); return; }
-  if (S.have_grid_file && !S.eclipse && S.h.modlevel == 1 && S.h.p0 != 0 && S.h.r0 != 0 && S.h.gsurf != 0 && th_world == 1) {
+  if (S.have_grid_file && !S.eclipse && !S.resampled && S.h.modlevel == 1 && S.h.p0 != 0 && S.h.r0 != 0 && S.h.gsurf != 0 && th_world == 1) {
     CK(tb_run_transit_batch(S.ctx, natm, re_input, S.h.toomuch, S.h.starrad * TH_SUNRADIUS, S.h.transparent, transit_out));
     return;
   }

@@ -13,7 +13,7 @@
 #include "th_internal.h"
 
 enum { O_IGN = 1, O_VERB, O_QUIET, O_CFG, O_ATM, O_LINEDB, O_OUTTOOMUCH, O_OUTSAMPLE, O_OUTSPEC, O_OUTINTENS,
-       O_MOLFILE, O_RADDELT, O_ALLOWQ, O_RPRESS, O_RRADIUS, O_GSURF, O_QMOL, O_QSCALE, O_WLLOW, O_WLHIGH,
+       O_MOLFILE, O_RADDELT, O_RADLOW, O_RADHIGH, O_RADFCT, O_ALLOWQ, O_RPRESS, O_RRADIUS, O_GSURF, O_QMOL, O_QSCALE, O_WLLOW, O_WLHIGH,
        O_WLFCT, O_WNLOW, O_WNHIGH, O_WNDELT, O_WNOSAMP, O_WNFCT, O_NDOP, O_NLOR, O_DMIN, O_DMAX, O_LMIN,
        O_LMAX, O_NWIDTH, O_ETHRESH, O_CLOUD, O_CLOUDTOP, O_SCATTERING, O_CSFILE, O_OPACITYFILE, O_TLOW,
        O_THIGH, O_TEMPDELT, O_OPABREAK, O_SOLUTION, O_TOOMUCH, O_STARRAD, O_TRANSPARENT, O_RAYGRID,
@@ -29,8 +29,8 @@ static const th_opt table[] = {
   {"outsample", 0, 1, NULL, O_OUTSAMPLE}, {"outspec", 0, 1, "outspectrum", O_OUTSPEC},
   {"outintens", 0, 1, NULL, O_OUTINTENS}, {"molfile", 0, 1, "../inputs/molecules.dat", O_MOLFILE},
   {"savefiles", 0, 1, "no", O_SAVEFILES},
-  {"raddelt", 0, 1, "-1", O_RADDELT}, {"radlow", 0, 1, "0", O_IGN}, {"radhigh", 0, 1, "0", O_IGN},
-  {"radfct", 0, 1, "0", O_IGN},
+  {"raddelt", 0, 1, "-1", O_RADDELT}, {"radlow", 0, 1, "0", O_RADLOW}, {"radhigh", 0, 1, "0", O_RADHIGH},
+  {"radfct", 0, 1, "0", O_RADFCT},
   {"allowq", 0, 1, "0.00001", O_ALLOWQ}, {"refpress", 0, 1, NULL, O_RPRESS}, {"refradius", 0, 1, NULL, O_RRADIUS},
   {"gsurf", 0, 1, NULL, O_GSURF}, {"qmol", 0, 1, NULL, O_QMOL}, {"qscale", 0, 1, NULL, O_QSCALE},
   {"wllow", 0, 1, NULL, O_WLLOW}, {"wlhigh", 0, 1, NULL, O_WLHIGH}, {"wlfct", 0, 1, "1e-4", O_WLFCT},
@@ -92,6 +92,9 @@ static void apply(th_hints *h, const th_opt *o, const char *v) {
     case O_OUTINTENS: setstr(&h->f_outintens, v); break;
     case O_MOLFILE: setstr(&h->f_molfile, v); break;
     case O_RADDELT: h->rad_d = atof(v); break;
+    case O_RADLOW: h->rad_i = atof(v); break;          /* argum.c:499-509 */
+    case O_RADHIGH: h->rad_f = atof(v); break;
+    case O_RADFCT: h->rad_fct = atof(v); break;
     case O_ALLOWQ: h->allowq = atof(v); break;
     case O_RPRESS: h->p0 = atof(v); break;
     case O_RRADIUS: h->r0 = atof(v); break;

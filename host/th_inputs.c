@@ -126,10 +126,43 @@ int th_read_atmosphere(th_state *s) {
   s->molpol = (double *)calloc(s->nmol, sizeof(double));
   read_moldata(s);
 
+  /* qmol / qscale (argum.c:881-890, readatm.c:394-406): log10 scale factors for the named species, applied to every
+   * data row as it is read; H2 and He are then renormalised at their own ratio so that the row adds up again */
+  const int nmol = s->nmol;
+  int nq = 0, qidx[64];
+  double qsc[64];
+  if (s->h.qscale) {
+    const char *lp = s->h.qscale;
+    while (*lp == ' ') lp++;
+    while (*lp && nq < 64) {
+      qsc[nq++] = atof(lp);
+      while (*lp && *lp != ' ') lp++;
+      while (*lp == ' ') lp++;
+    }
+    int nn = 0;
+    lp = s->h.qmol ? s->h.qmol : "";
+    while (*lp == ' ') lp++;
+    while (*lp) {
+      char nm[TH_MAXNAME];
+      int k = 0;
+      while (*lp && *lp != ' ') { if (k < TH_MAXNAME - 1) nm[k++] = *lp; lp++; }
+      nm[k] = 0;
+      while (*lp == ' ') lp++;
+      if (nn < 64) {
+        qidx[nn] = -1;
+        for (int j = 0; j < nmol; j++) if (strcmp(nm, s->molname[j]) == 0) { qidx[nn] = j; break; }
+      }
+      nn++;
+    }
+    if (nn != nq) th_die("qscale (%d) and qmol (%d) should have the same number of elements.\n", nq, nn);
+  }
+  int iH2 = -1, iHe = -1;                            /* valueinarray(mol->ID, 105 | 2), readatm.c:465-466 */
+  for (int j = 0; j < nmol; j++) { if (s->molID[j] == 105 && iH2 < 0) iH2 = j; if (s->molID[j] == 2 && iHe < 0) iHe = j; }
+  if (nq > 0 && (iH2 < 0 || iHe < 0)) th_die("qscale needs H2 and He in the atmosphere file (readatm.c:536-541).\n");
+
   /* data rows (readatm.c:498-534) */
   fseek(fp, datapos, SEEK_SET);
   int cap = 64, n = 0;
-  const int nmol = s->nmol;
   double *rad = (double *)malloc(cap * sizeof(double)), *p = (double *)malloc(cap * sizeof(double));
   double *t = (double *)malloc(cap * sizeof(double)), *q = (double *)malloc((size_t)cap * nmol * sizeof(double));
   while (fgets(line, sizeof line, fp)) {
@@ -152,7 +185,16 @@ int th_read_atmosphere(th_state *s) {
       q[(size_t)n * nmol + i] = strtod(lp, &e);
       if (e == lp) th_die("The line %s of file %s contains %d abundance values, when there were %d expected.\n",
                           line, s->h.f_atm, i, nmol);
+      for (int j = 0; j < nq; j++)
+        if (qidx[j] == i) { q[(size_t)n * nmol + i] *= pow(10.0, qsc[j]); break; }     /* readatm.c:519-522 */
       if (q[(size_t)n * nmol + i] < 0) th_die("A negative abundance was found in atmosphere file %s.\n", s->h.f_atm);
+    }
+    if (nq > 0) {                                      /* readatm.c:536-541 */
+      double sumq2 = 0;
+      for (int i = 0; i < nmol; i++) if (i != iH2 && i != iHe) sumq2 += q[(size_t)n * nmol + i];
+      const double ratio = q[(size_t)n * nmol + iH2] / q[(size_t)n * nmol + iHe];
+      q[(size_t)n * nmol + iHe] = (1 - sumq2) / (1.0 + ratio);
+      q[(size_t)n * nmol + iH2] = ratio * (1 - sumq2) / (1.0 + ratio);
     }
     n++;
   }

@@ -25,6 +25,7 @@ typedef struct {
   char *solname;
   char *raygrid, *qmol, *qscale;
   double rad_d;                   /* raddelt (-1: keep the atmosphere file's layers)          */
+  double rad_i, rad_f, rad_fct;   /* radlow, radhigh, radfct (0: take the atmosphere file's)  */
   double wl_i, wl_f, wl_fct;      /* wllow, wlhigh, wlfct                                     */
   double wn_i, wn_f, wn_d, wn_fct;
   int wn_o;
@@ -46,6 +47,11 @@ typedef struct {          /* one TLI database (readlineinfo.c:87-244) */
   int nT, niso, first;    /* first: index of its first isotope in the global list */
   double *T;
 } th_db;
+
+typedef struct {        /* one set of layers: the atmosphere file's, or the resampled ones (raddelt != -1) */
+  int n, cap;
+  double *rad, *p, *t, *mm, *q, *d;
+} th_layers;
 
 typedef struct {
   th_hints h;
@@ -76,6 +82,14 @@ typedef struct {
   int ncs;
   /* sampled state handed to the device (makeradsample) */
   double *Zlayer;                 /* [niso][nlayer] */
+  int64_t zcap;
+  /* raddelt != -1 (makeradsample's makesample branch, makesample.c:484-486): nlayer/rad/p/t/mm/q/d above hold the
+   * RESAMPLED atmosphere once th_make_rad has run, and `other` keeps the file's own layers (run_transit's input) */
+  int resampled;
+  th_layers other;
+  double samp_f;                  /* the accepted final radius (what outsample prints; the last sample may fall short) */
+  int nip;                        /* impact parameters of makeipsample's makesample branch, top first */
+  double *ips;
   /* geometry */
   int eclipse, nang;
   double angles[16];
@@ -112,6 +126,7 @@ int  th_make_wn(th_state *s);
 int  th_densities(th_state *s);
 int  th_radpress(th_state *s);
 int  th_make_rad(th_state *s);
+void th_file_layers(th_state *s);   /* raddelt != -1: make the atmosphere file's layers current again (reloadatm works on them) */
 int  th_opacity(th_state *s);
 /* th_api.c: the reference's library interface */
 void transit_init(int argc, char **argv);

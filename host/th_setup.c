@@ -183,17 +183,85 @@ int th_radpress(th_state *s) {
   return 0;
 }
 
-/* ---- makeradsample with raddelt = -1: the atmosphere file's own layers; the partition
- * function of every isotope is splined in temperature at the layer temperatures, and the
- * sampled atmosphere goes to the device. */
+/* ---- makeradsample (makesample.c:408-549).  raddelt = -1 keeps the atmosphere file's own layers; a positive
+ * raddelt builds an equidistant radius sample between radlow and radhigh (the file's first / last radius where
+ * those are 0) by makesample (makesample.c:145-300) and carries temperature, pressure, mean molecular mass and
+ * every species' density and abundance over by natural cubic splines in radius (makesample.c:508-530).  In both
+ * cases the partition function of every isotope is splined in temperature at the layer temperatures and the
+ * sampled atmosphere goes to the device; the resampled case also makes the impact-parameter sample of
+ * makeipsample's second branch (makesample.c:577-596): from the top radius downwards in steps of raddelt. */
+void th_file_layers(th_state *s) {
+  if (!s->resampled) return;
+  /* current = resampled (capacity other.cap), other = file */
+  th_layers samp = {s->nlayer, s->other.cap, s->rad, s->p, s->t, s->mm, s->q, s->d};
+  const th_layers f = s->other;
+  s->nlayer = f.n; s->rad = f.rad; s->p = f.p; s->t = f.t; s->mm = f.mm; s->q = f.q; s->d = f.d;
+  s->other = samp;
+  s->resampled = 0;
+}
+
+static void resample_layers(th_state *s) {
+  const th_hints *h = &s->h;
+  const int fn = s->nlayer, nmol = s->nmol;
+  if (h->rad_d <= 0)
+    th_die("raddelt %g: the radius spacing has to be positive (or -1 to keep the atmosphere file's layers); "
+           "makesample.c:229-233, :585-596.\n", h->rad_d);
+  /* makesample(rad, hint = {radlow, radhigh, raddelt, radfct}, ref = atmosphere radii, TRH_RAD) */
+  if (h->rad_fct > 0) s->rad_fct = h->rad_fct;             /* makesample.c:157-160 (values are NOT converted there either) */
+  const double ri = h->rad_i <= 0 ? s->rad[0] : h->rad_i, rf = h->rad_f <= 0 ? s->rad[fn - 1] : h->rad_f;
+  const double dl = h->rad_d;
+  if (rf <= ri)
+    th_die("Initial accepted sampling value (%g) is greater or equal than final accepted sample value (%g). "
+           "radius was being hinted.\n", ri, rf);
+  long n = (long)(((1.0 + 1e-8) * rf - ri) / dl + 1);      /* makesample.c:248 */
+  if (n < 0) n = -n;
+  if (n < 1 || n > 100000) th_die("raddelt %g gives %ld radius samples.\n", dl, n);
+  th_layers *o = &s->other;                                 /* the spare set of buffers */
+  if (o->cap < n) {
+    o->cap = (int)n;
+    o->rad = (double *)realloc(o->rad, n * sizeof(double)); o->p = (double *)realloc(o->p, n * sizeof(double));
+    o->t = (double *)realloc(o->t, n * sizeof(double)); o->mm = (double *)realloc(o->mm, n * sizeof(double));
+    o->q = (double *)realloc(o->q, (size_t)n * nmol * sizeof(double));
+    o->d = (double *)realloc(o->d, (size_t)n * nmol * sizeof(double));
+  }
+  o->n = (int)n;
+  o->rad[0] = ri;
+  for (long k = 1; k < n; k++) o->rad[k] = ri + k * dl;     /* makesample.c:273-279, oversampling 1 */
+  splinterp(fn, s->rad, s->t, n, o->rad, o->t);             /* makesample.c:508-510 */
+  splinterp(fn, s->rad, s->p, n, o->rad, o->p);
+  splinterp(fn, s->rad, s->mm, n, o->rad, o->mm);
+  for (int i = 0; i < nmol; i++) {                          /* makesample.c:527-530 */
+    splinterp(fn, s->rad, s->d + (size_t)i * fn, n, o->rad, o->d + (size_t)i * n);
+    splinterp(fn, s->rad, s->q + (size_t)i * fn, n, o->rad, o->q + (size_t)i * n);
+  }
+  s->samp_f = rf;
+  /* current <- resampled, other <- file */
+  th_layers file = {fn, fn, s->rad, s->p, s->t, s->mm, s->q, s->d};
+  const th_layers samp = *o;
+  s->nlayer = samp.n; s->rad = samp.rad; s->p = samp.p; s->t = samp.t; s->mm = samp.mm; s->q = samp.q; s->d = samp.d;
+  file.cap = samp.cap;                                      /* `other.cap` always describes the RESAMPLED buffers */
+  s->other = file;
+  s->resampled = 1;
+  /* makeipsample: makesample(ips, hint = {0, -0, 0, 0}, ref = {d = -raddelt, i = top radius, f = bottom radius, o = 1}) */
+  const double ii = s->rad[n - 1], ff = s->rad[0], dd = -dl;
+  long nip = (long)(((1.0 - 1e-8) * ff - ii) / dd + 1);
+  if (nip < 0) nip = -nip;
+  s->ips = (double *)realloc(s->ips, (nip > 0 ? nip : 1) * sizeof(double));
+  s->nip = (int)nip;
+  for (long k = 0; k < nip; k++) s->ips[k] = k ? ii + k * dd : ii;
+}
+
 int th_make_rad(th_state *s) {
-  if (s->h.rad_d != -1) th_die("raddelt %g: only the atmosphere file's own layers (raddelt -1, the default) are supported.\n", s->h.rad_d);
+  if (s->h.rad_d != -1) resample_layers(s);
   const int n = s->nlayer, niso = s->niso;
   for (int i = 0; i < n; i++) {
     if (s->t[i] < s->tli_tmin) th_die("The layer %d in the atmospheric model has a lower temperature (%.1f K) than the lowest allowed TLI temperature (%.1f K).\n", i, s->t[i], s->tli_tmin);
     if (s->t[i] > s->tli_tmax) th_die("The layer %d in the atmospheric model has a higher temperature (%.1f K) than the highest allowed TLI temperature (%.1f K).\n", i, s->t[i], s->tli_tmax);
   }
-  if (!s->Zlayer) s->Zlayer = (double *)malloc((size_t)(niso ? niso : 1) * n * sizeof(double));
+  if (s->zcap < (int64_t)(niso ? niso : 1) * n) {
+    s->zcap = (int64_t)(niso ? niso : 1) * n;
+    s->Zlayer = (double *)realloc(s->Zlayer, (size_t)s->zcap * sizeof(double));
+  }
   if (!s->isoZ2 && niso) {        /* run_transit comes here once per spectrum: the tridiagonal solves are done once */
     int64_t zn = 0;
     for (int i = 0; i < niso; i++)
@@ -210,6 +278,9 @@ int th_make_rad(th_state *s) {
                      s->Zlayer + (size_t)i * n);                                             /* makesample.c:534-544 */
   }
   if (TH_DEV(tb_set_atmosphere(s->ctx, n, s->rad, s->rad_fct, s->p, s->p_fct, s->t, s->t_fct, s->d, niso ? s->Zlayer : NULL)))
+    th_die("%s\n", tb_last_error());
+  /* transit geometry integrates along the impact-parameter sample; eclipse along the reversed radii (tau.c:92-104) */
+  if (TH_DEV(tb_set_rays(s->ctx, s->resampled && !s->eclipse ? s->ips : NULL, s->resampled && !s->eclipse ? s->nip : 0, s->rad_fct)))
     th_die("%s\n", tb_last_error());
   return 0;
 }

@@ -90,6 +90,9 @@ int  tb_set_fused(tb_ctx *c, int on);
  * carried Doppler index (extinction.c:480-483; found by a bisection + backward scan instead of the list walk) are
  * fused as well (default 0: only states where every line refreshes its index) */
 int  tb_set_fused_reach(tb_ctx *c, int rmax, int carried);
+/* two-kernel path: tiles whose reach is at most r coarse bins (default 2) are summed one thread per bin, the
+ * others by the 16-warp window walk of k_accumulate (tuning knob; any value gives the same sums to rounding) */
+int  tb_set_narrow_reach(tb_ctx *c, int r);
 int  tb_set_trace(tb_ctx *c, int on);
 int  tb_get_fused_stats(tb_ctx *c, int64_t *fused_states, int64_t *fused_samples);
 /* ilor[niso] of state `s` of the last batch (extinction.c:394); with the trace's idop it names the Voigt cell */
@@ -126,6 +129,9 @@ int  tb_set_cloud(tb_ctx *c, int flag, double cloudext, double cloudtop, double 
  * rays h[nh]*hfct (impact parameters, top first; NULL = reversed radii as makeipsample
  * with raddelt=-1, makesample.c:564-573).                                             */
 int  tb_tau(tb_ctx *c, int geometry, double toomuch, const double *h, int nh, double hfct);
+/* the rays tb_spectrum uses (makeipsample, makesample.c:558-604): h[nh]*hfct, top first; NULL or nh = 0 goes back
+ * to the reversed radii.  A resampled radius grid (raddelt != -1) brings its own impact-parameter sample.   */
+int  tb_set_rays(tb_ctx *c, const double *h, int nh, double hfct);
 /* eclipse geometry: 1 (default) = the O(layers)-per-wavenumber streaming kernel (every ray's Simpson pairs end
  * at the top layer, so ray ri adds one pair to the sum of the rays above it); 0 = the general kernel that
  * integrates every ray on its own.  Same terms, pairs associated top down instead of bottom up.            */

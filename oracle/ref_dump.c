@@ -332,7 +332,7 @@ int main(int argc, char **argv){
 
   if(rerun){
     FILE *fi = fopen(rerun, "rb");
-    long nin = transit.rads.n * (1 + transit.ds.mol->nmol), nwn = transit.wns.n, nrr = 1, k;
+    long nin = transit.ds.at->rads.n * (1 + transit.ds.mol->nmol), nwn = transit.wns.n, nrr = 1, k;   /* reloadatm reads the atmosphere FILE's layers */
     if(fi){ fseek(fi, 0, SEEK_END); nrr = ftell(fi) / (8*nin); fseek(fi, 0, SEEK_SET); }
     if(nrr < 1) nrr = 1;
     double *in = malloc(nrr*nin*sizeof(double)), *o = malloc(nrr*nwn*sizeof(double));

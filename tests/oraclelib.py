@@ -292,14 +292,14 @@ def contrib(prob, sc_flag=0, sc_logext=0.0, cl_flag=0, cl_ext=0.0, cl_top=0.0, c
     return cb
 
 
-def tau(prob, e, e_cs, cb=None, lazy=True, rad=None, toomuch=None):
+def tau(prob, e, e_cs, cb=None, lazy=True, rad=None, toomuch=None, h=None):
     L = lib()
     cb = cb or contrib(prob)
     toomuch = prob.toomuch if toomuch is None else toomuch
     rad = c64(prob.rad if rad is None else rad).copy()
     nrad = prob.nrad
-    h = c64(rad[::-1])                       # makeipsample raddelt=-1 / tau.c:92-98
-    nh = nrad
+    h = c64(rad[::-1]) if h is None else c64(h)   # makeipsample raddelt=-1 / tau.c:92-98, or an explicit sample
+    nh = len(h)
     t = np.zeros((prob.nwn, nh)); last = np.zeros(prob.nwn, np.int64)
     comp = np.zeros(nrad, np.int16)
     e = c64(e); e_cs = c64(e_cs)
@@ -309,10 +309,10 @@ def tau(prob, e, e_cs, cb=None, lazy=True, rad=None, toomuch=None):
     return t, last, comp
 
 
-def modulation(prob, t, last, rad=None, transp=None, modlevel=1, toomuch=None):
+def modulation(prob, t, last, rad=None, transp=None, modlevel=1, toomuch=None, ip=None):
     L = lib()
     rad = prob.rad if rad is None else rad
-    ip = c64(rad[::-1])
+    ip = c64(rad[::-1]) if ip is None else c64(ip)
     out = np.zeros(prob.nwn)
     transp = prob.transp if transp is None else transp
     toomuch = prob.toomuch if toomuch is None else toomuch

@@ -268,6 +268,34 @@ def test_scattering_and_cloud_vs_oracle(ctxs):
     c.set_scattering(0, 0.0); c.set_cloud(0)
 
 
+def test_explicit_impact_parameters_vs_oracle(ctxs):
+    """tb_tau(h) / tb_set_rays: an impact-parameter sample that is NOT the reversed radii (makeipsample's second branch,
+    makesample.c:577-596, which a resampled radius grid brings along): more rays than layers, between the layers and
+    on them, top first -- tau, last[] and the modulation against the oracle's totaltau1 / modulation1 on the same rays,
+    and tb_spectrum with tb_set_rays against the staged calls."""
+    d, prob, c = ctxs["tiny_tra"]
+    c.cia_interp(); c.extinction_lbl(prob.ethresh)
+    e, ecs = c.get_extinction(), c.get_cia()
+    r = prob.rad
+    h = np.sort(np.concatenate([r[1:], 0.5 * (r[1:] + r[:-1]), r[:1] + 0.25 * (r[1] - r[0])]))[::-1].copy()
+    for fast in (False, True):
+        c.set_tau_streaming(fast)
+        c.tau(api.GEOM_TRANSIT, prob.toomuch, h, prob.rad_fct)
+        t, last = c.get_tau()
+        t0, last0, _ = O.tau(prob, e, ecs, lazy=False, h=h)
+        assert t.shape == (prob.nwn, len(h)) and np.array_equal(last, last0)
+        assert np.array_equal(t == 0, t0 == 0) and relerr(t[t0 != 0], t0[t0 != 0]) < 1e-9
+        out = c.modulation(prob.starrad, prob.transp)
+        assert relerr(out, O.modulation(prob, t0, last0, ip=h)) < SPEC_RTOL
+    c.set_tau_streaming(True)
+    c.set_rays(h, prob.rad_fct)
+    out2 = c.spectrum(api.GEOM_TRANSIT, prob.toomuch, prob.ethresh, prob.starrad, prob.transp)
+    c.set_rays(None, 1.0)
+    assert np.array_equal(out2, out)
+    out3 = c.spectrum(api.GEOM_TRANSIT, prob.toomuch, prob.ethresh, prob.starrad, prob.transp)
+    assert relerr(out3, d["out"]) < SPEC_RTOL                     # back on the reversed radii
+
+
 # ------------------------------------------------------------------ opacity grid (a6-a8)
 
 def test_tau_weight_form_vs_pairwise_kernel():

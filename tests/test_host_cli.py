@@ -350,3 +350,134 @@ def test_host_run_transit_setup_without_gpu(tmp_path):
     assert np.any(d["rad"] != prob.rad)                      # the radii really are the hydrostatic ones
     assert rel(d["dens"], g["rerun_mol_d"]) < 1e-13
     assert rel(d["Z"], g["rerun_iso_z"]) < 1e-13
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "ref_dump")),
+                    reason="oracle/_ref/ref_dump not built")
+@pytest.mark.parametrize("extra", [["--raddelt", "500"],
+                                   ["--raddelt", "300", "--radlow", "21000", "--radhigh", "26000"],
+                                   ["--qmol", "CH4", "--qscale", "0.5"],
+                                   ["--raddelt", "410", "--qmol", "CH4 H2", "--qscale", "-0.3 0.0"]])
+def test_host_resampled_layers_and_qscale_without_gpu(tmp_path, extra):
+    """makeradsample with raddelt != -1 (makesample.c:145-300,484-530: an equidistant radius sample, temperature,
+    pressure, mean molecular mass, densities and abundances carried over by natural splines, partition functions at
+    the new temperatures) and qmol/qscale (readatm.c:394-406,519-541), through the dry-run tap of the test build
+    against the UNMODIFIED reference's samplers (ref_dump)."""
+    _build()
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    import make_golden as MG
+    prob = workloads.make_problem("C1", scale=0.02, nlayers=20)
+    tmp = str(tmp_path)
+    cfg, _ = workloads.write_reference_inputs(prob, tmp)
+    dump = os.path.join(tmp, "dry.f64")
+    r = subprocess.run([HOST_TAPS, "-c", cfg] + extra, capture_output=True, text=True, cwd=tmp,
+                       env=dict(os.environ, TRANSIT_B200_DRYRUN=dump))
+    assert r.returncode == 0, r.stderr[-800:]
+    d = _read_dry(dump)
+    r = subprocess.run([os.path.join(ROOT, "oracle", "_ref", "ref_dump"), "ref.bin", "--", "-c", cfg] + extra,
+                       cwd=tmp, capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-500:]
+    g = MG.read_container(os.path.join(tmp, "ref.bin"))
+    rel = lambda a, b: float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)))
+    assert d["nlayer"] == len(g["rad_v"])
+    if "--raddelt" in extra:
+        assert d["nlayer"] != prob.nrad                      # really a new radius sample
+    else:
+        assert rel(d["dens"][2], prob.mol_d[2]) > 0.5        # really scaled: CH4 by 10^0.5
+    assert np.array_equal(d["rad"], g["rad_v"])
+    # the reference is a -ffast-math build: its splines come back within a few ulp
+    assert rel(d["t"], g["atm_t"]) < 1e-14 and rel(d["p"], g["atm_p"]) < 1e-14
+    assert rel(d["dens"], g["mol_d"]) < 1e-14 and rel(d["Z"], g["iso_z"]) < 1e-14
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,kw,nnew,more", [
+    ("C2", dict(scale=0.01, nlayers=20, wn_hi=3000.0, wnosamp=120), 26.3, []),
+    ("C1", dict(scale=0.02, nlayers=24, wn_hi=2900.0, wnosamp=120), 17.6, []),
+    ("C2", dict(scale=0.01, nlayers=20, wn_hi=3000.0, wnosamp=120), 15.2, ["--qmol", "H2O CH4", "--qscale", "0.4 -0.7"])])
+def test_resampled_radius_grid_and_qscale_match_reference(tmp_path, name, kw, nnew, more):
+    """raddelt != -1 end to end (transit: the impact-parameter sample of makeipsample's second branch goes to the
+    device through tb_set_rays; eclipse: the reversed resampled radii), with and without qmol/qscale, full
+    precision through transit_init + do_transit of both libraries.
+
+    Tolerances.  Eclipse: 1e-8 like every spectrum.  Transit: makeipsample builds the impact parameters from the top
+    radius DOWN (i + k*(-d)) and the radii from the bottom UP, so a third of them land one ulp below a layer radius
+    (checked on the reference's dump).  totaltau1 then integrates from r0 to that layer over a first interval of
+    ~40 cm in path length beside intervals of ~1e7 cm: the unequal-interval Simpson weights (numerical.c:454-525)
+    cancel to (h1/h0)^2 ~ 1e10 rounding errors, and the reference's own -ffast-math arithmetic is one realisation of
+    that noise (the CPU oracle, fed the reference's exact samples, differs from it by 3e-6 as well).  1e-4 here.
+
+    run_transit on a resampled grid is exercised on OUR side only: the reference's interpcs zeroes
+    wns.n*rads.n doubles of an array whose rows keep the stride of the FIRST call's layer count
+    (crosssec.c:38-40,284), so with a changed layer count it adds the new CIA extinction on top of stale values
+    (or writes past the array when the count grows); the per-atmosphere state it builds (radii, T, densities, Z) is
+    compared on CPU in test_host_resampled_layers_and_qscale_without_gpu / ..._rerun."""
+    _build()
+    prob, cfg = _inputs(tmp_path, name, **kw)
+    with open(cfg, "a") as f:
+        f.write(f"refpress {prob.p[6]:.6e}\nrefradius {prob.rad[6]:.6f}\ngsurf 2200.0\n")
+    delt = (prob.rad[-1] - prob.rad[0]) / nnew
+    argv = [b"transit", b"-c", cfg.encode(), b"--raddelt", f"{delt:.4f}".encode()] + [m.encode() for m in more]
+    # ... and one run_transit on top: reloadatm moves the hydrostatic radii, so the sample is rebuilt (another layer count)
+    np.save(tmp_path / "inp.npy", np.concatenate([prob.t * 1.02 + 5.0] + [prob.mol_q[j] for j in range(prob.nmol)]))
+    outs = []
+    for lib in (HOSTLIB, REFLIB):
+        dst = str(tmp_path) + "/out_" + os.path.basename(lib) + ".npy"
+        rerun = (f"inp = np.load({str(tmp_path / 'inp.npy')!r})\n"
+                 f"for k in (1, 2): L.run_transit(inp.ctypes.data_as(P), len(inp), out[k].ctypes.data_as(P), n)\n") if lib == HOSTLIB else ""
+        code = (f"import ctypes as C, numpy as np, os\n"
+                f"os.dup2(os.open(os.devnull, os.O_WRONLY), 1)\n"
+                f"L = C.CDLL({lib!r}); argv = {argv!r}; arr = (C.c_char_p * len(argv))(*argv)\n"
+                f"L.transit_init(len(argv), arr); L.get_no_samples.restype = C.c_int; n = L.get_no_samples()\n"
+                f"P = C.POINTER(C.c_double); out = np.zeros((3, n)); L.do_transit(out[0].ctypes.data_as(P))\n"
+                + rerun + f"np.save({dst!r}, out)\n")
+        r = subprocess.run(["python", "-c", code], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(np.load(dst))
+    ours, ref = outs
+    assert ours.shape == (3, prob.nwn) and np.all(ref[0] != 0)
+    assert np.max(np.abs(ours[0] - ref[0]) / np.abs(ref[0])) < (1e-8 if prob.eclipse else 1e-4)
+    assert np.all(np.isfinite(ours[1])) and np.all(ours[1] > 0) and np.array_equal(ours[1], ours[2])
+    assert np.max(np.abs(ours[1] - ours[0]) / np.abs(ours[0])) > 1e-4              # the second atmosphere is another one
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "ref_dump")),
+                    reason="oracle/_ref/ref_dump not built")
+def test_host_resampled_layers_rerun_without_gpu(tmp_path):
+    """run_transit with raddelt != -1: reloadatm updates the atmosphere FILE's layers (new T and abundances,
+    hydrostatic radii), makeradsample then rebuilds the equidistant sample from the moved radii -- another layer
+    count than at initialisation -- against the state the UNMODIFIED reference holds after the same call."""
+    _build()
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    import make_golden as MG
+    prob = workloads.make_problem("C2", scale=0.004, nlayers=23, wn_hi=2600.0, wnosamp=60)
+    tmp = str(tmp_path)
+    cfg, _ = workloads.write_reference_inputs(prob, tmp)
+    with open(cfg, "a") as f:
+        f.write(f"refpress {prob.p[6]:.6e}\nrefradius {prob.rad[6]:.6f}\ngsurf 2200.0\n")
+    delt = f"{(prob.rad[-1] - prob.rad[0]) / 26.3:.4f}"
+    inp = np.concatenate([prob.t * 1.02 + 5.0] + [prob.mol_q[j] for j in range(prob.nmol)])
+    inp.astype("<f8").tofile(os.path.join(tmp, "rerun.f64"))
+    np.save(tmp_path / "inp.npy", inp)
+    r = subprocess.run([os.path.join(ROOT, "oracle", "_ref", "ref_dump"), "ref.bin", "--rerun", "rerun.f64", "--",
+                        "-c", cfg, "--raddelt", delt], cwd=tmp, capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-800:]
+    g = MG.read_container(os.path.join(tmp, "ref.bin"))
+    argv = [b"transit", b"-c", cfg.encode(), b"--raddelt", delt.encode()]
+    dump = os.path.join(tmp, "dry.f64")
+    code = (f"import ctypes as C, numpy as np, os\n"
+            f"os.dup2(os.open(os.devnull, os.O_WRONLY), 1)\n"
+            f"L = C.CDLL({HOSTLIB_TAPS!r}); argv = {argv!r}; arr = (C.c_char_p * len(argv))(*argv)\n"
+            f"L.transit_init(len(argv), arr); L.get_no_samples.restype = C.c_int; n = L.get_no_samples()\n"
+            f"out = np.zeros(n); inp = np.load({str(tmp_path / 'inp.npy')!r}); P = C.POINTER(C.c_double)\n"
+            f"L.run_transit(inp.ctypes.data_as(P), len(inp), out.ctypes.data_as(P), n)\n")
+    r = subprocess.run(["python", "-c", code], capture_output=True, text=True,
+                       env=dict(os.environ, TRANSIT_B200_DRYRUN=dump))
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = _read_dry(dump)
+    rel = lambda a, b: float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)))
+    assert d["nlayer"] == len(g["rerun_rad_v"]) and d["nlayer"] != len(g["rad_v"]) and d["nlayer"] != prob.nrad
+    assert rel(d["rad"], g["rerun_rad_v"]) < 1e-13 and rel(d["t"], g["rerun_atm_t"]) < 1e-13
+    assert rel(d["dens"], g["rerun_mol_d"]) < 1e-12 and rel(d["Z"], g["rerun_iso_z"]) < 1e-12

@@ -52,6 +52,8 @@ ABI = {
     "tb_get_state_ilor": (C.c_int, [C.c_void_p, C.c_int, i32p]),
     "tb_set_fused": (C.c_int, [C.c_void_p, C.c_int]),
     "tb_set_fused_reach": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "tb_set_narrow_reach": (C.c_int, [C.c_void_p, C.c_int]),
+    "tb_set_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_double]),
     "tb_set_trace": (C.c_int, [C.c_void_p, C.c_int]),
     "tb_get_fused_stats": (C.c_int, [C.c_void_p, i64p, i64p]),
     "tb_get_line_molIDs": (C.c_int, [C.c_void_p, i32p, i32p]),
@@ -259,6 +261,18 @@ class Context:
         """0: two-kernel path; 1/True: fused where the grid has >= 96 tiles; 2: fused on small grids too."""
         self._ck(self.lib.tb_set_fused(self.h, int(on)), "tb_set_fused")
 
+    def set_rays(self, h, hfct):
+        """Impact parameters tb_spectrum integrates along (None: the reversed radii, makeipsample with raddelt -1)."""
+        self.user_nh = None if h is None else len(h)
+        if h is None:
+            self._ck(self.lib.tb_set_rays(self.h, None, 0, 1.0), "tb_set_rays")
+            return
+        h = np.ascontiguousarray(h, dtype=np.float64)
+        self._ck(self.lib.tb_set_rays(self.h, h.ctypes.data_as(C.c_void_p), len(h), float(hfct)), "tb_set_rays")
+
+    def set_narrow_reach(self, r):
+        self._ck(self.lib.tb_set_narrow_reach(self.h, int(r)), "tb_set_narrow_reach")
+
     def set_fused_reach(self, rmax, carried=False):
         self._ck(self.lib.tb_set_fused_reach(self.h, int(rmax), int(bool(carried))), "tb_set_fused_reach")
 
@@ -355,7 +369,7 @@ class Context:
             self.nang = len(a)
         self._ck(self.lib.tb_spectrum(self.h, geometry, toomuch, ethresh, starrad_cm, int(transparent), _p(a),
                                       0 if a is None else len(a), _p(out)), "tb_spectrum")
-        self.nh = self.nrad
+        self.nh = getattr(self, "user_nh", None) or self.nrad
         return out
 
     # -- taps ---------------------------------------------------------------------------

@@ -234,6 +234,7 @@ struct tb_ctx {
   DevBuf<LineRec> s_rec;      // [state][group]
   DevBuf<int32_t> s_fclass, s_fP, s_lastq2;   // s_lastq2: carried-index source of the fused states (k_lastq_scan)
   int fuse_rmax = 8;
+  int narrow_r = 2;              // NARROW_R of tb_lines.cu
   bool fuse_carried = false;     // fuse states whose lines partly keep a carried Doppler index (k_lastq_scan)   // per batch of 8 states: taken by k_linesum_fused? / widest half-size (fine bins)
   int fuse_enabled = 1;          // 0 off, 1 on where the grid has enough tiles, 2 always (tests)
   bool trace_enabled = false;
@@ -256,6 +257,8 @@ struct tb_ctx {
   int nh = 0, geometry = 0, nang = 0;
   double toomuch = 0;
   std::vector<double> h_h;
+  std::vector<double> user_h;    // tb_set_rays: impact parameters for tb_spectrum (empty: reversed radii)
+  double user_hfct = 1;
   double hfct = 1;
 
   // ---- ray geometry scratch

@@ -883,7 +883,7 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
              const int32_t *__restrict__ reach, const int32_t *__restrict__ reachP,
              const double *__restrict__ pdata, double *__restrict__ out,
              unsigned long long *__restrict__ nsamp, int S, double *__restrict__ part_g,
-             unsigned *__restrict__ tilecnt, const int32_t *__restrict__ fclass) {
+             unsigned *__restrict__ tilecnt, const int32_t *__restrict__ fclass, int narrow_r) {
   const int s = blockIdx.y;
   if (fclass[s >> 3]) return;                    // summed by k_linesum_fused
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -899,7 +899,7 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
   const int4 *rs = reinterpret_cast<const int4 *>(rec_in + (size_t)s * G);
   const int32_t *fbs = fbpid + (size_t)s * niso;
   unsigned long long cnt = 0;
-  if (WIDE != (P >= 0 && R > NARROW_R)) return;  // the other instance's tile
+  if (WIDE != (P >= 0 && R > narrow_r)) return;  // the other instance's tile
   if (P < 0) {                                   // nothing reaches this tile
     for (int row = 0; row < (permol ? nrows : 1); row++)
       if (inb) out[((size_t)s * (permol ? nrows : 1) + row) * nwn + j] = 0.0;
@@ -1724,11 +1724,11 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
                                           nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, tile_lo, c->binstart.p,
                                           c->substart.p, c->nsub, c->nsube, c->s_rec.p, c->s_fbpid.p, c->d_ptab.p,
                                           c->s_reach.p, c->s_reachP.p, c->d_pdata2.p, dst,
-                                          c->s_nsamp.p + s0, S, c->s_part.p, c->s_tcnt.p, c->s_fclass.p);
+                                          c->s_nsamp.p + s0, S, c->s_part.p, c->s_tcnt.p, c->s_fclass.p, c->narrow_r);
       k_accumulate<false><<<g4, ACC_TILE, 0, st>>>(nwn, G, cs, niso, c->o, fd_o, nrows, permol, ntiles, tile_lo, c->binstart.p,
                                           c->substart.p, c->nsub, c->nsube, c->s_rec.p, c->s_fbpid.p, c->d_ptab.p,
                                           c->s_reach.p, c->s_reachP.p, c->d_pdata2.p, dst,
-                                          c->s_nsamp.p + s0, 1, nullptr, nullptr, c->s_fclass.p);
+                                          c->s_nsamp.p + s0, 1, nullptr, nullptr, c->s_fclass.p, c->narrow_r);
     }
     tb_timer_end(c, "accumulate");
     c->launches += 3;
@@ -1880,6 +1880,13 @@ extern "C" int tb_get_fused_stats(tb_ctx *c, int64_t *fused_states, int64_t *fus
 // Which states the fused kernel takes (tuning / comparison tap): widest reach in coarse bins (default FUSE_RMAX) and
 // whether states whose lines partly keep a CARRIED Doppler index are fused too (default no: measured on C2, the
 // two-kernel path is as fast on those layers -- 25 us against 30 us per layer -- and k_lastq_scan costs 35 us).
+// Widest reach, in coarse bins, of a tile summed by the one-thread-per-bin schedule of k_accumulate (default NARROW_R)
+extern "C" int tb_set_narrow_reach(tb_ctx *c, int r) {
+  TB_REQUIRE(r >= 0 && r <= 4096, TB_ERR_ARG, "tb_set_narrow_reach: 0..4096 coarse bins");
+  c->narrow_r = r;
+  return TB_OK;
+}
+
 extern "C" int tb_set_fused_reach(tb_ctx *c, int rmax, int carried) {
   TB_REQUIRE(rmax >= 1 && rmax <= 4096, TB_ERR_ARG, "tb_set_fused_reach: 1..4096 coarse bins");
   c->fuse_rmax = rmax;

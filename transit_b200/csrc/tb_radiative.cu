@@ -912,7 +912,7 @@ k_tau_eclipse(TauPar P, const double *__restrict__ e, const double *__restrict__
 // start carry the weight zero, so the loop is the same for the four rays.  Early exit, last[] and the zero
 // tail as in k_tau_transit.
 #define TAU_WL 2      // wavenumbers per lane of k_tau_w (a block owns 32 * TAU_WL columns)
-__global__ void __launch_bounds__(32 * TAU_NW, 3)
+__global__ void __launch_bounds__(32 * TAU_NW, 4)
 k_tau_w(TauPar P, const double *__restrict__ e, const double *__restrict__ ecs,
         const double *__restrict__ press, const double *__restrict__ temp,
         const double *__restrict__ aux, const double *__restrict__ mol_d,
@@ -1160,6 +1160,16 @@ int tb_check_errors(tb_ctx *c) {
 // 1 (default): eclipse tau by the O(layers) streaming kernel; 0: the general O(layers^2) kernel (comparison tap)
 extern "C" int tb_set_tau_streaming(tb_ctx *c, int on) {
   c->tau_stream_ecl = on != 0;
+  return TB_OK;
+}
+
+// The impact-parameter sample tb_spectrum integrates along (makeipsample, makesample.c:558-604).  With raddelt = -1
+// it is the radius sample reversed (h = NULL, the default); a resampled radius grid comes with its own sample,
+// built from the top radius downwards, which is NOT bit for bit the reversed radii.
+extern "C" int tb_set_rays(tb_ctx *c, const double *h, int nh, double hfct) {
+  if (!h || nh <= 0) { c->user_h.clear(); return TB_OK; }
+  c->user_h.assign(h, h + nh);
+  c->user_hfct = hfct;
   return TB_OK;
 }
 
@@ -1419,7 +1429,11 @@ extern "C" int tb_spectrum(tb_ctx *c, int geometry, double toomuch, double ethre
   else rc_e = tb_extinction_lbl(c, ethresh);               // computemolext per layer
   TB_CUDA(cudaStreamWaitEvent(main_st, c->ev_join, 0));    // also on error: never leave the fork dangling
   TB_TRY(rc_e);
-  TB_TRY(tb_tau_run(c, geometry, toomuch, nullptr, 0, 0, false));   // tau, transit.c:165,189
+  if (c->user_h.empty()) TB_TRY(tb_tau_run(c, geometry, toomuch, nullptr, 0, 0, false));   // tau, transit.c:165,189
+  else {
+    const std::vector<double> h(c->user_h);
+    TB_TRY(tb_tau_run(c, geometry, toomuch, h.data(), (int)h.size(), c->user_hfct, false));
+  }
   if (geometry == TB_GEOM_ECLIPSE) return tb_intensity_flux(c, angles_deg, nang, out);
   return tb_modulation(c, starrad_cm, transparent, out);
 }
