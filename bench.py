@@ -452,6 +452,8 @@ def run_ours(args):
         ctx.set_fused_reach(args.fuse_rmax, True)
     if args.narrow_r >= 0:
         ctx.set_narrow_reach(args.narrow_r)
+    if args.fuse_variant >= 0:
+        ctx.set_fused_variant(args.fuse_variant)
     out = np.zeros(prob.nwn)
     gathered = [None]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
@@ -631,6 +633,7 @@ def main():
                     help="N>1: one atmosphere per rank (weak scaling, default) or one spectrum split into "
                          "wavenumber bands (strong scaling)")
     ap.add_argument("--scale", type=float, default=1.0, help="line-count multiplier (debugging only; 1.0 = the named config)")
+    ap.add_argument("--fuse-variant", type=int, default=-1, help="tuning: 0 block-wide fused kernel, 1 warp-autonomous")
     ap.add_argument("--narrow-r", type=int, default=-1, help="tuning: widest reach (coarse bins) of the one-thread-per-bin gather")
     ap.add_argument("--fuse-rmax", type=int, default=0, help="tuning: widest reach (coarse bins) of a fused state")
     ap.add_argument("--no-bands-leg", action="store_true", help="N>1: skip the wavenumber-band strong-scaling leg")

@@ -90,6 +90,9 @@ int  tb_set_fused(tb_ctx *c, int on);
  * carried Doppler index (extinction.c:480-483; found by a bisection + backward scan instead of the list walk) are
  * fused as well (default 0: only states where every line refreshes its index) */
 int  tb_set_fused_reach(tb_ctx *c, int rmax, int carried);
+/* which fused kernel: 1 (default) = a warp per 32 bins x 4 states, no block barriers; 0 = a block per 128 bins x 4
+ * states with block-wide phases.  Same sums, bit for bit (tested).                                          */
+int  tb_set_fused_variant(tb_ctx *c, int v);
 /* two-kernel path: tiles whose reach is at most r coarse bins (default 2) are summed one thread per bin, the
  * others by the 16-warp window walk of k_accumulate (tuning knob; any value gives the same sums to rounding) */
 int  tb_set_narrow_reach(tb_ctx *c, int r);

@@ -174,6 +174,14 @@ def test_fused_line_sum_vs_two_kernel_path():
         tr_a = [c.line_trace(r) for r in tr_layers]
         a2 = c.molext_states(T, dens, Z, prob.ethresh, permol=permol)
         assert np.array_equal(a, a2)                                   # deterministic
+        c.set_fused_variant(0)             # the block-wide kernel: same windows, same chains, same bits as the warp-autonomous one
+        a0 = c.molext_states(T, dens, Z, prob.ethresh, permol=permol)
+        assert np.array_equal(a, a0) and np.array_equal(na, c.sample_counts(prob.nrad))
+        for x, r in zip(tr_a, tr_layers):
+            y = c.line_trace(r)
+            for k in ("status", "iown", "idwn", "idop"):
+                assert np.array_equal(x[k], y[k]), k
+        c.set_fused_variant(1)
         c.set_fused(False)
         b = c.molext_states(T, dens, Z, prob.ethresh, permol=permol)
         nb = c.sample_counts(prob.nrad)

@@ -53,6 +53,7 @@ ABI = {
     "tb_set_fused": (C.c_int, [C.c_void_p, C.c_int]),
     "tb_set_fused_reach": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "tb_set_narrow_reach": (C.c_int, [C.c_void_p, C.c_int]),
+    "tb_set_fused_variant": (C.c_int, [C.c_void_p, C.c_int]),
     "tb_set_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_double]),
     "tb_set_trace": (C.c_int, [C.c_void_p, C.c_int]),
     "tb_get_fused_stats": (C.c_int, [C.c_void_p, i64p, i64p]),
@@ -269,6 +270,9 @@ class Context:
             return
         h = np.ascontiguousarray(h, dtype=np.float64)
         self._ck(self.lib.tb_set_rays(self.h, h.ctypes.data_as(C.c_void_p), len(h), float(hfct)), "tb_set_rays")
+
+    def set_fused_variant(self, v):
+        self._ck(self.lib.tb_set_fused_variant(self.h, int(v)), "tb_set_fused_variant")
 
     def set_narrow_reach(self, r):
         self._ck(self.lib.tb_set_narrow_reach(self.h, int(r)), "tb_set_narrow_reach")

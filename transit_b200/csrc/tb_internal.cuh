@@ -234,6 +234,7 @@ struct tb_ctx {
   DevBuf<LineRec> s_rec;      // [state][group]
   DevBuf<int32_t> s_fclass, s_fP, s_lastq2;   // s_lastq2: carried-index source of the fused states (k_lastq_scan)
   int fuse_rmax = 8;
+  int fuse_variant = 1;          // 0: k_linesum_fused, 1: k_linesum_fused_w
   int narrow_r = 2;              // NARROW_R of tb_lines.cu
   bool fuse_carried = false;     // fuse states whose lines partly keep a carried Doppler index (k_lastq_scan)   // per batch of 8 states: taken by k_linesum_fused? / widest half-size (fine bins)
   int fuse_enabled = 1;          // 0 off, 1 on where the grid has enough tiles, 2 always (tests)

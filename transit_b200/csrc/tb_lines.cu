@@ -1464,6 +1464,277 @@ k_linesum_fused(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol
   }
 }
 
+// ---- the same line sum with WARP-AUTONOMOUS phases.  k_linesum_fused spends a third of its stall samples at its
+// two block barriers (profiles/r2_prof_fused_summary.txt): 256 threads wait for the slowest warp's candidate loads
+// in phase 1 and for the ragged last pass of phase 2.  Here a warp owns 32 output bins x 4 states and runs the three
+// phases on its own window of groups with __syncwarp only; a block is 8 such warps = one 128-bin tile x one batch
+// of FB = 8 states (warps 0-3: states 0-3, warps 4-7: states 4-7), which share the per-(state, isotope) tables.
+//   phase 1  32 candidates per step through the log-domain pretest; the survivors join a QUEUE (ordered);
+//   phase 2  as soon as the queue holds 32 groups (or the window is exhausted) one lane per group evaluates them --
+//            always a full pass, the rest of the queue waits for the next round -- into 32 shared records per state;
+//   phase 3  lane = (bin mod 8, state): the round's 32 records span a bin or two, so the bins they can touch (first
+//            fine bin - P .. last + P) are a handful; each lane walks the 32 records of its state for its bin(s) of
+//            that range: 128-bit shared read, "covers my bin" test, table read + FMA.  Four accumulators per lane
+//            (bins bq, bq+8, bq+16, bq+24 of the unit).
+// The price is the halo: a 32-bin unit re-evaluates the groups within the widest profile of its edges (window
+// 32 + 2R bins instead of 128 + 2R), a few per cent where the profiles reach +-1..2 bins.  Each bin still sums its
+// records over rows and sorted records: the same FMA chain, the same bits as k_linesum_fused.
+#define FW_Q 64              // queue entries per warp (a round consumes 32)
+#define FW_NW 8              // warps per block
+template <bool CARRIED>
+__global__ void __launch_bounds__(32 * FW_NW, 4)
+k_linesum_fused_w(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nmol, int o, FastDiv fd_o, FastDiv fd_tile,
+                  int nrows, int permol, int tile_off, double wn_i, double odwn,
+                  const int32_t *__restrict__ fclass, const int32_t *__restrict__ fP,
+                  const int32_t *__restrict__ binstart, const int32_t *__restrict__ g_start,
+                  const int16_t *__restrict__ g_iso, const int32_t *__restrict__ g_iown,
+                  const double *__restrict__ g_wavn, const double *__restrict__ g_a0,
+                  const double *__restrict__ g_gf, const double *__restrict__ g_lg,
+                  const double *__restrict__ rtemp, const double *__restrict__ facz, const double *__restrict__ lcz,
+                  const double *__restrict__ xterm, int64_t X, float dop_lmin, float dop_rstep,
+                  const double *__restrict__ dens, const int *__restrict__ iso_imol, const int *__restrict__ iso_row,
+                  const double *__restrict__ alphad, const int32_t *__restrict__ ilor,
+                  const double *__restrict__ alphal, const double *__restrict__ ral, const int32_t *__restrict__ fbpid,
+                  const double *__restrict__ aDop, int nDop, const ProfEntry *__restrict__ ptab, int nLor,
+                  double ethresh, const double *__restrict__ kmax, const double *__restrict__ pdata,
+                  double *__restrict__ out, unsigned long long *__restrict__ nsamp, LineRec *__restrict__ rec_out) {
+  const int batch = blockIdx.y;
+  if (!fclass[batch]) return;                      // k_strength + k_accumulate take this batch
+  extern __shared__ __align__(16) unsigned char fsm[];
+  FuseRec *sh_rec_all = reinterpret_cast<FuseRec *>(fsm);                          // [FW_NW][FBK][32]
+  int *sh_q_all = reinterpret_cast<int *>(sh_rec_all + FW_NW * FBK * 32);           // [FW_NW][FW_Q] group index
+  int *sh_io_all = sh_q_all + FW_NW * FW_Q;                                        // [FW_NW][32] fine bins of the round
+  double *sh_aDop = reinterpret_cast<double *>(sh_io_all + FW_NW * 32);            // [256]
+  double *sh_rT = sh_aDop + 256;                                                   // [FB]
+  FuseTab *sh_tab = reinterpret_cast<FuseTab *>(sh_rT + FB);                       // [FB][niso]
+  int *sh_ilor = reinterpret_cast<int *>(sh_tab + FB * niso);                      // [FB][niso]
+  int *sh_fbpid = sh_ilor + FB * niso;                                             // [FB][niso] carried cell
+  unsigned char *sh_m_all = reinterpret_cast<unsigned char *>(sh_fbpid + FB * niso);   // [FW_NW][FW_Q] alive states
+  __shared__ int sh_Prow[16];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int sb = batch * FB;                       // first state of the batch
+  const int tile = blockIdx.x + tile_off;
+  const int Pb = fP[batch];
+  for (int i = tid; i <= nDop; i += 32 * FW_NW) sh_aDop[i] = aDop[i];              // [nDop] = +inf sentinel
+  if (tid < FB) sh_rT[tid] = rtemp[sb + tid < ns ? sb + tid : ns - 1];
+  if (tid < 16) sh_Prow[tid] = 0;
+  for (int i = tid; i < FB * niso; i += 32 * FW_NW) {
+    const int k = i / niso, iso = i % niso, s = sb + k < ns ? sb + k : ns - 1;
+    const int si = s * niso + iso;
+    FuseTab t;
+    t.lcz = lcz[si]; t.facz = facz[si];
+    t.thr = __dmul_rn(ethresh, kmax[s * nrows + (permol ? iso_row[iso] : 0)]);
+    t.densf = dens[s * nmol + iso_imol[iso]];
+    t.alphad = alphad[si]; t.alphal = alphal[si]; t.ral = ral[si];
+    sh_tab[i] = t;
+    sh_ilor[i] = ilor[si];
+    sh_fbpid[i] = CARRIED ? fbpid[si] : 0;
+  }
+  __syncthreads();
+  {  // the widest profile a line of each molecule row can take in this tile (see k_linesum_fused), over the batch
+    int64_t ftop = (int64_t)o * ((int64_t)tile * ACC_TILE + ACC_TILE - 1) + Pb + 1;
+    if (ftop > onwn - 1) ftop = onwn - 1;
+    const double wtop = tb_fine_wn(wn_i, odwn, ftop);
+    for (int i = tid; i < FB * niso; i += 32 * FW_NW) {
+      const int k = i / niso, iso = i % niso;
+      if (sb + k >= ns) continue;
+      const int id = tb_binsearchapprox(sh_aDop, __dmul_rn(sh_tab[i].alphad, wtop), 0, nDop);
+      const int row = nrows <= 16 ? iso_row[iso] : 0;
+      const int pc = CARRIED ? ptab[sh_fbpid[i]].psize : 0, pr_ = ptab[id * nLor + sh_ilor[i]].psize;
+      atomicMax(&sh_Prow[row], pc > pr_ ? pc : pr_);
+    }
+  }
+  __syncthreads();                                 // the last block-wide barrier
+  // ---- this warp's unit: bins jt .. jt+31 of the tile, states s0 .. s0+3
+  const int quad = warp >> 2;                      // 0: states 0-3 of the batch, 1: states 4-7
+  const int s0 = sb + quad * FBK;
+  const int64_t jt = (int64_t)tile * ACC_TILE + (warp & 3) * 32;
+  if (jt >= nwn || s0 >= ns) return;
+  FuseRec *sh_rec = sh_rec_all + (size_t)warp * FBK * 32;
+  int *sh_q = sh_q_all + warp * FW_Q, *sh_io = sh_io_all + warp * 32;
+  unsigned char *sh_m = sh_m_all + warp * FW_Q;
+  const FuseTab *tab = sh_tab + (size_t)quad * FBK * niso;
+  const int *qilor = sh_ilor + quad * FBK * niso, *qfbpid = sh_fbpid + quad * FBK * niso;
+  const double *qrT = sh_rT + quad * FBK;
+  const int myk = lane & 3, bq = lane >> 2;        // phase 3: this lane's state and its bin modulo 8
+  const FuseRec *myrec = sh_rec + myk * 32;
+  const int maxbin = (int)(nwn - 1 - jt < 31 ? nwn - 1 - jt : 31);
+  double acc[4];
+  unsigned cnt = 0u;
+#pragma unroll
+  for (int i = 0; i < 4; i++) acc[i] = 0.0;
+  const unsigned nsmask = ns - s0 >= FBK ? (1u << FBK) - 1u : (1u << (ns - s0)) - 1u;      // states that exist
+  for (int row = 0; row < nrows; row++) {
+    const int P = nrows <= 16 ? sh_Prow[row] : Pb;
+    const int R = P / o + 1;
+    const int64_t jlo = jt - R < 0 ? 0 : jt - R;
+    const int64_t jhi = jt + 32 + R > nwn ? nwn : jt + 32 + R;
+    const int pa = binstart[(size_t)row * nwn + jlo], pb = binstart[(size_t)row * nwn + jhi];
+    int p = pa, nq = 0;
+    while (true) {
+      // ---- phase 1: fill the queue
+      while (p < pb && nq < 32) {
+        const int q = p + lane;
+        unsigned m8 = 0;
+        if (q < pb) {
+          const double a0 = g_a0[q], lg = g_lg[q];
+          const FuseTab *tb = tab + g_iso[q];
+#pragma unroll
+          for (int k = 0; k < FBK; k++)
+            if (!(fma(a0, qrT[k], lg + tb[k * niso].lcz) < -1e-9)) m8 |= 1u << k;
+          m8 &= nsmask;
+        }
+        const unsigned ball = __ballot_sync(0xffffffffu, m8 != 0);
+        if (m8) {
+          const int c = nq + __popc(ball & ((1u << lane) - 1));
+          sh_q[c] = q;
+          sh_m[c] = (unsigned char)m8;
+        }
+        nq += __popc(ball);
+        p += 32;
+      }
+      if (nq == 0) break;
+      __syncwarp();
+      const int n = nq < 32 ? nq : 32;
+      // ---- phase 2: one lane per queued group, a loop over its alive states (k_linesum_fused's, verbatim)
+      int iown = 0;
+      if (lane < n) {
+        const int q = sh_q[lane];
+        const unsigned m8 = sh_m[lane];
+        const int iso = g_iso[q];
+        const int b = g_start[q], e = g_start[q + 1];
+        const double wlead = g_wavn[q], gf = g_gf[q], a0 = g_a0[q];
+        iown = g_iown[q];
+        const double wneg = __dmul_rn(-TB_EXPCTE, wlead);
+        bool home = false;
+        if (rec_out) { const int qbin = fd_div(iown, fd_o); home = qbin >= (int)jt && qbin < (int)jt + 32; }   // trace: written by the group's own unit
+        int lo = -1;
+#pragma unroll 1
+        for (int k = 0; k < FBK; k++) {
+          FuseRec rr;
+          rr.k = 0.0; rr.A = 0; rr.jl = 1; rr.jh = 0;                // dead unless proven otherwise
+          if ((m8 >> k) & 1u) {
+            const int s = s0 + k;
+            const double rT = qrT[k];
+            const FuseTab t = tab[k * niso + iso];
+            const double *xt = xterm + (size_t)s * X + (b - q);
+            const double x1 = e - b > 1 ? __ldg(xt) : 0.0;
+            const double ge1 = __dmul_rn(gf, tb_exp(a0 * rT));
+            double kk = 0.0;
+            bool below = (e - b == 1) && ge1 * t.facz < 0.999999 * t.thr;
+            if (!below) {
+              double a = __dmul_rn(ge1, (1 - tb_exp(wneg * rT)));
+              if (e - b > 1) {                                      // co-added members, in order (extinction.c:449-462)
+                a = __dadd_rn(a, x1);
+                for (int l = b + 2; l < e; l++) a = __dadd_rn(a, xt[l - b - 1]);
+              }
+              kk = __dmul_rn(a, t.facz);
+              below = kk < t.thr;                                  // extinction.c:467-470
+            }
+            if (!below) {
+              if (!permol) kk = __dmul_rn(kk, t.densf);
+              const double adw = __dmul_rn(t.alphad, wlead);
+              unsigned pid;
+              if (!CARRIED || tb_refresh(adw, t.alphal, t.ral)) {   // extinction.c:480-483
+                if (lo < 0) {
+                  lo = (int)((__log2f((float)adw) * 0.30102999566f - dop_lmin) * dop_rstep);
+                  lo = lo < 0 ? 0 : (lo > nDop - 1 ? nDop - 1 : lo);
+                }
+                while (lo > 0 && sh_aDop[lo] > adw) lo--;
+                while (sh_aDop[lo + 1] <= adw) lo++;
+                const int id = (fabs(sh_aDop[lo + 1] - adw) < fabs(sh_aDop[lo] - adw)) ? lo + 1 : lo;
+                pid = (unsigned)(id * nLor + qilor[k * niso + iso]);
+              } else
+                pid = (unsigned)qfbpid[k * niso + iso];
+              const ProfEntry pe = ptab[pid];
+              const int ps = pe.psize;
+              const int lof = iown - ps;
+              int jl = lof <= 0 ? 0 : fd_div(lof + o - 1, fd_o);
+              int jh = fd_div(iown + ps, fd_o);
+              if (jh > (int)(nwn - 1)) jh = (int)(nwn - 1);
+              const bool reach = jl <= jh;
+              if (reach) {
+                int i0 = o * jl - lof, m = 0;
+                if (i0 >= o) { m = fd_div(i0, fd_o); i0 -= m * o; }
+                jl -= (int)jt; jh -= (int)jt;
+                rr.k = kk;
+                rr.A = pe.off + i0 * pe.nk + m - jl;                // + unit-relative bin
+                rr.jl = (short)(jl < 0 ? 0 : jl);
+                rr.jh = (short)(jh > 31 ? 31 : jh);
+              }
+              if (home) {
+                LineRec r;
+                r.k = kk; r.iown = iown; r.pid = reach ? pid : (pid | PID_NOREACH);
+                rec_out[(size_t)s * G + q] = r;
+              }
+            }
+          }
+          sh_rec[k * 32 + lane] = rr;
+        }
+      }
+      sh_io[lane] = lane < n ? iown : 0x7fffffff;
+      // bins the round can touch: first fine bin - P .. last fine bin + P (the queue is in fine-bin order)
+      const int io_min = __shfl_sync(0xffffffffu, iown, 0), io_max = __shfl_sync(0xffffffffu, iown, n - 1);
+      int b_lo = io_min - P <= 0 ? 0 : fd_div(io_min - P, fd_o) - (int)jt;
+      int b_hi = fd_div(io_max + P, fd_o) - (int)jt;
+      if (b_lo < 0) b_lo = 0;
+      if (b_hi > maxbin) b_hi = maxbin;
+      // the part of the queue that waits for the next round moves to the front
+      int nxt_q = 0;
+      unsigned char nxt_m = 0;
+      if (lane + 32 < nq) { nxt_q = sh_q[lane + 32]; nxt_m = sh_m[lane + 32]; }
+      __syncwarp();
+      if (lane + 32 < nq) { sh_q[lane] = nxt_q; sh_m[lane] = nxt_m; }
+      nq -= n;
+      // ---- phase 3: lane = (bin mod 8, state) over the round's records
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        if (8 * i + 7 < b_lo || 8 * i > b_hi) continue;             // warp-uniform
+        const int bin = 8 * i + bq;
+        if (bin >= b_lo && bin <= b_hi) {
+          const int ob = o * ((int)jt + bin), lo_f = ob - P, hi_f = ob + P;
+          int c = 0;                                                // first record of the bin's window: 5 bisection steps
+#pragma unroll
+          for (int st = 16; st > 0; st >>= 1)
+            if (sh_io[c + st - 1] < lo_f) c += st;
+          for (; c < n && sh_io[c] <= hi_f; c++) {
+            const int4 v = *reinterpret_cast<const int4 *>(myrec + c);
+            const int jl = (int)(short)(v.w & 0xFFFF), jh = v.w >> 16;
+            if (bin >= jl && bin <= jh) {
+              acc[i] = fma(__hiloint2double(v.y, v.x), pdata[v.z + bin], acc[i]);
+              cnt++;
+            }
+          }
+        }
+      }
+      __syncwarp();                                // the next round rewrites the records
+    }
+    if (permol) {
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        const int s = s0 + myk;
+        if (8 * i + bq <= maxbin && s < ns) out[((size_t)s * nrows + row) * nwn + jt + 8 * i + bq] = acc[i];
+        acc[i] = 0.0;
+      }
+    }
+  }
+  if (!permol) {
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const int s = s0 + myk;
+      if (8 * i + bq <= maxbin && s < ns) out[(size_t)s * nwn + jt + 8 * i + bq] = acc[i];
+    }
+  }
+  // sample counters (integer atomics): lanes of equal state add up, one add per warp and state
+  for (int dlt = 4; dlt < 32; dlt <<= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, dlt);
+  if (lane < 4 && cnt && s0 + lane < ns) atomicAdd(&nsamp[s0 + lane], (unsigned long long)cnt);
+}
+
+static size_t fusew_shared_bytes(int niso) {
+  return (size_t)FW_NW * FBK * 32 * sizeof(FuseRec) + (size_t)FW_NW * FW_Q * 4 + (size_t)FW_NW * 32 * 4 + 256 * 8 + FB * 8 +
+         (size_t)FB * niso * sizeof(FuseTab) + (size_t)FB * niso * 8 + (size_t)FW_NW * FW_Q + 16;
+}
+
 static size_t fuse_shared_bytes(int niso) {
   return (size_t)FBK * FUSE_CAPA * sizeof(FuseRec) + (size_t)FUSE_CAPA * 4 * 2 + 256 * 8 + FBK * 8 +
          (size_t)FBK * niso * sizeof(FuseTab) + (size_t)FBK * niso * 8 + FUSE_CAPA + 16;
@@ -1511,14 +1782,16 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
   TB_TRY(c->s_rec.ensure((size_t)chunk * G + 1));
   const int nbatch_max = (chunk + FB - 1) / FB;
   TB_TRY(c->s_fclass.ensure(nbatch_max)); TB_TRY(c->s_fP.ensure(nbatch_max));
-  const size_t fuse_shm = fuse_shared_bytes(niso);
+  const size_t fuse_shm = fuse_shared_bytes(niso), fusew_shm = fusew_shared_bytes(niso);
   // a tile of 128 bins x 4 states is the fused kernel's unit of parallelism: a grid of a few dozen tiles (C1: 20)
   // cannot fill 148 SMs with it (measured: C1 1.29 -> 2.9 ms per step), so small grids keep the two-kernel path
-  const bool fuse_on = c->fuse_enabled && niso >= 1 && niso <= FUSE_MAXISO && G > 0 && fuse_shm <= 100 * 1024 &&
+  const bool fuse_on = c->fuse_enabled && niso >= 1 && niso <= FUSE_MAXISO && G > 0 && fuse_shm <= 100 * 1024 && fusew_shm <= 100 * 1024 &&
                        (ntiles >= FUSE_MIN_TILES || c->fuse_enabled > 1);
   if (fuse_on && c->fuse_shm_set != (int)fuse_shm) {
     TB_CUDA(cudaFuncSetAttribute(k_linesum_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fuse_shm));
     TB_CUDA(cudaFuncSetAttribute(k_linesum_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fuse_shm));
+    TB_CUDA(cudaFuncSetAttribute(k_linesum_fused_w<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fusew_shm));
+    TB_CUDA(cudaFuncSetAttribute(k_linesum_fused_w<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fusew_shm));
     c->fuse_shm_set = (int)fuse_shm;
   }
   double *d_out = d_out_rows;
@@ -1655,8 +1928,10 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
           trace_rec = c->s_rec.p;
         }
         const bool carried = scan_fused;
-        auto fused_kernel = carried ? k_linesum_fused<true> : k_linesum_fused<false>;
-        fused_kernel<<<dim3(tile_hi - tile_lo, nbatch * (FB / FBK)), FUSE_NT, fuse_shm, st>>>(
+        auto fused_kernel = c->fuse_variant ? (carried ? k_linesum_fused_w<true> : k_linesum_fused_w<false>)
+                                            : (carried ? k_linesum_fused<true> : k_linesum_fused<false>);
+        fused_kernel<<<dim3(tile_hi - tile_lo, c->fuse_variant ? nbatch : nbatch * (FB / FBK)),
+                       c->fuse_variant ? 32 * FW_NW : FUSE_NT, c->fuse_variant ? fusew_shm : fuse_shm, st>>>(
             nwn, c->onwn, G, cs, niso, nmol, c->o, fd_o, fd_tile, nrows, permol, tile_lo, c->wn_i, c->odwn,
             c->s_fclass.p, c->s_fP.p, c->binstart.p,
             c->g_start.p, c->g_iso.p, c->g_iown.p, c->g_wavn.p, c->g_a0.p, c->g_gf.p, c->g_lg.p, c->s_rtemp.p,
@@ -1880,6 +2155,14 @@ extern "C" int tb_get_fused_stats(tb_ctx *c, int64_t *fused_states, int64_t *fus
 // Which states the fused kernel takes (tuning / comparison tap): widest reach in coarse bins (default FUSE_RMAX) and
 // whether states whose lines partly keep a CARRIED Doppler index are fused too (default no: measured on C2, the
 // two-kernel path is as fast on those layers -- 25 us against 30 us per layer -- and k_lastq_scan costs 35 us).
+// Which fused kernel: 0 = k_linesum_fused (a block per 128 bins x 4 states, block barriers between the phases),
+// 1 = k_linesum_fused_w (a warp per 32 bins x 4 states, no block barrier).  Same sums, bit for bit.
+extern "C" int tb_set_fused_variant(tb_ctx *c, int v) {
+  TB_REQUIRE(v == 0 || v == 1, TB_ERR_ARG, "tb_set_fused_variant: 0 or 1");
+  c->fuse_variant = v;
+  return TB_OK;
+}
+
 // Widest reach, in coarse bins, of a tile summed by the one-thread-per-bin schedule of k_accumulate (default NARROW_R)
 extern "C" int tb_set_narrow_reach(tb_ctx *c, int r) {
   TB_REQUIRE(r >= 0 && r <= 4096, TB_ERR_ARG, "tb_set_narrow_reach: 0..4096 coarse bins");
