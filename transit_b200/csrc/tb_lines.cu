@@ -1697,13 +1697,20 @@ k_linesum_fused_w(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nm
 #pragma unroll
           for (int st = 16; st > 0; st >>= 1)
             if (sh_io[c + st - 1] < lo_f) c += st;
-          for (; c < n && sh_io[c] <= hi_f; c++) {
-            const int4 v = *reinterpret_cast<const int4 *>(myrec + c);
-            const int jl = (int)(short)(v.w & 0xFFFF), jh = v.w >> 16;
-            if (bin >= jl && bin <= jh) {
-              acc[i] = fma(__hiloint2double(v.y, v.x), pdata[v.z + bin], acc[i]);
-              cnt++;
-            }
+          int ce = 0;                                               // one past its last record
+#pragma unroll
+          for (int st = 16; st > 0; st >>= 1)
+            if (sh_io[ce + st - 1] <= hi_f) ce += st;
+          if (ce == 31 && sh_io[31] <= hi_f) ce = 32;
+          // two records per step: both table reads are in flight before the first FMA waits for its sample
+          for (; c < ce; c += 2) {
+            const int4 v0 = *reinterpret_cast<const int4 *>(myrec + c);
+            const int4 v1 = *reinterpret_cast<const int4 *>(myrec + (c + 1 < ce ? c + 1 : c));
+            const bool h0 = bin >= (int)(short)(v0.w & 0xFFFF) && bin <= (v0.w >> 16);
+            const bool h1 = c + 1 < ce && bin >= (int)(short)(v1.w & 0xFFFF) && bin <= (v1.w >> 16);
+            const double p0 = h0 ? pdata[v0.z + bin] : 0.0, p1 = h1 ? pdata[v1.z + bin] : 0.0;
+            if (h0) { acc[i] = fma(__hiloint2double(v0.y, v0.x), p0, acc[i]); cnt++; }
+            if (h1) { acc[i] = fma(__hiloint2double(v1.y, v1.x), p1, acc[i]); cnt++; }
           }
         }
       }
