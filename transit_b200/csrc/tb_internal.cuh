@@ -90,7 +90,7 @@ struct ProfEntry {
   int32_t off;      // offset of the profile in the polyphase float table
   int32_t psize;    // half size in fine samples
   int32_t nk;       // coarse samples per phase: 2*psize/o + 1
-  int32_t pad;
+  int32_t pad;      // psize / o
 };
 
 // What k_strength leaves per (state, group) for k_accumulate: one 16-byte record, so that a

@@ -1509,7 +1509,8 @@ k_linesum_fused_w(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nm
   FuseTab *sh_tab = reinterpret_cast<FuseTab *>(sh_rT + FB);                       // [FB][niso]
   int *sh_ilor = reinterpret_cast<int *>(sh_tab + FB * niso);                      // [FB][niso]
   int *sh_fbpid = sh_ilor + FB * niso;                                             // [FB][niso] carried cell
-  unsigned char *sh_m_all = reinterpret_cast<unsigned char *>(sh_fbpid + FB * niso);   // [FW_NW][FW_Q] alive states
+  int *sh_lo0 = sh_fbpid + FB * niso;                                              // [FB][niso] Doppler cell below the tile's window
+  unsigned char *sh_m_all = reinterpret_cast<unsigned char *>(sh_lo0 + FB * niso);   // [FW_NW][FW_Q] alive states
   __shared__ int sh_Prow[16];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int sb = batch * FB;                       // first state of the batch
@@ -1542,6 +1543,17 @@ k_linesum_fused_w(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nm
       const int row = nrows <= 16 ? iso_row[iso] : 0;
       const int pc = CARRIED ? ptab[sh_fbpid[i]].psize : 0, pr_ = ptab[id * nLor + sh_ilor[i]].psize;
       atomicMax(&sh_Prow[row], pc > pr_ ? pc : pr_);
+      // ... and the last cell at or below the Doppler width of the LOWEST wavenumber any candidate of the tile can
+      // have (tile start - the batch-wide reach - one bin): phase 2's search starts there and only walks up
+      int64_t fbot = (int64_t)o * ((int64_t)tile * ACC_TILE - 1) - Pb - 1;
+      if (fbot < 0) fbot = 0;
+      const double abot = __dmul_rn(sh_tab[i].alphad, tb_fine_wn(wn_i, odwn, fbot));
+      int l0 = 0, l1 = nDop - 1;                   // largest l in [0, nDop-1] with aDop[l] <= abot (0 if none)
+      while (l0 < l1) {
+        const int mid = (l0 + l1 + 1) >> 1;
+        if (sh_aDop[mid] <= abot) l0 = mid; else l1 = mid - 1;
+      }
+      sh_lo0[i] = l0;
     }
   }
   __syncthreads();                                 // the last block-wide barrier
@@ -1554,7 +1566,7 @@ k_linesum_fused_w(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nm
   int *sh_q = sh_q_all + warp * FW_Q, *sh_io = sh_io_all + warp * 32;
   unsigned char *sh_m = sh_m_all + warp * FW_Q;
   const FuseTab *tab = sh_tab + (size_t)quad * FBK * niso;
-  const int *qilor = sh_ilor + quad * FBK * niso, *qfbpid = sh_fbpid + quad * FBK * niso;
+  const int *qilor = sh_ilor + quad * FBK * niso, *qfbpid = sh_fbpid + quad * FBK * niso, *qlo0 = sh_lo0 + quad * FBK * niso;
   const double *qrT = sh_rT + quad * FBK;
   const int myk = lane & 3, bq = lane >> 2;        // phase 3: this lane's state and its bin modulo 8
   const FuseRec *myrec = sh_rec + myk * 32;
@@ -1606,9 +1618,8 @@ k_linesum_fused_w(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nm
         const double wlead = g_wavn[q], gf = g_gf[q], a0 = g_a0[q];
         iown = g_iown[q];
         const double wneg = __dmul_rn(-TB_EXPCTE, wlead);
-        bool home = false;
-        if (rec_out) { const int qbin = fd_div(iown, fd_o); home = qbin >= (int)jt && qbin < (int)jt + 32; }   // trace: written by the group's own unit
-        int lo = -1;
+        const int gq = fd_div(iown, fd_o), gr = iown - gq * o;      // iown = o*gq + gr: the bin ranges below need no division
+        const bool home = rec_out && gq >= (int)jt && gq < (int)jt + 32;   // trace: written by the group's own unit
 #pragma unroll 1
         for (int k = 0; k < FBK; k++) {
           FuseRec rr;
@@ -1636,11 +1647,9 @@ k_linesum_fused_w(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nm
               const double adw = __dmul_rn(t.alphad, wlead);
               unsigned pid;
               if (!CARRIED || tb_refresh(adw, t.alphal, t.ral)) {   // extinction.c:480-483
-                if (lo < 0) {
-                  lo = (int)((__log2f((float)adw) * 0.30102999566f - dop_lmin) * dop_rstep);
-                  lo = lo < 0 ? 0 : (lo > nDop - 1 ? nDop - 1 : lo);
-                }
-                while (lo > 0 && sh_aDop[lo] > adw) lo--;
+                // binsearchapprox (iomisc.c:1088-1108): the last cell at or below adw, found upwards from the tile's
+                // start cell (the Doppler width grows with the wavenumber), then the nearer of it and the next
+                int lo = qlo0[k * niso + iso];
                 while (sh_aDop[lo + 1] <= adw) lo++;
                 const int id = (fabs(sh_aDop[lo + 1] - adw) < fabs(sh_aDop[lo] - adw)) ? lo + 1 : lo;
                 pid = (unsigned)(id * nLor + qilor[k * niso + iso]);
@@ -1649,13 +1658,15 @@ k_linesum_fused_w(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nm
               const ProfEntry pe = ptab[pid];
               const int ps = pe.psize;
               const int lof = iown - ps;
-              int jl = lof <= 0 ? 0 : fd_div(lof + o - 1, fd_o);
-              int jh = fd_div(iown + ps, fd_o);
+              // ps = o*pe.pad + pr: ceil((iown - ps)/o) = gq - pad + (gr > pr), floor((iown + ps)/o) = gq + pad + (gr + pr >= o)
+              const int pr = ps - pe.pad * o;
+              int jl = lof <= 0 ? 0 : gq - pe.pad + (gr > pr ? 1 : 0);
+              int jh = gq + pe.pad + (gr + pr >= o ? 1 : 0);
               if (jh > (int)(nwn - 1)) jh = (int)(nwn - 1);
               const bool reach = jl <= jh;
               if (reach) {
                 int i0 = o * jl - lof, m = 0;
-                if (i0 >= o) { m = fd_div(i0, fd_o); i0 -= m * o; }
+                if (i0 >= o) { m = fd_div(i0, fd_o); i0 -= m * o; }    // only where jl was clamped to the grid start
                 jl -= (int)jt; jh -= (int)jt;
                 rr.k = kk;
                 rr.A = pe.off + i0 * pe.nk + m - jl;                // + unit-relative bin
@@ -1739,7 +1750,7 @@ k_linesum_fused_w(int64_t nwn, int64_t onwn, int64_t G, int ns, int niso, int nm
 
 static size_t fusew_shared_bytes(int niso) {
   return (size_t)FW_NW * FBK * 32 * sizeof(FuseRec) + (size_t)FW_NW * FW_Q * 4 + (size_t)FW_NW * 32 * 4 + 256 * 8 + FB * 8 +
-         (size_t)FB * niso * sizeof(FuseTab) + (size_t)FB * niso * 8 + (size_t)FW_NW * FW_Q + 16;
+         (size_t)FB * niso * sizeof(FuseTab) + (size_t)FB * niso * 12 + (size_t)FW_NW * FW_Q + 16;
 }
 
 static size_t fuse_shared_bytes(int niso) {

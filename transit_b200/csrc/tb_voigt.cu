@@ -229,7 +229,7 @@ extern "C" int tb_build_profiles(tb_ctx *c, int nDop, int nLor, float dmin, floa
       ptab[cell].off = off2[k];
       ptab[cell].psize = (int32_t)c->psize[cell];
       ptab[cell].nk = (int32_t)((2 * c->psize[cell]) / c->o + 1);
-      ptab[cell].pad = 0;
+      ptab[cell].pad = (int32_t)(c->psize[cell] / c->o);      // psize = o*pad + remainder: k_linesum_fused_w's bin range without a division
     }
   }
   TB_REQUIRE(blocks < 2147483647LL, TB_ERR_ARG, "Voigt table too large for one launch");
