@@ -957,12 +957,12 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
     for (int row = 0; row < nrows; row++) {
       const int32_t *bs = binstart + (size_t)row * nwn;
       const int p0 = bs[ulo], p1 = bs[uhi];
+      // the window's records in chunks of 32, dealt round-robin to the ACC_WW * S warps that share the tile: the
+      // alive records and their spans vary smoothly along the window, so every warp gets the same mix (contiguous
+      // runs left a quarter of the stall samples at the block's last barrier); a fixed deal, hence a fixed order
       const int nseg = ACC_WW * S;
-      const int seg = (((p1 - p0 + nseg - 1) / nseg) + 31) & ~31;       // records per warp, whole chunks
-      const int pa0 = p0 + (ksplit * ACC_WW + warp) * seg;
-      const int pa = pa0 < p1 ? pa0 : p1;
-      const int pb = pa + seg < p1 ? pa + seg : p1;
-      for (int base = pa; base < pb; base += 32) {
+      const int pb = p1;
+      for (int base = p0 + (ksplit * ACC_WW + warp) * 32; base < pb; base += nseg * 32) {
         const int p = base + lane;
         const int4 rr = p < pb ? __ldg(rs + p) : make_int4(0, 0, 0, PID_SKIP);
         unsigned pid = (unsigned)rr.w & 0xFFFFu;
