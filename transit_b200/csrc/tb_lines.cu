@@ -989,17 +989,41 @@ k_accumulate(int64_t nwn, int64_t G, int ns, int niso, int o, FastDiv fd, int nr
         }
         const unsigned m = __ballot_sync(0xffffffffu, alive);
         if (alive) w.rec[warp][__popc(m & ((1u << lane) - 1))] = rec;
+        // the 32-bin quarters of the tile any record of the chunk touches (the chunk's records are neighbours in
+        // fine bin: away from the deepest layers they all sit in one or two quarters)
+        unsigned qm = 0;
+        if (alive) {
+          const int lo = rec.lanes & 255, hi = lo + (rec.lanes >> 8);
+          qm = ((2u << (hi >> 5)) - 1u) & ~((1u << (lo >> 5)) - 1u);
+        }
+        qm = __reduce_or_sync(0xffffffffu, qm);
         __syncwarp();
         const int n = __popc(m);
+        if (__popc(qm) > 2) {
+          // record-major: four predicated (load, FMA) pairs per record
 #pragma unroll 2
-        for (int i = 0; i < n; i++) {
-          const AccRec r = w.rec[warp][i];
-          const int d = lane - (r.lanes & 255);                  // bin - lo for q = 0
-          const unsigned span = (unsigned)(r.lanes >> 8);        // hi - lo
-          const double *pp = pdata + r.addr0 + lane;
+          for (int i = 0; i < n; i++) {
+            const AccRec r = w.rec[warp][i];
+            const int d = lane - (r.lanes & 255);                  // bin - lo for q = 0
+            const unsigned span = (unsigned)(r.lanes >> 8);        // hi - lo
+            const double *pp = pdata + r.addr0 + lane;
 #pragma unroll
-          for (int q = 0; q < ACC_TILE / 32; q++)
-            if ((unsigned)(d + 32 * q) <= span) acc[q] = fma(r.k, __ldg(pp + 32 * q), acc[q]);
+            for (int q = 0; q < ACC_TILE / 32; q++)
+              if ((unsigned)(d + 32 * q) <= span) acc[q] = fma(r.k, __ldg(pp + 32 * q), acc[q]);
+          }
+        } else {
+          // quarter-major: only the touched quarters walk the records (same records in the same order per bin)
+#pragma unroll
+          for (int q = 0; q < ACC_TILE / 32; q++) {
+            if (!((qm >> q) & 1u)) continue;                       // warp-uniform
+            const int bin = lane + 32 * q;
+            const double *pp = pdata + bin;
+#pragma unroll 4
+            for (int i = 0; i < n; i++) {
+              const AccRec r = w.rec[warp][i];
+              if ((unsigned)(bin - (r.lanes & 255)) <= (unsigned)(r.lanes >> 8)) acc[q] = fma(r.k, __ldg(pp + r.addr0), acc[q]);
+            }
+          }
         }
         __syncwarp();
       }
