@@ -283,11 +283,11 @@ def rooflines(workload, k_ms, nsamp, nline_layers, nwn, nlayers, mb, hbm_peak, p
                          "ms": k_ms[name], "traffic": ncu_traffic(workload, name), "peak_source": peak_src,
                          "algorithmic_bytes": nbytes}
 
-    fp64("molext", "line sum, all kernels (k_kmax + k_linesum_fused + k_strength + k_accumulate)", samp_flop + pair_flop)
+    fp64("molext", "line sum, all kernels (k_kmax + k_linesum_fused_w + k_strength + k_accumulate)", samp_flop + pair_flop)
     fp64("strength", "k_strength", pair_flop * k_ms.get("_unfused_frac", 1.0),
          "reference work of the layers this kernel evaluates (2 exp + 12 flop per (line, layer)); the log-domain "
          "pretest executes far fewer instructions, so this is throughput in reference work, not pipe use")
-    fp64("fused", "k_linesum_fused (strength + gather of the narrow layers in one kernel)",
+    fp64("fused", "k_linesum_fused_w (strength + gather of the narrow layers in one kernel, a warp per 32 bins x 4 states)",
          pair_flop * (1.0 - k_ms.get("_unfused_frac", 1.0)) + 2.0 * k_ms.get("_fused_samples", 0.0))
     fp64("accumulate", "k_accumulate (wide + narrow instances)", 2.0 * k_ms.get("_unfused_samples", nsamp))
     if "accumulate" in out:

@@ -650,7 +650,7 @@ def run_c3(bench, args):
         c_exp = mb["dfma_tflops"] * 1e12 / (mb["dexp_gops"] * 1e9)
         flop = 2.0 * nsamp + (12.0 + 2.0 * c_exp) * nlines * ns            # SURVEY 8d, whole line sum of a step
         ach = flop / (float(np.mean(kms["molext"])) * 1e-3) / 1e12
-        line["roofline"] = {"kernel": "line sum, all kernels (k_kmax + k_linesum_fused + k_strength + k_accumulate)", "bound": "fp64",
+        line["roofline"] = {"kernel": "line sum, all kernels (k_kmax + k_linesum_fused_w + k_strength + k_accumulate)", "bound": "fp64",
                             "achieved": ach, "peak": mb["dfma_tflops"], "unit": "TFLOP/s", "frac": ach / mb["dfma_tflops"],
                             "traffic": None, "peak_source": "tb_microbench DFMA, measured in this run", "ms": float(np.mean(kms["molext"])),
                             "algorithmic_flop": flop, "c_exp_flop": c_exp}
