@@ -912,7 +912,10 @@ k_tau_eclipse(TauPar P, const double *__restrict__ e, const double *__restrict__
 // start carry the weight zero, so the loop is the same for the four rays.  Early exit, last[] and the zero
 // tail as in k_tau_transit.
 #define TAU_WL 2      // wavenumbers per lane of k_tau_w (a block owns 32 * TAU_WL columns)
-__global__ void __launch_bounds__(32 * TAU_NW, 4)
+// MINB = 4 (64 registers, 8 bytes spilled) puts a grid of up to 592 blocks -- C2: 490 -- on the machine in ONE wave
+// (0.090 -> 0.072 ms); a grid of many waves (C4, batches) runs the 80-register build at 3 blocks per SM.
+template <int MINB>
+__global__ void __launch_bounds__(32 * TAU_NW, MINB)
 k_tau_w(TauPar P, const double *__restrict__ e, const double *__restrict__ ecs,
         const double *__restrict__ press, const double *__restrict__ temp,
         const double *__restrict__ aux, const double *__restrict__ mol_d,
@@ -1116,10 +1119,12 @@ static int tb_tau_run(tb_ctx *c, int geometry, double toomuch, const double *h, 
     const size_t shm = (size_t)nrad * 32 * TAU_WL * sizeof(double);
     TB_REQUIRE(shm <= 200 * 1024, TB_ERR_ARG, "too many layers (%d) for the tau kernel's shared memory", nrad);
     if (c->tauw_shm_set != (int)shm) {
-      TB_CUDA(cudaFuncSetAttribute(k_tau_w, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
+      TB_CUDA(cudaFuncSetAttribute(k_tau_w<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
+      TB_CUDA(cudaFuncSetAttribute(k_tau_w<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
       c->tauw_shm_set = (int)shm;
     }
-    k_tau_w<<<nblk(ncol, 32 * TAU_WL), 32 * TAU_NW, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p, c->d_dens.p,
+    auto tauw = nblk(ncol, 32 * TAU_WL) <= 148 * 4 ? k_tau_w<4> : k_tau_w<3>;
+    tauw<<<nblk(ncol, 32 * TAU_WL), 32 * TAU_NW, shm, st>>>(P, c->d_e.p, c->d_ecs.p, c->d_p.p, c->d_t.p, c->d_es_aux.p, c->d_dens.p,
                                                     c->d_mol_pol.p, c->d_mol_mass.p, c->nmol, c->r_meta.p, c->r_par.p,
                                                     c->r_rcp.p, c->r_wg.p, c->r_w0.p, c->d_tau.p, c->d_last.p);
   } else {
@@ -1664,7 +1669,8 @@ extern "C" int tb_run_transit_batch(tb_ctx *c, int natm, const double *in, doubl
   }
   const size_t shm_tauw = (size_t)nrad * 32 * TAU_WL * sizeof(double);
   if (c->tauw_shm_set != (int)shm_tauw) {
-    TB_CUDA(cudaFuncSetAttribute(k_tau_w, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm_tauw));
+    TB_CUDA(cudaFuncSetAttribute(k_tau_w<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm_tauw));
+    TB_CUDA(cudaFuncSetAttribute(k_tau_w<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm_tauw));
     c->tauw_shm_set = (int)shm_tauw;
   }
   TB_REQUIRE(nh % TAU_RB == 0, TB_ERR_ARG, "tb_run_transit_batch: the layer count (%d) must be a multiple of %d", nh, TAU_RB);
@@ -1722,7 +1728,8 @@ extern "C" int tb_run_transit_batch(tb_ctx *c, int natm, const double *in, doubl
     TB_CUDA(cudaMemsetAsync(c->b_tau.p, 0, sizeof(double) * nvl * nwn, st));
     k_ray_geometry<<<nb * nh, 64, 0, st>>>(0, c->b_rad.p, nrad, c->am_rfct, c->b_ip.p, nh, c->am_rfct, stride, c->r_meta.p,
                                            c->r_par.p, c->r_coef.p, c->r_s.p, c->r_rcp.p, c->d_err.p, c->r_wg.p, c->r_w0.p);
-    k_tau_w<<<dim3(nblk(nwn, 32 * TAU_WL), nb), 32 * TAU_NW, shm_tauw, st>>>(P, c->b_e.p, c->b_ecs.p, c->b_p.p, c->b_traw.p, c->b_aux.p,
+    auto tauw = nblk(nwn, 32 * TAU_WL) * nb <= 148 * 4 ? k_tau_w<4> : k_tau_w<3>;
+    tauw<<<dim3(nblk(nwn, 32 * TAU_WL), nb), 32 * TAU_NW, shm_tauw, st>>>(P, c->b_e.p, c->b_ecs.p, c->b_p.p, c->b_traw.p, c->b_aux.p,
                                                                    c->b_dens.p, c->d_mol_pol.p, c->d_mol_mass.p, nmol,
                                                                    c->r_meta.p, c->r_par.p, c->r_rcp.p, c->r_wg.p, c->r_w0.p,
                                                                    c->b_tau.p, c->b_last.p);
