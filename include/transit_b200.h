@@ -143,6 +143,22 @@ int  tb_set_tau_streaming(tb_ctx *c, int on);
  * -1 = modulationm1 (slantpath.c:446-473, opaque disc at tau = toomuch); anything else is refused
  * with the reference's message.                                                          */
 int  tb_set_modlevel(tb_ctx *c, int level);
+/* tb_tau for transit geometry WITHOUT any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same kernels and results as tb_tau(TB_GEOM_TRANSIT) with scattering and clouds off; the scratch of the
+ * ray geometry (path coordinates, Simpson coefficients, the weight matrix of t = W er, error flags) lives in a
+ * file-scope `static __device__` array of TB_TAU_STATIC_SCRATCH_BYTES that every GPU loading the library holds until
+ * exit.  All pointers are DEVICE buffers of the caller: rad[nrad], h[nh] (impact parameters, top first), e[nrad][nwn],
+ * e_cs[nrad][nwn] (zeros if there is none), out tau[nh][nwn] (zero beyond last[], as tau.c:34 leaves it) and
+ * last[nwn] (int32).  nrad and nh beyond TB_TAU_STATIC_MAXLAYERS are refused with TB_ERR_ARG.  Work is enqueued on
+ * the context's stream; check != 0 reads the geometry's error flags back (one 16-byte copy + stream sync).  The
+ * array is shared by all calls on a device and keeps the last call's contents (the part a call uses is cleared
+ * first): calls that overlap on the GPU race on it -- serialise them.  Calls no cudaMalloc / cudaFree.        */
+#define TB_TAU_STATIC_MAXLAYERS 128
+#define TB_TAU_STATIC_SCRATCH_BYTES 544800
+int  tb_tau_transit_static(tb_ctx *c, int nrad, const double *d_rad, double rad_fct, int nh, const double *d_h,
+                           double hfct, int64_t nwn, const double *d_e, const double *d_ecs, double toomuch,
+                           double *d_tau, int32_t *d_last, int check);
 /* modulation/modulation1 (slantpath.c:274-436): out[nwn]                              */
 int  tb_modulation(tb_ctx *c, double starrad_cm, int transparent, double *out);
 /* eclipse_intens/emergent_intens/flux (eclipse.c:117-287): out[nwn] flux             */

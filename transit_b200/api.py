@@ -55,6 +55,8 @@ ABI = {
     "tb_set_narrow_reach": (C.c_int, [C.c_void_p, C.c_int]),
     "tb_set_fused_variant": (C.c_int, [C.c_void_p, C.c_int]),
     "tb_set_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_double]),
+    "tb_tau_transit_static": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_double, C.c_int, C.c_void_p, C.c_double,
+                                        C.c_int64, C.c_void_p, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_int]),
     "tb_set_trace": (C.c_int, [C.c_void_p, C.c_int]),
     "tb_get_fused_stats": (C.c_int, [C.c_void_p, i64p, i64p]),
     "tb_get_line_molIDs": (C.c_int, [C.c_void_p, i32p, i32p]),
@@ -261,6 +263,13 @@ class Context:
     def set_fused(self, on=1):
         """0: two-kernel path; 1/True: fused where the grid has >= 96 tiles; 2: fused on small grids too."""
         self._ck(self.lib.tb_set_fused(self.h, int(on)), "tb_set_fused")
+
+    def tau_transit_static(self, nrad, d_rad, rad_fct, nh, d_h, hfct, nwn, d_e, d_ecs, toomuch, d_tau, d_last, check=True):
+        """tb_tau_transit_static: every d_* is a DEVICE address (int) of a buffer the caller owns; nothing is allocated."""
+        self._ck(self.lib.tb_tau_transit_static(self.h, int(nrad), C.c_void_p(d_rad), float(rad_fct), int(nh),
+                                                C.c_void_p(d_h), float(hfct), int(nwn), C.c_void_p(d_e), C.c_void_p(d_ecs),
+                                                float(toomuch), C.c_void_p(d_tau), C.c_void_p(d_last), int(bool(check))),
+                 "tb_tau_transit_static")
 
     def set_rays(self, h, hfct):
         """Impact parameters tb_spectrum integrates along (None: the reversed radii, makeipsample with raddelt -1)."""

@@ -1753,3 +1753,102 @@ extern "C" int tb_run_transit_batch(tb_ctx *c, int natm, const double *in, doubl
   TB_REQUIRE(err[2] == 0, TB_ERR_DOMAIN, "less than 3 items for radial integration (slantpath.c:393-397)");
   return TB_OK;
 }
+
+// =============================================================== transit tau without any allocation
+//
+// tb_tau_transit_static: the transit optical depth t = W er (k_ray_geometry + k_tau_w, the kernels of tb_tau) for
+// callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+// It has no counterpart in the reference.  The ray geometry --
+// path coordinates, Simpson coefficients, the weight matrix W, the per-ray parabola constants, the error flags: the
+// scratch every call of tb_tau keeps in cudaMalloc'ed context buffers -- lives here in ONE file-scope device array of
+// fixed size: every GPU that loads the library holds TB_STATIC_SCRATCH_BYTES of it until the process exits.  Inputs
+// and outputs are the caller's device buffers.  The array is shared by every call on a device and keeps the last
+// call's contents: the part a call uses is cleared first, and calls that overlap on the GPU (two streams, two
+// contexts of one device) race on it -- the caller serialises them.
+#define TB_STATIC_MAXLAYERS 128            // most layers AND most rays of a call
+#define TB_STATIC_STRIDE (4 * ((TB_STATIC_MAXLAYERS + 2) / 2 + 1))
+#define TB_STATIC_NDBL ((size_t)TB_STATIC_MAXLAYERS * (TB_STATIC_MAXLAYERS + 3)      /* s     */ \
+                        + (size_t)TB_STATIC_MAXLAYERS * 4                            /* par   */ \
+                        + (size_t)TB_STATIC_MAXLAYERS * TB_STATIC_STRIDE             /* coef  */ \
+                        + (size_t)TB_STATIC_MAXLAYERS * 2                            /* rcp   */ \
+                        + (size_t)TB_STATIC_MAXLAYERS * TB_STATIC_MAXLAYERS          /* wg    */ \
+                        + (size_t)TB_STATIC_MAXLAYERS)                               /* w0    */
+#define TB_STATIC_NINT ((size_t)TB_STATIC_MAXLAYERS * 4 + 8)                         /* meta, err */
+#define TB_STATIC_SCRATCH_BYTES (TB_STATIC_NDBL * 8 + TB_STATIC_NINT * 4)
+static_assert(TB_STATIC_MAXLAYERS == TB_TAU_STATIC_MAXLAYERS && TB_STATIC_SCRATCH_BYTES == TB_TAU_STATIC_SCRATCH_BYTES,
+              "include/transit_b200.h states the limits of tb_tau_transit_static");
+static __device__ __align__(256) unsigned char tb_static_scratch[TB_STATIC_SCRATCH_BYTES];
+
+// In host code `tb_static_scratch` is a host-side stand-in, not a device address: the address a kernel can use comes
+// from cudaGetSymbolAddress, asked once per device with that device current.
+#define TB_STATIC_MAXDEV 64
+static unsigned char *tb_static_addr[TB_STATIC_MAXDEV];
+
+extern "C" int tb_tau_transit_static(tb_ctx *c, int nrad, const double *d_rad, double rad_fct, int nh,
+                                     const double *d_h, double hfct, int64_t nwn, const double *d_e,
+                                     const double *d_ecs, double toomuch, double *d_tau, int32_t *d_last, int check) {
+  TB_REQUIRE(c != nullptr, TB_ERR_ARG, "tb_tau_transit_static: no context");
+  TB_REQUIRE(d_rad && d_h && d_e && d_ecs && d_tau && d_last, TB_ERR_ARG,
+             "tb_tau_transit_static: rad, h, e, e_cs, tau and last are device buffers of the caller, none may be NULL");
+  TB_REQUIRE(nrad >= 2 && nrad <= TB_STATIC_MAXLAYERS, TB_ERR_ARG,
+             "tb_tau_transit_static: %d layers; the static scratch holds 2..%d (tb_tau has no such limit)", nrad,
+             TB_STATIC_MAXLAYERS);
+  TB_REQUIRE(nh >= 1 && nh <= TB_STATIC_MAXLAYERS, TB_ERR_ARG,
+             "tb_tau_transit_static: %d rays; the static scratch holds 1..%d (tb_tau has no such limit)", nh,
+             TB_STATIC_MAXLAYERS);
+  TB_REQUIRE(nwn >= 1 && nwn < ((int64_t)1 << 31), TB_ERR_ARG, "tb_tau_transit_static: %lld wavenumbers", (long long)nwn);
+  TB_REQUIRE(c->device >= 0 && c->device < TB_STATIC_MAXDEV, TB_ERR_ARG, "tb_tau_transit_static: device %d", c->device);
+  TB_CUDA(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  if (!tb_static_addr[c->device]) {            // once per device, that device current
+    unsigned char *ptr = nullptr;
+    TB_CUDA(cudaGetSymbolAddress((void **)&ptr, tb_static_scratch));
+    TB_REQUIRE(ptr != nullptr, TB_ERR_CUDA, "tb_tau_transit_static: no device address for the static scratch");
+    tb_static_addr[c->device] = ptr;
+  }
+  // ---- carve-up of the array (doubles first: every part stays 8-byte aligned)
+  const int stride = 4 * ((nrad + 2) / 2 + 1);
+  const int ngrp = (nh + TAU_RB - 1) / TAU_RB;
+  double *dbl = reinterpret_cast<double *>(tb_static_addr[c->device]);
+  double *s_s = dbl;                                  dbl += (size_t)nh * (nrad + 3);
+  double *s_par = dbl;                                dbl += (size_t)nh * 4;
+  double *s_coef = dbl;                               dbl += (size_t)nh * stride;
+  double *s_rcp = dbl;                                dbl += (size_t)nh * 2;
+  double *s_wg = dbl;                                 dbl += (size_t)ngrp * nrad * TAU_RB;
+  double *s_w0 = dbl;                                 dbl += nh;
+  int32_t *s_meta = reinterpret_cast<int32_t *>(dbl);
+  int32_t *s_err = s_meta + (size_t)nh * 4;
+  const size_t used = (size_t)(reinterpret_cast<unsigned char *>(s_err + 8) - tb_static_addr[c->device]);
+  TB_REQUIRE(used <= TB_STATIC_SCRATCH_BYTES, TB_ERR_ARG, "tb_tau_transit_static: internal: scratch carve-up too large");
+  // the array keeps the last call's contents: error flags, the weights of the rays a ragged last group of four
+  // does not have, and everything else this call will read start from zero
+  TB_CUDA(cudaMemsetAsync(tb_static_addr[c->device], 0, used, st));
+  TB_CUDA(cudaMemsetAsync(d_tau, 0, sizeof(double) * (size_t)nh * nwn, st));   // calloc, tau.c:34: zero beyond last[]
+  k_ray_geometry<<<nh, 64, 0, st>>>(0, d_rad, nrad, rad_fct, d_h, nh, hfct, stride, s_meta, s_par, s_coef, s_s, s_rcp,
+                                    s_err, s_wg, s_w0);
+  TauPar P;
+  memset(&P, 0, sizeof(P));
+  P.eclipse = 0; P.nrad = nrad; P.nh = nh; P.stride = stride; P.nwn = nwn; P.w0 = 0; P.w1 = nwn;
+  P.rfct = rad_fct; P.toomuch = toomuch; P.wn_i = 0; P.wn_d = 0; P.wn_fct = 1;
+  P.sc_flag = 0; P.cl_flag = 0;                      // no scattering, no cloud: the caller folds them into e
+  const size_t shm = (size_t)nrad * 32 * TAU_WL * sizeof(double);
+  const bool one_wave = nblk(nwn, 32 * TAU_WL) <= 148 * 4;
+  auto tauw = one_wave ? k_tau_w<4> : k_tau_w<3>;
+  {  // the dynamic shared memory limit of the kernel is per device and shared with tb_tau's launches: raise, never lower
+    cudaFuncAttributes fa;
+    TB_CUDA(cudaFuncGetAttributes(&fa, tauw));
+    if ((size_t)fa.maxDynamicSharedSizeBytes < shm)
+      TB_CUDA(cudaFuncSetAttribute(tauw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
+  }
+  tauw<<<nblk(nwn, 32 * TAU_WL), 32 * TAU_NW, shm, st>>>(P, d_e, d_ecs, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                                                        0, s_meta, s_par, s_rcp, s_wg, s_w0, d_tau, d_last);
+  c->launches += 2;
+  TB_CUDA(cudaGetLastError());
+  if (check) {                                       // the geometry's error flags, one small copy and a sync of the stream
+    int32_t err[4];
+    TB_CUDA(cudaMemcpyAsync(err, s_err, sizeof(err), cudaMemcpyDeviceToHost, st));
+    TB_CUDA(cudaStreamSynchronize(st));
+    TB_REQUIRE(err[1] == 0, TB_ERR_DOMAIN, "a ray's closest approach lies below the bottom layer (slantpath.c:40-44)");
+  }
+  return TB_OK;
+}
