@@ -233,6 +233,7 @@ struct tb_ctx {
   DevBuf<double> s_facz, s_rtemp, s_ral, s_xterm, s_lcz;
   DevBuf<LineRec> s_rec;      // [state][group]
   DevBuf<int32_t> s_fclass, s_fP, s_lastq2;   // s_lastq2: carried-index source of the fused states (k_lastq_scan)
+  bool kmax_block_skip = false;  // tb_upload_lines: no negative energies / gf, k_kmax may leave whole blocks
   int fuse_rmax = 8;
   int fuse_variant = 1;          // 0: k_linesum_fused, 1: k_linesum_fused_w
   int narrow_r = 2;              // NARROW_R of tb_lines.cu

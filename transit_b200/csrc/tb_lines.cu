@@ -244,6 +244,12 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
       lastwl[isoid[i]] = wl[i];
     }
   }
+  {  // k_kmax leaves whole blocks of its strength-ordered list when their strongest line cannot raise a maximum: that
+     // bound needs both exponential factors <= 1, i.e. no negative lower-state energy (and no negative gf or factor)
+    bool plain = efct > 0;
+    for (int64_t i = 0; i < n && plain; i++) plain = elow[i] >= 0 && gf[i] >= 0 && wl[i] > 0;
+    c->kmax_block_skip = plain;
+  }
   cudaStream_t st = c->stream;
   c->nlines = n; c->wfct = wfct; c->efct = efct;
   c->have_lines = false;
@@ -491,7 +497,7 @@ __global__ void k_kmax(int64_t l0, int64_t l1, int ns, int niso, const double *_
                        const double *__restrict__ q_a, const double *__restrict__ q_w,
                        const int16_t *__restrict__ q_iso, const double *__restrict__ rtemp,
                        const double *__restrict__ Z, const double *__restrict__ iso_mass,
-                       const int *__restrict__ iso_row, int permol, int nrows, double *kmax) {
+                       const int *__restrict__ iso_row, int permol, int nrows, double *kmax, int block_skip) {
   // the running maxima are read once per block (not per warp: every warp of the chip asking
   // one L2 slice for the same sector serialises there) and merged back once per block
   __shared__ unsigned long long sh_cur[SB][KMAX_ROWS], sh_new[SB][KMAX_ROWS];
@@ -511,12 +517,24 @@ __global__ void k_kmax(int64_t l0, int64_t l1, int ns, int niso, const double *_
     }
     __syncthreads();
     if (use_thr) {
+      // The list is in descending order of key = g/mass, and a line's strength is at most key/z (both exponential
+      // factors are <= 1, every rounding monotone).  If the key of the block's FIRST line is below
+      // (1-1e-9)*cur*z for every (state, isotope) of the block, no line of the block -- nor of any later block --
+      // can raise a maximum: the block leaves before reading its lines (1e-9: ten million times the rounding of
+      // the two products and the division).  The maxima stay exact; only the work depends on it.
+      __shared__ int sh_stay;
+      const int64_t lf = l0 + (int64_t)blockIdx.x * LPT * blockDim.x;
+      const double key0 = (block_skip && lf < l1) ? q_g[lf] / iso_mass[q_iso[lf]] : INFINITY;
+      if (threadIdx.x == 0) sh_stay = 0;
+      __syncthreads();
       for (int i = threadIdx.x; i < SB * niso; i += blockDim.x) {
         const int k = i / niso, iso = i % niso, s = s0 + k;
         const double cur = __longlong_as_double((long long)sh_cur[k][permol ? iso_row[iso] : 0]);
         sh_thr[k][iso] = s < ns ? 0.9999999999 * cur * iso_mass[iso] * Z[s * niso + iso] : 0.0;
+        if (s < ns && !(key0 < 0.999999999 * cur * Z[s * niso + iso])) sh_stay = 1;
       }
       __syncthreads();
+      if (!sh_stay) return;
     }
   }
 #pragma unroll 1
@@ -1913,7 +1931,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
         // (one line per thread: the seed is 16 384 lines, eight per thread would leave it 200 blocks for 148 SMs)
         k_kmax<SB, 1><<<dim3(nblk(seed, Tn), (cs + SB - 1) / SB), Tn, 0, st>>>(
             0, seed, cs, niso, c->q_g.p, c->q_a.p, c->q_w.p, c->q_iso.p, c->s_rtemp.p, c->s_Z.p, c->d_iso_mass.p,
-            c->d_iso_row.p, permol, nrows, c->s_kmax.p);
+            c->d_iso_row.p, permol, nrows, c->s_kmax.p, c->kmax_block_skip ? 1 : 0);
       // the bulk is split over the ranks of a sharded run (every rank ran the seed, so every
       // rank skips alike); the exact maximum is completed by the all-reduce below
       const int64_t per = (Mq - seed + c->shard_world - 1) / c->shard_world;
@@ -1921,7 +1939,7 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       if (q1 > q0)
         k_kmax<SBB><<<dim3(nblk(q1 - q0, Tn * KMAX_LPT), (cs + SBB - 1) / SBB), Tn, 0, st>>>(
             q0, q1, cs, niso, c->q_g.p, c->q_a.p, c->q_w.p, c->q_iso.p, c->s_rtemp.p, c->s_Z.p, c->d_iso_mass.p,
-            c->d_iso_row.p, permol, nrows, c->s_kmax.p);
+            c->d_iso_row.p, permol, nrows, c->s_kmax.p, c->kmax_block_skip ? 1 : 0);
       TB_LAUNCHED(c);
       if (c->shard_world > 1) {
         if (c->exch)
