@@ -113,6 +113,9 @@ int  tb_opacity_load(tb_ctx *c, int64_t Nmol, int64_t Ntemp, int64_t Nlayer, int
                      const int *molID, const double *temp, const double *press,
                      const double *grid);
 /* interpolmolext for every layer (extinction.c:534-581)                               */
+/* one grid in HBM for several contexts of ONE GPU (replaces shareopacity / the SysV segment, opacity.c:89-201,507-630):
+ * dst reads src's grid in place; src must keep its grid for as long as dst uses it                          */
+int  tb_opacity_share(tb_ctx *dst, tb_ctx *src);
 int  tb_extinction_interp(tb_ctx *c);
 
 /* readcs tables (crosssec.c:9-268) and interpcs/bicubicinterpolate (crosssec.c:271-428) */

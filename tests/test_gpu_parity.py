@@ -430,6 +430,18 @@ def test_opacity_grid_build_and_interp_vs_reference(golden):
                      d["rerun_mol_d"], d["rerun_iso_z"])
     out = c.spectrum(api.GEOM_TRANSIT, prob.toomuch, prob.ethresh, prob.starrad, prob.transp)
     assert relerr(out, d["rerun_out"]) < SPEC_RTOL
+    # a second context of the same GPU reads the first one's grid in place (tb_opacity_share: no copy, no line list)
+    c2 = setup_ctx(prob, d, lines=False)
+    with pytest.raises(api.TransitError, match="holds no opacity grid"):
+        c.opacity_share(c2)
+    c2.opacity_share(c)
+    c2.set_atmosphere(d["rerun_rad_v"], prob.rad_fct, prob.p, prob.p_fct, d["rerun_atm_t"], prob.t_fct,
+                      d["rerun_mol_d"], d["rerun_iso_z"])
+    out2 = c2.spectrum(api.GEOM_TRANSIT, prob.toomuch, prob.ethresh, prob.starrad, prob.transp)
+    assert np.array_equal(out2, out)
+    c2.close()                                     # the borrower goes first and frees nothing of the owner's
+    out3 = c.spectrum(api.GEOM_TRANSIT, prob.toomuch, prob.ethresh, prob.starrad, prob.transp)
+    assert np.array_equal(out3, out)
     c.close()
 
 

@@ -55,6 +55,7 @@ ABI = {
     "tb_set_narrow_reach": (C.c_int, [C.c_void_p, C.c_int]),
     "tb_set_fused_variant": (C.c_int, [C.c_void_p, C.c_int]),
     "tb_set_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_double]),
+    "tb_opacity_share": (C.c_int, [C.c_void_p, C.c_void_p]),
     "tb_tau_transit_static": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_double, C.c_int, C.c_void_p, C.c_double,
                                         C.c_int64, C.c_void_p, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_int]),
     "tb_set_trace": (C.c_int, [C.c_void_p, C.c_int]),
@@ -270,6 +271,10 @@ class Context:
                                                 C.c_void_p(d_h), float(hfct), int(nwn), C.c_void_p(d_e), C.c_void_p(d_ecs),
                                                 float(toomuch), C.c_void_p(d_tau), C.c_void_p(d_last), int(bool(check))),
                  "tb_tau_transit_static")
+
+    def opacity_share(self, src):
+        """Read the opacity grid of another context of the same GPU in place (no copy)."""
+        self._ck(self.lib.tb_opacity_share(self.h, src.h), "tb_opacity_share")
 
     def set_rays(self, h, hfct):
         """Impact parameters tb_spectrum integrates along (None: the reversed radii, makeipsample with raddelt -1)."""

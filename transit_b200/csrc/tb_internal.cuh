@@ -60,9 +60,15 @@ struct DevBuf {
   DevBuf(const DevBuf &) = delete;
   DevBuf &operator=(const DevBuf &) = delete;
   ~DevBuf() { release(); }
+  bool owned = true;           // false: p belongs to another context's buffer (borrow), never freed here
+  void borrow(T *q, size_t m) {
+    release();
+    p = q; n = m; owned = false;
+  }
   int ensure(size_t want) {
-    if (want <= n && p) return TB_OK;
-    if (p) cudaFree(p);
+    if (want <= n && p && owned) return TB_OK;
+    if (p && owned) cudaFree(p);
+    owned = true;
     p = nullptr;
     n = 0;
     if (want == 0) return TB_OK;
@@ -75,9 +81,10 @@ struct DevBuf {
     return TB_OK;
   }
   void release() {
-    if (p) cudaFree(p);
+    if (p && owned) cudaFree(p);
     p = nullptr;
     n = 0;
+    owned = true;
   }
 };
 

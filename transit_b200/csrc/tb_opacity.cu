@@ -36,6 +36,31 @@ extern "C" int tb_opacity_load(tb_ctx *c, int64_t Nmol, int64_t Ntemp, int64_t N
 }
 
 
+// One grid in HBM for several contexts of a GPU (what the reference's SysV shared-memory scheme,
+// opacity.c:89-201,507-630, does between processes): dst reads src's grid in place -- no second copy of a 2.6 GB
+// grid per retrieval thread.  The grid is read-only after tb_opacity_load; src must outlive dst's use of it (a grid
+// loaded again into src, or src destroyed, leaves dst with a dangling pointer: call tb_opacity_share again).
+extern "C" int tb_opacity_share(tb_ctx *dst, tb_ctx *src) {
+  TB_REQUIRE(dst && src && dst != src, TB_ERR_ARG, "tb_opacity_share: two different contexts");
+  TB_REQUIRE(src->have_grid_o && src->d_grid.p, TB_ERR_STATE, "tb_opacity_share: the source context holds no opacity grid");
+  TB_REQUIRE(dst->device == src->device, TB_ERR_ARG, "tb_opacity_share: contexts on devices %d and %d", dst->device, src->device);
+  TB_REQUIRE(dst->have_grid && dst->have_species, TB_ERR_STATE, "grid and species must be set before tb_opacity_share");
+  TB_REQUIRE(dst->nwn == src->gNwave, TB_ERR_ARG, "tb_opacity_share: the grid has %lld wavenumbers, the problem %lld",
+             (long long)src->gNwave, (long long)dst->nwn);
+  std::vector<int> idx(src->gNmol, -1);
+  for (int m = 0; m < src->gNmol; m++) {
+    for (int k = 0; k < dst->nmol; k++)
+      if (dst->mol_ID[k] == src->gmolID[m]) { idx[m] = k; break; }
+    TB_REQUIRE(idx[m] >= 0, TB_ERR_ARG, "opacity-grid molecule ID %d is not in the atmosphere", src->gmolID[m]);
+  }
+  dst->gNmol = src->gNmol; dst->gNtemp = src->gNtemp; dst->gNlayer = src->gNlayer; dst->gNwave = src->gNwave;
+  dst->gtemp = src->gtemp; dst->gpress = src->gpress; dst->gmolID = src->gmolID;
+  dst->gmol_idx = idx;
+  dst->d_grid.borrow(src->d_grid.p, src->d_grid.n);
+  dst->have_grid_o = true;
+  return TB_OK;
+}
+
 // extinction.c:568-578: e[r][w] = sum_m rho_m[r] * (o_lo*(T+ - T) + o_hi*(T - T-))/(T+ - T-)
 // A batch of atmospheres (tb_batch.cu) is nrad*natm "virtual layers": virtual layer v = a*ngrid + r reads the grid
 // planes of layer r = v % ngrid with its own temperature bracket and densities; rho[Nmol][nrad], e[nrad][nwn].
