@@ -1934,14 +1934,18 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
             c->d_iso_row.p, permol, nrows, c->s_kmax.p, c->kmax_block_skip ? 1 : 0);
       // the bulk is split over the ranks of a sharded run (every rank ran the seed, so every
       // rank skips alike); the exact maximum is completed by the all-reduce below
-      const int64_t per = (Mq - seed + c->shard_world - 1) / c->shard_world;
-      const int64_t q0 = seed + per * c->shard_rank, q1 = q0 + per < Mq ? q0 + per : Mq;
+      // (with the block skip of k_kmax the whole bulk costs ~0.04 ms: a rank of a library-sharded run then walks it all
+      // itself and needs no all-reduce -- one rendez-vous of the ranks less per spectrum, the same exact maxima)
+      const bool kmax_local = c->shard_world > 1 && !c->exch && c->kmax_block_skip;
+      const int kw = kmax_local ? 1 : c->shard_world, kr = kmax_local ? 0 : c->shard_rank;
+      const int64_t per = (Mq - seed + kw - 1) / kw;
+      const int64_t q0 = seed + per * kr, q1 = q0 + per < Mq ? q0 + per : Mq;
       if (q1 > q0)
         k_kmax<SBB><<<dim3(nblk(q1 - q0, Tn * KMAX_LPT), (cs + SBB - 1) / SBB), Tn, 0, st>>>(
             q0, q1, cs, niso, c->q_g.p, c->q_a.p, c->q_w.p, c->q_iso.p, c->s_rtemp.p, c->s_Z.p, c->d_iso_mass.p,
             c->d_iso_row.p, permol, nrows, c->s_kmax.p, c->kmax_block_skip ? 1 : 0);
       TB_LAUNCHED(c);
-      if (c->shard_world > 1) {
+      if (c->shard_world > 1 && !kmax_local) {
         if (c->exch)
           TB_REQUIRE(c->exch(c->exch_user, TB_EXCH_KMAX, c->s_kmax.p, (int64_t)cs * nrows) == 0, TB_ERR_STATE,
                      "exchange callback failed (strength maxima)");
