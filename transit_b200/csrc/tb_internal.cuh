@@ -203,6 +203,7 @@ struct tb_ctx {
   tb_exchange_fn exch = nullptr;
   void *exch_user = nullptr;
   std::vector<int32_t> h_binstart;    // host copy of binstart (group ranges of a band)
+  std::vector<int64_t> h_xr_key, h_xr; // co-added member ranges of the band's groups per row (k_extra), keyed by (pa, pb)
   // in-library exchange of a band-sharded run (tb_comm.cu): NCCL communicator, band table, gather staging
   void *comm = nullptr;
   int comm_rank = 0, comm_world = 1;

@@ -254,6 +254,7 @@ extern "C" int tb_upload_lines(tb_ctx *c, const double *wl, const double *elow, 
   c->nlines = n; c->wfct = wfct; c->efct = efct;
   c->have_lines = false;
   c->h_binstart.clear();
+  c->h_xr_key.clear();
   c->G = c->M = c->Mq = 0;
   const int64_t nkeys = (int64_t)c->nrows * c->nwn;
   TB_TRY(c->binstart.ensure(nkeys + 1));
@@ -580,18 +581,21 @@ __global__ void k_kmax(int64_t l0, int64_t l1, int ns, int niso, const double *_
 // gf*exp(-E/T)*(1-exp(-w/T)) are evaluated here, one thread per (member, state), so that
 // k_strength's member loop is loads and adds only (a divergent loop with two exp() in it
 // costs every warp the full price for one busy lane).
-__global__ void k_extra(int64_t X, int ns, const int32_t *__restrict__ x_line,
+// (one definition for k_extra and k_lastq_scan: the same instructions, the same bits)
+__device__ __forceinline__ double tb_member_term(int l, double rT, double efct, const double *__restrict__ m_wavn,
+                                                 const double *__restrict__ m_elow, const double *__restrict__ m_gf) {
+  const double a = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
+  return __dmul_rn(__dmul_rn(m_gf[l], tb_exp(a * rT)), (1 - tb_exp(__dmul_rn(-TB_EXPCTE, m_wavn[l]) * rT)));
+}
+// members x0 <= x < x1 (a band shard: only the members of the groups that can reach the band)
+__global__ void k_extra(int64_t X, int64_t x0, int64_t x1, int ns, const int32_t *__restrict__ x_line,
                         const double *__restrict__ m_wavn, const double *__restrict__ m_elow,
                         const double *__restrict__ m_gf, const double *__restrict__ rtemp, double efct,
                         double *__restrict__ xterm) {
-  const int64_t x = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t x = x0 + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   const int s = blockIdx.y;
-  if (x >= X) return;
-  const int l = x_line[x];
-  const double rT = rtemp[s];
-  const double a = __dmul_rn(__dmul_rn(-TB_EXPCTE, efct), m_elow[l]);
-  xterm[(size_t)s * X + x] =
-      __dmul_rn(__dmul_rn(m_gf[l], tb_exp(a * rT)), (1 - tb_exp(__dmul_rn(-TB_EXPCTE, m_wavn[l]) * rT)));
+  if (x >= x1) return;
+  xterm[(size_t)s * X + x] = tb_member_term(x_line[x], rtemp[s], efct, m_wavn, m_elow, m_gf);
 }
 
 // log-domain threshold offsets: lcz[s][iso] = log(facz) - log(ethresh*kmax[s][row(iso)]).  A lone
@@ -1177,6 +1181,20 @@ __device__ __forceinline__ bool tb_group_evaluated(int q, size_t sX, double rT, 
   for (int l = b + 1; l < e; l++) a = __dadd_rn(a, xterm[sX + (l - q - 1)]);
   return !(__dmul_rn(a, fz) < thr);
 }
+// ... with the co-added members' terms evaluated here (k_extra's expression) instead of read from xterm: k_lastq_scan
+// looks at groups anywhere in the list, a band shard's k_extra only fills the members its own groups need
+__device__ __forceinline__ bool tb_group_evaluated_x(int q, double rT, double fz, double thr, double efct,
+                                                     const int32_t *__restrict__ g_start, const double *__restrict__ g_gf,
+                                                     const double *__restrict__ g_a0, const double *__restrict__ g_wavn,
+                                                     const int32_t *__restrict__ x_line, const double *__restrict__ m_wavn,
+                                                     const double *__restrict__ m_elow, const double *__restrict__ m_gf) {
+  const int b = g_start[q], e = g_start[q + 1];
+  const double ge1 = __dmul_rn(g_gf[q], tb_exp(g_a0[q] * rT));
+  if ((e - b == 1) && ge1 * fz < 0.999999 * thr) return false;
+  double a = __dmul_rn(ge1, (1 - tb_exp(__dmul_rn(-TB_EXPCTE, g_wavn[q]) * rT)));
+  for (int l = b + 1; l < e; l++) a = __dadd_rn(a, tb_member_term(x_line[l - q - 1], rT, efct, m_wavn, m_elow, m_gf));
+  return !(__dmul_rn(a, fz) < thr);
+}
 
 // The carried Doppler index without walking the list (extinction.c:480-483): per (state, isotope) the reference
 // leaves, for the lines that do not refresh it, the index of the LAST line in file order that did refresh it and
@@ -1197,7 +1215,8 @@ k_lastq_scan(int ns, int niso, int nrows, int permol, double ethresh, double wn_
              const double *__restrict__ rtemp, const double *__restrict__ facz, const double *__restrict__ lcz,
              const double *__restrict__ kmax, const int *__restrict__ iso_row,
              const double *__restrict__ alphal, const double *__restrict__ alphad,
-             const double *__restrict__ ral, const double *__restrict__ xterm, int64_t X,
+             const double *__restrict__ ral, const int32_t *__restrict__ x_line, const double *__restrict__ m_wavn,
+             const double *__restrict__ m_elow, const double *__restrict__ m_gf, double efct,
              const int32_t *__restrict__ fclass, int all, int32_t *lastq /* preset to -1 */) {
   const int pair = blockIdx.x, s = pair / niso, iso = pair % niso;      // (x: up to 2^31 pairs; y: the chunk dealer)
   if (!all && !fclass[s / FB]) return;           // (else) k_strength finds it for the states it evaluates
@@ -1224,7 +1243,7 @@ k_lastq_scan(int ns, int niso, int nrows, int permol, double ethresh, double wn_
     if (og >= og0) {
       const int q = go_pos[og];
       if (!(fma(g_a0[q], rT, g_lg[q] + lz) < -1e-9) &&
-          tb_group_evaluated(q, (size_t)s * X, rT, fz, thr, g_start, g_gf, g_a0, g_wavn, xterm))
+          tb_group_evaluated_x(q, rT, fz, thr, efct, g_start, g_gf, g_a0, g_wavn, x_line, m_wavn, m_elow, m_gf))
         atomicMax(&sh_best, og);
     }
     __syncthreads();
@@ -1953,10 +1972,33 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
       }
       tb_timer_end(c, "kmax");
       tb_timer_begin(c, "strength");
-      if (X > 0) {
-        k_extra<<<dim3(nblk(X, Tn), cs), Tn, 0, st>>>(X, cs, c->x_line.p, c->m_wavn.p, c->m_elow.p, c->m_gf.p,
+      if (X > 0 && !banded) {
+        k_extra<<<dim3(nblk(X, Tn), cs), Tn, 0, st>>>(X, 0, X, cs, c->x_line.p, c->m_wavn.p, c->m_elow.p, c->m_gf.p,
                                                       c->s_rtemp.p, c->efct, c->s_xterm.p);
         TB_LAUNCHED(c);
+      } else if (X > 0) {
+        // a band shard: the members of the groups [pa, pb) of every row are x in [g_start[pa] - pa, g_start[pb] - pb)
+        // (the four numbers per row are read back once per band table)
+        std::vector<int64_t> key;
+        for (int r = 0; r < nrows; r++) { key.push_back(pa[r]); key.push_back(pb[r]); }
+        if (key != c->h_xr_key) {
+          std::vector<int32_t> gs(2 * (size_t)nrows, 0);
+          for (int r = 0; r < nrows; r++) {
+            TB_CUDA(cudaMemcpyAsync(&gs[2 * r], c->g_start.p + pa[r], sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+            TB_CUDA(cudaMemcpyAsync(&gs[2 * r + 1], c->g_start.p + pb[r], sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+          }
+          TB_CUDA(cudaStreamSynchronize(st));
+          c->h_xr.assign(2 * (size_t)nrows, 0);
+          for (int r = 0; r < nrows; r++) { c->h_xr[2 * r] = gs[2 * r] - pa[r]; c->h_xr[2 * r + 1] = gs[2 * r + 1] - pb[r]; }
+          c->h_xr_key = key;
+        }
+        for (int r = 0; r < nrows; r++) {
+          const int64_t x0 = c->h_xr[2 * r], x1 = c->h_xr[2 * r + 1];
+          if (x1 <= x0) continue;
+          k_extra<<<dim3(nblk(x1 - x0, Tn), cs), Tn, 0, st>>>(X, x0, x1, cs, c->x_line.p, c->m_wavn.p, c->m_elow.p, c->m_gf.p,
+                                                            c->s_rtemp.p, c->efct, c->s_xterm.p);
+          TB_LAUNCHED(c);
+        }
       }
       k_logthr<<<nblk((int64_t)cs * niso, 128), 128, 0, st>>>(cs, niso, nrows, permol, ethresh, c->d_iso_row.p,
                                                               c->s_facz.p, c->s_kmax.p, c->s_lcz.p);
@@ -1973,7 +2015,8 @@ int tb_states_run(tb_ctx *c, int ns, const double *T, const double *dens, const 
         k_lastq_scan<<<dim3(cs * niso, LASTQ_NB), 256, 0, st>>>(
             cs, niso, nrows, permol, ethresh, c->wn_i, c->iso_og0.p, c->iso_og1.p, c->go_pos.p, c->go_wavn.p, c->g_start.p,
             c->g_gf.p, c->g_a0.p, c->g_lg.p, c->g_wavn.p, c->s_rtemp.p, c->s_facz.p, c->s_lcz.p, c->s_kmax.p,
-            c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ral.p, c->s_xterm.p, X, c->s_fclass.p, scan_all ? 1 : 0,
+            c->d_iso_row.p, c->s_alphal.p, c->s_alphad.p, c->s_ral.p, c->x_line.p, c->m_wavn.p, c->m_elow.p, c->m_gf.p,
+            c->efct, c->s_fclass.p, scan_all ? 1 : 0,
             c->s_lastq2.p);
         TB_LAUNCHED(c);
       }
